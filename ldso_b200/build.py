@@ -1,0 +1,73 @@
+"""Build script: compiles libldso_gpu.so (sm_100a) in-tree and, for the tests / CPU baseline, the oracle.
+
+Usage: python -m ldso_b200.build [--force]
+"""
+import glob
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "ldso_b200", "csrc")
+LIBDIR = os.path.join(ROOT, "ldso_b200", "lib")
+GPU_LIB = os.path.join(LIBDIR, "libldso_gpu.so")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "liboracle.so")            # strict IEEE (-ffp-contract=off): the parity checker
+ORACLE_FAST_LIB = os.path.join(ORACLE_DIR, "liboracle_fast.so")  # -O3 with contraction: the timed CPU baseline
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "--expt-relaxed-constexpr",
+]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+        raise RuntimeError("build failed: " + cmd[0])
+    return r.stdout + r.stderr
+
+
+def build_gpu(force=False, verbose=False):
+    os.makedirs(LIBDIR, exist_ok=True)
+    srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
+        glob.glob(os.path.join(ROOT, "include", "*.h"))
+    if not force and _newer(GPU_LIB, deps):
+        return GPU_LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", GPU_LIB] + srcs
+    out = _run(cmd)
+    if verbose:
+        print(out)
+    return GPU_LIB
+
+
+def build_oracle(force=False):
+    srcs = sorted(glob.glob(os.path.join(ORACLE_DIR, "*.cpp")))
+    deps = srcs + glob.glob(os.path.join(ORACLE_DIR, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    common = ["g++", "-std=c++17", "-O3", "-march=x86-64-v3", "-DENABLE_SSE", "-fPIC", "-shared", "-pthread",
+              "-Wall", "-Wno-unused-function", "-Wno-unused-variable"]
+    if force or not _newer(ORACLE_LIB, deps):
+        _run(common + ["-ffp-contract=off", "-o", ORACLE_LIB] + srcs)
+    if force or not _newer(ORACLE_FAST_LIB, deps):
+        _run(common + ["-o", ORACLE_FAST_LIB] + srcs)
+    return ORACLE_LIB
+
+
+def build_all(force=False, verbose=False):
+    build_gpu(force, verbose)
+    build_oracle(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    print("built", GPU_LIB, ORACLE_LIB)

@@ -1,0 +1,218 @@
+"""ctypes binding of the C ABI declared in include/ldso_gpu.h.
+
+`load()` opens ldso_b200/lib/libldso_gpu.so and FAILS LOUDLY when it is missing: there is no CPU
+fallback anywhere in this package.  The `Api` class is prefix-agnostic so that the test-suite can drive
+a second library with the same signatures under another symbol prefix through the very same harness.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+GPU_LIB = os.path.join(ROOT, "lib", "libldso_gpu.so")
+
+MAX_LEVELS = 6
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("w", C.c_int), ("h", C.c_int),
+        ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+        ("device", C.c_int), ("n_frame_slots", C.c_int),
+        ("max_points", C.c_int), ("max_immature", C.c_int), ("max_residuals", C.c_int),
+        ("huber_th", C.c_float), ("coarse_cutoff_th", C.c_float), ("gamma_weights_pixel_select", C.c_int),
+        ("affine_opt_mode_a", C.c_float), ("affine_opt_mode_b", C.c_float),
+        ("outlier_th", C.c_float), ("outlier_th_sum_component", C.c_float), ("overall_energy_th_weight", C.c_float),
+        ("max_pix_search", C.c_float), ("trace_stepsize", C.c_float), ("trace_gn_iterations", C.c_int),
+        ("trace_gn_threshold", C.c_float), ("trace_extra_slack_on_th", C.c_float), ("trace_slack_interval", C.c_float),
+        ("trace_min_improvement", C.c_float), ("min_trace_test_radius", C.c_int),
+        ("min_grad_hist_cut", C.c_float), ("min_grad_hist_add", C.c_float), ("grad_downweight_per_level", C.c_float),
+        ("select_direction_distribution", C.c_int),
+        ("idepth_fix_prior", C.c_float), ("min_idepth_h_act", C.c_float), ("gn_its_on_point_activation", C.c_int),
+        ("frame_energy_th_n", C.c_float), ("frame_energy_th_fac_median", C.c_float),
+        ("frame_energy_th_const_weight", C.c_float),
+        ("tracker_solve_mode", C.c_int),
+        ("reserved", C.c_int * 8),
+    ]
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int)) if a is not None else None
+
+
+def f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class LdsoError(RuntimeError):
+    pass
+
+
+class Api:
+    """One loaded library exporting the ABI of include/ldso_gpu.h under symbol prefix `prefix`."""
+
+    def __init__(self, path, prefix):
+        if not os.path.exists(path):
+            raise LdsoError(f"{path} is missing — build it first (python -m ldso_b200.build); there is no fallback path")
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self.path = path
+        f = self.fn
+        f("default_config").restype = None
+        f("create").argtypes = [C.POINTER(Config), C.POINTER(C.c_void_p)]
+        f("destroy").argtypes = [C.c_void_p]
+        f("destroy").restype = None
+        f("last_error").argtypes = [C.c_void_p]
+        f("last_error").restype = C.c_char_p
+        f("launch_count").argtypes = [C.c_void_p]
+        f("launch_count").restype = C.c_longlong
+
+    def fn(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def default_config(self, **kw):
+        cfg = Config()
+        self.fn("default_config")(C.byref(cfg))
+        for k, v in kw.items():
+            setattr(cfg, k, v)
+        return cfg
+
+    def create(self, cfg):
+        return Ctx(self, cfg)
+
+
+class Ctx:
+    """One sequence context.  Thin, one method per C entry point."""
+
+    def __init__(self, api, cfg):
+        self.api = api
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        rc = api.fn("create")(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            msg = api.fn("last_error")(self.h).decode() if self.h else "?"
+            if self.h:
+                api.fn("destroy")(self.h)
+                self.h = None
+            raise LdsoError(f"{api.prefix}create failed rc={rc}: {msg}")
+        self.levels = api.fn("pyr_levels")(self.h)
+        self.sizes = []
+        for l in range(self.levels):
+            w, h = C.c_int(), C.c_int()
+            api.fn("level_size")(self.h, l, C.byref(w), C.byref(h))
+            self.sizes.append((w.value, h.value))
+
+    def close(self):
+        if self.h:
+            self.api.fn("destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _call(self, name, *args, ok=(0,)):
+        rc = self.api.fn(name)(self.h, *args)
+        if rc not in ok:
+            raise LdsoError(f"{self.api.prefix}{name} rc={rc}: {self.api.fn('last_error')(self.h).decode()}")
+        return rc
+
+    def sync(self):
+        self._call("sync")
+
+    def launch_count(self):
+        return self.api.fn("launch_count")(self.h)
+
+    def timer_start(self):
+        self._call("timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._call("timer_stop", C.byref(ms))
+        return ms.value
+
+    def set_gamma(self, B):
+        B = f32(B)
+        assert B.size == 256
+        self._call("set_gamma", _fp(B))
+
+    # K1
+    def make_images(self, slot, img):
+        img = f32(img)
+        assert img.size == self.cfg.w * self.cfg.h
+        self._call("frame_make_images", C.c_int(slot), _fp(img))
+
+    def make_images_dev(self, slot, dev_ptr):
+        self._call("frame_make_images_dev", C.c_int(slot), C.c_void_p(dev_ptr))
+
+    def download(self, slot, lvl, what):
+        w, h = self.sizes[lvl]
+        out = np.empty((h, w, 3) if what == 0 else (h, w), dtype=np.float32)
+        self._call("frame_download", C.c_int(slot), C.c_int(lvl), C.c_int(what), _fp(out))
+        return out
+
+    # K2
+    def tracker_make_k(self, trk, fx, fy, cx, cy):
+        self._call("tracker_make_k", C.c_int(trk), C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy))
+
+    def tracker_set_ref(self, trk, ref_slot, u, v, idepth, hdi, exposure=1.0, aff_a=0.0, aff_b=0.0):
+        u, v, idepth, hdi = f32(u), f32(v), f32(idepth), f32(hdi)
+        self._call("tracker_set_ref", C.c_int(trk), C.c_int(ref_slot), C.c_int(u.size), _fp(u), _fp(v), _fp(idepth), _fp(hdi),
+                   C.c_float(exposure), C.c_float(aff_a), C.c_float(aff_b))
+
+    def tracker_get_pc(self, trk, lvl):
+        w, h = self.sizes[lvl]
+        n = C.c_int()
+        arrs = [np.empty(w * h, dtype=np.float32) for _ in range(4)]
+        self._call("tracker_get_pc", C.c_int(trk), C.c_int(lvl), C.byref(n), *[_fp(a) for a in arrs])
+        return [a[: n.value].copy() for a in arrs]
+
+    # K3 / K4
+    def tracker_calc_res(self, trk, new_slot, lvl, pose12, aff_a, aff_b, cutoff, exposure=1.0):
+        pose12 = np.ascontiguousarray(pose12, dtype=np.float64)
+        out = np.empty(6, dtype=np.float32)
+        self._call("tracker_calc_res", C.c_int(trk), C.c_int(new_slot), C.c_float(exposure), C.c_int(lvl), _dp(pose12),
+                   C.c_float(aff_a), C.c_float(aff_b), C.c_float(cutoff), _fp(out))
+        return out
+
+    def tracker_calc_gs(self, trk, lvl, pose12, aff_a, aff_b):
+        pose12 = np.ascontiguousarray(pose12, dtype=np.float64)
+        H = np.empty((8, 8), dtype=np.float64)
+        b = np.empty(8, dtype=np.float64)
+        self._call("tracker_calc_gs", C.c_int(trk), C.c_int(lvl), _dp(pose12), C.c_float(aff_a), C.c_float(aff_b), _dp(H), _dp(b))
+        return H, b
+
+    def tracker_track(self, trk, new_slot, pose12, aff, coarsest_lvl=None, min_res=None, exposure=1.0):
+        pose = np.array(pose12, dtype=np.float64).copy()
+        aff = np.array(aff, dtype=np.float32).copy()
+        if coarsest_lvl is None:
+            coarsest_lvl = self.levels - 1
+        mr = f32(min_res if min_res is not None else [np.nan] * 5)
+        last = np.empty(5, dtype=np.float32)
+        flow = np.empty(3, dtype=np.float32)
+        iters = np.zeros(2, dtype=np.int32)
+        rc = self._call("tracker_track", C.c_int(trk), C.c_int(new_slot), C.c_float(exposure), _dp(pose), _fp(aff),
+                        C.c_int(coarsest_lvl), _fp(mr), _fp(last), _fp(flow), _ip(iters), ok=(0, 1))
+        return dict(ok=(rc == 0), pose=pose, aff=aff, last_residuals=last, flow=flow, iters=iters)
+
+
+_gpu_api = None
+
+
+def load():
+    """The product library.  Raises if it has not been built."""
+    global _gpu_api
+    if _gpu_api is None:
+        _gpu_api = Api(GPU_LIB, "ldso_gpu_")
+    return _gpu_api

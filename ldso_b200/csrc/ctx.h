@@ -1,0 +1,105 @@
+// ctx.h — per-sequence device context of libldso_gpu.so (internal; the public face is include/ldso_gpu.h).
+//
+// One ctx = one sequence: replaces the reference's process-global calibration
+// (src/internal/GlobalCalib.cc:7-18) and settings (src/Setting.cc) so that many sequences can live in
+// one process (BASELINE.json config 5).  All device memory is allocated once in ldso_gpu_create.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/ldso_gpu.h"
+#include "../../include/ldso_smallmat.h"
+
+#define LDSO_CUDA_OK(ctx, expr)                                                                      \
+    do {                                                                                             \
+        cudaError_t _e = (expr);                                                                     \
+        if (_e != cudaSuccess) {                                                                     \
+            (ctx)->set_error(std::string(#expr) + ": " + cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return -1;                                                                               \
+        }                                                                                            \
+    } while (0)
+
+#define LDSO_REQUIRE(ctx, cond)                                                      \
+    do {                                                                             \
+        if (!(cond)) {                                                               \
+            (ctx)->set_error(std::string("bad argument: ") + #cond, __FILE__, __LINE__); \
+            return -2;                                                               \
+        }                                                                            \
+    } while (0)
+
+// include/Settings.h:28-35
+#define LDSO_SCALE_XI_ROT 1.0f
+#define LDSO_SCALE_XI_TRANS 0.5f
+#define LDSO_SCALE_A 10.0f
+#define LDSO_SCALE_B 1000.0f
+
+// values reduced by the fused K3+K4 launch (see k34_tracker.cu)
+#define TRK_NRED 56          // 45 (9x9 upper) + E + flowT + flowRT + pad ; ints kept apart
+
+struct TrackerDev {
+    // makeK (CoarseTracker.cc:312-339), host copies
+    int w[LDSO_MAX_LEVELS], h[LDSO_MAX_LEVELS];
+    float fx[LDSO_MAX_LEVELS], fy[LDSO_MAX_LEVELS], cx[LDSO_MAX_LEVELS], cy[LDSO_MAX_LEVELS];
+    float K[LDSO_MAX_LEVELS][9], Ki[LDSO_MAX_LEVELS][9];
+    // device: per-level idepth / weightSums / weightSums_bak maps and the compacted point cloud
+    float* idepth[LDSO_MAX_LEVELS];
+    float* wsum[LDSO_MAX_LEVELS];
+    float* wsum_bak[LDSO_MAX_LEVELS];
+    float4* pc[LDSO_MAX_LEVELS];   // {u, v, idepth, color}  (pc_u, pc_v, pc_idepth, pc_color)
+    int* row_cnt;                  // per-row valid counts / offsets for the ordered compaction (all levels)
+    int* pc_n_dev;                 // [LDSO_MAX_LEVELS]
+    int pc_n[LDSO_MAX_LEVELS];     // host mirror
+    int row_base[LDSO_MAX_LEVELS + 1];
+    int ref_slot = -1;
+    float ref_exposure = 1, ref_aff_a = 0, ref_aff_b = 0;
+    // state of the last calc_res (for calc_gs)
+    int last_lvl = -1, new_slot = -1;
+    float new_exposure = 1;
+    double last_sums[48];
+    int last_counts[4];
+    float last_aff_a = 0, last_aff_b = 0;
+};
+
+struct ldso_gpu_ctx {
+    ldso_gpu_config cfg;
+    int levels = 0;
+    int wG[LDSO_MAX_LEVELS], hG[LDSO_MAX_LEVELS];
+    size_t lvl_off[LDSO_MAX_LEVELS + 1];   // pixel offset of each level inside a frame slot
+    cudaStream_t stream = nullptr;          // tracking stream
+    cudaStream_t stream_map = nullptr;      // mapping stream
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float4** frame = nullptr;               // [n_frame_slots] device float4 pyramids {I,dx,dy,absSquaredGrad}
+    float* img_dev = nullptr;               // staged input image
+    float* img_pinned = nullptr;
+    float* gammaB_dev = nullptr;            // B[256]
+    float* scratch_host = nullptr;          // pinned scratch, >= 16 B * pixels of level 0
+    TrackerDev trk[LDSO_NUM_TRACKERS];
+    // reduction workspace of the fused tracker launch
+    int trk_max_blocks = 0;                 // ceil(w*h / 128): every level-0 pixel could be a tracker point
+    float* trk_partials = nullptr;          // [trk_max_blocks][TRK_NRED]
+    int* trk_partials_i = nullptr;          // [trk_max_blocks][4]
+    unsigned int* trk_counter = nullptr;
+    double* trk_result_dev = nullptr;       // [64]
+    double* trk_result_pinned = nullptr;    // [64]
+    long long launches = 0;
+    std::string err;
+
+    void set_error(const std::string& what, const char* file, int line) {
+        char buf[64];
+        snprintf(buf, sizeof(buf), " (%s:%d)", strrchr(file, '/') ? strrchr(file, '/') + 1 : file, line);
+        err = what + buf;
+    }
+};
+
+// kernels (one translation unit each)
+int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev);
+int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u, const float* v, const float* id,
+               const float* hdi);
+struct TrackEvalOut {
+    double sums[48];   // 45 H entries (9x9 upper, row-major), E, flowT, flowRT
+    int counts[4];     // numTermsInE, numSaturated, numTermsInWarped, flowNum
+};
+int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew, float aff_a, float aff_b, float cutoffTH,
+             TrackEvalOut* out);

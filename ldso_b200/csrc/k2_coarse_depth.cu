@@ -1,0 +1,219 @@
+// k2_coarse_depth.cu — K2: CoarseTracker::makeCoarseDepthL0 (reference src/frontend/CoarseTracker.cc:357-538).
+//
+// Stages (all on the ctx's tracking stream, no host round trip until the final pc_n read-back):
+//   scatter   idepth*w and w of every qualifying point into the level-0 maps            (:363-382)
+//   pool      2x2 SUM up the pyramid, (a+b)+c+d association as in the reference          (:384-409)
+//   dilate    fill empty cells from 4 diagonal (levels 0,1) or axis (levels >=2) nbrs,
+//             reading the pre-dilation weight copy so the result is order-independent    (:412-495)
+//   compact   normalise and emit interior cells with weight>0 in ROW-MAJOR order into a
+//             float4 {u,v,idepth,color} point cloud per level                             (:498-537)
+// pc_n[] and the (u,v) sequence are bit-exact against the reference; idepth sums can differ in the last
+// bit only where >=3 points scatter into one pixel (atomicAdd order).
+#include "ctx.h"
+
+namespace {
+
+__global__ void k2_scatter_kernel(int n, const float* __restrict__ u, const float* __restrict__ v, const float* __restrict__ id,
+                                  const float* __restrict__ hdi, float* __restrict__ idepth0, float* __restrict__ wsum0, int w,
+                                  int h) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int x = (int)(u[k] + 0.5f);
+    int y = (int)(v[k] + 0.5f);
+    if (x < 0 || y < 0 || x >= w || y >= h) return;   // the reference would write out of bounds here
+    float weight = sqrtf((float)(1e-3 / ((double)hdi[k] + 1e-12)));
+    atomicAdd(idepth0 + x + w * y, id[k] * weight);
+    atomicAdd(wsum0 + x + w * y, weight);
+}
+
+__global__ void k2_pool_kernel(const float* __restrict__ id_lm, const float* __restrict__ ws_lm, float* __restrict__ id_l,
+                               float* __restrict__ ws_l, int wl, int hl, int wlm1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= wl * hl) return;
+    int y = i / wl, x = i - y * wl;
+    int bidx = 2 * x + 2 * y * wlm1;
+    id_l[i] = __fadd_rn(__fadd_rn(__fadd_rn(id_lm[bidx], id_lm[bidx + 1]), id_lm[bidx + wlm1]), id_lm[bidx + wlm1 + 1]);
+    ws_l[i] = __fadd_rn(__fadd_rn(__fadd_rn(ws_lm[bidx], ws_lm[bidx + 1]), ws_lm[bidx + wlm1]), ws_lm[bidx + wlm1 + 1]);
+}
+
+// reads ws_bak (pre-dilation copy), writes idepth/ws only where ws_bak<=0, reads idepth only where ws_bak>0
+__global__ void k2_dilate_kernel(float* __restrict__ idepth, float* __restrict__ ws, const float* __restrict__ ws_bak, int wl,
+                                 int hl, int diagonal) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x + wl;
+    if (i >= wl * hl - wl) return;
+    if (ws_bak[i] > 0) return;
+    int o0, o1, o2, o3;
+    if (diagonal) { o0 = 1 + wl; o1 = -1 - wl; o2 = wl - 1; o3 = -wl + 1; }
+    else { o0 = 1; o1 = -1; o2 = wl; o3 = -wl; }
+    float sum = 0, num = 0, numn = 0;
+    float b;
+    b = ws_bak[i + o0]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o0]); num = __fadd_rn(num, b); numn++; }
+    b = ws_bak[i + o1]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o1]); num = __fadd_rn(num, b); numn++; }
+    b = ws_bak[i + o2]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o2]); num = __fadd_rn(num, b); numn++; }
+    b = ws_bak[i + o3]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o3]); num = __fadd_rn(num, b); numn++; }
+    if (numn > 0) {
+        idepth[i] = __fdiv_rn(sum, numn);
+        ws[i] = __fdiv_rn(num, numn);
+    }
+}
+
+struct K2Levels {
+    int levels;
+    int w[LDSO_MAX_LEVELS], h[LDSO_MAX_LEVELS];
+    int row_base[LDSO_MAX_LEVELS + 1];   // first compaction row of each level in the flat row list
+    float* idepth[LDSO_MAX_LEVELS];
+    float* ws[LDSO_MAX_LEVELS];
+    float4* pc[LDSO_MAX_LEVELS];
+    const float4* ref[LDSO_MAX_LEVELS];
+};
+
+__device__ __forceinline__ bool k2_valid(const K2Levels& p, int l, int i, float& nid, float& color) {
+    float wsum = p.ws[l][i];
+    if (!(wsum > 0)) return false;
+    nid = __fdiv_rn(p.idepth[l][i], wsum);
+    color = p.ref[l][i].x;
+    return isfinite(color) && (nid > 0);
+}
+
+// one warp per interior row (y in [2,h-2)) of every level: count
+__global__ void k2_count_rows_kernel(const K2Levels p, int* __restrict__ row_cnt) {
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    int lane = threadIdx.x & 31;
+    if (row >= p.row_base[p.levels]) return;
+    int l = 0;
+    while (row >= p.row_base[l + 1]) l++;
+    int y = row - p.row_base[l] + 2;
+    int wl = p.w[l];
+    int cnt = 0;
+    for (int x = 2 + lane; x < wl - 2; x += 32) {
+        float nid, col;
+        cnt += k2_valid(p, l, x + y * wl, nid, col) ? 1 : 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) row_cnt[row] = cnt;
+}
+
+// one CTA per level: exclusive scan of that level's row counts (in place), total -> pc_n[l]
+__global__ void k2_scan_rows_kernel(const K2Levels p, int* __restrict__ row_cnt, int* __restrict__ pc_n) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    int l = blockIdx.x;
+    int base = p.row_base[l], n = p.row_base[l + 1] - base;
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int start = 0; start < n; start += blockDim.x) {
+        int i = start + threadIdx.x;
+        int v = i < n ? row_cnt[base + i] : 0;
+        int incl = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_tot[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            int t = lane < (blockDim.x >> 5) ? warp_tot[lane] : 0;
+            int ti = t;
+            for (int o = 1; o < 32; o <<= 1) {
+                int s = __shfl_up_sync(0xffffffffu, ti, o);
+                if (lane >= o) ti += s;
+            }
+            warp_tot[lane] = ti - t;   // exclusive
+        }
+        __syncthreads();
+        int excl = carry + warp_tot[wid] + incl - v;
+        if (i < n) row_cnt[base + i] = excl;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) pc_n[l] = carry;
+}
+
+// one warp per row: ordered emit (CoarseTracker.cc:513-533), also normalises the idepth map
+__global__ void k2_emit_rows_kernel(const K2Levels p, const int* __restrict__ row_off) {
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    int lane = threadIdx.x & 31;
+    if (row >= p.row_base[p.levels]) return;
+    int l = 0;
+    while (row >= p.row_base[l + 1]) l++;
+    int y = row - p.row_base[l] + 2;
+    int wl = p.w[l];
+    int off = row_off[row];
+    float4* pc = p.pc[l];
+    for (int x0 = 2; x0 < wl - 2; x0 += 32) {
+        int x = x0 + lane;
+        bool ok = false;
+        float nid = 0, col = 0;
+        if (x < wl - 2) {
+            int i = x + y * wl;
+            ok = k2_valid(p, l, i, nid, col);
+            p.idepth[l][i] = ok ? nid : -1.f;
+        }
+        unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) pc[off + __popc(m & ((1u << lane) - 1u))] = make_float4((float)x, (float)y, nid, col);
+        off += __popc(m);
+    }
+}
+
+}  // namespace
+
+int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u, const float* v, const float* id,
+               const float* hdi) {
+    TrackerDev& T = c->trk[tracker];
+    cudaStream_t s = c->stream;
+    const int L = c->levels;
+    // upload the point list through the pinned scratch buffer (4 arrays)
+    float* hp = c->scratch_host;
+    float* dp = (float*)c->img_dev;   // reuse of the staged-image buffer: n <= w*h/4 guaranteed by max_points check
+    if (n > 0) {
+        memcpy(hp, u, n * sizeof(float));
+        memcpy(hp + n, v, n * sizeof(float));
+        memcpy(hp + 2 * n, id, n * sizeof(float));
+        memcpy(hp + 3 * n, hdi, n * sizeof(float));
+        LDSO_CUDA_OK(c, cudaMemcpyAsync(dp, hp, 4 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice, s));
+    }
+    size_t n0 = (size_t)T.w[0] * T.h[0];
+    LDSO_CUDA_OK(c, cudaMemsetAsync(T.idepth[0], 0, n0 * sizeof(float), s));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(T.wsum[0], 0, n0 * sizeof(float), s));
+    if (n > 0) {
+        k2_scatter_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, dp, dp + n, dp + 2 * n, dp + 3 * n, T.idepth[0], T.wsum[0], T.w[0],
+                                                          T.h[0]);
+        c->launches++;
+    }
+    for (int l = 1; l < L; l++) {
+        int nl = T.w[l] * T.h[l];
+        k2_pool_kernel<<<(nl + 255) / 256, 256, 0, s>>>(T.idepth[l - 1], T.wsum[l - 1], T.idepth[l], T.wsum[l], T.w[l], T.h[l],
+                                                        T.w[l - 1]);
+        c->launches++;
+    }
+    for (int l = 0; l < L; l++) {
+        int nl = T.w[l] * T.h[l];
+        LDSO_CUDA_OK(c, cudaMemcpyAsync(T.wsum_bak[l], T.wsum[l], nl * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        k2_dilate_kernel<<<(nl + 255) / 256, 256, 0, s>>>(T.idepth[l], T.wsum[l], T.wsum_bak[l], T.w[l], T.h[l], l < 2 ? 1 : 0);
+        c->launches++;
+    }
+    K2Levels p;
+    p.levels = L;
+    for (int l = 0; l < L; l++) {
+        p.w[l] = T.w[l]; p.h[l] = T.h[l];
+        p.row_base[l] = T.row_base[l];
+        p.idepth[l] = T.idepth[l]; p.ws[l] = T.wsum[l]; p.pc[l] = T.pc[l];
+        p.ref[l] = c->frame[ref_slot] + c->lvl_off[l];
+    }
+    p.row_base[L] = T.row_base[L];
+    int rows = T.row_base[L];
+    k2_count_rows_kernel<<<(rows + 7) / 8, 256, 0, s>>>(p, T.row_cnt);
+    k2_scan_rows_kernel<<<L, 256, 0, s>>>(p, T.row_cnt, T.pc_n_dev);
+    k2_emit_rows_kernel<<<(rows + 7) / 8, 256, 0, s>>>(p, T.row_cnt);
+    c->launches += 3;
+    LDSO_CUDA_OK(c, cudaGetLastError());
+    int* hn = (int*)c->trk_result_pinned;
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(hn, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    for (int l = 0; l < L; l++) T.pc_n[l] = hn[l];
+    T.ref_slot = ref_slot;
+    T.last_lvl = -1;
+    return 0;
+}

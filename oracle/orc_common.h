@@ -1,0 +1,87 @@
+// oracle/orc_common.h — TEST INFRASTRUCTURE, not product code.
+//
+// CPU restatement of the LDSO hot path (reference: n-lalanne/LDSO, CPU/SSE only).  It exists to
+// (a) check the CUDA path in tests/ and __graft_entry__.smoke(), and (b) be timed as the CPU baseline
+// by bench.py.  Nothing under ldso_b200/ may include, link or call it.
+//
+// PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures for this path
+//  and cannot be compiled here (Eigen/glog/OpenCV/DBoW3 absent).  Correctness of
+// this restatement is argued by line-by-line correspondence (every function cites the reference
+// file:line it follows), numpy/scipy cross-checks of the small dense algebra, and end-to-end
+// behaviour on synthetic sequences with known ground truth.
+//
+// Every exported function has the same signature as its ldso_gpu_* counterpart in
+// include/ldso_gpu.h with the prefix orc_ and ctx type orc_ctx, so the parity tests drive both
+// libraries through one harness.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <xmmintrin.h>
+
+#include "../include/ldso_gpu.h"
+#include "../include/ldso_smallmat.h"
+
+namespace orc {
+
+// include/Settings.h:28-35
+constexpr float SCALE_IDEPTH = 1.0f, SCALE_XI_ROT = 1.0f, SCALE_XI_TRANS = 0.5f, SCALE_F = 50.0f, SCALE_C = 50.0f,
+                SCALE_W = 1.0f, SCALE_A = 10.0f, SCALE_B = 1000.0f;
+
+struct Frame {
+    // FrameHessian::dIp / absSquaredGrad (include/internal/FrameHessian.h)
+    std::vector<float> dIp[LDSO_MAX_LEVELS];   // 3 floats per pixel {I,dx,dy}
+    std::vector<float> absSquaredGrad[LDSO_MAX_LEVELS];
+    bool valid = false;
+};
+
+// include/internal/OptimizationBackend/MatrixAccumulators.h:1104-1643
+struct Accumulator9 {
+    float H[9][9];
+    size_t num;
+    alignas(16) float SSEData[4 * 45], SSEData1k[4 * 45], SSEData1m[4 * 45];
+    float numIn1, numIn1k, numIn1m;
+    void initialize();
+    void finish();
+    void updateSSE_eighted(const __m128* J, __m128 w);   // J[0..8]
+    void updateSSE(const __m128* J);
+    void updateSingle(const float* J, int off = 0);
+    void updateSingleWeighted(const float* J, float w, int off = 0);
+    void shiftUp(bool force);
+};
+
+struct Tracker {
+    // CoarseTracker members (include/frontend/CoarseTracker.h)
+    int w[LDSO_MAX_LEVELS], h[LDSO_MAX_LEVELS];
+    float fx[LDSO_MAX_LEVELS], fy[LDSO_MAX_LEVELS], cx[LDSO_MAX_LEVELS], cy[LDSO_MAX_LEVELS];
+    float K[LDSO_MAX_LEVELS][9], Ki[LDSO_MAX_LEVELS][9];
+    std::vector<float> idepth[LDSO_MAX_LEVELS], weightSums[LDSO_MAX_LEVELS], weightSums_bak[LDSO_MAX_LEVELS];
+    std::vector<float> pc_u[LDSO_MAX_LEVELS], pc_v[LDSO_MAX_LEVELS], pc_idepth[LDSO_MAX_LEVELS], pc_color[LDSO_MAX_LEVELS];
+    int pc_n[LDSO_MAX_LEVELS];
+    float *buf_warped_idepth, *buf_warped_u, *buf_warped_v, *buf_warped_dx, *buf_warped_dy, *buf_warped_residual,
+        *buf_warped_weight, *buf_warped_refColor;
+    std::vector<float> buf_store;
+    int buf_warped_n = 0;
+    int ref_slot = -1;
+    float ref_exposure = 1, ref_aff_a = 0, ref_aff_b = 0;   // lastRef->ab_exposure, lastRef_aff_g2l
+    int new_slot = -1;
+    float new_exposure = 1;
+    Accumulator9 acc;
+};
+
+}  // namespace orc
+
+struct orc_ctx {
+    ldso_gpu_config cfg;
+    int levels;
+    int wG[LDSO_MAX_LEVELS], hG[LDSO_MAX_LEVELS];
+    float B[256];
+    std::vector<orc::Frame> frames;
+    orc::Tracker trk[LDSO_NUM_TRACKERS];
+    std::string err;
+    long long launches = 0;
+};
