@@ -17,6 +17,9 @@ ORACLE_FAST_LIB = os.path.join(ORACLE_DIR, "liboracle_fast.so")  # -O3 with cont
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+    # per-item float math must round like a strict-IEEE evaluation of the reference's expressions (threshold tests
+    # feed discrete decisions); these kernels are gather/bandwidth-bound, so unfused mul+add costs nothing measurable
+    "-fmad=false", "-prec-div=true", "-prec-sqrt=true",
     "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function", "--expt-relaxed-constexpr",
 ]
 

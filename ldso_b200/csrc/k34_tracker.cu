@@ -53,9 +53,13 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
     if (i < p.n) {
         const float4 q = __ldg(pc + i);
         const float x = q.x, y = q.y, id = q.z, refColor = q.w;
-        float pt0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2] + p.t[0] * id;
-        float pt1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5] + p.t[1] * id;
-        float pt2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8] + p.t[2] * id;
+        // r = RKi*(x,y,1); pt = r + t*id — same association as the reference's Eigen expression, and the
+        // library is compiled with -fmad=false, so every per-point value below is bit-identical to a
+        // strict-IEEE evaluation of CoarseTracker.cc:575-585 (threshold tests cannot flip on FMA rounding).
+        const float r0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2];
+        const float r1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5];
+        const float r2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8];
+        float pt0 = r0 + p.t[0] * id, pt1 = r1 + p.t[1] * id, pt2 = r2 + p.t[2] * id;
         float u = pt0 / pt2, v = pt1 / pt2;
         float Ku = p.fx * u + p.cx, Kv = p.fy * v + p.cy;
         float new_idepth = id / pt2;
@@ -66,7 +70,6 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
             float zT = k2 + p.t[2] * id, zT2 = k2 - p.t[2] * id;
             float KuT = p.fx * ((k0 + p.t[0] * id) / zT) + p.cx, KvT = p.fy * ((k1 + p.t[1] * id) / zT) + p.cy;
             float KuT2 = p.fx * ((k0 - p.t[0] * id) / zT2) + p.cx, KvT2 = p.fy * ((k1 - p.t[1] * id) / zT2) + p.cy;
-            float r0 = pt0 - p.t[0] * id, r1 = pt1 - p.t[1] * id, r2 = pt2 - p.t[2] * id;   // RKi*(x,y,1)
             float z3 = r2 - p.t[2] * id;
             float Ku3 = p.fx * ((r0 - p.t[0] * id) / z3) + p.cx, Kv3 = p.fy * ((r1 - p.t[1] * id) / z3) + p.cy;
             acc[46] = ((KuT - x) * (KuT - x) + (KvT - y) * (KvT - y)) + ((KuT2 - x) * (KuT2 - x) + (KvT2 - y) * (KvT2 - y));
