@@ -84,6 +84,10 @@ long long ldso_gpu_launch_count(const ldso_gpu_ctx* ctx);
 /* CUDA-event stopwatch on the ctx's tracking stream (the stream every kernel of this ctx is launched on) */
 int ldso_gpu_timer_start(ldso_gpu_ctx* ctx);
 int ldso_gpu_timer_stop(ldso_gpu_ctx* ctx, float* ms);
+/* Per-kernel CUDA-event profile.  enable(1) zeroes the counters; which = 0: fused tracker kernel (K3+K4).
+ * total_ms = summed launch durations, units = items processed (points). */
+int ldso_gpu_profile_enable(ldso_gpu_ctx* ctx, int on);
+int ldso_gpu_profile_get(ldso_gpu_ctx* ctx, int which, double* total_ms, long long* launches, double* units);
 
 /* CalibHessian::B inverse-response LUT used by getBGradOnly (include/internal/CalibHessian.h:102-111).
  * Default: identity (B[i] = i), i.e. no photometric calibration. */

@@ -142,6 +142,14 @@ class Ctx:
         self._call("timer_stop", C.byref(ms))
         return ms.value
 
+    def profile_enable(self, on=True):
+        self._call("profile_enable", C.c_int(1 if on else 0))
+
+    def profile_get(self, which=0):
+        ms, n, units = C.c_double(), C.c_longlong(), C.c_double()
+        self._call("profile_get", C.c_int(which), C.byref(ms), C.byref(n), C.byref(units))
+        return ms.value, n.value, units.value
+
     def set_gamma(self, B):
         B = f32(B)
         assert B.size == 256

@@ -53,6 +53,8 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaStreamCreateWithFlags(&c->stream_map, cudaStreamNonBlocking));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev0));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev1));
+    LDSO_CUDA_OK(c, cudaEventCreate(&c->pev0));
+    LDSO_CUDA_OK(c, cudaEventCreate(&c->pev1));
     c->frame = new float4*[cfg.n_frame_slots]();
     for (int s = 0; s < cfg.n_frame_slots; s++) LDSO_CUDA_OK(c, cudaMalloc(&c->frame[s], off * sizeof(float4)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->img_dev, npx0 * sizeof(float)));
@@ -130,6 +132,8 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     cudaFreeHost(c->trk_result_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->pev0) cudaEventDestroy(c->pev0);
+    if (c->pev1) cudaEventDestroy(c->pev1);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->stream_map) cudaStreamDestroy(c->stream_map);
     delete c;
@@ -157,6 +161,17 @@ extern "C" int ldso_gpu_timer_stop(ldso_gpu_ctx* c, float* ms) {
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev1, c->stream));
     LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev1));
     LDSO_CUDA_OK(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
+    return 0;
+}
+
+extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
+    c->profile_on = on;
+    if (on) for (int i = 0; i < 8; i++) { c->prof_ms[i] = 0; c->prof_launches[i] = 0; c->prof_units[i] = 0; }
+    return 0;
+}
+extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms, long long* launches, double* units) {
+    LDSO_REQUIRE(c, which >= 0 && which < 8);
+    *total_ms = c->prof_ms[which]; *launches = c->prof_launches[which]; *units = c->prof_units[which];
     return 0;
 }
 

@@ -84,6 +84,12 @@ struct ldso_gpu_ctx {
     double* trk_result_dev = nullptr;       // [64]
     double* trk_result_pinned = nullptr;    // [64]
     long long launches = 0;
+    // optional per-kernel CUDA-event profile (ldso_gpu_profile_*): [0] = fused tracker kernel
+    int profile_on = 0;
+    cudaEvent_t pev0 = nullptr, pev1 = nullptr;
+    double prof_ms[8] = {0};
+    long long prof_launches[8] = {0};
+    double prof_units[8] = {0};
     std::string err;
 
     void set_error(const std::string& what, const char* file, int line) {

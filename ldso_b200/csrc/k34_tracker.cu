@@ -157,16 +157,18 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    // last CTA: fp64 fold over CTAs in index order
-    if (threadIdx.x < NF) {
+    // last CTA: fp64 fold over CTAs.  Warp w owns values w, w+4, ...; lanes stride over CTAs, then a fixed
+    // shuffle tree — the summation order depends only on gridDim, so results are run-to-run deterministic.
+    for (int k = wid; k < NF + NI; k += TRK_THREADS / 32) {
         double s = 0.0;
-        for (unsigned b = 0; b < gridDim.x; b++) s += (double)__ldcg(partials + b * TRK_NRED + threadIdx.x);
-        result[threadIdx.x] = s;
-    } else if (threadIdx.x < NF + NI) {
-        int f = threadIdx.x - NF;
-        long long s = 0;
-        for (unsigned b = 0; b < gridDim.x; b++) s += __ldcg(partials_i + b * NI + f);
-        result[threadIdx.x] = (double)s;
+        if (k < NF) {
+            for (unsigned b = lane; b < gridDim.x; b += 32) s += (double)__ldcg(partials + b * TRK_NRED + k);
+        } else {
+            for (unsigned b = lane; b < gridDim.x; b += 32) s += (double)__ldcg(partials_i + b * NI + (k - NF));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) result[k] = s;
     }
     if (threadIdx.x == 0) *counter = 0u;
 }
@@ -209,12 +211,19 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     }
     int blocks = (p.n + TRK_THREADS - 1) / TRK_THREADS;
     if (blocks > c->trk_max_blocks) { c->set_error("tracker point cloud too large", __FILE__, __LINE__); return -2; }
+    if (c->profile_on) cudaEventRecord(c->pev0, c->stream);
     k34_track_eval_kernel<<<blocks, TRK_THREADS, 0, c->stream>>>(T.pc[lvl], c->frame[T.new_slot] + c->lvl_off[lvl], p,
                                                                  c->trk_partials, c->trk_partials_i, c->trk_counter,
                                                                  c->trk_result_dev);
     c->launches++;
+    if (c->profile_on) cudaEventRecord(c->pev1, c->stream);
     LDSO_CUDA_OK(c, cudaMemcpyAsync(res, c->trk_result_dev, (NF + NI) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    if (c->profile_on) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->pev0, c->pev1);
+        c->prof_ms[0] += ms; c->prof_launches[0]++; c->prof_units[0] += p.n;
+    }
     for (int k = 0; k < NF; k++) out->sums[k] = res[k];
     for (int k = 0; k < NI; k++) out->counts[k] = (int)res[NF + k];
     return 0;

@@ -25,28 +25,7 @@ def frames(calib="c1", seed=1001, idx=(40, 42)):
     return out
 
 
-def pick_points(img, depth, n, seed=7, border=6):
-    """n high-gradient pixels spread over the image (one per grid cell), with ground-truth inverse depth."""
-    h, w = img.shape
-    gy, gx = np.gradient(img.astype(np.float64))
-    g = gx * gx + gy * gy
-    g[:border] = 0; g[-border:] = 0; g[:, :border] = 0; g[:, -border:] = 0
-    cell = max(2, int(np.sqrt(w * h / float(n))))
-    pts = []
-    for y0 in range(0, h - cell + 1, cell):
-        for x0 in range(0, w - cell + 1, cell):
-            blk = g[y0:y0 + cell, x0:x0 + cell]
-            k = int(np.argmax(blk))
-            if blk.flat[k] > 4.0:
-                pts.append((x0 + k % cell, y0 + k // cell))
-    pts = np.array(pts[: n], dtype=np.float32)
-    rng = np.random.default_rng(seed)
-    u = pts[:, 0] + rng.uniform(-0.3, 0.3, len(pts)).astype(np.float32)
-    v = pts[:, 1] + rng.uniform(-0.3, 0.3, len(pts)).astype(np.float32)
-    d = depth[pts[:, 1].astype(int), pts[:, 0].astype(int)]
-    idepth = (1.0 / d).astype(np.float32)
-    hdi = rng.uniform(1e-4, 5e-3, len(pts)).astype(np.float32)
-    return u.astype(np.float32), v.astype(np.float32), idepth, hdi
+pick_points = synth.pick_points
 
 
 def make_ctx(api, calib="c1", **kw):
