@@ -134,6 +134,89 @@ int ldso_gpu_tracker_track(ldso_gpu_ctx* ctx, int tracker, int new_slot, float n
                            const float min_res_for_abort[5], float last_residuals[5], float flow[3],
                            int iters_out[2]);
 
+
+/* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
+ * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps
+ * points and residuals as SoA/AoS pools.  Index conventions follow the reference: pair tables are
+ * indexed [host + n * target] (EnergyFunctional.cc:523-609), points are in allPoints order (frames ->
+ * features, EnergyFunctional.cc:505-519; hence contiguous per host frame), residuals in p->residuals
+ * order, flattened point-major with a CSR offset array. */
+#define LDSO_MAX_WINDOW 12
+#define LDSO_PRECALC_STRIDE 32
+/* one FrameFramePrecalc (src/internal/FrameFramePrecalc.cc:6-35) as 32 floats:
+ * [0..8] PRE_RTll_0 (row-major) [9..11] PRE_tTll_0 [12..20] PRE_KRKiTll [21..23] PRE_KtTll
+ * [24..25] PRE_aff_mode [26] PRE_b0_mode [27..31] reserved */
+/* ResState (include/internal/Residuals.h:33-35) */
+#define LDSO_RES_IN 0
+#define LDSO_RES_OOB 1
+#define LDSO_RES_OUTLIER 2
+/* residual flag bits */
+#define LDSO_RF_LINEARIZED 1   /* PointFrameResidual::isLinearized */
+#define LDSO_RF_ACTIVE 2       /* isActiveAndIsGoodNEW */
+#define LDSO_RF_NEW 4          /* isNew */
+/* RawResidualJacobian (include/internal/RawResidualJacobian.h:13-39) as 72 floats:
+ * [0..7] resF [8..15] JIdx[0] [16..23] JIdx[1] [24..31] JabF[0] [32..39] JabF[1] [40..45] Jpdxi[0] [46..51] Jpdxi[1]
+ * [52..55] Jpdc[0] [56..59] Jpdc[1] [60..61] Jpdd [62..64] JIdx2 (00,01,11) [65..68] JabJIdx (00,01,10,11)
+ * [69..71] Jab2 (00,01,11) */
+#define LDSO_J_FLOATS 72
+
+/* frames of the window: pyramid slot of each, n*n precalc table, frameEnergyTH per frame, and
+ * CalibHessian fxl,fyl,cxl,cyl (setPrecalcValues, src/frontend/FullSystem.cc:1667-1675) */
+int ldso_gpu_window_set_frames(ldso_gpu_ctx* ctx, int n_frames, const int* slots, const float* precalc,
+                               const float* frame_energy_th, const float calib[4]);
+/* active points (PointHessian fields: u,v,idepth(_scaled),idepth_zero(_scaled),color[8],weights[8],priorF;
+ * host = frame index) and the CSR offsets of their residual lists (n_points+1 entries) */
+int ldso_gpu_window_set_points(ldso_gpu_ctx* ctx, int n_points, const float* u, const float* v, const float* idepth,
+                               const float* idepth_zero, const int* host, const float* color, const float* weights,
+                               const float* prior, const int* res_begin);
+/* residuals (PointFrameResidual): target frame index, state_state, flag bits; optional res_to_zero [n][8] */
+int ldso_gpu_window_set_residuals(ldso_gpu_ctx* ctx, int n_res, const int* target, const int* state,
+                                  const unsigned char* flags, const float* res_to_zero);
+/* EnergyFunctional::setAdjointsF / setDeltaF products (EnergyFunctional.cc:523-609): adHost, adTarget
+ * [n*n][64] row-major double, adHTdeltaF [n*n][8], cDeltaF[4], cPrior[4], per-frame prior[8] and delta_prior[8] */
+int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* ctx, const double* ad_host, const double* ad_target, const float* ad_ht_delta,
+                                 const float c_delta[4], const double c_prior[4], const double* frame_prior,
+                                 const double* frame_delta_prior);
+/* new point depths after a step (doStepFromBackup, FullSystem.cc:1826-1932) without re-sending the window */
+int ldso_gpu_window_set_idepth(ldso_gpu_ctx* ctx, const float* idepth, const float* idepth_zero);
+
+/* ---- K7: FullSystem::linearizeAll -> PointFrameResidual::linearize (src/internal/Residuals.cc:15-217)
+ * over every residual that is not linearized; stats = [sum energy, 0, #state_NewState==IN]
+ * (FullSystem.cc:1716-1741).  Also runs setNewFrameEnergyTH (:2078-2109) for the newest frame and returns
+ * it in new_frame_energy_th.  fix_linearization != 0 additionally does applyRes(true) and the isNew
+ * bookkeeping (maxRelBaseline, numGoodResiduals) of linearizeAll_Reductor (:1786-1820). */
+int ldso_gpu_window_linearize(ldso_gpu_ctx* ctx, int fix_linearization, double stats[3], float* new_frame_energy_th);
+/* FullSystem::applyRes_Reductor(true) (FullSystem.cc:2022-2027; include/internal/Residuals.h:70-88,124-129) */
+int ldso_gpu_window_apply_res(ldso_gpu_ctx* ctx);
+/* PointFrameResidual::resetOOB for every non-linearized residual (FullSystem.cc:864-867) */
+int ldso_gpu_window_reset_oob(ldso_gpu_ctx* ctx);
+/* PointFrameResidual::fixLinearizationF (Residuals.cc:219-245) for the residuals whose mask byte is non-zero */
+int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* ctx, const unsigned char* mask);
+
+/* ---- K8 + K9: EnergyFunctional::accumulateAF_MT / accumulateLF_MT / accumulateSCF_MT (EnergyFunctional.cc:670-749)
+ * = AccumulatedTopHessianSSE::addPoint<0>, <1> + stitchDoubleMT, AccumulatedSCHessianSSE::addPoint + stitch.
+ * Each H is (8n+4)^2 row-major double, each b is 8n+4.  counts = [resInA, resInL]. */
+int ldso_gpu_window_accumulate(ldso_gpu_ctx* ctx, double* HA, double* bA, double* HL, double* bL, double* Hsc, double* bsc,
+                               int counts[2]);
+/* ---- H1: the dense part of EnergyFunctional::solveSystemF (EnergyFunctional.cc:310-432), host code.
+ * HM,bM: marginalisation prior; delta: getStitchedDeltaF(); N: (8n+4) x n_null nullspace columns (may be NULL)
+ * used by orthogonalize() when iteration >= 2.  x_out: 8n+4. */
+int ldso_gpu_window_solve(ldso_gpu_ctx* ctx, int iteration, double lambda, const double* HA, const double* bA,
+                          const double* HL, const double* bL, const double* Hsc, const double* bsc, const double* HM,
+                          const double* bM, const double* delta, const double* N, int n_null, double* x_out);
+/* ---- K10: EnergyFunctional::resubstituteF_MT / resubstituteFPt (EnergyFunctional.cc:611-667): per-point step */
+int ldso_gpu_window_resubstitute(ldso_gpu_ctx* ctx, const double* x, float lambda, float* step_out);
+
+/* read-backs (host mirrors of public members other reference code reads directly) */
+/* what: 0 J [n][72], 1 res_toZeroF [n][8], 2 JpJdF [n][8], 3 centerProjectedTo [n][3],
+ *       4 state_NewEnergy, 5 state_NewEnergyWithOutlier, 6 state_energy  (float each) */
+int ldso_gpu_window_get_residual_floats(ldso_gpu_ctx* ctx, int what, float* dst);
+/* what: 0 state_state, 1 state_NewState, 2 flag bits */
+int ldso_gpu_window_get_residual_ints(ldso_gpu_ctx* ctx, int what, int* dst);
+/* what: 0 Hdd_accAF 1 bd_accAF 2 Hcd_accAF[4] 3 Hdd_accLF 4 bd_accLF 5 Hcd_accLF[4] 6 HdiF 7 bdSumF
+ *       8 idepth_hessian 9 maxRelBaseline 10 numGoodResiduals (as float) 11 step */
+int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* ctx, int what, float* dst);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,60 @@ struct Tracker {
     Accumulator9 acc;
 };
 
+
+// ---- windowed BA state (host structs of the reference flattened; see include/ldso_gpu.h) ----
+// include/internal/OptimizationBackend/MatrixAccumulators.h:749-1102
+struct AccumulatorApprox {
+    float H[13][13];
+    size_t num;
+    alignas(16) float Data[60], Data1k[60], Data1m[60];
+    alignas(16) float TopRight_Data[32], TopRight_Data1k[32], TopRight_Data1m[32];
+    alignas(16) float BotRight_Data[8], BotRight_Data1k[8], BotRight_Data1m[8];
+    float numIn1, numIn1k, numIn1m;
+    void initialize();
+    void finish();
+    void update(const float* x4, const float* x6, const float* y4, const float* y6, float a, float b, float c);
+    void updateTopRight(const float* x4, const float* x6, const float* y4, const float* y6, float TR00, float TR10, float TR01,
+                        float TR11, float TR02, float TR12);
+    void updateBotRight(float a00, float a01, float a02, float a11, float a12, float a22);
+    void shiftUp(bool force);
+};
+// MatrixAccumulators.h:20-64 (AccumulatorXX<i,j>) and :150-198 (AccumulatorX<i>), sizes fixed at run time
+struct AccumulatorMat {
+    int rows = 0, cols = 0;
+    std::vector<float> A, A1k, A1m;
+    size_t num = 0;
+    float numIn1 = 0, numIn1k = 0, numIn1m = 0;
+    void initialize(int r, int c);
+    void update(const float* L, const float* R, float w);   // A += w * L * R^T   (cols==1, R==nullptr: A += w*L)
+    void finish();
+    void shiftUp(bool force);
+};
+
+struct Window {
+    int n = 0;
+    int slots[LDSO_MAX_WINDOW];
+    float precalc[LDSO_MAX_WINDOW * LDSO_MAX_WINDOW][LDSO_PRECALC_STRIDE];
+    float frameEnergyTH[LDSO_MAX_WINDOW];
+    float fxl, fyl, cxl, cyl, fxli, fyli, cxli, cyli;
+    // points
+    int np = 0;
+    std::vector<float> u, v, idepth, idepth_zero, prior, color, weights, deltaF;
+    std::vector<int> host, res_begin;
+    std::vector<float> Hdd_accAF, bd_accAF, Hcd_accAF, Hdd_accLF, bd_accLF, Hcd_accLF, HdiF, bdSumF, idepth_hessian,
+        maxRelBaseline, numGoodResiduals, step;
+    // residuals
+    int nr = 0;
+    std::vector<int> r_point, r_target, state_state, state_NewState, flags;
+    std::vector<double> state_energy, state_NewEnergy, state_NewEnergyWithOutlier;
+    std::vector<float> J, res_toZeroF, JpJdF, center;
+    // adjoints / deltas
+    std::vector<double> adHost, adTarget, fprior, fdelta_prior;
+    std::vector<float> adHostF, adTargetF, adHTdeltaF;
+    float cDeltaF[4] = {0, 0, 0, 0};
+    double cPrior[4] = {0, 0, 0, 0};
+};
+
 }  // namespace orc
 
 struct orc_ctx {
@@ -82,6 +136,7 @@ struct orc_ctx {
     float B[256];
     std::vector<orc::Frame> frames;
     orc::Tracker trk[LDSO_NUM_TRACKERS];
+    orc::Window win;
     std::string err;
     long long launches = 0;
 };
