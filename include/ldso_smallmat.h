@@ -227,7 +227,7 @@ inline bool ldlt_solve(int n, const double* Ain, const double* b, double* x) {
         if (d == 0) { ok = false; continue; }
         for (int i = k + 1; i < n; i++) {
             double l = A[i * n + k] / d;
-            for (int j = k + 1; j <= i; j++) A[i * n + j] -= l * A[j * n + k];
+            for (int j = k + 1; j <= i; j++) A[i * n + j] -= l * A[k * n + j];   // row k (upper mirror) still holds a_jk
             A[i * n + k] = l;
         }
         for (int i = k + 1; i < n; i++)

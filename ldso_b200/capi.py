@@ -215,6 +215,95 @@ class Ctx:
         return dict(ok=(rc == 0), pose=pose, aff=aff, last_residuals=last, flow=flow, iters=iters)
 
 
+    # ---- windowed BA (K7-K10, H1) ----
+    def window_load(self, W, slots=None):
+        """upload a window description dict (see synth.make_window); frames must already be in their slots"""
+        n = W["n"]
+        slots = np.ascontiguousarray(slots if slots is not None else np.arange(n), dtype=np.int32)
+        self.win_n, self.win_np, self.win_nr = n, len(W["u"]), len(W["target"])
+        pc, eth, cal = f32(W["precalc"]), f32(W["frame_energy_th"]), f32(W["calib"])
+        self._call("window_set_frames", C.c_int(n), _ip(slots), _fp(pc), _fp(eth), _fp(cal))
+        a = [f32(W[k]) for k in ("u", "v", "idepth", "idepth_zero")]
+        host = np.ascontiguousarray(W["host"], dtype=np.int32)
+        col, wgt, pri = f32(W["color"]), f32(W["weights"]), f32(W["prior"])
+        rb = np.ascontiguousarray(W["res_begin"], dtype=np.int32)
+        self._call("window_set_points", C.c_int(self.win_np), _fp(a[0]), _fp(a[1]), _fp(a[2]), _fp(a[3]), _ip(host), _fp(col),
+                   _fp(wgt), _fp(pri), _ip(rb))
+        tg = np.ascontiguousarray(W["target"], dtype=np.int32)
+        st = np.ascontiguousarray(W["state"], dtype=np.int32)
+        fl = np.ascontiguousarray(W["flags"], dtype=np.uint8)
+        rtz = f32(W["res_to_zero"])
+        self._call("window_set_residuals", C.c_int(self.win_nr), _ip(tg), _ip(st), fl.ctypes.data_as(C.c_void_p), _fp(rtz))
+        adH = np.ascontiguousarray(W["adH"], dtype=np.float64); adT = np.ascontiguousarray(W["adT"], dtype=np.float64)
+        dl, cd = f32(W["adHTdelta"]), f32(W["c_delta"])
+        cp = np.ascontiguousarray(W["c_prior"], dtype=np.float64)
+        fp_ = np.ascontiguousarray(W["frame_prior"], dtype=np.float64)
+        fd = np.ascontiguousarray(W["frame_delta_prior"], dtype=np.float64)
+        self._call("window_set_adjoints", _dp(adH), _dp(adT), _fp(dl), _fp(cd), _dp(cp), _dp(fp_), _dp(fd))
+
+    def window_set_idepth(self, idepth, idepth_zero):
+        a, b = f32(idepth), f32(idepth_zero)
+        self._call("window_set_idepth", _fp(a), _fp(b))
+
+    def window_linearize(self, fix=False):
+        stats = np.zeros(3, dtype=np.float64)
+        th = C.c_float()
+        self._call("window_linearize", C.c_int(1 if fix else 0), _dp(stats), C.byref(th))
+        return stats, th.value
+
+    def window_apply_res(self):
+        self._call("window_apply_res")
+
+    def window_reset_oob(self):
+        self._call("window_reset_oob")
+
+    def window_fix_linearization(self, mask):
+        m = np.ascontiguousarray(mask, dtype=np.uint8)
+        self._call("window_fix_linearization", m.ctypes.data_as(C.c_void_p))
+
+    def window_accumulate(self):
+        D = 8 * self.win_n + 4
+        Hs = [np.zeros((D, D)) for _ in range(3)]
+        bs = [np.zeros(D) for _ in range(3)]
+        cnt = np.zeros(2, dtype=np.int32)
+        self._call("window_accumulate", _dp(Hs[0]), _dp(bs[0]), _dp(Hs[1]), _dp(bs[1]), _dp(Hs[2]), _dp(bs[2]), _ip(cnt))
+        return dict(HA=Hs[0], bA=bs[0], HL=Hs[1], bL=bs[1], Hsc=Hs[2], bsc=bs[2], counts=cnt)
+
+    def window_solve(self, iteration, lam, acc, HM, bM, delta, N=None):
+        D = 8 * self.win_n + 4
+        x = np.zeros(D)
+        c64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        HM, bM, delta = c64(HM), c64(bM), c64(delta)
+        Nn = c64(N) if N is not None else None
+        self._call("window_solve", C.c_int(iteration), C.c_double(lam), _dp(acc["HA"]), _dp(acc["bA"]), _dp(acc["HL"]),
+                   _dp(acc["bL"]), _dp(acc["Hsc"]), _dp(acc["bsc"]), _dp(HM), _dp(bM), _dp(delta), _dp(Nn),
+                   C.c_int(0 if N is None else Nn.shape[1]), _dp(x))
+        return x
+
+    def window_resubstitute(self, x, lam=0.0):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        step = np.zeros(self.win_np, dtype=np.float32)
+        self._call("window_resubstitute", _dp(x), C.c_float(lam), _fp(step))
+        return step
+
+    def window_residual_floats(self, what):
+        k = {0: 72, 1: 8, 2: 8, 3: 3}.get(what, 1)
+        out = np.zeros((self.win_nr, k) if k > 1 else self.win_nr, dtype=np.float32)
+        self._call("window_get_residual_floats", C.c_int(what), _fp(out))
+        return out
+
+    def window_residual_ints(self, what):
+        out = np.zeros(self.win_nr, dtype=np.int32)
+        self._call("window_get_residual_ints", C.c_int(what), _ip(out))
+        return out
+
+    def window_point_floats(self, what):
+        k = 4 if what in (2, 5) else 1
+        out = np.zeros((self.win_np, k) if k > 1 else self.win_np, dtype=np.float32)
+        self._call("window_get_point_floats", C.c_int(what), _fp(out))
+        return out
+
+
 _gpu_api = None
 
 

@@ -91,6 +91,7 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaMemset(c->trk_counter, 0, sizeof(unsigned int)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->trk_result_dev, 64 * sizeof(double)));
     LDSO_CUDA_OK(c, cudaMallocHost(&c->trk_result_pinned, 64 * sizeof(double)));
+    if (win_alloc(c)) return -1;
     LDSO_CUDA_OK(c, cudaDeviceSynchronize());
     return 0;
 }
@@ -127,6 +128,7 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
         }
         cudaFree(c->trk[t].row_cnt); cudaFree(c->trk[t].pc_n_dev);
     }
+    win_free(c);
     cudaFree(c->img_dev); cudaFreeHost(c->img_pinned); cudaFreeHost(c->scratch_host); cudaFree(c->gammaB_dev);
     cudaFree(c->trk_partials); cudaFree(c->trk_partials_i); cudaFree(c->trk_counter); cudaFree(c->trk_result_dev);
     cudaFreeHost(c->trk_result_pinned);

@@ -11,6 +11,7 @@
 
 #include "../../include/ldso_gpu.h"
 #include "../../include/ldso_smallmat.h"
+#include "window.h"
 
 #define LDSO_CUDA_OK(ctx, expr)                                                                      \
     do {                                                                                             \
@@ -83,6 +84,7 @@ struct ldso_gpu_ctx {
     unsigned int* trk_counter = nullptr;
     double* trk_result_dev = nullptr;       // [64]
     double* trk_result_pinned = nullptr;    // [64]
+    WindowDev win;
     long long launches = 0;
     // optional per-kernel CUDA-event profile (ldso_gpu_profile_*): [0] = fused tracker kernel
     int profile_on = 0;

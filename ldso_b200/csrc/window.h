@@ -1,0 +1,74 @@
+// window.h — device-resident sliding window (points, residuals, accumulators) of one sequence.
+// Internal to libldso_gpu.so; the public face is the ldso_gpu_window_* group of include/ldso_gpu.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <vector>
+
+#include "../../include/ldso_gpu.h"
+
+#define WIN_TOP_STRIDE 96    // 91 unique AccumulatorApprox entries (55 + 30 + 6), padded
+#define WIN_PT_ROWS 16       // per-point output rows, see PT_* below
+
+// rows of WindowDev::pt_out ([row][cap_p])
+enum { PT_HDD_A = 0, PT_BD_A = 1, PT_HCD_A = 2 /*..5*/, PT_HDD_L = 6, PT_BD_L = 7, PT_HCD_L = 8 /*..11*/, PT_HDI = 12,
+       PT_BDSUM = 13, PT_IDH = 14, PT_STEP = 15 };
+
+struct WindowDev {
+    int n = 0, np = 0, nr = 0;
+    int cap_p = 0, cap_r = 0;
+    int slots[LDSO_MAX_WINDOW];
+    float frameEnergyTH[LDSO_MAX_WINDOW];
+    float fxl = 0, fyl = 0, cxl = 0, cyl = 0, fxli = 0, fyli = 0;
+    // device: frames
+    float* precalc = nullptr;      // [n*n][32]
+    // device: points (SoA)
+    float *u = nullptr, *v = nullptr, *idepth = nullptr, *idepth_zero = nullptr, *prior = nullptr;
+    float *color = nullptr, *weights = nullptr;   // [cap_p][8]
+    int *host = nullptr, *res_begin = nullptr;
+    float* pt_out = nullptr;       // [WIN_PT_ROWS][cap_p]
+    float* max_rel_baseline = nullptr;   // [cap_p] (atomicMax on the bit pattern: values are >= 0)
+    float* num_good = nullptr;     // [cap_p]
+    // device: residuals
+    int *r_point = nullptr, *r_target = nullptr, *state = nullptr, *new_state = nullptr, *flags = nullptr;
+    float *energy = nullptr, *new_energy = nullptr, *new_energy_wo = nullptr;
+    float* J = nullptr;            // [cap_r][72]  AoS record = RawResidualJacobian
+    float* rtz = nullptr;          // [cap_r][8]   res_toZeroF
+    float* JpJdF = nullptr;        // [cap_r][8]
+    float* center = nullptr;       // [cap_r][4]   centerProjectedTo (+pad)
+    float* res_pt = nullptr;       // [cap_r][8]   per-residual Hdd, bd, Hcd[4] contribution + mode tag
+    int* order = nullptr;          // residual ids sorted by accumulator key (mode * n^2 + host + n * target)
+    int* chunk = nullptr;          // [n_chunks][3] = key, start, count
+    int n_chunks = 0;
+    int* sc_blocks = nullptr;      // [n_sc_blocks][3] = host, first point, end point (K9 CTA table)
+    int n_sc_blocks = 0;
+    // device: small tables
+    float* adHTdelta = nullptr;    // [n*n][8]
+    float* xAd = nullptr;          // [n*n][8] + xc[4]
+    double* stats = nullptr;       // [4]
+    // device: accumulators (double, filled with atomicAdd of per-CTA fp32 partial sums)
+    double* acc_top = nullptr;     // [2][n*n][WIN_TOP_STRIDE]
+    int* acc_top_cnt = nullptr;    // [2][n*n]
+    double* acc_sc = nullptr;      // accD [n^3][64] | accE [n^2][32] | accEB [n^2][8] | accHcc [16] | accbc [4]
+    size_t acc_sc_size = 0;
+    // host mirrors
+    std::vector<int> h_host, h_res_begin, h_target, h_point, h_host_begin;
+    std::vector<unsigned char> h_lin;
+    std::vector<double> adHost, adTarget, fprior, fdelta_prior;
+    std::vector<float> adHostF, adTargetF;
+    float cDeltaF[4] = {0, 0, 0, 0};
+    double cPrior[4] = {0, 0, 0, 0};
+    // pinned staging
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+};
+
+struct ldso_gpu_ctx;
+int win_alloc(ldso_gpu_ctx* c);
+void win_free(ldso_gpu_ctx* c);
+int k7_linearize(ldso_gpu_ctx* c, int fix);
+int k7_apply_res(ldso_gpu_ctx* c);
+int k7_reset_oob(ldso_gpu_ctx* c);
+int k7_fix_linearization(ldso_gpu_ctx* c, const unsigned char* mask_dev);
+int k8_accumulate_top(ldso_gpu_ctx* c);
+int k9_accumulate_sc(ldso_gpu_ctx* c);
+int k10_resubstitute(ldso_gpu_ctx* c, float lambda);

@@ -1,0 +1,615 @@
+// window_api.cu — C-ABI entry points of the windowed bundle adjustment (ldso_gpu_window_*): window upload,
+// launch of K7-K10, and the small dense fp64 host algebra (H1) the reference keeps on the host too:
+// stitching the accumulators with the adjoints (AccumulatedTopHessian.cc:193-255,
+// AccumulatedSCHessian.cc:53-119) and the dense part of EnergyFunctional::solveSystemF (:310-432).
+#include "ctx.h"
+
+#include <algorithm>
+#include <cmath>
+
+#define CPARS 4
+
+namespace {
+
+template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
+    LDSO_CUDA_OK(c, cudaMalloc((void**)p, n * sizeof(T)));
+    return 0;
+}
+
+// pinned staging that grows on demand (window uploads happen once per keyframe, not per frame)
+void* staging(ldso_gpu_ctx* c, size_t bytes) {
+    WindowDev& W = c->win;
+    if (W.pinned_bytes < bytes) {
+        if (W.pinned) cudaFreeHost(W.pinned);
+        W.pinned = nullptr;
+        size_t nb = std::max(bytes, (size_t)1 << 20);
+        if (cudaMallocHost(&W.pinned, nb) != cudaSuccess) { W.pinned_bytes = 0; return nullptr; }
+        W.pinned_bytes = nb;
+    }
+    return W.pinned;
+}
+
+int upload(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
+    if (bytes == 0) return 0;
+    // synchronous w.r.t. the host buffer: copy through pinned staging, then wait (cold path)
+    void* st = staging(c, bytes);
+    if (!st) { c->set_error("pinned staging allocation failed", __FILE__, __LINE__); return -1; }
+    memcpy(st, src, bytes);
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(dst, st, bytes, cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+int download(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
+    if (bytes == 0) return 0;
+    void* st = staging(c, bytes);
+    if (!st) { c->set_error("pinned staging allocation failed", __FILE__, __LINE__); return -1; }
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    memcpy(dst, st, bytes);
+    return 0;
+}
+
+}  // namespace
+
+int win_alloc(ldso_gpu_ctx* c) {
+    WindowDev& W = c->win;
+    W.cap_p = std::max(c->cfg.max_points, 16);
+    W.cap_r = std::max(c->cfg.max_residuals, 16);
+    const size_t P = W.cap_p, R = W.cap_r, M = LDSO_MAX_WINDOW;
+    int rc = 0;
+    rc |= dalloc(c, &W.precalc, M * M * LDSO_PRECALC_STRIDE);
+    rc |= dalloc(c, &W.u, P); rc |= dalloc(c, &W.v, P); rc |= dalloc(c, &W.idepth, P); rc |= dalloc(c, &W.idepth_zero, P);
+    rc |= dalloc(c, &W.prior, P); rc |= dalloc(c, &W.color, 8 * P); rc |= dalloc(c, &W.weights, 8 * P);
+    rc |= dalloc(c, &W.host, P); rc |= dalloc(c, &W.res_begin, P + 1);
+    rc |= dalloc(c, &W.pt_out, WIN_PT_ROWS * P); rc |= dalloc(c, &W.max_rel_baseline, P); rc |= dalloc(c, &W.num_good, P);
+    rc |= dalloc(c, &W.r_point, R); rc |= dalloc(c, &W.r_target, R); rc |= dalloc(c, &W.state, R); rc |= dalloc(c, &W.new_state, R);
+    rc |= dalloc(c, &W.flags, R); rc |= dalloc(c, &W.energy, R); rc |= dalloc(c, &W.new_energy, R);
+    rc |= dalloc(c, &W.new_energy_wo, R);
+    rc |= dalloc(c, &W.J, R * LDSO_J_FLOATS); rc |= dalloc(c, &W.rtz, R * 8); rc |= dalloc(c, &W.JpJdF, R * 8);
+    rc |= dalloc(c, &W.center, R * 4); rc |= dalloc(c, &W.res_pt, R * 8);
+    rc |= dalloc(c, &W.order, R); rc |= dalloc(c, &W.chunk, 3 * (R / 1 + 2 * M * M + 8));
+    rc |= dalloc(c, &W.sc_blocks, 3 * (P + M + 8));
+    rc |= dalloc(c, &W.adHTdelta, M * M * 8); rc |= dalloc(c, &W.xAd, M * M * 8 + 8); rc |= dalloc(c, &W.stats, 4);
+    rc |= dalloc(c, &W.acc_top, 2 * M * M * WIN_TOP_STRIDE); rc |= dalloc(c, &W.acc_top_cnt, 2 * M * M);
+    W.acc_sc_size = M * M * M * 64 + M * M * 40 + 20;
+    rc |= dalloc(c, &W.acc_sc, W.acc_sc_size);
+    return rc ? -1 : 0;
+}
+
+void win_free(ldso_gpu_ctx* c) {
+    WindowDev& W = c->win;
+    void* ptrs[] = {W.precalc, W.u, W.v, W.idepth, W.idepth_zero, W.prior, W.color, W.weights, W.host, W.res_begin, W.pt_out,
+                    W.max_rel_baseline, W.num_good, W.r_point, W.r_target, W.state, W.new_state, W.flags, W.energy, W.new_energy,
+                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.adHTdelta, W.xAd,
+                    W.stats, W.acc_top, W.acc_top_cnt, W.acc_sc};
+    for (void* p : ptrs) cudaFree(p);
+    if (W.pinned) cudaFreeHost(W.pinned);
+}
+
+// ---- window description --------------------------------------------------------------------------
+extern "C" int ldso_gpu_window_set_frames(ldso_gpu_ctx* c, int n, const int* slots, const float* precalc, const float* eth,
+                                          const float calib[4]) {
+    LDSO_REQUIRE(c, n >= 1 && n <= LDSO_MAX_WINDOW && slots && precalc && eth && calib);
+    WindowDev& W = c->win;
+    for (int i = 0; i < n; i++) {
+        LDSO_REQUIRE(c, slots[i] >= 0 && slots[i] < c->cfg.n_frame_slots);
+        W.slots[i] = slots[i];
+        W.frameEnergyTH[i] = eth[i];
+    }
+    W.n = n;
+    W.fxl = calib[0]; W.fyl = calib[1]; W.cxl = calib[2]; W.cyl = calib[3];
+    W.fxli = 1.0f / W.fxl; W.fyli = 1.0f / W.fyl;   // CalibHessian::value_scaledi (include/internal/CalibHessian.h:93-99)
+    return upload(c, W.precalc, precalc, sizeof(float) * n * n * LDSO_PRECALC_STRIDE);
+}
+
+extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* u, const float* v, const float* idepth,
+                                          const float* idepth_zero, const int* host, const float* color, const float* weights,
+                                          const float* prior, const int* res_begin) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, np >= 0 && np <= W.cap_p && W.n > 0);
+    LDSO_REQUIRE(c, np == 0 || (u && v && idepth && idepth_zero && host && color && weights && prior && res_begin));
+    for (int i = 0; i < np; i++) LDSO_REQUIRE(c, host[i] >= 0 && host[i] < W.n && (i == 0 || host[i] >= host[i - 1]));
+    W.np = np;
+    W.h_host.assign(host, host + np);
+    W.h_res_begin.assign(res_begin, res_begin + np + 1);
+    int rc = 0;
+    rc |= upload(c, W.u, u, sizeof(float) * np); rc |= upload(c, W.v, v, sizeof(float) * np);
+    rc |= upload(c, W.idepth, idepth, sizeof(float) * np); rc |= upload(c, W.idepth_zero, idepth_zero, sizeof(float) * np);
+    rc |= upload(c, W.host, host, sizeof(int) * np); rc |= upload(c, W.color, color, sizeof(float) * 8 * np);
+    rc |= upload(c, W.weights, weights, sizeof(float) * 8 * np); rc |= upload(c, W.prior, prior, sizeof(float) * np);
+    rc |= upload(c, W.res_begin, res_begin, sizeof(int) * (np + 1));
+    if (rc) return -1;
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * WIN_PT_ROWS * W.cap_p, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.max_rel_baseline, 0, sizeof(float) * W.cap_p, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.num_good, 0, sizeof(float) * W.cap_p, c->stream));
+    // K9 CTA table: 64 consecutive points of one host per CTA
+    std::vector<int> blk;
+    int p = 0;
+    while (p < np) {
+        int h = host[p], e = p;
+        while (e < np && host[e] == h && e - p < 64) e++;
+        blk.push_back(h); blk.push_back(p); blk.push_back(e);
+        p = e;
+    }
+    W.n_sc_blocks = (int)blk.size() / 3;
+    return upload(c, W.sc_blocks, blk.data(), sizeof(int) * blk.size());
+}
+
+// (re)build the K8 work list: residual ids sorted by key = mode * n^2 + host + n * target, cut into <=128 chunks
+static int build_order(ldso_gpu_ctx* c) {
+    WindowDev& W = c->win;
+    const int nn = W.n * W.n, nr = W.nr;
+    std::vector<int> cnt(2 * nn + 1, 0), key(nr);
+    for (int r = 0; r < nr; r++) {
+        key[r] = (W.h_lin[r] ? nn : 0) + W.h_host[W.h_point[r]] + W.n * W.h_target[r];
+        cnt[key[r] + 1]++;
+    }
+    for (int k = 0; k < 2 * nn; k++) cnt[k + 1] += cnt[k];
+    std::vector<int> order(nr), pos(cnt.begin(), cnt.end() - 1), chunk;
+    for (int r = 0; r < nr; r++) order[pos[key[r]]++] = r;
+    for (int k = 0; k < 2 * nn; k++)
+        for (int s = cnt[k]; s < cnt[k + 1]; s += 128) {
+            chunk.push_back(k); chunk.push_back(s); chunk.push_back(std::min(128, cnt[k + 1] - s));
+        }
+    W.n_chunks = (int)chunk.size() / 3;
+    int rc = upload(c, W.order, order.data(), sizeof(int) * nr);
+    rc |= upload(c, W.chunk, chunk.data(), sizeof(int) * chunk.size());
+    return rc ? -1 : 0;
+}
+
+extern "C" int ldso_gpu_window_set_residuals(ldso_gpu_ctx* c, int nr, const int* target, const int* state,
+                                             const unsigned char* flags, const float* res_to_zero) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, nr >= 0 && nr <= W.cap_r && (int)W.h_res_begin.size() == W.np + 1 && W.h_res_begin[W.np] == nr);
+    LDSO_REQUIRE(c, nr == 0 || (target && state && flags));
+    W.nr = nr;
+    W.h_target.assign(target, target + nr);
+    W.h_point.resize(nr);
+    W.h_lin.resize(nr);
+    std::vector<int> fl(nr);
+    for (int p = 0; p < W.np; p++)
+        for (int r = W.h_res_begin[p]; r < W.h_res_begin[p + 1]; r++) W.h_point[r] = p;
+    for (int r = 0; r < nr; r++) {
+        LDSO_REQUIRE(c, target[r] >= 0 && target[r] < W.n);
+        fl[r] = flags[r];
+        W.h_lin[r] = (flags[r] & LDSO_RF_LINEARIZED) ? 1 : 0;
+    }
+    int rc = 0;
+    rc |= upload(c, W.r_target, target, sizeof(int) * nr); rc |= upload(c, W.r_point, W.h_point.data(), sizeof(int) * nr);
+    rc |= upload(c, W.state, state, sizeof(int) * nr); rc |= upload(c, W.flags, fl.data(), sizeof(int) * nr);
+    if (rc) return -1;
+    std::vector<int> ns(nr, LDSO_RES_OUTLIER);
+    rc |= upload(c, W.new_state, ns.data(), sizeof(int) * nr);
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.energy, 0, sizeof(float) * nr, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.new_energy, 0, sizeof(float) * nr, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.new_energy_wo, 0, sizeof(float) * nr, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.J, 0, sizeof(float) * (size_t)nr * LDSO_J_FLOATS, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.JpJdF, 0, sizeof(float) * (size_t)nr * 8, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.center, 0, sizeof(float) * (size_t)nr * 4, c->stream));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.res_pt, 0, sizeof(float) * (size_t)nr * 8, c->stream));
+    if (res_to_zero) rc |= upload(c, W.rtz, res_to_zero, sizeof(float) * 8 * (size_t)nr);
+    else LDSO_CUDA_OK(c, cudaMemsetAsync(W.rtz, 0, sizeof(float) * (size_t)nr * 8, c->stream));
+    if (rc) return -1;
+    return build_order(c);
+}
+
+extern "C" int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* c, const double* adH, const double* adT, const float* adHTdelta,
+                                            const float cDelta[4], const double cPrior[4], const double* fprior,
+                                            const double* fdelta_prior) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && adH && adT && adHTdelta && cDelta && cPrior && fprior && fdelta_prior);
+    const int nn = W.n * W.n;
+    W.adHost.assign(adH, adH + 64 * nn); W.adTarget.assign(adT, adT + 64 * nn);
+    W.adHostF.resize(64 * nn); W.adTargetF.resize(64 * nn);
+    for (int i = 0; i < 64 * nn; i++) { W.adHostF[i] = (float)adH[i]; W.adTargetF[i] = (float)adT[i]; }
+    for (int i = 0; i < 4; i++) { W.cDeltaF[i] = cDelta[i]; W.cPrior[i] = cPrior[i]; }
+    W.fprior.assign(fprior, fprior + 8 * W.n); W.fdelta_prior.assign(fdelta_prior, fdelta_prior + 8 * W.n);
+    return upload(c, W.adHTdelta, adHTdelta, sizeof(float) * 8 * nn);
+}
+
+extern "C" int ldso_gpu_window_set_idepth(ldso_gpu_ctx* c, const float* idepth, const float* idepth_zero) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, idepth && idepth_zero);
+    int rc = upload(c, W.idepth, idepth, sizeof(float) * W.np);
+    rc |= upload(c, W.idepth_zero, idepth_zero, sizeof(float) * W.np);
+    return rc ? -1 : 0;
+}
+
+// ---- K7 ------------------------------------------------------------------------------------------
+extern "C" int ldso_gpu_window_linearize(ldso_gpu_ctx* c, int fix, double stats[3], float* new_th) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && stats);
+    int rc = k7_linearize(c, fix);
+    if (rc) return rc;
+    // read back [sum E, #IN] and the per-residual energies the frame threshold is drawn from
+    const size_t bytes = 4 * sizeof(double) + sizeof(float) * (size_t)W.nr;
+    char* st = (char*)staging(c, bytes);
+    LDSO_REQUIRE(c, st != nullptr);
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, W.stats, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (W.nr) LDSO_CUDA_OK(c, cudaMemcpyAsync(st + 4 * sizeof(double), W.new_energy_wo, sizeof(float) * W.nr, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    const double* ds = (const double*)st;
+    stats[0] = ds[0]; stats[1] = 0; stats[2] = ds[1];
+    // FullSystem::setNewFrameEnergyTH (src/frontend/FullSystem.cc:2078-2109): 70th percentile over the residuals
+    // into the newest frame — a selection over ~2000 floats whose result the host needs anyway
+    const float* e = (const float*)(st + 4 * sizeof(double));
+    std::vector<float> all;
+    const int newest = W.n - 1;
+    for (int r = 0; r < W.nr; r++)
+        if (!W.h_lin[r] && W.h_target[r] == newest && e[r] >= 0) all.push_back(e[r]);
+    float th;
+    if (all.empty()) {
+        th = 12 * 12 * LDSO_PATTERN_NUM;
+    } else {
+        int nth = (int)(c->cfg.frame_energy_th_n * all.size());
+        std::nth_element(all.begin(), all.begin() + nth, all.end());
+        th = sqrtf(all[nth]) * c->cfg.frame_energy_th_fac_median;
+        th = 26.0f * c->cfg.frame_energy_th_const_weight + th * (1 - c->cfg.frame_energy_th_const_weight);
+        th = th * th;
+        th *= c->cfg.overall_energy_th_weight * c->cfg.overall_energy_th_weight;
+    }
+    W.frameEnergyTH[newest] = th;
+    if (new_th) *new_th = th;
+    return 0;
+}
+
+extern "C" int ldso_gpu_window_apply_res(ldso_gpu_ctx* c) { return k7_apply_res(c); }
+extern "C" int ldso_gpu_window_reset_oob(ldso_gpu_ctx* c) { return k7_reset_oob(c); }
+
+extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned char* mask) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, mask || W.nr == 0);
+    if (W.nr == 0) return 0;
+    // the mask rides in the (currently unused) res_pt scratch rows? no: keep it simple, stage it in `order`'s tail
+    unsigned char* dmask = reinterpret_cast<unsigned char*>(W.res_pt);   // res_pt is rewritten by the next K8 launch
+    int rc = upload(c, dmask, mask, W.nr);
+    if (rc) return rc;
+    rc = k7_fix_linearization(c, dmask);
+    if (rc) return rc;
+    for (int r = 0; r < W.nr; r++)
+        if (mask[r]) W.h_lin[r] = 1;
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    return build_order(c);
+}
+
+// ---- K8 + K9 + stitching -------------------------------------------------------------------------
+namespace {
+
+struct Dense {
+    int D;
+    double* H;
+    double* b;
+    double& at(int r, int cc) { return H[(size_t)r * D + cc]; }
+    // H[r0.., c0..] += A(8x8) * M(8 x m) * B^T (m x 8), m == 8
+    void add_ABt(int r0, int c0, const double* AM, const double* B) {
+        for (int i = 0; i < 8; i++)
+            for (int j = 0; j < 8; j++) {
+                double s = 0;
+                for (int l = 0; l < 8; l++) s += AM[i * 8 + l] * B[j * 8 + l];
+                at(r0 + i, c0 + j) += s;
+            }
+    }
+};
+
+void mul88(const double* A, const double* M, double* out) {
+    for (int i = 0; i < 8; i++)
+        for (int j = 0; j < 8; j++) {
+            double s = 0;
+            for (int l = 0; l < 8; l++) s += A[i * 8 + l] * M[l * 8 + j];
+            out[i * 8 + j] = s;
+        }
+}
+
+// AccumulatorApprox::finish layout -> 13x13 (MatrixAccumulators.h:771-800)
+void unpack13(const double* a, double M[13][13]) {
+    int idx = 0;
+    for (int r = 0; r < 10; r++)
+        for (int cc = r; cc < 10; cc++) M[r][cc] = M[cc][r] = a[idx++];
+    for (int r = 0; r < 10; r++)
+        for (int cc = 0; cc < 3; cc++) M[r][10 + cc] = M[10 + cc][r] = a[55 + 3 * r + cc];
+    M[10][10] = a[85]; M[10][11] = M[11][10] = a[86]; M[10][12] = M[12][10] = a[87];
+    M[11][11] = a[88]; M[11][12] = M[12][11] = a[89]; M[12][12] = a[90];
+}
+
+// AccumulatedTopHessianSSE::stitchDoubleInternal + the symmetrisation of stitchDoubleMT
+void stitch_top(WindowDev& W, const double* acc, const int* cnt, bool usePrior, double* Hout, double* bout) {
+    const int n = W.n, D = 8 * n + CPARS;
+    Dense S{D, Hout, bout};
+    std::fill(Hout, Hout + (size_t)D * D, 0.0);
+    std::fill(bout, bout + D, 0.0);
+    for (int k = 0; k < n * n; k++) {
+        if (cnt[k] == 0) continue;
+        const int h = k % n, t = k / n, hI = CPARS + 8 * h, tI = CPARS + 8 * t;
+        double M[13][13];
+        unpack13(acc + (size_t)k * WIN_TOP_STRIDE, M);
+        const double* AH = &W.adHost[64 * k];
+        const double* AT = &W.adTarget[64 * k];
+        double P[64], AHP[64], ATP[64];
+        for (int i = 0; i < 8; i++)
+            for (int j = 0; j < 8; j++) P[i * 8 + j] = M[CPARS + i][CPARS + j];
+        mul88(AH, P, AHP);
+        mul88(AT, P, ATP);
+        S.add_ABt(hI, hI, AHP, AH);
+        S.add_ABt(tI, tI, ATP, AT);
+        S.add_ABt(hI, tI, AHP, AT);
+        for (int i = 0; i < 8; i++) {
+            double bh = 0, bt = 0;
+            for (int l = 0; l < 8; l++) { bh += AH[i * 8 + l] * M[CPARS + l][8 + CPARS]; bt += AT[i * 8 + l] * M[CPARS + l][8 + CPARS]; }
+            bout[hI + i] += bh; bout[tI + i] += bt;
+            for (int j = 0; j < CPARS; j++) {
+                double sh = 0, st = 0;
+                for (int l = 0; l < 8; l++) { sh += AH[i * 8 + l] * M[CPARS + l][j]; st += AT[i * 8 + l] * M[CPARS + l][j]; }
+                S.at(hI + i, j) += sh; S.at(tI + i, j) += st;
+            }
+        }
+        for (int i = 0; i < CPARS; i++) {
+            for (int j = 0; j < CPARS; j++) S.at(i, j) += M[i][j];
+            bout[i] += M[i][8 + CPARS];
+        }
+    }
+    if (usePrior) {
+        for (int i = 0; i < CPARS; i++) { S.at(i, i) += W.cPrior[i]; bout[i] += W.cPrior[i] * (double)W.cDeltaF[i]; }
+        for (int h = 0; h < n; h++)
+            for (int i = 0; i < 8; i++) {
+                S.at(CPARS + 8 * h + i, CPARS + 8 * h + i) += W.fprior[8 * h + i];
+                bout[CPARS + 8 * h + i] += W.fprior[8 * h + i] * W.fdelta_prior[8 * h + i];
+            }
+    }
+    for (int h = 0; h < n; h++) {
+        const int hI = CPARS + 8 * h;
+        for (int i = 0; i < CPARS; i++)
+            for (int j = 0; j < 8; j++) S.at(i, hI + j) = S.at(hI + j, i);
+        for (int t = h + 1; t < n; t++) {
+            const int tI = CPARS + 8 * t;
+            for (int i = 0; i < 8; i++)
+                for (int j = 0; j < 8; j++) S.at(hI + i, tI + j) += S.at(tI + j, hI + i);
+            for (int i = 0; i < 8; i++)
+                for (int j = 0; j < 8; j++) S.at(tI + i, hI + j) = S.at(hI + j, tI + i);
+        }
+    }
+}
+
+// AccumulatedSCHessianSSE::stitchDoubleInternal + stitchDoubleMT tail
+void stitch_sc(WindowDev& W, const double* acc, double* Hout, double* bout) {
+    const int n = W.n, nn = n * n, D = 8 * n + CPARS;
+    Dense S{D, Hout, bout};
+    std::fill(Hout, Hout + (size_t)D * D, 0.0);
+    std::fill(bout, bout + D, 0.0);
+    const double* accD = acc;
+    const double* accE = acc + (size_t)nn * n * 64;
+    const double* accEB = accE + (size_t)nn * 32;
+    const double* accHcc = accEB + (size_t)nn * 8;
+    const double* accbc = accHcc + 16;
+    for (int ij = 0; ij < nn; ij++) {
+        const int i = ij % n, j = ij / n, iI = CPARS + 8 * i, jI = CPARS + 8 * j;
+        const double* AHij = &W.adHost[64 * ij];
+        const double* ATij = &W.adTarget[64 * ij];
+        const double* E = accE + (size_t)ij * 32;
+        const double* EB = accEB + (size_t)ij * 8;
+        for (int a = 0; a < 8; a++) {
+            double bh = 0, bt = 0;
+            for (int l = 0; l < 8; l++) { bh += AHij[a * 8 + l] * EB[l]; bt += ATij[a * 8 + l] * EB[l]; }
+            bout[iI + a] += bh; bout[jI + a] += bt;
+            for (int q = 0; q < CPARS; q++) {
+                double sh = 0, st = 0;
+                for (int l = 0; l < 8; l++) { sh += AHij[a * 8 + l] * E[l * 4 + q]; st += ATij[a * 8 + l] * E[l * 4 + q]; }
+                S.at(iI + a, q) += sh; S.at(jI + a, q) += st;
+            }
+        }
+        for (int k = 0; k < n; k++) {
+            const double* Dm = accD + (size_t)(ij + k * nn) * 64;
+            bool any = false;
+            for (int q = 0; q < 64 && !any; q++) any = Dm[q] != 0.0;
+            if (!any) continue;
+            const int kI = CPARS + 8 * k, ik = i + n * k;
+            const double* AHik = &W.adHost[64 * ik];
+            const double* ATik = &W.adTarget[64 * ik];
+            double AHD[64], ATD[64];
+            mul88(AHij, Dm, AHD);
+            mul88(ATij, Dm, ATD);
+            S.add_ABt(iI, iI, AHD, AHik);
+            S.add_ABt(jI, kI, ATD, ATik);
+            S.add_ABt(jI, iI, ATD, AHik);
+            S.add_ABt(iI, kI, AHD, ATik);
+        }
+    }
+    for (int a = 0; a < CPARS; a++) {
+        for (int q = 0; q < CPARS; q++) S.at(a, q) += accHcc[a * 4 + q];
+        bout[a] += accbc[a];
+    }
+    for (int h = 0; h < n; h++)
+        for (int a = 0; a < CPARS; a++)
+            for (int q = 0; q < 8; q++) S.at(a, CPARS + 8 * h + q) = S.at(CPARS + 8 * h + q, a);
+}
+
+}  // namespace
+
+extern "C" int ldso_gpu_window_accumulate(ldso_gpu_ctx* c, double* HA, double* bA, double* HL, double* bL, double* Hsc,
+                                          double* bsc, int counts[2]) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && HA && bA && HL && bL && Hsc && bsc);
+    LDSO_REQUIRE(c, (int)W.adHost.size() == 64 * W.n * W.n);
+    int rc = k8_accumulate_top(c);
+    if (rc) return rc;
+    rc = k9_accumulate_sc(c);
+    if (rc) return rc;
+    const int n = W.n, nn = n * n;
+    const size_t nTop = (size_t)2 * nn * WIN_TOP_STRIDE, nSc = (size_t)nn * n * 64 + (size_t)nn * 40 + 20;
+    const size_t bytes = sizeof(double) * (nTop + nSc) + sizeof(int) * 2 * nn;
+    char* st = (char*)staging(c, bytes);
+    LDSO_REQUIRE(c, st != nullptr);
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, W.acc_top, sizeof(double) * nTop, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + sizeof(double) * nTop, W.acc_sc, sizeof(double) * nSc, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + sizeof(double) * (nTop + nSc), W.acc_top_cnt, sizeof(int) * 2 * nn, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    const double* top = (const double*)st;
+    const double* sc = top + nTop;
+    const int* cnt = (const int*)(st + sizeof(double) * (nTop + nSc));
+    stitch_top(W, top, cnt, false, HA, bA);
+    stitch_top(W, top + (size_t)nn * WIN_TOP_STRIDE, cnt + nn, true, HL, bL);
+    stitch_sc(W, sc, Hsc, bsc);
+    if (counts) {
+        counts[0] = counts[1] = 0;
+        for (int k = 0; k < nn; k++) { counts[0] += cnt[k]; counts[1] += cnt[nn + k]; }
+    }
+    return 0;
+}
+
+// ---- H1: dense solve ------------------------------------------------------------------------------
+namespace {
+
+// x -= P x with P the symmetrised projector onto span(N) built from N's pseudo-inverse
+// (EnergyFunctional::orthogonalize, EnergyFunctional.cc:809-841; only the `b` form is used by solveSystemF)
+void project_out_nullspace(int D, const double* Nin, int k, double* x) {
+    std::vector<double> N((size_t)D * k), U((size_t)D * k), S(k), V((size_t)k * k), Npi((size_t)D * k);
+    for (int j = 0; j < k; j++) {
+        double s = 0;
+        for (int i = 0; i < D; i++) s += Nin[(size_t)i * k + j] * Nin[(size_t)i * k + j];
+        s = std::sqrt(s);
+        for (int i = 0; i < D; i++) N[(size_t)i * k + j] = Nin[(size_t)i * k + j] / s;
+    }
+    ldso_sm::jacobi_svd(D, k, N.data(), U.data(), S.data(), V.data());
+    double smax = 0;
+    for (int i = 0; i < k; i++) smax = std::max(smax, S[i]);
+    for (int i = 0; i < k; i++) S[i] = S[i] > 1e-5 * smax ? 1.0 / S[i] : 0.0;   // setting_solverModeDelta (src/Setting.cc:24)
+    for (int i = 0; i < D; i++)
+        for (int j = 0; j < k; j++) {
+            double s = 0;
+            for (int l = 0; l < k; l++) s += U[(size_t)i * k + l] * S[l] * V[(size_t)j * k + l];
+            Npi[(size_t)i * k + j] = s;
+        }
+    std::vector<double> px(k), nx(k);
+    for (int j = 0; j < k; j++) {
+        double a = 0, b = 0;
+        for (int i = 0; i < D; i++) { a += Npi[(size_t)i * k + j] * x[i]; b += N[(size_t)i * k + j] * x[i]; }
+        px[j] = a; nx[j] = b;
+    }
+    for (int i = 0; i < D; i++) {
+        double s = 0;
+        for (int j = 0; j < k; j++) s += N[(size_t)i * k + j] * px[j] + Npi[(size_t)i * k + j] * nx[j];
+        x[i] -= 0.5 * s;
+    }
+}
+
+}  // namespace
+
+extern "C" int ldso_gpu_window_solve(ldso_gpu_ctx* c, int iteration, double lambda, const double* HA, const double* bA,
+                                     const double* HL, const double* bL, const double* Hsc, const double* bsc, const double* HM,
+                                     const double* bM, const double* delta, const double* N, int n_null, double* x_out) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && HA && bA && HL && bL && Hsc && bsc && HM && bM && delta && x_out);
+    const int D = 8 * W.n + CPARS;
+    // setting_solverMode = SOLVER_FIX_LAMBDA | SOLVER_ORTHOGONALIZE_X_LATER (src/Setting.cc:23): lambda is pinned
+    (void)lambda;
+    const double lam = 1e-5;
+    const double scw = (double)(1.0f / (1 + lam));
+    std::vector<double> Hf((size_t)D * D), rhs(D), sdiag(D), y(D);
+    for (int i = 0; i < D; i++) {
+        double bm = bM[i];
+        for (int j = 0; j < D; j++) bm += HM[(size_t)i * D + j] * delta[j];   // bM_top = bM + HM * delta (:310)
+        rhs[i] = bL[i] + bm + bA[i] - bsc[i] / (1 + lam);
+        for (int j = i; j < D; j++) {   // only the upper triangle is defined (:347, :378), mirrored by selfadjointView
+            double v = HL[(size_t)i * D + j] + HM[(size_t)i * D + j] + HA[(size_t)i * D + j];
+            if (j == i) v *= (1 + lam);
+            v -= Hsc[(size_t)i * D + j] * scw;
+            Hf[(size_t)i * D + j] = Hf[(size_t)j * D + i] = v;
+        }
+    }
+    for (int i = 0; i < D; i++) sdiag[i] = 1.0 / std::sqrt(Hf[(size_t)i * D + i] + 10);   // :415
+    for (int i = 0; i < D; i++) {
+        rhs[i] *= sdiag[i];
+        for (int j = 0; j < D; j++) Hf[(size_t)i * D + j] *= sdiag[i] * sdiag[j];
+    }
+    ldso_sm::ldlt_solve(D, Hf.data(), rhs.data(), y.data());
+    for (int i = 0; i < D; i++) x_out[i] = sdiag[i] * y[i];
+    if (iteration >= 2 && N && n_null > 0) project_out_nullspace(D, N, n_null, x_out);
+    return 0;
+}
+
+// ---- K10 -----------------------------------------------------------------------------------------
+extern "C" int ldso_gpu_window_resubstitute(ldso_gpu_ctx* c, const double* x, float lambda, float* step_out) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && x && (int)W.adHostF.size() == 64 * W.n * W.n);
+    const int n = W.n;
+    // xAd[h*n + t] = x_h^T adHostF[h + n t] + x_t^T adTargetF[h + n t]   (EnergyFunctional.cc:618-627), float
+    std::vector<float> tab((size_t)n * n * 8 + 4);
+    for (int h = 0; h < n; h++)
+        for (int t = 0; t < n; t++) {
+            const float* AH = &W.adHostF[64 * (h + n * t)];
+            const float* AT = &W.adTargetF[64 * (h + n * t)];
+            for (int j = 0; j < 8; j++) {
+                float a = 0, b = 0;
+                for (int i = 0; i < 8; i++) {
+                    a += (float)x[CPARS + 8 * h + i] * AH[i * 8 + j];
+                    b += (float)x[CPARS + 8 * t + i] * AT[i * 8 + j];
+                }
+                tab[(size_t)(n * h + t) * 8 + j] = a + b;
+            }
+        }
+    for (int i = 0; i < 4; i++) tab[(size_t)n * n * 8 + i] = (float)x[i];
+    int rc = upload(c, W.xAd, tab.data(), sizeof(float) * tab.size());
+    if (rc) return rc;
+    rc = k10_resubstitute(c, lambda);
+    if (rc) return rc;
+    if (step_out) return download(c, step_out, W.pt_out + (size_t)PT_STEP * W.cap_p, sizeof(float) * W.np);
+    return 0;
+}
+
+// ---- read-backs -----------------------------------------------------------------------------------
+extern "C" int ldso_gpu_window_get_residual_floats(ldso_gpu_ctx* c, int what, float* dst) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, dst && what >= 0 && what <= 6);
+    const size_t nr = W.nr;
+    switch (what) {
+        case 0: return download(c, dst, W.J, sizeof(float) * nr * LDSO_J_FLOATS);
+        case 1: return download(c, dst, W.rtz, sizeof(float) * nr * 8);
+        case 2: return download(c, dst, W.JpJdF, sizeof(float) * nr * 8);
+        case 3: {
+            std::vector<float> t(nr * 4);
+            int rc = download(c, t.data(), W.center, sizeof(float) * nr * 4);
+            for (size_t r = 0; r < nr; r++) { dst[3 * r] = t[4 * r]; dst[3 * r + 1] = t[4 * r + 1]; dst[3 * r + 2] = t[4 * r + 2]; }
+            return rc;
+        }
+        case 4: return download(c, dst, W.new_energy, sizeof(float) * nr);
+        case 5: return download(c, dst, W.new_energy_wo, sizeof(float) * nr);
+        default: return download(c, dst, W.energy, sizeof(float) * nr);
+    }
+}
+
+extern "C" int ldso_gpu_window_get_residual_ints(ldso_gpu_ctx* c, int what, int* dst) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, dst && what >= 0 && what <= 2);
+    const int* src = what == 0 ? W.state : what == 1 ? W.new_state : W.flags;
+    return download(c, dst, src, sizeof(int) * (size_t)W.nr);
+}
+
+extern "C" int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* c, int what, float* dst) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, dst && what >= 0 && what <= 11);
+    const size_t np = W.np, cap = W.cap_p;
+    auto row = [&](int r, float* out) { return download(c, out, W.pt_out + (size_t)r * cap, sizeof(float) * np); };
+    auto rows4 = [&](int r0) {
+        std::vector<float> t(np);
+        for (int i = 0; i < 4; i++) {
+            int rc = row(r0 + i, t.data());
+            if (rc) return rc;
+            for (size_t p = 0; p < np; p++) dst[4 * p + i] = t[p];
+        }
+        return 0;
+    };
+    switch (what) {
+        case 0: return row(PT_HDD_A, dst);
+        case 1: return row(PT_BD_A, dst);
+        case 2: return rows4(PT_HCD_A);
+        case 3: return row(PT_HDD_L, dst);
+        case 4: return row(PT_BD_L, dst);
+        case 5: return rows4(PT_HCD_L);
+        case 6: return row(PT_HDI, dst);
+        case 7: return row(PT_BDSUM, dst);
+        case 8: return row(PT_IDH, dst);
+        case 9: return download(c, dst, W.max_rel_baseline, sizeof(float) * np);
+        case 10: return download(c, dst, W.num_good, sizeof(float) * np);
+        default: return row(PT_STEP, dst);
+    }
+}

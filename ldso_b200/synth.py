@@ -128,3 +128,80 @@ def pick_points(img, depth, n, seed=7, border=6):
     idepth = (1.0 / d).astype(np.float32)
     hdi = rng.uniform(1e-4, 5e-3, len(pts)).astype(np.float32)
     return u.astype(np.float32), v.astype(np.float32), idepth, hdi
+
+
+PATTERN = np.array([[0, -2], [-1, -1], [1, -1], [-2, 0], [0, 0], [2, 0], [-1, 1], [0, 2]], dtype=np.int64)   # src/Setting.cc:275
+
+
+def make_window(seed=1001, frame_ids=(40, 46, 52, 58, 64, 70, 76), pts_per_frame=300, w=640, h=480, fx=384.0, fy=384.0,
+                cx=319.5, cy=239.5, pose_noise=2e-4, idepth_noise=0.02, lin_frac=0.25, rng_seed=5):
+    """A frozen sliding window with realistic distributions: n keyframes of the synthetic sequence, points hosted in
+    every frame with ground-truth inverse depth (+noise), one residual per (point, other frame).  Returns a dict of the
+    arrays the window C ABI takes.  Frame states are slightly perturbed from ground truth so that the system has a
+    non-trivial gradient; the FEJ evaluation point differs slightly from the current state."""
+    from . import window_host as wh
+    rng = np.random.default_rng(rng_seed)
+    sc = Scene(seed)
+    n = len(frame_ids)
+    imgs, deps, w2c_gt = [], [], []
+    for i in frame_ids:
+        R, t = trajectory(i)
+        img, dep = render(sc, w, h, fx, fy, cx, cy, R, t)
+        imgs.append(img); deps.append(dep)
+        w2c_gt.append((R.T, -R.T @ t))
+
+    def perturb(T, s):
+        r = rng.normal(0, s, 3); dt = rng.normal(0, s, 3)
+        th = np.linalg.norm(r)
+        K = wh.hat(r / th) if th > 0 else np.zeros((3, 3))
+        dR = np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K
+        return dR @ T[0], dR @ T[1] + dt
+
+    w2c_eval = [perturb(T, pose_noise) for T in w2c_gt]
+    w2c = [perturb(T, pose_noise * 0.3) for T in w2c_eval]
+    aff0 = [(0.0, 0.0)] * n
+    aff = [(float(rng.normal(0, 0.01)), float(rng.normal(0, 0.5))) for _ in range(n)]
+    exposure = [1.0] * n
+    calib = (fx, fy, cx, cy)
+    precalc = wh.precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure)
+    adH, adT = wh.adjoints(w2c_eval, aff0, exposure)
+    state_minus_zero = [np.concatenate([rng.normal(0, 1e-3, 6), [aff[i][0] / wh.SCALE_A, aff[i][1] / wh.SCALE_B]]) for i in range(n)]
+    adHTdelta = wh.ad_ht_delta(adH, adT, state_minus_zero)
+    U, V, ID, IDZ, HOST, COL, WGT, PRIOR = [], [], [], [], [], [], [], []
+    res_begin, target, state, flags = [0], [], [], []
+    for hidx in range(n):
+        u, v, idp, _ = pick_points(imgs[hidx], deps[hidx], pts_per_frame, seed=hidx + 11, border=8)
+        u = np.round(u); v = np.round(v)                      # DSO points sit on integer pixels
+        gy, gx = np.gradient(imgs[hidx].astype(np.float64))
+        for k in range(len(u)):
+            xi, yi = int(u[k]), int(v[k])
+            px = xi + PATTERN[:, 0]; py = yi + PATTERN[:, 1]
+            col = imgs[hidx][py, px]
+            g2 = gx[py, px] ** 2 + gy[py, px] ** 2
+            wgt = np.sqrt(2500.0 / (2500.0 + g2))            # ImmaturePoint ctor, ImmaturePoint.cc:27-31
+            idn = idp[k] * (1 + idepth_noise * rng.standard_normal())
+            U.append(u[k]); V.append(v[k]); ID.append(idn); IDZ.append(idn * (1 + 1e-3 * rng.standard_normal()))
+            HOST.append(hidx); COL.append(col); WGT.append(wgt)
+            PRIOR.append(2500.0 if (hidx == 0 and k % 7 == 0) else 0.0)
+            for t in range(n):
+                if t == hidx:
+                    continue
+                target.append(t); state.append(0)
+                lin = rng.uniform() < lin_frac and t != n - 1
+                flags.append((1 | 2) if lin else 4)          # linearised residuals are active; fresh ones are new
+            res_begin.append(len(target))
+    nr = len(target)
+    D = 8 * n + 4
+    A = rng.normal(0, 1, (D, D))
+    HM = (A @ A.T) * 1e2
+    return dict(n=n, frame_ids=list(frame_ids), imgs=imgs, depths=deps, calib=np.array(calib, np.float32),
+                precalc=precalc, frame_energy_th=np.full(n, 8 * 8 * 8.0, np.float32), adH=adH, adT=adT, adHTdelta=adHTdelta,
+                c_delta=rng.normal(0, 1e-3, 4).astype(np.float32), c_prior=np.full(4, 5e9), 
+                frame_prior=np.where(np.arange(8 * n) < 8, 1e10, 0.0).astype(np.float64).reshape(n, 8),
+                frame_delta_prior=rng.normal(0, 1e-4, (n, 8)),
+                u=np.array(U, np.float32), v=np.array(V, np.float32), idepth=np.array(ID, np.float32),
+                idepth_zero=np.array(IDZ, np.float32), host=np.array(HOST, np.int32), color=np.array(COL, np.float32),
+                weights=np.array(WGT, np.float32), prior=np.array(PRIOR, np.float32), res_begin=np.array(res_begin, np.int32),
+                target=np.array(target, np.int32), state=np.array(state, np.int32), flags=np.array(flags, np.uint8),
+                res_to_zero=rng.normal(0, 2.0, (nr, 8)).astype(np.float32), HM=HM, bM=rng.normal(0, 10, D),
+                delta=rng.normal(0, 1e-3, D), w2c_gt=w2c_gt, w2c=w2c)

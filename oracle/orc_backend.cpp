@@ -814,7 +814,7 @@ extern "C" int orc_window_resubstitute(orc_ctx* c, const double* x, float lambda
             b -= s;
         }
         if (!std::isfinite(b)) break;   // the reference returns from the whole loop (:660-662)
-        W.step[p] = -b * W.HdiF[p] / (1 + lambda);
+        W.step[p] = -b * W.HdiF[p] / (1 + (double)lambda);   // currentLambda is a double in the reference
     }
     if (step_out) memcpy(step_out, W.step.data(), sizeof(float) * W.np);
     return 0;
