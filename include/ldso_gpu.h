@@ -135,6 +135,14 @@ int ldso_gpu_tracker_track(ldso_gpu_ctx* ctx, int tracker, int new_slot, float n
                            int iters_out[2]);
 
 
+/* ---- A2: PixelSelector::makeMaps (src/frontend/PixelSelector2.cc:111-169) incl. makeHists (:36-109) and
+ * select (:171-316).  map_out: w*h floats in {0,1,2,4} (PixelSelectorStatus as the reference stores it);
+ * potential_io: PixelSelector::currentPotential, persistent across keyframes (initially 3); returns the
+ * number of selected pixels in *n_selected.  The threshold tables are zero-filled at allocation (the
+ * reference leaves them uninitialised off the 32-pixel grid, SURVEY.md trap T3). */
+int ldso_gpu_select_make_maps(ldso_gpu_ctx* ctx, int slot, float density, int recursions_left, float th_factor,
+                              int* potential_io, float* map_out, int* n_selected);
+
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps
  * points and residuals as SoA/AoS pools.  Index conventions follow the reference: pair tables are

@@ -215,6 +215,16 @@ class Ctx:
         return dict(ok=(rc == 0), pose=pose, aff=aff, last_residuals=last, flow=flow, iters=iters)
 
 
+    # A2
+    def select_make_maps(self, slot, density, potential=3, recursions=1, th_factor=1.0):
+        w, h = self.sizes[0]
+        out = np.zeros((h, w), dtype=np.float32)
+        pot = C.c_int(potential)
+        n = C.c_int()
+        self._call("select_make_maps", C.c_int(slot), C.c_float(density), C.c_int(recursions), C.c_float(th_factor), C.byref(pot),
+                   _fp(out), C.byref(n))
+        return out, n.value, pot.value
+
     # ---- windowed BA (K7-K10, H1) ----
     def window_load(self, W, slots=None):
         """upload a window description dict (see synth.make_window); frames must already be in their slots"""
