@@ -143,6 +143,32 @@ int ldso_gpu_tracker_track(ldso_gpu_ctx* ctx, int tracker, int new_slot, float n
 int ldso_gpu_select_make_maps(ldso_gpu_ctx* ctx, int slot, float density, int recursions_left, float th_factor,
                               int* potential_io, float* map_out, int* n_selected);
 
+/* ---- K5 / K6: immature points (src/internal/ImmaturePoint.cc) ---------------------------------------
+ * The pool of immature points lives on the device; the host re-sends it after it adds or removes points
+ * (once per keyframe) and reads back what it branches on.  ImmaturePointStatus codes as in
+ * include/internal/ImmaturePoint.h:31-38 (0 GOOD, 1 OOB, 2 OUTLIER, 3 SKIPPED, 4 BADCONDITION, 5 UNINITIALIZED). */
+/* ImmaturePoint::ImmaturePoint (:14-39): color[8], weights[8], gradH (xx,xy,yy) and energyTH of n new points
+ * hosted in frame `slot` (energyTH = NaN marks a point whose patch is not finite) */
+int ldso_gpu_immature_create(ldso_gpu_ctx* ctx, int slot, int n, const float* u, const float* v, float* color,
+                             float* weights, float* grad_h, float* energy_th);
+/* upload the pool: host = index into the per-host tables passed to trace / the window frames for activate */
+int ldso_gpu_immature_set(ldso_gpu_ctx* ctx, int n, const int* host, const float* u, const float* v, const float* color,
+                          const float* weights, const float* grad_h, const float* energy_th, const float* idepth_min,
+                          const float* idepth_max, const float* quality, const int* status);
+/* FullSystem::traceNewCoarse (src/frontend/FullSystem.cc:1157-1195) = ImmaturePoint::traceOn (:47-317) for every
+ * pool point against frame new_slot; KRKi [n_hosts][9], Kt [n_hosts][3], aff [n_hosts][2] are the per-host
+ * hostToFrame tables of :1171-1176.  counts_out[6]: number of points per resulting status. */
+int ldso_gpu_immature_trace(ldso_gpu_ctx* ctx, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
+                            const float* aff, int counts_out[6]);
+/* any pointer may be NULL */
+int ldso_gpu_immature_get(ldso_gpu_ctx* ctx, float* idepth_min, float* idepth_max, float* quality, int* status,
+                          float* last_trace_uv, float* last_trace_pixel_interval);
+/* FullSystem::optimizeImmaturePoint (:1035-1155) for the listed pool points against the current window frames
+ * (ldso_gpu_window_set_frames): ok_out[i] = 1 when a PointHessian would be created, idepth_out its inverse depth,
+ * res_state_out [n_cand][n_frames] the final ResState per target (-1 for the host frame itself). */
+int ldso_gpu_immature_activate(ldso_gpu_ctx* ctx, int n_cand, const int* cand, int min_obs, float* idepth_out,
+                               int* ok_out, int* res_state_out);
+
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps
  * points and residuals as SoA/AoS pools.  Index conventions follow the reference: pair tables are
@@ -150,10 +176,10 @@ int ldso_gpu_select_make_maps(ldso_gpu_ctx* ctx, int slot, float density, int re
  * features, EnergyFunctional.cc:505-519; hence contiguous per host frame), residuals in p->residuals
  * order, flattened point-major with a CSR offset array. */
 #define LDSO_MAX_WINDOW 12
-#define LDSO_PRECALC_STRIDE 32
-/* one FrameFramePrecalc (src/internal/FrameFramePrecalc.cc:6-35) as 32 floats:
+#define LDSO_PRECALC_STRIDE 48
+/* one FrameFramePrecalc (src/internal/FrameFramePrecalc.cc:6-35) as 48 floats:
  * [0..8] PRE_RTll_0 (row-major) [9..11] PRE_tTll_0 [12..20] PRE_KRKiTll [21..23] PRE_KtTll
- * [24..25] PRE_aff_mode [26] PRE_b0_mode [27..31] reserved */
+ * [24..25] PRE_aff_mode [26] PRE_b0_mode [27..35] PRE_RTll [36..38] PRE_tTll [39] distanceLL [40..47] reserved */
 /* ResState (include/internal/Residuals.h:33-35) */
 #define LDSO_RES_IN 0
 #define LDSO_RES_OOB 1

@@ -225,14 +225,57 @@ class Ctx:
                    _fp(out), C.byref(n))
         return out, n.value, pot.value
 
+    # ---- K5 / K6: immature points ----
+    def immature_create(self, slot, u, v):
+        """ImmaturePoint constructor: (color[n,8], weights[n,8], gradH[n,3], energyTH[n])"""
+        u, v = f32(u), f32(v)
+        n = len(u)
+        col = np.zeros((n, 8), np.float32); wgt = np.zeros((n, 8), np.float32)
+        gh = np.zeros((n, 3), np.float32); eth = np.zeros(n, np.float32)
+        self._call("immature_create", C.c_int(slot), C.c_int(n), _fp(u), _fp(v), _fp(col), _fp(wgt), _fp(gh), _fp(eth))
+        return col, wgt, gh, eth
+
+    def immature_set(self, host, u, v, color, weights, grad_h, energy_th, idepth_min, idepth_max, quality, status):
+        host = np.ascontiguousarray(host, dtype=np.int32); status = np.ascontiguousarray(status, dtype=np.int32)
+        a = [f32(x) for x in (u, v, color, weights, grad_h, energy_th, idepth_min, idepth_max, quality)]
+        self.imm_n = len(host)
+        self._call("immature_set", C.c_int(self.imm_n), _ip(host), *[_fp(x) for x in a], _ip(status))
+
+    def immature_trace(self, new_slot, KRKi, Kt, aff):
+        KRKi, Kt, aff = f32(KRKi), f32(Kt), f32(aff)
+        cnt = np.zeros(6, np.int32)
+        self._call("immature_trace", C.c_int(new_slot), C.c_int(len(Kt)), _fp(KRKi), _fp(Kt), _fp(aff), _ip(cnt))
+        return cnt
+
+    def immature_get(self):
+        n = self.imm_n
+        out = dict(idepth_min=np.zeros(n, np.float32), idepth_max=np.zeros(n, np.float32), quality=np.zeros(n, np.float32),
+                   status=np.zeros(n, np.int32), uv=np.zeros((n, 2), np.float32), interval=np.zeros(n, np.float32))
+        self._call("immature_get", _fp(out["idepth_min"]), _fp(out["idepth_max"]), _fp(out["quality"]), _ip(out["status"]),
+                   _fp(out["uv"]), _fp(out["interval"]))
+        return out
+
+    def immature_activate(self, cand, min_obs=1):
+        cand = np.ascontiguousarray(cand, dtype=np.int32)
+        n = len(cand)
+        idepth = np.zeros(n, np.float32); ok = np.zeros(n, np.int32); st = np.zeros((n, self.win_n), np.int32)
+        self._call("immature_activate", C.c_int(n), _ip(cand), C.c_int(min_obs), _fp(idepth), _ip(ok), _ip(st))
+        return idepth, ok, st
+
     # ---- windowed BA (K7-K10, H1) ----
+    def window_set_frames(self, W, slots=None):
+        n = W["n"]
+        slots = np.ascontiguousarray(slots if slots is not None else np.arange(n), dtype=np.int32)
+        self.win_n = n
+        pc, eth, cal = f32(W["precalc"]), f32(W["frame_energy_th"]), f32(W["calib"])
+        self._call("window_set_frames", C.c_int(n), _ip(slots), _fp(pc), _fp(eth), _fp(cal))
+
     def window_load(self, W, slots=None):
         """upload a window description dict (see synth.make_window); frames must already be in their slots"""
         n = W["n"]
         slots = np.ascontiguousarray(slots if slots is not None else np.arange(n), dtype=np.int32)
         self.win_n, self.win_np, self.win_nr = n, len(W["u"]), len(W["target"])
-        pc, eth, cal = f32(W["precalc"]), f32(W["frame_energy_th"]), f32(W["calib"])
-        self._call("window_set_frames", C.c_int(n), _ip(slots), _fp(pc), _fp(eth), _fp(cal))
+        self.window_set_frames(W, slots)
         a = [f32(W[k]) for k in ("u", "v", "idepth", "idepth_zero")]
         host = np.ascontiguousarray(W["host"], dtype=np.int32)
         col, wgt, pri = f32(W["color"]), f32(W["weights"]), f32(W["prior"])

@@ -86,6 +86,7 @@ struct ldso_gpu_ctx {
     double* trk_result_pinned = nullptr;    // [64]
     WindowDev win;
     void* selector = nullptr;               // SelectorDev (a2_selector.cu), created on first use
+    void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use
     long long launches = 0;
     // optional per-kernel CUDA-event profile (ldso_gpu_profile_*): [0] = fused tracker kernel
     int profile_on = 0;
@@ -104,6 +105,7 @@ struct ldso_gpu_ctx {
 
 // kernels (one translation unit each)
 void selector_free(ldso_gpu_ctx* c);
+void immature_free(ldso_gpu_ctx* c);
 int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev);
 int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u, const float* v, const float* id,
                const float* hdi);

@@ -6,7 +6,7 @@ Index convention everywhere: pair tables are [host + n * target].
 import numpy as np
 
 SCALE_XI_ROT, SCALE_XI_TRANS, SCALE_A, SCALE_B = 1.0, 0.5, 10.0, 1000.0
-PRECALC_STRIDE = 32
+PRECALC_STRIDE = 48
 
 
 def hat(v):
@@ -62,6 +62,7 @@ def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
             row[0:9] = R0.reshape(-1); row[9:12] = t0
             row[12:21] = KRKi.reshape(-1); row[21:24] = Kt
             row[24] = a; row[25] = b; row[26] = np.float32(aff0[h][1])
+            row[27:36] = R.reshape(-1); row[36:39] = tt; row[39] = np.float32(np.linalg.norm(l[1]))
     return out
 
 

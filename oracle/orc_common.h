@@ -19,6 +19,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 #include <xmmintrin.h>
@@ -137,6 +138,7 @@ struct orc_ctx {
     std::vector<orc::Frame> frames;
     orc::Tracker trk[LDSO_NUM_TRACKERS];
     orc::Window win;
+    std::shared_ptr<void> selector, immature;   // per-ctx state of orc_selector.cpp / orc_immature.cpp (die with the ctx)
     std::string err;
     long long launches = 0;
 };

@@ -17,16 +17,15 @@ struct Selector {
 };
 
 Selector& sel_of(orc_ctx* c) {
-    static std::vector<std::pair<orc_ctx*, Selector*>> all;   // the oracle is single-threaded test code
-    for (auto& p : all) if (p.first == c) return *p.second;
-    Selector* s = new Selector();
+    if (c->selector) return *(Selector*)c->selector.get();
+    std::shared_ptr<Selector> s = std::make_shared<Selector>();
     int w = c->wG[0], h = c->hG[0];
     s->randomPattern.resize((size_t)w * h);
     std::srand(3141592);
     for (int i = 0; i < w * h; i++) s->randomPattern[i] = rand() & 0xFF;
     s->ths.assign((size_t)(w / 32 + 1) * (h / 32 + 1) + 100, 0.f);
     s->thsSmoothed.assign((size_t)(w / 32 + 1) * (h / 32 + 1) + 100, 0.f);
-    all.emplace_back(c, s);
+    c->selector = s;
     return *s;
 }
 

@@ -52,3 +52,63 @@ def setup_tracker(ctx, calib="c1", n_points=2000, idx=(40, 42), seed=1001, idept
 def rel_err(a, b):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def immature_scene(calib="small", host_ids=(40, 44), new_ids=(46, 48, 50), pts_per_host=300, seed=1001):
+    """Keyframes hosting fresh immature points + later frames to trace them on (FullSystem::traceNewCoarse)."""
+    c = CALIB[calib]
+    fr = frames(calib, seed, tuple(host_ids) + tuple(new_ids))
+    K = np.array([[c["fx"], 0, c["cx"]], [0, c["fy"], c["cy"]], [0, 0, 1]], dtype=np.float32)
+    Ki = np.linalg.inv(K.astype(np.float64)).astype(np.float32)
+    nh = len(host_ids)
+    U, V, H, GT = [], [], [], []
+    for hi in range(nh):
+        img, dep, _, _ = fr[hi]
+        u, v, idp, _ = pick_points(img, dep, pts_per_host, seed=hi + 3, border=8)
+        U.append(np.round(u)); V.append(np.round(v)); H.append(np.full(len(u), hi, np.int32)); GT.append(idp)
+    tables = []
+    for ni in range(len(new_ids)):
+        _, _, Rn, tn = fr[nh + ni]
+        KRKi, Kt, aff = [], [], []
+        for hi in range(nh):
+            _, _, Rh, th = fr[hi]
+            R = (Rn.T @ Rh).astype(np.float32); t = (Rn.T @ (th - tn)).astype(np.float32)
+            KRKi.append((K @ R @ Ki).astype(np.float32)); Kt.append((K @ t).astype(np.float32)); aff.append([1.0, 0.0])
+        tables.append((np.array(KRKi, np.float32), np.array(Kt, np.float32), np.array(aff, np.float32)))
+    w2c = [(R.T, -R.T @ t) for (_, _, R, t) in fr]
+    return dict(calib=c, frames=fr, n_hosts=nh, u=np.concatenate(U).astype(np.float32), v=np.concatenate(V).astype(np.float32),
+                host=np.concatenate(H), gt_idepth=np.concatenate(GT).astype(np.float32), tables=tables, w2c=w2c)
+
+
+def run_immature(ctx, S, activate=True):
+    """Drive create -> set -> trace on every new frame -> activate through one C ABI (oracle or GPU)."""
+    from ldso_b200 import window_host as wh
+    nh, fr = S["n_hosts"], S["frames"]
+    for i, f in enumerate(fr):
+        ctx.make_images(i, f[0])
+    cols, wgts, ghs, eths = [], [], [], []
+    for hi in range(nh):
+        m = S["host"] == hi
+        col, wgt, gh, eth = ctx.immature_create(hi, S["u"][m], S["v"][m])
+        cols.append(col); wgts.append(wgt); ghs.append(gh); eths.append(eth)
+    col, wgt, gh, eth = [np.concatenate(x) for x in (cols, wgts, ghs, eths)]
+    n = len(S["u"])
+    ctx.immature_set(S["host"], S["u"], S["v"], col, wgt, gh, eth, np.zeros(n, np.float32), np.full(n, np.nan, np.float32),
+                     np.full(n, 10000.0, np.float32), np.full(n, 5, np.int32))
+    out = dict(color=col, weights=wgt, grad_h=gh, energy_th=eth, traces=[], counts=[])
+    for ni, (KRKi, Kt, aff) in enumerate(S["tables"]):
+        out["counts"].append(ctx.immature_trace(nh + ni, KRKi, Kt, aff))
+        out["traces"].append(ctx.immature_get())
+    if activate:
+        c = S["calib"]
+        nf = len(fr)
+        w2c = S["w2c"]
+        pc = wh.precalc_table(w2c, w2c, (c["fx"], c["fy"], c["cx"], c["cy"]), [(0.0, 0.0)] * nf, [(0.0, 0.0)] * nf, [1.0] * nf)
+        W = dict(n=nf, precalc=pc, frame_energy_th=np.full(nf, 512.0, np.float32),
+                 calib=np.array([c["fx"], c["fy"], c["cx"], c["cy"]], np.float32))
+        ctx.window_set_frames(W)
+        last = out["traces"][-1]
+        cand = np.nonzero((last["status"] == 0) | (last["status"] == 3) | (last["status"] == 4))[0].astype(np.int32)
+        out["cand"] = cand
+        out["act"] = ctx.immature_activate(cand, min_obs=1)
+    return out
