@@ -25,12 +25,23 @@ from ldso_b200 import capi, synth  # noqa: E402
 
 CALIB = dict(w=640, h=480, fx=384.0, fy=384.0, cx=319.5, cy=239.5)
 N_POINTS = 2000          # setting_desiredPointDensity (preset 0)
-KF_EVERY = 6             # a new tracking reference every KF_EVERY frames
+N_IMMATURE = 1500        # setting_desiredImmatureDensity (preset 0)
+WINDOW = 7               # setting_maxFrames (preset 0)
+KF_EVERY = 6             # a keyframe every KF_EVERY frames (the reference decides by optical flow; ~5-10 on this motion)
+BA_ITS = 6               # setting_maxOptIterations
+N_ACTIVATE = 300         # immature points activated per keyframe (~ N_POINTS / WINDOW leave with the oldest frame)
 FIRST_FRAME = 40
+PRE = (WINDOW - 1) * KF_EVERY      # frames rendered before the first stepped frame so that the window is full from the start
 IDENT = np.concatenate([np.eye(3).reshape(-1), np.zeros(3)])
-WORKLOAD = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level pyramid, %d points; per frame: "
-            "makeImages (K1) + trackNewestCoarse (K3/K4 LM, all levels); every %d-th frame also "
-            "setCoarseTrackingRef/makeCoarseDepthL0 (K2) + window BA pass (K7-K10) when built" % (N_POINTS, KF_EVERY))
+WORKLOAD = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level pyramid, %d active points, %d-keyframe window. "
+            "Per frame: makeImages (K1), trackNewestCoarse (K3/K4 LM, all levels), traceNewCoarse over the immature pool (K5). "
+            "Every %d-th frame is a keyframe: activation of %d immature points (K6), window BA = linearizeAll + %d x "
+            "(accumulate K8/K9, solve H1, resubstitute K10, linearizeAll K7) + fixLinearization pass, setCoarseTrackingRef "
+            "(K2), PixelSelector::makeMaps (A2) + ImmaturePoint construction (K6) for the new keyframe. Keyframe cadence "
+            "and the window contents (ground-truth poses/depths + noise) are fixed by the harness, not by the reference's "
+            "FullSystem heuristics" % (N_POINTS, WINDOW, KF_EVERY, N_ACTIVATE, BA_ITS))
+# algorithmic bytes per unit
+BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 5000.0}
 
 
 def rank_info():
@@ -76,71 +87,219 @@ class ClockSampler:
 
 
 class Sequence:
-    """Synthetic sequence + the per-frame driver, written against the prefix-agnostic C ABI binding so the
-    same stepping runs the product (GPU) and, for the CPU baseline only, the oracle."""
+    """Synthetic sequence + the per-frame / per-keyframe driver, written against the prefix-agnostic C ABI binding so
+    the same stepping runs the product (GPU) and, for the CPU baseline only, the oracle.  Frame f of the sequence is
+    synthetic frame FIRST_FRAME + f; frames 0..PRE are the keyframes that fill the window before stepping starts."""
 
-    def __init__(self, api, seed, n_frames, device=0):
-        self.api = api
-        cfg = api.default_config(device=device, affine_opt_mode_a=0.0, affine_opt_mode_b=0.0, **CALIB)
+    KF_SLOTS = WINDOW + 1            # ring of keyframe pyramids (window + the incoming one); 2 more slots for plain frames
+
+    def __init__(self, api, seed, n_steps, device=0):
+        from ldso_b200 import window_host as wh
+        self.api, self.wh = api, wh
+        cfg = api.default_config(device=device, affine_opt_mode_a=0.0, affine_opt_mode_b=0.0, n_frame_slots=self.KF_SLOTS + 2,
+                                 **CALIB)
         self.ctx = api.create(cfg)
+        n_frames = PRE + 1 + n_steps
         self.frames, self.depths, self.poses = synth.make_sequence(seed, n_frames, start=FIRST_FRAME, **CALIB)
-        # tracking-reference point sets (stand-in for the window's active points), prepared outside the timed region
-        self.ref_points = {i: synth.pick_points(self.frames[i], self.depths[i], N_POINTS) for i in range(0, n_frames, KF_EVERY)}
+        self.K = np.array([[CALIB["fx"], 0, CALIB["cx"]], [0, CALIB["fy"], CALIB["cy"]], [0, 0, 1]], dtype=np.float32)
+        self.Ki = np.linalg.inv(self.K.astype(np.float64)).astype(np.float32)
+        # everything below is prepared outside the timed region: per-keyframe window descriptions (the stand-in for the
+        # reference's host-side point/residual graph), tracking-reference point sets, per-frame host->frame tables
+        self.kfs = list(range(0, n_frames, KF_EVERY))
+        self.windows, self.ref_points = {}, {}
+        for k in self.kfs:
+            if k < PRE:
+                continue
+            ids = list(range(k - PRE, k + 1, KF_EVERY))
+            rend = [(self.frames[f], self.depths[f], self.poses[f]) for f in ids]
+            W = synth.make_window(rendered=rend, pts_per_frame=N_POINTS // WINDOW, rng_seed=5 + k, **CALIB)
+            W["HM"] = W["HM"] * 1e6; W["bM"] = W["bM"] * 0; W["delta"] = W["delta"] * 0     # frames frozen by the prior
+            W["slots"] = np.array([self.kf_slot(f) for f in ids], dtype=np.int32)
+            W["ids"] = ids
+            self.windows[k] = W
+            self.ref_points[k] = synth.pick_points(self.frames[k], self.depths[k], N_POINTS)
+        self.tables = {}
+        for f in range(PRE, n_frames):
+            k = (f - 1) // KF_EVERY * KF_EVERY if f > PRE else PRE            # newest keyframe before frame f
+            hosts = list(range(k - PRE, k + 1, KF_EVERY))
+            self.tables[f] = (hosts,) + self.host_tables(hosts, f)
+        self.pool = None
         self.ref_idx = None
+        self.phase = {}
         self.last_rel = IDENT.copy()
-        self.n_slots = cfg.n_frame_slots
         self.results = []
+        self.kf_log = []
 
-    def set_ref(self, i):
-        u, v, idp, hdi = self.ref_points[i]
-        self.ctx.tracker_set_ref(0, i % self.n_slots, u, v, idp, hdi)
-        self.ref_idx = i
-        self.last_rel = IDENT.copy()
+    def tick(self, name, t0):
+        """host wall-clock per phase (each phase ends with its results on the host), for the breakdown in the JSON line"""
+        t1 = time.perf_counter()
+        self.phase[name] = self.phase.get(name, 0.0) + (t1 - t0)
+        return t1
+
+    def kf_slot(self, f):
+        return (f // KF_EVERY) % self.KF_SLOTS
+
+    def slot(self, f):
+        return self.kf_slot(f) if f % KF_EVERY == 0 else self.KF_SLOTS + (f % 2)
+
+    def host_tables(self, hosts, f):
+        """hostToFrame KRKi / Kt / affine per host keyframe (FullSystem.cc:1171-1176), from the ground-truth poses"""
+        Rn, tn = self.poses[f]
+        KRKi, Kt, aff = [], [], []
+        for hf in hosts:
+            Rh, th = self.poses[hf]
+            R = (Rn.T @ Rh).astype(np.float32); t = (Rn.T @ (th - tn)).astype(np.float32)
+            KRKi.append((self.K @ R @ self.Ki).astype(np.float32)); Kt.append((self.K @ t).astype(np.float32)); aff.append([1.0, 0.0])
+        return np.array(KRKi, np.float32), np.array(Kt, np.float32), np.array(aff, np.float32)
+
+    # ---- immature pool (host-managed like the reference's per-frame immaturePoints lists) ----
+    def new_immature(self, f, host_idx):
+        """PixelSelector::makeMaps + ImmaturePoint constructor for keyframe f (FullSystem::makeNewTraces, :1426-1482)"""
+        sl = self.kf_slot(f)
+        m, n, self.potential = self.ctx.select_make_maps(sl, N_IMMATURE, potential=getattr(self, "potential", 3))
+        m[:5, :] = 0; m[-5:, :] = 0; m[:, :5] = 0; m[:, -5:] = 0          # patternPadding+1 border (:1444-1446)
+        v, u = np.nonzero(m)
+        u = u.astype(np.float32); v = v.astype(np.float32)
+        col, wgt, gh, eth = self.ctx.immature_create(sl, u, v)
+        ok = np.isfinite(eth)
+        k = int(ok.sum())
+        return dict(host=np.full(k, host_idx, np.int32), u=u[ok], v=v[ok], color=col[ok], weights=wgt[ok], grad_h=gh[ok],
+                    energy_th=eth[ok], idepth_min=np.zeros(k, np.float32), idepth_max=np.full(k, np.nan, np.float32),
+                    quality=np.full(k, 10000.0, np.float32), status=np.full(k, 5, np.int32))
+
+    def upload_pool(self):
+        P = self.pool
+        self.ctx.immature_set(P["host"], P["u"], P["v"], P["color"], P["weights"], P["grad_h"], P["energy_th"], P["idepth_min"],
+                              P["idepth_max"], P["quality"], P["status"])
 
     def prime(self):
-        self.ctx.make_images(0, self.frames[0])
-        self.set_ref(0)
+        """untimed: pyramids of the first WINDOW keyframes, their immature points, the first tracking reference"""
+        parts = []
+        for hi, f in enumerate(range(0, PRE + 1, KF_EVERY)):
+            self.ctx.make_images(self.kf_slot(f), self.frames[f])
+            parts.append(self.new_immature(f, hi))
+        self.pool = {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
+        self.upload_pool()
+        self.set_ref(PRE)
 
-    def step(self, i, dev_ptr=None):
-        """frame i: K1 + track against the current reference; returns the tracked pose (host)"""
-        slot = i % self.n_slots
+    def set_ref(self, f):
+        u, v, idp, hdi = self.ref_points[f]
+        self.ctx.tracker_set_ref(0, self.kf_slot(f), u, v, idp, hdi)
+        self.ref_idx = f
+        self.last_rel = IDENT.copy()
+
+    # ---- per frame ----
+    def step(self, f, dev_ptr=None):
+        """frame f: makeImages, trackNewestCoarse against the current reference, traceNewCoarse; keyframe work if due"""
+        sl = self.slot(f)
+        t = time.perf_counter()
         if dev_ptr is None:
-            self.ctx.make_images(slot, self.frames[i])
+            self.ctx.make_images(sl, self.frames[f])
         else:
-            self.ctx.make_images_dev(slot, dev_ptr)
-        r = self.ctx.tracker_track(0, slot, self.last_rel, [0.0, 0.0])
+            self.ctx.make_images_dev(sl, dev_ptr)
+        t = self.tick("K1 makeImages", t)
+        r = self.ctx.tracker_track(0, sl, self.last_rel, [0.0, 0.0])
+        t = self.tick("K3/K4 trackNewestCoarse", t)
         if r["ok"]:
             self.last_rel = r["pose"]
-        self.results.append((i, r["ok"], r["pose"].copy(), r["iters"].copy()))
-        if (i - self.ref_idx) >= KF_EVERY:
-            self.set_ref(i)
+        self.results.append((f, self.ref_idx, r["ok"], r["pose"].copy(), r["iters"].copy()))
+        hosts, KRKi, Kt, aff = self.tables[f]
+        counts = self.ctx.immature_trace(sl, KRKi, Kt, aff)
+        t = self.tick("K5 traceNewCoarse", t)
+        if f % KF_EVERY == 0:
+            self.keyframe(f, counts)
         return r
 
+    def keyframe(self, f, counts):
+        """FullSystem::makeKeyFrame cadence (FullSystem.cc:485-699) with harness-provided window contents"""
+        ctx, W = self.ctx, self.windows[f]
+        t = time.perf_counter()
+        # pool bookkeeping: read back what the host branches on, drop the frame that leaves the window
+        tr = ctx.immature_get()
+        P = self.pool
+        P["idepth_min"], P["idepth_max"], P["quality"], P["status"] = tr["idepth_min"], tr["idepth_max"], tr["quality"], tr["status"]
+        keep = (P["host"] > 0) & (P["status"] != 1)                    # OOB points are deleted (:1279-1284)
+        P = {k: a[keep] for k, a in P.items()}
+        P["host"] = P["host"] - 1
+        self.pool = P
+        self.upload_pool()
+        t = self.tick("KF pool bookkeeping", t)
+        # activatePointsMT -> optimizeImmaturePoint (K6) on the best-traced candidates
+        ctx.window_set_frames(W, W["slots"])
+        good = np.nonzero(np.isfinite(P["idepth_max"]) & ((P["status"] == 0) | (P["status"] == 3) | (P["status"] == 4)) &
+                          (P["quality"] > 3))[0]                       # setting_minTraceQuality
+        cand = good[:N_ACTIVATE].astype(np.int32)
+        n_ok = 0
+        if len(cand):
+            idp, ok, st = ctx.immature_activate(cand, min_obs=1)
+            n_ok = int(ok.sum())
+            keep = np.ones(len(P["host"]), bool); keep[cand] = False   # activated or dropped either way (:1301-1318)
+            self.pool = P = {k: a[keep] for k, a in P.items()}
+        t = self.tick("KF K6 activate", t)
+        # window BA: FullSystem::optimize (:844-1007)
+        ctx.window_load(W, W["slots"])
+        t = self.tick("KF window upload", t)
+        idepth = W["idepth"].copy()
+        st, _ = ctx.window_linearize(False)
+        ctx.window_apply_res()
+        t = self.tick("KF K7 linearizeAll", t)
+        e0 = st[0]
+        lam = 1e-1
+        for it in range(BA_ITS):
+            acc = ctx.window_accumulate()
+            t = self.tick("KF K8/K9 accumulate+stitch", t)
+            x = ctx.window_solve(it, lam, acc, W["HM"], W["bM"], W["delta"])
+            t = self.tick("KF H1 solve", t)
+            step = ctx.window_resubstitute(x, lam)
+            idepth = (idepth + step).astype(np.float32)
+            ctx.window_set_idepth(idepth, W["idepth_zero"])
+            ctx.window_set_frames(W, W["slots"])                        # setPrecalcValues after the step
+            t = self.tick("KF K10 resubstitute+step", t)
+            st, _ = ctx.window_linearize(False)
+            ctx.window_apply_res()
+            t = self.tick("KF K7 linearizeAll", t)
+            lam *= 0.25
+        st, eth = ctx.window_linearize(True)
+        ctx.window_apply_res()
+        hdi = ctx.window_point_floats(6)                               # HdiF, maxRelBaseline, centerProjectedTo: what
+        mrb = ctx.window_point_floats(9)                               # flagPointsForRemoval / makeCoarseDepthL0 read
+        cen = ctx.window_residual_floats(3)
+        t = self.tick("KF K7 linearizeAll", t)
+        # setCoarseTrackingRef for the next frames, then new immature points on this keyframe
+        self.set_ref(f)
+        t = self.tick("KF K2 setCoarseTrackingRef", t)
+        newp = self.new_immature(f, WINDOW - 1)
+        self.pool = {k: np.concatenate([self.pool[k], newp[k]]) for k in newp}
+        self.upload_pool()
+        t = self.tick("KF A2 makeMaps + K6 create", t)
+        self.kf_log.append(dict(frame=f, trace_counts=counts.tolist(), activated=n_ok, candidates=int(len(cand)), e0=float(e0),
+                                e_final=float(st[0]), n_in=int(st[2]), pool=int(len(self.pool["host"])),
+                                residuals=int(len(W["target"])), new_immature=int(len(newp["host"]))))
 
     def gt_error(self):
         """max translation error of the tracked relative poses vs ground truth — proves the timed work is real tracking"""
         worst = 0.0
-        ref = 0
-        for (i, ok, pose, _) in self.results:
-            while ref + KF_EVERY < i:
-                ref += KF_EVERY
-            gt = synth.rel_pose(self.poses[ref][0], self.poses[ref][1], self.poses[i][0], self.poses[i][1])
+        for (f, ref, ok, pose, _) in self.results:
+            gt = synth.rel_pose(self.poses[ref][0], self.poses[ref][1], self.poses[f][0], self.poses[f][1])
             worst = max(worst, float(np.abs(pose[9:] - gt[9:]).max()))
         return worst
 
 
-def run_sequence_timed(seq, first, steps, warmup, use_dev, flush=None, torch=None):
-    """W untimed + K timed steps.  Returns (per-step seconds list, launches in the timed region)."""
+def run_sequence_timed(seq, steps, warmup, use_dev, flush=None, torch=None):
+    """W untimed + K timed steps starting at frame PRE+1.  Returns (per-step seconds, launches, h2d bytes, d2h bytes)
+    of the timed region."""
     dev_imgs = None
     if use_dev:
         dev_imgs = [torch.from_numpy(f).cuda() for f in seq.frames]
         torch.cuda.synchronize()
-    i = first
+    i = PRE + 1
     for _ in range(warmup):
         seq.step(i, dev_imgs[i].data_ptr() if use_dev else None)
         i += 1
     seq.ctx.sync()
     l0 = seq.ctx.launch_count()
+    io0 = seq.ctx.io_bytes()
+    seq.phase = {}
     times = []
     for _ in range(steps):
         if flush is not None:
@@ -151,10 +310,11 @@ def run_sequence_timed(seq, first, steps, warmup, use_dev, flush=None, torch=Non
             times.append(seq.ctx.timer_stop() * 1e-3)
         else:
             t0 = time.perf_counter()
-            seq.step(i, None)            # returns after the pose has been read back to the host
+            seq.step(i, None)            # returns after every result of the frame has been read back to the host
             times.append(time.perf_counter() - t0)
         i += 1
-    return times, seq.ctx.launch_count() - l0
+    io1 = seq.ctx.io_bytes()
+    return times, seq.ctx.launch_count() - l0, io1[0] - io0[0], io1[1] - io0[1]
 
 
 def cpu_run(steps, warmup, seed, fast=True):
@@ -162,19 +322,25 @@ def cpu_run(steps, warmup, seed, fast=True):
     from ldso_b200 import build
     build.build_oracle()
     api = capi.Api(build.ORACLE_FAST_LIB if fast else build.ORACLE_LIB, "orc_")
-    seq = Sequence(api, seed, 1 + warmup + steps)
+    seq = Sequence(api, seed, warmup + steps)
     seq.prime()
-    times, _ = run_sequence_timed(seq, 1, steps, warmup, use_dev=False)
+    times = run_sequence_timed(seq, steps, warmup, use_dev=False)[0]
     return seq, times
+
+
+PROF = [("k34_track_eval_kernel", 0, "k34", "points"), ("k5_trace_kernel", 1, "k5", "search steps"),
+        ("k7_linearize_kernel", 2, "k7", "residuals"), ("k8_top_kernel", 3, "k8", "residuals"),
+        ("k9_sc_kernel", 4, "k9", "residuals"), ("k1_pyramid_kernel+k1_wrap_columns_kernel", 5, "k1", "frames")]
+BYTES_PER_UNIT["k5"] = 128.0
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=42)
+    ap.add_argument("--warmup", type=int, default=6)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-steps", type=int, default=20, help="frames of the bounded cpu_baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=18, help="frames of the bounded cpu_baseline sample")
     args = ap.parse_args()
     rank, local_rank, world = rank_info()
     steps, warmup = args.steps, max(args.warmup, 0)
@@ -191,10 +357,11 @@ def main():
         fps = steps / sum(times)
         line = dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps, n_gpus=args.gpus,
                     cpu_baseline={"value": fps, "unit": "frames/s", "cores": 1, "kind": "port",
-                                  "sample": "%d frames of the same sequence, oracle restatement (-O3 -march=x86-64-v3), "
-                                            "single-threaded as the reference's tracking path is" % steps},
+                                  "sample": "%d frames (%d keyframes) of the same sequence, oracle restatement (-O3 "
+                                            "-march=x86-64-v3), single-threaded" % (steps, len(seq.kf_log))},
                     e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                    gt_max_translation_error_m=seq.gt_error())
+                    host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq.phase.items()},
+                    gt_max_translation_error_m=seq.gt_error(), keyframes=seq.kf_log[-2:])
         line["config"] = dict(base["config"], l2="n/a (CPU)")
         print(json.dumps(line))
         return
@@ -205,9 +372,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     gpu = capi.load()
-    n_frames = 1 + warmup + steps
-    seq = Sequence(gpu, 1001 + rank, n_frames, device=local_rank)
-    seq_e2e = Sequence(gpu, 1001 + rank, n_frames, device=local_rank)
+    seq = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
+    seq_e2e = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def flush():
@@ -222,9 +388,9 @@ def main():
     seq.prime(); seq_e2e.prime()
     with ClockSampler(local_rank) as clk:
         barrier()
-        times, launches = run_sequence_timed(seq, 1, steps, warmup, use_dev=True, flush=flush, torch=torch)
+        times, launches, _, _ = run_sequence_timed(seq, steps, warmup, use_dev=True, flush=flush, torch=torch)
         barrier()
-        times_e2e, _ = run_sequence_timed(seq_e2e, 1, steps, warmup, use_dev=False, flush=flush)
+        times_e2e, _, h2d, d2h = run_sequence_timed(seq_e2e, steps, warmup, use_dev=False, flush=flush)
         barrier()
     t_dev, t_e2e = sum(times), sum(times_e2e)
     if world > 1:
@@ -232,12 +398,13 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_dev, t_e2e = tt.tolist()
 
-    # roofline pass: same steps again with per-launch CUDA events around the dominant kernel
-    seq_p = Sequence(gpu, 1001 + rank, n_frames, device=local_rank)
+    # roofline pass: the same steps again with CUDA events around every launch of the main kernels
+    seq_p = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
     seq_p.prime()
+    seq_p.ctx.sync()
     seq_p.ctx.profile_enable(True)
-    run_sequence_timed(seq_p, 1, steps, warmup, use_dev=False, flush=flush)
-    k_ms, k_launches, k_units = seq_p.ctx.profile_get(0)
+    run_sequence_timed(seq_p, steps, 0, use_dev=False, flush=flush)
+    prof = {name: seq_p.ctx.profile_get(which) + (key, unit) for (name, which, key, unit) in PROF}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -248,26 +415,35 @@ def main():
     except Exception:
         pass
     peak = peaks.get("hbm_gbs", 6650.0)
-    bytes_per_point = 16 + 4 * 16        # float4 point + four float4 texels
-    achieved = (k_units * bytes_per_point) / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    kernels = {}
+    for name, (ms, n, units, key, unit) in prof.items():
+        if n == 0:
+            continue
+        gbs = units * BYTES_PER_UNIT[key] / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        kernels[name] = {"launches": int(n), "total_ms": ms, "avg_us": 1e3 * ms / n, "units_per_launch": units / n, "unit": unit,
+                         "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
+    top = max(kernels, key=lambda k: kernels[k]["total_ms"])
     line = dict(base, value=world * steps / t_dev, ms_per_step=1e3 * t_dev / steps,
-                e2e={"value": world * steps / t_e2e, "unit": "frames/s", "h2d_bytes_per_step": CALIB["w"] * CALIB["h"] * 4,
-                     "d2h_bytes_per_step": 52 * 8 * int(round(k_launches / max(steps + warmup, 1))) + 12 * 8},
+                e2e={"value": world * steps / t_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
+                     "d2h_bytes_per_step": d2h / steps},
                 gpu_launches=int(launches),
                 clocks=clk.summary(),
-                roofline={"bound": "hbm", "kernel": "k34_track_eval_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                          "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
-                          "launches": int(k_launches), "avg_us": 1e3 * k_ms / max(k_launches, 1),
-                          "points_per_launch": k_units / max(k_launches, 1),
-                          "note": "single-sequence launches are latency-bound (L2-resident working set); see DESIGN.md"},
-                gt_max_translation_error_m=seq.gt_error())
+                roofline={"bound": "hbm", "kernel": top, "achieved": kernels[top]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                          "frac": kernels[top]["frac"], "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                          "launches": kernels[top]["launches"], "avg_us": kernels[top]["avg_us"],
+                          "units_per_launch": kernels[top]["units_per_launch"],
+                          "note": "dominant kernel by summed launch time; single-sequence launches are latency-bound "
+                                  "(L2-resident working set), see DESIGN.md section 4"},
+                kernels=kernels,
+                host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
+                gt_max_translation_error_m=seq.gt_error(), keyframes=seq.kf_log[-2:])
     if args.gpus == 1:
-        cseq, ctimes = cpu_run(min(args.cpu_steps, steps), 2, 1001)
+        cseq, ctimes = cpu_run(min(args.cpu_steps, steps), KF_EVERY, 1001)
         n = len(ctimes)
         line["cpu_baseline"] = {"value": n / sum(ctimes), "unit": "frames/s", "cores": 1, "kind": "port",
-                                "sample": "%d frames of the same sequence and workload through the oracle (g++ -O3 "
-                                          "-march=x86-64-v3), single thread: the reference's tracking path is single-threaded "
-                                          "(SURVEY.md §2.2); host has %d cores" % (n, os.cpu_count())}
+                                "sample": "%d frames (%d keyframes) of the same sequence and workload through the oracle (g++ -O3 "
+                                          "-march=x86-64-v3), single thread; host has %d cores"
+                                          % (n, sum(1 for k in cseq.kf_log if k["frame"] > PRE + KF_EVERY), os.cpu_count())}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

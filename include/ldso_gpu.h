@@ -81,11 +81,24 @@ int ldso_gpu_level_size(const ldso_gpu_ctx* ctx, int lvl, int* w, int* h); /* wG
 int ldso_gpu_sync(ldso_gpu_ctx* ctx);                                 /* drain the ctx's streams */
 /* number of kernel launches issued through this ctx since creation (bench.py "gpu_launches") */
 long long ldso_gpu_launch_count(const ldso_gpu_ctx* ctx);
+/* bytes copied host->device / device->host by the entry points of this ctx since creation (bench.py "e2e") */
+int ldso_gpu_io_bytes(ldso_gpu_ctx* ctx, long long* h2d, long long* d2h);
 /* CUDA-event stopwatch on the ctx's tracking stream (the stream every kernel of this ctx is launched on) */
 int ldso_gpu_timer_start(ldso_gpu_ctx* ctx);
 int ldso_gpu_timer_stop(ldso_gpu_ctx* ctx, float* ms);
-/* Per-kernel CUDA-event profile.  enable(1) zeroes the counters; which = 0: fused tracker kernel (K3+K4).
- * total_ms = summed launch durations, units = items processed (points). */
+/* Per-kernel CUDA-event profile (events on the launching stream, resolved in profile_get).  enable(1) zeroes the
+ * counters.  total_ms = summed launch durations, units = items processed (points / residuals / pixels). */
+#define LDSO_PROF_K34 0      /* fused tracker kernel, units = points */
+#define LDSO_PROF_K5 1       /* traceOn, units = epipolar search steps (+9 per searched point for the fixed part) */
+#define LDSO_PROF_K7 2       /* linearize, units = residuals */
+#define LDSO_PROF_K8 3       /* top Hessian accumulation (both modes), units = residuals */
+#define LDSO_PROF_K9 4       /* Schur accumulation, units = residuals */
+#define LDSO_PROF_K1 5       /* pyramid (both kernels), units = frames */
+#define LDSO_PROF_A2 6       /* selector kernels of one makeMaps call, units = level-0 pixels per pass */
+#define LDSO_PROF_K6 7       /* activation, units = candidates */
+#define LDSO_PROF_K10 8      /* resubstitute, units = points */
+#define LDSO_PROF_K2 9       /* makeCoarseDepthL0 kernels, units = points */
+#define LDSO_PROF_SLOTS 12
 int ldso_gpu_profile_enable(ldso_gpu_ctx* ctx, int on);
 int ldso_gpu_profile_get(ldso_gpu_ctx* ctx, int which, double* total_ms, long long* launches, double* units);
 

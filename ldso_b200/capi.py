@@ -134,6 +134,11 @@ class Ctx:
     def launch_count(self):
         return self.api.fn("launch_count")(self.h)
 
+    def io_bytes(self):
+        a, b = C.c_longlong(), C.c_longlong()
+        self._call("io_bytes", C.byref(a), C.byref(b))
+        return a.value, b.value
+
     def timer_start(self):
         self._call("timer_start")
 

@@ -314,8 +314,10 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     const float4* l2 = c->frame[slot] + c->lvl_off[2];
     LDSO_CUDA_OK(c, cudaMemsetAsync(S->map, 0, sizeof(float) * (size_t)g.w * g.h, s));
     LDSO_CUDA_OK(c, cudaMemsetAsync(S->counts, 0, 8 * sizeof(int), s));
+    prof_begin(c, s);
     a2_cand0_kernel<<<(nslots + 127) / 128, 128, 0, s>>>(g, l0, S->thsS, S->mask, S->cand, nslots);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(S->mask_pinned, S->mask, (size_t)nslots * sizeof(unsigned short), cudaMemcpyDeviceToHost, s));
+    prof_end(c, s, LDSO_PROF_A2, (double)g.w * g.h);
+    LDSO_CUDA_OK(c, ldso_copy(c, S->mask_pinned, S->mask, (size_t)nslots * sizeof(unsigned short), cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
     // the ordered scan: which direction each pot-block sees, and the running level-0 count
     int n2 = 0;
@@ -325,11 +327,13 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
         S->dsel_pinned[b] = (unsigned char)d;
         n2 += (S->mask_pinned[b] >> d) & 1;
     }
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(S->dsel, S->dsel_pinned, nslots, cudaMemcpyHostToDevice, s));
+    LDSO_CUDA_OK(c, ldso_copy(c, S->dsel, S->dsel_pinned, nslots, cudaMemcpyHostToDevice, s));
     const int n4blocks = g.n4x * g.n4y;
+    prof_begin(c, s);
     a2_final_kernel<<<(n4blocks + 63) / 64, 64, 0, s>>>(g, l0, l1, l2, S->thsS, S->mask, S->cand, S->dsel, S->map, S->counts);
+    prof_end(c, s, LDSO_PROF_A2, 0);
     c->launches += 2;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
     n[0] = n2; n[1] = S->counts_pinned[1]; n[2] = S->counts_pinned[2];
     return 0;
@@ -380,7 +384,7 @@ extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float densit
         a2_thin_scan_kernel<<<1, 1024, 0, s>>>(S->row_cnt, h);
         a2_thin_apply_kernel<<<(h + 7) / 8, 256, 0, s>>>(S->map, w, h, S->row_cnt, S->rp, charTH, S->counts + 4);
         c->launches += 3;
-        LDSO_CUDA_OK(c, cudaMemcpyAsync(S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
+        LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
         LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
         numHaveSub -= S->counts_pinned[4];
     }
@@ -388,7 +392,7 @@ extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float densit
     *n_selected = numHaveSub;
     LDSO_CUDA_OK(c, cudaGetLastError());
     float* hmap = (float*)c->scratch_host;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(hmap, S->map, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, ldso_copy(c, hmap, S->map, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
     memcpy(map_out, hmap, sizeof(float) * (size_t)w * h);
     return 0;

@@ -53,8 +53,6 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaStreamCreateWithFlags(&c->stream_map, cudaStreamNonBlocking));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev0));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev1));
-    LDSO_CUDA_OK(c, cudaEventCreate(&c->pev0));
-    LDSO_CUDA_OK(c, cudaEventCreate(&c->pev1));
     c->frame = new float4*[cfg.n_frame_slots]();
     for (int s = 0; s < cfg.n_frame_slots; s++) LDSO_CUDA_OK(c, cudaMalloc(&c->frame[s], off * sizeof(float4)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->img_dev, npx0 * sizeof(float)));
@@ -91,6 +89,9 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaMemset(c->trk_counter, 0, sizeof(unsigned int)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->trk_result_dev, 64 * sizeof(double)));
     LDSO_CUDA_OK(c, cudaMallocHost(&c->trk_result_pinned, 64 * sizeof(double)));
+    LDSO_CUDA_OK(c, cudaHostAlloc(&c->trk_mailbox, 64 * sizeof(double), cudaHostAllocMapped));
+    LDSO_CUDA_OK(c, cudaHostGetDevicePointer((void**)&c->trk_mailbox_dev, c->trk_mailbox, 0));
+    memset(c->trk_mailbox, 0, 64 * sizeof(double));
     if (win_alloc(c)) return -1;
     LDSO_CUDA_OK(c, cudaDeviceSynchronize());
     return 0;
@@ -134,10 +135,11 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     cudaFree(c->img_dev); cudaFreeHost(c->img_pinned); cudaFreeHost(c->scratch_host); cudaFree(c->gammaB_dev);
     cudaFree(c->trk_partials); cudaFree(c->trk_partials_i); cudaFree(c->trk_counter); cudaFree(c->trk_result_dev);
     cudaFreeHost(c->trk_result_pinned);
+    cudaFreeHost(c->trk_mailbox);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
-    if (c->pev0) cudaEventDestroy(c->pev0);
-    if (c->pev1) cudaEventDestroy(c->pev1);
+    prof_drain(c);
+    for (cudaEvent_t e : c->prof_free) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->stream_map) cudaStreamDestroy(c->stream_map);
     delete c;
@@ -157,6 +159,10 @@ extern "C" int ldso_gpu_sync(ldso_gpu_ctx* c) {
 }
 extern "C" long long ldso_gpu_launch_count(const ldso_gpu_ctx* c) { return c->launches; }
 
+extern "C" int ldso_gpu_io_bytes(ldso_gpu_ctx* c, long long* h2d, long long* d2h) {
+    *h2d = c->h2d_bytes; *d2h = c->d2h_bytes;
+    return 0;
+}
 extern "C" int ldso_gpu_timer_start(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev0, c->stream));
     return 0;
@@ -168,19 +174,51 @@ extern "C" int ldso_gpu_timer_stop(ldso_gpu_ctx* c, float* ms) {
     return 0;
 }
 
+static cudaEvent_t prof_event(ldso_gpu_ctx* c) {
+    if (!c->prof_free.empty()) { cudaEvent_t e = c->prof_free.back(); c->prof_free.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+void prof_begin(ldso_gpu_ctx* c, cudaStream_t s) {
+    if (!c->profile_on) return;
+    c->prof_cur = prof_event(c);
+    cudaEventRecord(c->prof_cur, s);
+}
+int prof_end(ldso_gpu_ctx* c, cudaStream_t s, int which, double units) {
+    if (!c->profile_on || !c->prof_cur) return -1;
+    cudaEvent_t e1 = prof_event(c);
+    cudaEventRecord(e1, s);
+    c->prof_pending.push_back({which, units, c->prof_cur, e1});
+    c->prof_cur = nullptr;
+    return (int)c->prof_pending.size() - 1;
+}
+void prof_drain(ldso_gpu_ctx* c) {
+    for (auto& r : c->prof_pending) {
+        float ms = 0;
+        cudaEventSynchronize(r.e1);
+        if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+            c->prof_ms[r.which] += ms; c->prof_launches[r.which]++; c->prof_units[r.which] += r.units;
+        }
+        c->prof_free.push_back(r.e0); c->prof_free.push_back(r.e1);
+    }
+    c->prof_pending.clear();
+}
 extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
+    prof_drain(c);
     c->profile_on = on;
-    if (on) for (int i = 0; i < 8; i++) { c->prof_ms[i] = 0; c->prof_launches[i] = 0; c->prof_units[i] = 0; }
+    if (on) for (int i = 0; i < LDSO_PROF_SLOTS; i++) { c->prof_ms[i] = 0; c->prof_launches[i] = 0; c->prof_units[i] = 0; }
     return 0;
 }
 extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms, long long* launches, double* units) {
-    LDSO_REQUIRE(c, which >= 0 && which < 8);
+    LDSO_REQUIRE(c, which >= 0 && which < LDSO_PROF_SLOTS);
+    prof_drain(c);
     *total_ms = c->prof_ms[which]; *launches = c->prof_launches[which]; *units = c->prof_units[which];
     return 0;
 }
 
 extern "C" int ldso_gpu_set_gamma(ldso_gpu_ctx* c, const float B[256]) {
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(c->gammaB_dev, B, 256 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, c->gammaB_dev, B, 256 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -193,7 +231,7 @@ extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float
     // consume the image synchronously into pinned staging, then go asynchronous.
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // previous H2D out of img_pinned has drained
     memcpy(c->img_pinned, img, bytes);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(c->img_dev, c->img_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, c->img_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
     return k1_make_images(c, slot, c->img_dev);
 }
 extern "C" int ldso_gpu_frame_make_images_dev(ldso_gpu_ctx* c, int slot, const float* img_dev) {
@@ -205,7 +243,7 @@ extern "C" int ldso_gpu_frame_download(ldso_gpu_ctx* c, int slot, int lvl, int w
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && lvl >= 0 && lvl < c->levels && dst);
     const size_t n = (size_t)c->wG[lvl] * c->hG[lvl];
     float4* h = (float4*)c->scratch_host;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(h, c->frame[slot] + c->lvl_off[lvl], n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, h, c->frame[slot] + c->lvl_off[lvl], n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     if (what == 0) {
         for (size_t i = 0; i < n; i++) { dst[3 * i] = h[i].x; dst[3 * i + 1] = h[i].y; dst[3 * i + 2] = h[i].z; }
@@ -260,7 +298,7 @@ extern "C" int ldso_gpu_tracker_get_pc(ldso_gpu_ctx* c, int tracker, int lvl, in
     *n = m;
     if (m == 0 || !(u || v || idepth || color)) return 0;
     float4* h = (float4*)c->scratch_host;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(h, T.pc[lvl], (size_t)m * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, h, T.pc[lvl], (size_t)m * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     for (int i = 0; i < m; i++) {
         if (u) u[i] = h[i].x;

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "../../include/ldso_gpu.h"
 #include "../../include/ldso_smallmat.h"
@@ -83,17 +84,25 @@ struct ldso_gpu_ctx {
     int* trk_partials_i = nullptr;          // [trk_max_blocks][4]
     unsigned int* trk_counter = nullptr;
     double* trk_result_dev = nullptr;       // [64]
-    double* trk_result_pinned = nullptr;    // [64]
+    double* trk_result_pinned = nullptr;    // [64] scratch for small read-backs
+    double* trk_mailbox = nullptr;          // [64] mapped pinned: the fused tracker kernel writes its sums + a sequence number here
+    double* trk_mailbox_dev = nullptr;      // device alias of trk_mailbox
+    unsigned long long trk_seq = 0;
     WindowDev win;
     void* selector = nullptr;               // SelectorDev (a2_selector.cu), created on first use
     void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use
     long long launches = 0;
-    // optional per-kernel CUDA-event profile (ldso_gpu_profile_*): [0] = fused tracker kernel
+    long long h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by the entry points (bench.py e2e accounting)
+    // optional per-kernel CUDA-event profile (ldso_gpu_profile_*); slots: see LDSO_PROF_* in include/ldso_gpu.h.
+    // Event pairs are recorded around launches and resolved lazily in profile_get, so profiling adds no sync.
     int profile_on = 0;
-    cudaEvent_t pev0 = nullptr, pev1 = nullptr;
-    double prof_ms[8] = {0};
-    long long prof_launches[8] = {0};
-    double prof_units[8] = {0};
+    struct ProfRec { int which; double units; cudaEvent_t e0, e1; };
+    std::vector<ProfRec> prof_pending;
+    std::vector<cudaEvent_t> prof_free;
+    cudaEvent_t prof_cur = nullptr;
+    double prof_ms[LDSO_PROF_SLOTS] = {0};
+    long long prof_launches[LDSO_PROF_SLOTS] = {0};
+    double prof_units[LDSO_PROF_SLOTS] = {0};
     std::string err;
 
     void set_error(const std::string& what, const char* file, int line) {
@@ -103,8 +112,18 @@ struct ldso_gpu_ctx {
     }
 };
 
+// every host<->device copy of the library goes through here so that the traffic is accounted
+inline cudaError_t ldso_copy(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
+    if (kind == cudaMemcpyHostToDevice) c->h2d_bytes += (long long)bytes;
+    else if (kind == cudaMemcpyDeviceToHost) c->d2h_bytes += (long long)bytes;
+    return cudaMemcpyAsync(dst, src, bytes, kind, s);
+}
+
 // kernels (one translation unit each)
 void selector_free(ldso_gpu_ctx* c);
+void prof_begin(ldso_gpu_ctx* c, cudaStream_t s);
+int prof_end(ldso_gpu_ctx* c, cudaStream_t s, int which, double units);   // index into prof_pending or -1
+void prof_drain(ldso_gpu_ctx* c);
 void immature_free(ldso_gpu_ctx* c);
 int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev);
 int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u, const float* v, const float* id,

@@ -160,8 +160,10 @@ int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
         attr_set = true;
     }
     dim3 grid((c->wG[0] + K1_TW - 1) / K1_TW, (c->hG[0] + K1_TH - 1) / K1_TH);
+    prof_begin(c, c->stream);
     k1_pyramid_kernel<<<grid, K1_THREADS, smem_floats * sizeof(float), c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p);
     k1_wrap_columns_kernel<<<(border + 127) / 128, 128, 0, c->stream>>>(c->frame[slot], c->gammaB_dev, p);
+    prof_end(c, c->stream, LDSO_PROF_K1, 1);
     c->launches += 2;
     LDSO_CUDA_OK(c, cudaGetLastError());
     return 0;

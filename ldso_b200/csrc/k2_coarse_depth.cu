@@ -172,8 +172,9 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
         memcpy(hp + n, v, n * sizeof(float));
         memcpy(hp + 2 * n, id, n * sizeof(float));
         memcpy(hp + 3 * n, hdi, n * sizeof(float));
-        LDSO_CUDA_OK(c, cudaMemcpyAsync(dp, hp, 4 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice, s));
+        LDSO_CUDA_OK(c, ldso_copy(c, dp, hp, 4 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice, s));
     }
+    prof_begin(c, s);
     size_t n0 = (size_t)T.w[0] * T.h[0];
     LDSO_CUDA_OK(c, cudaMemsetAsync(T.idepth[0], 0, n0 * sizeof(float), s));
     LDSO_CUDA_OK(c, cudaMemsetAsync(T.wsum[0], 0, n0 * sizeof(float), s));
@@ -190,7 +191,7 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
     }
     for (int l = 0; l < L; l++) {
         int nl = T.w[l] * T.h[l];
-        LDSO_CUDA_OK(c, cudaMemcpyAsync(T.wsum_bak[l], T.wsum[l], nl * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        LDSO_CUDA_OK(c, ldso_copy(c, T.wsum_bak[l], T.wsum[l], nl * sizeof(float), cudaMemcpyDeviceToDevice, s));
         k2_dilate_kernel<<<(nl + 255) / 256, 256, 0, s>>>(T.idepth[l], T.wsum[l], T.wsum_bak[l], T.w[l], T.h[l], l < 2 ? 1 : 0);
         c->launches++;
     }
@@ -208,9 +209,10 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
     k2_scan_rows_kernel<<<L, 256, 0, s>>>(p, T.row_cnt, T.pc_n_dev);
     k2_emit_rows_kernel<<<(rows + 7) / 8, 256, 0, s>>>(p, T.row_cnt);
     c->launches += 3;
+    prof_end(c, s, LDSO_PROF_K2, n);
     LDSO_CUDA_OK(c, cudaGetLastError());
     int* hn = (int*)c->trk_result_pinned;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(hn, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, ldso_copy(c, hn, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
     for (int l = 0; l < L; l++) T.pc_n[l] = hn[l];
     T.ref_slot = ref_slot;

@@ -10,6 +10,9 @@
 // The warped buffers never exist.  Algorithmic traffic: 16 B point + 4x16 B texels per point.
 #include "ctx.h"
 
+#include <atomic>
+#include <immintrin.h>
+
 namespace {
 
 constexpr int TRK_THREADS = 128;
@@ -43,7 +46,7 @@ __device__ __forceinline__ float4 lerp_texel(const float4* __restrict__ img, flo
 __global__ void __launch_bounds__(TRK_THREADS)
 k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ newImg, const TrkParams p,
                       float* __restrict__ partials, int* __restrict__ partials_i, unsigned int* __restrict__ counter,
-                      double* __restrict__ result) {
+                      double* __restrict__ result, double seq) {
     float acc[NF];
 #pragma unroll
     for (int k = 0; k < NF; k++) acc[k] = 0.f;
@@ -129,6 +132,7 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
     __shared__ float s_f[TRK_THREADS / 32][NF];
     __shared__ unsigned s_i[TRK_THREADS / 32];
     __shared__ bool s_last;
+    __shared__ double s_res[NF + NI];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (lane == 0) {
 #pragma unroll
@@ -168,9 +172,20 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) result[k] = s;
+        if (lane == 0) s_res[k] = s;
     }
-    if (threadIdx.x == 0) *counter = 0u;
+    // `result` is mapped host memory: one warp publishes the sums (a few combined PCIe writes, one system fence),
+    // then the sequence number the host is polling for
+    __syncthreads();
+    if (wid == 0) {
+        for (int k = lane; k < NF + NI; k += 32) result[k] = s_res[k];
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+            *counter = 0u;
+            *reinterpret_cast<volatile double*>(result + 63) = seq;
+        }
+    }
 }
 
 }  // namespace
@@ -204,26 +219,33 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     p.huberTH = c->cfg.huber_th;
     p.cutoffTH = cutoffTH;
     p.maxEnergy = 2 * p.huberTH * cutoffTH - p.huberTH * p.huberTH;   // :563-564
-    double* res = c->trk_result_pinned;
+    volatile double* res = c->trk_mailbox;
     if (p.n <= 0) {
         memset(out, 0, sizeof(*out));
         return 0;
     }
     int blocks = (p.n + TRK_THREADS - 1) / TRK_THREADS;
     if (blocks > c->trk_max_blocks) { c->set_error("tracker point cloud too large", __FILE__, __LINE__); return -2; }
-    if (c->profile_on) cudaEventRecord(c->pev0, c->stream);
+    prof_begin(c, c->stream);
     k34_track_eval_kernel<<<blocks, TRK_THREADS, 0, c->stream>>>(T.pc[lvl], c->frame[T.new_slot] + c->lvl_off[lvl], p,
                                                                  c->trk_partials, c->trk_partials_i, c->trk_counter,
-                                                                 c->trk_result_dev);
+                                                                 c->trk_mailbox_dev, (double)(++c->trk_seq));
     c->launches++;
-    if (c->profile_on) cudaEventRecord(c->pev1, c->stream);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(res, c->trk_result_dev, (NF + NI) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
-    if (c->profile_on) {
-        float ms = 0;
-        cudaEventElapsedTime(&ms, c->pev0, c->pev1);
-        c->prof_ms[0] += ms; c->prof_launches[0]++; c->prof_units[0] += p.n;
+    prof_end(c, c->stream, LDSO_PROF_K34, p.n);
+    LDSO_CUDA_OK(c, cudaGetLastError());
+    // the kernel's last CTA writes the 52 sums and then the sequence number straight into mapped pinned memory:
+    // poll for it instead of paying a D2H copy + stream synchronisation per LM evaluation
+    const double want = (double)c->trk_seq;
+    for (unsigned spin = 1; res[63] != want; spin++) {
+        _mm_pause();
+        if ((spin & 0xfffff) == 0) {   // every ~1M polls make sure the stream is still alive
+            cudaError_t q = cudaStreamQuery(c->stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);
+            if (q == cudaSuccess && res[63] != want) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
+        }
     }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    c->d2h_bytes += (NF + NI + 1) * sizeof(double);
     for (int k = 0; k < NF; k++) out->sums[k] = res[k];
     for (int k = 0; k < NI; k++) out->counts[k] = (int)res[NF + k];
     return 0;

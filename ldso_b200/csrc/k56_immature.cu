@@ -120,7 +120,7 @@ struct K5Params {
 __global__ void __launch_bounds__(IM_THREADS) k5_trace_kernel(const K5Params p) {
     enum { GOOD = 0, OOB, OUTLIER, SKIPPED, BADCONDITION, UNINIT };
     __shared__ float errors[IM_PTS][100];
-    __shared__ int cnt[8];
+    __shared__ int cnt[8];   // [0..5] status histogram, [6] search steps, [7] points that reached the search
     if (threadIdx.x < 8) cnt[threadIdx.x] = 0;
     __syncthreads();
     const int gid = blockIdx.x * IM_THREADS + threadIdx.x;
@@ -319,9 +319,10 @@ __global__ void __launch_bounds__(IM_THREADS) k5_trace_kernel(const K5Params p) 
             if (write_depth) { p.idmin[pt] = idepth_min; p.idmax[pt] = idepth_max; }
         }
         atomicAdd(&cnt[result], 1);
+        if (numSteps > 0) { atomicAdd(&cnt[6], numSteps); atomicAdd(&cnt[7], 1); }
     }
     __syncthreads();
-    if (threadIdx.x < 6 && cnt[threadIdx.x]) atomicAdd(&p.counts[threadIdx.x], cnt[threadIdx.x]);
+    if (threadIdx.x < 8 && cnt[threadIdx.x]) atomicAdd(&p.counts[threadIdx.x], cnt[threadIdx.x]);
 }
 
 // ---- K6b: activation (optimizeImmaturePoint) ----------------------------------------------------------------
@@ -514,14 +515,14 @@ extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const 
     LDSO_REQUIRE(c, u && v && color && weights && grad_h && energy_th);
     float* st = (float*)P->pinned;
     memcpy(st, u, 4 * (size_t)n); memcpy(st + n, v, 4 * (size_t)n);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(P->cr, st, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, P->cr, st, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
     float eth = 8 * c->cfg.outlier_th;
     eth *= c->cfg.overall_energy_th_weight * c->cfg.overall_energy_th_weight;
     k6_create_kernel<<<(8 * n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, c->stream>>>(c->frame[slot], c->wG[0], n,
                                                                                          c->cfg.outlier_th_sum_component, eth, P->cr);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, P->cr + 2 * (size_t)n, 80 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st, P->cr + 2 * (size_t)n, 80 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     for (int i = 0; i < n; i++) {
         const float* r = st + 20 * (size_t)i;
@@ -545,7 +546,7 @@ extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, co
     const size_t N = n;
     auto put = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
         memcpy(st + off, src, bytes);
-        cudaError_t e = cudaMemcpyAsync(dst, st + off, bytes, cudaMemcpyHostToDevice, c->stream);
+        cudaError_t e = ldso_copy(c, dst, st + off, bytes, cudaMemcpyHostToDevice, c->stream);
         off += bytes;
         return e;
     };
@@ -575,7 +576,7 @@ extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_host
         memcpy(T, KRKi + 9 * h, 36); memcpy(T + 9, Kt + 3 * h, 12); memcpy(T + 12, aff + 2 * h, 8);
         T[14] = T[15] = 0;
     }
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(P->tables, st, 64 * (size_t)n_hosts, cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, P->tables, st, 64 * (size_t)n_hosts, cudaMemcpyHostToDevice, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(P->counts, 0, 32, c->stream));
     K5Params p;
     p.img = c->frame[new_slot]; p.n = P->n; p.w = c->wG[0]; p.h = c->hG[0];
@@ -586,21 +587,17 @@ extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_host
     p.host = P->host; p.status = P->status; p.u = P->u; p.v = P->v; p.color = P->color; p.weights = P->weights; p.gradH = P->gradH;
     p.energyTH = P->energyTH; p.tables = P->tables; p.idmin = P->idmin; p.idmax = P->idmax; p.quality = P->quality;
     p.lastUV = P->lastUV; p.interval = P->interval; p.counts = P->counts;
-    const bool prof = c->profile_on;
-    if (prof) cudaEventRecord(c->pev0, c->stream);
+    prof_begin(c, c->stream);
     k5_trace_kernel<<<(8 * P->n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, c->stream>>>(p);
-    if (prof) cudaEventRecord(c->pev1, c->stream);
+    const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K5, P->n);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
     int* cnt = (int*)(st + 16 * LDSO_MAX_WINDOW);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(cnt, P->counts, 24, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, cnt, P->counts, 32, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
-    if (prof) {
-        float ms = 0;
-        cudaEventElapsedTime(&ms, c->pev0, c->pev1);
-        c->prof_ms[1] += ms; c->prof_launches[1]++; c->prof_units[1] += P->n;
-    }
     for (int i = 0; i < 6; i++) counts_out[i] = cnt[i];
+    // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
+    if (prof_idx >= 0) c->prof_pending[prof_idx].units = (double)cnt[6] + 9.0 * cnt[7];
     return 0;
 }
 
@@ -617,7 +614,7 @@ extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* 
     auto get = [&](void* dst, const void* src, size_t bytes) -> cudaError_t {
         if (!dst) return cudaSuccess;
         jobs[nj++] = {dst, off, bytes};
-        cudaError_t e = cudaMemcpyAsync(st + off, src, bytes, cudaMemcpyDeviceToHost, c->stream);
+        cudaError_t e = ldso_copy(c, st + off, src, bytes, cudaMemcpyDeviceToHost, c->stream);
         off += bytes;
         return e;
     };
@@ -640,7 +637,7 @@ extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int
     for (int i = 0; i < n_cand; i++) LDSO_REQUIRE(c, cand[i] >= 0 && cand[i] < P->n);
     int* st = (int*)P->pinned;
     memcpy(st, cand, 4 * (size_t)n_cand);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(P->cand, st, 4 * (size_t)n_cand, cudaMemcpyHostToDevice, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, P->cand, st, 4 * (size_t)n_cand, cudaMemcpyHostToDevice, c->stream));
     K6Params p;
     for (int f = 0; f < LDSO_MAX_WINDOW; f++) p.frame[f] = f < W.n ? c->frame[W.slots[f]] : nullptr;
     p.n = W.n; p.n_cand = n_cand; p.w = c->wG[0]; p.h = c->hG[0]; p.gn_its = c->cfg.gn_its_on_point_activation; p.min_obs = min_obs;
@@ -649,13 +646,15 @@ extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int
     p.precalc = W.precalc; p.cand = P->cand; p.host = P->host; p.u = P->u; p.v = P->v; p.color = P->color; p.weights = P->weights;
     p.energyTH = P->energyTH; p.idmin = P->idmin; p.idmax = P->idmax;
     p.idepth_out = P->act_idepth; p.ok_out = P->act_ok; p.state_out = P->act_state;
+    prof_begin(c, c->stream);
     k6_activate_kernel<<<(8 * n_cand + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, c->stream>>>(p);
+    prof_end(c, c->stream, LDSO_PROF_K6, n_cand);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
     const size_t N = n_cand;
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, P->act_idepth, 4 * N, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + N, P->act_ok, 4 * N, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + 2 * N, P->act_state, 4 * N * W.n, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st, P->act_idepth, 4 * N, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st + N, P->act_ok, 4 * N, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st + 2 * N, P->act_state, 4 * N * W.n, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     memcpy(idepth_out, st, 4 * N); memcpy(ok_out, st + N, 4 * N); memcpy(res_state_out, st + 2 * N, 4 * N * W.n);
     return 0;

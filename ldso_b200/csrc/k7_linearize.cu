@@ -322,7 +322,9 @@ int k7_linearize(ldso_gpu_ctx* c, int fix) {
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.stats, 0, 4 * sizeof(double), c->stream));
     if (W.nr > 0) {
         int threads = W.nr * 8;
+        prof_begin(c, c->stream);
         k7_linearize_kernel<<<(threads + K7_THREADS - 1) / K7_THREADS, K7_THREADS, 0, c->stream>>>(p);
+        prof_end(c, c->stream, LDSO_PROF_K7, W.nr);
         c->launches++;
     }
     LDSO_CUDA_OK(c, cudaGetLastError());

@@ -146,9 +146,11 @@ int k8_accumulate_top(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.acc_top_cnt, 0, sizeof(int) * 2 * nn, c->stream));
     if (W.n_chunks > 0) {
         float4 cd = make_float4(W.cDeltaF[0], W.cDeltaF[1], W.cDeltaF[2], W.cDeltaF[3]);
+        prof_begin(c, c->stream);
         k8_top_kernel<<<W.n_chunks, K8_THREADS, 0, c->stream>>>(W.n, W.chunk, W.order, W.flags, W.r_point, W.r_target, W.host, W.J,
                                                                 W.rtz, W.adHTdelta, cd, W.idepth, W.idepth_zero, W.res_pt,
                                                                 W.acc_top, W.acc_top_cnt);
+        prof_end(c, c->stream, LDSO_PROF_K8, W.nr);
         c->launches++;
     }
     LDSO_CUDA_OK(c, cudaGetLastError());

@@ -41,6 +41,7 @@ struct WindowDev {
     int n_chunks = 0;
     int* sc_blocks = nullptr;      // [n_sc_blocks][3] = host, first point, end point (K9 CTA table)
     int n_sc_blocks = 0;
+    int* ridx = nullptr;           // [cap_p][LDSO_MAX_WINDOW] residual id of (point, target) or -1 (written by K9a)
     // device: small tables
     float* adHTdelta = nullptr;    // [n*n][8]
     float* xAd = nullptr;          // [n*n][8] + xc[4]
@@ -50,6 +51,9 @@ struct WindowDev {
     int* acc_top_cnt = nullptr;    // [2][n*n]
     double* acc_sc = nullptr;      // accD [n^3][64] | accE [n^2][32] | accEB [n^2][8] | accHcc [16] | accbc [4]
     size_t acc_sc_size = 0;
+    double *adH_dev = nullptr, *adT_dev = nullptr;   // [n*n][64] adjoints (setAdjointsF)
+    double* prior_dev = nullptr;   // cPrior[4] cDelta[4] fprior[8n] fdelta_prior[8n]
+    double* stitched = nullptr;    // [3] x ((8n+4)^2 + (8n+4)): H,b of the active, linearised and Schur systems
     // host mirrors
     std::vector<int> h_host, h_res_begin, h_target, h_point, h_host_begin;
     std::vector<unsigned char> h_lin;
@@ -59,7 +63,7 @@ struct WindowDev {
     double cPrior[4] = {0, 0, 0, 0};
     // pinned staging
     void* pinned = nullptr;
-    size_t pinned_bytes = 0;
+    size_t pinned_bytes = 0, pinned_off = 0;
 };
 
 struct ldso_gpu_ctx;
@@ -72,3 +76,4 @@ int k7_fix_linearization(ldso_gpu_ctx* c, const unsigned char* mask_dev);
 int k8_accumulate_top(ldso_gpu_ctx* c);
 int k9_accumulate_sc(ldso_gpu_ctx* c);
 int k10_resubstitute(ldso_gpu_ctx* c, float lambda);
+int h1_stitch(ldso_gpu_ctx* c);

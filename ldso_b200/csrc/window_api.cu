@@ -16,27 +16,33 @@ template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
     return 0;
 }
 
-// pinned staging that grows on demand (window uploads happen once per keyframe, not per frame)
+// Pinned staging ring.  Uploads are queued: the host buffer is copied into the ring at the cursor and the H2D copy
+// is issued without waiting (the caller may reuse its buffer at once; kernels on the same stream are ordered behind
+// the copy).  The ring is only rewound after a stream synchronisation, so a window upload costs one sync at most.
 void* staging(ldso_gpu_ctx* c, size_t bytes) {
     WindowDev& W = c->win;
-    if (W.pinned_bytes < bytes) {
-        if (W.pinned) cudaFreeHost(W.pinned);
-        W.pinned = nullptr;
-        size_t nb = std::max(bytes, (size_t)1 << 20);
-        if (cudaMallocHost(&W.pinned, nb) != cudaSuccess) { W.pinned_bytes = 0; return nullptr; }
-        W.pinned_bytes = nb;
+    const size_t need = (bytes + 255) & ~(size_t)255;
+    if (W.pinned_off + need > W.pinned_bytes) {
+        if (W.pinned_off > 0) { cudaStreamSynchronize(c->stream); W.pinned_off = 0; }
+        if (need > W.pinned_bytes) {
+            if (W.pinned) cudaFreeHost(W.pinned);
+            W.pinned = nullptr;
+            size_t nb = std::max(need, (size_t)4 << 20);
+            if (cudaMallocHost(&W.pinned, nb) != cudaSuccess) { W.pinned_bytes = 0; return nullptr; }
+            W.pinned_bytes = nb;
+        }
     }
-    return W.pinned;
+    void* p = (char*)W.pinned + W.pinned_off;
+    W.pinned_off += need;
+    return p;
 }
 
 int upload(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return 0;
-    // synchronous w.r.t. the host buffer: copy through pinned staging, then wait (cold path)
     void* st = staging(c, bytes);
     if (!st) { c->set_error("pinned staging allocation failed", __FILE__, __LINE__); return -1; }
     memcpy(st, src, bytes);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(dst, st, bytes, cudaMemcpyHostToDevice, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, dst, st, bytes, cudaMemcpyHostToDevice, c->stream));
     return 0;
 }
 
@@ -44,9 +50,10 @@ int download(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return 0;
     void* st = staging(c, bytes);
     if (!st) { c->set_error("pinned staging allocation failed", __FILE__, __LINE__); return -1; }
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st, src, bytes, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     memcpy(dst, st, bytes);
+    c->win.pinned_off = 0;   // everything queued before has completed
     return 0;
 }
 
@@ -70,10 +77,13 @@ int win_alloc(ldso_gpu_ctx* c) {
     rc |= dalloc(c, &W.center, R * 4); rc |= dalloc(c, &W.res_pt, R * 8);
     rc |= dalloc(c, &W.order, R); rc |= dalloc(c, &W.chunk, 3 * (R / 1 + 2 * M * M + 8));
     rc |= dalloc(c, &W.sc_blocks, 3 * (P + M + 8));
+    rc |= dalloc(c, &W.ridx, P * M);
     rc |= dalloc(c, &W.adHTdelta, M * M * 8); rc |= dalloc(c, &W.xAd, M * M * 8 + 8); rc |= dalloc(c, &W.stats, 4);
     rc |= dalloc(c, &W.acc_top, 2 * M * M * WIN_TOP_STRIDE); rc |= dalloc(c, &W.acc_top_cnt, 2 * M * M);
     W.acc_sc_size = M * M * M * 64 + M * M * 40 + 20;
     rc |= dalloc(c, &W.acc_sc, W.acc_sc_size);
+    rc |= dalloc(c, &W.adH_dev, M * M * 64); rc |= dalloc(c, &W.adT_dev, M * M * 64); rc |= dalloc(c, &W.prior_dev, 8 + 16 * M);
+    rc |= dalloc(c, &W.stitched, 3 * ((8 * M + 4) * (8 * M + 4) + (8 * M + 4)));
     return rc ? -1 : 0;
 }
 
@@ -81,8 +91,8 @@ void win_free(ldso_gpu_ctx* c) {
     WindowDev& W = c->win;
     void* ptrs[] = {W.precalc, W.u, W.v, W.idepth, W.idepth_zero, W.prior, W.color, W.weights, W.host, W.res_begin, W.pt_out,
                     W.max_rel_baseline, W.num_good, W.r_point, W.r_target, W.state, W.new_state, W.flags, W.energy, W.new_energy,
-                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.adHTdelta, W.xAd,
-                    W.stats, W.acc_top, W.acc_top_cnt, W.acc_sc};
+                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.ridx, W.adHTdelta, W.xAd,
+                    W.stats, W.acc_top, W.acc_top_cnt, W.acc_sc, W.adH_dev, W.adT_dev, W.prior_dev, W.stitched};
     for (void* p : ptrs) cudaFree(p);
     if (W.pinned) cudaFreeHost(W.pinned);
 }
@@ -123,7 +133,7 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * WIN_PT_ROWS * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.max_rel_baseline, 0, sizeof(float) * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.num_good, 0, sizeof(float) * W.cap_p, c->stream));
-    // K9 CTA table: 64 consecutive points of one host per CTA
+    // K9 CTA table: up to 64 consecutive points of one host per CTA
     std::vector<int> blk;
     int p = 0;
     while (p < np) {
@@ -205,7 +215,14 @@ extern "C" int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* c, const double* adH, 
     for (int i = 0; i < 64 * nn; i++) { W.adHostF[i] = (float)adH[i]; W.adTargetF[i] = (float)adT[i]; }
     for (int i = 0; i < 4; i++) { W.cDeltaF[i] = cDelta[i]; W.cPrior[i] = cPrior[i]; }
     W.fprior.assign(fprior, fprior + 8 * W.n); W.fdelta_prior.assign(fdelta_prior, fdelta_prior + 8 * W.n);
-    return upload(c, W.adHTdelta, adHTdelta, sizeof(float) * 8 * nn);
+    std::vector<double> pr(8 + 16 * (size_t)W.n);
+    for (int i = 0; i < 4; i++) { pr[i] = cPrior[i]; pr[4 + i] = (double)cDelta[i]; }
+    for (int i = 0; i < 8 * W.n; i++) { pr[8 + i] = fprior[i]; pr[8 + 8 * W.n + i] = fdelta_prior[i]; }
+    int rc = upload(c, W.adH_dev, adH, sizeof(double) * 64 * nn);
+    rc |= upload(c, W.adT_dev, adT, sizeof(double) * 64 * nn);
+    rc |= upload(c, W.prior_dev, pr.data(), sizeof(double) * pr.size());
+    rc |= upload(c, W.adHTdelta, adHTdelta, sizeof(float) * 8 * nn);
+    return rc ? -1 : 0;
 }
 
 extern "C" int ldso_gpu_window_set_idepth(ldso_gpu_ctx* c, const float* idepth, const float* idepth_zero) {
@@ -226,9 +243,10 @@ extern "C" int ldso_gpu_window_linearize(ldso_gpu_ctx* c, int fix, double stats[
     const size_t bytes = 4 * sizeof(double) + sizeof(float) * (size_t)W.nr;
     char* st = (char*)staging(c, bytes);
     LDSO_REQUIRE(c, st != nullptr);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, W.stats, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    if (W.nr) LDSO_CUDA_OK(c, cudaMemcpyAsync(st + 4 * sizeof(double), W.new_energy_wo, sizeof(float) * W.nr, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st, W.stats, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (W.nr) LDSO_CUDA_OK(c, ldso_copy(c, st + 4 * sizeof(double), W.new_energy_wo, sizeof(float) * W.nr, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    W.pinned_off = 0;
     const double* ds = (const double*)st;
     stats[0] = ds[0]; stats[1] = 0; stats[2] = ds[1];
     // FullSystem::setNewFrameEnergyTH (src/frontend/FullSystem.cc:2078-2109): 70th percentile over the residuals
@@ -273,158 +291,7 @@ extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned
     return build_order(c);
 }
 
-// ---- K8 + K9 + stitching -------------------------------------------------------------------------
-namespace {
-
-struct Dense {
-    int D;
-    double* H;
-    double* b;
-    double& at(int r, int cc) { return H[(size_t)r * D + cc]; }
-    // H[r0.., c0..] += A(8x8) * M(8 x m) * B^T (m x 8), m == 8
-    void add_ABt(int r0, int c0, const double* AM, const double* B) {
-        for (int i = 0; i < 8; i++)
-            for (int j = 0; j < 8; j++) {
-                double s = 0;
-                for (int l = 0; l < 8; l++) s += AM[i * 8 + l] * B[j * 8 + l];
-                at(r0 + i, c0 + j) += s;
-            }
-    }
-};
-
-void mul88(const double* A, const double* M, double* out) {
-    for (int i = 0; i < 8; i++)
-        for (int j = 0; j < 8; j++) {
-            double s = 0;
-            for (int l = 0; l < 8; l++) s += A[i * 8 + l] * M[l * 8 + j];
-            out[i * 8 + j] = s;
-        }
-}
-
-// AccumulatorApprox::finish layout -> 13x13 (MatrixAccumulators.h:771-800)
-void unpack13(const double* a, double M[13][13]) {
-    int idx = 0;
-    for (int r = 0; r < 10; r++)
-        for (int cc = r; cc < 10; cc++) M[r][cc] = M[cc][r] = a[idx++];
-    for (int r = 0; r < 10; r++)
-        for (int cc = 0; cc < 3; cc++) M[r][10 + cc] = M[10 + cc][r] = a[55 + 3 * r + cc];
-    M[10][10] = a[85]; M[10][11] = M[11][10] = a[86]; M[10][12] = M[12][10] = a[87];
-    M[11][11] = a[88]; M[11][12] = M[12][11] = a[89]; M[12][12] = a[90];
-}
-
-// AccumulatedTopHessianSSE::stitchDoubleInternal + the symmetrisation of stitchDoubleMT
-void stitch_top(WindowDev& W, const double* acc, const int* cnt, bool usePrior, double* Hout, double* bout) {
-    const int n = W.n, D = 8 * n + CPARS;
-    Dense S{D, Hout, bout};
-    std::fill(Hout, Hout + (size_t)D * D, 0.0);
-    std::fill(bout, bout + D, 0.0);
-    for (int k = 0; k < n * n; k++) {
-        if (cnt[k] == 0) continue;
-        const int h = k % n, t = k / n, hI = CPARS + 8 * h, tI = CPARS + 8 * t;
-        double M[13][13];
-        unpack13(acc + (size_t)k * WIN_TOP_STRIDE, M);
-        const double* AH = &W.adHost[64 * k];
-        const double* AT = &W.adTarget[64 * k];
-        double P[64], AHP[64], ATP[64];
-        for (int i = 0; i < 8; i++)
-            for (int j = 0; j < 8; j++) P[i * 8 + j] = M[CPARS + i][CPARS + j];
-        mul88(AH, P, AHP);
-        mul88(AT, P, ATP);
-        S.add_ABt(hI, hI, AHP, AH);
-        S.add_ABt(tI, tI, ATP, AT);
-        S.add_ABt(hI, tI, AHP, AT);
-        for (int i = 0; i < 8; i++) {
-            double bh = 0, bt = 0;
-            for (int l = 0; l < 8; l++) { bh += AH[i * 8 + l] * M[CPARS + l][8 + CPARS]; bt += AT[i * 8 + l] * M[CPARS + l][8 + CPARS]; }
-            bout[hI + i] += bh; bout[tI + i] += bt;
-            for (int j = 0; j < CPARS; j++) {
-                double sh = 0, st = 0;
-                for (int l = 0; l < 8; l++) { sh += AH[i * 8 + l] * M[CPARS + l][j]; st += AT[i * 8 + l] * M[CPARS + l][j]; }
-                S.at(hI + i, j) += sh; S.at(tI + i, j) += st;
-            }
-        }
-        for (int i = 0; i < CPARS; i++) {
-            for (int j = 0; j < CPARS; j++) S.at(i, j) += M[i][j];
-            bout[i] += M[i][8 + CPARS];
-        }
-    }
-    if (usePrior) {
-        for (int i = 0; i < CPARS; i++) { S.at(i, i) += W.cPrior[i]; bout[i] += W.cPrior[i] * (double)W.cDeltaF[i]; }
-        for (int h = 0; h < n; h++)
-            for (int i = 0; i < 8; i++) {
-                S.at(CPARS + 8 * h + i, CPARS + 8 * h + i) += W.fprior[8 * h + i];
-                bout[CPARS + 8 * h + i] += W.fprior[8 * h + i] * W.fdelta_prior[8 * h + i];
-            }
-    }
-    for (int h = 0; h < n; h++) {
-        const int hI = CPARS + 8 * h;
-        for (int i = 0; i < CPARS; i++)
-            for (int j = 0; j < 8; j++) S.at(i, hI + j) = S.at(hI + j, i);
-        for (int t = h + 1; t < n; t++) {
-            const int tI = CPARS + 8 * t;
-            for (int i = 0; i < 8; i++)
-                for (int j = 0; j < 8; j++) S.at(hI + i, tI + j) += S.at(tI + j, hI + i);
-            for (int i = 0; i < 8; i++)
-                for (int j = 0; j < 8; j++) S.at(tI + i, hI + j) = S.at(hI + j, tI + i);
-        }
-    }
-}
-
-// AccumulatedSCHessianSSE::stitchDoubleInternal + stitchDoubleMT tail
-void stitch_sc(WindowDev& W, const double* acc, double* Hout, double* bout) {
-    const int n = W.n, nn = n * n, D = 8 * n + CPARS;
-    Dense S{D, Hout, bout};
-    std::fill(Hout, Hout + (size_t)D * D, 0.0);
-    std::fill(bout, bout + D, 0.0);
-    const double* accD = acc;
-    const double* accE = acc + (size_t)nn * n * 64;
-    const double* accEB = accE + (size_t)nn * 32;
-    const double* accHcc = accEB + (size_t)nn * 8;
-    const double* accbc = accHcc + 16;
-    for (int ij = 0; ij < nn; ij++) {
-        const int i = ij % n, j = ij / n, iI = CPARS + 8 * i, jI = CPARS + 8 * j;
-        const double* AHij = &W.adHost[64 * ij];
-        const double* ATij = &W.adTarget[64 * ij];
-        const double* E = accE + (size_t)ij * 32;
-        const double* EB = accEB + (size_t)ij * 8;
-        for (int a = 0; a < 8; a++) {
-            double bh = 0, bt = 0;
-            for (int l = 0; l < 8; l++) { bh += AHij[a * 8 + l] * EB[l]; bt += ATij[a * 8 + l] * EB[l]; }
-            bout[iI + a] += bh; bout[jI + a] += bt;
-            for (int q = 0; q < CPARS; q++) {
-                double sh = 0, st = 0;
-                for (int l = 0; l < 8; l++) { sh += AHij[a * 8 + l] * E[l * 4 + q]; st += ATij[a * 8 + l] * E[l * 4 + q]; }
-                S.at(iI + a, q) += sh; S.at(jI + a, q) += st;
-            }
-        }
-        for (int k = 0; k < n; k++) {
-            const double* Dm = accD + (size_t)(ij + k * nn) * 64;
-            bool any = false;
-            for (int q = 0; q < 64 && !any; q++) any = Dm[q] != 0.0;
-            if (!any) continue;
-            const int kI = CPARS + 8 * k, ik = i + n * k;
-            const double* AHik = &W.adHost[64 * ik];
-            const double* ATik = &W.adTarget[64 * ik];
-            double AHD[64], ATD[64];
-            mul88(AHij, Dm, AHD);
-            mul88(ATij, Dm, ATD);
-            S.add_ABt(iI, iI, AHD, AHik);
-            S.add_ABt(jI, kI, ATD, ATik);
-            S.add_ABt(jI, iI, ATD, AHik);
-            S.add_ABt(iI, kI, AHD, ATik);
-        }
-    }
-    for (int a = 0; a < CPARS; a++) {
-        for (int q = 0; q < CPARS; q++) S.at(a, q) += accHcc[a * 4 + q];
-        bout[a] += accbc[a];
-    }
-    for (int h = 0; h < n; h++)
-        for (int a = 0; a < CPARS; a++)
-            for (int q = 0; q < 8; q++) S.at(a, CPARS + 8 * h + q) = S.at(CPARS + 8 * h + q, a);
-}
-
-}  // namespace
-
+// ---- K8 + K9 + stitching (h1_stitch.cu) --------------------------------------------------------------
 extern "C" int ldso_gpu_window_accumulate(ldso_gpu_ctx* c, double* HA, double* bA, double* HL, double* bL, double* Hsc,
                                           double* bsc, int counts[2]) {
     WindowDev& W = c->win;
@@ -434,22 +301,26 @@ extern "C" int ldso_gpu_window_accumulate(ldso_gpu_ctx* c, double* HA, double* b
     if (rc) return rc;
     rc = k9_accumulate_sc(c);
     if (rc) return rc;
-    const int n = W.n, nn = n * n;
-    const size_t nTop = (size_t)2 * nn * WIN_TOP_STRIDE, nSc = (size_t)nn * n * 64 + (size_t)nn * 40 + 20;
-    const size_t bytes = sizeof(double) * (nTop + nSc) + sizeof(int) * 2 * nn;
+    rc = h1_stitch(c);
+    if (rc) return rc;
+    const int n = W.n, nn = n * n, D = 8 * n + CPARS;
+    const size_t sysz = (size_t)D * D + D;
+    const size_t bytes = sizeof(double) * 3 * sysz + sizeof(int) * 2 * nn;
     char* st = (char*)staging(c, bytes);
     LDSO_REQUIRE(c, st != nullptr);
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st, W.acc_top, sizeof(double) * nTop, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + sizeof(double) * nTop, W.acc_sc, sizeof(double) * nSc, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaMemcpyAsync(st + sizeof(double) * (nTop + nSc), W.acc_top_cnt, sizeof(int) * 2 * nn, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * 2 * nn, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
-    const double* top = (const double*)st;
-    const double* sc = top + nTop;
-    const int* cnt = (const int*)(st + sizeof(double) * (nTop + nSc));
-    stitch_top(W, top, cnt, false, HA, bA);
-    stitch_top(W, top + (size_t)nn * WIN_TOP_STRIDE, cnt + nn, true, HL, bL);
-    stitch_sc(W, sc, Hsc, bsc);
+    W.pinned_off = 0;
+    const double* sys = (const double*)st;
+    double* Hs[3] = {HA, HL, Hsc};
+    double* bs[3] = {bA, bL, bsc};
+    for (int q = 0; q < 3; q++) {
+        memcpy(Hs[q], sys + q * sysz, sizeof(double) * D * D);
+        memcpy(bs[q], sys + q * sysz + (size_t)D * D, sizeof(double) * D);
+    }
     if (counts) {
+        const int* cnt = (const int*)(st + sizeof(double) * 3 * sysz);
         counts[0] = counts[1] = 0;
         for (int k = 0; k < nn; k++) { counts[0] += cnt[k]; counts[1] += cnt[nn + k]; }
     }

@@ -134,19 +134,24 @@ PATTERN = np.array([[0, -2], [-1, -1], [1, -1], [-2, 0], [0, 0], [2, 0], [-1, 1]
 
 
 def make_window(seed=1001, frame_ids=(40, 46, 52, 58, 64, 70, 76), pts_per_frame=300, w=640, h=480, fx=384.0, fy=384.0,
-                cx=319.5, cy=239.5, pose_noise=2e-4, idepth_noise=0.02, lin_frac=0.25, rng_seed=5):
+                cx=319.5, cy=239.5, pose_noise=2e-4, idepth_noise=0.02, lin_frac=0.25, rng_seed=5, rendered=None):
     """A frozen sliding window with realistic distributions: n keyframes of the synthetic sequence, points hosted in
     every frame with ground-truth inverse depth (+noise), one residual per (point, other frame).  Returns a dict of the
     arrays the window C ABI takes.  Frame states are slightly perturbed from ground truth so that the system has a
-    non-trivial gradient; the FEJ evaluation point differs slightly from the current state."""
+    non-trivial gradient; the FEJ evaluation point differs slightly from the current state.
+    rendered: optional list of (img, depth, (R, t)) already rendered for frame_ids (bench.py reuses its sequence)."""
     from . import window_host as wh
     rng = np.random.default_rng(rng_seed)
-    sc = Scene(seed)
     n = len(frame_ids)
     imgs, deps, w2c_gt = [], [], []
-    for i in frame_ids:
-        R, t = trajectory(i)
-        img, dep = render(sc, w, h, fx, fy, cx, cy, R, t)
+    if rendered is None:
+        sc = Scene(seed)
+        rendered = []
+        for i in frame_ids:
+            R, t = trajectory(i)
+            img, dep = render(sc, w, h, fx, fy, cx, cy, R, t)
+            rendered.append((img, dep, (R, t)))
+    for img, dep, (R, t) in rendered:
         imgs.append(img); deps.append(dep)
         w2c_gt.append((R.T, -R.T @ t))
 

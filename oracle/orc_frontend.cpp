@@ -77,6 +77,7 @@ extern "C" int orc_create(const ldso_gpu_config* cfg, orc_ctx** out) {
     return 0;
 }
 extern "C" void orc_destroy(orc_ctx* c) { delete c; }
+extern "C" int orc_io_bytes(orc_ctx*, long long* h2d, long long* d2h) { *h2d = 0; *d2h = 0; return 0; }   // no device
 extern "C" const char* orc_last_error(const orc_ctx* c) { return c->err.c_str(); }
 extern "C" int orc_pyr_levels(const orc_ctx* c) { return c->levels; }
 extern "C" int orc_level_size(const orc_ctx* c, int lvl, int* w, int* h) {
