@@ -156,11 +156,15 @@ class Sequence:
     def new_immature(self, f, host_idx):
         """PixelSelector::makeMaps + ImmaturePoint constructor for keyframe f (FullSystem::makeNewTraces, :1426-1482)"""
         sl = self.kf_slot(f)
+        t = time.perf_counter()
         m, n, self.potential = self.ctx.select_make_maps(sl, N_IMMATURE, potential=getattr(self, "potential", 3))
+        t = self.tick("KF A2 makeMaps", t)
         m[:5, :] = 0; m[-5:, :] = 0; m[:, :5] = 0; m[:, -5:] = 0          # patternPadding+1 border (:1444-1446)
         v, u = np.nonzero(m)
         u = u.astype(np.float32); v = v.astype(np.float32)
+        t = self.tick("KF host: map -> point list", t)
         col, wgt, gh, eth = self.ctx.immature_create(sl, u, v)
+        t = self.tick("KF K6 ImmaturePoint ctor", t)
         ok = np.isfinite(eth)
         k = int(ok.sum())
         return dict(host=np.full(k, host_idx, np.int32), u=u[ok], v=v[ok], color=col[ok], weights=wgt[ok], grad_h=gh[ok],
@@ -269,9 +273,10 @@ class Sequence:
         self.set_ref(f)
         t = self.tick("KF K2 setCoarseTrackingRef", t)
         newp = self.new_immature(f, WINDOW - 1)
+        t_pool = time.perf_counter()
         self.pool = {k: np.concatenate([self.pool[k], newp[k]]) for k in newp}
         self.upload_pool()
-        t = self.tick("KF A2 makeMaps + K6 create", t)
+        self.phase["KF pool bookkeeping"] = self.phase.get("KF pool bookkeeping", 0.0) + (time.perf_counter() - t_pool)
         self.kf_log.append(dict(frame=f, trace_counts=counts.tolist(), activated=n_ok, candidates=int(len(cand)), e0=float(e0),
                                 e_final=float(st[0]), n_in=int(st[2]), pool=int(len(self.pool["host"])),
                                 residuals=int(len(W["target"])), new_immature=int(len(newp["host"]))))
@@ -315,6 +320,25 @@ def run_sequence_timed(seq, steps, warmup, use_dev, flush=None, torch=None):
         i += 1
     io1 = seq.ctx.io_bytes()
     return times, seq.ctx.launch_count() - l0, io1[0] - io0[0], io1[1] - io0[1]
+
+
+def rank_seed(rank):
+    """sequence s goes to GPU s mod G; one sequence per rank here"""
+    return 1001 + rank
+
+
+def max_over_ranks(vals, world, dist, torch, device):
+    """the timed region of a multi-rank run is the slowest rank's (no data-path collective: this is the only exchange)"""
+    if world <= 1:
+        return list(vals)
+    tt = torch.tensor(list(vals), dtype=torch.float64, device=device)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    return tt.tolist()
+
+
+def aggregate_fps(world, steps, t_max):
+    """whole-job throughput: every rank processed `steps` frames of its own sequence in at most t_max seconds"""
+    return world * steps / t_max
 
 
 def cpu_run(steps, warmup, seed, fast=True):
@@ -372,8 +396,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     gpu = capi.load()
-    seq = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
-    seq_e2e = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
+    seq = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+    seq_e2e = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def flush():
@@ -392,14 +416,10 @@ def main():
         barrier()
         times_e2e, _, h2d, d2h = run_sequence_timed(seq_e2e, steps, warmup, use_dev=False, flush=flush)
         barrier()
-    t_dev, t_e2e = sum(times), sum(times_e2e)
-    if world > 1:
-        tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_dev, t_e2e = tt.tolist()
+    t_dev, t_e2e = max_over_ranks([sum(times), sum(times_e2e)], world, dist, torch, "cuda")
 
     # roofline pass: the same steps again with CUDA events around every launch of the main kernels
-    seq_p = Sequence(gpu, 1001 + rank, warmup + steps, device=local_rank)
+    seq_p = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
     seq_p.prime()
     seq_p.ctx.sync()
     seq_p.ctx.profile_enable(True)
@@ -423,8 +443,8 @@ def main():
         kernels[name] = {"launches": int(n), "total_ms": ms, "avg_us": 1e3 * ms / n, "units_per_launch": units / n, "unit": unit,
                          "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
-    line = dict(base, value=world * steps / t_dev, ms_per_step=1e3 * t_dev / steps,
-                e2e={"value": world * steps / t_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
+    line = dict(base, value=aggregate_fps(world, steps, t_dev), ms_per_step=1e3 * t_dev / steps,
+                e2e={"value": aggregate_fps(world, steps, t_e2e), "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
                      "d2h_bytes_per_step": d2h / steps},
                 gpu_launches=int(launches),
                 clocks=clk.summary(),

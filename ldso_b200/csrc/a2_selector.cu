@@ -86,100 +86,144 @@ __device__ __forceinline__ bool slot_origin(const SelGeom& g, int b, int& x, int
     return x < g.w && y < g.h;
 }
 
+// lpb (1, 8 or 32) consecutive lanes share one pot-block: each lane keeps the first strict maximum of the pixels it
+// scans (q = lane, lane + lpb, ... in the reference's y1-major order), then a (value, scan position) arg-max per
+// direction across the group restores the reference's first-occurrence winner.
 __global__ void a2_cand0_kernel(const SelGeom g, const float4* __restrict__ l0, const float* __restrict__ thsS,
-                                unsigned short* __restrict__ mask, int* __restrict__ cand, int nslots) {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= nslots) return;
-    int x0, y0;
-    unsigned m = 0;
+                                unsigned short* __restrict__ mask, int* __restrict__ cand, int nslots, int lpb) {
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = gid / lpb, sub = gid % lpb;
+    int x0 = 0, y0 = 0;
     float best[16];
-    int bidx[16];
+    int bidx[16], bq[16];
 #pragma unroll
-    for (int d = 0; d < 16; d++) { best[d] = 0.f; bidx[d] = -1; }
-    if (slot_origin(g, b, x0, y0)) {
-        int my1 = min(g.pot, g.h - y0), mx1 = min(g.pot, g.w - x0);
-        for (int y1 = 0; y1 < my1; y1++)
-            for (int x1 = 0; x1 < mx1; x1++) {
-                int xf = x0 + x1, yf = y0 + y1;
-                if (xf < 4 || xf >= g.w - 5 || yf < 4 || yf > g.h - 4) continue;
-                int idx = xf + g.w * yf;
-                float4 t = __ldg(l0 + idx);
-                float th0 = thsS[(xf >> 5) + (yf >> 5) * g.thsStep];
-                if (t.w > th0 * g.thFactor) {
+    for (int d = 0; d < 16; d++) { best[d] = 0.f; bidx[d] = -1; bq[d] = 0; }
+    const bool live = b < nslots && slot_origin(g, b, x0, y0);
+    if (live) {
+        const int pp = g.pot * g.pot;
+        for (int q = sub; q < pp; q += lpb) {
+            const int y1 = q / g.pot, x1 = q - y1 * g.pot;
+            const int xf = x0 + x1, yf = y0 + y1;
+            if (xf >= g.w || yf >= g.h) continue;
+            if (xf < 4 || xf >= g.w - 5 || yf < 4 || yf > g.h - 4) continue;
+            const int idx = xf + g.w * yf;
+            const float4 t = __ldg(l0 + idx);
+            const float th0 = thsS[(xf >> 5) + (yf >> 5) * g.thsStep];
+            if (t.w > th0 * g.thFactor) {
 #pragma unroll
-                    for (int d = 0; d < 16; d++) {
-                        float dn = g.dirDist ? fabsf(t.y * c_dirs[d][0] + t.z * c_dirs[d][1]) : t.w;
-                        if (dn > best[d]) { best[d] = dn; bidx[d] = idx; }
-                    }
+                for (int d = 0; d < 16; d++) {
+                    const float dn = g.dirDist ? fabsf(t.y * c_dirs[d][0] + t.z * c_dirs[d][1]) : t.w;
+                    if (dn > best[d]) { best[d] = dn; bidx[d] = idx; bq[d] = q; }
                 }
             }
+        }
+    }
+    for (int o = lpb >> 1; o > 0; o >>= 1) {
+#pragma unroll
+        for (int d = 0; d < 16; d++) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best[d], o);
+            const int oq = __shfl_xor_sync(0xffffffffu, bq[d], o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bidx[d], o);
+            if (oi >= 0 && (bidx[d] < 0 || ov > best[d] || (ov == best[d] && oq < bq[d]))) { best[d] = ov; bq[d] = oq; bidx[d] = oi; }
+        }
+    }
+    if (b >= nslots) return;
+    if (sub == 0) {
+        unsigned m = 0;
 #pragma unroll
         for (int d = 0; d < 16; d++) m |= (bidx[d] > 0 ? 1u : 0u) << d;
+        mask[b] = (unsigned short)m;
     }
-    mask[b] = (unsigned short)m;
+    // the 16 winners of the block, spread over the group's lanes
+    for (int d = sub; d < 16; d += lpb) {
+        int v = -1;
 #pragma unroll
-    for (int d = 0; d < 16; d++) cand[(size_t)b * 16 + d] = bidx[d];
+        for (int e = 0; e < 16; e++) if (e == d) v = bidx[e];
+        cand[(size_t)b * 16 + d] = v;
+    }
 }
 
-__global__ void a2_final_kernel(const SelGeom g, const float4* __restrict__ l0, const float4* __restrict__ l1,
-                                const float4* __restrict__ l2, const float* __restrict__ thsS,
-                                const unsigned short* __restrict__ mask, const int* __restrict__ cand,
-                                const unsigned char* __restrict__ dsel, float* __restrict__ map, int* __restrict__ counts) {
-    int i4 = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i4 >= g.n4x * g.n4y) return;
-    const int b4 = i4 << 4;
-    const float d4x = c_dirs[dsel[b4]][0], d4y = c_dirs[dsel[b4]][1];
-    int bestIdx4 = -1;
-    float bestVal4 = 0.f;
-    bool dead4 = false;
-    int n3 = 0;
-    for (int s3 = 0; s3 < 4; s3++) {
-        const int b3 = b4 + (s3 << 2);
-        int xa, ya;
-        if (!slot_origin(g, b3, xa, ya)) continue;
-        bool hit0 = false;
-        for (int s2 = 0; s2 < 4; s2++) {
-            const int b = b3 + s2;
-            const int d = dsel[b];
-            if ((mask[b] >> d) & 1) {
-                map[cand[(size_t)b * 16 + d]] = 1.f;
-                hit0 = true;
-            }
-        }
-        if (hit0) { dead4 = true; continue; }
-        const float d3x = c_dirs[dsel[b3]][0], d3y = c_dirs[dsel[b3]][1];
-        int bestIdx3 = -1;
-        float bestVal3 = 0.f;
-        for (int s2 = 0; s2 < 4; s2++) {
-            int x0, y0;
-            if (!slot_origin(g, b3 + s2, x0, y0)) continue;
-            int my1 = min(g.pot, g.h - y0), mx1 = min(g.pot, g.w - x0);
-            for (int y1 = 0; y1 < my1; y1++)
-                for (int x1 = 0; x1 < mx1; x1++) {
-                    int xf = x0 + x1, yf = y0 + y1;
-                    if (xf < 4 || xf >= g.w - 5 || yf < 4 || yf > g.h - 4) continue;
-                    int idx = xf + g.w * yf;
-                    float th0 = thsS[(xf >> 5) + (yf >> 5) * g.thsStep];
-                    float th1 = th0 * g.dw1;
-                    float th2 = th1 * g.dw2;
-                    float4 t = __ldg(l0 + idx);
-                    float ag1 = l1[(int)(xf * 0.5f + 0.25f) + (int)(yf * 0.5f + 0.25f) * g.w1].w;
-                    if (ag1 > th1 * g.thFactor) {
-                        float dn = g.dirDist ? fabsf(t.y * d3x + t.z * d3y) : ag1;
-                        if (dn > bestVal3) { bestVal3 = dn; bestIdx3 = idx; dead4 = true; }
-                    }
-                    if (dead4) continue;
-                    float ag2 = l2[(int)((double)(xf * 0.25f) + 0.125) + (int)((double)(yf * 0.25f) + 0.125) * g.w2].w;
-                    if (ag2 > th2 * g.thFactor) {
-                        float dn = g.dirDist ? fabsf(t.y * d4x + t.z * d4y) : ag2;
-                        if (dn > bestVal4) { bestVal4 = dn; bestIdx4 = idx; }
-                    }
-                }
-        }
-        if (bestIdx3 > 0) { map[bestIdx3] = 2.f; n3++; }
+// first-occurrence arg-max across the warp: larger value wins, ties go to the earlier scan position
+__device__ __forceinline__ void warp_argmax(float& v, int& q, int& idx) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        const int oq = __shfl_xor_sync(0xffffffffu, q, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (oi >= 0 && (idx < 0 || ov > v || (ov == v && oq < q))) { v = ov; q = oq; idx = oi; }
     }
-    if (n3) atomicAdd(counts + 1, n3);
-    if (!dead4 && bestIdx4 > 0) { map[bestIdx4] = 4.f; atomicAdd(counts + 2, 1); }
+}
+
+// One CTA per 4pot-block, one warp per 2pot-block.  The reference scans the pixels of a 2pot-block in order and keeps
+// the first strict maximum; its level-2 candidates only matter when the whole 4pot-block produced neither a level-0
+// nor a level-1 pick (dead4), so the scan parallelises as per-lane strict maxima + a (value, scan position) arg-max.
+__global__ void __launch_bounds__(128)
+a2_final_kernel(const SelGeom g, const float4* __restrict__ l0, const float4* __restrict__ l1, const float4* __restrict__ l2,
+                const float* __restrict__ thsS, const unsigned short* __restrict__ mask, const int* __restrict__ cand,
+                const unsigned char* __restrict__ dsel, float* __restrict__ map, int* __restrict__ counts) {
+    __shared__ int s_dead[4], s_i4[4];
+    __shared__ float s_v4[4];
+    const int i4 = blockIdx.x, b4 = i4 << 4, s3 = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b3 = b4 + (s3 << 2);
+    int xa, ya;
+    const bool valid3 = slot_origin(g, b3, xa, ya);
+    int i3 = -1, q3 = 0, i4b = -1, q4 = 0;
+    float v3 = 0.f, v4 = 0.f;
+    bool hit0 = false;
+    if (valid3) {
+        bool hme = false;
+        if (lane < 4) {
+            const int b = b3 + lane, d = dsel[b];
+            if ((mask[b] >> d) & 1) { map[cand[(size_t)b * 16 + d]] = 1.f; hme = true; }
+        }
+        hit0 = __any_sync(0xffffffffu, hme);
+        if (!hit0) {
+            const float d3x = c_dirs[dsel[b3]][0], d3y = c_dirs[dsel[b3]][1];
+            const float d4x = c_dirs[dsel[b4]][0], d4y = c_dirs[dsel[b4]][1];
+            const int pp = g.pot * g.pot;
+            for (int q = lane; q < 4 * pp; q += 32) {
+                const int s2 = q / pp, r = q - s2 * pp, y1 = r / g.pot, x1 = r - y1 * g.pot;
+                int x0, y0;
+                if (!slot_origin(g, b3 + s2, x0, y0)) continue;
+                const int xf = x0 + x1, yf = y0 + y1;
+                if (xf >= g.w || yf >= g.h) continue;
+                if (xf < 4 || xf >= g.w - 5 || yf < 4 || yf > g.h - 4) continue;
+                const int idx = xf + g.w * yf;
+                const float th0 = thsS[(xf >> 5) + (yf >> 5) * g.thsStep];
+                const float th1 = th0 * g.dw1;
+                const float th2 = th1 * g.dw2;
+                const float4 t = __ldg(l0 + idx);
+                const float ag1 = l1[(int)(xf * 0.5f + 0.25f) + (int)(yf * 0.5f + 0.25f) * g.w1].w;
+                if (ag1 > th1 * g.thFactor) {
+                    const float dn = g.dirDist ? fabsf(t.y * d3x + t.z * d3y) : ag1;
+                    if (dn > v3) { v3 = dn; i3 = idx; q3 = q; }
+                }
+                const float ag2 = l2[(int)((double)(xf * 0.25f) + 0.125) + (int)((double)(yf * 0.25f) + 0.125) * g.w2].w;
+                if (ag2 > th2 * g.thFactor) {
+                    const float dn = g.dirDist ? fabsf(t.y * d4x + t.z * d4y) : ag2;
+                    if (dn > v4) { v4 = dn; i4b = idx; q4 = q; }
+                }
+            }
+            warp_argmax(v3, q3, i3);
+            warp_argmax(v4, q4, i4b);
+        }
+    }
+    if (lane == 0) {
+        const bool has3 = i3 > 0;
+        if (has3) { map[i3] = 2.f; atomicAdd(counts + 1, 1); }
+        s_dead[s3] = (hit0 || has3) ? 1 : 0;
+        s_v4[s3] = v4; s_i4[s3] = i4b;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (!(s_dead[0] | s_dead[1] | s_dead[2] | s_dead[3])) {
+            float bv = 0.f;
+            int bi = -1;
+            for (int k = 0; k < 4; k++)
+                if (s_i4[k] >= 0 && s_v4[k] > bv) { bv = s_v4[k]; bi = s_i4[k]; }
+            if (bi > 0) { map[bi] = 4.f; atomicAdd(counts + 2, 1); }
+        }
+    }
 }
 
 // ---- thinning: row-major rank of every selected pixel ---------------------------------------------
@@ -315,7 +359,8 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     LDSO_CUDA_OK(c, cudaMemsetAsync(S->map, 0, sizeof(float) * (size_t)g.w * g.h, s));
     LDSO_CUDA_OK(c, cudaMemsetAsync(S->counts, 0, 8 * sizeof(int), s));
     prof_begin(c, s);
-    a2_cand0_kernel<<<(nslots + 127) / 128, 128, 0, s>>>(g, l0, S->thsS, S->mask, S->cand, nslots);
+    const int lpb = pot * pot >= 64 ? 32 : pot * pot >= 16 ? 8 : 1;
+    a2_cand0_kernel<<<(int)(((size_t)nslots * lpb + 127) / 128), 128, 0, s>>>(g, l0, S->thsS, S->mask, S->cand, nslots, lpb);
     prof_end(c, s, LDSO_PROF_A2, (double)g.w * g.h);
     LDSO_CUDA_OK(c, ldso_copy(c, S->mask_pinned, S->mask, (size_t)nslots * sizeof(unsigned short), cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
@@ -330,7 +375,7 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     LDSO_CUDA_OK(c, ldso_copy(c, S->dsel, S->dsel_pinned, nslots, cudaMemcpyHostToDevice, s));
     const int n4blocks = g.n4x * g.n4y;
     prof_begin(c, s);
-    a2_final_kernel<<<(n4blocks + 63) / 64, 64, 0, s>>>(g, l0, l1, l2, S->thsS, S->mask, S->cand, S->dsel, S->map, S->counts);
+    a2_final_kernel<<<n4blocks, 128, 0, s>>>(g, l0, l1, l2, S->thsS, S->mask, S->cand, S->dsel, S->map, S->counts);
     prof_end(c, s, LDSO_PROF_A2, 0);
     c->launches += 2;
     LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
