@@ -396,8 +396,6 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     gpu = capi.load()
-    seq = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
-    seq_e2e = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def flush():
@@ -409,16 +407,24 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    seq.prime(); seq_e2e.prime()
+    # three passes over the same sequence, one context alive at a time: device-resident input (value), host input
+    # through the C ABI (e2e), and the per-kernel CUDA-event profile (roofline)
     with ClockSampler(local_rank) as clk:
+        seq = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+        seq.prime()
         barrier()
         times, launches, _, _ = run_sequence_timed(seq, steps, warmup, use_dev=True, flush=flush, torch=torch)
         barrier()
+        gt_err, kf_tail = seq.gt_error(), seq.kf_log[-2:]
+        seq.ctx.close()
+        seq_e2e = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+        seq_e2e.prime()
+        barrier()
         times_e2e, _, h2d, d2h = run_sequence_timed(seq_e2e, steps, warmup, use_dev=False, flush=flush)
         barrier()
+        seq_e2e.ctx.close()
     t_dev, t_e2e = max_over_ranks([sum(times), sum(times_e2e)], world, dist, torch, "cuda")
 
-    # roofline pass: the same steps again with CUDA events around every launch of the main kernels
     seq_p = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
     seq_p.prime()
     seq_p.ctx.sync()
@@ -456,7 +462,7 @@ def main():
                                   "(L2-resident working set), see DESIGN.md section 4"},
                 kernels=kernels,
                 host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
-                gt_max_translation_error_m=seq.gt_error(), keyframes=seq.kf_log[-2:])
+                gt_max_translation_error_m=gt_err, keyframes=kf_tail)
     if args.gpus == 1:
         cseq, ctimes = cpu_run(min(args.cpu_steps, steps), KF_EVERY, 1001)
         n = len(ctimes)
