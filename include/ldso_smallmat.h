@@ -16,24 +16,30 @@
 #include <vector>
 #include <algorithm>
 
+#ifdef __CUDACC__
+#define LDSO_HD __host__ __device__
+#else
+#define LDSO_HD
+#endif
+
 namespace ldso_sm {
 
 // ---------------------------------------------------------------------------------------------
 // 3x3 helpers (row-major)
-template <class T> inline void mat3_mul(const T* A, const T* B, T* C) {
+template <class T> LDSO_HD inline void mat3_mul(const T* A, const T* B, T* C) {
     T r[9];
     for (int i = 0; i < 3; i++)
         for (int j = 0; j < 3; j++) r[i * 3 + j] = A[i * 3 + 0] * B[0 * 3 + j] + A[i * 3 + 1] * B[1 * 3 + j] + A[i * 3 + 2] * B[2 * 3 + j];
     for (int i = 0; i < 9; i++) C[i] = r[i];
 }
-template <class T> inline void mat3_vec(const T* A, const T* v, T* o) {
+template <class T> LDSO_HD inline void mat3_vec(const T* A, const T* v, T* o) {
     T r0 = A[0] * v[0] + A[1] * v[1] + A[2] * v[2];
     T r1 = A[3] * v[0] + A[4] * v[1] + A[5] * v[2];
     T r2 = A[6] * v[0] + A[7] * v[1] + A[8] * v[2];
     o[0] = r0; o[1] = r1; o[2] = r2;
 }
 // cofactor inverse (what Eigen's fixed-size 3x3 inverse() does), any scalar type
-template <class T> inline void mat3_inv(const T* m, T* o) {
+template <class T> LDSO_HD inline void mat3_inv(const T* m, T* o) {
     T c00 = m[4] * m[8] - m[5] * m[7];
     T c10 = m[5] * m[6] - m[3] * m[8];
     T c20 = m[3] * m[7] - m[4] * m[6];
@@ -51,7 +57,7 @@ template <class T> inline void mat3_inv(const T* m, T* o) {
     r[8] = (m[0] * m[4] - m[1] * m[3]) * id;
     for (int i = 0; i < 9; i++) o[i] = r[i];
 }
-inline void hat(const double* w, double* O) {
+LDSO_HD inline void hat(const double* w, double* O) {
     O[0] = 0; O[1] = -w[2]; O[2] = w[1];
     O[3] = w[2]; O[4] = 0; O[5] = -w[0];
     O[6] = -w[1]; O[7] = w[0]; O[8] = 0;
@@ -64,7 +70,7 @@ struct SE3 {
     double t[3] = {0, 0, 0};
 
     // Eigen::Quaternion::toRotationMatrix
-    void rotationMatrix(double* R) const {
+    LDSO_HD void rotationMatrix(double* R) const {
         const double tx = 2 * qx, ty = 2 * qy, tz = 2 * qz;
         const double twx = tx * qw, twy = ty * qw, twz = tz * qw;
         const double txx = tx * qx, txy = ty * qx, txz = tz * qx;
@@ -74,18 +80,18 @@ struct SE3 {
         R[6] = txz - twy;       R[7] = tyz + twx;       R[8] = 1 - (txx + tyy);
     }
     // q * p * q^-1 (so3.hpp:354-363)
-    void rotate(const double* p, double* o) const {
+    LDSO_HD void rotate(const double* p, double* o) const {
         double uv[3] = {qy * p[2] - qz * p[1], qz * p[0] - qx * p[2], qx * p[1] - qy * p[0]};
         uv[0] += uv[0]; uv[1] += uv[1]; uv[2] += uv[2];
         double c[3] = {qy * uv[2] - qz * uv[1], qz * uv[0] - qx * uv[2], qx * uv[1] - qy * uv[0]};
         double r0 = p[0] + qw * uv[0] + c[0], r1 = p[1] + qw * uv[1] + c[1], r2 = p[2] + qw * uv[2] + c[2];
         o[0] = r0; o[1] = r1; o[2] = r2;
     }
-    void normalize() {
+    LDSO_HD void normalize() {
         double n = std::sqrt(qw * qw + qx * qx + qy * qy + qz * qz);
         qw /= n; qx /= n; qy /= n; qz /= n;
     }
-    SE3 operator*(const SE3& b) const {   // so3.hpp:321-335, se3.hpp:270-281
+    LDSO_HD SE3 operator*(const SE3& b) const {   // so3.hpp:321-335, se3.hpp:270-281
         SE3 r;
         r.qw = qw * b.qw - qx * b.qx - qy * b.qy - qz * b.qz;
         r.qx = qw * b.qx + qx * b.qw + qy * b.qz - qz * b.qy;
@@ -99,7 +105,7 @@ struct SE3 {
         if (std::fabs(n2 - 1.0) > 1e-15) { double n = std::sqrt(n2); r.qw /= n; r.qx /= n; r.qy /= n; r.qz /= n; }
         return r;
     }
-    SE3 inverse() const {
+    LDSO_HD SE3 inverse() const {
         SE3 r;
         r.qw = qw; r.qx = -qx; r.qy = -qy; r.qz = -qz;
         double rt[3];
@@ -107,7 +113,7 @@ struct SE3 {
         r.t[0] = -rt[0]; r.t[1] = -rt[1]; r.t[2] = -rt[2];
         return r;
     }
-    static SE3 exp(const double* a) {   // a = [upsilon(3), omega(3)]
+    LDSO_HD static SE3 exp(const double* a) {   // a = [upsilon(3), omega(3)]
         const double* om = a + 3;
         double th2 = om[0] * om[0] + om[1] * om[1] + om[2] * om[2];
         double th = std::sqrt(th2), half = 0.5 * th, imag, real;
@@ -174,8 +180,8 @@ struct SE3 {
             }
     }
     // [R(9 row-major) | t(3)] exchange format used across the C ABI
-    void toRt(double* Rt) const { rotationMatrix(Rt); Rt[9] = t[0]; Rt[10] = t[1]; Rt[11] = t[2]; }
-    static SE3 fromRt(const double* Rt) {   // Eigen::Quaternion(Matrix3) (Shepperd)
+    LDSO_HD void toRt(double* Rt) const { rotationMatrix(Rt); Rt[9] = t[0]; Rt[10] = t[1]; Rt[11] = t[2]; }
+    LDSO_HD static SE3 fromRt(const double* Rt) {   // Eigen::Quaternion(Matrix3) (Shepperd)
         SE3 r;
         const double* m = Rt;
         double tr = m[0] + m[4] + m[8];

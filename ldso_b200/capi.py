@@ -33,7 +33,8 @@ class Config(C.Structure):
         ("frame_energy_th_n", C.c_float), ("frame_energy_th_fac_median", C.c_float),
         ("frame_energy_th_const_weight", C.c_float),
         ("tracker_solve_mode", C.c_int),
-        ("reserved", C.c_int * 8),
+        ("tracker_lm_mode", C.c_int),
+        ("reserved", C.c_int * 7),
     ]
 
 

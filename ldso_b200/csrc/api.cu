@@ -214,6 +214,11 @@ extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms
     LDSO_REQUIRE(c, which >= 0 && which < LDSO_PROF_SLOTS);
     prof_drain(c);
     *total_ms = c->prof_ms[which]; *launches = c->prof_launches[which]; *units = c->prof_units[which];
+    if (c->cfg.reserved[0] == 3 && which == LDSO_PROF_K34) {
+        fprintf(stderr, "lm phase clocks: eval %.0f barrier %.0f fold %.0f decide %.0f solve %.0f candidate %.0f\n", c->lm_dbg_clocks[0],
+                c->lm_dbg_clocks[1], c->lm_dbg_clocks[2], c->lm_dbg_clocks[3], c->lm_dbg_clocks[4], c->lm_dbg_clocks[5]);
+        for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] = 0;
+    }
     return 0;
 }
 
@@ -424,53 +429,61 @@ extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot
     bool repeated = false;
     int nEval = 0, nAccept = 0, rc;
     TrackEvalOut ev;
+    const bool device_lm = c->cfg.tracker_lm_mode == 0;
     for (int lvl = coarsest_lvl; lvl >= 0; lvl--) {
         double H[64], b[8], resOld[6], resNew[6];
         float cutoffRepeat = 1;
-        if ((rc = k34_eval(c, tracker, lvl, cur, cur_a, cur_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
-        nEval++;
-        fill_vec6(ev, resOld);
-        while (resOld[5] > 0.6 && cutoffRepeat < 50) {
-            cutoffRepeat *= 2;
+        if (device_lm) {
+            // the whole LM loop of this level runs inside one cooperative kernel
+            int ne = 0, na = 0;
+            if ((rc = k34_track_level(c, tracker, lvl, cur, cur_a, cur_b, maxIterations[lvl], resOld, &cutoffRepeat, &ne, &na))) return rc;
+            nEval += ne; nAccept += na;
+        } else {
             if ((rc = k34_eval(c, tracker, lvl, cur, cur_a, cur_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
             nEval++;
             fill_vec6(ev, resOld);
-        }
-        fill_Hb(ev, H, b);
-        float lambda = 0.01f;
-        for (int it = 0; it < maxIterations[lvl]; it++) {
-            double inc[8], incS[8];
-            solve_step(H, b, lambda, c->cfg.tracker_solve_mode, optA, optB, inc);
-            float extrap = 1;
-            if (lambda < extrapLimit) extrap = sqrtf(sqrt(extrapLimit / lambda));
-            double sq = 0;
-            for (int i = 0; i < 8; i++) {
-                inc[i] *= extrap;
-                incS[i] = inc[i] * (i < 3 ? LDSO_SCALE_XI_TRANS : i < 6 ? LDSO_SCALE_XI_ROT : i == 6 ? LDSO_SCALE_A : LDSO_SCALE_B);
-                sq += incS[i] * incS[i];
+            while (resOld[5] > 0.6 && cutoffRepeat < 50) {
+                cutoffRepeat *= 2;
+                if ((rc = k34_eval(c, tracker, lvl, cur, cur_a, cur_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
+                nEval++;
+                fill_vec6(ev, resOld);
             }
-            if (!std::isfinite(sq))
-                for (int i = 0; i < 8; i++) inc[i] = incS[i] = 0;
-            SE3 cand = SE3::exp(incS) * cur;
-            float cand_a = cur_a, cand_b = cur_b;
-            cand_a += incS[6];
-            cand_b += incS[7];
-            if ((rc = k34_eval(c, tracker, lvl, cand, cand_a, cand_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
-            nEval++;
-            fill_vec6(ev, resNew);
-            if ((resNew[0] / resNew[1]) < (resOld[0] / resOld[1])) {
-                fill_Hb(ev, H, b);   // the fused launch already accumulated the system at the accepted pose
-                memcpy(resOld, resNew, sizeof(resOld));
-                cur = cand; cur_a = cand_a; cur_b = cand_b;
-                lambda *= 0.5;
-                nAccept++;
-            } else {
-                lambda *= 4.0;
-                if (lambda < extrapLimit) lambda = extrapLimit;
+            fill_Hb(ev, H, b);
+            float lambda = 0.01f;
+            for (int it = 0; it < maxIterations[lvl]; it++) {
+                double inc[8], incS[8];
+                solve_step(H, b, lambda, c->cfg.tracker_solve_mode, optA, optB, inc);
+                float extrap = 1;
+                if (lambda < extrapLimit) extrap = sqrtf(sqrt(extrapLimit / lambda));
+                double sq = 0;
+                for (int i = 0; i < 8; i++) {
+                    inc[i] *= extrap;
+                    incS[i] = inc[i] * (i < 3 ? LDSO_SCALE_XI_TRANS : i < 6 ? LDSO_SCALE_XI_ROT : i == 6 ? LDSO_SCALE_A : LDSO_SCALE_B);
+                    sq += incS[i] * incS[i];
+                }
+                if (!std::isfinite(sq))
+                    for (int i = 0; i < 8; i++) inc[i] = incS[i] = 0;
+                SE3 cand = SE3::exp(incS) * cur;
+                float cand_a = cur_a, cand_b = cur_b;
+                cand_a += incS[6];
+                cand_b += incS[7];
+                if ((rc = k34_eval(c, tracker, lvl, cand, cand_a, cand_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
+                nEval++;
+                fill_vec6(ev, resNew);
+                if ((resNew[0] / resNew[1]) < (resOld[0] / resOld[1])) {
+                    fill_Hb(ev, H, b);   // the fused launch already accumulated the system at the accepted pose
+                    memcpy(resOld, resNew, sizeof(resOld));
+                    cur = cand; cur_a = cand_a; cur_b = cand_b;
+                    lambda *= 0.5;
+                    nAccept++;
+                } else {
+                    lambda *= 4.0;
+                    if (lambda < extrapLimit) lambda = extrapLimit;
+                }
+                double nrm = 0;
+                for (int i = 0; i < 8; i++) nrm += inc[i] * inc[i];
+                if (!(std::sqrt(nrm) > 1e-3)) break;
             }
-            double nrm = 0;
-            for (int i = 0; i < 8; i++) nrm += inc[i] * inc[i];
-            if (!(std::sqrt(nrm) > 1e-3)) break;
         }
         last_residuals[lvl] = sqrtf((float)(resOld[0] / resOld[1]));
         flow[0] = (float)resOld[2]; flow[1] = (float)resOld[3]; flow[2] = (float)resOld[4];

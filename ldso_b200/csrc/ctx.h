@@ -88,6 +88,8 @@ struct ldso_gpu_ctx {
     double* trk_mailbox = nullptr;          // [64] mapped pinned: the fused tracker kernel writes its sums + a sequence number here
     double* trk_mailbox_dev = nullptr;      // device alias of trk_mailbox
     unsigned long long trk_seq = 0;
+    double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
+    int trk_coop_max = 0;                   // co-resident CTA budget of the device-resident LM kernel
     WindowDev win;
     void* selector = nullptr;               // SelectorDev (a2_selector.cu), created on first use
     void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use
@@ -132,5 +134,7 @@ struct TrackEvalOut {
     double sums[48];   // 45 H entries (9x9 upper, row-major), E, flowT, flowRT
     int counts[4];     // numTermsInE, numSaturated, numTermsInWarped, flowNum
 };
+int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, float& aff_a, float& aff_b, int maxIt,
+                    double resOld[6], float* cutoffRepeat, int* nEval, int* nAccept);
 int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew, float aff_a, float aff_b, float cutoffTH,
              TrackEvalOut* out);

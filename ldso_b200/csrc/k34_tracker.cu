@@ -10,7 +10,9 @@
 // The warped buffers never exist.  Algorithmic traffic: 16 B point + 4x16 B texels per point.
 #include "ctx.h"
 
+#include <algorithm>
 #include <atomic>
+#include <cooperative_groups.h>
 #include <immintrin.h>
 
 namespace {
@@ -43,6 +45,71 @@ __device__ __forceinline__ float4 lerp_texel(const float4* __restrict__ img, flo
     return r;
 }
 
+// one tracker point: calcRes (CoarseTracker.cc:566-661) + the calcGSSSE products (:692-723), added into acc / counters
+__device__ __forceinline__ void eval_point(const TrkParams& p, const float4 q, const int i, const float4* __restrict__ newImg,
+                                           float (&acc)[NF], int& cE, int& cSat, int& cWarp, int& cFlow) {
+    const float x = q.x, y = q.y, id = q.z, refColor = q.w;
+    // r = RKi*(x,y,1); pt = r + t*id — same association as the reference's Eigen expression, and the
+    // library is compiled with -fmad=false, so every per-point value below is bit-identical to a
+    // strict-IEEE evaluation of CoarseTracker.cc:575-585 (threshold tests cannot flip on FMA rounding).
+    const float r0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2];
+    const float r1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5];
+    const float r2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8];
+    float pt0 = r0 + p.t[0] * id, pt1 = r1 + p.t[1] * id, pt2 = r2 + p.t[2] * id;
+    float u = pt0 / pt2, v = pt1 / pt2;
+    float Ku = p.fx * u + p.cx, Kv = p.fy * v + p.cy;
+    float new_idepth = id / pt2;
+
+    if (p.lvl == 0 && (i & 31) == 0) {   // CoarseTracker.cc:587-617
+        float k0 = p.Ki[0] * x + p.Ki[1] * y + p.Ki[2], k1 = p.Ki[3] * x + p.Ki[4] * y + p.Ki[5],
+              k2 = p.Ki[6] * x + p.Ki[7] * y + p.Ki[8];
+        float zT = k2 + p.t[2] * id, zT2 = k2 - p.t[2] * id;
+        float KuT = p.fx * ((k0 + p.t[0] * id) / zT) + p.cx, KvT = p.fy * ((k1 + p.t[1] * id) / zT) + p.cy;
+        float KuT2 = p.fx * ((k0 - p.t[0] * id) / zT2) + p.cx, KvT2 = p.fy * ((k1 - p.t[1] * id) / zT2) + p.cy;
+        float z3 = r2 - p.t[2] * id;
+        float Ku3 = p.fx * ((r0 - p.t[0] * id) / z3) + p.cx, Kv3 = p.fy * ((r1 - p.t[1] * id) / z3) + p.cy;
+        acc[46] += ((KuT - x) * (KuT - x) + (KvT - y) * (KvT - y)) + ((KuT2 - x) * (KuT2 - x) + (KvT2 - y) * (KvT2 - y));
+        acc[47] += ((Ku - x) * (Ku - x) + (Kv - y) * (Kv - y)) + ((Ku3 - x) * (Ku3 - x) + (Kv3 - y) * (Kv3 - y));
+        cFlow += 2;
+    }
+
+    if (Ku > 2 && Kv > 2 && Ku < p.w - 3 && Kv < p.h - 3 && new_idepth > 0) {
+        float4 hit = lerp_texel(newImg, Ku, Kv, p.w);
+        if (isfinite(hit.x)) {
+            float residual = hit.x - (p.aff0 * refColor + p.aff1);
+            float ar = fabsf(residual);
+            float hw = ar < p.huberTH ? 1.f : p.huberTH / ar;
+            cE += 1;
+            if (ar > p.cutoffTH) {
+                acc[45] += p.maxEnergy;
+                cSat += 1;
+            } else {
+                acc[45] += hw * residual * residual * (2 - hw);
+                cWarp += 1;
+                // calcGSSSE Jacobian (CoarseTracker.cc:692-723)
+                float dx = hit.y * p.fx, dy = hit.z * p.fy;
+                float J[9];
+                J[0] = new_idepth * dx;
+                J[1] = new_idepth * dy;
+                J[2] = -(new_idepth * (u * dx + v * dy));
+                J[3] = -(u * v * dx + dy * (1 + v * v));
+                J[4] = u * v * dy + dx * (1 + u * u);
+                J[5] = u * dy - v * dx;
+                J[6] = p.aJ * (p.b0 - refColor);
+                J[7] = -1.f;
+                J[8] = residual;
+                int k = 0;
+#pragma unroll
+                for (int r = 0; r < 9; r++) {
+                    float Jw = J[r] * hw;
+#pragma unroll
+                    for (int cidx = r; cidx < 9; cidx++) acc[k++] += Jw * J[cidx];
+                }
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(TRK_THREADS)
 k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ newImg, const TrkParams p,
                       float* __restrict__ partials, int* __restrict__ partials_i, unsigned int* __restrict__ counter,
@@ -53,69 +120,7 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
     int cE = 0, cSat = 0, cWarp = 0, cFlow = 0;
 
     const int i = blockIdx.x * TRK_THREADS + threadIdx.x;
-    if (i < p.n) {
-        const float4 q = __ldg(pc + i);
-        const float x = q.x, y = q.y, id = q.z, refColor = q.w;
-        // r = RKi*(x,y,1); pt = r + t*id — same association as the reference's Eigen expression, and the
-        // library is compiled with -fmad=false, so every per-point value below is bit-identical to a
-        // strict-IEEE evaluation of CoarseTracker.cc:575-585 (threshold tests cannot flip on FMA rounding).
-        const float r0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2];
-        const float r1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5];
-        const float r2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8];
-        float pt0 = r0 + p.t[0] * id, pt1 = r1 + p.t[1] * id, pt2 = r2 + p.t[2] * id;
-        float u = pt0 / pt2, v = pt1 / pt2;
-        float Ku = p.fx * u + p.cx, Kv = p.fy * v + p.cy;
-        float new_idepth = id / pt2;
-
-        if (p.lvl == 0 && (i & 31) == 0) {   // CoarseTracker.cc:587-617
-            float k0 = p.Ki[0] * x + p.Ki[1] * y + p.Ki[2], k1 = p.Ki[3] * x + p.Ki[4] * y + p.Ki[5],
-                  k2 = p.Ki[6] * x + p.Ki[7] * y + p.Ki[8];
-            float zT = k2 + p.t[2] * id, zT2 = k2 - p.t[2] * id;
-            float KuT = p.fx * ((k0 + p.t[0] * id) / zT) + p.cx, KvT = p.fy * ((k1 + p.t[1] * id) / zT) + p.cy;
-            float KuT2 = p.fx * ((k0 - p.t[0] * id) / zT2) + p.cx, KvT2 = p.fy * ((k1 - p.t[1] * id) / zT2) + p.cy;
-            float z3 = r2 - p.t[2] * id;
-            float Ku3 = p.fx * ((r0 - p.t[0] * id) / z3) + p.cx, Kv3 = p.fy * ((r1 - p.t[1] * id) / z3) + p.cy;
-            acc[46] = ((KuT - x) * (KuT - x) + (KvT - y) * (KvT - y)) + ((KuT2 - x) * (KuT2 - x) + (KvT2 - y) * (KvT2 - y));
-            acc[47] = ((Ku - x) * (Ku - x) + (Kv - y) * (Kv - y)) + ((Ku3 - x) * (Ku3 - x) + (Kv3 - y) * (Kv3 - y));
-            cFlow = 2;
-        }
-
-        if (Ku > 2 && Kv > 2 && Ku < p.w - 3 && Kv < p.h - 3 && new_idepth > 0) {
-            float4 hit = lerp_texel(newImg, Ku, Kv, p.w);
-            if (isfinite(hit.x)) {
-                float residual = hit.x - (p.aff0 * refColor + p.aff1);
-                float ar = fabsf(residual);
-                float hw = ar < p.huberTH ? 1.f : p.huberTH / ar;
-                cE = 1;
-                if (ar > p.cutoffTH) {
-                    acc[45] = p.maxEnergy;
-                    cSat = 1;
-                } else {
-                    acc[45] = hw * residual * residual * (2 - hw);
-                    cWarp = 1;
-                    // calcGSSSE Jacobian (CoarseTracker.cc:692-723)
-                    float dx = hit.y * p.fx, dy = hit.z * p.fy;
-                    float J[9];
-                    J[0] = new_idepth * dx;
-                    J[1] = new_idepth * dy;
-                    J[2] = -(new_idepth * (u * dx + v * dy));
-                    J[3] = -(u * v * dx + dy * (1 + v * v));
-                    J[4] = u * v * dy + dx * (1 + u * u);
-                    J[5] = u * dy - v * dx;
-                    J[6] = p.aJ * (p.b0 - refColor);
-                    J[7] = -1.f;
-                    J[8] = residual;
-                    int k = 0;
-#pragma unroll
-                    for (int r = 0; r < 9; r++) {
-                        float Jw = J[r] * hw;
-#pragma unroll
-                        for (int cidx = r; cidx < 9; cidx++) acc[k++] = Jw * J[cidx];
-                    }
-                }
-            }
-        }
-    }
+    if (i < p.n) eval_point(p, __ldg(pc + i), i, newImg, acc, cE, cSat, cWarp, cFlow);
 
     // warp reduction (fp32)
 #pragma unroll
@@ -190,6 +195,427 @@ k34_track_eval_kernel(const float4* __restrict__ pc, const float4* __restrict__ 
 
 }  // namespace
 
+// =====================================================================================================
+// Device-resident LM loop of one pyramid level (CoarseTracker::trackNewestCoarse, CoarseTracker.cc:86-249).
+// One cooperative launch runs every evaluation of the level: all CTAs evaluate the points, publish per-CTA partial
+// sums, meet at ONE grid barrier per evaluation, and then every CTA folds the partials (fp64, fixed order) and runs
+// the same scalar LM transition on its thread 0 (accept/reject, 8x8 LDLT, SE3 exponential) — identical inputs give
+// identical next parameters in every CTA, so no second barrier or broadcast is needed.  Partials are double-buffered
+// by evaluation parity.  The host sees one mailbox message per level instead of one per evaluation.
+namespace {
+
+namespace cg = cooperative_groups;
+
+// CTAs of the cooperative launch: the grid barrier and the all-CTA fold both grow with the grid, the evaluation
+// itself is a few hundred points per CTA either way
+constexpr int LM_MAX_CTAS = 32;
+
+struct LmConst {
+    float Ki[9], fx, fy, cx, cy;
+    int w, h, n, lvl, maxIt, solveMode, dbg;   // dbg (cfg.reserved[0], measurement only): 1 = fixed 12 evaluations without the LM transition, 2 = also without the fold
+    float huberTH, coarseCutoff, optA, optB;
+    float refExposure, newExposure, refAffA, refAffB;
+    double q[4], t[3];          // initial refToNew
+    float affA, affB;           // initial aff_g2l
+};
+
+struct LmState {                // plain data: lives in shared memory, only thread 0 touches it
+    double q[4], t[3];          // current accepted pose
+    double cq[4], ct[3];        // candidate pose
+    float a, b, ca, cb;
+    double H[2][64], bv[2][8], resOld[6], inc[8];   // [hsel] = system at the accepted pose, [hsel ^ 1] = latest evaluation
+    float lambda, cutoffRepeat;
+    int it, phase, nEval, nAccept, hsel;
+};
+
+__device__ inline ldso_sm::SE3 se3_of(const double* q, const double* t) {
+    ldso_sm::SE3 s;
+    s.qw = q[0]; s.qx = q[1]; s.qy = q[2]; s.qz = q[3];
+    s.t[0] = t[0]; s.t[1] = t[1]; s.t[2] = t[2];
+    return s;
+}
+
+// the per-evaluation parameters k34_eval builds on the host (CoarseTracker.cc:546-564, 681-685)
+__device__ void lm_make_params(const LmConst& k, const double* q, const double* t, float a, float b, float cutoffTH,
+                               TrkParams& p) {
+    double Rd[9];
+    se3_of(q, t).rotationMatrix(Rd);
+    float Rf[9];
+    for (int i = 0; i < 9; i++) Rf[i] = (float)Rd[i];
+    ldso_sm::mat3_mul<float>(Rf, k.Ki, p.RKi);
+    for (int i = 0; i < 3; i++) p.t[i] = (float)t[i];
+    for (int i = 0; i < 9; i++) p.Ki[i] = k.Ki[i];
+    p.fx = k.fx; p.fy = k.fy; p.cx = k.cx; p.cy = k.cy; p.w = k.w; p.h = k.h; p.n = k.n; p.lvl = k.lvl;
+    float eF = k.refExposure, eT = k.newExposure;
+    if (eF == 0 || eT == 0) eT = eF = 1;
+    const float aa = expf(a - k.refAffA) * eT / eF;   // AffLight::fromToVecExposure (include/AffLight.h:27-35)
+    p.aff0 = aa; p.aff1 = b - aa * k.refAffB;
+    p.aJ = p.aff0; p.b0 = k.refAffB;
+    p.huberTH = k.huberTH; p.cutoffTH = cutoffTH;
+    p.maxEnergy = 2 * k.huberTH * cutoffTH - k.huberTH * k.huberTH;
+}
+
+// LDLT with diagonal pivoting on the leading n x n block, same operation order as ldso_sm::ldlt_solve
+__device__ __noinline__ void lm_ldlt(int n, const double* M8, const double* rhs, double* x) {
+    double A[64];
+    int perm[8];
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j <= i; j++) A[i * n + j] = A[j * n + i] = M8[i * 8 + j];
+    for (int i = 0; i < n; i++) perm[i] = i;
+    for (int k = 0; k < n; k++) {
+        int p = k;
+        double best = fabs(A[k * n + k]);
+        for (int i = k + 1; i < n; i++)
+            if (fabs(A[i * n + i]) > best) { best = fabs(A[i * n + i]); p = i; }
+        if (p != k) {
+            for (int j = 0; j < n; j++) { double s = A[k * n + j]; A[k * n + j] = A[p * n + j]; A[p * n + j] = s; }
+            for (int j = 0; j < n; j++) { double s = A[j * n + k]; A[j * n + k] = A[j * n + p]; A[j * n + p] = s; }
+            int s = perm[k]; perm[k] = perm[p]; perm[p] = s;
+        }
+        const double d = A[k * n + k];
+        if (d == 0) continue;
+        for (int i = k + 1; i < n; i++) {
+            const double l = A[i * n + k] / d;
+            for (int j = k + 1; j <= i; j++) A[i * n + j] -= l * A[k * n + j];
+            A[i * n + k] = l;
+        }
+        for (int i = k + 1; i < n; i++)
+            for (int j = k + 1; j < i; j++) A[j * n + i] = A[i * n + j];
+    }
+    double y[8];
+    for (int i = 0; i < n; i++) y[i] = rhs[perm[i]];
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < i; j++) y[i] -= A[i * n + j] * y[j];
+    for (int i = 0; i < n; i++) {
+        const double d = A[i * n + i];
+        y[i] = (d == 0) ? 0 : y[i] / d;
+    }
+    for (int i = n - 1; i >= 0; i--)
+        for (int j = i + 1; j < n; j++) y[i] -= A[j * n + i] * y[j];
+    for (int i = 0; i < n; i++) x[perm[i]] = y[i];
+}
+
+// fixed-affine variants of solve_step (setting_affineOptModeA/B < 0): rare, kept out of line the common case is solved by lm_ldlt8_warp
+__device__ __noinline__ void lm_solve_step_fixed(const double* H, const double* b, float lambda, int mode, bool fixA, bool fixB,
+                                                 double* inc) {
+    double Hl[64], rhs[8];
+    for (int i = 0; i < 8; i++) {
+        for (int j = 0; j < 8; j++) Hl[i * 8 + j] = (mode == 1 && j < i) ? 0.0 : H[i * 8 + j];
+        Hl[i * 8 + i] *= (1 + lambda);
+        rhs[i] = -b[i];
+    }
+    if (fixA && fixB) { lm_ldlt(6, Hl, rhs, inc); inc[6] = inc[7] = 0; }
+    else if (!fixA && fixB) { lm_ldlt(7, Hl, rhs, inc); inc[7] = 0; }
+    else if (fixA && !fixB) {
+        double Hs[64], rs[8], xs[8];
+        for (int i = 0; i < 64; i++) Hs[i] = Hl[i];
+        for (int i = 0; i < 8; i++) Hs[i * 8 + 6] = Hs[i * 8 + 7];
+        for (int j = 0; j < 8; j++) Hs[6 * 8 + j] = Hs[7 * 8 + j];
+        for (int i = 0; i < 8; i++) rs[i] = -b[i];
+        rs[6] = -b[7];
+        lm_ldlt(7, Hs, rs, xs);
+        for (int i = 0; i < 6; i++) inc[i] = xs[i];
+        inc[6] = 0; inc[7] = xs[6];
+    }
+}
+
+// fill_vec6 / fill_Hb of api.cu (CoarseTracker.cc:664-672, 725-740) on the folded sums
+__device__ void lm_vec6(const double* r, double rs[6]) {
+    rs[0] = (float)r[45];
+    rs[1] = (int)r[NF + 0];
+    const float num = (float)(int)r[NF + 3];
+    rs[2] = (float)r[46] / (num + 0.1);
+    rs[3] = 0;
+    rs[4] = (float)r[47] / (num + 0.1);
+    rs[5] = (int)r[NF + 1] / (float)(int)r[NF + 0];
+}
+// entry t (0..44) of the 9x9 upper triangle, one thread each
+__device__ void lm_Hb_entry(const double* r, double* H, double* b, int t) {
+    const int n = ((int)r[NF + 2] + 3) & ~3;
+    const double invn = (double)(1.0f / n);
+    int rr = 0, rem = t;
+    while (rem >= 9 - rr) { rem -= 9 - rr; rr++; }
+    const int cc = rr + rem;
+    auto sc = [](int i) { return i < 3 ? (double)LDSO_SCALE_XI_TRANS : i < 6 ? (double)LDSO_SCALE_XI_ROT : i == 6 ? (double)LDSO_SCALE_A : (double)LDSO_SCALE_B; };
+    const double v = r[t] * invn;
+    if (rr < 8 && cc < 8) H[rr * 8 + cc] = H[cc * 8 + rr] = v * sc(rr) * sc(cc);
+    else if (rr < 8) b[rr] = v * sc(rr);
+}
+
+enum { LM_FIRST = 0, LM_ITER = 1, LM_CONT = 0, LM_DONE = 1, LM_SOLVE = 2 };
+
+// ---- the LM transition between two evaluations, split so that the heavy pieces run on many threads ------------
+// (1) lm_decide, thread 0: accept / reject, lambda, termination (CoarseTracker.cc:97-104, 213-247).  Hn/bn = the
+//     system of the evaluation that just finished, already formed by 45 threads.
+// (2) lm_ldlt8_warp, warp 0: the damped 8x8 solve.
+// (3) lm_candidate, thread 0: extrapolation, SE3 exponential, the next evaluation's parameters (:118-211).
+__device__ int lm_decide(const LmConst& k, LmState& s, const double* r, TrkParams& p) {
+    s.nEval++;
+    if (s.phase == LM_FIRST) {
+        lm_vec6(r, s.resOld);
+        if (s.resOld[5] > 0.6 && s.cutoffRepeat < 50) {
+            s.cutoffRepeat *= 2;
+            lm_make_params(k, s.q, s.t, s.a, s.b, k.coarseCutoff * s.cutoffRepeat, p);
+            return LM_CONT;
+        }
+        s.hsel ^= 1;            // take the new system
+        s.lambda = 0.01f;
+        s.it = 0;
+        s.phase = LM_ITER;
+        return s.it >= k.maxIt ? LM_DONE : LM_SOLVE;
+    }
+    double resNew[6];
+    lm_vec6(r, resNew);
+    if ((resNew[0] / resNew[1]) < (s.resOld[0] / s.resOld[1])) {
+        s.hsel ^= 1;
+        for (int i = 0; i < 6; i++) s.resOld[i] = resNew[i];
+        for (int i = 0; i < 4; i++) s.q[i] = s.cq[i];
+        for (int i = 0; i < 3; i++) s.t[i] = s.ct[i];
+        s.a = s.ca; s.b = s.cb;
+        s.lambda *= 0.5;
+        s.nAccept++;
+    } else {
+        s.lambda *= 4.0;
+        if (s.lambda < 0.001f) s.lambda = 0.001f;
+    }
+    double nrm = 0;
+    for (int i = 0; i < 8; i++) nrm += s.inc[i] * s.inc[i];
+    if (!(sqrt(nrm) > 1e-3)) return LM_DONE;
+    s.it++;
+    return s.it >= k.maxIt ? LM_DONE : LM_SOLVE;
+}
+
+// LDLT with diagonal pivoting of the damped system on one warp: lane l owns matrix elements l and l + 32 of the 8x8
+// array in shared memory.  Every element sees the same operations in the same order as in ldso_sm::ldlt_solve
+// (the lower triangle is eliminated, the upper one mirrors it), so the factor is bit-identical to the serial code.
+__device__ void lm_ldlt8_warp(const double* H, const double* bv, float lambda, int mode, double* A, double* inc, int lane) {
+    const int e0 = lane, e1 = lane + 32;
+    const int i0 = e0 >> 3, j0 = e0 & 7, i1 = e1 >> 3, j1 = e1 & 7;
+    {   // Hl = H with the diagonal times (1 + lambda) (trap T4: mode 1 drops the strict lower triangle), symmetrised from
+        // its lower triangle as Eigen's LDLT reads it
+        auto hl = [&](int i, int j) {
+            const int r = j <= i ? i : j, c = j <= i ? j : i;   // lower-triangle source (r >= c)
+            double v = (mode == 1 && c < r) ? 0.0 : H[r * 8 + c];
+            if (r == c) v *= (1 + lambda);
+            return v;
+        };
+        A[e0] = hl(i0, j0); A[e1] = hl(i1, j1);
+    }
+    int perm = lane < 8 ? lane : 0;   // lane i < 8 holds perm[i]
+    __syncwarp();
+    for (int kk = 0; kk < 8; kk++) {
+        // pivot: first index of the largest |diagonal| among rows kk..7 (lane i looks at row i)
+        double best = (lane < 8 && lane >= kk) ? fabs(A[lane * 9]) : -1.0;
+        int p = lane;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int op = __shfl_xor_sync(0xffffffffu, p, o);
+            if (ov > best || (ov == best && op < p)) { best = ov; p = op; }
+        }
+        p = __shfl_sync(0xffffffffu, p, 0);
+        if (p != kk) {   // uniform
+            auto pi = [&](int i) { return i == kk ? p : i == p ? kk : i; };
+            const double a0 = A[pi(i0) * 8 + pi(j0)], a1 = A[pi(i1) * 8 + pi(j1)];
+            const int pk = __shfl_sync(0xffffffffu, perm, kk), pp = __shfl_sync(0xffffffffu, perm, p);
+            if (lane == kk) perm = pp;
+            else if (lane == p) perm = pk;
+            __syncwarp();
+            A[e0] = a0; A[e1] = a1;
+            __syncwarp();
+        }
+        const double d = A[kk * 9];
+        if (d == 0) continue;
+        // one division per row, on the lane that owns the row index
+        const double lrow = (lane < 8 && lane > kk) ? A[lane * 8 + kk] / d : 0.0;
+        const double l0 = __shfl_sync(0xffffffffu, lrow, j0 <= i0 ? i0 : j0);
+        const double l1 = __shfl_sync(0xffffffffu, lrow, j1 <= i1 ? i1 : j1);
+        auto upd = [&](int i, int j, double cur, double l) {
+            if (i > kk && j == kk) return l;
+            if (i > kk && j > kk && j <= i) return cur - l * A[kk * 8 + j];
+            if (i > kk && j > i) return A[j * 8 + i] - l * A[kk * 8 + i];
+            return cur;
+        };
+        const double n0 = upd(i0, j0, A[e0], l0), n1 = upd(i1, j1, A[e1], l1);
+        __syncwarp();
+        A[e0] = n0; A[e1] = n1;
+        __syncwarp();
+    }
+    // substitutions: lane i < 8 holds y[i]
+    double y = 0;
+    {
+        const int pm = perm;                       // rhs[perm[i]] with rhs = -b
+        if (lane < 8) y = -bv[pm];
+    }
+    for (int j = 0; j < 8; j++) {                  // forward: y[i] -= L[i][j] * y[j], j ascending
+        const double yj = __shfl_sync(0xffffffffu, y, j);
+        if (lane < 8 && lane > j) y -= A[lane * 8 + j] * yj;
+    }
+    if (lane < 8) { const double d = A[lane * 9]; y = (d == 0) ? 0 : y / d; }
+    for (int i = 7; i >= 0; i--) {                 // backward: y[i] -= sum_{j > i} L[j][i] * y[j], j ascending, i descending
+        double acc = __shfl_sync(0xffffffffu, y, i);
+        for (int j = i + 1; j < 8; j++) acc -= A[j * 8 + i] * __shfl_sync(0xffffffffu, y, j);
+        if (lane == i) y = acc;
+    }
+    if (lane < 8) inc[perm] = y;
+    __syncwarp();
+}
+
+__device__ void lm_candidate(const LmConst& k, LmState& s, TrkParams& p) {
+    double incS[8];
+    const float extrapLimit = 0.001f;
+    float extrap = 1;
+    if (s.lambda < extrapLimit) extrap = sqrtf(sqrt(extrapLimit / s.lambda));
+    double sq = 0;
+    for (int i = 0; i < 8; i++) {
+        s.inc[i] *= extrap;
+        incS[i] = s.inc[i] * (i < 3 ? LDSO_SCALE_XI_TRANS : i < 6 ? LDSO_SCALE_XI_ROT : i == 6 ? LDSO_SCALE_A : LDSO_SCALE_B);
+        sq += incS[i] * incS[i];
+    }
+    if (!isfinite(sq))
+        for (int i = 0; i < 8; i++) s.inc[i] = incS[i] = 0;
+    const ldso_sm::SE3 cand = ldso_sm::SE3::exp(incS) * se3_of(s.q, s.t);
+    s.cq[0] = cand.qw; s.cq[1] = cand.qx; s.cq[2] = cand.qy; s.cq[3] = cand.qz;
+    s.ct[0] = cand.t[0]; s.ct[1] = cand.t[1]; s.ct[2] = cand.t[2];
+    s.ca = s.a; s.cb = s.b;
+    s.ca += incS[6];
+    s.cb += incS[7];
+    lm_make_params(k, s.cq, s.ct, s.ca, s.cb, k.coarseCutoff * s.cutoffRepeat, p);
+}
+
+__global__ void __launch_bounds__(TRK_THREADS)
+k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__ newImg, const LmConst k,
+                       float* __restrict__ partials, int* __restrict__ partials_i, double* __restrict__ mailbox, double seq) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ TrkParams sp;
+    __shared__ LmState st;
+    __shared__ double s_res[NF + NI];
+    __shared__ float s_f[TRK_THREADS / 32][NF];
+    __shared__ int s_i[TRK_THREADS / 32][NI];
+    __shared__ double s_A[64];
+    __shared__ int s_cmd;
+    __shared__ long long s_t[8];   // dbg == 3: SM clocks spent per phase (CTA 0, thread 0)
+    long long tk = 0;
+    if (threadIdx.x < 8) s_t[threadIdx.x] = 0;
+#define LM_TICK(slot) do { if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[slot] += now - tk; tk = now; } } while (0)
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int G = gridDim.x;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 4; i++) st.q[i] = k.q[i];
+        for (int i = 0; i < 3; i++) st.t[i] = k.t[i];
+        st.a = k.affA; st.b = k.affB;
+        st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.nEval = 0; st.nAccept = 0; st.lambda = 0.01f; st.hsel = 0;
+        for (int i = 0; i < 8; i++) st.inc[i] = 0;
+        lm_make_params(k, st.q, st.t, st.a, st.b, k.coarseCutoff, sp);
+    }
+    __syncthreads();
+    tk = clock64();
+    for (int ev = 0;; ev++) {
+        float acc[NF];
+#pragma unroll
+        for (int q = 0; q < NF; q++) acc[q] = 0.f;
+        int cnt[NI] = {0, 0, 0, 0};
+        for (int i = blockIdx.x * TRK_THREADS + threadIdx.x; i < k.n; i += G * TRK_THREADS)
+            eval_point(sp, __ldg(pc + i), i, newImg, acc, cnt[0], cnt[1], cnt[2], cnt[3]);
+#pragma unroll
+        for (int q = 0; q < NF; q++) {
+            float v = acc[q];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            acc[q] = v;
+        }
+#pragma unroll
+        for (int q = 0; q < NI; q++)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) cnt[q] += __shfl_xor_sync(0xffffffffu, cnt[q], o);
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < NF; q++) s_f[wid][q] = acc[q];
+#pragma unroll
+            for (int q = 0; q < NI; q++) s_i[wid][q] = cnt[q];
+        }
+        __syncthreads();
+        float* pf = partials + (size_t)(ev & 1) * G * TRK_NRED;
+        int* pi = partials_i + (size_t)(ev & 1) * G * NI;
+        if (threadIdx.x < NF) {
+            float v = 0.f;
+#pragma unroll
+            for (int wq = 0; wq < TRK_THREADS / 32; wq++) v += s_f[wq][threadIdx.x];
+            pf[threadIdx.x * G + blockIdx.x] = v;            // [value][CTA]: the fold reads whole rows
+        } else if (threadIdx.x < NF + NI) {
+            const int f = threadIdx.x - NF;
+            int v = 0;
+#pragma unroll
+            for (int wq = 0; wq < TRK_THREADS / 32; wq++) v += s_i[wq][f];
+            pi[f * G + blockIdx.x] = v;
+        }
+        LM_TICK(0);
+        grid.sync();
+        LM_TICK(1);
+        if (k.dbg == 2) { if (ev == 11) break; continue; }
+        // every CTA folds all partials in the same fixed order (lanes stride over CTAs, then a shuffle tree); warp w owns
+        // values w, w + 4, ...: 13 independent load streams per lane, so the fold costs about one L2 round trip
+        {
+            double acc13[13];
+#pragma unroll
+            for (int qq = 0; qq < 13; qq++) acc13[qq] = 0.0;
+            for (int b = lane; b < G; b += 32) {
+#pragma unroll
+                for (int qq = 0; qq < 13; qq++) {
+                    const int q = wid + 4 * qq;
+                    if (qq < 12) acc13[qq] += (double)__ldcg(pf + q * G + b);
+                    else acc13[qq] += (double)__ldcg(pi + (q - NF) * G + b);
+                }
+            }
+#pragma unroll
+            for (int qq = 0; qq < 13; qq++) {
+                double v = acc13[qq];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) s_res[wid + 4 * qq] = v;
+            }
+        }
+        __syncthreads();
+        LM_TICK(2);
+        if (k.dbg == 1) { if (ev == 11) break; continue; }
+        if (threadIdx.x < 45) lm_Hb_entry(s_res, st.H[st.hsel ^ 1], st.bv[st.hsel ^ 1], threadIdx.x);
+        __syncthreads();
+        if (threadIdx.x == 0) s_cmd = lm_decide(k, st, s_res, sp);
+        __syncthreads();
+        LM_TICK(3);
+        if (s_cmd == LM_DONE) break;
+        if (s_cmd == LM_SOLVE) {
+            const bool fixed = k.optA < 0 || k.optB < 0;
+            if (!fixed && wid == 0) lm_ldlt8_warp(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, s_A, st.inc, lane);
+            if (fixed && threadIdx.x == 0)
+                lm_solve_step_fixed(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, k.optA < 0, k.optB < 0, st.inc);
+            __syncthreads();
+            LM_TICK(4);
+            if (threadIdx.x == 0) lm_candidate(k, st, sp);
+            __syncthreads();
+            LM_TICK(5);
+        }
+    }
+    if (blockIdx.x != 0 || wid != 0) return;
+    // message to the host: pose (q, t), affine, resOld[6], cutoffRepeat, nEval, nAccept — then the sequence number
+    double v = 0.0;
+    if (lane < 4) v = st.q[lane];
+    else if (lane < 7) v = st.t[lane - 4];
+    else if (lane == 7) v = st.a;
+    else if (lane == 8) v = st.b;
+    else if (lane < 15) v = st.resOld[lane - 9];
+    else if (lane == 15) v = st.cutoffRepeat;
+    else if (lane == 16) v = st.nEval;
+    else if (lane == 17) v = st.nAccept;
+    if (lane < 18) mailbox[lane] = v;
+    if (k.dbg == 3 && lane < 8) mailbox[20 + lane] = (double)s_t[lane];
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile double*>(mailbox + 63) = seq;
+}
+
+}  // namespace
+
 // include/AffLight.h:27-35 (float arithmetic, returned as double in the reference)
 static inline void from_to_vec_exposure(float exposureF, float exposureT, float aF, float bF, float aT, float bT, float* a_out,
                                         float* b_out) {
@@ -248,5 +674,64 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     c->d2h_bytes += (NF + NI + 1) * sizeof(double);
     for (int k = 0; k < NF; k++) out->sums[k] = res[k];
     for (int k = 0; k < NI; k++) out->counts[k] = (int)res[NF + k];
+    return 0;
+}
+
+// One pyramid level of trackNewestCoarse on the device (see k34_track_level_kernel).  In/out: pose, affine.
+int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, float& aff_a, float& aff_b, int maxIt,
+                    double resOld[6], float* cutoffRepeat, int* nEval, int* nAccept) {
+    TrackerDev& T = c->trk[tracker];
+    LmConst k;
+    for (int i = 0; i < 9; i++) k.Ki[i] = T.Ki[lvl][i];
+    k.fx = T.fx[lvl]; k.fy = T.fy[lvl]; k.cx = T.cx[lvl]; k.cy = T.cy[lvl];
+    k.w = T.w[lvl]; k.h = T.h[lvl]; k.n = T.pc_n[lvl]; k.lvl = lvl; k.maxIt = maxIt; k.solveMode = c->cfg.tracker_solve_mode;
+    k.huberTH = c->cfg.huber_th; k.coarseCutoff = c->cfg.coarse_cutoff_th;
+    k.optA = c->cfg.affine_opt_mode_a; k.optB = c->cfg.affine_opt_mode_b;
+    k.refExposure = T.ref_exposure; k.newExposure = T.new_exposure; k.refAffA = T.ref_aff_a; k.refAffB = T.ref_aff_b;
+    k.q[0] = cur.qw; k.q[1] = cur.qx; k.q[2] = cur.qy; k.q[3] = cur.qz;
+    k.t[0] = cur.t[0]; k.t[1] = cur.t[1]; k.t[2] = cur.t[2];
+    k.affA = aff_a; k.affB = aff_b;
+    k.dbg = c->cfg.reserved[0];
+    if (c->trk_coop_max == 0) {
+        int per_sm = 0, sms = 0, dev = 0, coop = 0;
+        LDSO_CUDA_OK(c, cudaGetDevice(&dev));
+        LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+        if (!coop) { c->set_error("device lacks cooperative launch", __FILE__, __LINE__); return -1; }
+        LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        LDSO_CUDA_OK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k34_track_level_kernel, TRK_THREADS, 0));
+        c->trk_coop_max = std::max(1, std::min(per_sm * sms, LM_MAX_CTAS));
+    }
+    int blocks = std::max(1, (k.n + TRK_THREADS - 1) / TRK_THREADS);
+    blocks = std::min(blocks, std::min(c->trk_coop_max, c->trk_max_blocks / 2));
+    const float4* pc = T.pc[lvl];
+    const float4* img = c->frame[T.new_slot] + c->lvl_off[lvl];
+    float* pf = c->trk_partials;
+    int* pi = c->trk_partials_i;
+    double* mb = c->trk_mailbox_dev;
+    double seq = (double)(++c->trk_seq);
+    void* args[] = {(void*)&pc, (void*)&img, (void*)&k, (void*)&pf, (void*)&pi, (void*)&mb, (void*)&seq};
+    prof_begin(c, c->stream);
+    LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(TRK_THREADS), args, 0, c->stream));
+    c->launches++;
+    const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
+    volatile double* res = c->trk_mailbox;
+    for (unsigned spin = 1; res[63] != seq; spin++) {
+        _mm_pause();
+        if ((spin & 0xfffff) == 0) {
+            cudaError_t q = cudaStreamQuery(c->stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);
+            if (q == cudaSuccess && res[63] != seq) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    c->d2h_bytes += 19 * sizeof(double);
+    cur.qw = res[0]; cur.qx = res[1]; cur.qy = res[2]; cur.qz = res[3];
+    cur.t[0] = res[4]; cur.t[1] = res[5]; cur.t[2] = res[6];
+    aff_a = (float)res[7]; aff_b = (float)res[8];
+    for (int i = 0; i < 6; i++) resOld[i] = res[9 + i];
+    *cutoffRepeat = (float)res[15];
+    *nEval = (int)res[16]; *nAccept = (int)res[17];
+    if (prof_idx >= 0) c->prof_pending[prof_idx].units = (double)k.n * *nEval;   // point evaluations of this launch
+    if (k.dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[20 + i];
     return 0;
 }
