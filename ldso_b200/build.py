@@ -58,11 +58,11 @@ def build_oracle(force=False):
     srcs = sorted(glob.glob(os.path.join(ORACLE_DIR, "*.cpp")))
     deps = srcs + glob.glob(os.path.join(ORACLE_DIR, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
     common = ["g++", "-std=c++17", "-O3", "-march=x86-64-v3", "-DENABLE_SSE", "-fPIC", "-shared", "-pthread",
-              "-Wall", "-Wno-unused-function", "-Wno-unused-variable"]
+              "-Wall", "-Wno-unused-function", "-Wno-unused-variable", "-Wno-unknown-pragmas"]
     if force or not _newer(ORACLE_LIB, deps):
         _run(common + ["-ffp-contract=off", "-o", ORACLE_LIB] + srcs)
     if force or not _newer(ORACLE_FAST_LIB, deps):
-        _run(common + ["-o", ORACLE_FAST_LIB] + srcs)
+        _run(common + ["-fopenmp", "-o", ORACLE_FAST_LIB] + srcs)   # timing build: contraction + worker threads (ORC_THREADS)
     return ORACLE_LIB
 
 

@@ -388,7 +388,12 @@ static float new_frame_energy_th(orc_ctx* c) {
 extern "C" int orc_window_linearize(orc_ctx* c, int fix, double stats[3], float* new_th) {
     Window& W = c->win;
     double E = 0, num = 0;
-    for (int r = 0; r < W.nr; r++) {
+    const int T = orc_threads(c);
+    // FullSystem::linearizeAll_Reductor splits activeResiduals over the worker threads (FullSystem.cc:1716-1824); here the
+    // split is by point so that the per-point bookkeeping of the fix pass stays race-free
+#pragma omp parallel for num_threads(T) if (T > 1) schedule(static) reduction(+ : E, num)
+    for (int p = 0; p < W.np; p++)
+    for (int r = W.res_begin[p]; r < W.res_begin[p + 1]; r++) {
         if (W.flags[r] & LDSO_RF_LINEARIZED) continue;   // activeResiduals = !isLinearized (FullSystem.cc:864)
         E += linearize_one(c, r);
         if (W.state_NewState[r] == LDSO_RES_IN) num += 1;
@@ -687,26 +692,56 @@ static void sc_stitch(orc_ctx* c, SCAcc& S, double* H, double* b) {
 }
 
 // EnergyFunctional::accumulateAF_MT / LF_MT / SCF_MT, MT=false paths (EnergyFunctional.cc:670-749)
+// Per-thread accumulators merged before stitching, as the reference's accSSE_top_A[tid] / accE[tid] are
+// (AccumulatedTopHessian.cc:193-213, AccumulatedSCHessian.cc:53-75).  Only the timing build is threaded.
+static void merge_into(AccumulatorApprox& d, AccumulatorApprox& s) {
+    d.finish(); s.finish();
+    for (int i = 0; i < 60; i++) d.Data1m[i] += s.Data1m[i];
+    for (int i = 0; i < 32; i++) d.TopRight_Data1m[i] += s.TopRight_Data1m[i];
+    for (int i = 0; i < 8; i++) d.BotRight_Data1m[i] += s.BotRight_Data1m[i];
+    d.numIn1m += s.num;
+}
+static void merge_into(AccumulatorMat& d, AccumulatorMat& s) {
+    d.finish(); s.finish();
+    for (size_t i = 0; i < d.A1m.size(); i++) d.A1m[i] += s.A1m[i];
+    d.numIn1m += s.num;
+}
+
 extern "C" int orc_window_accumulate(orc_ctx* c, double* HA, double* bA, double* HL, double* bL, double* Hsc, double* bsc,
                                      int counts[2]) {
     Window& W = c->win;
     const int n = W.n;
-    std::vector<AccumulatorApprox> accA(n * n), accL(n * n);
-    for (auto& a : accA) a.initialize();
-    for (auto& a : accL) a.initialize();
-    int nresA = 0, nresL = 0;
-    for (int p = 0; p < W.np; p++) top_add_point(c, 0, p, accA, nresA);
-    top_stitch(c, accA, false, HA, bA);
-    for (int p = 0; p < W.np; p++) top_add_point(c, 1, p, accL, nresL);
-    top_stitch(c, accL, true, HL, bL);
-    SCAcc S;
-    S.accE.resize(n * n); S.accEB.resize(n * n); S.accD.resize(n * n * n);
-    for (auto& a : S.accE) a.initialize(8, 4);
-    for (auto& a : S.accEB) a.initialize(8, 1);
-    for (auto& a : S.accD) a.initialize(8, 8);
-    S.accHcc.initialize(4, 4); S.accbc.initialize(4, 1);
-    for (int p = 0; p < W.np; p++) sc_add_point(c, p, true, S);
-    sc_stitch(c, S, Hsc, bsc);
+    const int T = orc_threads(c);
+    std::vector<std::vector<AccumulatorApprox>> accA(T, std::vector<AccumulatorApprox>(n * n)), accL = accA;
+    std::vector<SCAcc> S(T);
+    std::vector<int> nA(T, 0), nL(T, 0);
+#pragma omp parallel num_threads(T) if (T > 1)
+    {
+        const int tid = orc_thread_id();
+        for (auto& a : accA[tid]) a.initialize();
+        for (auto& a : accL[tid]) a.initialize();
+        SCAcc& St = S[tid];
+        St.accE.resize(n * n); St.accEB.resize(n * n); St.accD.resize(n * n * n);
+        for (auto& a : St.accE) a.initialize(8, 4);
+        for (auto& a : St.accEB) a.initialize(8, 1);
+        for (auto& a : St.accD) a.initialize(8, 8);
+        St.accHcc.initialize(4, 4); St.accbc.initialize(4, 1);
+        const int p0 = (int)((long long)W.np * tid / T), p1 = (int)((long long)W.np * (tid + 1) / T);
+        for (int p = p0; p < p1; p++) top_add_point(c, 0, p, accA[tid], nA[tid]);
+        for (int p = p0; p < p1; p++) top_add_point(c, 1, p, accL[tid], nL[tid]);
+        for (int p = p0; p < p1; p++) sc_add_point(c, p, true, St);
+    }
+    int nresA = nA[0], nresL = nL[0];
+    for (int t = 1; t < T; t++) {
+        for (int k = 0; k < n * n; k++) { merge_into(accA[0][k], accA[t][k]); merge_into(accL[0][k], accL[t][k]); }
+        for (int k = 0; k < n * n; k++) { merge_into(S[0].accE[k], S[t].accE[k]); merge_into(S[0].accEB[k], S[t].accEB[k]); }
+        for (int k = 0; k < n * n * n; k++) merge_into(S[0].accD[k], S[t].accD[k]);
+        merge_into(S[0].accHcc, S[t].accHcc); merge_into(S[0].accbc, S[t].accbc);
+        nresA += nA[t]; nresL += nL[t];
+    }
+    top_stitch(c, accA[0], false, HA, bA);
+    top_stitch(c, accL[0], true, HL, bL);
+    sc_stitch(c, S[0], Hsc, bsc);
     if (counts) { counts[0] = nresA; counts[1] = nresL; }
     return 0;
 }

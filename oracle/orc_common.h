@@ -141,4 +141,14 @@ struct orc_ctx {
     std::shared_ptr<void> selector, immature;   // per-ctx state of orc_selector.cpp / orc_immature.cpp (die with the ctx)
     std::string err;
     long long launches = 0;
+    int threads = 1;   // worker threads of the timing build (env ORC_THREADS at create; the reference uses NUM_THREADS = 6)
 };
+
+#ifdef _OPENMP
+#include <omp.h>
+inline int orc_threads(const orc_ctx* c) { return c->threads > 1 ? c->threads : 1; }
+inline int orc_thread_id() { return omp_get_thread_num(); }
+#else
+inline int orc_threads(const orc_ctx*) { return 1; }
+inline int orc_thread_id() { return 0; }
+#endif

@@ -3,6 +3,8 @@
 // makeCoarseDepthL0, calcRes, calcGSSSE, trackNewestCoarse}, Accumulator9.
 #include "orc_common.h"
 
+#include <algorithm>
+
 using namespace orc;
 using ldso_sm::SE3;
 
@@ -63,6 +65,7 @@ extern "C" int orc_create(const ldso_gpu_config* cfg, orc_ctx** out) {
     c->cfg = *cfg;
     c->levels = derive_levels(cfg->w, cfg->h, c->wG, c->hG);
     for (int i = 0; i < 256; i++) c->B[i] = (float)i;
+    if (const char* e = getenv("ORC_THREADS")) c->threads = std::max(1, atoi(e));
     c->frames.resize(cfg->n_frame_slots);
     for (auto& f : c->frames)
         for (int l = 0; l < c->levels; l++) {

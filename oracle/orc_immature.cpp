@@ -311,6 +311,8 @@ extern "C" int orc_immature_activate(orc_ctx* c, int n_cand, const int* cand, in
                                      int* res_state_out) {
     Pool& P = pool_of(c);
     Window& W = c->win;
+    const int T = orc_threads(c);   // activatePointsMT_Reductor (FullSystem.cc:1339-1354)
+#pragma omp parallel for num_threads(T) if (T > 1) schedule(static)
     for (int q = 0; q < n_cand; q++) {
         const int k = cand[q];
         ok_out[q] = 0; idepth_out[q] = 0;
