@@ -135,7 +135,6 @@ class Sequence:
             k = (f - 1) // KF_EVERY * KF_EVERY if f > PRE else PRE            # newest keyframe before frame f
             hosts = list(range(k - PRE, k + 1, KF_EVERY))
             self.tables[f] = (hosts,) + self.host_tables(hosts, f)
-        self.pool = None
         self.ref_idx = None
         self.phase = {}
         self.last_rel = IDENT.copy()
@@ -166,36 +165,25 @@ class Sequence:
 
     # ---- immature pool (host-managed like the reference's per-frame immaturePoints lists) ----
     def new_immature(self, f, host_idx):
-        """PixelSelector::makeMaps + ImmaturePoint constructor for keyframe f (FullSystem::makeNewTraces, :1426-1482)"""
+        """PixelSelector::makeMaps + ImmaturePoint constructor for keyframe f (FullSystem::makeNewTraces, :1426-1482); the new
+        points join the device-resident pool, only their pixel list visits the host"""
         sl = self.kf_slot(f)
         t = time.perf_counter()
-        m, n, self.potential = self.ctx.select_make_maps(sl, N_IMMATURE, potential=getattr(self, "potential", 3))
-        t = self.tick("KF A2 makeMaps", t)
-        m[:5, :] = 0; m[-5:, :] = 0; m[:, :5] = 0; m[:, -5:] = 0          # patternPadding+1 border (:1444-1446)
-        v, u = np.nonzero(m)
-        u = u.astype(np.float32); v = v.astype(np.float32)
-        t = self.tick("KF host: map -> point list", t)
-        col, wgt, gh, eth = self.ctx.immature_create(sl, u, v)
-        t = self.tick("KF K6 ImmaturePoint ctor", t)
-        ok = np.isfinite(eth)
-        k = int(ok.sum())
-        return dict(host=np.full(k, host_idx, np.int32), u=u[ok], v=v[ok], color=col[ok], weights=wgt[ok], grad_h=gh[ok],
-                    energy_th=eth[ok], idepth_min=np.zeros(k, np.float32), idepth_max=np.full(k, np.nan, np.float32),
-                    quality=np.full(k, 10000.0, np.float32), status=np.full(k, 5, np.int32))
-
-    def upload_pool(self):
-        P = self.pool
-        self.ctx.immature_set(P["host"], P["u"], P["v"], P["color"], P["weights"], P["grad_h"], P["energy_th"], P["idepth_min"],
-                              P["idepth_max"], P["quality"], P["status"])
+        u, v, typ, self.potential = self.ctx.select_points(sl, N_IMMATURE, potential=getattr(self, "potential", 3), border=5)
+        t = self.tick("KF A2 makeMaps -> point list", t)
+        n_pool = self.ctx.immature_append(sl, host_idx, u, v)
+        t = self.tick("KF K6 ImmaturePoint ctor + append", t)
+        return len(u), n_pool
 
     def prime(self):
         """untimed: pyramids of the first WINDOW keyframes, their immature points, the first tracking reference"""
-        parts = []
+        z = np.zeros(0, np.float32)
+        self.ctx.immature_set(np.zeros(0, np.int32), z, z, np.zeros((0, 8)), np.zeros((0, 8)), np.zeros((0, 3)), z, z, z, z,
+                              np.zeros(0, np.int32))
         for hi, f in enumerate(range(0, PRE + 1, KF_EVERY)):
             self.ctx.make_images(self.kf_slot(f), self.frames[f])
-            parts.append(self.new_immature(f, hi))
-        self.pool = {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
-        self.upload_pool()
+            self.new_immature(f, hi)
+        self.pending_remove = np.zeros(0, np.int32)
         self.set_ref(PRE)
 
     def set_ref(self, f):
@@ -230,15 +218,10 @@ class Sequence:
         """FullSystem::makeKeyFrame cadence (FullSystem.cc:485-699) with harness-provided window contents"""
         ctx, W = self.ctx, self.windows[f]
         t = time.perf_counter()
-        # pool bookkeeping: read back what the host branches on, drop the frame that leaves the window
-        tr = ctx.immature_get()
-        P = self.pool
-        P["idepth_min"], P["idepth_max"], P["quality"], P["status"] = tr["idepth_min"], tr["idepth_max"], tr["quality"], tr["status"]
-        keep = (P["host"] > 0) & (P["status"] != 1)                    # OOB points are deleted (:1279-1284)
-        P = {k: a[keep] for k, a in P.items()}
-        P["host"] = P["host"] - 1
-        self.pool = P
-        self.upload_pool()
+        # the pool stays on the device: drop the frame that leaves the window, OOB points (:1279-1284) and the points
+        # activated at the previous keyframe, then read back only what candidate selection branches on
+        ctx.immature_compact(drop_host=0, drop_oob=True, remove=self.pending_remove)
+        P = ctx.immature_get(("status", "idepth_max", "quality"))
         t = self.tick("KF pool bookkeeping", t)
         # activatePointsMT -> optimizeImmaturePoint (K6) on the best-traced candidates
         ctx.window_set_frames(W, W["slots"])
@@ -249,8 +232,7 @@ class Sequence:
         if len(cand):
             idp, ok, st = ctx.immature_activate(cand, min_obs=1)
             n_ok = int(ok.sum())
-            keep = np.ones(len(P["host"]), bool); keep[cand] = False   # activated or dropped either way (:1301-1318)
-            self.pool = P = {k: a[keep] for k, a in P.items()}
+        self.pending_remove = cand                                     # activated or dropped either way (:1301-1318)
         t = self.tick("KF K6 activate", t)
         # window BA: FullSystem::optimize (:844-1007)
         ctx.window_load(W, W["slots"])
@@ -284,14 +266,10 @@ class Sequence:
         # setCoarseTrackingRef for the next frames, then new immature points on this keyframe
         self.set_ref(f)
         t = self.tick("KF K2 setCoarseTrackingRef", t)
-        newp = self.new_immature(f, WINDOW - 1)
-        t_pool = time.perf_counter()
-        self.pool = {k: np.concatenate([self.pool[k], newp[k]]) for k in newp}
-        self.upload_pool()
-        self.phase["KF pool bookkeeping"] = self.phase.get("KF pool bookkeeping", 0.0) + (time.perf_counter() - t_pool)
+        n_new, n_pool = self.new_immature(f, WINDOW - 1)
         self.kf_log.append(dict(frame=f, trace_counts=counts.tolist(), activated=n_ok, candidates=int(len(cand)), e0=float(e0),
-                                e_final=float(st[0]), n_in=int(st[2]), pool=int(len(self.pool["host"])),
-                                residuals=int(len(W["target"])), new_immature=int(len(newp["host"]))))
+                                e_final=float(st[0]), n_in=int(st[2]), pool=int(n_pool),
+                                residuals=int(len(W["target"])), new_immature=int(n_new)))
 
     def gt_error(self):
         """max translation error of the tracked relative poses vs ground truth — proves the timed work is real tracking"""

@@ -158,6 +158,13 @@ int ldso_gpu_tracker_track(ldso_gpu_ctx* ctx, int tracker, int new_slot, float n
 int ldso_gpu_select_make_maps(ldso_gpu_ctx* ctx, int slot, float density, int recursions_left, float th_factor,
                               int* potential_io, float* map_out, int* n_selected);
 
+/* PixelSelector::makeMaps followed by the pixel loop of FullSystem::makeNewTraces (src/frontend/FullSystem.cc:1440-1460):
+ * the selected pixels with border <= x < w - border, border <= y < h - border in row-major order as (u, v, type) lists,
+ * type = the map value 1 / 2 / 4.  At most max_points are returned. */
+int ldso_gpu_select_points(ldso_gpu_ctx* ctx, int slot, float density, int recursions_left, float th_factor,
+                           int* potential_io, int border, int max_points, float* u_out, float* v_out, float* type_out,
+                           int* n_points);
+
 /* ---- K5 / K6: immature points (src/internal/ImmaturePoint.cc) ---------------------------------------
  * The pool of immature points lives on the device; the host re-sends it after it adds or removes points
  * (once per keyframe) and reads back what it branches on.  ImmaturePointStatus codes as in
@@ -183,6 +190,17 @@ int ldso_gpu_immature_get(ldso_gpu_ctx* ctx, float* idepth_min, float* idepth_ma
  * res_state_out [n_cand][n_frames] the final ResState per target (-1 for the host frame itself). */
 int ldso_gpu_immature_activate(ldso_gpu_ctx* ctx, int n_cand, const int* cand, int min_obs, float* idepth_out,
                                int* ok_out, int* res_state_out);
+
+/* Device-resident pool maintenance: the pool never has to come back to the host to change shape.
+ * compact: drop every point hosted by frame index drop_host (-1: none) — the frame that leaves the window
+ *          (FullSystem::marginalizeFrame) —, every point whose status is OOB when drop_oob != 0 (FullSystem.cc:1279-1284),
+ *          and the listed pool indices (points that were activated or discarded, :1301-1318).  Order is preserved and
+ *          host indices above drop_host move down by one.  n_out: new pool size.
+ * append:  ImmaturePoint constructor (:14-39) for n pixels of frame `slot` + append to the pool with host index host_idx,
+ *          idepth_min 0, idepth_max NaN, quality 10000, status UNINITIALIZED (OOB where the patch is not finite, the
+ *          reference deletes such points: FullSystem.cc:1456-1458).  n_pool: new pool size. */
+int ldso_gpu_immature_compact(ldso_gpu_ctx* ctx, int drop_host, int drop_oob, int n_remove, const int* remove_idx, int* n_out);
+int ldso_gpu_immature_append(ldso_gpu_ctx* ctx, int slot, int host_idx, int n, const float* u, const float* v, int* n_pool);
 
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps

@@ -231,6 +231,17 @@ class Ctx:
                    _fp(out), C.byref(n))
         return out, n.value, pot.value
 
+    def select_points(self, slot, density, potential=3, recursions=1, th_factor=1.0, border=5, max_points=None):
+        """makeMaps + row-major list of the selected pixels inside the border: (u, v, type, potential)"""
+        w, h = self.sizes[0]
+        cap = max_points if max_points is not None else (w * h) // 2
+        u = np.empty(cap, np.float32); v = np.empty(cap, np.float32); t = np.empty(cap, np.float32)
+        pot = C.c_int(potential)
+        n = C.c_int()
+        self._call("select_points", C.c_int(slot), C.c_float(density), C.c_int(recursions), C.c_float(th_factor), C.byref(pot),
+                   C.c_int(border), C.c_int(cap), _fp(u), _fp(v), _fp(t), C.byref(n))
+        return u[: n.value].copy(), v[: n.value].copy(), t[: n.value].copy(), pot.value
+
     # ---- K5 / K6: immature points ----
     def immature_create(self, slot, u, v):
         """ImmaturePoint constructor: (color[n,8], weights[n,8], gradH[n,3], energyTH[n])"""
@@ -253,13 +264,32 @@ class Ctx:
         self._call("immature_trace", C.c_int(new_slot), C.c_int(len(Kt)), _fp(KRKi), _fp(Kt), _fp(aff), _ip(cnt))
         return cnt
 
-    def immature_get(self):
+    def immature_get(self, fields=None):
+        """read back pool state; fields: subset of (idepth_min, idepth_max, quality, status, uv, interval), default all"""
         n = self.imm_n
-        out = dict(idepth_min=np.zeros(n, np.float32), idepth_max=np.zeros(n, np.float32), quality=np.zeros(n, np.float32),
-                   status=np.zeros(n, np.int32), uv=np.zeros((n, 2), np.float32), interval=np.zeros(n, np.float32))
-        self._call("immature_get", _fp(out["idepth_min"]), _fp(out["idepth_max"]), _fp(out["quality"]), _ip(out["status"]),
-                   _fp(out["uv"]), _fp(out["interval"]))
+        names = ("idepth_min", "idepth_max", "quality", "status", "uv", "interval")
+        want = names if fields is None else fields
+        out = {}
+        for k in names:
+            if k in want:
+                out[k] = np.zeros((n, 2) if k == "uv" else n, np.int32 if k == "status" else np.float32)
+        g = lambda k: (_ip(out[k]) if k == "status" else _fp(out[k])) if k in out else None
+        self._call("immature_get", g("idepth_min"), g("idepth_max"), g("quality"), g("status"), g("uv"), g("interval"))
         return out
+
+    def immature_compact(self, drop_host=-1, drop_oob=True, remove=None):
+        rm = np.ascontiguousarray(remove if remove is not None else [], dtype=np.int32)
+        n = C.c_int()
+        self._call("immature_compact", C.c_int(drop_host), C.c_int(1 if drop_oob else 0), C.c_int(len(rm)), _ip(rm), C.byref(n))
+        self.imm_n = n.value
+        return n.value
+
+    def immature_append(self, slot, host_idx, u, v):
+        u, v = f32(u), f32(v)
+        n = C.c_int()
+        self._call("immature_append", C.c_int(slot), C.c_int(host_idx), C.c_int(len(u)), _fp(u), _fp(v), C.byref(n))
+        self.imm_n = n.value
+        return n.value
 
     def immature_activate(self, cand, min_obs=1):
         cand = np.ascontiguousarray(cand, dtype=np.int32)

@@ -276,6 +276,33 @@ __global__ void a2_thin_apply_kernel(float* __restrict__ map, int w, int h, cons
     if (lane == 0 && rem) atomicAdd(removed, rem);
 }
 
+// ---- selected pixels as a row-major list (inside the border) ----------------------------------------------
+__global__ void a2_list_count_kernel(const float* __restrict__ map, int w, int h, int border, int* __restrict__ row_cnt) {
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row > h) return;
+    int cnt = 0;
+    if (row >= border && row < h - border)
+        for (int x = border + lane; x < w - border; x += 32) cnt += map[(size_t)row * w + x] != 0.f;
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) row_cnt[row] = cnt;      // row h: sentinel, becomes the total after the exclusive scan
+}
+__global__ void a2_list_emit_kernel(const float* __restrict__ map, int w, int h, int border, const int* __restrict__ row_off,
+                                    float* __restrict__ list, int max_list) {
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= h || row < border || row >= h - border) return;
+    int off = row_off[row];
+    for (int x0 = border; x0 < w - border; x0 += 32) {
+        int x = x0 + lane;
+        float m = x < w - border ? map[(size_t)row * w + x] : 0.f;
+        unsigned bal = __ballot_sync(0xffffffffu, m != 0.f);
+        if (m != 0.f) {
+            int k = off + __popc(bal & ((1u << lane) - 1u));
+            if (k < max_list) { list[3 * k] = (float)x; list[3 * k + 1] = (float)row; list[3 * k + 2] = m; }
+        }
+        off += __popc(bal);
+    }
+}
+
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------------------
@@ -287,6 +314,8 @@ struct SelectorDev {
     int* cand = nullptr;
     unsigned char* dsel = nullptr;
     int *row_cnt = nullptr, *counts = nullptr;
+    float* list = nullptr;   // [max_list][3] selected (u, v, type)
+    int max_list = 0;
     unsigned short* mask_pinned = nullptr;
     unsigned char* dsel_pinned = nullptr;
     int* counts_pinned = nullptr;
@@ -325,7 +354,9 @@ static int selector_init(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaMalloc(&S->mask, (size_t)S->max_slots * sizeof(unsigned short)));
     LDSO_CUDA_OK(c, cudaMalloc(&S->cand, (size_t)S->max_slots * 16 * sizeof(int)));
     LDSO_CUDA_OK(c, cudaMalloc(&S->dsel, (size_t)S->max_slots));
-    LDSO_CUDA_OK(c, cudaMalloc(&S->row_cnt, (h + 1) * sizeof(int)));
+    LDSO_CUDA_OK(c, cudaMalloc(&S->row_cnt, (h + 2) * sizeof(int)));
+    S->max_list = (int)std::min(wh, c->scratch_host ? wh / 2 : wh);
+    LDSO_CUDA_OK(c, cudaMalloc(&S->list, (size_t)S->max_list * 3 * sizeof(float)));
     LDSO_CUDA_OK(c, cudaMalloc(&S->counts, 8 * sizeof(int)));
     LDSO_CUDA_OK(c, cudaMallocHost(&S->mask_pinned, (size_t)S->max_slots * sizeof(unsigned short)));
     LDSO_CUDA_OK(c, cudaMallocHost(&S->dsel_pinned, (size_t)S->max_slots));
@@ -337,7 +368,7 @@ void selector_free(ldso_gpu_ctx* c) {
     SelectorDev* S = (SelectorDev*)c->selector;
     if (!S) return;
     cudaFree(S->rp); cudaFree(S->ths); cudaFree(S->thsS); cudaFree(S->map); cudaFree(S->mask); cudaFree(S->cand);
-    cudaFree(S->dsel); cudaFree(S->row_cnt); cudaFree(S->counts);
+    cudaFree(S->dsel); cudaFree(S->row_cnt); cudaFree(S->counts); cudaFree(S->list);
     cudaFreeHost(S->mask_pinned); cudaFreeHost(S->dsel_pinned); cudaFreeHost(S->counts_pinned);
     delete S;
     c->selector = nullptr;
@@ -384,9 +415,10 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     return 0;
 }
 
-extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor,
-                                         int* potential_io, float* map_out, int* n_selected) {
-    LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && potential_io && map_out && n_selected);
+// makeMaps with the map left on the device (S->map)
+static int make_maps_device(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor, int* potential_io,
+                            int* n_selected) {
+    LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && potential_io && n_selected);
     LDSO_REQUIRE(c, c->levels >= 3 && *potential_io >= 1);
     int rc = selector_init(c);
     if (rc) return rc;
@@ -436,9 +468,50 @@ extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float densit
     *potential_io = ideal;
     *n_selected = numHaveSub;
     LDSO_CUDA_OK(c, cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor,
+                                         int* potential_io, float* map_out, int* n_selected) {
+    LDSO_REQUIRE(c, map_out != nullptr);
+    int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, n_selected);
+    if (rc) return rc;
+    SelectorDev* S = (SelectorDev*)c->selector;
+    const int w = c->wG[0], h = c->hG[0];
     float* hmap = (float*)c->scratch_host;
-    LDSO_CUDA_OK(c, ldso_copy(c, hmap, S->map, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_copy(c, hmap, S->map, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     memcpy(map_out, hmap, sizeof(float) * (size_t)w * h);
+    return 0;
+}
+
+// makeMaps + the pixel loop of FullSystem::makeNewTraces (src/frontend/FullSystem.cc:1440-1460): the selected pixels
+// inside the border, in row-major order, as (u, v, type) lists — 12 bytes per selected point cross the bus instead of
+// the whole map
+extern "C" int ldso_gpu_select_points(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor,
+                                      int* potential_io, int border, int max_points, float* u_out, float* v_out,
+                                      float* type_out, int* n_points) {
+    LDSO_REQUIRE(c, u_out && v_out && type_out && n_points && border >= 0 && max_points >= 0);
+    int nsel = 0;
+    int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, &nsel);
+    if (rc) return rc;
+    SelectorDev* S = (SelectorDev*)c->selector;
+    cudaStream_t s = c->stream;
+    const int w = c->wG[0], h = c->hG[0];
+    a2_list_count_kernel<<<(h + 8) / 8, 256, 0, s>>>(S->map, w, h, border, S->row_cnt);
+    a2_thin_scan_kernel<<<1, 1024, 0, s>>>(S->row_cnt, h + 1);
+    a2_list_emit_kernel<<<(h + 7) / 8, 256, 0, s>>>(S->map, w, h, border, S->row_cnt, S->list, S->max_list);
+    c->launches += 3;
+    LDSO_CUDA_OK(c, cudaGetLastError());
+    int* total = (int*)S->counts_pinned;
+    LDSO_CUDA_OK(c, ldso_copy(c, total, S->row_cnt + h, sizeof(int), cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    int n = std::min(std::min(*total, max_points), S->max_list);
+    *n_points = n;
+    if (n == 0) return 0;
+    float* hl = (float*)c->scratch_host;
+    LDSO_CUDA_OK(c, ldso_copy(c, hl, S->list, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    for (int i = 0; i < n; i++) { u_out[i] = hl[3 * i]; v_out[i] = hl[3 * i + 1]; type_out[i] = hl[3 * i + 2]; }
     return 0;
 }

@@ -9,6 +9,8 @@
 // shared memory (100 floats per point) for the second-best scan of :213-219.
 #include "ctx.h"
 
+#include <algorithm>
+
 namespace {
 
 constexpr int IM_THREADS = 128;              // 16 points per CTA
@@ -19,6 +21,11 @@ struct ImmatureDev {
     int *host = nullptr, *status = nullptr;
     float *u = nullptr, *v = nullptr, *color = nullptr, *weights = nullptr, *gradH = nullptr, *energyTH = nullptr;
     float *idmin = nullptr, *idmax = nullptr, *quality = nullptr, *lastUV = nullptr, *interval = nullptr;
+    // second set of pool arrays: compaction writes here, then the two sets swap
+    int *host2 = nullptr, *status2 = nullptr;
+    float *u2 = nullptr, *v2 = nullptr, *color2 = nullptr, *weights2 = nullptr, *gradH2 = nullptr, *energyTH2 = nullptr;
+    float *idmin2 = nullptr, *idmax2 = nullptr, *quality2 = nullptr, *lastUV2 = nullptr, *interval2 = nullptr;
+    int *keep = nullptr, *pos = nullptr;     // [cap + 1] compaction flags / exclusive scan
     float* tables = nullptr;                 // per-host KRKi[9] Kt[3] aff[2] (stride 16)
     int* counts = nullptr;                   // [8]
     // activation scratch
@@ -472,6 +479,83 @@ __global__ void __launch_bounds__(IM_THREADS) k6_activate_kernel(const K6Params 
     p.idepth_out[q] = good ? currentIdepth : 0.f;
 }
 
+// ---- device-resident pool maintenance --------------------------------------------------------------------------
+struct PoolPtrs {
+    int *host, *status;
+    float *u, *v, *color, *weights, *gradH, *energyTH, *idmin, *idmax, *quality, *lastUV, *interval;
+};
+
+__global__ void im_flag_kernel(int n, const int* __restrict__ host, const int* __restrict__ status, int drop_host, int drop_oob,
+                               int* __restrict__ keep) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // keep[] was cleared to 0 and the explicit removals were marked -1 before this launch
+    const bool rm = keep[i] < 0 || (drop_host >= 0 && host[i] == drop_host) || (drop_oob && status[i] == 1);
+    keep[i] = rm ? 0 : 1;
+}
+__global__ void im_mark_kernel(int n_remove, const int* __restrict__ idx, int* __restrict__ keep) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_remove) keep[idx[i]] = -1;
+}
+// exclusive scan of keep[0..n) into pos[0..n], pos[n] = total; one CTA
+__global__ void __launch_bounds__(1024) im_scan_kernel(int n, const int* __restrict__ keep, int* __restrict__ pos) {
+    __shared__ int s[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int st = 0; st < n; st += 1024) {
+        const int i = st + threadIdx.x;
+        const int v = i < n ? keep[i] : 0;
+        s[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            const int t = threadIdx.x >= o ? s[threadIdx.x - o] : 0;
+            __syncthreads();
+            s[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < n) pos[i] = carry + s[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += s[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) pos[n] = carry;
+}
+__global__ void im_scatter_kernel(int n, const int* __restrict__ keep, const int* __restrict__ pos, int drop_host, const PoolPtrs a,
+                                  const PoolPtrs b) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !keep[i]) return;
+    const int o = pos[i];
+    const int h = a.host[i];
+    b.host[o] = (drop_host >= 0 && h > drop_host) ? h - 1 : h;
+    b.status[o] = a.status[i];
+    b.u[o] = a.u[i]; b.v[o] = a.v[i]; b.energyTH[o] = a.energyTH[i];
+    b.idmin[o] = a.idmin[i]; b.idmax[o] = a.idmax[i]; b.quality[o] = a.quality[i]; b.interval[o] = a.interval[i];
+    b.lastUV[2 * o] = a.lastUV[2 * i]; b.lastUV[2 * o + 1] = a.lastUV[2 * i + 1];
+    b.gradH[3 * o] = a.gradH[3 * i]; b.gradH[3 * o + 1] = a.gradH[3 * i + 1]; b.gradH[3 * o + 2] = a.gradH[3 * i + 2];
+    const float4* ca = reinterpret_cast<const float4*>(a.color + 8 * (size_t)i);
+    const float4* wa = reinterpret_cast<const float4*>(a.weights + 8 * (size_t)i);
+    float4* cb = reinterpret_cast<float4*>(b.color + 8 * (size_t)o);
+    float4* wb = reinterpret_cast<float4*>(b.weights + 8 * (size_t)o);
+    cb[0] = ca[0]; cb[1] = ca[1]; wb[0] = wa[0]; wb[1] = wa[1];
+}
+// new points of one keyframe: constructor results (cr scratch) -> pool rows [base, base + n)
+__global__ void im_append_kernel(int n, int base, int host_idx, const float* __restrict__ cr, const PoolPtrs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* out = cr + 2 * (size_t)n + 20 * (size_t)i;
+    const int o = base + i;
+    a.host[o] = host_idx;
+    a.u[o] = cr[i]; a.v[o] = cr[n + i];
+    for (int k = 0; k < 8; k++) { a.color[8 * (size_t)o + k] = out[k]; a.weights[8 * (size_t)o + k] = out[8 + k]; }
+    a.gradH[3 * o] = out[16]; a.gradH[3 * o + 1] = out[17]; a.gradH[3 * o + 2] = out[18];
+    const float eth = out[19];
+    a.energyTH[o] = eth;
+    a.status[o] = isfinite(eth) ? 5 : 1;     // a non-finite patch never becomes a point (FullSystem.cc:1456-1458): OOB
+    a.idmin[o] = 0.f; a.idmax[o] = __int_as_float(0x7fc00000); a.quality[o] = 10000.f;
+    a.lastUV[2 * o] = 0.f; a.lastUV[2 * o + 1] = 0.f; a.interval[o] = 0.f;
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------
 ImmatureDev* pool(ldso_gpu_ctx* c) {
     if (c->immature) return (ImmatureDev*)c->immature;
@@ -483,7 +567,12 @@ ImmatureDev* pool(ldso_gpu_ctx* c) {
     da((void**)&P->host, 4 * N); da((void**)&P->status, 4 * N); da((void**)&P->u, 4 * N); da((void**)&P->v, 4 * N);
     da((void**)&P->color, 32 * N); da((void**)&P->weights, 32 * N); da((void**)&P->gradH, 12 * N); da((void**)&P->energyTH, 4 * N);
     da((void**)&P->idmin, 4 * N); da((void**)&P->idmax, 4 * N); da((void**)&P->quality, 4 * N); da((void**)&P->lastUV, 8 * N);
-    da((void**)&P->interval, 4 * N); da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 32);
+    da((void**)&P->interval, 4 * N);
+    da((void**)&P->host2, 4 * N); da((void**)&P->status2, 4 * N); da((void**)&P->u2, 4 * N); da((void**)&P->v2, 4 * N);
+    da((void**)&P->color2, 32 * N); da((void**)&P->weights2, 32 * N); da((void**)&P->gradH2, 12 * N); da((void**)&P->energyTH2, 4 * N);
+    da((void**)&P->idmin2, 4 * N); da((void**)&P->idmax2, 4 * N); da((void**)&P->quality2, 4 * N); da((void**)&P->lastUV2, 8 * N);
+    da((void**)&P->interval2, 4 * N); da((void**)&P->keep, 4 * (N + 1)); da((void**)&P->pos, 4 * (N + 1));
+    da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 32);
     da((void**)&P->cand, 4 * N); da((void**)&P->act_idepth, 4 * N); da((void**)&P->act_ok, 4 * N);
     da((void**)&P->act_state, 4 * N * LDSO_MAX_WINDOW); da((void**)&P->cr, 4 * 22 * N);
     P->pinned_bytes = 4 * 32 * N + 4096;
@@ -499,7 +588,9 @@ void immature_free(ldso_gpu_ctx* c) {
     ImmatureDev* P = (ImmatureDev*)c->immature;
     if (!P) return;
     void* ptrs[] = {P->host, P->status, P->u, P->v, P->color, P->weights, P->gradH, P->energyTH, P->idmin, P->idmax, P->quality,
-                    P->lastUV, P->interval, P->tables, P->counts, P->cand, P->act_idepth, P->act_ok, P->act_state, P->cr};
+                    P->lastUV, P->interval, P->tables, P->counts, P->cand, P->act_idepth, P->act_ok, P->act_state, P->cr,
+                    P->host2, P->status2, P->u2, P->v2, P->color2, P->weights2, P->gradH2, P->energyTH2, P->idmin2, P->idmax2,
+                    P->quality2, P->lastUV2, P->interval2, P->keep, P->pos};
     for (void* p : ptrs) cudaFree(p);
     if (P->pinned) cudaFreeHost(P->pinned);
     delete P;
@@ -657,5 +748,70 @@ extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int
     LDSO_CUDA_OK(c, ldso_copy(c, st + 2 * N, P->act_state, 4 * N * W.n, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     memcpy(idepth_out, st, 4 * N); memcpy(ok_out, st + N, 4 * N); memcpy(res_state_out, st + 2 * N, 4 * N * W.n);
+    return 0;
+}
+
+static PoolPtrs pool_ptrs(ImmatureDev* P, bool alt) {
+    if (!alt) return {P->host, P->status, P->u, P->v, P->color, P->weights, P->gradH, P->energyTH, P->idmin, P->idmax, P->quality,
+                      P->lastUV, P->interval};
+    return {P->host2, P->status2, P->u2, P->v2, P->color2, P->weights2, P->gradH2, P->energyTH2, P->idmin2, P->idmax2, P->quality2,
+            P->lastUV2, P->interval2};
+}
+
+extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int drop_oob, int n_remove, const int* remove_idx,
+                                         int* n_out) {
+    ImmatureDev* P = pool(c);
+    if (!P) return -1;
+    LDSO_REQUIRE(c, n_remove >= 0 && n_remove <= P->n && (n_remove == 0 || remove_idx) && n_out);
+    const int n = P->n;
+    if (n == 0) { *n_out = 0; return 0; }
+    for (int i = 0; i < n_remove; i++) LDSO_REQUIRE(c, remove_idx[i] >= 0 && remove_idx[i] < n);
+    cudaStream_t s = c->stream;
+    LDSO_CUDA_OK(c, cudaMemsetAsync(P->keep, 0, 4 * (size_t)(n + 1), s));
+    if (n_remove) {
+        int* st = (int*)P->pinned;
+        memcpy(st, remove_idx, 4 * (size_t)n_remove);
+        LDSO_CUDA_OK(c, ldso_copy(c, P->cand, st, 4 * (size_t)n_remove, cudaMemcpyHostToDevice, s));
+        im_mark_kernel<<<(n_remove + 255) / 256, 256, 0, s>>>(n_remove, P->cand, P->keep);
+        c->launches++;
+    }
+    im_flag_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, P->host, P->status, drop_host, drop_oob, P->keep);
+    im_scan_kernel<<<1, 1024, 0, s>>>(n, P->keep, P->pos);
+    im_scatter_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, P->keep, P->pos, drop_host, pool_ptrs(P, false), pool_ptrs(P, true));
+    c->launches += 3;
+    LDSO_CUDA_OK(c, cudaGetLastError());
+    int* total = (int*)P->pinned + P->cap;
+    LDSO_CUDA_OK(c, ldso_copy(c, total, P->pos + n, 4, cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    std::swap(P->host, P->host2); std::swap(P->status, P->status2); std::swap(P->u, P->u2); std::swap(P->v, P->v2);
+    std::swap(P->color, P->color2); std::swap(P->weights, P->weights2); std::swap(P->gradH, P->gradH2);
+    std::swap(P->energyTH, P->energyTH2); std::swap(P->idmin, P->idmin2); std::swap(P->idmax, P->idmax2);
+    std::swap(P->quality, P->quality2); std::swap(P->lastUV, P->lastUV2); std::swap(P->interval, P->interval2);
+    P->n = *total;
+    *n_out = P->n;
+    return 0;
+}
+
+extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx, int n, const float* u, const float* v,
+                                        int* n_pool) {
+    ImmatureDev* P = pool(c);
+    if (!P) return -1;
+    LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && P->n + n <= P->cap && n_pool);
+    LDSO_REQUIRE(c, host_idx >= 0 && host_idx < LDSO_MAX_WINDOW && (n == 0 || (u && v)));
+    if (n > 0) {
+        float* st = (float*)P->pinned;
+        memcpy(st, u, 4 * (size_t)n); memcpy(st + n, v, 4 * (size_t)n);
+        LDSO_CUDA_OK(c, ldso_copy(c, P->cr, st, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        float eth = 8 * c->cfg.outlier_th;
+        eth *= c->cfg.overall_energy_th_weight * c->cfg.overall_energy_th_weight;
+        k6_create_kernel<<<(8 * n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, c->stream>>>(c->frame[slot], c->wG[0], n,
+                                                                                             c->cfg.outlier_th_sum_component, eth, P->cr);
+        im_append_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, P->n, host_idx, P->cr, pool_ptrs(P, false));
+        c->launches += 2;
+        LDSO_CUDA_OK(c, cudaGetLastError());
+        P->n += n;
+        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the pinned staging is reused by the next entry point
+    }
+    *n_pool = P->n;
     return 0;
 }

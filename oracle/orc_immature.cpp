@@ -358,3 +358,49 @@ extern "C" int orc_immature_activate(orc_ctx* c, int n_cand, const int* cand, in
     }
     return 0;
 }
+
+// device-resident pool maintenance of the GPU library, restated on the host vectors
+extern "C" int orc_immature_compact(orc_ctx* c, int drop_host, int drop_oob, int n_remove, const int* remove_idx, int* n_out) {
+    Pool& P = pool_of(c);
+    std::vector<char> rm(P.n, 0);
+    for (int i = 0; i < n_remove; i++) {
+        if (remove_idx[i] < 0 || remove_idx[i] >= P.n) return -2;
+        rm[remove_idx[i]] = 1;
+    }
+    int o = 0;
+    for (int i = 0; i < P.n; i++) {
+        if (rm[i] || (drop_host >= 0 && P.host[i] == drop_host) || (drop_oob && P.status[i] == 1)) continue;
+        P.host[o] = (drop_host >= 0 && P.host[i] > drop_host) ? P.host[i] - 1 : P.host[i];
+        P.status[o] = P.status[i]; P.u[o] = P.u[i]; P.v[o] = P.v[i]; P.energyTH[o] = P.energyTH[i];
+        P.idepth_min[o] = P.idepth_min[i]; P.idepth_max[o] = P.idepth_max[i]; P.quality[o] = P.quality[i];
+        P.lastInterval[o] = P.lastInterval[i]; P.lastUV[2 * o] = P.lastUV[2 * i]; P.lastUV[2 * o + 1] = P.lastUV[2 * i + 1];
+        for (int k = 0; k < 3; k++) P.gradH[3 * o + k] = P.gradH[3 * i + k];
+        for (int k = 0; k < 8; k++) { P.color[8 * o + k] = P.color[8 * i + k]; P.weights[8 * o + k] = P.weights[8 * i + k]; }
+        o++;
+    }
+    P.n = o;
+    *n_out = o;
+    return 0;
+}
+
+extern "C" int orc_immature_append(orc_ctx* c, int slot, int host_idx, int n, const float* u, const float* v, int* n_pool) {
+    Pool& P = pool_of(c);
+    std::vector<float> col(8 * (size_t)n), wgt(8 * (size_t)n), gh(3 * (size_t)n), eth(n);
+    if (n > 0) orc_immature_create(c, slot, n, u, v, col.data(), wgt.data(), gh.data(), eth.data());
+    const size_t N = (size_t)P.n + n;
+    P.host.resize(N); P.status.resize(N); P.u.resize(N); P.v.resize(N); P.energyTH.resize(N); P.idepth_min.resize(N);
+    P.idepth_max.resize(N); P.quality.resize(N); P.lastInterval.resize(N); P.lastUV.resize(2 * N); P.gradH.resize(3 * N);
+    P.color.resize(8 * N); P.weights.resize(8 * N);
+    for (int i = 0; i < n; i++) {
+        const int o = P.n + i;
+        P.host[o] = host_idx; P.u[o] = u[i]; P.v[o] = v[i]; P.energyTH[o] = eth[i];
+        P.status[o] = std::isfinite(eth[i]) ? 5 : 1;
+        P.idepth_min[o] = 0; P.idepth_max[o] = NAN; P.quality[o] = 10000; P.lastInterval[o] = 0;
+        P.lastUV[2 * o] = P.lastUV[2 * o + 1] = 0;
+        for (int k = 0; k < 3; k++) P.gradH[3 * o + k] = gh[3 * i + k];
+        for (int k = 0; k < 8; k++) { P.color[8 * o + k] = col[8 * i + k]; P.weights[8 * o + k] = wgt[8 * i + k]; }
+    }
+    P.n = (int)N;
+    *n_pool = P.n;
+    return 0;
+}

@@ -203,3 +203,22 @@ extern "C" int orc_select_make_maps(orc_ctx* c, int slot, float density, int rec
     *potential_io = pot;
     return 0;
 }
+
+// makeMaps + the pixel loop of FullSystem::makeNewTraces (src/frontend/FullSystem.cc:1440-1460)
+extern "C" int orc_select_points(orc_ctx* c, int slot, float density, int recursions_left, float th_factor, int* potential_io,
+                                 int border, int max_points, float* u_out, float* v_out, float* type_out, int* n_points) {
+    const int w = c->wG[0], h = c->hG[0];
+    std::vector<float> map((size_t)w * h);
+    int nsel = 0;
+    int rc = orc_select_make_maps(c, slot, density, recursions_left, th_factor, potential_io, map.data(), &nsel);
+    if (rc) return rc;
+    int n = 0;
+    for (int y = border; y < h - border; y++)
+        for (int x = border; x < w - border; x++) {
+            const float m = map[(size_t)y * w + x];
+            if (m == 0) continue;
+            if (n < max_points) { u_out[n] = (float)x; v_out[n] = (float)y; type_out[n] = m; n++; }
+        }
+    *n_points = n;
+    return 0;
+}

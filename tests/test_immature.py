@@ -135,3 +135,78 @@ def test_gpu_immature_edge_cases(oracle, gpu):
     assert np.array_equal(ca, cb)
     for key in ta:
         assert np.array_equal(ta[key], tb[key], equal_nan=True), key
+
+
+def _pool_scenario(ctx, S):
+    """create -> append (device-resident) -> trace -> compact -> trace again; returns everything the host can observe"""
+    nh = S["n_hosts"]
+    for i, f in enumerate(S["frames"]):
+        ctx.make_images(i, f[0])
+    z = np.zeros(0, np.float32)
+    ctx.immature_set(np.zeros(0, np.int32), z, z, np.zeros((0, 8)), np.zeros((0, 8)), np.zeros((0, 3)), z, z, z, z, np.zeros(0, np.int32))
+    sizes = []
+    for hi in range(nh):
+        m = S["host"] == hi
+        sizes.append(ctx.immature_append(hi, hi, S["u"][m], S["v"][m]))
+    out = dict(sizes=sizes)
+    KRKi, Kt, aff = S["tables"][0]
+    out["c0"] = ctx.immature_trace(nh, KRKi, Kt, aff)
+    out["t0"] = ctx.immature_get()
+    st = out["t0"]["status"]
+    remove = np.nonzero(st == GOOD)[0][::3].astype(np.int32)          # "activated" points
+    out["n1"] = ctx.immature_compact(drop_host=0, drop_oob=True, remove=remove)
+    out["t1"] = ctx.immature_get()
+    # the window slid by one: old host 1 is now host 0
+    KRKi2, Kt2, aff2 = S["tables"][1]
+    out["c2"] = ctx.immature_trace(nh + 1, KRKi2[1:], Kt2[1:], aff2[1:])
+    out["t2"] = ctx.immature_get()
+    keep = (S["host"] != 0) & (st != OOB)
+    keep[remove] = False
+    out["expect_keep"] = keep
+    return out
+
+
+def test_oracle_pool_compact_and_append(oracle):
+    S = util.immature_scene("small")
+    ctx = util.make_ctx(oracle, "small", n_frame_slots=8)
+    o = _pool_scenario(ctx, S)
+    assert o["sizes"][-1] == len(S["u"])
+    keep = o["expect_keep"]
+    assert o["n1"] == keep.sum() == len(o["t1"]["status"])
+    for key in ("idepth_min", "idepth_max", "quality", "status", "interval"):
+        assert np.array_equal(o["t1"][key], o["t0"][key][keep], equal_nan=True), key    # order preserved, fields carried over
+    assert o["c2"].sum() == o["n1"]
+
+
+@pytest.mark.gpu
+def test_gpu_pool_compact_and_append_parity(oracle, gpu):
+    S = util.immature_scene("small")
+    a = _pool_scenario(util.make_ctx(oracle, "small", n_frame_slots=8), S)
+    b = _pool_scenario(util.make_ctx(gpu, "small", n_frame_slots=8), S)
+    assert a["sizes"] == b["sizes"] and a["n1"] == b["n1"]
+    for k in ("c0", "c2"):
+        assert np.array_equal(a[k], b[k])
+    for k in ("t0", "t1", "t2"):
+        for key in a[k]:
+            assert np.array_equal(a[k][key], b[k][key], equal_nan=True), (k, key)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("calib", ["small", "c1", "c4"])
+def test_gpu_select_points_matches_map(oracle, gpu, calib):
+    """the compacted list equals np.nonzero of the map in row-major order, on both libraries"""
+    res = []
+    for api in (oracle, gpu):
+        c1 = util.make_ctx(api, calib); c2 = util.make_ctx(api, calib)
+        img = util.frames(calib)[0][0]
+        c1.make_images(0, img); c2.make_images(0, img)
+        m, n, pot_m = c1.select_make_maps(0, 1500.0, potential=3)
+        u, v, t, pot_l = c2.select_points(0, 1500.0, potential=3, border=5)
+        mm = m.copy(); mm[:5] = 0; mm[-5:] = 0; mm[:, :5] = 0; mm[:, -5:] = 0
+        ys, xs = np.nonzero(mm)
+        assert pot_m == pot_l
+        assert np.array_equal(u, xs.astype(np.float32)) and np.array_equal(v, ys.astype(np.float32))
+        assert np.array_equal(t, mm[ys, xs])
+        res.append((u, v, t))
+    for x, y in zip(res[0], res[1]):
+        assert np.array_equal(x, y)
