@@ -4,7 +4,7 @@
  * The reference (n-lalanne/LDSO) has no FFI layer: its boundary is the C++ class surface in
  * namespace ldso / ldso::internal that FullSystem calls.  Every entry point below names the reference
  * method it replaces (file:line relative to the reference tree).  The C++ shim classes in
- * include/ldso_shim.h keep the reference's class and method names and forward here.
+ * include/ldso_shim.hpp keep the reference's class and method names and forward here.
  *
  * Conventions
  *   - every function returns int: 0 = OK, <0 = CUDA/driver/usage failure (sticky, see
