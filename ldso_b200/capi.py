@@ -330,6 +330,15 @@ class Ctx:
         fd = np.ascontiguousarray(W["frame_delta_prior"], dtype=np.float64)
         self._call("window_set_adjoints", _dp(adH), _dp(adT), _fp(dl), _fp(cd), _dp(cp), _dp(fp_), _dp(fd))
 
+    def window_set_adjoints_only(self, adH, adT, W):
+        """setAdjointsF after a pose step; the delta / prior terms of W are re-sent unchanged"""
+        adH = np.ascontiguousarray(adH, dtype=np.float64); adT = np.ascontiguousarray(adT, dtype=np.float64)
+        dl, cd = f32(W["adHTdelta"]), f32(W["c_delta"])
+        cp = np.ascontiguousarray(W["c_prior"], dtype=np.float64)
+        fp_ = np.ascontiguousarray(W["frame_prior"], dtype=np.float64)
+        fd = np.ascontiguousarray(W["frame_delta_prior"], dtype=np.float64)
+        self._call("window_set_adjoints", _dp(adH), _dp(adT), _fp(dl), _fp(cd), _dp(cp), _dp(fp_), _dp(fd))
+
     def window_set_idepth(self, idepth, idepth_zero):
         a, b = f32(idepth), f32(idepth_zero)
         self._call("window_set_idepth", _fp(a), _fp(b))
