@@ -40,6 +40,15 @@ WORKLOAD = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level py
             "(K2), PixelSelector::makeMaps (A2) + ImmaturePoint construction (K6) for the new keyframe. Keyframe cadence "
             "and the window contents (ground-truth poses/depths + noise) are fixed by the harness, not by the reference's "
             "FullSystem heuristics" % (N_POINTS, WINDOW, KF_EVERY, N_ACTIVATE, BA_ITS))
+WORKLOAD_ODOMETRY = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level pyramid, %d desired active points, %d desired "
+                     "immature points per keyframe, %d-keyframe window, closed loop. One step = one frame through the reference's "
+                     "FullSystem::addActiveFrame flow (restated in ldso_b200/odometry.py over the C ABI): makeImages (K1), "
+                     "trackNewCoarse with motion hypotheses (K3/K4 LM), keyframe decision by optical flow, traceNewCoarse (K5); on a "
+                     "keyframe: frame selection for dropping, new residuals, activatePointsMT (K6), optimize = linearizeAll + <= %d x "
+                     "(accumulate K8/K9, solve H1, resubstitute K10, step, linearizeAll K7) + fix pass, removal of OOB/outlier points, "
+                     "setCoarseTrackingRef (K2), makeNewTraces (A2 + K6). Bootstrapped from the ground-truth depth of frame 0 "
+                     "(CoarseInitializer is SURVEY 8f N1); no marginalisation prior (points / frames leaving the window are dropped)"
+                     % (N_POINTS, N_IMMATURE, WINDOW, BA_ITS))
 # algorithmic bytes per unit
 BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 5000.0}
 
@@ -140,6 +149,7 @@ class Sequence:
         self.last_rel = IDENT.copy()
         self.results = []
         self.kf_log = []
+        self.first_step = PRE + 1
 
     def tick(self, name, t0):
         """host wall-clock per phase (each phase ends with its results on the host), for the breakdown in the JSON line"""
@@ -280,6 +290,56 @@ class Sequence:
         return worst
 
 
+class ClosedLoop:
+    """The default workload: the reference's own per-frame state machine (ldso_b200/odometry.py restates the control flow of
+    FullSystem::addActiveFrame: track, trace, keyframe decision, activation, window BA, frame dropping, new tracking
+    reference, new immature points) on the synthetic sequence, bootstrapped from the ground-truth depth of frame 0.
+    Same interface as Sequence so the timing code is shared."""
+
+    PRIME = 24          # frames after the bootstrap frame that are run before the warm-up steps (the first keyframe falls here)
+
+    def __init__(self, api, seed, n_steps, device=0):
+        from ldso_b200 import odometry
+        self.odometry = odometry
+        self.frames, self.depths, self.poses = rendered_sequence(seed, 1 + self.PRIME + n_steps)
+        self.od = odometry.Odometry(api, CALIB, desired_points=N_POINTS, desired_immature=N_IMMATURE, max_frames=WINDOW,
+                                    ba_iterations=BA_ITS, device=device)
+        self.ctx = self.od.ctx
+        self.first_step = 1 + self.PRIME
+
+    @property
+    def phase(self):
+        return self.od.phase
+
+    @phase.setter
+    def phase(self, v):
+        self.od.phase = v
+
+    @property
+    def kf_log(self):
+        return [l for l in self.od.log if l.get("kf")]
+
+    def prime(self):
+        R0, t0 = self.poses[0]
+        self.od.add_frame(self.frames[0], gt_depth=self.depths[0], gt_w2c=(R0.T, -R0.T @ t0))
+        for i in range(1, self.first_step):
+            self.od.add_frame(self.frames[i])
+
+    def step(self, f, dev_ptr=None):
+        return self.od.add_frame(self.frames[f], dev_ptr=dev_ptr)
+
+    def trajectory_error(self):
+        ids = sorted(self.od.poses)
+        est = np.array([-self.od.poses[i][0].T @ self.od.poses[i][1] for i in ids])
+        gt = np.array([self.poses[i][1] for i in ids])
+        ate, scale = self.odometry.ate_rmse(est, gt)
+        return dict(ate_rmse_m=ate, sim3_scale=scale, path_m=float(np.linalg.norm(np.diff(gt, axis=0), axis=1).sum()),
+                    max_abs_m=float(np.abs(est - gt).max()), frames=len(ids), lost=sum(1 for l in self.od.log if l.get("lost")))
+
+    def gt_error(self):
+        return self.trajectory_error()["max_abs_m"]
+
+
 def run_sequence_timed(seq, steps, warmup, use_dev, flush=None, torch=None):
     """W untimed + K timed steps starting at frame PRE+1.  Returns (per-step seconds, launches, h2d bytes, d2h bytes)
     of the timed region."""
@@ -287,7 +347,7 @@ def run_sequence_timed(seq, steps, warmup, use_dev, flush=None, torch=None):
     if use_dev:
         dev_imgs = [torch.from_numpy(f).cuda() for f in seq.frames]
         torch.cuda.synchronize()
-    i = PRE + 1
+    i = getattr(seq, "first_step", PRE + 1)
     for _ in range(warmup):
         seq.step(i, dev_imgs[i].data_ptr() if use_dev else None)
         i += 1
@@ -331,7 +391,7 @@ def aggregate_fps(world, steps, t_max):
     return world * steps / t_max
 
 
-def cpu_run(steps, warmup, seed, fast=True):
+def cpu_run(WL, steps, warmup, seed, fast=True):
     """The oracle restatement of the reference CPU path on this box's host cores (bench's cpu_baseline / reference
     arm).  Tracking and tracing are single-threaded in the reference; linearizeAll, the Hessian accumulation and point
     activation use its 6 worker threads (IndexThreadReduce, NUM_THREADS = 6), so both 6 and 1 oracle threads are tried
@@ -344,17 +404,17 @@ def cpu_run(steps, warmup, seed, fast=True):
     cand = [6, 1] if (os.cpu_count() or 1) >= 7 else [1]
     for t in cand:
         os.environ["ORC_THREADS"] = str(t)
-        seq = Sequence(api, seed, 2 * KF_EVERY)
+        pn = 30 if WL is ClosedLoop else KF_EVERY
+        seq = WL(api, seed, 2 * pn)
         seq.prime()
-        probe[t] = sum(run_sequence_timed(seq, KF_EVERY, KF_EVERY, use_dev=False)[0])
+        probe[t] = sum(run_sequence_timed(seq, pn, pn, use_dev=False)[0]) / pn
         seq.ctx.close()
     best = min(probe, key=probe.get)
     os.environ["ORC_THREADS"] = str(best)
-    seq = Sequence(api, seed, warmup + steps)
+    seq = WL(api, seed, warmup + steps)
     seq.prime()
     times = run_sequence_timed(seq, steps, warmup, use_dev=False)[0]
-    note = "oracle worker threads tried on %d frames: %s" % (KF_EVERY, ", ".join("%d -> %.1f ms/frame" % (t, 1e3 * v / KF_EVERY)
-                                                                                 for t, v in probe.items()))
+    note = "oracle worker threads tried on a short sample: %s" % ", ".join("%d -> %.1f ms/frame" % (t, 1e3 * v) for t, v in probe.items())
     return seq, times, best, note
 
 
@@ -367,32 +427,42 @@ BYTES_PER_UNIT["k5"] = 128.0
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=42)
-    ap.add_argument("--warmup", type=int, default=6)
+    ap.add_argument("--steps", type=int, default=None, help="timed frames (default 120 closed loop / 42 cadence)")
+    ap.add_argument("--warmup", type=int, default=None, help="untimed frames before them (default 30 / 6)")
+    ap.add_argument("--workload", default="odometry", choices=["odometry", "cadence"],
+                    help="odometry: closed loop through the reference's per-frame flow (default); cadence: fixed keyframe every "
+                         "6 frames on harness-built windows (heavier mapping load)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-steps", type=int, default=18, help="frames of the bounded cpu_baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=None, help="frames of the bounded cpu_baseline sample (default 90 / 18)")
     args = ap.parse_args()
     rank, local_rank, world = rank_info()
-    steps, warmup = args.steps, max(args.warmup, 0)
+    odo = args.workload == "odometry"
+    WL = ClosedLoop if odo else Sequence
+    steps = args.steps if args.steps is not None else (120 if odo else 42)
+    warmup = max(args.warmup if args.warmup is not None else (30 if odo else 6), 0)
+    cpu_steps = args.cpu_steps if args.cpu_steps is not None else (90 if odo else 18)
+    cpu_warm = 30 if odo else KF_EVERY
     base = {"metric": "tracked frames/s (whole job, all sequences)", "unit": "frames/s", "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic (procedural box room, seeded, uint8-quantised)",
-            "config": {"workload": WORKLOAD, "sequences": args.gpus, "parallelism": "independent sequences, no collective",
+            "config": {"workload": WORKLOAD_ODOMETRY if odo else WORKLOAD, "sequences": args.gpus, "parallelism": "independent sequences, no collective",
                        "l2": "flushed with a 256 MiB write between timed steps"}}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        seq, times, threads, note = cpu_run(steps, warmup, 1001)
+        seq, times, threads, note = cpu_run(WL, steps, warmup, 1001)
         fps = steps / sum(times)
         line = dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps, n_gpus=args.gpus,
                     cpu_baseline={"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
                                   "sample": "%d frames (%d keyframes) of the same sequence, oracle restatement (-O3 "
                                             "-march=x86-64-v3 -fopenmp); %s; host has %d cores"
-                                            % (steps, len(seq.kf_log), note, os.cpu_count())},
+                                            % (steps, sum(1 for k in seq.kf_log if k["frame"] >= seq.first_step + warmup), note, os.cpu_count())},
                     e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq.phase.items()},
                     gt_max_translation_error_m=seq.gt_error(), keyframes=seq.kf_log[-2:])
+        if odo:
+            line["trajectory"] = seq.trajectory_error()
         line["config"] = dict(base["config"], l2="n/a (CPU)")
         print(json.dumps(line))
         return
@@ -417,14 +487,15 @@ def main():
     # three passes over the same sequence, one context alive at a time: device-resident input (value), host input
     # through the C ABI (e2e), and the per-kernel CUDA-event profile (roofline)
     with ClockSampler(local_rank) as clk:
-        seq = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+        seq = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
         seq.prime()
         barrier()
         times, launches, _, _ = run_sequence_timed(seq, steps, warmup, use_dev=True, flush=flush, torch=torch)
         barrier()
         gt_err, kf_tail = seq.gt_error(), seq.kf_log[-2:]
+        traj = seq.trajectory_error() if odo else None
         seq.ctx.close()
-        seq_e2e = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+        seq_e2e = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
         seq_e2e.prime()
         barrier()
         times_e2e, _, h2d, d2h = run_sequence_timed(seq_e2e, steps, warmup, use_dev=False, flush=flush)
@@ -432,7 +503,7 @@ def main():
         seq_e2e.ctx.close()
     t_dev, t_e2e = max_over_ranks([sum(times), sum(times_e2e)], world, dist, torch, "cuda")
 
-    seq_p = Sequence(gpu, rank_seed(rank), warmup + steps, device=local_rank)
+    seq_p = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
     seq_p.prime()
     seq_p.ctx.sync()
     seq_p.ctx.profile_enable(True)
@@ -470,13 +541,18 @@ def main():
                 kernels=kernels,
                 host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
                 gt_max_translation_error_m=gt_err, keyframes=kf_tail)
+    if odo:
+        line["trajectory"] = traj
+        line["keyframes_in_timed_region"] = sum(1 for k in seq_e2e.kf_log if k["frame"] >= seq_e2e.first_step + warmup)
     if args.gpus == 1:
-        cseq, ctimes, cthreads, cnote = cpu_run(min(args.cpu_steps, steps), KF_EVERY, 1001)
+        cseq, ctimes, cthreads, cnote = cpu_run(WL, min(cpu_steps, steps), cpu_warm, 1001)
         n = len(ctimes)
         line["cpu_baseline"] = {"value": n / sum(ctimes), "unit": "frames/s", "cores": cthreads, "kind": "port",
                                 "sample": "%d frames (%d keyframes) of the same sequence and workload through the oracle (g++ -O3 "
                                           "-march=x86-64-v3 -fopenmp); %s; host has %d cores"
-                                          % (n, sum(1 for k in cseq.kf_log if k["frame"] > PRE + KF_EVERY), cnote, os.cpu_count())}
+                                          % (n, sum(1 for k in cseq.kf_log if k["frame"] >= cseq.first_step + cpu_warm), cnote, os.cpu_count())}
+        if odo:
+            line["cpu_baseline"]["trajectory"] = cseq.trajectory_error()
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -12,6 +12,8 @@ Deliberate simplifications (host-side orchestration is outside SURVEY section 8a
     prior on the oldest keyframe; consequently Jacobians are evaluated at the current state (no FEJ, no linearised
     residuals) and steps are always accepted (setting_forceAceptStep = true in the reference, Setting.cc);
   * activation spacing uses an occupancy grid at level-1 resolution instead of CoarseDistanceMap's BFS (8f N2)."""
+import time
+
 import numpy as np
 
 from . import window_host as wh
@@ -69,11 +71,17 @@ class Odometry:
         self.ref_id = None
         self.first_rmse = -1.0
         self.log = []
+        self.phase = {}
         self.n_frames_seen = 0
 
     # ---- small helpers -------------------------------------------------------------------------------
     def pos_of(self, fid):
         return [f["id"] for f in self.frames].index(fid)
+
+    def positions(self, host_ids):
+        """window position of each host frame id (keyframe ids are increasing along self.frames)"""
+        ids = np.array([f["id"] for f in self.frames], np.int64)
+        return np.searchsorted(ids, np.asarray(host_ids, np.int64))
 
     def host_tables(self, w2c_new, aff_new=(0.0, 0.0)):
         """hostToFrame KRKi / Kt / affine per keyframe of the window (FullSystem.cc:1171-1176)"""
@@ -88,7 +96,7 @@ class Odometry:
 
     def upload_immature(self):
         I = self.I
-        host_pos = np.array([self.pos_of(h) for h in I["host"]], np.int32) if len(I["host"]) else np.zeros(0, np.int32)
+        host_pos = self.positions(I["host"]).astype(np.int32)
         self.ctx.immature_set(host_pos, I["u"], I["v"], I["color"], I["weights"], I["grad_h"], I["energy_th"], I["idepth_min"],
                               I["idepth_max"], I["quality"], I["status"])
 
@@ -115,11 +123,22 @@ class Odometry:
         return k
 
     # ---- per frame (FullSystem::addActiveFrame, :78-187) ---------------------------------------------
-    def add_frame(self, img, gt_depth=None, gt_w2c=None):
+    def tick(self, name, t0):
+        t1 = time.perf_counter()
+        self.phase[name] = self.phase.get(name, 0.0) + (t1 - t0)
+        return t1
+
+    def add_frame(self, img, gt_depth=None, gt_w2c=None, dev_ptr=None):
+        """img: host float image; dev_ptr: optional device pointer of the same image (skips the upload)"""
         fid = self.n_frames_seen
         self.n_frames_seen += 1
         slot = self.free_slots.pop()
-        self.ctx.make_images(slot, img)
+        t = time.perf_counter()
+        if dev_ptr is None:
+            self.ctx.make_images(slot, img)
+        else:
+            self.ctx.make_images_dev(slot, dev_ptr)
+        t = self.tick("K1 makeImages", t)
         if not self.frames:
             w2c = gt_w2c if gt_w2c is not None else (np.eye(3), np.zeros(3))
             f = dict(id=fid, slot=slot, w2c=(w2c[0].copy(), w2c[1].copy()), aff=(0.0, 0.0))
@@ -128,6 +147,7 @@ class Odometry:
             return dict(kf=True, ok=True)
         ref = self.frames[-1]
         ok, rel, aff, tr = self.track(slot)
+        t = self.tick("K3/K4 trackNewestCoarse", t)
         if not ok:
             self.free_slots.append(slot)
             self.log.append(dict(frame=fid, lost=True))
@@ -148,10 +168,12 @@ class Odometry:
         if self.I is not None and len(self.I["host"]):
             KRKi, Kt, affs = self.host_tables(w2c, aff)
             counts = self.ctx.immature_trace(slot, KRKi, Kt, affs)
+        t = self.tick("K5 traceNewCoarse", t)
         self.log.append(dict(frame=fid, kf=bool(need_kf), score=float(score), res=res0, iters=tr["iters"].tolist(),
                              trace=None if counts is None else counts.tolist()))
         if need_kf:
             self.make_keyframe(dict(id=fid, slot=slot, w2c=w2c, aff=(float(aff[0]), float(aff[1]))))
+            t = self.tick("KF makeKeyFrame total (Python orchestration included)", t)
         else:
             self.free_slots.append(slot)
         return dict(kf=bool(need_kf), ok=True)
@@ -202,18 +224,22 @@ class Odometry:
 
     # ---- keyframe (FullSystem::makeKeyFrame, :485-699) -------------------------------------------------
     def make_keyframe(self, f):
+        t = time.perf_counter()
         self.sync_immature()
         drop = self.flag_frames_for_marginalization(f)
         self.frames.append(f)
         npts = len(self.P["host"])
         self.res = np.concatenate([self.res, np.full((npts, 1), IN, np.int8)], axis=1)     # new residuals into f (:549-560)
+        t = self.tick("KF  pool sync + frame selection", t)
         n_act = self.activate_points()
+        t = self.tick("KF  activatePointsMT (K6 + host candidate spacing)", t)
         rmse = self.optimize()
+        t = self.tick("KF  optimize (K7-K10, H1 + host pose tables)", t)
         st_newest = self.res[:, -1].copy()
         st_prev = self.res[:, -2].copy() if self.res.shape[1] >= 2 else st_newest
         self.res[self.res != IN] = -1                                      # linearizeAll(true): non-IN residuals are dropped
         # flagPointsForRemoval (:1356-1424) without the marginalisation branch: isOOB points and points of the leaving frame go
-        host_pos = np.array([self.pos_of(h) for h in self.P["host"]], np.int64)
+        host_pos = self.positions(self.P["host"])
         kill = (self.P["idepth"] < 0) | ((self.res >= 0).sum(1) == 0)
         kill |= (st_newest == OOB) | ((st_newest == OUTLIER) & (st_prev == OUTLIER))
         for d in drop:
@@ -228,8 +254,11 @@ class Odometry:
                 self.I = {k: a[m] for k, a in self.I.items()}
         self.keep_points((self.res >= 0).sum(1) > 0)
         # setCoarseTrackingRef on the new keyframe (:614-621, CoarseTracker.cc:347-538)
+        t = self.tick("KF  point / frame removal", t)
         self.set_tracking_ref()
+        t = self.tick("KF  setCoarseTrackingRef (K2)", t)
         n_new = self.make_new_traces(f)
+        t = self.tick("KF  makeNewTraces (A2 + K6 ctor)", t)
         self.log[-1].update(dict(points=int(len(self.P["host"])), activated=int(n_act), immature=int(len(self.I["host"])),
                                  window=[fr["id"] for fr in self.frames], rmse=float(rmse), new_immature=int(n_new)))
 
@@ -307,17 +336,19 @@ class Odometry:
         pc = project(I["host"], I["u"].astype(np.float64), I["v"].astype(np.float64), 0.5 * idm.astype(np.float64))
         cand = []
         rad = 8
-        for k in np.nonzero(can)[0]:
-            x, y = pc[k]
-            if not (x > 0 and y > 0 and x < w1 and y < h1):
-                delete[k] = True
-                continue
-            xi, yi = int(x), int(y)
-            if dist[yi, xi] + (x - np.floor(x)) > self.min_act_dist * I["type"][k]:
+        ky, kx = np.mgrid[-rad:rad + 1, -rad:rad + 1]
+        kern = np.maximum(np.abs(ky), np.abs(kx)).astype(np.float32)       # chessboard distance to the accepted pixel
+        fx = pc[:, 0] - np.floor(pc[:, 0])
+        inb = (pc[:, 0] > 0) & (pc[:, 1] > 0) & (pc[:, 0] < w1) & (pc[:, 1] < h1)
+        delete |= can & ~inb
+        thr = self.min_act_dist * I["type"]
+        for k in np.nonzero(can & inb)[0]:                                 # order-dependent (addIntoDistFinal), as in the reference
+            xi, yi = int(pc[k, 0]), int(pc[k, 1])
+            if dist[yi, xi] + fx[k] > thr[k]:
                 cand.append(k)
                 y0, y1, x0, x1 = max(0, yi - rad), min(h1, yi + rad + 1), max(0, xi - rad), min(w1, xi + rad + 1)
-                yy, xx = np.mgrid[y0:y1, x0:x1]
-                np.minimum(dist[y0:y1, x0:x1], np.maximum(np.abs(yy - yi), np.abs(xx - xi)), out=dist[y0:y1, x0:x1])
+                sub = dist[y0:y1, x0:x1]
+                np.minimum(sub, kern[y0 - yi + rad:y1 - yi + rad, x0 - xi + rad:x1 - xi + rad], out=sub)
         n_ok = 0
         if cand:
             cand = np.array(cand, np.int32)
@@ -357,7 +388,7 @@ class Odometry:
 
     def optimize(self):
         ctx, n = self.ctx, len(self.frames)
-        host_pos = np.array([self.pos_of(h) for h in self.P["host"]], np.int64)
+        host_pos = self.positions(self.P["host"])
         order = np.argsort(host_pos, kind="stable")                          # allPoints order: contiguous per host frame
         self.P = {k: a[order] for k, a in self.P.items()}
         self.res = self.res[order]

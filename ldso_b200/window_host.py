@@ -41,6 +41,17 @@ def from_to_vec_exposure(expF, expT, g2F, g2T):
     return np.float32(a), np.float32(b)
 
 
+def _pairs(w2c):
+    """T_target * T_host^-1 for every pair, as stacks indexed [target][host] (float64)"""
+    R = np.stack([T[0] for T in w2c]).astype(np.float64)
+    t = np.stack([T[1] for T in w2c]).astype(np.float64)
+    Ri = R.transpose(0, 2, 1)
+    ti = -(Ri @ t[:, :, None])[:, :, 0]
+    Rl = R[:, None] @ Ri[None, :]                       # [t][h]
+    tl = (R[:, None] @ ti[None, :, :, None])[..., 0] + t[:, None]
+    return Rl, tl
+
+
 def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
     """FrameFramePrecalc::Set for every (host, target) pair (src/internal/FrameFramePrecalc.cc:6-35).
     w2c_eval / w2c: lists of (R, t) world-to-camera at the FEJ evaluation point / current state."""
@@ -48,39 +59,43 @@ def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
     fx, fy, cx, cy = [np.float32(c) for c in calib]
     K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=np.float32)
     Ki = np.linalg.inv(K.astype(np.float64)).astype(np.float32)
-    out = np.zeros((n * n, PRECALC_STRIDE), dtype=np.float32)
+    R0, t0 = _pairs(w2c_eval)
+    R, tt = _pairs(w2c)
+    R0f, t0f, Rf, tf = R0.astype(np.float32), t0.astype(np.float32), R.astype(np.float32), tt.astype(np.float32)
+    KRKi = (K @ Rf @ Ki).astype(np.float32)
+    Kt = (K @ tf[..., None])[..., 0].astype(np.float32)
+    out = np.zeros((n, n, PRECALC_STRIDE), dtype=np.float32)      # [t][h] == flat index h + n * t
+    out[..., 0:9] = R0f.reshape(n, n, 9); out[..., 9:12] = t0f
+    out[..., 12:21] = KRKi.reshape(n, n, 9); out[..., 21:24] = Kt
+    out[..., 27:36] = Rf.reshape(n, n, 9); out[..., 36:39] = tf
+    out[..., 39] = np.linalg.norm(tt, axis=-1).astype(np.float32)
     for h in range(n):
         for t in range(n):
-            l0 = se3_mul(w2c_eval[t], se3_inv(w2c_eval[h]))
-            l = se3_mul(w2c[t], se3_inv(w2c[h]))
-            R0, t0 = l0[0].astype(np.float32), l0[1].astype(np.float32)
-            R, tt = l[0].astype(np.float32), l[1].astype(np.float32)
-            KRKi = (K @ R @ Ki).astype(np.float32)
-            Kt = (K @ tt).astype(np.float32)
             a, b = from_to_vec_exposure(exposure[h], exposure[t], aff[h], aff[t])
-            row = out[h + n * t]
-            row[0:9] = R0.reshape(-1); row[9:12] = t0
-            row[12:21] = KRKi.reshape(-1); row[21:24] = Kt
-            row[24] = a; row[25] = b; row[26] = np.float32(aff0[h][1])
-            row[27:36] = R.reshape(-1); row[36:39] = tt; row[39] = np.float32(np.linalg.norm(l[1]))
-    return out
+            out[t, h, 24] = a; out[t, h, 25] = b; out[t, h, 26] = np.float32(aff0[h][1])
+    return out.reshape(n * n, PRECALC_STRIDE)
 
 
 def adjoints(w2c_eval, aff0, exposure):
     """EnergyFunctional::setAdjointsF (src/internal/OptimizationBackend/EnergyFunctional.cc:551-609)"""
     n = len(w2c_eval)
-    adH = np.zeros((n * n, 8, 8)); adT = np.zeros((n * n, 8, 8))
     scale = np.array([SCALE_XI_TRANS] * 3 + [SCALE_XI_ROT] * 3 + [SCALE_A, SCALE_B])
+    Rl, tl = _pairs(w2c_eval)                                     # [t][h]
+    H = np.zeros((n, n, 3, 3))
+    H[..., 0, 1] = -tl[..., 2]; H[..., 0, 2] = tl[..., 1]; H[..., 1, 0] = tl[..., 2]
+    H[..., 1, 2] = -tl[..., 0]; H[..., 2, 0] = -tl[..., 1]; H[..., 2, 1] = tl[..., 0]
+    A = np.zeros((n, n, 6, 6))
+    A[..., :3, :3] = Rl; A[..., :3, 3:] = H @ Rl; A[..., 3:, 3:] = Rl
+    adH = np.zeros((n, n, 8, 8)); adT = np.zeros((n, n, 8, 8))
+    adH[..., 6, 6] = 1; adH[..., 7, 7] = 1
+    adT[..., np.arange(8), np.arange(8)] = 1
+    adH[..., :6, :6] = -A.transpose(0, 1, 3, 2)
     for h in range(n):
         for t in range(n):
-            h2t = se3_mul(w2c_eval[t], se3_inv(w2c_eval[h]))
-            AH = np.eye(8); AT = np.eye(8)
-            AH[:6, :6] = -se3_adj(h2t).T
             a, _ = from_to_vec_exposure(exposure[h], exposure[t], aff0[h], aff0[t])
-            AT[6, 6] = -a; AH[6, 6] = a; AT[7, 7] = -1; AH[7, 7] = a
-            AH *= scale[:, None]; AT *= scale[:, None]
-            adH[h + n * t] = AH; adT[h + n * t] = AT
-    return adH, adT
+            adT[t, h, 6, 6] = -a; adH[t, h, 6, 6] = a; adT[t, h, 7, 7] = -1; adH[t, h, 7, 7] = a
+    adH *= scale[:, None]; adT *= scale[:, None]
+    return adH.reshape(n * n, 8, 8), adT.reshape(n * n, 8, 8)
 
 
 def ad_ht_delta(adH, adT, state_minus_zero):
