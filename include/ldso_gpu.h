@@ -274,6 +274,29 @@ int ldso_gpu_window_solve(ldso_gpu_ctx* ctx, int iteration, double lambda, const
 /* ---- K10: EnergyFunctional::resubstituteF_MT / resubstituteFPt (EnergyFunctional.cc:611-667): per-point step */
 int ldso_gpu_window_resubstitute(ldso_gpu_ctx* ctx, const double* x, float lambda, float* step_out);
 
+/* ---- marginalisation (EnergyFunctional.cc:109-262) and the energies the step acceptance test reads (:473-497, :751-806)
+ *
+ * marginalizePointsF (:205-262): marg[np] != 0 marks the points whose status is MARGINALIZED.  Their prior is multiplied
+ * by idepth_fix_prior_marg_fac (setting_idepthFixPriorMargFac = 600^2), AccumulatedTopHessianSSE::addPoint<2>
+ * (AccumulatedTopHessian.cc:9-118, resApprox = res_toZeroF) and AccumulatedSCHessianSSE::addPoint(p, false) run over
+ * them, both accumulators are stitched without priors and H = M - Msc, b = Mb - Mbsc are returned ((8n+4)^2, 8n+4).
+ * The caller keeps HM,bM on the host and adds marg_weight_fac * H, b (setting_margWeightFac = 0.25) — with the default
+ * solver mode no orthogonalisation happens here.  n_res = residuals that went in (resInM +=).  As removePoint does,
+ * the residuals of those points are inactive afterwards. */
+int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* ctx, const unsigned char* marg, float idepth_fix_prior_marg_fac,
+                                       double* H, double* b, int* n_res);
+/* marginalizeFrame (:109-191), the dense part (H1, host code): moves frame idx (0-based window position, n frames) to
+ * the end of HM,bM ((8n+4)^2, 8n+4), adds its prior / prior*delta_prior, takes the diagonally scaled Schur complement
+ * with util::MatrixInverter::invertPosDef (src/util/MatrixInverter.cc:31-50, SVD form) of the 8x8 block and
+ * symmetrises.  HM_out,bM_out: (8(n-1)+4)^2, 8(n-1)+4.  Needs no window state. */
+int ldso_gpu_window_marginalize_frame(ldso_gpu_ctx* ctx, int n, int idx, const double* HM, const double* bM,
+                                      const double prior[8], const double delta_prior[8], double* HM_out, double* bM_out);
+/* calcLEnergyF_MT (:481-497, calcLEnergyPt :751-806) and calcMEnergyF (:473-479).  energy[0] = linearised energy
+ * (frame priors + calibration prior + sum over linearised active residuals of (2 res_toZeroF + J delta) . J delta +
+ * per-point deltaF^2 priorF), energy[1] = delta . (2 bM + HM delta).  Uses the adjoint / delta tables of
+ * ldso_gpu_window_set_adjoints and the idepths of set_points / set_idepth. */
+int ldso_gpu_window_calc_energy(ldso_gpu_ctx* ctx, const double* HM, const double* bM, const double* delta, double energy[2]);
+
 /* read-backs (host mirrors of public members other reference code reads directly) */
 /* what: 0 J [n][72], 1 res_toZeroF [n][8], 2 JpJdF [n][8], 3 centerProjectedTo [n][3],
  *       4 state_NewEnergy, 5 state_NewEnergyWithOutlier, 6 state_energy  (float each) */

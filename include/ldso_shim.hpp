@@ -65,6 +65,9 @@ int LDSO_API(window_accumulate)(LDSO_SHIM_CTX*, double*, double*, double*, doubl
 int LDSO_API(window_solve)(LDSO_SHIM_CTX*, int, double, const double*, const double*, const double*, const double*, const double*,
                            const double*, const double*, const double*, const double*, const double*, int, double*);
 int LDSO_API(window_resubstitute)(LDSO_SHIM_CTX*, const double*, float, float*);
+int LDSO_API(window_marginalize_points)(LDSO_SHIM_CTX*, const unsigned char*, float, double*, double*, int*);
+int LDSO_API(window_marginalize_frame)(LDSO_SHIM_CTX*, int, int, const double*, const double*, const double*, const double*, double*, double*);
+int LDSO_API(window_calc_energy)(LDSO_SHIM_CTX*, const double*, const double*, const double*, double*);
 }
 #endif
 
@@ -282,6 +285,34 @@ public:
         c.check(LDSO_API(window_resubstitute)(c.h, lastX.data(), lambda, step.data()));
     }
     void setIdepth(Context& c, const float* idepth, const float* idepth_zero) { c.check(LDSO_API(window_set_idepth)(c.h, idepth, idepth_zero)); }
+    // void marginalizePointsF() (EnergyFunctional.cc:205-262): HM += margWeightFac * (M - Msc), bM likewise; HM,bM are the caller's
+    // dim() x dim() / dim() prior (the reference keeps them as members); marg[nPoints] marks Point::PointStatus::MARGINALIZED
+    int resInM = 0;
+    void marginalizePointsF(Context& c, const unsigned char* marg, std::vector<double>& HM, std::vector<double>& bM,
+                            float idepthFixPriorMargFac = 600.f * 600.f, double margWeightFac = 0.5 * 0.5) {
+        const size_t D = dim();
+        std::vector<double> H(D * D), b(D);
+        int nres = 0;
+        c.check(LDSO_API(window_marginalize_points)(c.h, marg, idepthFixPriorMargFac, H.data(), b.data(), &nres));
+        resInM += nres;
+        for (size_t i = 0; i < D * D; i++) HM[i] += margWeightFac * H[i];
+        for (size_t i = 0; i < D; i++) bM[i] += margWeightFac * b[i];
+    }
+    // void marginalizeFrame(shared_ptr<FrameHessian> fh) (:109-191): fh->idx = idx, fh->prior / fh->delta_prior; shrinks HM,bM
+    void marginalizeFrame(Context& c, int idx, const double prior[8], const double deltaPrior[8], std::vector<double>& HM,
+                          std::vector<double>& bM) {
+        const size_t Dn = dim() - 8;
+        std::vector<double> Ho(Dn * Dn), bo(Dn);
+        c.check(LDSO_API(window_marginalize_frame)(c.h, nFrames, idx, HM.data(), bM.data(), prior, deltaPrior, Ho.data(), bo.data()));
+        HM.swap(Ho); bM.swap(bo);
+        nFrames--;
+    }
+    // double calcLEnergyF_MT() / double calcMEnergyF() (:473-497)
+    void calcEnergies(Context& c, const double* HM, const double* bM, const double* delta, double& LEnergy, double& MEnergy) {
+        double e[2];
+        c.check(LDSO_API(window_calc_energy)(c.h, HM, bM, delta, e));
+        LEnergy = e[0]; MEnergy = e[1];
+    }
 };
 
 }  // namespace ldso_b200

@@ -367,6 +367,33 @@ class Ctx:
         self._call("window_accumulate", _dp(Hs[0]), _dp(bs[0]), _dp(Hs[1]), _dp(bs[1]), _dp(Hs[2]), _dp(bs[2]), _ip(cnt))
         return dict(HA=Hs[0], bA=bs[0], HL=Hs[1], bL=bs[1], Hsc=Hs[2], bsc=bs[2], counts=cnt)
 
+    def window_marginalize_points(self, marg, fac=600.0 * 600.0):
+        """EnergyFunctional::marginalizePointsF: returns (H, b, n_res) with H = M - Msc of the masked points"""
+        D = 8 * self.win_n + 4
+        m = np.ascontiguousarray(marg, dtype=np.uint8)
+        assert len(m) == self.win_np
+        H, b, nres = np.zeros((D, D)), np.zeros(D), C.c_int(0)
+        self._call("window_marginalize_points", m.ctypes.data_as(C.c_void_p), C.c_float(fac), _dp(H), _dp(b), C.byref(nres))
+        return H, b, nres.value
+
+    def window_marginalize_frame(self, n, idx, HM, bM, prior, delta_prior):
+        """EnergyFunctional::marginalizeFrame (dense part): returns (HM', bM') of dimension 8(n-1)+4"""
+        c64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        HM, bM, prior, delta_prior = c64(HM), c64(bM), c64(prior), c64(delta_prior)
+        D = 8 * n + 4
+        assert HM.shape == (D, D) and bM.shape == (D,)
+        Ho, bo = np.zeros((D - 8, D - 8)), np.zeros(D - 8)
+        self._call("window_marginalize_frame", C.c_int(n), C.c_int(idx), _dp(HM), _dp(bM), _dp(prior), _dp(delta_prior), _dp(Ho), _dp(bo))
+        return Ho, bo
+
+    def window_calc_energy(self, HM, bM, delta):
+        """(calcLEnergyF_MT, calcMEnergyF)"""
+        c64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        HM, bM, delta = c64(HM), c64(bM), c64(delta)
+        e = np.zeros(2)
+        self._call("window_calc_energy", _dp(HM), _dp(bM), _dp(delta), _dp(e))
+        return float(e[0]), float(e[1])
+
     def window_solve(self, iteration, lam, acc, HM, bM, delta, N=None):
         D = 8 * self.win_n + 4
         x = np.zeros(D)

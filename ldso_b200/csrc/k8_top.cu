@@ -1,4 +1,4 @@
-// k8_top.cu — K8: AccumulatedTopHessianSSE::addPoint<0> and <1>
+// k8_top.cu — K8: AccumulatedTopHessianSSE::addPoint<0>, <1> and <2>
 // (reference src/internal/OptimizationBackend/AccumulatedTopHessian.cc:9-118) with AccumulatorApprox
 // (MatrixAccumulators.h:749-1102).
 //
@@ -22,10 +22,10 @@ k8_top_kernel(int n, const int* __restrict__ chunk, const int* __restrict__ orde
               const int* __restrict__ r_point, const int* __restrict__ r_target, const int* __restrict__ host,
               const float* __restrict__ J, const float* __restrict__ rtz, const float* __restrict__ adHTdelta, float4 cDelta,
               const float* __restrict__ idepth, const float* __restrict__ idepth_zero, float* __restrict__ res_pt,
-              double* __restrict__ acc_top, int* __restrict__ acc_cnt) {
+              double* __restrict__ acc_top, int* __restrict__ acc_cnt, int marg) {
     const int key = chunk[3 * blockIdx.x], start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
     const int nn = n * n;
-    const int mode = key >= nn ? 1 : 0;
+    const int mode = marg ? 2 : key >= nn ? 1 : 0;   // marg: addPoint<2>, the list holds only the marginalised points' residuals
     float acc[NV];
 #pragma unroll
     for (int i = 0; i < NV; i++) acc[i] = 0.f;
@@ -47,6 +47,9 @@ k8_top_kernel(int n, const int* __restrict__ chunk, const int* __restrict__ orde
             if (mode == 0) {
 #pragma unroll
                 for (int i = 0; i < 8; i++) res[i] = j[i];
+            } else if (mode == 2) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) res[i] = rtz[8 * (size_t)r + i];
             } else {
                 // resApprox = res_toZeroF + J * delta (AccumulatedTopHessian.cc:47-64)
                 const int pt = r_point[r];
@@ -137,9 +140,53 @@ k8_top_kernel(int n, const int* __restrict__ chunk, const int* __restrict__ orde
     }
 }
 
+// EnergyFunctional::calcLEnergyPt (EnergyFunctional.cc:751-806): one thread per point, per-point fp32 sum in the
+// reference's order, warp fold, one fp64 atomic per warp.
+__global__ void __launch_bounds__(128)
+k8_lenergy_kernel(int n, int np, const int* __restrict__ res_begin, const int* __restrict__ flags, const int* __restrict__ r_target,
+                  const int* __restrict__ host, const float* __restrict__ J, const float* __restrict__ rtz,
+                  const float* __restrict__ adHTdelta, float4 cDelta, const float* __restrict__ idepth,
+                  const float* __restrict__ idepth_zero, const float* __restrict__ prior, double* __restrict__ out) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    float E = 0.f;
+    if (p < np) {
+        const float dd = idepth[p] - idepth_zero[p];
+        const float cd[4] = {cDelta.x, cDelta.y, cDelta.z, cDelta.w};
+        const int h = host[p];
+        for (int r = res_begin[p]; r < res_begin[p + 1]; r++) {
+            const int fl = flags[r];
+            if (!(fl & LDSO_RF_LINEARIZED) || !(fl & LDSO_RF_ACTIVE)) continue;
+            const float* j = J + (size_t)r * LDSO_J_FLOATS;
+            const float* dp = adHTdelta + 8 * (h + n * r_target[r]);
+            float dx = 0, dy = 0, cx = 0, cy = 0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) { dx += j[40 + i] * dp[i]; dy += j[46 + i] * dp[i]; }
+#pragma unroll
+            for (int i = 0; i < 4; i++) { cx += j[52 + i] * cd[i]; cy += j[56 + i] * cd[i]; }
+            const float Jx = dx + cx + j[60] * dd, Jy = dy + cy + j[61] * dd;
+            const float da = dp[6], db = dp[7];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                float Jd = j[8 + i] * Jx;
+                Jd = Jd + j[16 + i] * Jy;
+                Jd = Jd + j[24 + i] * da;
+                Jd = Jd + j[32 + i] * db;
+                float r0 = rtz[8 * (size_t)r + i];
+                r0 = r0 + r0;
+                r0 = r0 + Jd;
+                E += Jd * r0;
+            }
+        }
+        E += dd * dd * prior[p];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+    if ((threadIdx.x & 31) == 0 && E != 0.f) atomicAdd(out, (double)E);
+}
+
 }  // namespace
 
-int k8_accumulate_top(ldso_gpu_ctx* c) {
+int k8_accumulate_top(ldso_gpu_ctx* c, int marg) {
     WindowDev& W = c->win;
     const int nn = W.n * W.n;
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.acc_top, 0, sizeof(double) * 2 * nn * WIN_TOP_STRIDE, c->stream));
@@ -149,8 +196,21 @@ int k8_accumulate_top(ldso_gpu_ctx* c) {
         prof_begin(c, c->stream);
         k8_top_kernel<<<W.n_chunks, K8_THREADS, 0, c->stream>>>(W.n, W.chunk, W.order, W.flags, W.r_point, W.r_target, W.host, W.J,
                                                                 W.rtz, W.adHTdelta, cd, W.idepth, W.idepth_zero, W.res_pt,
-                                                                W.acc_top, W.acc_top_cnt);
+                                                                W.acc_top, W.acc_top_cnt, marg);
         prof_end(c, c->stream, LDSO_PROF_K8, W.nr);
+        c->launches++;
+    }
+    LDSO_CUDA_OK(c, cudaGetLastError());
+    return 0;
+}
+
+int k8_linearized_energy(ldso_gpu_ctx* c, double* e_dev) {
+    WindowDev& W = c->win;
+    LDSO_CUDA_OK(c, cudaMemsetAsync(e_dev, 0, sizeof(double), c->stream));
+    if (W.np > 0) {
+        float4 cd = make_float4(W.cDeltaF[0], W.cDeltaF[1], W.cDeltaF[2], W.cDeltaF[3]);
+        k8_lenergy_kernel<<<(W.np + 127) / 128, 128, 0, c->stream>>>(W.n, W.np, W.res_begin, W.flags, W.r_target, W.host, W.J, W.rtz,
+                                                                     W.adHTdelta, cd, W.idepth, W.idepth_zero, W.prior, e_dev);
         c->launches++;
     }
     LDSO_CUDA_OK(c, cudaGetLastError());

@@ -23,9 +23,11 @@ __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin
                                 const int* __restrict__ r_target, const float* __restrict__ res_pt,
                                 const float* __restrict__ prior, const float* __restrict__ idepth,
                                 const float* __restrict__ idepth_zero, float* __restrict__ pt_out,
-                                float* __restrict__ max_rel_baseline, int cap_p, int* __restrict__ ridx) {
+                                float* __restrict__ max_rel_baseline, int cap_p, int* __restrict__ ridx,
+                                const unsigned char* __restrict__ marg, float prior_fac) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= np) return;
+    if (marg && !marg[p]) return;   // marginalizePointsF touches the marginalised points only
     const int rb = res_begin[p], re = res_begin[p + 1];
     float HddA = 0, bdA = 0, HddL = 0, bdL = 0, HcdA[4] = {0, 0, 0, 0}, HcdL[4] = {0, 0, 0, 0};
     int ngood = 0;
@@ -38,7 +40,7 @@ __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin
         const float4 a = __ldg(reinterpret_cast<const float4*>(res_pt + 8 * (size_t)r));
         const float4 b = __ldg(reinterpret_cast<const float4*>(res_pt + 8 * (size_t)r) + 1);
         if (b.z == 0.f) continue;   // not seen by K8 (cannot happen for an active residual)
-        if (fl & LDSO_RF_LINEARIZED) {
+        if (marg || (fl & LDSO_RF_LINEARIZED)) {   // addPoint<2> books everything under the L fields and zeroes the A fields
             HddL += a.x; bdL += a.y; HcdL[0] += a.z; HcdL[1] += a.w; HcdL[2] += b.x; HcdL[3] += b.y;
         } else {
             HddA += a.x; bdA += a.y; HcdA[0] += a.z; HcdA[1] += a.w; HcdA[2] += b.x; HcdA[3] += b.y;
@@ -46,12 +48,13 @@ __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin
     }
     float HdiF = 0.f, bdSum = 0.f, idh = 0.f;
     if (ngood > 0) {
-        float H = HddA + HddL + prior[p];
+        const float pr = marg ? prior[p] * prior_fac : prior[p];   // p->priorF *= setting_idepthFixPriorMargFac
+        float H = HddA + HddL + pr;
         if (H < 1e-10) H = 1e-10;
         idh = H;
         HdiF = (float)(1.0 / (double)H);
         bdSum = bdA + bdL;
-        bdSum += prior[p] * (idepth[p] - idepth_zero[p]);   // shiftPriorToZero
+        if (!marg) bdSum += pr * (idepth[p] - idepth_zero[p]);   // shiftPriorToZero
     }
     pt_out[PT_HDD_A * cap_p + p] = HddA; pt_out[PT_BD_A * cap_p + p] = bdA;
     pt_out[PT_HDD_L * cap_p + p] = HddL; pt_out[PT_BD_L * cap_p + p] = bdL;
@@ -65,7 +68,8 @@ __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin
 
 __global__ void __launch_bounds__(K9_THREADS)
 k9_sc_kernel(int n, const int* __restrict__ blocks, const int* __restrict__ ridx, const float* __restrict__ JpJdF,
-             const float* __restrict__ pt_out, int cap_p, double* __restrict__ acc_sc) {
+             const float* __restrict__ pt_out, int cap_p, double* __restrict__ acc_sc,
+             const unsigned char* __restrict__ marg) {
     extern __shared__ float sm[];
     float* sJ = sm;                               // [K9_TILE][n][8]
     float* sHdi = sJ + K9_TILE * n * 8;           // [K9_TILE]
@@ -85,15 +89,15 @@ k9_sc_kernel(int n, const int* __restrict__ blocks, const int* __restrict__ ridx
         for (int i = threadIdx.x; i < K9_TILE * n * 2; i += K9_THREADS) {   // one float4 (half a JpJdF row) per thread
             const int half = i & 1, t = (i >> 1) % n, q = (i >> 1) / n;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (q < cnt) {
+            if (q < cnt && (!marg || marg[base + q])) {
                 const int r = ridx[(size_t)(base + q) * LDSO_MAX_WINDOW + t];
                 if (r >= 0) v = __ldg(reinterpret_cast<const float4*>(JpJdF + 8 * (size_t)r) + half);
             }
             reinterpret_cast<float4*>(sJ)[i] = v;
         }
         for (int q = threadIdx.x; q < K9_TILE; q += K9_THREADS) {
-            const bool in = q < cnt;
             const int p = base + q;
+            const bool in = q < cnt && (!marg || marg[p]);
             sHdi[q] = in ? pt_out[PT_HDI * cap_p + p] : 0.f;
             sBd[q] = in ? pt_out[PT_BDSUM * cap_p + p] : 0.f;
 #pragma unroll
@@ -187,7 +191,7 @@ __global__ void k10_resubstitute_kernel(int n, int np, const int* __restrict__ r
 
 }  // namespace
 
-int k9_accumulate_sc(ldso_gpu_ctx* c) {
+int k9_accumulate_sc(ldso_gpu_ctx* c, const unsigned char* marg_mask, float prior_fac) {
     WindowDev& W = c->win;
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.acc_sc, 0, sizeof(double) * W.acc_sc_size, c->stream));
     // CTA table: up to 64 consecutive points of one host per CTA (built by window_set_points)
@@ -199,8 +203,8 @@ int k9_accumulate_sc(ldso_gpu_ctx* c) {
         prof_begin(c, c->stream);
         k9_point_kernel<<<(W.np + 127) / 128, 128, 0, c->stream>>>(n, W.np, W.res_begin, W.flags, W.r_target, W.res_pt, W.prior,
                                                                    W.idepth, W.idepth_zero, W.pt_out, W.max_rel_baseline, W.cap_p,
-                                                                   W.ridx);
-        k9_sc_kernel<<<nblk, K9_THREADS, smem, c->stream>>>(n, W.sc_blocks, W.ridx, W.JpJdF, W.pt_out, W.cap_p, W.acc_sc);
+                                                                   W.ridx, marg_mask, prior_fac);
+        k9_sc_kernel<<<nblk, K9_THREADS, smem, c->stream>>>(n, W.sc_blocks, W.ridx, W.JpJdF, W.pt_out, W.cap_p, W.acc_sc, marg_mask);
         prof_end(c, c->stream, LDSO_PROF_K9, W.nr);
         c->launches += 2;
     }

@@ -41,6 +41,7 @@ struct WindowDev {
     int n_chunks = 0;
     int* sc_blocks = nullptr;      // [n_sc_blocks][3] = host, first point, end point (K9 CTA table)
     int n_sc_blocks = 0;
+    unsigned char* pmask = nullptr;   // [cap_p] point mask of marginalizePointsF
     int* ridx = nullptr;           // [cap_p][LDSO_MAX_WINDOW] residual id of (point, target) or -1 (written by K9a)
     // device: small tables
     float* adHTdelta = nullptr;    // [n*n][8]
@@ -73,7 +74,8 @@ int k7_linearize(ldso_gpu_ctx* c, int fix);
 int k7_apply_res(ldso_gpu_ctx* c);
 int k7_reset_oob(ldso_gpu_ctx* c);
 int k7_fix_linearization(ldso_gpu_ctx* c, const unsigned char* mask_dev);
-int k8_accumulate_top(ldso_gpu_ctx* c);
-int k9_accumulate_sc(ldso_gpu_ctx* c);
+int k8_accumulate_top(ldso_gpu_ctx* c, int marg = 0);
+int k9_accumulate_sc(ldso_gpu_ctx* c, const unsigned char* marg_mask = nullptr, float prior_fac = 1.f);
+int k8_linearized_energy(ldso_gpu_ctx* c, double* e_out);
 int k10_resubstitute(ldso_gpu_ctx* c, float lambda);
 int h1_stitch(ldso_gpu_ctx* c);

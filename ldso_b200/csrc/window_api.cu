@@ -77,7 +77,7 @@ int win_alloc(ldso_gpu_ctx* c) {
     rc |= dalloc(c, &W.center, R * 4); rc |= dalloc(c, &W.res_pt, R * 8);
     rc |= dalloc(c, &W.order, R); rc |= dalloc(c, &W.chunk, 3 * (R / 1 + 2 * M * M + 8));
     rc |= dalloc(c, &W.sc_blocks, 3 * (P + M + 8));
-    rc |= dalloc(c, &W.ridx, P * M);
+    rc |= dalloc(c, &W.ridx, P * M); rc |= dalloc(c, &W.pmask, P);
     rc |= dalloc(c, &W.adHTdelta, M * M * 8); rc |= dalloc(c, &W.xAd, M * M * 8 + 8); rc |= dalloc(c, &W.stats, 4);
     rc |= dalloc(c, &W.acc_top, 2 * M * M * WIN_TOP_STRIDE); rc |= dalloc(c, &W.acc_top_cnt, 2 * M * M);
     W.acc_sc_size = M * M * M * 64 + M * M * 40 + 20;
@@ -91,7 +91,7 @@ void win_free(ldso_gpu_ctx* c) {
     WindowDev& W = c->win;
     void* ptrs[] = {W.precalc, W.u, W.v, W.idepth, W.idepth_zero, W.prior, W.color, W.weights, W.host, W.res_begin, W.pt_out,
                     W.max_rel_baseline, W.num_good, W.r_point, W.r_target, W.state, W.new_state, W.flags, W.energy, W.new_energy,
-                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.ridx, W.adHTdelta, W.xAd,
+                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.ridx, W.pmask, W.adHTdelta, W.xAd,
                     W.stats, W.acc_top, W.acc_top_cnt, W.acc_sc, W.adH_dev, W.adT_dev, W.prior_dev, W.stitched};
     for (void* p : ptrs) cudaFree(p);
     if (W.pinned) cudaFreeHost(W.pinned);
@@ -147,23 +147,25 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
 }
 
 // (re)build the K8 work list: residual ids sorted by key = mode * n^2 + host + n * target, cut into <=128 chunks
-static int build_order(ldso_gpu_ctx* c) {
+// With `only` (a point mask) the list holds just those points' residuals, all under the mode-0 keys (addPoint<2>).
+static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
     WindowDev& W = c->win;
     const int nn = W.n * W.n, nr = W.nr;
     std::vector<int> cnt(2 * nn + 1, 0), key(nr);
     for (int r = 0; r < nr; r++) {
-        key[r] = (W.h_lin[r] ? nn : 0) + W.h_host[W.h_point[r]] + W.n * W.h_target[r];
+        if (only && !only[W.h_point[r]]) { key[r] = -1; continue; }
+        key[r] = (!only && W.h_lin[r] ? nn : 0) + W.h_host[W.h_point[r]] + W.n * W.h_target[r];
         cnt[key[r] + 1]++;
     }
     for (int k = 0; k < 2 * nn; k++) cnt[k + 1] += cnt[k];
-    std::vector<int> order(nr), pos(cnt.begin(), cnt.end() - 1), chunk;
-    for (int r = 0; r < nr; r++) order[pos[key[r]]++] = r;
+    std::vector<int> order(std::max(nr, 1)), pos(cnt.begin(), cnt.end() - 1), chunk;
+    for (int r = 0; r < nr; r++) if (key[r] >= 0) order[pos[key[r]]++] = r;
     for (int k = 0; k < 2 * nn; k++)
         for (int s = cnt[k]; s < cnt[k + 1]; s += 128) {
             chunk.push_back(k); chunk.push_back(s); chunk.push_back(std::min(128, cnt[k + 1] - s));
         }
     W.n_chunks = (int)chunk.size() / 3;
-    int rc = upload(c, W.order, order.data(), sizeof(int) * nr);
+    int rc = upload(c, W.order, order.data(), sizeof(int) * cnt[2 * nn]);
     rc |= upload(c, W.chunk, chunk.data(), sizeof(int) * chunk.size());
     return rc ? -1 : 0;
 }
@@ -483,4 +485,153 @@ extern "C" int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* c, int what, float
         case 10: return download(c, dst, W.num_good, sizeof(float) * np);
         default: return row(PT_STEP, dst);
     }
+}
+
+// ---- marginalisation + energies (EnergyFunctional.cc:109-262, :473-497) -----------------------------
+namespace {
+
+// EnergyFunctional::removePoint for the masked points: their residuals leave the active set
+__global__ void win_deactivate_kernel(int nr, const int* __restrict__ r_point, const unsigned char* __restrict__ mask,
+                                      int* __restrict__ flags) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < nr && mask[r_point[r]]) flags[r] &= ~LDSO_RF_ACTIVE;
+}
+
+// util::MatrixInverter::invertPosDef, SVD form (src/util/MatrixInverter.cc:31-50); only the upper triangle of the
+// result is defined there, the caller reads it through selfadjointView<Upper>
+void invert_pos_def8(const double* M, double* res) {
+    const int n = 8;
+    double SVecI[8], Ms[64], U[64], S[8], V[64];
+    for (int i = 0; i < n; i++) SVecI[i] = 1.0 / std::sqrt(std::fabs(M[i * n + i]) + 10);
+    for (int i = 0; i < n; i++)
+        for (int j = i; j < n; j++) Ms[i * n + j] = Ms[j * n + i] = SVecI[i] * M[i * n + j] * SVecI[j];
+    ldso_sm::jacobi_svd(n, n, Ms, U, S, V);
+    for (int i = 0; i < n; i++) S[i] = S[i] <= 0 ? 0.0 : 1.0 / S[i];
+    for (int i = 0; i < n; i++)
+        for (int j = i; j < n; j++) {
+            double s = 0;
+            for (int l = 0; l < n; l++) s += V[i * n + l] * S[l] * U[j * n + l];
+            res[i * n + j] = res[j * n + i] = SVecI[i] * s * SVecI[j];
+        }
+}
+
+}  // namespace
+
+extern "C" int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* c, const unsigned char* marg, float fac, double* H, double* b,
+                                                  int* n_res) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && H && b && (marg || W.np == 0));
+    LDSO_REQUIRE(c, (int)W.adHost.size() == 64 * W.n * W.n);
+    const int n = W.n, nn = n * n, D = 8 * n + CPARS;
+    int rc = upload(c, W.pmask, marg, W.np);
+    if (rc) return rc;
+    rc = build_order(c, marg);
+    if (rc) return rc;
+    rc = k8_accumulate_top(c, 1);
+    if (rc) return rc;
+    rc = k9_accumulate_sc(c, W.pmask, fac);
+    if (rc) return rc;
+    rc = h1_stitch(c);
+    if (rc) return rc;
+    if (W.nr > 0) {
+        win_deactivate_kernel<<<(W.nr + 255) / 256, 256, 0, c->stream>>>(W.nr, W.r_point, W.pmask, W.flags);
+        c->launches++;
+    }
+    const size_t sysz = (size_t)D * D + D;
+    const size_t bytes = sizeof(double) * 3 * sysz + sizeof(int) * nn;
+    char* st = (char*)staging(c, bytes);
+    LDSO_REQUIRE(c, st != nullptr);
+    LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * nn, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    W.pinned_off = 0;
+    const double *M = (const double*)st, *Msc = M + 2 * sysz;
+    for (size_t i = 0; i < (size_t)D * D; i++) H[i] = M[i] - Msc[i];
+    for (int i = 0; i < D; i++) b[i] = M[(size_t)D * D + i] - Msc[(size_t)D * D + i];
+    if (n_res) {
+        const int* cnt = (const int*)(st + sizeof(double) * 3 * sysz);
+        *n_res = 0;
+        for (int k = 0; k < nn; k++) *n_res += cnt[k];
+    }
+    return build_order(c);   // back to the A/L work list of the remaining residuals (inactive ones are skipped by flag)
+}
+
+extern "C" int ldso_gpu_window_marginalize_frame(ldso_gpu_ctx* c, int n, int idx, const double* HMin, const double* bMin,
+                                                 const double prior[8], const double delta_prior[8], double* HM_out,
+                                                 double* bM_out) {
+    LDSO_REQUIRE(c, n >= 1 && n <= LDSO_MAX_WINDOW && idx >= 0 && idx < n && HMin && bMin && prior && delta_prior && HM_out && bM_out);
+    const int odim = 8 * n + CPARS, ndim = odim - 8;
+    // permutation that moves the frame's 8 rows/cols to the end, keeping the order of the rest (:127-146)
+    std::vector<int> perm(odim);
+    {
+        int k = 0;
+        const int io = 8 * idx + CPARS;
+        for (int i = 0; i < odim; i++) if (i < io || i >= io + 8) perm[k++] = i;
+        for (int i = 0; i < 8; i++) perm[k++] = io + i;
+    }
+    std::vector<double> HM((size_t)odim * odim), bM(odim), SVec(odim), SVecI(odim);
+    for (int i = 0; i < odim; i++) {
+        bM[i] = bMin[perm[i]];
+        for (int j = 0; j < odim; j++) HM[(size_t)i * odim + j] = HMin[(size_t)perm[i] * odim + perm[j]];
+    }
+    for (int i = 0; i < 8; i++) {   // the frame's own prior goes in here instead of into the active system (:150-151)
+        HM[(size_t)(ndim + i) * odim + ndim + i] += prior[i];
+        bM[ndim + i] += prior[i] * delta_prior[i];
+    }
+    for (int i = 0; i < odim; i++) { SVec[i] = std::sqrt(std::fabs(HM[(size_t)i * odim + i]) + 10); SVecI[i] = 1.0 / SVec[i]; }
+    for (int i = 0; i < odim; i++) {
+        bM[i] *= SVecI[i];
+        for (int j = 0; j < odim; j++) HM[(size_t)i * odim + j] *= SVecI[i] * SVecI[j];
+    }
+    double hp[64], hpi[64];
+    for (int i = 0; i < 8; i++)
+        for (int j = 0; j < 8; j++) hp[i * 8 + j] = HM[(size_t)(ndim + i) * odim + ndim + j];
+    invert_pos_def8(hp, hpi);
+    // bli = bottomLeft^T * hpi ; top-left -= bli * bottomLeft ; b_head -= bli * b_tail   (:166-169)
+    std::vector<double> bli((size_t)ndim * 8);
+    for (int i = 0; i < ndim; i++)
+        for (int j = 0; j < 8; j++) {
+            double s = 0;
+            for (int l = 0; l < 8; l++) s += HM[(size_t)(ndim + l) * odim + i] * hpi[l * 8 + j];
+            bli[(size_t)i * 8 + j] = s;
+        }
+    std::vector<double> Hn((size_t)ndim * ndim);
+    for (int i = 0; i < ndim; i++) {
+        double sb = 0;
+        for (int l = 0; l < 8; l++) sb += bli[(size_t)i * 8 + l] * bM[ndim + l];
+        bM_out[i] = (bM[i] - sb) * SVec[i];
+        for (int j = 0; j < ndim; j++) {
+            double s = 0;
+            for (int l = 0; l < 8; l++) s += bli[(size_t)i * 8 + l] * HM[(size_t)(ndim + l) * odim + j];
+            Hn[(size_t)i * ndim + j] = (HM[(size_t)i * odim + j] - s) * SVec[i] * SVec[j];
+        }
+    }
+    for (int i = 0; i < ndim; i++)
+        for (int j = 0; j < ndim; j++) HM_out[(size_t)i * ndim + j] = 0.5 * (Hn[(size_t)i * ndim + j] + Hn[(size_t)j * ndim + i]);
+    return 0;
+}
+
+extern "C" int ldso_gpu_window_calc_energy(ldso_gpu_ctx* c, const double* HM, const double* bM, const double* delta,
+                                           double energy[2]) {
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && HM && bM && delta && energy && (int)W.fprior.size() == 8 * W.n);
+    const int D = 8 * W.n + CPARS;
+    int rc = k8_linearized_energy(c, W.stats + 2);
+    if (rc) return rc;
+    double eL = 0;
+    rc = download(c, &eL, W.stats + 2, sizeof(double));
+    if (rc) return rc;
+    double E = 0;
+    for (int i = 0; i < 8 * W.n; i++) E += W.fdelta_prior[i] * W.fprior[i] * W.fdelta_prior[i];
+    float ec = 0;
+    for (int i = 0; i < 4; i++) ec += W.cDeltaF[i] * (float)W.cPrior[i] * W.cDeltaF[i];   // cDeltaF.cwiseProduct(cPriorF).dot(cDeltaF)
+    energy[0] = E + ec + eL;
+    double em = 0;   // calcMEnergyF: delta . (2 bM + HM delta)
+    for (int i = 0; i < D; i++) {
+        double s = 2 * bM[i];
+        for (int j = 0; j < D; j++) s += HM[(size_t)i * D + j] * delta[j];
+        em += delta[i] * s;
+    }
+    energy[1] = em;
+    return 0;
 }

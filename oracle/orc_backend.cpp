@@ -885,3 +885,174 @@ extern "C" int orc_window_get_point_floats(orc_ctx* c, int what, float* dst) {
     memcpy(dst, s[what]->data(), sizeof(float) * s[what]->size());
     return 0;
 }
+
+// ================================================================================================
+// EnergyFunctional::marginalizePointsF (EnergyFunctional.cc:205-262), single-threaded as in the reference
+extern "C" int orc_window_marginalize_points(orc_ctx* c, const unsigned char* marg, float fac, double* H, double* b, int* n_res) {
+    Window& W = c->win;
+    const int n = W.n, D = 8 * n + CPARS;
+    std::vector<AccumulatorApprox> acc(n * n);
+    for (auto& a : acc) a.initialize();
+    SCAcc S;
+    S.accE.resize(n * n); S.accEB.resize(n * n); S.accD.resize(n * n * n);
+    for (auto& a : S.accE) a.initialize(8, 4);
+    for (auto& a : S.accEB) a.initialize(8, 1);
+    for (auto& a : S.accD) a.initialize(8, 8);
+    S.accHcc.initialize(4, 4); S.accbc.initialize(4, 1);
+    int nres = 0;
+    for (int p = 0; p < W.np; p++) {
+        if (!marg[p]) continue;
+        W.prior[p] *= fac;                       // p->priorF *= setting_idepthFixPriorMargFac (:217)
+        top_add_point(c, 2, p, acc, nres);       // :235
+        sc_add_point(c, p, false, S);            // :236
+        for (int r = W.res_begin[p]; r < W.res_begin[p + 1]; r++) W.flags[r] &= ~LDSO_RF_ACTIVE;   // removePoint (:193-203)
+    }
+    std::vector<double> M((size_t)D * D), Mb(D), Msc((size_t)D * D), Mbsc(D);
+    top_stitch(c, acc, false, M.data(), Mb.data());   // stitchDouble(M, Mb, this, false, false) (:242)
+    sc_stitch(c, S, Msc.data(), Mbsc.data());
+    for (size_t i = 0; i < (size_t)D * D; i++) H[i] = M[i] - Msc[i];
+    for (int i = 0; i < D; i++) b[i] = Mb[i] - Mbsc[i];
+    if (n_res) *n_res = nres;
+    return 0;
+}
+
+// util::MatrixInverter::invertPosDef(M, fast = false) (src/util/MatrixInverter.cc:31-50)
+static void invert_pos_def(int n, const double* M, double* res) {
+    std::vector<double> sv(n), Ms((size_t)n * n), U((size_t)n * n), S(n), V((size_t)n * n);
+    for (int i = 0; i < n; i++) sv[i] = 1.0 / std::sqrt(std::fabs(M[i * n + i]) + 10);
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) {
+            const double m = i <= j ? M[i * n + j] : M[j * n + i];   // selfadjointView<Upper>
+            Ms[i * n + j] = sv[i] * m * sv[j];
+        }
+    ldso_sm::jacobi_svd(n, n, Ms.data(), U.data(), S.data(), V.data());
+    for (int i = 0; i < n; i++) S[i] = S[i] <= 0 ? 0 : 1 / S[i];
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) {
+            double s = 0;
+            for (int l = 0; l < n; l++) s += V[i * n + l] * S[l] * U[j * n + l];
+            res[i * n + j] = sv[i] * s * sv[j];
+        }
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < i; j++) res[i * n + j] = res[j * n + i];   // read back through selfadjointView<Upper>
+}
+
+// EnergyFunctional::marginalizeFrame (EnergyFunctional.cc:109-191): the moves are done block by block as there
+extern "C" int orc_window_marginalize_frame(orc_ctx*, int nFrames, int idx, const double* HMin, const double* bMin,
+                                            const double prior[8], const double delta_prior[8], double* HM_out, double* bM_out) {
+    const int ndim = nFrames * 8 + CPARS - 8, odim = nFrames * 8 + CPARS;
+    std::vector<double> HM(HMin, HMin + (size_t)odim * odim), bM(bMin, bMin + odim);
+    auto at = [&](std::vector<double>& A, int r, int cc) -> double& { return A[(size_t)r * odim + cc]; };
+    if (idx != nFrames - 1) {
+        const int io = idx * 8 + CPARS, ntail = 8 * (nFrames - idx - 1);
+        std::vector<double> bTmp(bM.begin() + io, bM.begin() + io + 8), tail(bM.end() - ntail, bM.end());
+        for (int i = 0; i < ntail; i++) bM[io + i] = tail[i];
+        for (int i = 0; i < 8; i++) bM[odim - 8 + i] = bTmp[i];
+        std::vector<double> T = HM;                                   // columns
+        for (int r = 0; r < odim; r++) {
+            for (int i = 0; i < ntail; i++) at(HM, r, io + i) = at(T, r, odim - ntail + i);
+            for (int i = 0; i < 8; i++) at(HM, r, odim - 8 + i) = at(T, r, io + i);
+        }
+        T = HM;                                                       // rows
+        for (int cc = 0; cc < odim; cc++) {
+            for (int i = 0; i < ntail; i++) at(HM, io + i, cc) = at(T, odim - ntail + i, cc);
+            for (int i = 0; i < 8; i++) at(HM, odim - 8 + i, cc) = at(T, io + i, cc);
+        }
+    }
+    for (int i = 0; i < 8; i++) {
+        at(HM, ndim + i, ndim + i) += prior[i];
+        bM[ndim + i] += prior[i] * delta_prior[i];
+    }
+    std::vector<double> SVec(odim), SVecI(odim);
+    for (int i = 0; i < odim; i++) { SVec[i] = std::sqrt(std::fabs(at(HM, i, i)) + 10); SVecI[i] = 1 / SVec[i]; }
+    std::vector<double> HS((size_t)odim * odim), bS(odim);
+    for (int i = 0; i < odim; i++) {
+        bS[i] = SVecI[i] * bM[i];
+        for (int j = 0; j < odim; j++) at(HS, i, j) = SVecI[i] * at(HM, i, j) * SVecI[j];
+    }
+    double hp[64], hpi[64];
+    for (int i = 0; i < 8; i++) for (int j = 0; j < 8; j++) hp[i * 8 + j] = at(HS, ndim + i, ndim + j);
+    invert_pos_def(8, hp, hpi);
+    std::vector<double> BL((size_t)8 * ndim), BLt((size_t)ndim * 8), bli((size_t)ndim * 8), prod((size_t)ndim * ndim), pb(ndim);
+    for (int i = 0; i < 8; i++) for (int j = 0; j < ndim; j++) { BL[(size_t)i * ndim + j] = at(HS, ndim + i, j); BLt[(size_t)j * 8 + i] = BL[(size_t)i * ndim + j]; }
+    mm(BLt.data(), hpi, bli.data(), ndim, 8, 8);
+    mm(bli.data(), BL.data(), prod.data(), ndim, 8, ndim);
+    mm(bli.data(), &bS[ndim], pb.data(), ndim, 8, 1);
+    for (int i = 0; i < ndim; i++) {
+        bS[i] -= pb[i];
+        for (int j = 0; j < ndim; j++) at(HS, i, j) -= prod[(size_t)i * ndim + j];
+    }
+    for (int i = 0; i < odim; i++) {
+        bS[i] *= SVec[i];
+        for (int j = 0; j < odim; j++) at(HS, i, j) *= SVec[i] * SVec[j];
+    }
+    for (int i = 0; i < ndim; i++) {
+        bM_out[i] = bS[i];
+        for (int j = 0; j < ndim; j++) HM_out[(size_t)i * ndim + j] = 0.5 * (at(HS, i, j) + at(HS, j, i));
+    }
+    return 0;
+}
+
+// EnergyFunctional::calcLEnergyF_MT / calcLEnergyPt (:481-497, :751-806) with Accumulator11
+// (MatrixAccumulators.h:68-142), and calcMEnergyF (:473-479)
+namespace {
+struct Acc11 {
+    float A = 0, d[4] = {0, 0, 0, 0}, d1k[4] = {0, 0, 0, 0}, d1m[4] = {0, 0, 0, 0}, n1 = 0, n1k = 0, n1m = 0;
+    void shiftUp(bool force) {
+        if (n1 > 1000 || force) { for (int i = 0; i < 4; i++) { d1k[i] = d[i] + d1k[i]; d[i] = 0; } n1k += n1; n1 = 0; }
+        if (n1k > 1000 || force) { for (int i = 0; i < 4; i++) { d1m[i] = d1k[i] + d1m[i]; d1k[i] = 0; } n1m += n1k; n1k = 0; }
+    }
+    void sse_noshift(const float* v) { for (int i = 0; i < 4; i++) d[i] += v[i]; n1++; }
+    void single(float v) { d[0] += v; n1++; shiftUp(false); }
+    void finish() { shiftUp(true); A = d1m[0] + d1m[1] + d1m[2] + d1m[3]; }
+};
+}  // namespace
+
+extern "C" int orc_window_calc_energy(orc_ctx* c, const double* HM, const double* bM, const double* delta, double energy[2]) {
+    Window& W = c->win;
+    const int n = W.n, D = 8 * n + CPARS;
+    double E = 0;
+    for (int i = 0; i < 8 * n; i++) E += W.fdelta_prior[i] * W.fprior[i] * W.fdelta_prior[i];
+    float ec = 0;
+    for (int i = 0; i < 4; i++) ec += W.cDeltaF[i] * (float)W.cPrior[i] * W.cDeltaF[i];
+    E += ec;
+    Acc11 A;
+    const float* dc = W.cDeltaF;
+    for (int p = 0; p < W.np; p++) {
+        const float dd = W.deltaF[p];
+        for (int r = W.res_begin[p]; r < W.res_begin[p + 1]; r++) {
+            if (!(W.flags[r] & LDSO_RF_LINEARIZED) || !(W.flags[r] & LDSO_RF_ACTIVE)) continue;
+            const float* J = &W.J[(size_t)r * LDSO_J_FLOATS];
+            const float* dp = &W.adHTdeltaF[8 * (W.host[p] + n * W.r_target[r])];
+            float dx = 0, dy = 0, cx = 0, cy = 0;
+            for (int i = 0; i < 6; i++) { dx += J[40 + i] * dp[i]; dy += J[46 + i] * dp[i]; }
+            for (int i = 0; i < 4; i++) { cx += J[52 + i] * dc[i]; cy += J[56 + i] * dc[i]; }
+            const float Jx = dx + cx + J[60] * dd, Jy = dy + cy + J[61] * dd;
+            for (int i = 0; i + 3 < 8; i += 4) {
+                float v[4];
+                for (int l = 0; l < 4; l++) {
+                    float Jd = J[8 + i + l] * Jx;
+                    Jd = Jd + J[16 + i + l] * Jy;
+                    Jd = Jd + J[24 + i + l] * dp[6];
+                    Jd = Jd + J[32 + i + l] * dp[7];
+                    float r0 = W.res_toZeroF[8 * (size_t)r + i + l];
+                    r0 = r0 + r0;
+                    r0 = r0 + Jd;
+                    v[l] = Jd * r0;
+                }
+                A.sse_noshift(v);
+            }
+        }
+        A.single(dd * dd * W.prior[p]);
+    }
+    A.finish();
+    energy[0] = E + A.A;
+    double em = 0;
+    for (int i = 0; i < D; i++) {
+        double s = 2 * bM[i];
+        for (int j = 0; j < D; j++) s += HM[(size_t)i * D + j] * delta[j];
+        em += delta[i] * s;
+    }
+    energy[1] = em;
+    return 0;
+}

@@ -158,3 +158,63 @@ def test_large_window_c4_shape(gpu, oracle):
     for k in ("HA", "bA", "HL", "bL", "Hsc", "bsc"):
         assert util.rel_err(ag[k], ao[k]) < 1e-4, (k, util.rel_err(ag[k], ao[k]))
     g.close(); o.close()
+
+
+def linearised(api, W):
+    ctx = load(api, W)
+    ctx.window_linearize(True)
+    fl = ctx.window_residual_ints(2)
+    ctx.window_fix_linearization(((fl & 2) != 0).astype(np.uint8))
+    return ctx
+
+
+def test_marginalize_points_parity(gpu, oracle, window):
+    """EnergyFunctional::marginalizePointsF: addPoint<2> + SC addPoint(p, false) over a subset of the points"""
+    g, o = linearised(gpu, window), linearised(oracle, window)
+    np_ = len(window["u"])
+    for rnd, sel in enumerate((np.arange(np_) % 3 == 0, np.arange(np_) % 3 == 1)):      # twice: the second call sees removed points
+        m = sel.astype(np.uint8)
+        Hg, bg, ng = g.window_marginalize_points(m)
+        Ho, bo, no = o.window_marginalize_points(m)
+        assert ng == no and no > 500
+        assert util.rel_err(Hg, Ho) < 1e-4 and util.rel_err(bg, bo) < 1e-4, (util.rel_err(Hg, Ho), util.rel_err(bg, bo))
+        n = window["n"]
+        for h in range(n):
+            for t in range(n):
+                a, b = Hg[4 + 8 * h:12 + 8 * h, 4 + 8 * t:12 + 8 * t], Ho[4 + 8 * h:12 + 8 * h, 4 + 8 * t:12 + 8 * t]
+                assert np.linalg.norm(a - b) <= 1e-4 * np.linalg.norm(b) + 1e-7 * np.linalg.norm(Ho), (rnd, h, t)
+        for what in (0, 1, 2, 3, 4, 5, 6, 7, 8):                                         # per-point fields of the marginalised points
+            a, b = g.window_point_floats(what), o.window_point_floats(what)
+            assert np.array_equal(bits(a[sel]), bits(b[sel])), (rnd, what)
+        assert np.array_equal(g.window_residual_ints(2), o.window_residual_ints(2))       # removePoint
+    # the remaining third still accumulates like the oracle's
+    ag, ao = g.window_accumulate(), o.window_accumulate()
+    assert np.array_equal(ag["counts"], ao["counts"]) and ao["counts"][1] > 500
+    for k in ("HL", "bL", "Hsc", "bsc"):
+        assert util.rel_err(ag[k], ao[k]) < 1e-4, k
+    g.close(); o.close()
+
+
+@pytest.mark.parametrize("n,idx", [(7, 0), (7, 4), (7, 6), (10, 2), (1, 0)])
+def test_marginalize_frame_parity(gpu, oracle, n, idx):
+    rng = np.random.default_rng(n * 10 + idx)
+    D = 8 * n + 4
+    A = rng.normal(size=(D, 2 * D))
+    HM = A @ A.T * rng.uniform(1, 1e4, size=(D, 1)) ** 0.5 * rng.uniform(1, 1e4, size=(1, D)) ** 0.5
+    HM = 0.5 * (HM + HM.T)
+    bM = rng.normal(size=D) * 100
+    prior, dprior = rng.uniform(0, 50, 8), rng.normal(size=8)
+    g, o = util.make_ctx(gpu, "c1"), util.make_ctx(oracle, "c1")
+    Hg, bg = g.window_marginalize_frame(n, idx, HM, bM, prior, dprior)
+    Ho, bo = o.window_marginalize_frame(n, idx, HM, bM, prior, dprior)
+    assert util.rel_err(Hg, Ho) < 1e-10 and util.rel_err(bg, bo) < 1e-10
+    g.close(); o.close()
+
+
+def test_calc_energy_parity(gpu, oracle, window):
+    g, o = linearised(gpu, window), linearised(oracle, window)
+    eg = g.window_calc_energy(window["HM"], window["bM"], window["delta"])
+    eo = o.window_calc_energy(window["HM"], window["bM"], window["delta"])
+    assert abs(eg[0] - eo[0]) <= 1e-4 * abs(eo[0]) and eo[0] != 0, (eg, eo)
+    assert abs(eg[1] - eo[1]) <= 1e-12 * max(abs(eo[1]), 1.0)
+    g.close(); o.close()
