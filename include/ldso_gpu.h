@@ -100,6 +100,8 @@ int ldso_gpu_timer_stop(ldso_gpu_ctx* ctx, float* ms);
 #define LDSO_PROF_K6 7       /* activation, units = candidates */
 #define LDSO_PROF_K10 8      /* resubstitute, units = points */
 #define LDSO_PROF_K2 9       /* makeCoarseDepthL0 kernels, units = points */
+#define LDSO_PROF_N2 10      /* distance map, units = level-1 cells */
+#define LDSO_PROF_N2SEL 11   /* activation walk, units = pool points */
 #define LDSO_PROF_SLOTS 12
 int ldso_gpu_profile_enable(ldso_gpu_ctx* ctx, int on);
 int ldso_gpu_profile_get(ldso_gpu_ctx* ctx, int which, double* total_ms, long long* launches, double* units);
@@ -201,6 +203,32 @@ int ldso_gpu_immature_activate(ldso_gpu_ctx* ctx, int n_cand, const int* cand, i
  *          reference deletes such points: FullSystem.cc:1456-1458).  n_pool: new pool size. */
 int ldso_gpu_immature_compact(ldso_gpu_ctx* ctx, int drop_host, int drop_oob, int n_remove, const int* remove_idx, int* n_out);
 int ldso_gpu_immature_append(ldso_gpu_ctx* ctx, int slot, int host_idx, int n, const float* u, const float* v, int* n_pool);
+
+/* ---- N2: CoarseDistanceMap and the candidate walk of FullSystem::activatePointsMT ----------------------
+ * ImmaturePoint::my_type of the pool rows [first, first + n): 1 / 2 / 4, the `type` of ldso_gpu_select_points
+ * (include/internal/ImmaturePoint.h, set in FullSystem::makeNewTraces :1449).  Rows made by immature_set /
+ * immature_append start with 1. */
+int ldso_gpu_immature_set_types(ldso_gpu_ctx* ctx, int first, int n, const float* type);
+/* CoarseDistanceMap::makeDistanceMap + growDistBFS (src/frontend/CoarseTracker.cc:795-923) on the level-1 grid
+ * (w/2 x h/2).  The n_points active points (host = window index, u, v, idepth_scaled) are projected with
+ * KRKi[host] = K[1] R Ki[0] and Kt[host] = K[1] t of host -> newest frame (FullSystem.cc:1236-1238); cells they hit
+ * start at 0, every other cell at 1000, and 39 rings grow from them, odd rings over 8 neighbours, even rings over 4,
+ * never out of a border cell.  Points with host < 0 are skipped (the newest frame's own points). */
+int ldso_gpu_distmap_make(ldso_gpu_ctx* ctx, int n_hosts, const float* KRKi, const float* Kt, int n_points,
+                          const int* host, const float* u, const float* v, const float* idepth);
+/* CoarseDistanceMap::fwdWarpedIDDistFinal, (w/2)*(h/2) floats */
+int ldso_gpu_distmap_get(ldso_gpu_ctx* ctx, float* dist);
+/* The walk over the immature points of activatePointsMT (FullSystem.cc:1226-1298) in pool order (= frames, then
+ * features) against the current distance map, which every accepted point updates at once
+ * (CoarseDistanceMap::addIntoDistFinal, CoarseTracker.cc:925-930) — the walk is order dependent.
+ * action_out[n_pool]: 0 stays immature, 1 deleted (never traced successfully, outlier on the last trace, cannot be
+ * activated and will be out, or projects outside the newest frame), 2 accepted for activation (toOptimize, pool order).
+ * host_skip[h] != 0: frame h is the newest keyframe, its points are not visited; host_flagged[h]:
+ * flaggedForMarginalization.  min_trace_quality = setting_minTraceQuality (3).  counts_out = {accepted, deleted}. */
+int ldso_gpu_immature_select_activation(ldso_gpu_ctx* ctx, int n_hosts, const float* KRKi, const float* Kt,
+                                        const unsigned char* host_skip, const unsigned char* host_flagged,
+                                        float current_min_act_dist, float min_trace_quality, unsigned char* action_out,
+                                        int counts_out[2]);
 
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps

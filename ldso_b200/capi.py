@@ -284,12 +284,44 @@ class Ctx:
         self.imm_n = n.value
         return n.value
 
-    def immature_append(self, slot, host_idx, u, v):
+    def immature_append(self, slot, host_idx, u, v, types=None):
         u, v = f32(u), f32(v)
         n = C.c_int()
+        first = self.imm_n
         self._call("immature_append", C.c_int(slot), C.c_int(host_idx), C.c_int(len(u)), _fp(u), _fp(v), C.byref(n))
         self.imm_n = n.value
+        if types is not None and len(u):
+            self.immature_set_types(first, types)
         return n.value
+
+    # ---- N2: CoarseDistanceMap + activation walk ----
+    def immature_set_types(self, first, types):
+        t = f32(types)
+        self._call("immature_set_types", C.c_int(first), C.c_int(len(t)), _fp(t))
+
+    def distmap_make(self, KRKi, Kt, host, u, v, idepth):
+        KRKi, Kt = f32(KRKi).reshape(-1, 9), f32(Kt).reshape(-1, 3)
+        host = np.ascontiguousarray(host, dtype=np.int32)
+        u, v, idepth = f32(u), f32(v), f32(idepth)
+        self._call("distmap_make", C.c_int(len(KRKi)), _fp(KRKi), _fp(Kt), C.c_int(len(host)), _ip(host), _fp(u), _fp(v), _fp(idepth))
+
+    def distmap_get(self):
+        w, h = self.sizes[1]
+        d = np.zeros((h, w), np.float32)
+        self._call("distmap_get", _fp(d))
+        return d
+
+    def immature_select_activation(self, KRKi, Kt, host_skip, host_flagged, min_act_dist, min_trace_quality=3.0):
+        """returns (action[n_pool] uint8: 0 keep / 1 delete / 2 activate, (n_accepted, n_deleted))"""
+        KRKi, Kt = f32(KRKi).reshape(-1, 9), f32(Kt).reshape(-1, 3)
+        sk = np.ascontiguousarray(host_skip, dtype=np.uint8); fl = np.ascontiguousarray(host_flagged, dtype=np.uint8)
+        assert len(sk) == len(KRKi) == len(fl) == len(Kt)
+        act = np.zeros(max(self.imm_n, 1), np.uint8)
+        cnt = np.zeros(2, np.int32)
+        self._call("immature_select_activation", C.c_int(len(KRKi)), _fp(KRKi), _fp(Kt), sk.ctypes.data_as(C.c_void_p),
+                   fl.ctypes.data_as(C.c_void_p), C.c_float(min_act_dist), C.c_float(min_trace_quality),
+                   act.ctypes.data_as(C.c_void_p), _ip(cnt))
+        return act[:self.imm_n], (int(cnt[0]), int(cnt[1]))
 
     def immature_activate(self, cand, min_obs=1):
         cand = np.ascontiguousarray(cand, dtype=np.int32)

@@ -1,0 +1,40 @@
+// immature.h — device-resident pool of immature points (K5 / K6 / N2), internal to libldso_gpu.so
+#pragma once
+#include "ctx.h"
+
+struct ImmatureDev {
+    int cap = 0, n = 0;
+    int *host = nullptr, *status = nullptr;
+    float *u = nullptr, *v = nullptr, *color = nullptr, *weights = nullptr, *gradH = nullptr, *energyTH = nullptr;
+    float *idmin = nullptr, *idmax = nullptr, *quality = nullptr, *lastUV = nullptr, *interval = nullptr;
+    float* type = nullptr;                   // ImmaturePoint::my_type (1 / 2 / 4: the selector level the pixel came from)
+    // second set of pool arrays: compaction writes here, then the two sets swap
+    int *host2 = nullptr, *status2 = nullptr;
+    float *u2 = nullptr, *v2 = nullptr, *color2 = nullptr, *weights2 = nullptr, *gradH2 = nullptr, *energyTH2 = nullptr;
+    float *idmin2 = nullptr, *idmax2 = nullptr, *quality2 = nullptr, *lastUV2 = nullptr, *interval2 = nullptr;
+    float* type2 = nullptr;
+    int *keep = nullptr, *pos = nullptr;     // [cap + 1] compaction flags / exclusive scan
+    float* tables = nullptr;                 // per-host KRKi[9] Kt[3] aff[2] (stride 16)
+    int* counts = nullptr;                   // [8]
+    // activation scratch
+    int* cand = nullptr;                     // [cap]
+    float* act_idepth = nullptr;             // [cap]
+    int* act_ok = nullptr;                   // [cap]
+    int* act_state = nullptr;                // [cap][LDSO_MAX_WINDOW]
+    // create scratch: u, v in; color[8], weights[8], gradH[3], energyTH out
+    float* cr = nullptr;                     // [cap][22]
+    // N2: CoarseDistanceMap (level-1 grid, one byte per cell: BFS ring 0..39, 255 = the reference's 1000) and the
+    // activation walk's outputs
+    unsigned char* dmap = nullptr;           // [w1 * h1] (+ padding to a multiple of 16)
+    unsigned char* action = nullptr;         // [cap] 0 keep, 1 delete, 2 candidate
+    int* sel_cnt = nullptr;                  // [4] candidates, deleted
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+};
+
+struct PoolPtrs {
+    int *host, *status;
+    float *u, *v, *color, *weights, *gradH, *energyTH, *idmin, *idmax, *quality, *lastUV, *interval, *type;
+};
+
+ImmatureDev* immature_pool(ldso_gpu_ctx* c);   // allocates on first use; nullptr (and the ctx error set) on failure

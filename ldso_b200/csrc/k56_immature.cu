@@ -7,7 +7,7 @@
 // Hessian and step is bit-identical to a sequential strict-IEEE evaluation of the reference loops and no
 // status / accept decision can flip on summation order.  The epipolar search keeps its per-step energies in
 // shared memory (100 floats per point) for the second-best scan of :213-219.
-#include "ctx.h"
+#include "immature.h"
 
 #include <algorithm>
 
@@ -16,28 +16,6 @@ namespace {
 constexpr int IM_THREADS = 128;              // 16 points per CTA
 constexpr int IM_PTS = IM_THREADS / 8;
 
-struct ImmatureDev {
-    int cap = 0, n = 0;
-    int *host = nullptr, *status = nullptr;
-    float *u = nullptr, *v = nullptr, *color = nullptr, *weights = nullptr, *gradH = nullptr, *energyTH = nullptr;
-    float *idmin = nullptr, *idmax = nullptr, *quality = nullptr, *lastUV = nullptr, *interval = nullptr;
-    // second set of pool arrays: compaction writes here, then the two sets swap
-    int *host2 = nullptr, *status2 = nullptr;
-    float *u2 = nullptr, *v2 = nullptr, *color2 = nullptr, *weights2 = nullptr, *gradH2 = nullptr, *energyTH2 = nullptr;
-    float *idmin2 = nullptr, *idmax2 = nullptr, *quality2 = nullptr, *lastUV2 = nullptr, *interval2 = nullptr;
-    int *keep = nullptr, *pos = nullptr;     // [cap + 1] compaction flags / exclusive scan
-    float* tables = nullptr;                 // per-host KRKi[9] Kt[3] aff[2] (stride 16)
-    int* counts = nullptr;                   // [8]
-    // activation scratch
-    int* cand = nullptr;                     // [cap]
-    float* act_idepth = nullptr;             // [cap]
-    int* act_ok = nullptr;                   // [cap]
-    int* act_state = nullptr;                // [cap][LDSO_MAX_WINDOW]
-    // create scratch: u, v in; color[8], weights[8], gradH[3], energyTH out
-    float* cr = nullptr;                     // [cap][22]
-    void* pinned = nullptr;
-    size_t pinned_bytes = 0;
-};
 
 __device__ __forceinline__ float seq8(float v, int base) {
     float s = 0.f;
@@ -480,10 +458,6 @@ __global__ void __launch_bounds__(IM_THREADS) k6_activate_kernel(const K6Params 
 }
 
 // ---- device-resident pool maintenance --------------------------------------------------------------------------
-struct PoolPtrs {
-    int *host, *status;
-    float *u, *v, *color, *weights, *gradH, *energyTH, *idmin, *idmax, *quality, *lastUV, *interval;
-};
 
 __global__ void im_flag_kernel(int n, const int* __restrict__ host, const int* __restrict__ status, int drop_host, int drop_oob,
                                int* __restrict__ keep) {
@@ -492,6 +466,10 @@ __global__ void im_flag_kernel(int n, const int* __restrict__ host, const int* _
     // keep[] was cleared to 0 and the explicit removals were marked -1 before this launch
     const bool rm = keep[i] < 0 || (drop_host >= 0 && host[i] == drop_host) || (drop_oob && status[i] == 1);
     keep[i] = rm ? 0 : 1;
+}
+__global__ void im_fill_kernel(int n, float v, float* __restrict__ dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = v;
 }
 __global__ void im_mark_kernel(int n_remove, const int* __restrict__ idx, int* __restrict__ keep) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -531,6 +509,7 @@ __global__ void im_scatter_kernel(int n, const int* __restrict__ keep, const int
     b.status[o] = a.status[i];
     b.u[o] = a.u[i]; b.v[o] = a.v[i]; b.energyTH[o] = a.energyTH[i];
     b.idmin[o] = a.idmin[i]; b.idmax[o] = a.idmax[i]; b.quality[o] = a.quality[i]; b.interval[o] = a.interval[i];
+    b.type[o] = a.type[i];
     b.lastUV[2 * o] = a.lastUV[2 * i]; b.lastUV[2 * o + 1] = a.lastUV[2 * i + 1];
     b.gradH[3 * o] = a.gradH[3 * i]; b.gradH[3 * o + 1] = a.gradH[3 * i + 1]; b.gradH[3 * o + 2] = a.gradH[3 * i + 2];
     const float4* ca = reinterpret_cast<const float4*>(a.color + 8 * (size_t)i);
@@ -554,10 +533,13 @@ __global__ void im_append_kernel(int n, int base, int host_idx, const float* __r
     a.status[o] = isfinite(eth) ? 5 : 1;     // a non-finite patch never becomes a point (FullSystem.cc:1456-1458): OOB
     a.idmin[o] = 0.f; a.idmax[o] = __int_as_float(0x7fc00000); a.quality[o] = 10000.f;
     a.lastUV[2 * o] = 0.f; a.lastUV[2 * o + 1] = 0.f; a.interval[o] = 0.f;
+    a.type[o] = 1.f;
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------
-ImmatureDev* pool(ldso_gpu_ctx* c) {
+}  // namespace
+
+ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     if (c->immature) return (ImmatureDev*)c->immature;
     ImmatureDev* P = new ImmatureDev();
     P->cap = c->cfg.max_immature > 16 ? c->cfg.max_immature : 16;
@@ -567,7 +549,8 @@ ImmatureDev* pool(ldso_gpu_ctx* c) {
     da((void**)&P->host, 4 * N); da((void**)&P->status, 4 * N); da((void**)&P->u, 4 * N); da((void**)&P->v, 4 * N);
     da((void**)&P->color, 32 * N); da((void**)&P->weights, 32 * N); da((void**)&P->gradH, 12 * N); da((void**)&P->energyTH, 4 * N);
     da((void**)&P->idmin, 4 * N); da((void**)&P->idmax, 4 * N); da((void**)&P->quality, 4 * N); da((void**)&P->lastUV, 8 * N);
-    da((void**)&P->interval, 4 * N);
+    da((void**)&P->interval, 4 * N); da((void**)&P->type, 4 * N); da((void**)&P->type2, 4 * N);
+    da((void**)&P->dmap, (size_t)c->wG[1] * c->hG[1] + 64); da((void**)&P->action, N); da((void**)&P->sel_cnt, 16);
     da((void**)&P->host2, 4 * N); da((void**)&P->status2, 4 * N); da((void**)&P->u2, 4 * N); da((void**)&P->v2, 4 * N);
     da((void**)&P->color2, 32 * N); da((void**)&P->weights2, 32 * N); da((void**)&P->gradH2, 12 * N); da((void**)&P->energyTH2, 4 * N);
     da((void**)&P->idmin2, 4 * N); da((void**)&P->idmax2, 4 * N); da((void**)&P->quality2, 4 * N); da((void**)&P->lastUV2, 8 * N);
@@ -582,7 +565,6 @@ ImmatureDev* pool(ldso_gpu_ctx* c) {
     return P;
 }
 
-}  // namespace
 
 void immature_free(ldso_gpu_ctx* c) {
     ImmatureDev* P = (ImmatureDev*)c->immature;
@@ -590,7 +572,7 @@ void immature_free(ldso_gpu_ctx* c) {
     void* ptrs[] = {P->host, P->status, P->u, P->v, P->color, P->weights, P->gradH, P->energyTH, P->idmin, P->idmax, P->quality,
                     P->lastUV, P->interval, P->tables, P->counts, P->cand, P->act_idepth, P->act_ok, P->act_state, P->cr,
                     P->host2, P->status2, P->u2, P->v2, P->color2, P->weights2, P->gradH2, P->energyTH2, P->idmin2, P->idmax2,
-                    P->quality2, P->lastUV2, P->interval2, P->keep, P->pos};
+                    P->quality2, P->lastUV2, P->interval2, P->keep, P->pos, P->type, P->type2, P->dmap, P->action, P->sel_cnt};
     for (void* p : ptrs) cudaFree(p);
     if (P->pinned) cudaFreeHost(P->pinned);
     delete P;
@@ -599,7 +581,7 @@ void immature_free(ldso_gpu_ctx* c) {
 
 extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const float* u, const float* v, float* color,
                                         float* weights, float* grad_h, float* energy_th) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && n <= P->cap);
     if (n == 0) return 0;
@@ -626,7 +608,7 @@ extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const 
 extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, const float* u, const float* v, const float* color,
                                      const float* weights, const float* grad_h, const float* energy_th, const float* idepth_min,
                                      const float* idepth_max, const float* quality, const int* status) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n >= 0 && n <= P->cap);
     P->n = n;
@@ -649,13 +631,14 @@ extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, co
     LDSO_CUDA_OK(c, put(P->quality, quality, 4 * N));
     LDSO_CUDA_OK(c, cudaMemsetAsync(P->lastUV, 0, 8 * N, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(P->interval, 0, 4 * N, c->stream));
+    im_fill_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, 1.f, P->type);   // my_type: see ldso_gpu_immature_set_types
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     return 0;
 }
 
 extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
                                        const float* aff, int counts_out[6]) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt &&
                         aff && counts_out);
@@ -694,7 +677,7 @@ extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_host
 
 extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* idepth_max, float* quality, int* status,
                                      float* last_trace_uv, float* last_trace_pixel_interval) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     const size_t N = P->n;
     if (N == 0) return 0;
@@ -719,7 +702,7 @@ extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* 
 
 extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int* cand, int min_obs, float* idepth_out,
                                           int* ok_out, int* res_state_out) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, n_cand >= 0 && n_cand <= P->cap && W.n >= 1);
@@ -753,14 +736,14 @@ extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int
 
 static PoolPtrs pool_ptrs(ImmatureDev* P, bool alt) {
     if (!alt) return {P->host, P->status, P->u, P->v, P->color, P->weights, P->gradH, P->energyTH, P->idmin, P->idmax, P->quality,
-                      P->lastUV, P->interval};
+                      P->lastUV, P->interval, P->type};
     return {P->host2, P->status2, P->u2, P->v2, P->color2, P->weights2, P->gradH2, P->energyTH2, P->idmin2, P->idmax2, P->quality2,
-            P->lastUV2, P->interval2};
+            P->lastUV2, P->interval2, P->type2};
 }
 
 extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int drop_oob, int n_remove, const int* remove_idx,
                                          int* n_out) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n_remove >= 0 && n_remove <= P->n && (n_remove == 0 || remove_idx) && n_out);
     const int n = P->n;
@@ -786,7 +769,7 @@ extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int dro
     std::swap(P->host, P->host2); std::swap(P->status, P->status2); std::swap(P->u, P->u2); std::swap(P->v, P->v2);
     std::swap(P->color, P->color2); std::swap(P->weights, P->weights2); std::swap(P->gradH, P->gradH2);
     std::swap(P->energyTH, P->energyTH2); std::swap(P->idmin, P->idmin2); std::swap(P->idmax, P->idmax2);
-    std::swap(P->quality, P->quality2); std::swap(P->lastUV, P->lastUV2); std::swap(P->interval, P->interval2);
+    std::swap(P->quality, P->quality2); std::swap(P->lastUV, P->lastUV2); std::swap(P->interval, P->interval2); std::swap(P->type, P->type2);
     P->n = *total;
     *n_out = P->n;
     return 0;
@@ -794,7 +777,7 @@ extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int dro
 
 extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx, int n, const float* u, const float* v,
                                         int* n_pool) {
-    ImmatureDev* P = pool(c);
+    ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && P->n + n <= P->cap && n_pool);
     LDSO_REQUIRE(c, host_idx >= 0 && host_idx < LDSO_MAX_WINDOW && (n == 0 || (u && v)));

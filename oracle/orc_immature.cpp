@@ -14,7 +14,10 @@ const int patternP[8][2] = {{0, -2}, {-1, -1}, {1, -1}, {-2, 0}, {0, 0}, {2, 0},
 struct Pool {
     int n = 0;
     std::vector<int> host, status;
-    std::vector<float> u, v, color, weights, gradH, energyTH, idepth_min, idepth_max, quality, lastUV, lastInterval;
+    std::vector<float> u, v, color, weights, gradH, energyTH, idepth_min, idepth_max, quality, lastUV, lastInterval, type;
+    // CoarseDistanceMap (include/frontend/CoarseTracker.h:120-160): fwdWarpedIDDistFinal and the two BFS lists
+    std::vector<float> dist;
+    std::vector<int> bfs1, bfs2;
 };
 Pool& pool_of(orc_ctx* c) {
     if (!c->immature) c->immature = std::make_shared<Pool>();
@@ -88,7 +91,7 @@ extern "C" int orc_immature_set(orc_ctx* c, int n, const int* host, const float*
     P.u.assign(u, u + n); P.v.assign(v, v + n); P.color.assign(color, color + 8 * n); P.weights.assign(weights, weights + 8 * n);
     P.gradH.assign(gradH, gradH + 3 * n); P.energyTH.assign(energyTH, energyTH + n);
     P.idepth_min.assign(idmin, idmin + n); P.idepth_max.assign(idmax, idmax + n); P.quality.assign(quality, quality + n);
-    P.lastUV.assign(2 * n, 0.f); P.lastInterval.assign(n, 0.f);
+    P.lastUV.assign(2 * n, 0.f); P.lastInterval.assign(n, 0.f); P.type.assign(n, 1.f);
     return 0;
 }
 
@@ -373,6 +376,7 @@ extern "C" int orc_immature_compact(orc_ctx* c, int drop_host, int drop_oob, int
         P.host[o] = (drop_host >= 0 && P.host[i] > drop_host) ? P.host[i] - 1 : P.host[i];
         P.status[o] = P.status[i]; P.u[o] = P.u[i]; P.v[o] = P.v[i]; P.energyTH[o] = P.energyTH[i];
         P.idepth_min[o] = P.idepth_min[i]; P.idepth_max[o] = P.idepth_max[i]; P.quality[o] = P.quality[i];
+        P.type[o] = P.type[i];
         P.lastInterval[o] = P.lastInterval[i]; P.lastUV[2 * o] = P.lastUV[2 * i]; P.lastUV[2 * o + 1] = P.lastUV[2 * i + 1];
         for (int k = 0; k < 3; k++) P.gradH[3 * o + k] = P.gradH[3 * i + k];
         for (int k = 0; k < 8; k++) { P.color[8 * o + k] = P.color[8 * i + k]; P.weights[8 * o + k] = P.weights[8 * i + k]; }
@@ -390,9 +394,10 @@ extern "C" int orc_immature_append(orc_ctx* c, int slot, int host_idx, int n, co
     const size_t N = (size_t)P.n + n;
     P.host.resize(N); P.status.resize(N); P.u.resize(N); P.v.resize(N); P.energyTH.resize(N); P.idepth_min.resize(N);
     P.idepth_max.resize(N); P.quality.resize(N); P.lastInterval.resize(N); P.lastUV.resize(2 * N); P.gradH.resize(3 * N);
-    P.color.resize(8 * N); P.weights.resize(8 * N);
+    P.color.resize(8 * N); P.weights.resize(8 * N); P.type.resize(N);
     for (int i = 0; i < n; i++) {
         const int o = P.n + i;
+        P.type[o] = 1;
         P.host[o] = host_idx; P.u[o] = u[i]; P.v[o] = v[i]; P.energyTH[o] = eth[i];
         P.status[o] = std::isfinite(eth[i]) ? 5 : 1;
         P.idepth_min[o] = 0; P.idepth_max[o] = NAN; P.quality[o] = 10000; P.lastInterval[o] = 0;
@@ -402,5 +407,120 @@ extern "C" int orc_immature_append(orc_ctx* c, int slot, int host_idx, int n, co
     }
     P.n = (int)N;
     *n_pool = P.n;
+    return 0;
+}
+
+// ================================================================================================
+// N2 — CoarseDistanceMap (src/frontend/CoarseTracker.cc:795-930) and the candidate walk of
+// FullSystem::activatePointsMT (src/frontend/FullSystem.cc:1226-1298)
+extern "C" int orc_immature_set_types(orc_ctx* c, int first, int n, const float* type) {
+    Pool& P = pool_of(c);
+    if (first < 0 || n < 0 || first + n > P.n) return -2;
+    for (int i = 0; i < n; i++) P.type[first + i] = type[i];
+    return 0;
+}
+
+namespace {
+// CoarseDistanceMap::growDistBFS (:828-923); the lists hold packed (x, y)
+void grow_dist_bfs(orc_ctx* c, Pool& P, int bfsNum) {
+    const int w1 = c->wG[1], h1 = c->hG[1];
+    float* D = P.dist.data();
+    for (int k = 1; k < 40; k++) {
+        int bfsNum2 = bfsNum;
+        std::swap(P.bfs1, P.bfs2);
+        bfsNum = 0;
+        auto visit = [&](int x, int y) {
+            float& d = D[x + y * w1];
+            if (d > k) { d = (float)k; P.bfs1[2 * bfsNum] = x; P.bfs1[2 * bfsNum + 1] = y; bfsNum++; }
+        };
+        for (int i = 0; i < bfsNum2; i++) {
+            int x = P.bfs2[2 * i], y = P.bfs2[2 * i + 1];
+            if (x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1) continue;
+            visit(x + 1, y); visit(x - 1, y); visit(x, y + 1); visit(x, y - 1);
+            if (k % 2 != 0) { visit(x + 1, y + 1); visit(x - 1, y + 1); visit(x - 1, y - 1); visit(x + 1, y - 1); }
+        }
+    }
+}
+void dist_alloc(orc_ctx* c, Pool& P) {
+    const size_t wh1 = (size_t)c->wG[1] * c->hG[1];
+    if (P.dist.size() != wh1) { P.dist.assign(wh1, 1000.f); P.bfs1.assign(2 * wh1, 0); P.bfs2.assign(2 * wh1, 0); }
+}
+}  // namespace
+
+extern "C" int orc_distmap_make(orc_ctx* c, int n_hosts, const float* KRKi, const float* Kt, int n_points, const int* host,
+                                const float* u, const float* v, const float* idepth) {
+    Pool& P = pool_of(c);
+    dist_alloc(c, P);
+    const int w1 = c->wG[1], h1 = c->hG[1];
+    for (auto& d : P.dist) d = 1000;
+    int numItems = 0;
+    for (int i = 0; i < n_points; i++) {
+        const int h = host[i];
+        if (h < 0) continue;
+        if (h >= n_hosts) return -2;
+        const float *K = KRKi + 9 * h, *t = Kt + 3 * h;
+        float ptp[3];
+        for (int r = 0; r < 3; r++) ptp[r] = (K[3 * r] * u[i] + K[3 * r + 1] * v[i] + K[3 * r + 2] * 1) + t[r] * idepth[i];
+        int x = ptp[0] / ptp[2] + 0.5f;
+        int y = ptp[1] / ptp[2] + 0.5f;
+        if (!(x > 0 && y > 0 && x < w1 && y < h1)) continue;
+        P.dist[x + w1 * y] = 0;
+        P.bfs1[2 * numItems] = x; P.bfs1[2 * numItems + 1] = y;
+        numItems++;
+        if (2 * (size_t)(numItems + 1) > P.bfs1.size()) { P.bfs1.resize(2 * P.bfs1.size()); P.bfs2.resize(P.bfs1.size()); }
+    }
+    grow_dist_bfs(c, P, numItems);
+    return 0;
+}
+
+extern "C" int orc_distmap_get(orc_ctx* c, float* dist) {
+    Pool& P = pool_of(c);
+    dist_alloc(c, P);
+    std::copy(P.dist.begin(), P.dist.end(), dist);
+    return 0;
+}
+
+extern "C" int orc_immature_select_activation(orc_ctx* c, int n_hosts, const float* KRKi, const float* Kt,
+                                              const unsigned char* host_skip, const unsigned char* host_flagged,
+                                              float currentMinActDist, float minTraceQuality, unsigned char* action_out,
+                                              int counts_out[2]) {
+    Pool& P = pool_of(c);
+    dist_alloc(c, P);
+    const int w1 = c->wG[1], h1 = c->hG[1];
+    counts_out[0] = counts_out[1] = 0;
+    for (int i = 0; i < P.n; i++) {
+        const int h = P.host[i];
+        if (h < 0 || h >= n_hosts) return -2;
+        action_out[i] = 0;
+        if (host_skip[h]) continue;                                           // host == newestFr (:1231)
+        const int st = P.status[i];
+        if (!std::isfinite(P.idepth_max[i]) || st == 2) { action_out[i] = 1; counts_out[1]++; continue; }   // :1247-1251
+        const bool canActivate = (st == 0 || st == 3 || st == 4 || st == 1) && P.lastInterval[i] < 8 &&
+                                 P.quality[i] > minTraceQuality && (P.idepth_max[i] + P.idepth_min[i]) > 0;       // :1253-1259
+        if (!canActivate) {
+            if (host_flagged[h] || st == 1) { action_out[i] = 1; counts_out[1]++; }                           // :1261-1268
+            continue;
+        }
+        const float *K = KRKi + 9 * h, *t = Kt + 3 * h;
+        const float idp = 0.5f * (P.idepth_max[i] + P.idepth_min[i]);
+        float ptp[3];
+        for (int r = 0; r < 3; r++) ptp[r] = (K[3 * r] * P.u[i] + K[3 * r + 1] * P.v[i] + K[3 * r + 2] * 1) + t[r] * idp;
+        const float px = ptp[0] / ptp[2], py = ptp[1] / ptp[2];
+        int x = px + 0.5f;
+        int y = py + 0.5f;
+        if (x > 0 && y > 0 && x < w1 && y < h1) {
+            // NOTE: the reference adds the fractional part of ptp[0] (not of ptp[0] / ptp[2]) — :1279-1280 reads
+            // `ptp[0] - floorf((float)(ptp[0]))` on the homogeneous coordinate; kept
+            float dist = P.dist[x + w1 * y] + (ptp[0] - floorf((float)(ptp[0])));
+            if (dist >= currentMinActDist * P.type[i]) {
+                P.bfs1[0] = x; P.bfs1[1] = y;                                // addIntoDistFinal (:925-930)
+                P.dist[x + w1 * y] = 0;
+                grow_dist_bfs(c, P, 1);
+                action_out[i] = 2; counts_out[0]++;
+            }
+        } else {
+            action_out[i] = 1; counts_out[1]++;
+        }
+    }
     return 0;
 }
