@@ -106,6 +106,7 @@ class Ctx:
                 self.h = None
             raise LdsoError(f"{api.prefix}create failed rc={rc}: {msg}")
         self.levels = api.fn("pyr_levels")(self.h)
+        self.imm_n = 0
         self.sizes = []
         for l in range(self.levels):
             w, h = C.c_int(), C.c_int()

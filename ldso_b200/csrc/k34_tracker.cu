@@ -385,6 +385,58 @@ __device__ int lm_decide(const LmConst& k, LmState& s, const double* r, TrkParam
     return s.it >= k.maxIt ? LM_DONE : LM_SOLVE;
 }
 
+// Register-resident 8x8 LDL^T without pivoting, one thread, fully unrolled (all indices static).  The damped tracker
+// system is symmetric positive definite, so the factorisation exists without pivoting and agrees with Eigen's pivoted
+// LDLT (CoarseTracker.cc:159-179) to fp64 rounding (~1e-13 relative, eight orders below the fp32 noise of H).  A pivot
+// that is not safely positive sends the caller to the pivoted warp version below, which mirrors the oracle's
+// operation order and handles semi-definite systems.  Dependent chain: 8 x (div, mul, fma) + 16 substitution steps,
+// about 1 us against 6 us for the shared-memory warp version.
+__device__ __forceinline__ bool lm_ldlt8_fast(const double* H, const double* bv, float lambda, int mode, double* inc) {
+    double a[8][8];   // lower triangle used
+    double dmax = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) {
+            double v = (mode == 1 && j < i) ? 0.0 : H[i * 8 + j];
+            if (i == j) { v *= (1 + lambda); dmax = fmax(dmax, fabs(v)); }
+            a[i][j] = v;
+        }
+    double y[8], inv[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) y[i] = -bv[i];
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const double d = a[k][k];
+        ok = ok && (d > 1e-12 * dmax);
+        inv[k] = 1.0 / d;
+        double l[8];
+#pragma unroll
+        for (int i = k + 1; i < 8; i++) l[i] = a[i][k] * inv[k];
+#pragma unroll
+        for (int i = k + 1; i < 8; i++)
+#pragma unroll
+            for (int j = k + 1; j <= i; j++) a[i][j] -= l[i] * a[j][k];
+#pragma unroll
+        for (int i = k + 1; i < 8; i++) a[i][k] = l[i];
+    }
+    if (!ok) return false;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < i; j++) y[i] -= a[i][j] * y[j];
+#pragma unroll
+    for (int i = 0; i < 8; i++) y[i] *= inv[i];
+#pragma unroll
+    for (int i = 7; i >= 0; i--)
+#pragma unroll
+        for (int j = i + 1; j < 8; j++) y[i] -= a[j][i] * y[j];
+#pragma unroll
+    for (int i = 0; i < 8; i++) inc[i] = y[i];
+    return true;
+}
+
 // LDLT with diagonal pivoting of the damped system on one warp: lane l owns matrix elements l and l + 32 of the 8x8
 // array in shared memory.  Every element sees the same operations in the same order as in ldso_sm::ldlt_solve
 // (the lower triangle is eliminated, the upper one mirrors it), so the factor is bit-identical to the serial code.
@@ -580,12 +632,23 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
         if (k.dbg == 1) { if (ev == 11) break; continue; }
         if (threadIdx.x < 45) lm_Hb_entry(s_res, st.H[st.hsel ^ 1], st.bv[st.hsel ^ 1], threadIdx.x);
         __syncthreads();
-        if (threadIdx.x == 0) s_cmd = lm_decide(k, st, s_res, sp);
+        const bool fixed = k.optA < 0 || k.optB < 0;
+        if (threadIdx.x == 0) {
+            // decide -> solve -> candidate on one thread without a barrier in between (the common case)
+            int cmd = lm_decide(k, st, s_res, sp);
+            LM_TICK(3);
+            if (cmd == LM_SOLVE && !fixed && k.dbg != 4 &&
+                lm_ldlt8_fast(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, st.inc)) {
+                LM_TICK(4);
+                lm_candidate(k, st, sp);
+                LM_TICK(5);
+                cmd = LM_CONT;
+            }
+            s_cmd = cmd;
+        }
         __syncthreads();
-        LM_TICK(3);
         if (s_cmd == LM_DONE) break;
-        if (s_cmd == LM_SOLVE) {
-            const bool fixed = k.optA < 0 || k.optB < 0;
+        if (s_cmd == LM_SOLVE) {   // fixed affine parameters, or a pivot the fast factorisation refused
             if (!fixed && wid == 0) lm_ldlt8_warp(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, s_A, st.inc, lane);
             if (fixed && threadIdx.x == 0)
                 lm_solve_step_fixed(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, k.optA < 0, k.optB < 0, st.inc);

@@ -11,7 +11,8 @@ Deliberate simplifications (host-side orchestration is outside SURVEY section 8a
   * no marginalisation prior: points and frames that leave the window are dropped, HM = bM = 0, the gauge is held by a
     prior on the oldest keyframe; consequently Jacobians are evaluated at the current state (no FEJ, no linearised
     residuals) and steps are always accepted (setting_forceAceptStep = true in the reference, Setting.cc);
-  * activation spacing uses an occupancy grid at level-1 resolution instead of CoarseDistanceMap's BFS (8f N2)."""
+  * the immature pool lives on the device (append / trace / select_activation / activate / compact); the host keeps only
+    the static fields it needs to turn an activated point into a PointHessian (u, v, color, weights)."""
 import time
 
 import numpy as np
@@ -94,32 +95,15 @@ class Odometry:
             aff.append([a, b])
         return np.array(KRKi, np.float32), np.array(Kt, np.float32), np.array(aff, np.float32)
 
-    def upload_immature(self):
-        I = self.I
-        host_pos = self.positions(I["host"]).astype(np.int32)
-        self.ctx.immature_set(host_pos, I["u"], I["v"], I["color"], I["weights"], I["grad_h"], I["energy_th"], I["idepth_min"],
-                              I["idepth_max"], I["quality"], I["status"])
-
-    def sync_immature(self):
-        if self.I is None or len(self.I["host"]) == 0:
-            return
-        t = self.ctx.immature_get()
-        for k in ("idepth_min", "idepth_max", "quality", "status"):
-            self.I[k] = t[k]
-        self.I["interval"] = t["interval"]
-
     def make_new_traces(self, f):
-        """FullSystem::makeNewTraces (:1426-1482): selector + ImmaturePoint constructor on keyframe f"""
+        """FullSystem::makeNewTraces (:1426-1482): selector + ImmaturePoint constructor on keyframe f, appended to the device pool"""
         u, v, typ, self.potential = self.ctx.select_points(f["slot"], self.desired_immature, potential=self.potential, border=5)
         col, wgt, gh, eth = self.ctx.immature_create(f["slot"], u, v)
         ok = np.isfinite(eth)
         k = int(ok.sum())
-        new = dict(host=np.full(k, f["id"], np.int64), u=u[ok], v=v[ok], color=col[ok], weights=wgt[ok], grad_h=gh[ok],
-                   energy_th=eth[ok], idepth_min=np.zeros(k, np.float32), idepth_max=np.full(k, np.nan, np.float32),
-                   quality=np.full(k, 10000.0, np.float32), status=np.full(k, UNINIT, np.int32), interval=np.zeros(k, np.float32),
-                   type=typ[ok])
+        new = dict(host=np.full(k, f["id"], np.int64), u=u[ok], v=v[ok], color=col[ok], weights=wgt[ok], type=typ[ok])
         self.I = new if self.I is None else {k2: np.concatenate([self.I[k2], new[k2]]) for k2 in new}
-        self.upload_immature()
+        self.ctx.immature_append(f["slot"], len(self.frames) - 1, new["u"], new["v"], types=new["type"])
         return k
 
     # ---- per frame (FullSystem::addActiveFrame, :78-187) ---------------------------------------------
@@ -225,13 +209,12 @@ class Odometry:
     # ---- keyframe (FullSystem::makeKeyFrame, :485-699) -------------------------------------------------
     def make_keyframe(self, f):
         t = time.perf_counter()
-        self.sync_immature()
         drop = self.flag_frames_for_marginalization(f)
         self.frames.append(f)
         npts = len(self.P["host"])
         self.res = np.concatenate([self.res, np.full((npts, 1), IN, np.int8)], axis=1)     # new residuals into f (:549-560)
         t = self.tick("KF  pool sync + frame selection", t)
-        n_act = self.activate_points()
+        n_act = self.activate_points(drop)
         t = self.tick("KF  activatePointsMT (K6 + host candidate spacing)", t)
         rmse = self.optimize()
         t = self.tick("KF  optimize (K7-K10, H1 + host pose tables)", t)
@@ -252,6 +235,7 @@ class Odometry:
             if self.I is not None:
                 m = self.I["host"] != fr["id"]
                 self.I = {k: a[m] for k, a in self.I.items()}
+                self.ctx.immature_compact(drop_host=d, drop_oob=False)
         self.keep_points((self.res >= 0).sum(1) > 0)
         # setCoarseTrackingRef on the new keyframe (:614-621, CoarseTracker.cc:347-538)
         t = self.tick("KF  point / frame removal", t)
@@ -286,8 +270,19 @@ class Odometry:
                 best, best_score = i, s
         return [best]
 
-    def activate_points(self):
-        """FullSystem::activatePointsMT (:1197-1337)"""
+    def level1_tables(self):
+        """KRKi = K[1] R Ki[0], Kt = K[1] t of every window frame -> newest keyframe (FullSystem.cc:1236-1238)"""
+        newest = self.frames[-1]
+        K1 = self.K.copy(); K1[0, 0] *= 0.5; K1[1, 1] *= 0.5; K1[0, 2] = (K1[0, 2] + 0.5) / 2 - 0.5; K1[1, 2] = (K1[1, 2] + 0.5) / 2 - 0.5
+        KRKi, Kt = [], []
+        for fr in self.frames:
+            R, t = wh.se3_mul(newest["w2c"], wh.se3_inv(fr["w2c"]))
+            KRKi.append(K1 @ R.astype(np.float32) @ self.Ki); Kt.append(K1 @ t.astype(np.float32))
+        return np.array(KRKi, np.float32), np.array(Kt, np.float32)
+
+    def activate_points(self, flagged=()):
+        """FullSystem::activatePointsMT (:1197-1337): distance map, ordered candidate walk (N2) and activation (K6), all on
+        the device-resident pool"""
         I = self.I
         if I is None or len(I["host"]) == 0:
             return 0
@@ -303,57 +298,16 @@ class Odometry:
                     self.min_act_dist += d
                     break
         self.min_act_dist = float(np.clip(self.min_act_dist, 0.0, 4.0))
-        newest = self.frames[-1]
-        w1, h1 = self.c["w"] // 2, self.c["h"] // 2
-        K1 = self.K.astype(np.float64).copy(); K1[0, 0] *= 0.5; K1[1, 1] *= 0.5; K1[0, 2] = (K1[0, 2] + 0.5) / 2 - 0.5; K1[1, 2] = (K1[1, 2] + 0.5) / 2 - 0.5
-        Ki0 = self.Ki.astype(np.float64)
-
-        def project(host_ids, u, v, idp):
-            out = np.full((len(u), 2), -1.0)
-            for fr in self.frames[:-1]:
-                m = host_ids == fr["id"]
-                if not m.any():
-                    continue
-                R, t = wh.se3_mul(newest["w2c"], wh.se3_inv(fr["w2c"]))
-                p = (K1 @ R @ Ki0) @ np.stack([u[m], v[m], np.ones(m.sum())]) + (K1 @ t)[:, None] * idp[m]
-                out[m] = (p[:2] / p[2]).T
-                out[m][p[2] <= 0] = -1
-            return out
-        # distance map from the active points (CoarseDistanceMap::makeDistanceMap, CoarseTracker.cc:795-932, as an exact
-        # chessboard distance transform instead of the reference's 40-ring BFS)
-        from scipy import ndimage
-        occ = np.zeros((h1, w1), bool)
-        pa = project(self.P["host"], self.P["u"].astype(np.float64), self.P["v"].astype(np.float64), self.P["idepth"].astype(np.float64))
-        ok = (pa[:, 0] > 0) & (pa[:, 1] > 0) & (pa[:, 0] < w1 - 1) & (pa[:, 1] < h1 - 1)
-        occ[pa[ok, 1].astype(int), pa[ok, 0].astype(int)] = True
-        dist = ndimage.distance_transform_cdt(~occ, metric="chessboard").astype(np.float32) if occ.any() else np.full((h1, w1), 1000.0, np.float32)
-        st, itv = I["status"], I["interval"]
-        idm = (I["idepth_max"] + I["idepth_min"])
-        can = np.isin(st, (GOOD, SKIPPED, BADCOND, T_OOB)) & (itv < 8) & (I["quality"] > 3) & (idm > 0) & np.isfinite(I["idepth_max"])
-        can &= I["host"] != newest["id"]
-        delete = (~np.isfinite(I["idepth_max"]) & (st != UNINIT)) | (st == T_OUTLIER) | (~can & (st == T_OOB))
-        delete &= I["host"] != newest["id"]
-        pc = project(I["host"], I["u"].astype(np.float64), I["v"].astype(np.float64), 0.5 * idm.astype(np.float64))
-        cand = []
-        rad = 8
-        ky, kx = np.mgrid[-rad:rad + 1, -rad:rad + 1]
-        kern = np.maximum(np.abs(ky), np.abs(kx)).astype(np.float32)       # chessboard distance to the accepted pixel
-        fx = pc[:, 0] - np.floor(pc[:, 0])
-        inb = (pc[:, 0] > 0) & (pc[:, 1] > 0) & (pc[:, 0] < w1) & (pc[:, 1] < h1)
-        delete |= can & ~inb
-        thr = self.min_act_dist * I["type"]
-        for k in np.nonzero(can & inb)[0]:                                 # order-dependent (addIntoDistFinal), as in the reference
-            xi, yi = int(pc[k, 0]), int(pc[k, 1])
-            if dist[yi, xi] + fx[k] > thr[k]:
-                cand.append(k)
-                y0, y1, x0, x1 = max(0, yi - rad), min(h1, yi + rad + 1), max(0, xi - rad), min(w1, xi + rad + 1)
-                sub = dist[y0:y1, x0:x1]
-                np.minimum(sub, kern[y0 - yi + rad:y1 - yi + rad, x0 - xi + rad:x1 - xi + rad], out=sub)
+        n = len(self.frames)
+        KRKi, Kt = self.level1_tables()
+        self.ctx.distmap_make(KRKi, Kt, self.positions(self.P["host"]), self.P["u"], self.P["v"], self.P["idepth"])
+        skip = np.zeros(n, np.uint8); skip[-1] = 1
+        flg = np.zeros(n, np.uint8); flg[list(flagged)] = 1
+        action, _ = self.ctx.immature_select_activation(KRKi, Kt, skip, flg, self.min_act_dist)
+        cand = np.nonzero(action == 2)[0].astype(np.int32)
         n_ok = 0
-        if cand:
-            cand = np.array(cand, np.int32)
+        if len(cand):
             self.window_frames_only()
-            self.upload_immature()                                         # host indices = current window positions
             idp, okk, rst = self.ctx.immature_activate(cand, min_obs=1)
             good = okk == 1
             n_ok = int(good.sum())
@@ -365,8 +319,10 @@ class Odometry:
                 rs = rst[good].astype(np.int8)
                 rs[rs != IN] = -1                                          # only IN residuals are created (:1130-1150)
                 self.res = np.concatenate([self.res, rs], axis=0)
-            delete[cand] = True                                            # activated or discarded (:1301-1318)
-        self.I = {k: a[~delete] for k, a in I.items()}
+        gone = np.nonzero(action != 0)[0]                                  # deleted, activated or discarded (:1301-1318)
+        if len(gone):
+            self.ctx.immature_compact(drop_host=-1, drop_oob=False, remove=gone)
+            self.I = {k: a[action == 0] for k, a in I.items()}
         return n_ok
 
     # ---- window BA (FullSystem::optimize, :844-1007) ---------------------------------------------------
