@@ -430,15 +430,20 @@ extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot
     int nEval = 0, nAccept = 0, rc;
     TrackEvalOut ev;
     const bool device_lm = c->cfg.tracker_lm_mode == 0;
-    for (int lvl = coarsest_lvl; lvl >= 0; lvl--) {
+    if (device_lm) {
+        // the level loop with its LM iterations runs inside one cooperative kernel
+        int status = 0;
+        if ((rc = k34_track_all(c, tracker, coarsest_lvl, maxIterations, min_res_for_abort, cur, cur_a, cur_b, last_residuals, flow,
+                                &status, &nEval, &nAccept))) return rc;
+        if (status) {
+            if (iters_out) { iters_out[0] = nEval; iters_out[1] = nAccept; }
+            return 1;
+        }
+    }
+    for (int lvl = coarsest_lvl; lvl >= 0 && !device_lm; lvl--) {
         double H[64], b[8], resOld[6], resNew[6];
         float cutoffRepeat = 1;
-        if (device_lm) {
-            // the whole LM loop of this level runs inside one cooperative kernel
-            int ne = 0, na = 0;
-            if ((rc = k34_track_level(c, tracker, lvl, cur, cur_a, cur_b, maxIterations[lvl], resOld, &cutoffRepeat, &ne, &na))) return rc;
-            nEval += ne; nAccept += na;
-        } else {
+        {
             if ((rc = k34_eval(c, tracker, lvl, cur, cur_a, cur_b, c->cfg.coarse_cutoff_th * cutoffRepeat, &ev))) return rc;
             nEval++;
             fill_vec6(ev, resOld);

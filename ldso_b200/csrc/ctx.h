@@ -134,7 +134,8 @@ struct TrackEvalOut {
     double sums[48];   // 45 H entries (9x9 upper, row-major), E, flowT, flowRT
     int counts[4];     // numTermsInE, numSaturated, numTermsInWarped, flowNum
 };
-int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, float& aff_a, float& aff_b, int maxIt,
-                    double resOld[6], float* cutoffRepeat, int* nEval, int* nAccept);
+int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
+                  ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
+                  int* nEval, int* nAccept);
 int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew, float aff_a, float aff_b, float cutoffTH,
              TrackEvalOut* out);

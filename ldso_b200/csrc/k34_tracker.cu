@@ -210,13 +210,26 @@ namespace cg = cooperative_groups;
 // itself is a few hundred points per CTA either way
 constexpr int LM_MAX_CTAS = 32;
 
-struct LmConst {
+struct LmConst {                // the level being tracked; lives in shared memory, rewritten by thread 0 at each level start
     float Ki[9], fx, fy, cx, cy;
     int w, h, n, lvl, maxIt, solveMode, dbg;   // dbg (cfg.reserved[0], measurement only): 1 = fixed 12 evaluations without the LM transition, 2 = also without the fold
     float huberTH, coarseCutoff, optA, optB;
     float refExposure, newExposure, refAffA, refAffB;
     double q[4], t[3];          // initial refToNew
     float affA, affB;           // initial aff_g2l
+    const float4 *pc, *img;     // reference point cloud and new-frame image of this level
+};
+
+struct LmLevel {
+    float Ki[9], fx, fy, cx, cy;
+    int w, h, n, maxIt;
+    float minResForAbort;
+    const float4 *pc, *img;
+};
+struct LmAll {                  // kernel parameter of the all-levels tracker
+    LmConst base;               // everything that does not depend on the level + the initial pose
+    LmLevel lv[5];
+    int coarsest;
 };
 
 struct LmState {                // plain data: lives in shared memory, only thread 0 touches it
@@ -226,6 +239,10 @@ struct LmState {                // plain data: lives in shared memory, only thre
     double H[2][64], bv[2][8], resOld[6], inc[8];   // [hsel] = system at the accepted pose, [hsel ^ 1] = latest evaluation
     float lambda, cutoffRepeat;
     int it, phase, nEval, nAccept, hsel;
+    // across levels (CoarseTracker.cc:71-260)
+    int lvl, repeated, status;
+    float lastRes[5], flow[3];
+    double work;                // point evaluations so far (profile units)
 };
 
 __device__ inline ldso_sm::SE3 se3_of(const double* q, const double* t) {
@@ -536,9 +553,10 @@ __device__ void lm_candidate(const LmConst& k, LmState& s, TrkParams& p) {
 }
 
 __global__ void __launch_bounds__(TRK_THREADS)
-k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__ newImg, const LmConst k,
-                       float* __restrict__ partials, int* __restrict__ partials_i, double* __restrict__ mailbox, double seq) {
+k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restrict__ partials_i, double* __restrict__ mailbox,
+                       double seq) {
     cg::grid_group grid = cg::this_grid();
+    __shared__ LmConst k;
     __shared__ TrkParams sp;
     __shared__ LmState st;
     __shared__ double s_res[NF + NI];
@@ -553,21 +571,37 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int G = gridDim.x;
     if (threadIdx.x == 0) {
+        k = A.base;
         for (int i = 0; i < 4; i++) st.q[i] = k.q[i];
         for (int i = 0; i < 3; i++) st.t[i] = k.t[i];
         st.a = k.affA; st.b = k.affB;
-        st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.nEval = 0; st.nAccept = 0; st.lambda = 0.01f; st.hsel = 0;
+        st.nEval = 0; st.nAccept = 0; st.hsel = 0; st.lvl = A.coarsest; st.repeated = 0; st.status = 0; st.work = 0;
+        for (int i = 0; i < 5; i++) st.lastRes[i] = __int_as_float(0x7fc00000);
+        for (int i = 0; i < 3; i++) st.flow[i] = 1000.f;
+    }
+    __syncthreads();
+    tk = clock64();
+    int gev = 0;                 // evaluations since launch: selects the partials buffer across level boundaries too
+  while (true) {                 // one pass per pyramid level, coarsest first (CoarseTracker.cc:71)
+    if (threadIdx.x == 0) {
+        const LmLevel& L = A.lv[st.lvl];
+        for (int i = 0; i < 9; i++) k.Ki[i] = L.Ki[i];
+        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
+        k.pc = L.pc; k.img = L.img;
+        st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.lambda = 0.01f;
         for (int i = 0; i < 8; i++) st.inc[i] = 0;
         lm_make_params(k, st.q, st.t, st.a, st.b, k.coarseCutoff, sp);
     }
     __syncthreads();
-    tk = clock64();
-    for (int ev = 0;; ev++) {
+    const float4* __restrict__ pc = k.pc;
+    const float4* __restrict__ newImg = k.img;
+    const int npts = k.n;
+    for (int ev = 0;; ev++, gev++) {
         float acc[NF];
 #pragma unroll
         for (int q = 0; q < NF; q++) acc[q] = 0.f;
         int cnt[NI] = {0, 0, 0, 0};
-        for (int i = blockIdx.x * TRK_THREADS + threadIdx.x; i < k.n; i += G * TRK_THREADS)
+        for (int i = blockIdx.x * TRK_THREADS + threadIdx.x; i < npts; i += G * TRK_THREADS)
             eval_point(sp, __ldg(pc + i), i, newImg, acc, cnt[0], cnt[1], cnt[2], cnt[3]);
 #pragma unroll
         for (int q = 0; q < NF; q++) {
@@ -587,8 +621,8 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
             for (int q = 0; q < NI; q++) s_i[wid][q] = cnt[q];
         }
         __syncthreads();
-        float* pf = partials + (size_t)(ev & 1) * G * TRK_NRED;
-        int* pi = partials_i + (size_t)(ev & 1) * G * NI;
+        float* pf = partials + (size_t)(gev & 1) * G * TRK_NRED;
+        int* pi = partials_i + (size_t)(gev & 1) * G * NI;
         if (threadIdx.x < NF) {
             float v = 0.f;
 #pragma unroll
@@ -604,7 +638,7 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
         LM_TICK(0);
         grid.sync();
         LM_TICK(1);
-        if (k.dbg == 2) { if (ev == 11) break; continue; }
+        if (k.dbg == 2) { if (ev == 11) { gev++; break; } continue; }
         // every CTA folds all partials in the same fixed order (lanes stride over CTAs, then a shuffle tree); warp w owns
         // values w, w + 4, ...: 13 independent load streams per lane, so the fold costs about one L2 round trip
         {
@@ -629,12 +663,13 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
         }
         __syncthreads();
         LM_TICK(2);
-        if (k.dbg == 1) { if (ev == 11) break; continue; }
+        if (k.dbg == 1) { if (ev == 11) { gev++; break; } continue; }
         if (threadIdx.x < 45) lm_Hb_entry(s_res, st.H[st.hsel ^ 1], st.bv[st.hsel ^ 1], threadIdx.x);
         __syncthreads();
         const bool fixed = k.optA < 0 || k.optB < 0;
         if (threadIdx.x == 0) {
             // decide -> solve -> candidate on one thread without a barrier in between (the common case)
+            st.work += npts;
             int cmd = lm_decide(k, st, s_res, sp);
             LM_TICK(3);
             if (cmd == LM_SOLVE && !fixed && k.dbg != 4 &&
@@ -647,7 +682,7 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
             s_cmd = cmd;
         }
         __syncthreads();
-        if (s_cmd == LM_DONE) break;
+        if (s_cmd == LM_DONE) { gev++; break; }
         if (s_cmd == LM_SOLVE) {   // fixed affine parameters, or a pivot the fast factorisation refused
             if (!fixed && wid == 0) lm_ldlt8_warp(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, s_A, st.inc, lane);
             if (fixed && threadIdx.x == 0)
@@ -659,19 +694,41 @@ k34_track_level_kernel(const float4* __restrict__ pc, const float4* __restrict__
             LM_TICK(5);
         }
     }
+    // ---- between levels (CoarseTracker.cc:249-259): residual of the level, abort test, one repeat of a level whose
+    // cutoff had to be relaxed; every CTA takes the same decision from the same folded sums
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int lvl = st.lvl;
+        if (k.dbg != 1 && k.dbg != 2) {
+            st.lastRes[lvl] = sqrtf((float)(st.resOld[0] / st.resOld[1]));
+            st.flow[0] = (float)st.resOld[2]; st.flow[1] = (float)st.resOld[3]; st.flow[2] = (float)st.resOld[4];
+        }
+        int next = lvl;
+        if ((double)st.lastRes[lvl] > 1.5 * (double)A.lv[lvl].minResForAbort) { st.status = 1; next = -1; }
+        else {
+            if (st.cutoffRepeat > 1 && !st.repeated) { next++; st.repeated = 1; }
+            next--;
+        }
+        st.lvl = next;
+    }
+    __syncthreads();
+    if (st.lvl < 0) break;
+  }
     if (blockIdx.x != 0 || wid != 0) return;
-    // message to the host: pose (q, t), affine, resOld[6], cutoffRepeat, nEval, nAccept — then the sequence number
+    // message to the host: pose (q, t), affine, lastResiduals[5], flow[3], nEval, nAccept, status, work — then the sequence number
     double v = 0.0;
     if (lane < 4) v = st.q[lane];
     else if (lane < 7) v = st.t[lane - 4];
     else if (lane == 7) v = st.a;
     else if (lane == 8) v = st.b;
-    else if (lane < 15) v = st.resOld[lane - 9];
-    else if (lane == 15) v = st.cutoffRepeat;
-    else if (lane == 16) v = st.nEval;
-    else if (lane == 17) v = st.nAccept;
-    if (lane < 18) mailbox[lane] = v;
-    if (k.dbg == 3 && lane < 8) mailbox[20 + lane] = (double)s_t[lane];
+    else if (lane < 14) v = st.lastRes[lane - 9];
+    else if (lane < 17) v = st.flow[lane - 14];
+    else if (lane == 17) v = st.nEval;
+    else if (lane == 18) v = st.nAccept;
+    else if (lane == 19) v = st.status;
+    else if (lane == 20) v = st.work;
+    if (lane < 21) mailbox[lane] = v;
+    if (k.dbg == 3 && lane < 8) mailbox[24 + lane] = (double)s_t[lane];
     __threadfence_system();
     __syncwarp();
     if (lane == 0) *reinterpret_cast<volatile double*>(mailbox + 63) = seq;
@@ -740,14 +797,16 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     return 0;
 }
 
-// One pyramid level of trackNewestCoarse on the device (see k34_track_level_kernel).  In/out: pose, affine.
-int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, float& aff_a, float& aff_b, int maxIt,
-                    double resOld[6], float* cutoffRepeat, int* nEval, int* nAccept) {
+// trackNewestCoarse's level loop on the device (see k34_track_level_kernel): ONE cooperative launch walks the pyramid
+// from coarsest_lvl down, the host polls the mapped mailbox once.  In/out: pose, affine.
+int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
+                  ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
+                  int* nEval, int* nAccept) {
     TrackerDev& T = c->trk[tracker];
-    LmConst k;
-    for (int i = 0; i < 9; i++) k.Ki[i] = T.Ki[lvl][i];
-    k.fx = T.fx[lvl]; k.fy = T.fy[lvl]; k.cx = T.cx[lvl]; k.cy = T.cy[lvl];
-    k.w = T.w[lvl]; k.h = T.h[lvl]; k.n = T.pc_n[lvl]; k.lvl = lvl; k.maxIt = maxIt; k.solveMode = c->cfg.tracker_solve_mode;
+    LmAll A;
+    memset(&A, 0, sizeof(A));
+    LmConst& k = A.base;
+    k.solveMode = c->cfg.tracker_solve_mode;
     k.huberTH = c->cfg.huber_th; k.coarseCutoff = c->cfg.coarse_cutoff_th;
     k.optA = c->cfg.affine_opt_mode_a; k.optB = c->cfg.affine_opt_mode_b;
     k.refExposure = T.ref_exposure; k.newExposure = T.new_exposure; k.refAffA = T.ref_aff_a; k.refAffB = T.ref_aff_b;
@@ -755,6 +814,18 @@ int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, fl
     k.t[0] = cur.t[0]; k.t[1] = cur.t[1]; k.t[2] = cur.t[2];
     k.affA = aff_a; k.affB = aff_b;
     k.dbg = c->cfg.reserved[0];
+    A.coarsest = coarsest_lvl;
+    int nmax = 1;
+    for (int lvl = 0; lvl <= coarsest_lvl; lvl++) {
+        LmLevel& L = A.lv[lvl];
+        for (int i = 0; i < 9; i++) L.Ki[i] = T.Ki[lvl][i];
+        L.fx = T.fx[lvl]; L.fy = T.fy[lvl]; L.cx = T.cx[lvl]; L.cy = T.cy[lvl];
+        L.w = T.w[lvl]; L.h = T.h[lvl]; L.n = T.pc_n[lvl]; L.maxIt = maxIt[lvl];
+        L.minResForAbort = min_res_for_abort[lvl];
+        L.pc = T.pc[lvl];
+        L.img = c->frame[T.new_slot] + c->lvl_off[lvl];
+        nmax = std::max(nmax, L.n);
+    }
     if (c->trk_coop_max == 0) {
         int per_sm = 0, sms = 0, dev = 0, coop = 0;
         LDSO_CUDA_OK(c, cudaGetDevice(&dev));
@@ -764,15 +835,13 @@ int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, fl
         LDSO_CUDA_OK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k34_track_level_kernel, TRK_THREADS, 0));
         c->trk_coop_max = std::max(1, std::min(per_sm * sms, LM_MAX_CTAS));
     }
-    int blocks = std::max(1, (k.n + TRK_THREADS - 1) / TRK_THREADS);
+    int blocks = std::max(1, (nmax + TRK_THREADS - 1) / TRK_THREADS);   // sized for the finest level; coarser levels leave CTAs idle
     blocks = std::min(blocks, std::min(c->trk_coop_max, c->trk_max_blocks / 2));
-    const float4* pc = T.pc[lvl];
-    const float4* img = c->frame[T.new_slot] + c->lvl_off[lvl];
     float* pf = c->trk_partials;
     int* pi = c->trk_partials_i;
     double* mb = c->trk_mailbox_dev;
     double seq = (double)(++c->trk_seq);
-    void* args[] = {(void*)&pc, (void*)&img, (void*)&k, (void*)&pf, (void*)&pi, (void*)&mb, (void*)&seq};
+    void* args[] = {(void*)&A, (void*)&pf, (void*)&pi, (void*)&mb, (void*)&seq};
     prof_begin(c, c->stream);
     LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(TRK_THREADS), args, 0, c->stream));
     c->launches++;
@@ -787,14 +856,14 @@ int k34_track_level(ldso_gpu_ctx* c, int tracker, int lvl, ldso_sm::SE3& cur, fl
         }
     }
     std::atomic_thread_fence(std::memory_order_acquire);
-    c->d2h_bytes += 19 * sizeof(double);
+    c->d2h_bytes += 22 * sizeof(double);
     cur.qw = res[0]; cur.qx = res[1]; cur.qy = res[2]; cur.qz = res[3];
     cur.t[0] = res[4]; cur.t[1] = res[5]; cur.t[2] = res[6];
     aff_a = (float)res[7]; aff_b = (float)res[8];
-    for (int i = 0; i < 6; i++) resOld[i] = res[9 + i];
-    *cutoffRepeat = (float)res[15];
-    *nEval = (int)res[16]; *nAccept = (int)res[17];
-    if (prof_idx >= 0) c->prof_pending[prof_idx].units = (double)k.n * *nEval;   // point evaluations of this launch
-    if (k.dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[20 + i];
+    for (int i = 0; i < 5; i++) last_residuals[i] = (float)res[9 + i];
+    for (int i = 0; i < 3; i++) flow[i] = (float)res[14 + i];
+    *nEval = (int)res[17]; *nAccept = (int)res[18]; *status = (int)res[19];
+    if (prof_idx >= 0) c->prof_pending[prof_idx].units = res[20];   // point evaluations of this launch
+    if (k.dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[24 + i];
     return 0;
 }
