@@ -209,6 +209,7 @@ namespace cg = cooperative_groups;
 // CTAs of the cooperative launch: the grid barrier and the all-CTA fold both grow with the grid, the evaluation
 // itself is a few hundred points per CTA either way
 constexpr int LM_MAX_CTAS = 32;
+constexpr int LM_THREADS = 128;   // threads per CTA of the device-resident LM kernel (the fold uses its first four warps)
 
 struct LmConst {                // the level being tracked; lives in shared memory, rewritten by thread 0 at each level start
     float Ki[9], fx, fy, cx, cy;
@@ -552,7 +553,7 @@ __device__ void lm_candidate(const LmConst& k, LmState& s, TrkParams& p) {
     lm_make_params(k, s.cq, s.ct, s.ca, s.cb, k.coarseCutoff * s.cutoffRepeat, p);
 }
 
-__global__ void __launch_bounds__(TRK_THREADS)
+__global__ void __launch_bounds__(LM_THREADS)
 k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restrict__ partials_i, double* __restrict__ mailbox,
                        double seq) {
     cg::grid_group grid = cg::this_grid();
@@ -560,8 +561,8 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
     __shared__ TrkParams sp;
     __shared__ LmState st;
     __shared__ double s_res[NF + NI];
-    __shared__ float s_f[TRK_THREADS / 32][NF];
-    __shared__ int s_i[TRK_THREADS / 32][NI];
+    __shared__ float s_f[LM_THREADS / 32][NF];
+    __shared__ int s_i[LM_THREADS / 32][NI];
     __shared__ double s_A[64];
     __shared__ int s_cmd;
     __shared__ long long s_t[8];   // dbg == 3: SM clocks spent per phase (CTA 0, thread 0)
@@ -601,7 +602,7 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
 #pragma unroll
         for (int q = 0; q < NF; q++) acc[q] = 0.f;
         int cnt[NI] = {0, 0, 0, 0};
-        for (int i = blockIdx.x * TRK_THREADS + threadIdx.x; i < npts; i += G * TRK_THREADS)
+        for (int i = blockIdx.x * LM_THREADS + threadIdx.x; i < npts; i += G * LM_THREADS)
             eval_point(sp, __ldg(pc + i), i, newImg, acc, cnt[0], cnt[1], cnt[2], cnt[3]);
 #pragma unroll
         for (int q = 0; q < NF; q++) {
@@ -626,13 +627,13 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
         if (threadIdx.x < NF) {
             float v = 0.f;
 #pragma unroll
-            for (int wq = 0; wq < TRK_THREADS / 32; wq++) v += s_f[wq][threadIdx.x];
+            for (int wq = 0; wq < LM_THREADS / 32; wq++) v += s_f[wq][threadIdx.x];
             pf[threadIdx.x * G + blockIdx.x] = v;            // [value][CTA]: the fold reads whole rows
         } else if (threadIdx.x < NF + NI) {
             const int f = threadIdx.x - NF;
             int v = 0;
 #pragma unroll
-            for (int wq = 0; wq < TRK_THREADS / 32; wq++) v += s_i[wq][f];
+            for (int wq = 0; wq < LM_THREADS / 32; wq++) v += s_i[wq][f];
             pi[f * G + blockIdx.x] = v;
         }
         LM_TICK(0);
@@ -641,7 +642,7 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
         if (k.dbg == 2) { if (ev == 11) { gev++; break; } continue; }
         // every CTA folds all partials in the same fixed order (lanes stride over CTAs, then a shuffle tree); warp w owns
         // values w, w + 4, ...: 13 independent load streams per lane, so the fold costs about one L2 round trip
-        {
+        if (wid < 4) {
             double acc13[13];
 #pragma unroll
             for (int qq = 0; qq < 13; qq++) acc13[qq] = 0.0;
@@ -832,10 +833,10 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
         LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
         if (!coop) { c->set_error("device lacks cooperative launch", __FILE__, __LINE__); return -1; }
         LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        LDSO_CUDA_OK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k34_track_level_kernel, TRK_THREADS, 0));
+        LDSO_CUDA_OK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k34_track_level_kernel, LM_THREADS, 0));
         c->trk_coop_max = std::max(1, std::min(per_sm * sms, LM_MAX_CTAS));
     }
-    int blocks = std::max(1, (nmax + TRK_THREADS - 1) / TRK_THREADS);   // sized for the finest level; coarser levels leave CTAs idle
+    int blocks = std::max(1, (nmax + LM_THREADS - 1) / LM_THREADS);   // sized for the finest level; coarser levels leave CTAs idle
     blocks = std::min(blocks, std::min(c->trk_coop_max, c->trk_max_blocks / 2));
     float* pf = c->trk_partials;
     int* pi = c->trk_partials_i;
@@ -843,7 +844,7 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
     double seq = (double)(++c->trk_seq);
     void* args[] = {(void*)&A, (void*)&pf, (void*)&pi, (void*)&mb, (void*)&seq};
     prof_begin(c, c->stream);
-    LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(TRK_THREADS), args, 0, c->stream));
+    LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(LM_THREADS), args, 0, c->stream));
     c->launches++;
     const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
     volatile double* res = c->trk_mailbox;
