@@ -28,6 +28,9 @@ struct ImmatureDev {
     unsigned char* dmap = nullptr;           // [w1 * h1] (+ padding to a multiple of 16)
     unsigned char* action = nullptr;         // [cap] 0 keep, 1 delete, 2 candidate
     int* sel_cnt = nullptr;                  // [4] candidates, deleted
+    int* src_cells = nullptr;                // [src_cap] level-1 cell of every source of the map (active points, then accepted ones), -1 = none
+    int* src_n = nullptr;                    // device: length of the list
+    int src_cap = 0, src_n_host = 0;         // host: capacity and an upper bound of the current length
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
 };

@@ -558,6 +558,9 @@ ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 32);
     da((void**)&P->cand, 4 * N); da((void**)&P->act_idepth, 4 * N); da((void**)&P->act_ok, 4 * N);
     da((void**)&P->act_state, 4 * N * LDSO_MAX_WINDOW); da((void**)&P->cr, 4 * 22 * N);
+    P->src_cap = (int)(8 * N);
+    da((void**)&P->src_cells, 4 * (size_t)P->src_cap); da((void**)&P->src_n, 32);   // [0] length, [1..4] corner values after a walk
+    if (ok) cudaMemset(P->src_n, 0, 32);
     P->pinned_bytes = 4 * 32 * N + 4096;
     ok = ok && cudaMallocHost(&P->pinned, P->pinned_bytes) == cudaSuccess;
     c->immature = P;
@@ -572,7 +575,8 @@ void immature_free(ldso_gpu_ctx* c) {
     void* ptrs[] = {P->host, P->status, P->u, P->v, P->color, P->weights, P->gradH, P->energyTH, P->idmin, P->idmax, P->quality,
                     P->lastUV, P->interval, P->tables, P->counts, P->cand, P->act_idepth, P->act_ok, P->act_state, P->cr,
                     P->host2, P->status2, P->u2, P->v2, P->color2, P->weights2, P->gradH2, P->energyTH2, P->idmin2, P->idmax2,
-                    P->quality2, P->lastUV2, P->interval2, P->keep, P->pos, P->type, P->type2, P->dmap, P->action, P->sel_cnt};
+                    P->quality2, P->lastUV2, P->interval2, P->keep, P->pos, P->type, P->type2, P->dmap, P->action, P->sel_cnt,
+                    P->src_cells, P->src_n};
     for (void* p : ptrs) cudaFree(p);
     if (P->pinned) cudaFreeHost(P->pinned);
     delete P;

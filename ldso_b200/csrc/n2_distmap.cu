@@ -2,23 +2,34 @@
 // src/frontend/CoarseTracker.cc:795-930) and the candidate walk of FullSystem::activatePointsMT
 // (src/frontend/FullSystem.cc:1226-1298).
 //
-// The level-1 grid (w/2 x h/2: 76.8 k cells at 640x480) is held as ONE BYTE per cell in the shared memory of a single
-// CTA: ring number 0..39, 255 standing for the reference's 1000.f.
-//   * makeDistanceMap: the reference keeps explicit BFS lists; from a map that holds only 0 and 1000 the frontier of
-//     ring k is exactly the set of cells with value k - 1, so ring k is a stencil pass "value > k and a non-border
-//     neighbour (8-connected for odd k, 4-connected for even k) holds k - 1 -> k".  Writes only turn values > k into k
-//     and reads only test for k - 1, so the pass runs in place.  39 passes, 1024 threads, no global traffic.
+// The level-1 grid (w/2 x h/2: 76.8 k cells at 640x480) is held as ONE BYTE per cell: ring number 0..39, 255 standing
+// for the reference's 1000.f.
+//   * The reference grows explicit BFS lists ring by ring; ring k spreads over 8 neighbours when k is odd and over 4
+//     when k is even, never out of a border cell, and claims a cell only if it still holds more than k.  Because the
+//     neighbourhood of ring k depends on k alone, the grown map is the pointwise minimum over the sources of the
+//     single-source ring distance, which for interior cells has the closed form
+//         d(dx, dy) = max(a, k*),  a = max(|dx|,|dy|),  k* = least k with k + ceil(k/2) >= |dx| + |dy|
+//     (monotone shortest paths stay inside the bounding box of two interior cells, so the border rule never bites).
+//     A border cell c is claimed by the first interior neighbour q that can reach it: min over q of D[q] + 1, where a
+//     diagonal q only counts if D[q] + 1 is odd.  Sources on the border hold 0 and spread nothing.
+//     (tests/test_distmap.py pins the oracle's literal BFS against this form; the GPU is compared with the oracle.)
+//   * makeDistanceMap: n2_project_kernel turns the active points into a source-cell list, n2_map_kernel (one CTA per
+//     16x16 tile, sources filtered to those within 39 cells of the tile, in chunks through shared memory) takes the
+//     minimum for interior cells, n2_border_kernel finishes the border.  No ring iteration, no single-CTA pass.
 //   * the candidate walk is order dependent (every accepted point lowers the map for the ones after it) and stays
 //     sequential in pool order, but only over ACCEPTED points: all threads classify the pool in parallel first, then
-//     one warp tests 32 points at a time against the current map, accepts the first that passes, grows its rings with
-//     an explicit frontier (byte claims through atomicCAS on the containing word) and re-tests the lanes behind it.
-//     A rejected point can never become acceptable later (the map only decreases), so skipping them is exact.
+//     one warp tests 32 points at a time against a shared-memory copy of the map, accepts the first that passes, stamps
+//     its ring distances over the radius that can still change a decision (thresholds are <= 4 * minActDist) and
+//     re-tests the lanes behind it.  A rejected point can never become acceptable later (the map only decreases), so
+//     skipping them is exact.  Accepted cells are appended to the source list and the two map kernels rebuild the
+//     full-radius fwdWarpedIDDistFinal afterwards.
 #include "immature.h"
 
 namespace {
 
 constexpr int N2_THREADS = 1024;
-constexpr int N2_FCAP = 512;        // ring k of one source has at most 8k <= 312 cells
+constexpr int N2_TILE = 16;         // n2_map_kernel: cells per tile edge
+constexpr int N2_RMAX = 39;         // rings grown by growDistBFS
 
 __device__ __forceinline__ void project(const float* __restrict__ tab, int h, float u, float v, float idepth, float& px, float& py, float& p0) {
     const float* K = tab + 12 * h;
@@ -28,65 +39,110 @@ __device__ __forceinline__ void project(const float* __restrict__ tab, int h, fl
     px = p0 / p2; py = p1 / p2;
 }
 
-__device__ __forceinline__ void fill_map(unsigned char* D, int cells16) {
-    uint4* d4 = reinterpret_cast<uint4*>(D);
-    for (int i = threadIdx.x; i < cells16; i += blockDim.x) d4[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+// single-source ring distance between interior cells (see the header comment); >= 40 means "not reached"
+__device__ __forceinline__ int ring_dist(int dx, int dy) {
+    dx = abs(dx); dy = abs(dy);
+    const int a = max(dx, dy), s = dx + dy;
+    int k = (2 * s) / 3;
+    if (k + ((k + 1) >> 1) < s) k++;
+    return max(k, a);
 }
 
-__global__ void __launch_bounds__(N2_THREADS)
-n2_distmap_kernel(int w1, int h1, int n_points, const float* __restrict__ tab, const int* __restrict__ host,
-                  const float* __restrict__ u, const float* __restrict__ v, const float* __restrict__ idepth,
-                  unsigned char* __restrict__ dmap) {
-    extern __shared__ __align__(16) unsigned char D[];
-    const int cells = w1 * h1, cells16 = (cells + 15) / 16;
-    fill_map(D, cells16);
-    __syncthreads();
-    for (int i = threadIdx.x; i < n_points; i += N2_THREADS) {
-        const int h = host[i];
-        if (h < 0) continue;
+// value a border cell takes from its interior neighbours: min D[q] + 1, diagonal q only when D[q] + 1 is odd
+__device__ __forceinline__ int border_value(const unsigned char* D, int x, int y, int w1, int h1) {
+    int best = 255;
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+        for (int dx = -1; dx <= 1; dx++) {
+            if (dx == 0 && dy == 0) continue;
+            const int qx = x + dx, qy = y + dy;
+            if (qx <= 0 || qy <= 0 || qx >= w1 - 1 || qy >= h1 - 1) continue;
+            const int j = D[qx + w1 * qy];
+            if (j >= N2_RMAX) continue;
+            const int cand = j + 1;
+            if (dx != 0 && dy != 0 && !(cand & 1)) continue;
+            best = min(best, cand);
+        }
+    return best;
+}
+
+// CoarseDistanceMap::makeDistanceMap, first half (CoarseTracker.cc:795-835): active points -> level-1 source cells
+__global__ void n2_project_kernel(int w1, int h1, int n_points, const float* __restrict__ tab, const int* __restrict__ host,
+                                  const float* __restrict__ u, const float* __restrict__ v, const float* __restrict__ idepth,
+                                  int* __restrict__ cells, int* __restrict__ src_n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *src_n = n_points;
+    if (i >= n_points) return;
+    int cell = -1;
+    const int h = host[i];
+    if (h >= 0) {
         float px, py, p0;
         project(tab, h, u[i], v[i], idepth[i], px, py, p0);
         const int x = (int)(px + 0.5f), y = (int)(py + 0.5f);
-        if (x > 0 && y > 0 && x < w1 && y < h1) D[x + w1 * y] = 0;
+        if (x > 0 && y > 0 && x < w1 && y < h1) cell = x + w1 * y;
     }
-    __syncthreads();
-    for (int k = 1; k < 40; k++) {
-        const int want = k - 1;
-        const bool diag = (k & 1) != 0;
-        int changed = 0;
-        for (int i = threadIdx.x; i < cells; i += N2_THREADS) {
-            if (D[i] <= k) continue;
-            const int y = i / w1, x = i - y * w1;
-            bool hit = false;
-            // neighbour q propagates when it is not a border cell and holds k - 1
-#pragma unroll
-            for (int dy = -1; dy <= 1; dy++)
-#pragma unroll
-                for (int dx = -1; dx <= 1; dx++) {
-                    if ((dx == 0 && dy == 0) || (!diag && dx != 0 && dy != 0)) continue;
-                    const int qx = x + dx, qy = y + dy;
-                    if (qx <= 0 || qy <= 0 || qx >= w1 - 1 || qy >= h1 - 1) continue;
-                    hit = hit || D[qx + w1 * qy] == want;
-                }
-            if (hit) { D[i] = (unsigned char)k; changed = 1; }
-        }
-        if (!__syncthreads_or(changed)) break;
-    }
-    uint4* o4 = reinterpret_cast<uint4*>(dmap);
-    const uint4* d4 = reinterpret_cast<const uint4*>(D);
-    for (int i = threadIdx.x; i < cells16; i += N2_THREADS) o4[i] = d4[i];
+    cells[i] = cell;
 }
 
-__device__ __forceinline__ bool claim(unsigned* Dw, int idx, unsigned k) {
-    unsigned* w = Dw + (idx >> 2);
-    const int sh = (idx & 3) * 8;
-    unsigned old = *reinterpret_cast<volatile unsigned*>(w);
-    while (true) {
-        if (((old >> sh) & 255u) <= k) return false;
-        const unsigned nw = (old & ~(255u << sh)) | (k << sh);
-        const unsigned prev = atomicCAS(w, old, nw);
-        if (prev == old) return true;
-        old = prev;
+// growDistBFS over all sources (CoarseTracker.cc:837-923) for the interior cells of one 16x16 tile
+__global__ void __launch_bounds__(N2_TILE * N2_TILE)
+n2_map_kernel(int w1, int h1, const int* __restrict__ cells, const int* __restrict__ src_n, unsigned char* __restrict__ dmap) {
+    __shared__ short2 s_src[N2_TILE * N2_TILE];
+    __shared__ int s_warp[N2_TILE * N2_TILE / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int X0 = blockIdx.x * N2_TILE, Y0 = blockIdx.y * N2_TILE;
+    const int x = X0 + (tid & (N2_TILE - 1)), y = Y0 + tid / N2_TILE;
+    const int n = *src_n;
+    int best = 255;
+    for (int base = 0; base < n; base += N2_TILE * N2_TILE) {
+        const int i = base + tid;
+        const int c = i < n ? __ldg(cells + i) : -1;
+        int sx = 0, sy = 0;
+        bool near = false;
+        if (c >= 0) {
+            sy = c / w1; sx = c - sy * w1;
+            near = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1 &&            // border sources spread nothing
+                   sx >= X0 - N2_RMAX && sx < X0 + N2_TILE + N2_RMAX && sy >= Y0 - N2_RMAX && sy < Y0 + N2_TILE + N2_RMAX;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, near);
+        if (lane == 0) s_warp[wid] = __popc(m);
+        __syncthreads();
+        int off = 0, total = 0;
+#pragma unroll
+        for (int q = 0; q < N2_TILE * N2_TILE / 32; q++) { if (q < wid) off += s_warp[q]; total += s_warp[q]; }
+        if (near) s_src[off + __popc(m & ((1u << lane) - 1))] = make_short2((short)sx, (short)sy);
+        __syncthreads();
+        for (int k = 0; k < total; k++) {
+            const short2 q = s_src[k];
+            best = min(best, ring_dist(x - q.x, y - q.y));
+        }
+        __syncthreads();
+    }
+    if (x > 0 && y > 0 && x < w1 - 1 && y < h1 - 1) dmap[x + w1 * y] = (unsigned char)(best <= N2_RMAX ? best : 255);
+}
+
+// the border ring of the map, then the border sources themselves
+__global__ void __launch_bounds__(N2_THREADS)
+n2_border_kernel(int w1, int h1, const int* __restrict__ cells, const int* __restrict__ src_n, unsigned char* __restrict__ dmap,
+                 const int* __restrict__ corner) {
+    const int nb = 2 * w1 + 2 * (h1 - 2);
+    for (int b = threadIdx.x; b < nb; b += N2_THREADS) {
+        int x, y;
+        if (b < w1) { x = b; y = 0; }
+        else if (b < 2 * w1) { x = b - w1; y = h1 - 1; }
+        else { const int r = b - 2 * w1; y = 1 + (r >> 1); x = (r & 1) ? w1 - 1 : 0; }
+        int val = border_value(dmap, x, y, w1, h1);
+        if (corner && (x == 0 || x == w1 - 1) && (y == 0 || y == h1 - 1)) val = min(val, corner[(x ? 1 : 0) + (y ? 2 : 0)]);
+        dmap[x + w1 * y] = (unsigned char)val;
+    }
+    __syncthreads();
+    const int n = *src_n;
+    for (int i = threadIdx.x; i < n; i += N2_THREADS) {
+        const int c = cells[i];
+        if (c < 0) continue;
+        const int y = c / w1, x = c - y * w1;
+        if (x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1) dmap[c] = 0;
     }
 }
 
@@ -99,25 +155,58 @@ struct N2Sel {
     int* cell; float* frac; float* thr;   // scratch [n]
     unsigned char* action;            // [n]
     int* cnt;                         // [2]
-    unsigned char* dmap;
+    const unsigned char* dmap;
+    int* src_cells; int* src_n;       // source list of the map kernels: accepted cells are appended
+    int* corner;                      // [4] values of the four corner cells after the walk (see n2_select_kernel)
 };
+
+// CoarseDistanceMap::addIntoDistFinal + growDistBFS(1) (CoarseTracker.cc:925-930) on the shared-memory map, by one warp,
+// out to ring R (rings beyond the largest activation threshold cannot change a decision of the walk)
+__device__ __forceinline__ void stamp_source(unsigned char* D, int c0, int R, int w1, int h1, int lane) {
+    const int sy = c0 / w1, sx = c0 - sy * w1;
+    if (lane == 0) D[c0] = 0;
+    __syncwarp();
+    if (sx == 0 || sy == 0 || sx == w1 - 1 || sy == h1 - 1 || R <= 0) return;
+    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R), ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
+    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
+    for (int t = lane; t < nc; t += 32) {
+        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
+        const int d = ring_dist(x - sx, y - sy);
+        const int idx = x + w1 * y;
+        if (d <= R && D[idx] > d) D[idx] = (unsigned char)d;
+    }
+    __syncwarp();
+    if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {
+        // the box reaches the border ring: those cells follow from their interior neighbours
+        const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
+        const int bbw = bx1 - bx0 + 1, nbc = bbw * (by1 - by0 + 1);
+        for (int t = lane; t < nbc; t += 32) {
+            const int ty = t / bbw, x = bx0 + (t - ty * bbw), y = by0 + ty;
+            if (!(x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1)) continue;
+            const int v = border_value(D, x, y, w1, h1);
+            if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
+        }
+        __syncwarp();
+    }
+}
 
 __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
     extern __shared__ __align__(16) unsigned char D[];
-    __shared__ short2 fl[2][N2_FCAP];
-    __shared__ int fcnt, s_acc, s_del;
+    __shared__ int s_acc, s_del;
+    __shared__ unsigned s_thmax;
     const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
     {
         uint4* d4 = reinterpret_cast<uint4*>(D);
         const uint4* g4 = reinterpret_cast<const uint4*>(p.dmap);
         for (int i = threadIdx.x; i < cells16; i += N2_THREADS) d4[i] = g4[i];
     }
-    if (threadIdx.x == 0) { s_acc = 0; s_del = 0; }
+    if (threadIdx.x == 0) { s_acc = 0; s_del = 0; s_thmax = 0u; }
     __syncthreads();
     // ---- classification, all threads (FullSystem.cc:1243-1296 without the map test)
     const float* skip = p.tab + 12 * p.n_hosts;
     const float* flagged = skip + p.n_hosts;
     int ndel = 0;
+    float thmax = 0.f;
     for (int i = threadIdx.x; i < p.n; i += N2_THREADS) {
         const int h = p.host[i];
         int act = 0, cell = -1;
@@ -140,6 +229,7 @@ __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
                         cell = x + p.w1 * y;
                         fr = p0 - floorf(p0);   // the reference takes the fraction of the homogeneous ptp[0] (FullSystem.cc:1279-1280)
                         th = p.minActDist * p.type[i];
+                        thmax = fmaxf(thmax, th);
                     } else {
                         act = 1;
                     }
@@ -151,16 +241,29 @@ __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
         ndel += act;
     }
     if (ndel) atomicAdd(&s_del, ndel);
+    if (thmax > 0.f) atomicMax(&s_thmax, __float_as_uint(thmax));
     __syncthreads();
     // ---- the ordered walk, warp 0
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
-        unsigned* Dw = reinterpret_cast<unsigned*>(D);
+        const float tm = __uint_as_float(s_thmax);
+        const int R = tm >= (float)N2_RMAX ? N2_RMAX : min(N2_RMAX, (int)ceilf(tm) + 1);
+        const int n0 = *p.src_n;
         int nacc = 0;
+        // A corner cell has ONE interior neighbour, a diagonal one, which can claim it only on an odd ring.  The
+        // reference's incremental BFS therefore leaves a corner at the best value that neighbour ever offered while the
+        // walk lowered it — not a function of the final map.  Lanes 0..3 follow one corner each.
+        const int kx = (lane & 1) ? p.w1 - 1 : 0, ky = (lane & 2) ? p.h1 - 1 : 0;
+        const int qx = (lane & 1) ? p.w1 - 2 : 1, qy = (lane & 2) ? p.h1 - 2 : 1;
+        int cv = 255, qv = 255;
+        if (lane < 4) { cv = D[kx + p.w1 * ky]; qv = D[qx + p.w1 * qy]; }
+        int cell = lane < p.n ? p.cell[lane] : -1;
+        float fr = lane < p.n ? p.frac[lane] : 0.f, th = lane < p.n ? p.thr[lane] : 0.f;
         for (int base = 0; base < p.n; base += 32) {
-            const int i = base + lane;
-            const int cell = i < p.n ? p.cell[i] : -1;
-            const float fr = i < p.n ? p.frac[i] : 0.f, th = i < p.n ? p.thr[i] : 0.f;
+            const int i = base + lane, inext = i + 32;
+            // next chunk's operands are in flight while this one is walked
+            const int cell_n = inext < p.n ? p.cell[inext] : -1;
+            const float fr_n = inext < p.n ? p.frac[inext] : 0.f, th_n = inext < p.n ? p.thr[inext] : 0.f;
             int from = 0;
             while (true) {
                 bool pass = false;
@@ -173,49 +276,30 @@ __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
                 if (!m) break;
                 const int j = __ffs(m) - 1;
                 const int c0 = __shfl_sync(0xffffffffu, cell, j);
-                if (lane == j) p.action[i] = 2;
+                if (lane == j) { p.action[i] = 2; p.src_cells[n0 + nacc] = c0; }
                 nacc++;
                 from = j + 1;
-                // addIntoDistFinal + growDistBFS(1)
-                const int sy = c0 / p.w1, sx = c0 - sy * p.w1;
-                if (lane == 0) { D[c0] = 0; fl[0][0] = make_short2((short)sx, (short)sy); }
-                int cur = 0, nf = 1;
-                __syncwarp();
-                for (int k = 1; k < 40 && nf > 0; k++) {
-                    if (lane == 0) fcnt = 0;
-                    __syncwarp();
-                    const bool diag = (k & 1) != 0;
-                    for (int it = lane; it < nf; it += 32) {
-                        const short2 q = fl[cur][it];
-                        const int x = q.x, y = q.y;
-                        if (x == 0 || y == 0 || x == p.w1 - 1 || y == p.h1 - 1) continue;
-#pragma unroll
-                        for (int dy = -1; dy <= 1; dy++)
-#pragma unroll
-                            for (int dx = -1; dx <= 1; dx++) {
-                                if ((dx == 0 && dy == 0) || (!diag && dx != 0 && dy != 0)) continue;
-                                const int nx = x + dx, ny = y + dy;
-                                if (claim(Dw, nx + p.w1 * ny, (unsigned)k)) {
-                                    const int pos = atomicAdd(&fcnt, 1);
-                                    if (pos < N2_FCAP) fl[cur ^ 1][pos] = make_short2((short)nx, (short)ny);
-                                }
-                            }
+                stamp_source(D, c0, R, p.w1, p.h1, lane);
+                if (lane < 4) {
+                    const int sy = c0 / p.w1, sx = c0 - sy * p.w1;
+                    if (sx == kx && sy == ky) cv = 0;
+                    if (sx > 0 && sy > 0 && sx < p.w1 - 1 && sy < p.h1 - 1) {
+                        qv = min(qv, ring_dist(qx - sx, qy - sy));
+                        const int cand = qv + 1;
+                        if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
                     }
-                    __syncwarp();
-                    nf = min(*reinterpret_cast<volatile int*>(&fcnt), N2_FCAP);
-                    cur ^= 1;
-                    __syncwarp();
+                    if (cv < D[kx + p.w1 * ky]) D[kx + p.w1 * ky] = (unsigned char)cv;
                 }
+                __syncwarp();
                 if (from >= 32) break;
             }
+            cell = cell_n; fr = fr_n; th = th_n;
         }
-        if (lane == 0) s_acc = nacc;
+        if (lane == 0) { s_acc = nacc; *p.src_n = n0 + nacc; }
+        if (lane < 4) p.corner[lane] = cv;
     }
     __syncthreads();
     if (threadIdx.x == 0) { p.cnt[0] = s_acc; p.cnt[1] = s_del; }
-    uint4* o4 = reinterpret_cast<uint4*>(p.dmap);
-    const uint4* d4 = reinterpret_cast<const uint4*>(D);
-    for (int i = threadIdx.x; i < cells16; i += N2_THREADS) o4[i] = d4[i];
 }
 
 __global__ void n2_types_kernel(int n, const float* __restrict__ src, float* __restrict__ dst) {
@@ -241,6 +325,17 @@ int put_tables(ldso_gpu_ctx* c, ImmatureDev* P, int n_hosts, const float* KRKi, 
         st[13 * n_hosts + h] = flagged && flagged[h] ? 1.f : 0.f;
     }
     LDSO_CUDA_OK(c, ldso_copy(c, P->tables, st, sizeof(float) * 14 * n_hosts, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+// interior cells by tiles, then the border ring: the full fwdWarpedIDDistFinal of the current source list
+int launch_map(ldso_gpu_ctx* c, ImmatureDev* P, bool after_walk) {
+    const int w1 = c->wG[1], h1 = c->hG[1];
+    dim3 grid((w1 + N2_TILE - 1) / N2_TILE, (h1 + N2_TILE - 1) / N2_TILE);
+    n2_map_kernel<<<grid, N2_TILE * N2_TILE, 0, c->stream>>>(w1, h1, P->src_cells, P->src_n, P->dmap);
+    n2_border_kernel<<<1, N2_THREADS, 0, c->stream>>>(w1, h1, P->src_cells, P->src_n, P->dmap, after_walk ? P->src_n + 1 : nullptr);
+    c->launches += 2;
+    LDSO_CUDA_OK(c, cudaGetLastError());
     return 0;
 }
 
@@ -278,15 +373,15 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
         memcpy(sp, host, 4 * N); memcpy(sp + N, u, 4 * N); memcpy(sp + 2 * N, v, 4 * N); memcpy(sp + 3 * N, idepth, 4 * N);
         LDSO_CUDA_OK(c, ldso_copy(c, P->cr, sp, 16 * N, cudaMemcpyHostToDevice, c->stream));
     }
-    const size_t smem = map_bytes(c);
-    rc = set_smem(c, (const void*)n2_distmap_kernel, smem);
-    if (rc) return rc;
+    LDSO_REQUIRE(c, n_points <= P->src_cap);
+    P->src_n_host = n_points;
     prof_begin(c, c->stream);
-    n2_distmap_kernel<<<1, N2_THREADS, smem, c->stream>>>(c->wG[1], c->hG[1], n_points, P->tables, (const int*)P->cr, P->cr + N,
-                                                          P->cr + 2 * N, P->cr + 3 * N, P->dmap);
+    n2_project_kernel<<<(n_points + 255) / 256 + 1, 256, 0, c->stream>>>(c->wG[1], c->hG[1], n_points, P->tables, (const int*)P->cr,
+                                                                        P->cr + N, P->cr + 2 * N, P->cr + 3 * N, P->src_cells, P->src_n);
+    rc = launch_map(c, P, false);
     prof_end(c, c->stream, LDSO_PROF_N2, c->wG[1] * c->hG[1]);
     c->launches++;
-    LDSO_CUDA_OK(c, cudaGetLastError());
+    if (rc) return rc;
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the pinned staging is reused by the next entry point
     return 0;
 }
@@ -323,7 +418,9 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     p.quality = P->quality; p.interval = P->interval; p.type = P->type;
     p.minActDist = current_min_act_dist; p.minQuality = min_trace_quality;
     p.cell = P->act_state; p.frac = (float*)(P->act_state + P->cap); p.thr = (float*)(P->act_state + 2 * (size_t)P->cap);
-    p.action = P->action; p.cnt = P->sel_cnt; p.dmap = P->dmap;
+    p.action = P->action; p.cnt = P->sel_cnt; p.dmap = P->dmap; p.src_cells = P->src_cells; p.src_n = P->src_n; p.corner = P->src_n + 1;
+    LDSO_REQUIRE(c, P->src_n_host + P->n <= P->src_cap);
+    P->src_n_host += P->n;   // upper bound of the list length after this walk
     const size_t smem = map_bytes(c);
     rc = set_smem(c, (const void*)n2_select_kernel, smem);
     if (rc) return rc;
@@ -332,6 +429,8 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     prof_end(c, c->stream, LDSO_PROF_N2SEL, P->n);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
+    rc = launch_map(c, P, true);   // the accepted cells joined the source list: rebuild the full-radius map behind the read-back
+    if (rc) return rc;
     unsigned char* sa = (unsigned char*)P->pinned + 4096;
     LDSO_REQUIRE(c, (size_t)P->n + 4096 <= P->pinned_bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, sa, P->action, P->n, cudaMemcpyDeviceToHost, c->stream));
