@@ -230,6 +230,36 @@ int ldso_gpu_immature_select_activation(ldso_gpu_ctx* ctx, int n_hosts, const fl
                                         float current_min_act_dist, float min_trace_quality, unsigned char* action_out,
                                         int counts_out[2]);
 
+/* ---- N1: CoarseInitializer (src/frontend/CoarseInitializer.cc, include/frontend/CoarseInitializer.h) ----------
+ * One initializer per ctx.  Point state (struct Pnt, CoarseInitializer.h:23-63) lives on the device per pyramid level.
+ * setFirst (:656-737): makeK (:811-837); level 0 = PixelSelector::makeMaps(density 0.03 w h, recursions 1, thFactor 2)
+ * with currentPotential reset to 3, levels > 0 = makePixelStatus (include/frontend/PixelSelector2.h:63-278) with
+ * densities {0.05, 0.15, 0.5, 1} w h and the file-static sparsityFactor carried from level to level (starts at 5);
+ * points are the selected pixels with patternPadding + 1 <= x < w_l - patternPadding - 2 (same for y) in row-major
+ * order at (x + 0.1, y + 0.1), idepth = iR = 1; makeNN (:839-906): 10 nearest neighbours per point on its level
+ * (the point itself comes first; equal distances resolve to the lower index — nanoflann's tie order is not specified)
+ * and the nearest point of the next coarser level to (0.5 u - 0.25, 0.5 v - 0.25) as parent.
+ * num_points_out[levels]. */
+int ldso_gpu_init_set_first(ldso_gpu_ctx* ctx, int slot, int* num_points_out);
+/* trackFrame (:45-183) of the pyramid in `slot` against the first frame: per level, coarse to fine, propagateDown
+ * (:606-631), resetPoints (:739-761), then the Levenberg-Marquardt loop over calcResAndGS (:186-342 =
+ * calculateAllResiduals :391-518 + calculateAlphaEnergy :376-389 + calculateSC :349-374), doStep (:763-789),
+ * calcEC (:520-536), applyStep (:791-809), optReg (:538-567); finally propagateUp (:570-604).
+ * exposure_first / exposure_new: ab_exposure of the two frames (:71-73).  Out: thisToNext as 12 doubles (R row-major,
+ * then t), thisToNext_aff, snapped, the return value of trackFrame in *ready (snapped && frameID > snappedAt + 5),
+ * latest_res[3] = the last level-0 {energy, alphaEnergy, num} of calcResAndGS, iterations per level (may be NULL). */
+int ldso_gpu_init_track_frame(ldso_gpu_ctx* ctx, int slot, float exposure_first, float exposure_new, double pose_out[12],
+                              float aff_out[2], int* snapped, int* ready, float latest_res[3], int iters_out[LDSO_MAX_LEVELS]);
+/* Pnt fields of level lvl (any pointer may be NULL): u, v, idepth, iR, isGood, my_type, lastHessian, energy[0] */
+int ldso_gpu_init_get_points(ldso_gpu_ctx* ctx, int lvl, int* n, float* u, float* v, float* idepth, float* iR,
+                             unsigned char* is_good, float* my_type, float* last_hessian, float* energy);
+/* neighbours [n][10] and parent [n] of level lvl (makeNN) */
+int ldso_gpu_init_get_graph(ldso_gpu_ctx* ctx, int lvl, int* neighbours, int* parent);
+/* one calcResAndGS (:186-342) at level lvl for the given refToNew / affine, on the current point state: H, Hsc 8x8 and
+ * b, bsc as floats, res[3] = {energy, alphaEnergy, num}.  For parity tests of the per-point kernels. */
+int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* ctx, int slot, int lvl, const double ref_to_new[12], float aff_a, float aff_b,
+                                  float H[64], float b[8], float Hsc[64], float bsc[8], float res[3]);
+
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps
  * points and residuals as SoA/AoS pools.  Index conventions follow the reference: pair tables are

@@ -324,6 +324,48 @@ class Ctx:
                    act.ctypes.data_as(C.c_void_p), _ip(cnt))
         return act[:self.imm_n], (int(cnt[0]), int(cnt[1]))
 
+    # ---- N1: CoarseInitializer ----
+    def init_set_first(self, slot):
+        n = np.zeros(MAX_LEVELS, np.int32)
+        self._call("init_set_first", C.c_int(slot), _ip(n))
+        self.init_n = n[:self.levels].copy()
+        return self.init_n
+
+    def init_track_frame(self, slot, exposure_first=1.0, exposure_new=1.0):
+        pose = np.zeros(12, np.float64); aff = np.zeros(2, np.float32); res = np.zeros(3, np.float32)
+        snapped, ready = C.c_int(), C.c_int()
+        iters = np.zeros(MAX_LEVELS, np.int32)
+        self._call("init_track_frame", C.c_int(slot), C.c_float(exposure_first), C.c_float(exposure_new), _dp(pose), _fp(aff),
+                   C.byref(snapped), C.byref(ready), _fp(res), _ip(iters))
+        return dict(pose=pose, aff=aff, snapped=bool(snapped.value), ready=bool(ready.value), res=res, iters=iters[:self.levels].copy())
+
+    def init_get_points(self, lvl):
+        n = int(self.init_n[lvl])
+        m = max(n, 1)
+        a = {k: np.zeros(m, np.float32) for k in ("u", "v", "idepth", "iR", "type", "lastHessian", "energy")}
+        good = np.zeros(m, np.uint8)
+        nn = C.c_int()
+        self._call("init_get_points", C.c_int(lvl), C.byref(nn), _fp(a["u"]), _fp(a["v"]), _fp(a["idepth"]), _fp(a["iR"]),
+                   good.ctypes.data_as(C.c_void_p), _fp(a["type"]), _fp(a["lastHessian"]), _fp(a["energy"]))
+        assert nn.value == n
+        out = {k: x[:n] for k, x in a.items()}
+        out["isGood"] = good[:n].astype(bool)
+        return out
+
+    def init_get_graph(self, lvl):
+        n = int(self.init_n[lvl])
+        nb = np.zeros((max(n, 1), 10), np.int32); par = np.zeros(max(n, 1), np.int32)
+        self._call("init_get_graph", C.c_int(lvl), _ip(nb), _ip(par))
+        return nb[:n], par[:n]
+
+    def init_calc_res_and_gs(self, slot, lvl, pose12, aff=(0.0, 0.0)):
+        pose = np.ascontiguousarray(pose12, dtype=np.float64)
+        H = np.zeros(64, np.float32); b = np.zeros(8, np.float32); Hsc = np.zeros(64, np.float32); bsc = np.zeros(8, np.float32)
+        res = np.zeros(3, np.float32)
+        self._call("init_calc_res_and_gs", C.c_int(slot), C.c_int(lvl), _dp(pose), C.c_float(aff[0]), C.c_float(aff[1]),
+                   _fp(H), _fp(b), _fp(Hsc), _fp(bsc), _fp(res))
+        return H.reshape(8, 8), b, Hsc.reshape(8, 8), bsc, res
+
     def immature_activate(self, cand, min_obs=1):
         cand = np.ascontiguousarray(cand, dtype=np.int32)
         n = len(cand)
