@@ -46,8 +46,9 @@ WORKLOAD_ODOMETRY = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4
                      "trackNewCoarse with motion hypotheses (K3/K4 LM), keyframe decision by optical flow, traceNewCoarse (K5); on a "
                      "keyframe: frame selection for dropping, new residuals, activatePointsMT (K6), optimize = linearizeAll + <= %d x "
                      "(accumulate K8/K9, solve H1, resubstitute K10, step, linearizeAll K7) + fix pass, removal of OOB/outlier points, "
-                     "setCoarseTrackingRef (K2), makeNewTraces (A2 + K6). Bootstrapped from the ground-truth depth of frame 0 "
-                     "(CoarseInitializer is SURVEY 8f N1); no marginalisation prior (points / frames leaving the window are dropped)"
+                     "setCoarseTrackingRef (K2), makeNewTraces (A2 + K6). Bootstrapped by CoarseInitializer (N1) on the first ~10 frames, "
+                     "before the timed region (the map is therefore up to scale; ATE is Sim(3)-aligned); no marginalisation prior "
+                     "(points / frames leaving the window are dropped)"
                      % (N_POINTS, N_IMMATURE, WINDOW, BA_ITS))
 # algorithmic bytes per unit
 BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 5000.0}
@@ -296,7 +297,7 @@ class ClosedLoop:
     reference, new immature points) on the synthetic sequence, bootstrapped from the ground-truth depth of frame 0.
     Same interface as Sequence so the timing code is shared."""
 
-    PRIME = 24          # frames after the bootstrap frame that are run before the warm-up steps (the first keyframe falls here)
+    PRIME = 24          # frames after the first one that are run before the warm-up steps (initialisation and the first keyframe fall here)
 
     def __init__(self, api, seed, n_steps, device=0):
         from ldso_b200 import odometry
@@ -321,7 +322,7 @@ class ClosedLoop:
 
     def prime(self):
         R0, t0 = self.poses[0]
-        self.od.add_frame(self.frames[0], gt_depth=self.depths[0], gt_w2c=(R0.T, -R0.T @ t0))
+        self.od.add_frame(self.frames[0], gt_w2c=(R0.T, -R0.T @ t0))       # no depth given: CoarseInitializer (N1) bootstraps
         for i in range(1, self.first_step):
             self.od.add_frame(self.frames[i])
 

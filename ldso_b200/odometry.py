@@ -7,7 +7,8 @@ prefix-agnostic binding, so the same loop runs the CUDA library and the CPU orac
 compared with each other and with ground truth (the ATE parity gate).
 
 Deliberate simplifications (host-side orchestration is outside SURVEY section 8a; they are the same for both libraries):
-  * bootstrap from ground-truth depth of the first frame instead of CoarseInitializer (8f N1);
+  * bootstrap either through CoarseInitializer (N1; add_frame without gt_depth) or from ground-truth depth of the first
+    frame (add_frame(gt_depth=...), kept for the tests that need a metric trajectory);
   * no marginalisation prior: points and frames that leave the window are dropped, HM = bM = 0, the gauge is held by a
     prior on the oldest keyframe; consequently Jacobians are evaluated at the current state (no FEJ, no linearised
     residuals) and steps are always accepted (setting_forceAceptStep = true in the reference, Setting.cc);
@@ -36,6 +37,21 @@ def se3_exp(xi):
         R = np.eye(3) + A * O + B * O @ O
         V = np.eye(3) + B * O + C * O @ O
     return R, V @ ups
+
+
+_LIBC = []
+
+
+def _libc():
+    """glibc rand(): the reference sub-selects the initializer's points with it (FullSystem.cc:1486, :1516)"""
+    if not _LIBC:
+        import ctypes
+        _LIBC.append(ctypes.CDLL("libc.so.6"))
+    return _LIBC[0]
+
+
+def odometry_from_rt12(p):
+    return p[:9].reshape(3, 3).copy(), p[9:].copy()
 
 
 def rt12(T):
@@ -74,6 +90,7 @@ class Odometry:
         self.log = []
         self.phase = {}
         self.n_frames_seen = 0
+        self.init_first = None           # first frame of the CoarseInitializer while the system is not initialised
 
     # ---- small helpers -------------------------------------------------------------------------------
     def pos_of(self, fid):
@@ -125,6 +142,8 @@ class Odometry:
         t = self.tick("K1 makeImages", t)
         if not self.frames:
             w2c = gt_w2c if gt_w2c is not None else (np.eye(3), np.zeros(3))
+            if gt_depth is None:
+                return self.initializer_step(fid, slot, w2c)
             f = dict(id=fid, slot=slot, w2c=(w2c[0].copy(), w2c[1].copy()), aff=(0.0, 0.0))
             self.bootstrap(f, gt_depth)
             self.poses[fid] = f["w2c"]
@@ -189,6 +208,51 @@ class Odometry:
             return False, None, None, None
         self.last_aff = (float(best[2][0]), float(best[2][1]))
         return best
+
+    # ---- bootstrap through CoarseInitializer (FullSystem::addActiveFrame :92-126, initializeFromInitializer :1484-1665) ----
+    def initializer_step(self, fid, slot, w2c_first):
+        """frames before the system is initialised: setFirst on the first one, trackFrame on the following ones; when the
+        initializer reports ready the first frame becomes keyframe 0 with the initializer's points and the current frame
+        goes through makeKeyFrame"""
+        t = time.perf_counter()
+        if self.init_first is None:
+            self.init_first = dict(id=fid, slot=slot, w2c=(w2c_first[0].copy(), w2c_first[1].copy()), aff=(0.0, 0.0))
+            self.ctx.init_set_first(slot)
+            self.tick("N1 CoarseInitializer", t)
+            return dict(kf=False, ok=True, init=True)
+        r = self.ctx.init_track_frame(slot)
+        self.tick("N1 CoarseInitializer", t)
+        if not r["ready"]:
+            self.free_slots.append(slot)
+            self.log.append(dict(frame=fid, init=True, snapped=r["snapped"]))
+            return dict(kf=False, ok=True, init=True)
+        first = self.init_first
+        P0 = self.ctx.init_get_points(0)
+        npts = len(P0["u"])
+        rescale = 1.0 / ((1e-5 + float(np.sum(P0["iR"], dtype=np.float32))) / (1e-5 + npts))
+        keep = self.desired_points / float(npts)
+        libc = _libc()
+        libc.srand(549812361)                                              # FullSystem.cc:1486
+        sel = np.array([libc.rand() / float(2147483647) <= keep for _ in range(npts)], bool)
+        u, v = (P0["u"][sel] + np.float32(0.5)).astype(np.float32), (P0["v"][sel] + np.float32(0.5)).astype(np.float32)
+        col, wgt, gh, eth = self.ctx.immature_create(first["slot"], u, v)
+        ok = np.isfinite(eth)
+        idp = (P0["iR"][sel][ok] * np.float32(rescale)).astype(np.float32)
+        n = int(ok.sum())
+        self.frames.append(first)
+        self.poses[first["id"]] = first["w2c"]
+        self.P = dict(host=np.full(n, first["id"], np.int64), u=u[ok], v=v[ok], idepth=idp, color=col[ok], weights=wgt[ok],
+                      hdi=np.full(n, 1e-3, np.float32))
+        self.res = np.full((n, 1), -1, np.int8)
+        R, tt = odometry_from_rt12(r["pose"])
+        rel = (R, tt / rescale)                                            # firstToNew.translation() /= rescaleFactor (:1547)
+        w2c = wh.se3_mul(rel, first["w2c"])
+        self.poses[fid] = w2c
+        self.init_first = None
+        self.log.append(dict(frame=fid, kf=True, init_done=True, rescale=float(rescale), init_points=n))
+        self.make_keyframe(dict(id=fid, slot=slot, w2c=w2c, aff=(float(r["aff"][0]), float(r["aff"][1]))))
+        self.tick("KF makeKeyFrame total (Python orchestration included)", time.perf_counter())
+        return dict(kf=True, ok=True, init=True)
 
     # ---- bootstrap: the first keyframe with ground-truth depth (stands in for CoarseInitializer) ----
     def bootstrap(self, f, gt_depth):
@@ -415,14 +479,14 @@ class Odometry:
         self.last_aff = newest["aff"]
 
 
-def run(api, calib_name, frames, depths, poses_c2w, calib, n_frames=None, **kw):
+def run(api, calib_name, frames, depths, poses_c2w, calib, n_frames=None, bootstrap="gt", **kw):
     """feed a synthetic sequence; returns (odometry object, estimated camera centres, ground-truth centres, frame ids)"""
     od = Odometry(api, calib, **kw)
     n = len(frames) if n_frames is None else n_frames
     R0, t0 = poses_c2w[0]
     for i in range(n):
         w2c0 = (R0.T, -R0.T @ t0)
-        od.add_frame(frames[i], gt_depth=depths[i] if i == 0 else None, gt_w2c=w2c0 if i == 0 else None)
+        od.add_frame(frames[i], gt_depth=depths[i] if (i == 0 and bootstrap == "gt") else None, gt_w2c=w2c0 if i == 0 else None)
     ids = sorted(od.poses)
     est = np.array([-od.poses[i][0].T @ od.poses[i][1] for i in ids])
     gt = np.array([poses_c2w[i][1] for i in ids])

@@ -50,3 +50,33 @@ def test_gpu_closed_loop_matches_oracle(gpu, oracle):
         if lg["frame"] != lo["frame"]:
             break
         assert abs(lg["points"] - lo["points"]) <= 0.02 * lo["points"] + 5
+
+
+def test_oracle_closed_loop_from_the_initializer(oracle):
+    """no ground-truth depth anywhere: CoarseInitializer (N1) bootstraps the map, so the trajectory is up to scale"""
+    c = util.CALIB["c1"]
+    frames, depths, poses = synth.make_sequence(1001, 45, start=0, **c)
+    od, est, gt, ids = odometry.run(oracle, "c1", frames, depths, poses, c, bootstrap="init")
+    done = [l for l in od.log if l.get("init_done")]
+    assert len(done) == 1 and done[0]["frame"] <= 12 and done[0]["init_points"] > 1500
+    assert not any(l.get("lost") for l in od.log) and len(ids) >= 45 - done[0]["frame"]
+    ate, scale = odometry.ate_rmse(est, gt)
+    path = np.linalg.norm(np.diff(gt, axis=0), axis=1).sum()
+    assert ate < 0.01 * path, (ate, path)
+
+
+@pytest.mark.gpu
+def test_gpu_closed_loop_from_the_initializer_matches_oracle(gpu, oracle):
+    c = util.CALIB["c1"]
+    frames, depths, poses = synth.make_sequence(1001, 70, start=0, **c)
+    og, eg, gt, ids_g = odometry.run(gpu, "c1", frames, depths, poses, c, bootstrap="init")
+    oo, eo, _, ids_o = odometry.run(oracle, "c1", frames, depths, poses, c, bootstrap="init")
+    assert ids_g == ids_o
+    dg, do = [l for l in og.log if l.get("init_done")][0], [l for l in oo.log if l.get("init_done")][0]
+    assert dg["frame"] == do["frame"] and dg["init_points"] == do["init_points"] and abs(dg["rescale"] / do["rescale"] - 1) < 1e-3
+    path = np.linalg.norm(np.diff(gt, axis=0), axis=1).sum()
+    ate_g, sg = odometry.ate_rmse(eg, gt)
+    ate_o, so = odometry.ate_rmse(eo, gt)
+    print("ATE gpu %.3e oracle %.3e path %.3f scale %.3f %.3f" % (ate_g, ate_o, path, sg, so))
+    assert ate_g < 0.01 * path and ate_o < 0.01 * path
+    assert abs(sg / so - 1) < 2e-2 and abs(ate_g - ate_o) < max(0.2 * ate_o, 3e-4)
