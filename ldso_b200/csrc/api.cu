@@ -53,6 +53,7 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaStreamCreateWithFlags(&c->stream_map, cudaStreamNonBlocking));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev0));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev1));
+    LDSO_CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_h2d, cudaEventDisableTiming));
     c->frame = new float4*[cfg.n_frame_slots]();
     for (int s = 0; s < cfg.n_frame_slots; s++) LDSO_CUDA_OK(c, cudaMalloc(&c->frame[s], off * sizeof(float4)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->img_dev, npx0 * sizeof(float)));
@@ -139,6 +140,7 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     cudaFreeHost(c->trk_mailbox);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_h2d) cudaEventDestroy(c->ev_h2d);
     prof_drain(c);
     for (cudaEvent_t e : c->prof_free) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -235,6 +237,18 @@ extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float
     const size_t bytes = (size_t)c->cfg.w * c->cfg.h * sizeof(float);
     // the caller deletes its ImageAndExposure right after addActiveFrame (run_dso_tum_mono.cc:405-429):
     // consume the image synchronously into pinned staging, then go asynchronous.
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, img) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
+        // the caller's image already lives in page-locked memory (cudaMallocHost / cudaHostRegister, e.g. the shim's
+        // ImageAndExposure allocator): DMA straight out of it, queue the pyramid behind the copy, and give the buffer
+        // back as soon as the copy — not the kernel — has finished
+        LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, img, bytes, cudaMemcpyHostToDevice, c->stream));
+        LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream));
+        int rc = k1_make_images(c, slot, c->img_dev);
+        LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_h2d));
+        return rc;
+    }
+    (void)cudaGetLastError();                            // an unregistered pointer is reported as an error on some drivers
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // previous H2D out of img_pinned has drained
     memcpy(c->img_pinned, img, bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, c->img_pinned, bytes, cudaMemcpyHostToDevice, c->stream));

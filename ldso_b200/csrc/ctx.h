@@ -71,7 +71,7 @@ struct ldso_gpu_ctx {
     size_t lvl_off[LDSO_MAX_LEVELS + 1];   // pixel offset of each level inside a frame slot
     cudaStream_t stream = nullptr;          // tracking stream
     cudaStream_t stream_map = nullptr;      // mapping stream
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_h2d = nullptr;
     float4** frame = nullptr;               // [n_frame_slots] device float4 pyramids {I,dx,dy,absSquaredGrad}
     float* img_dev = nullptr;               // staged input image
     float* img_pinned = nullptr;

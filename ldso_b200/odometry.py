@@ -101,16 +101,22 @@ class Odometry:
         ids = np.array([f["id"] for f in self.frames], np.int64)
         return np.searchsorted(ids, np.asarray(host_ids, np.int64))
 
+    def rel_to(self, w2c_new):
+        """(R, t) of every window frame -> the frame with pose w2c_new, stacked"""
+        Rh = np.stack([f["w2c"][0] for f in self.frames]); th = np.stack([f["w2c"][1] for f in self.frames])
+        R = w2c_new[0] @ Rh.transpose(0, 2, 1)
+        t = w2c_new[1] - np.einsum("nij,nj->ni", R, th)
+        return R, t
+
     def host_tables(self, w2c_new, aff_new=(0.0, 0.0)):
         """hostToFrame KRKi / Kt / affine per keyframe of the window (FullSystem.cc:1171-1176)"""
-        KRKi, Kt, aff = [], [], []
-        for f in self.frames:
-            R, t = wh.se3_mul(w2c_new, wh.se3_inv(f["w2c"]))
-            KRKi.append((self.K @ R.astype(np.float32) @ self.Ki).astype(np.float32))
-            Kt.append((self.K @ t.astype(np.float32)).astype(np.float32))
-            a, b = wh.from_to_vec_exposure(1.0, 1.0, f["aff"], aff_new)
-            aff.append([a, b])
-        return np.array(KRKi, np.float32), np.array(Kt, np.float32), np.array(aff, np.float32)
+        R, t = self.rel_to(w2c_new)
+        KRKi = (self.K @ R.astype(np.float32)) @ self.Ki
+        Kt = t.astype(np.float32) @ self.K.T
+        fa = np.array([f["aff"] for f in self.frames], np.float32)
+        a = np.exp(np.float32(aff_new[0]) - fa[:, 0]).astype(np.float32)          # AffLight::fromToVecExposure, exposures 1
+        b = (np.float32(aff_new[1]) - a * fa[:, 1]).astype(np.float32)
+        return np.ascontiguousarray(KRKi, np.float32), np.ascontiguousarray(Kt, np.float32), np.stack([a, b], 1)
 
     def make_new_traces(self, f):
         """FullSystem::makeNewTraces (:1426-1482): selector + ImmaturePoint constructor on keyframe f, appended to the device pool"""
@@ -336,13 +342,11 @@ class Odometry:
 
     def level1_tables(self):
         """KRKi = K[1] R Ki[0], Kt = K[1] t of every window frame -> newest keyframe (FullSystem.cc:1236-1238)"""
-        newest = self.frames[-1]
         K1 = self.K.copy(); K1[0, 0] *= 0.5; K1[1, 1] *= 0.5; K1[0, 2] = (K1[0, 2] + 0.5) / 2 - 0.5; K1[1, 2] = (K1[1, 2] + 0.5) / 2 - 0.5
-        KRKi, Kt = [], []
-        for fr in self.frames:
-            R, t = wh.se3_mul(newest["w2c"], wh.se3_inv(fr["w2c"]))
-            KRKi.append(K1 @ R.astype(np.float32) @ self.Ki); Kt.append(K1 @ t.astype(np.float32))
-        return np.array(KRKi, np.float32), np.array(Kt, np.float32)
+        R, t = self.rel_to(self.frames[-1]["w2c"])
+        KRKi = (K1 @ R.astype(np.float32)) @ self.Ki
+        Kt = t.astype(np.float32) @ K1.T
+        return np.ascontiguousarray(KRKi, np.float32), np.ascontiguousarray(Kt, np.float32)
 
     def activate_points(self, flagged=()):
         """FullSystem::activatePointsMT (:1197-1337): distance map, ordered candidate walk (N2) and activation (K6), all on
