@@ -532,17 +532,22 @@ def main():
         kernels[name] = {"launches": int(n), "total_ms": ms, "avg_us": 1e3 * ms / n, "units_per_launch": units / n, "unit": unit,
                          "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
+    # (profiles/r1k_frame_full.md: tracker 3.332864 MB + 1.024 KB, traceOn 2.419456 MB, pyramid 1.240320 MB + 0.256 KB)
+    traffic = {"k34_track_eval_kernel": 3333888.0, "k5_trace_kernel": 2419456.0, "k1_pyramid_kernel+k1_wrap_columns_kernel": 1240576.0}
     line = dict(base, value=aggregate_fps(world, steps, t_dev), ms_per_step=1e3 * t_dev / steps,
                 e2e={"value": aggregate_fps(world, steps, t_e2e), "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
                      "d2h_bytes_per_step": d2h / steps},
                 gpu_launches=int(launches),
                 clocks=clk.summary(),
                 roofline={"bound": "hbm", "kernel": top, "achieved": kernels[top]["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                          "frac": kernels[top]["frac"], "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                          "frac": kernels[top]["frac"], "traffic": traffic.get(top), "peak_source": "measured" if peaks else "fallback",
                           "launches": kernels[top]["launches"], "avg_us": kernels[top]["avg_us"],
                           "units_per_launch": kernels[top]["units_per_launch"],
-                          "note": "dominant kernel by summed launch time; single-sequence launches are latency-bound "
-                                  "(L2-resident working set), see DESIGN.md section 4"},
+                          "note": "dominant kernel by summed launch time (k34_track_level_kernel: the whole pyramid walk of one "
+                                  "frame in one cooperative launch, ~38 LM evaluations); single-sequence launches are "
+                                  "latency-bound (L2-resident working set), see DESIGN.md section 4; traffic from "
+                                  "profiles/r1k_frame_full.md; batched-window bandwidth figures: profiles/r1k_notes.md"},
                 kernels=kernels,
                 host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
                 gt_error_m=gt_err, keyframes=kf_tail)
