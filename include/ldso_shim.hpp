@@ -52,6 +52,13 @@ int LDSO_API(immature_compact)(LDSO_SHIM_CTX*, int, int, int, const int*, int*);
 int LDSO_API(immature_trace)(LDSO_SHIM_CTX*, int, int, const float*, const float*, const float*, int*);
 int LDSO_API(immature_get)(LDSO_SHIM_CTX*, float*, float*, float*, int*, float*, float*);
 int LDSO_API(immature_activate)(LDSO_SHIM_CTX*, int, const int*, int, float*, int*, int*);
+int LDSO_API(distmap_make)(LDSO_SHIM_CTX*, int, const float*, const float*, int, const int*, const float*, const float*, const float*);
+int LDSO_API(distmap_get)(LDSO_SHIM_CTX*, float*);
+int LDSO_API(immature_select_activation)(LDSO_SHIM_CTX*, int, const float*, const float*, const unsigned char*, const unsigned char*,
+                                         float, float, unsigned char*, int*);
+int LDSO_API(init_set_first)(LDSO_SHIM_CTX*, int, int*);
+int LDSO_API(init_track_frame)(LDSO_SHIM_CTX*, int, float, float, double*, float*, int*, int*, float*, int*);
+int LDSO_API(init_get_points)(LDSO_SHIM_CTX*, int, int*, float*, float*, float*, float*, unsigned char*, float*, float*, float*);
 int LDSO_API(window_set_frames)(LDSO_SHIM_CTX*, int, const int*, const float*, const float*, const float*);
 int LDSO_API(window_set_points)(LDSO_SHIM_CTX*, int, const float*, const float*, const float*, const float*, const int*,
                                 const float*, const float*, const float*, const int*);
@@ -190,10 +197,79 @@ public:
     }
 };
 
-// The immature points of the window as one device-resident pool (ldso::internal::ImmaturePoint, batched)
-class ImmaturePool {
+struct ImmaturePoolSize { int size = 0; };   // base of ImmaturePool (declared early for CoarseDistanceMap)
+
+// ldso::CoarseInitializer (include/frontend/CoarseInitializer.h:66-196)
+class CoarseInitializer {
 public:
-    int size = 0;
+    struct Pnt { float u, v, idepth, iR, my_type, lastHessian, energy; bool isGood; };   // the fields other code reads (:23-63)
+    int frameID = -1;
+    int numPoints[LDSO_MAX_LEVELS] = {0};
+    SE3 thisToNext;
+    AffLight thisToNext_aff;
+    const FrameHessian* firstFrame = nullptr;
+    bool snapped = false;
+    // void setFirst(shared_ptr<CalibHessian>, shared_ptr<FrameHessian>)  (CoarseInitializer.cc:656-737)
+    void setFirst(Context& c, const FrameHessian& first) {
+        firstFrame = &first;
+        c.check(LDSO_API(init_set_first)(c.h, first.slot, numPoints));
+        thisToNext = SE3(); thisToNext_aff = AffLight(); snapped = false; frameID = 0;
+    }
+    // bool trackFrame(shared_ptr<FrameHessian>)  (:45-183)
+    bool trackFrame(Context& c, const FrameHessian& newFrame) {
+        double Rt[12];
+        float aff[2], res[3];
+        int sn = 0, ready = 0, iters[LDSO_MAX_LEVELS];
+        c.check(LDSO_API(init_track_frame)(c.h, newFrame.slot, firstFrame->ab_exposure, newFrame.ab_exposure, Rt, aff, &sn, &ready, res,
+                                           iters));
+        thisToNext = SE3::fromRt(Rt);
+        thisToNext_aff.a = aff[0]; thisToNext_aff.b = aff[1];
+        snapped = sn != 0;
+        frameID++;
+        return ready != 0;
+    }
+    // points[lvl] as FullSystem::initializeFromInitializer reads them (FullSystem.cc:1500-1544)
+    std::vector<Pnt> points(Context& c, int lvl) {
+        int n = numPoints[lvl];
+        std::vector<float> u(n + 1), v(n + 1), id(n + 1), iR(n + 1), ty(n + 1), lh(n + 1), en(n + 1);
+        std::vector<unsigned char> good(n + 1);
+        c.check(LDSO_API(init_get_points)(c.h, lvl, &n, u.data(), v.data(), id.data(), iR.data(), good.data(), ty.data(), lh.data(),
+                                          en.data()));
+        std::vector<Pnt> out(n);
+        for (int i = 0; i < n; i++) out[i] = Pnt{u[i], v[i], id[i], iR[i], ty[i], lh[i], en[i], good[i] != 0};
+        return out;
+    }
+};
+
+// ldso::CoarseDistanceMap (include/frontend/CoarseTracker.h:95-135) + the candidate walk of FullSystem::activatePointsMT
+class CoarseDistanceMap {
+public:
+    // void makeDistanceMap(frameHessians, frame)  (CoarseTracker.cc:795-835): host[i] = window index of point i's host frame (-1: the
+    // newest frame's own points), KRKi / Kt = K[1] R Ki[0], K[1] t of host -> newest frame (FullSystem.cc:1236-1238)
+    void makeDistanceMap(Context& c, int nHosts, const float* KRKi, const float* Kt, const std::vector<int>& host,
+                         const std::vector<float>& u, const std::vector<float>& v, const std::vector<float>& idepth) {
+        c.check(LDSO_API(distmap_make)(c.h, nHosts, KRKi, Kt, (int)host.size(), host.data(), u.data(), v.data(), idepth.data()));
+    }
+    // float* fwdWarpedIDDistFinal, (w/2)*(h/2)
+    void fwdWarpedIDDistFinal(Context& c, std::vector<float>& out, int w1, int h1) {
+        out.resize((size_t)w1 * h1);
+        c.check(LDSO_API(distmap_get)(c.h, out.data()));
+    }
+    // FullSystem.cc:1226-1298 over the immature pool, addIntoDistFinal (CoarseTracker.cc:925-930) for every accepted point;
+    // action[i]: 0 keep, 1 delete, 2 optimise
+    void selectForActivation(Context& c, const ImmaturePoolSize& pool, int nHosts, const float* KRKi, const float* Kt,
+                             const unsigned char* hostIsNewest, const unsigned char* hostFlagged, float currentMinActDist,
+                             float minTraceQuality, std::vector<unsigned char>& action, int counts[2]) {
+        action.resize(pool.size > 0 ? pool.size : 1);
+        c.check(LDSO_API(immature_select_activation)(c.h, nHosts, KRKi, Kt, hostIsNewest, hostFlagged, currentMinActDist, minTraceQuality,
+                                                     action.data(), counts));
+        action.resize(pool.size);
+    }
+};
+
+// The immature points of the window as one device-resident pool (ldso::internal::ImmaturePoint, batched)
+class ImmaturePool : public ImmaturePoolSize {
+public:
     void clear(Context& c) {
         int dummy_i = 0;
         float dummy_f = 0;

@@ -66,6 +66,26 @@ int main(int argc, char** argv) {
         for (int i = 0; i < pool.size; i++)
             if (status[i] == (int)ImmaturePointStatus::IPS_GOOD) { sum += idmin[i] + idmax[i]; good++; }
         printf("depth %d %.9g\n", good, sum);
+        // CoarseInitializer::setFirst + one trackFrame, CoarseDistanceMap::makeDistanceMap (identity warp of the tracker points)
+        CoarseInitializer init;
+        init.setFirst(c, ref);
+        const bool ready = init.trackFrame(c, cur);
+        double iRt[12];
+        init.thisToNext.toRt(iRt);
+        auto pts = init.points(c, 0);
+        double irs = 0;
+        for (auto& p : pts) irs += p.iR;
+        printf("init %d %d %d %d %.9g %.9g %.9g %.9g\n", init.numPoints[0], init.numPoints[1], ready ? 1 : 0, init.snapped ? 1 : 0, iRt[9],
+               iRt[10], iRt[11], irs);
+        CoarseDistanceMap dm;
+        const float K1[9] = {0.5f, 0, -0.25f, 0, 0.5f, -0.25f, 0, 0, 1}, Kt0[3] = {0, 0, 0};
+        std::vector<int> hostIdx(n, 0);
+        dm.makeDistanceMap(c, 1, K1, Kt0, hostIdx, u, v, idp);
+        std::vector<float> D;
+        dm.fwdWarpedIDDistFinal(c, D, w / 2, h / 2);
+        double dsum = 0;
+        for (float d : D) dsum += d;
+        printf("distmap %.9g\n", dsum);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 1;

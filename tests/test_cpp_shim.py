@@ -44,7 +44,14 @@ def _expected(api, calib, data):
     cnt = ctx.immature_trace(1, tab[:9].reshape(1, 9), tab[9:12].reshape(1, 3), tab[12:14].reshape(1, 2))
     g = ctx.immature_get()
     good = g["status"] == 0
-    return r, len(su), pot, cnt, int(good.sum()), float((g["idepth_min"][good].astype(np.float64) + g["idepth_max"][good]).sum())
+    out = (r, len(su), pot, cnt, int(good.sum()), float((g["idepth_min"][good].astype(np.float64) + g["idepth_max"][good]).sum()))
+    n = ctx.init_set_first(0)
+    ri = ctx.init_track_frame(1)
+    P = ctx.init_get_points(0)
+    K1 = np.array([[0.5, 0, -0.25], [0, 0.5, -0.25], [0, 0, 1]], np.float32)[None]
+    ctx.distmap_make(K1, np.zeros((1, 3), np.float32), np.zeros(len(u), np.int32), u, v, idp)
+    extra = (n, ri, float(P["iR"].astype(np.float64).sum()), float(ctx.distmap_get().astype(np.float64).sum()))
+    return out + (extra,)
 
 
 def _run(exe, blob):
@@ -54,7 +61,12 @@ def _run(exe, blob):
 
 
 def _check(got, exp):
-    r, nsel, pot, cnt, ngood, dsum = exp
+    r, nsel, pot, cnt, ngood, dsum, (n_init, ri, irs, dmsum) = exp
+    it = got["init"]
+    assert [int(it[0]), int(it[1])] == [int(n_init[0]), int(n_init[1])] and int(it[2]) == int(ri["ready"]) and int(it[3]) == int(ri["snapped"])
+    assert np.allclose([float(x) for x in it[4:7]], ri["pose"][9:], rtol=1e-4, atol=1e-7)
+    assert abs(float(it[7]) - irs) <= 1e-4 * abs(irs)
+    assert abs(float(got["distmap"][0]) - dmsum) <= 1e-6 * abs(dmsum)
     tr = [float(x) for x in got["track"]]
     assert int(tr[0]) == int(r["ok"])
     assert np.allclose(tr[1:13], r["pose"], rtol=0, atol=1e-12)
