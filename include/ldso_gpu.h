@@ -260,6 +260,24 @@ int ldso_gpu_init_get_graph(ldso_gpu_ctx* ctx, int lvl, int* neighbours, int* pa
 int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* ctx, int slot, int lvl, const double ref_to_new[12], float aff_a, float aff_b,
                                   float H[64], float b[8], float Hsc[64], float bsc[8], float res[3]);
 
+/* ---- N4: photometric + geometric undistortion in front of makeImages (src/frontend/Undistort.cc) -----------------
+ * Tables of an Undistort object, uploaded once: the raw sensor size, the inverse response G (PhotometricUndistorter::G,
+ * g_depth = 256 or 65536 entries; NULL = no photometric calibration), vignetteMapInv [w_org*h_org] (NULL = none), and the
+ * rectification lookup remapX / remapY [w*h] of the output size of this ctx (Undistort.cc:300-364 builds them on the host
+ * from the camera model; NULL = passthrough, which needs w_org == w and h_org == h).  photometric_mode =
+ * setting_photometricCalibration (0 off, 1 response only, 2 response + vignette). */
+int ldso_gpu_undistort_set(ldso_gpu_ctx* ctx, int w_org, int h_org, int g_depth, const float* G, const float* vignette_inv,
+                           const float* remap_x, const float* remap_y, int photometric_mode);
+/* Undistort::undistort<T> (:366-458) = PhotometricUndistorter::processFrame<T> (:190-230: factor * raw when there is no
+ * calibration or exposure_time <= 0, else G[raw] (* vignetteMapInv)) followed by the bilinear remap (out = 0 where
+ * remapX < 0), then FrameHessian::makeImages on the result, all on the device: only the raw 8- or 16-bit image
+ * (bytes_per_pixel 1 or 2) crosses the bus.  The benchmark-only noise / blur options (benchmark_varNoise,
+ * benchmark_varBlurNoise) are not part of this path. */
+int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* ctx, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
+                                   float factor);
+/* ImageAndExposure::image of the last ldso_gpu_frame_make_images_raw: w*h floats */
+int ldso_gpu_undistort_get_image(ldso_gpu_ctx* ctx, float* image_out);
+
 /* ==== windowed bundle adjustment (K7-K10, H1) ======================================================
  * The window is described by the host (it owns the shared_ptr graph) as index arrays; the device keeps
  * points and residuals as SoA/AoS pools.  Index conventions follow the reference: pair tables are

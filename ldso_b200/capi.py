@@ -324,6 +324,27 @@ class Ctx:
                    act.ctypes.data_as(C.c_void_p), _ip(cnt))
         return act[:self.imm_n], (int(cnt[0]), int(cnt[1]))
 
+    # ---- N4: undistortion in front of makeImages ----
+    def undistort_set(self, w_org, h_org, G=None, vignette_inv=None, remap_x=None, remap_y=None, photometric_mode=2):
+        G = None if G is None else f32(G)
+        vig = None if vignette_inv is None else f32(vignette_inv)
+        rx = None if remap_x is None else f32(remap_x)
+        ry = None if remap_y is None else f32(remap_y)
+        self._call("undistort_set", C.c_int(w_org), C.c_int(h_org), C.c_int(0 if G is None else len(G)), _fp(G), _fp(vig), _fp(rx),
+                   _fp(ry), C.c_int(photometric_mode))
+
+    def make_images_raw(self, slot, raw, exposure_time=1.0, factor=1.0):
+        raw = np.ascontiguousarray(raw)
+        assert raw.dtype in (np.uint8, np.uint16)
+        self._call("frame_make_images_raw", C.c_int(slot), raw.ctypes.data_as(C.c_void_p), C.c_int(raw.dtype.itemsize),
+                   C.c_float(exposure_time), C.c_float(factor))
+
+    def undistort_get_image(self):
+        w, h = self.sizes[0]
+        out = np.zeros((h, w), np.float32)
+        self._call("undistort_get_image", _fp(out))
+        return out
+
     # ---- N1: CoarseInitializer ----
     def init_set_first(self, slot):
         n = np.zeros(MAX_LEVELS, np.int32)

@@ -42,10 +42,12 @@ __device__ __forceinline__ float abs_sq_grad(float I, float dx, float dy, const 
     return a;
 }
 
+// L = number of pyramid levels, a template parameter so that the shared-memory tile geometry is a compile-time constant:
+// the fill / box / store loops unroll completely and all global loads of a thread are in flight at once
+template <int L>
 __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __restrict__ img, float4* __restrict__ out,
                                                                  const float* __restrict__ B, const K1Params p) {
     extern __shared__ float sm[];
-    const int L = p.levels;
     const int tid = threadIdx.x;
     const int X0 = blockIdx.x * K1_TW, Y0 = blockIdx.y * K1_TH;
     int soff[LDSO_MAX_LEVELS], sw[LDSO_MAX_LEVELS], sh[LDSO_MAX_LEVELS];
@@ -67,7 +69,10 @@ __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __r
         const int h0 = 1 << (L - 1);
         const int w = p.w[0], h = p.h[0];
         const int n = sw[0] * sh[0];
-        for (int i = tid; i < n; i += K1_THREADS) {
+#pragma unroll
+        for (int k_ = 0; k_ < (n + K1_THREADS - 1) / K1_THREADS; k_++) {
+            const int i = tid + k_ * K1_THREADS;
+            if (i >= n) continue;
             int sy = i / sw[0], sx = i - sy * sw[0];
             int gx = X0 - h0 + sx, gy = Y0 - h0 + sy;
             float v = 0.f;
@@ -77,12 +82,16 @@ __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __r
     }
     __syncthreads();
     // levels 1..L-1: hierarchical 2x2 box, FrameHessian.cc:86-92
+#pragma unroll
     for (int l = 1; l < L; l++) {
         const float* src = sm + soff[l - 1];
         float* dst = sm + soff[l];
         const int swp = sw[l - 1];
         const int n = sw[l] * sh[l];
-        for (int i = tid; i < n; i += K1_THREADS) {
+#pragma unroll
+        for (int k_ = 0; k_ < (n + K1_THREADS - 1) / K1_THREADS; k_++) {
+            const int i = tid + k_ * K1_THREADS;
+            if (i >= n) continue;
             int sy = i / sw[l], sx = i - sy * sw[l];
             const float* q = src + (2 * sy) * swp + 2 * sx;
             float s = __fadd_rn(__fadd_rn(__fadd_rn(q[0], q[1]), q[swp]), q[swp + 1]);
@@ -91,6 +100,7 @@ __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __r
         __syncthreads();
     }
     // gradients + fused texel store, FrameHessian.cc:95-114
+#pragma unroll
     for (int l = 0; l < L; l++) {
         const int hl = 1 << (L - 1 - l);
         const int tw = K1_TW >> l, th = K1_TH >> l;
@@ -99,7 +109,10 @@ __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __r
         const int swl = sw[l];
         float4* o = out + p.off[l];
         const int n = tw * th;
-        for (int i = tid; i < n; i += K1_THREADS) {
+#pragma unroll
+        for (int k_ = 0; k_ < (n + K1_THREADS - 1) / K1_THREADS; k_++) {
+            const int i = tid + k_ * K1_THREADS;
+            if (i >= n) continue;
             int ty = i / tw, tx = i - ty * tw;
             int gx = (X0 >> l) + tx, gy = (Y0 >> l) + ty;
             if (gx >= wl || gy >= hgt) continue;
@@ -154,14 +167,20 @@ int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
         smem_floats += ((K1_TW >> l) + 2 * hl) * ((K1_TH >> l) + 2 * hl);
         border += 2 * (c->hG[l] - 2);
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k1_pyramid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        attr_set = true;
-    }
     dim3 grid((c->wG[0] + K1_TW - 1) / K1_TW, (c->hG[0] + K1_TH - 1) / K1_TH);
+    const size_t smem = smem_floats * sizeof(float);
     prof_begin(c, c->stream);
-    k1_pyramid_kernel<<<grid, K1_THREADS, smem_floats * sizeof(float), c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p);
+#define K1_LAUNCH(LV)                                                                                                          \
+    case LV: {                                                                                                                 \
+        static bool attr_set = false;                                                                                          \
+        if (!attr_set) { cudaFuncSetAttribute(k1_pyramid_kernel<LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr_set = true; } \
+        k1_pyramid_kernel<LV><<<grid, K1_THREADS, smem, c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p);             \
+    } break;
+    switch (c->levels) {
+        K1_LAUNCH(1) K1_LAUNCH(2) K1_LAUNCH(3) K1_LAUNCH(4) K1_LAUNCH(5) K1_LAUNCH(6)
+        default: LDSO_REQUIRE(c, c->levels >= 1 && c->levels <= 6);
+    }
+#undef K1_LAUNCH
     k1_wrap_columns_kernel<<<(border + 127) / 128, 128, 0, c->stream>>>(c->frame[slot], c->gammaB_dev, p);
     prof_end(c, c->stream, LDSO_PROF_K1, 1);
     c->launches += 2;

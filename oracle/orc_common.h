@@ -138,7 +138,7 @@ struct orc_ctx {
     std::vector<orc::Frame> frames;
     orc::Tracker trk[LDSO_NUM_TRACKERS];
     orc::Window win;
-    std::shared_ptr<void> selector, immature, initializer;   // per-ctx state of orc_selector.cpp / orc_immature.cpp / orc_initializer.cpp (die with the ctx)
+    std::shared_ptr<void> selector, immature, initializer, undistort;   // per-ctx state of orc_selector.cpp / orc_immature.cpp / orc_initializer.cpp (die with the ctx)
     std::string err;
     long long launches = 0;
     int threads = 1;   // worker threads of the timing build (env ORC_THREADS at create; the reference uses NUM_THREADS = 6)

@@ -639,3 +639,70 @@ extern "C" int orc_tracker_track(orc_ctx* c, int tracker, int new_slot, float ne
     aff_io[0] = out_a; aff_io[1] = out_b;
     return 0;
 }
+
+// =================================================================================================
+// N4 — Undistort::undistort<T> (src/frontend/Undistort.cc:366-458) with PhotometricUndistorter::processFrame<T>
+// (:190-230), in the reference's two passes: the whole raw image through the response / vignette first, then the remap.
+namespace {
+struct UndistortState {
+    int w_org = 0, h_org = 0, g_depth = 0, mode = 0;
+    bool has_G = false, has_vig = false, has_remap = false;
+    std::vector<float> G, vig, remap_x, remap_y, image;
+};
+UndistortState* undist(orc_ctx* c) {
+    if (!c->undistort) c->undistort = std::make_shared<UndistortState>();
+    return (UndistortState*)c->undistort.get();
+}
+}  // namespace
+
+extern "C" int orc_undistort_set(orc_ctx* c, int w_org, int h_org, int g_depth, const float* G, const float* vignette_inv,
+                                 const float* remap_x, const float* remap_y, int photometric_mode) {
+    if (w_org <= 0 || h_org <= 0 || ((remap_x == nullptr) != (remap_y == nullptr))) return -2;
+    if (!remap_x && (w_org != c->cfg.w || h_org != c->cfg.h)) return -2;
+    c->undistort = std::make_shared<UndistortState>();
+    UndistortState* U = undist(c);
+    U->w_org = w_org; U->h_org = h_org; U->g_depth = g_depth; U->mode = photometric_mode;
+    const size_t no = (size_t)w_org * h_org, n = (size_t)c->cfg.w * c->cfg.h;
+    if (G) { U->G.assign(G, G + g_depth); U->has_G = true; }
+    if (vignette_inv) { U->vig.assign(vignette_inv, vignette_inv + no); U->has_vig = true; }
+    if (remap_x) { U->remap_x.assign(remap_x, remap_x + n); U->remap_y.assign(remap_y, remap_y + n); U->has_remap = true; }
+    return 0;
+}
+
+extern "C" int orc_frame_make_images_raw(orc_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time, float factor) {
+    auto U = undist(c);
+    if (U->w_org == 0 || !raw || (bytes_per_pixel != 1 && bytes_per_pixel != 2)) return -2;
+    const int wOrg = U->w_org, hOrg = U->h_org, w = c->cfg.w, h = c->cfg.h;
+    const int wh = wOrg * hOrg;
+    std::vector<float> data(wh);
+    auto in = [&](int i) -> unsigned { return bytes_per_pixel == 1 ? ((const unsigned char*)raw)[i] : ((const unsigned short*)raw)[i]; };
+    if (!U->has_G || exposure_time <= 0 || U->mode == 0) {                       // processFrame :197-204
+        for (int i = 0; i < wh; i++) data[i] = factor * (float)in(i);
+    } else {
+        for (int i = 0; i < wh; i++) data[i] = U->G[in(i)];
+        if (U->mode == 2 && U->has_vig)
+            for (int i = 0; i < wh; i++) data[i] *= U->vig[i];
+    }
+    U->image.assign((size_t)w * h, 0.f);
+    if (U->has_remap) {
+        for (int idx = w * h - 1; idx >= 0; idx--) {                             // undistort :400-447
+            float xx = U->remap_x[idx], yy = U->remap_y[idx];
+            if (xx < 0) { U->image[idx] = 0; continue; }
+            int xxi = xx, yyi = yy;
+            xx -= xxi; yy -= yyi;
+            float xxyy = xx * yy;
+            const float* src = data.data() + xxi + yyi * wOrg;
+            U->image[idx] = xxyy * src[1 + wOrg] + (yy - xxyy) * src[wOrg] + (xx - xxyy) * src[1] + (1 - xx - yy + xxyy) * src[0];
+        }
+    } else {
+        memcpy(U->image.data(), data.data(), sizeof(float) * (size_t)w * h);
+    }
+    return orc_frame_make_images(c, slot, U->image.data());
+}
+
+extern "C" int orc_undistort_get_image(orc_ctx* c, float* image_out) {
+    auto U = undist(c);
+    if (U->image.empty()) return -2;
+    memcpy(image_out, U->image.data(), sizeof(float) * U->image.size());
+    return 0;
+}
