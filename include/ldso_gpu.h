@@ -260,6 +260,18 @@ int ldso_gpu_init_get_graph(ldso_gpu_ctx* ctx, int lvl, int* neighbours, int* pa
 int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* ctx, int slot, int lvl, const double ref_to_new[12], float aff_a, float aff_b,
                                   float H[64], float b[8], float Hsc[64], float bsc[8], float res[3]);
 
+/* ---- N3: FeatureDetector::DetectCorners (src/frontend/FeatureDetector.cc:34-124), the part before the descriptors ------
+ * The image is cut into cells of gridsize = int(sqrtf(w h / n_features) + 0.5); in every cell away from the border
+ * (skip = 2 HALF_PATCH_SIZE / gridsize + 1 cells) the pixels whose absSquaredGrad exceeds max(0.5 * cell maximum, 5) are
+ * scored with ShiTomasiScore (include/frontend/FeatureDetector.h:50-81, 8x8 box of dIp gradients) and the best
+ * floor(nfeatInGrid) + 1 become features, cells in column-major order (gx outer, gy inner), features of a cell by
+ * descending score (equal scores keep the candidate order x outer, y inner: std::sort's order among ties is unspecified).
+ * is_corner: score > 0.01 * (maximum score over ALL candidates), minus the lower-scored one of every pair of such
+ * features closer than 5 px (:95-110).  IC_Angle and the rotated-BRIEF descriptor (:112-123) stay on the host.
+ * Returns at most max_out features; *n_out = number written, *n_corners = how many carry is_corner. */
+int ldso_gpu_detect_corners(ldso_gpu_ctx* ctx, int slot, int n_features, int max_out, float* x, float* y, float* score,
+                            unsigned char* is_corner, int* n_out, int* n_corners);
+
 /* ---- N4: photometric + geometric undistortion in front of makeImages (src/frontend/Undistort.cc) -----------------
  * Tables of an Undistort object, uploaded once: the raw sensor size, the inverse response G (PhotometricUndistorter::G,
  * g_depth = 256 or 65536 entries; NULL = no photometric calibration), vignetteMapInv [w_org*h_org] (NULL = none), and the

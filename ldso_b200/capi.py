@@ -324,6 +324,18 @@ class Ctx:
                    act.ctypes.data_as(C.c_void_p), _ip(cnt))
         return act[:self.imm_n], (int(cnt[0]), int(cnt[1]))
 
+    # ---- N3: FeatureDetector::DetectCorners ----
+    def detect_corners(self, slot, n_features, max_out=None):
+        w, h = self.sizes[0]
+        max_out = max_out or 4 * n_features + 64
+        x, y, sc = (np.zeros(max_out, np.float32) for _ in range(3))
+        fl = np.zeros(max_out, np.uint8)
+        n, nc = C.c_int(), C.c_int()
+        self._call("detect_corners", C.c_int(slot), C.c_int(n_features), C.c_int(max_out), _fp(x), _fp(y), _fp(sc),
+                   fl.ctypes.data_as(C.c_void_p), C.byref(n), C.byref(nc))
+        k = n.value
+        return x[:k], y[:k], sc[:k], fl[:k].astype(bool), nc.value
+
     # ---- N4: undistortion in front of makeImages ----
     def undistort_set(self, w_org, h_org, G=None, vignette_inv=None, remap_x=None, remap_y=None, photometric_mode=2):
         G = None if G is None else f32(G)

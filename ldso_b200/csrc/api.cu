@@ -135,6 +135,7 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     immature_free(c);
     initializer_free(c);
     undistort_free(c);
+    corners_free(c);
     cudaFree(c->img_dev); cudaFreeHost(c->img_pinned); cudaFreeHost(c->scratch_host); cudaFree(c->gammaB_dev);
     cudaFree(c->trk_partials); cudaFree(c->trk_partials_i); cudaFree(c->trk_counter); cudaFree(c->trk_result_dev);
     cudaFreeHost(c->trk_result_pinned);

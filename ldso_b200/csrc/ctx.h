@@ -95,6 +95,7 @@ struct ldso_gpu_ctx {
     void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use
     void* initializer = nullptr;            // InitDev (n1_initializer.cu), created on first use
     void* undistort = nullptr;              // UndistortDev (n4_undistort.cu), created by ldso_gpu_undistort_set
+    void* corners = nullptr;                // N3Dev (n3_corners.cu), created on first use
     long long launches = 0;
     long long h2d_bytes = 0, d2h_bytes = 0;   // bytes moved by the entry points (bench.py e2e accounting)
     // optional per-kernel CUDA-event profile (ldso_gpu_profile_*); slots: see LDSO_PROF_* in include/ldso_gpu.h.
@@ -131,6 +132,7 @@ void prof_drain(ldso_gpu_ctx* c);
 void immature_free(ldso_gpu_ctx* c);
 void initializer_free(ldso_gpu_ctx* c);
 void undistort_free(ldso_gpu_ctx* c);
+void corners_free(ldso_gpu_ctx* c);
 int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev);
 int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u, const float* v, const float* id,
                const float* hdi);

@@ -4,6 +4,8 @@
 // Decision recorded in SURVEY.md trap T3: ths / thsSmoothed are zero-filled at allocation.
 #include "orc_common.h"
 
+#include <algorithm>
+
 using namespace orc;
 
 namespace {
@@ -220,5 +222,92 @@ extern "C" int orc_select_points(orc_ctx* c, int slot, float density, int recurs
             if (n < max_points) { u_out[n] = (float)x; v_out[n] = (float)y; type_out[n] = m; n++; }
         }
     *n_points = n;
+    return 0;
+}
+
+// =================================================================================================
+// N3 — FeatureDetector::DetectCorners (src/frontend/FeatureDetector.cc:34-124) up to the corner flags;
+// ShiTomasiScore: include/frontend/FeatureDetector.h:50-81
+namespace {
+float shiTomasiScore(const float* dIp, int wl, int hl, float u, float v) {
+    const int halfbox = 4;
+    float dXX = 0.0, dYY = 0.0, dXY = 0.0;
+    const int box_size = 2 * halfbox, box_area = box_size * box_size;
+    const int x_min = u - halfbox, x_max = u + halfbox, y_min = v - halfbox, y_max = v + halfbox;
+    if (x_min < 1 || x_max >= wl - 1 || y_min < 1 || y_max >= hl - 1) return 0.0;
+    for (int y = y_min; y < y_max; ++y)
+        for (int x = x_min; x < x_max; ++x) {
+            const float dx = dIp[3 * (y * wl + x) + 1], dy = dIp[3 * (y * wl + x) + 2];
+            dXX += dx * dx; dYY += dy * dy; dXY += dx * dy;
+        }
+    dXX = dXX / (2.0 * box_area); dYY = dYY / (2.0 * box_area); dXY = dXY / (2.0 * box_area);
+    // `using namespace std` is in effect in the reference (include/NumTypes.h:12), so its unqualified sqrt(float) is std::sqrt(float)
+    return 0.5 * (dXX + dYY - sqrtf((dXX + dYY) * (dXX + dYY) - 4 * (dXX * dYY - dXY * dXY)));
+}
+}  // namespace
+
+extern "C" int orc_detect_corners(orc_ctx* c, int slot, int nFeatures, int max_out, float* ox, float* oy, float* oscore,
+                                  unsigned char* is_corner, int* n_out, int* n_corners) {
+    const int w = c->wG[0], h = c->hG[0];
+    const float* grad = c->frames[slot].absSquaredGrad[0].data();
+    const float* dIp = c->frames[slot].dIp[0].data();
+    const int HALF_PATCH_SIZE = 15;
+    int gridsize = int(sqrtf(w * h / nFeatures) + 0.5);
+    int gridX = w / gridsize + 1, gridY = h / gridsize + 1;
+    float nfeatInGrid = float(nFeatures) / (w * h) * (gridsize * gridsize);
+    float maxScore = 0, scoreTH = 0;
+    int skip = (HALF_PATCH_SIZE * 2 / gridsize) + 1;
+    struct F { float x, y, score; bool corner; };
+    std::vector<F> feats;
+    for (int gx = skip; gx < gridX - skip; gx++)
+        for (int gy = skip; gy < gridY - skip; gy++) {
+            float maxGrad = 0, gradTH = 0;
+            const float* gradData = &grad[gy * gridsize * w + gx * gridsize];
+            for (int x = 0; x < gridsize; x++)
+                for (int y = 0; y < gridsize; y++)
+                    if (gradData[y * w + x] > maxGrad) maxGrad = gradData[y * w + x];
+            std::vector<std::pair<int, float>> candidate;
+            gradTH = (0.5 * maxGrad) > 5 ? 0.5 * maxGrad : 5;
+            int picked = 0;
+            for (int x = 0; x < gridsize; x++)
+                for (int y = 0; y < gridsize; y++) {
+                    int idx = y * gridsize + x;
+                    if (gradData[y * w + x] > gradTH) {
+                        int realX = gx * gridsize + x, realY = gy * gridsize + y;
+                        float s = shiTomasiScore(dIp, w, h, realX, realY);
+                        candidate.push_back(std::pair<int, float>(idx, s));
+                        if (s > maxScore) maxScore = s;
+                    }
+                }
+            std::stable_sort(candidate.begin(), candidate.end(),
+                             [](const std::pair<int, float>& p1, const std::pair<int, float>& p2) { return p1.second > p2.second; });
+            for (auto& p : candidate) {
+                int x = p.first % gridsize, y = p.first / gridsize;
+                feats.push_back(F{(float)(gx * gridsize + x), (float)(gy * gridsize + y), p.second, false});
+                picked++;
+                if (picked > (nfeatInGrid)) break;
+            }
+        }
+    scoreTH = 0.01 * maxScore;
+    std::vector<int> corners;
+    for (size_t i = 0; i < feats.size(); i++)
+        if (feats[i].score > scoreTH) { feats[i].corner = true; corners.push_back((int)i); }
+    for (size_t i = 0; i < corners.size(); i++)
+        for (size_t j = i + 1; j < corners.size(); j++) {
+            F &f1 = feats[corners[i]], &f2 = feats[corners[j]];
+            const float dx = f1.x - f2.x, dy = f1.y - f2.y;
+            if (sqrtf(dx * dx + dy * dy) < 5) {
+                if (f1.score > f2.score) f2.corner = false;
+                else f1.corner = false;
+            }
+        }
+    int n = 0, nc = 0;
+    for (const F& f : feats) {
+        if (n >= max_out) break;
+        ox[n] = f.x; oy[n] = f.y; oscore[n] = f.score; is_corner[n] = f.corner ? 1 : 0;
+        nc += f.corner ? 1 : 0;
+        n++;
+    }
+    *n_out = n; *n_corners = nc;
     return 0;
 }
