@@ -63,13 +63,15 @@ def from_rt12(p):
 
 
 class Odometry:
-    def __init__(self, api, calib, desired_points=2000, desired_immature=1500, max_frames=7, ba_iterations=6, seed=0, **cfg_kw):
+    def __init__(self, api, calib, desired_points=2000, desired_immature=1500, max_frames=7, ba_iterations=6, seed=0,
+                 point_selection=0, **cfg_kw):
         self.c = dict(calib)
         cfg = api.default_config(w=calib["w"], h=calib["h"], fx=calib["fx"], fy=calib["fy"], cx=calib["cx"], cy=calib["cy"],
                                  affine_opt_mode_a=0.0, affine_opt_mode_b=0.0, n_frame_slots=max_frames + 3,
                                  max_points=4 * desired_points, max_residuals=4 * desired_points * max_frames, **cfg_kw)
         self.ctx = api.create(cfg)
         self.desired_points, self.desired_immature, self.max_frames, self.ba_its = desired_points, desired_immature, max_frames, ba_iterations
+        self.point_selection = point_selection       # setting_pointSelection: 0 = DSO PixelSelector, 1 = LDSO corner detector (N3)
         self.K = np.array([[calib["fx"], 0, calib["cx"]], [0, calib["fy"], calib["cy"]], [0, 0, 1]], dtype=np.float32)
         self.Ki = np.linalg.inv(self.K.astype(np.float64)).astype(np.float32)
         self.frames = []                 # keyframes in the window: dict(id, slot, w2c=(R,t), aff=(a,b))
@@ -120,7 +122,13 @@ class Odometry:
 
     def make_new_traces(self, f):
         """FullSystem::makeNewTraces (:1426-1482): selector + ImmaturePoint constructor on keyframe f, appended to the device pool"""
-        u, v, typ, self.potential = self.ctx.select_points(f["slot"], self.desired_immature, potential=self.potential, border=5)
+        if self.point_selection == 1:
+            # FullSystem.cc:1428-1438: every feature of FeatureDetector::DetectCorners becomes an immature point of type 1
+            u, v, _, corner, _ = self.ctx.detect_corners(f["slot"], self.desired_immature)
+            typ = np.ones(len(u), np.float32)
+            f["n_corners"] = int(corner.sum())
+        else:
+            u, v, typ, self.potential = self.ctx.select_points(f["slot"], self.desired_immature, potential=self.potential, border=5)
         col, wgt, gh, eth = self.ctx.immature_create(f["slot"], u, v)
         ok = np.isfinite(eth)
         k = int(ok.sum())
