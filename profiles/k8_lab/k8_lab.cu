@@ -1,0 +1,499 @@
+// k8_lab.cu — standalone timing lab for the K8 top-Hessian accumulation (profiles/r1k_notes.md): synthetic 72-float records,
+// key-sorted gather order like a 64x batched window, several kernel designs timed with CUDA events after an L2 flush.
+//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -fmad=false -o k8_lab k8_lab.cu && ./k8_lab
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <numeric>
+#include <vector>
+
+constexpr int JF = 72, NV = 91, STRIDE = 96, T = 128;
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); exit(1); } } while (0)
+
+// the 91 products of one record (mode 0 of k8_top_kernel), accumulated into acc
+__device__ __forceinline__ void products(const float* j, float* acc) {
+    float JI_r0 = 0, JI_r1 = 0, Jab_r0 = 0, Jab_r1 = 0, rr = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        JI_r0 += j[i] * j[8 + i]; JI_r1 += j[i] * j[16 + i]; Jab_r0 += j[i] * j[24 + i]; Jab_r1 += j[i] * j[32 + i]; rr += j[i] * j[i];
+    }
+    float x[10], y[10];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { x[i] = j[52 + i]; y[i] = j[56 + i]; }
+#pragma unroll
+    for (int i = 0; i < 6; i++) { x[4 + i] = j[40 + i]; y[4 + i] = j[46 + i]; }
+    const float a = j[62], b = j[63], cc = j[64];
+    int idx = 0;
+#pragma unroll
+    for (int r = 0; r < 10; r++)
+#pragma unroll
+        for (int c = r; c < 10; c++) acc[idx++] += a * x[c] * x[r] + cc * y[c] * y[r] + b * (x[c] * y[r] + y[c] * x[r]);
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        acc[55 + 3 * r] += x[r] * j[65] + y[r] * j[66];
+        acc[56 + 3 * r] += x[r] * j[67] + y[r] * j[68];
+        acc[57 + 3 * r] += x[r] * JI_r0 + y[r] * JI_r1;
+    }
+    acc[85] += j[69]; acc[86] += j[70]; acc[87] += Jab_r0; acc[88] += j[71]; acc[89] += Jab_r1; acc[90] += rr;
+}
+
+// the same 91 sums with the 2x2 weight applied once per column (p = a x + b y, q = b x + c y; entry = x_c p_r + y_c q_r) and
+// explicit fused multiply-adds: 2 FMA per Hessian entry instead of 9 mul/add.  Rounding differs from the reference's
+// mul/add order by ~1 ulp per term; the sums are compared at 1e-4 anyway (summation order).
+__device__ __forceinline__ void products_fast(const float* j, float* acc) {
+    float JI_r0 = 0, JI_r1 = 0, Jab_r0 = 0, Jab_r1 = 0, rr = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        JI_r0 = __fmaf_rn(j[i], j[8 + i], JI_r0); JI_r1 = __fmaf_rn(j[i], j[16 + i], JI_r1);
+        Jab_r0 = __fmaf_rn(j[i], j[24 + i], Jab_r0); Jab_r1 = __fmaf_rn(j[i], j[32 + i], Jab_r1); rr = __fmaf_rn(j[i], j[i], rr);
+    }
+    float x[10], y[10], p[10], q[10];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { x[i] = j[52 + i]; y[i] = j[56 + i]; }
+#pragma unroll
+    for (int i = 0; i < 6; i++) { x[4 + i] = j[40 + i]; y[4 + i] = j[46 + i]; }
+    const float a = j[62], b = j[63], cc = j[64];
+#pragma unroll
+    for (int i = 0; i < 10; i++) { p[i] = __fmaf_rn(b, y[i], a * x[i]); q[i] = __fmaf_rn(cc, y[i], b * x[i]); }
+    int idx = 0;
+#pragma unroll
+    for (int r = 0; r < 10; r++)
+#pragma unroll
+        for (int c = r; c < 10; c++) { acc[idx] = __fmaf_rn(x[c], p[r], __fmaf_rn(y[c], q[r], acc[idx])); idx++; }
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        acc[55 + 3 * r] = __fmaf_rn(x[r], j[65], __fmaf_rn(y[r], j[66], acc[55 + 3 * r]));
+        acc[56 + 3 * r] = __fmaf_rn(x[r], j[67], __fmaf_rn(y[r], j[68], acc[56 + 3 * r]));
+        acc[57 + 3 * r] = __fmaf_rn(x[r], JI_r0, __fmaf_rn(y[r], JI_r1, acc[57 + 3 * r]));
+    }
+    acc[85] += j[69]; acc[86] += j[70]; acc[87] += Jab_r0; acc[88] += j[71]; acc[89] += Jab_r1; acc[90] += rr;
+}
+#ifdef FAST
+#define products products_fast
+#endif
+
+__device__ __forceinline__ void cta_reduce_and_add(float* acc, int key, double* out) {
+    __shared__ float s[T / 32][STRIDE];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        float v = acc[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s[wid][i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        float v = 0;
+#pragma unroll
+        for (int q = 0; q < T / 32; q++) v += s[q][threadIdx.x];
+        if (v != 0.f) atomicAdd(out + (size_t)key * STRIDE + threadIdx.x, (double)v);
+    }
+}
+
+// A: the shipped design — thread per record, 18 LDG.128 at 288-byte lane stride
+__global__ void __launch_bounds__(T) kA(const int* chunk, const int* order, const float* J, double* out) {
+    const int key = chunk[3 * blockIdx.x], start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0;
+    for (int t = threadIdx.x; t < count; t += T) {
+        const float4* j4 = (const float4*)(J + (size_t)order[start + t] * JF);
+        float j[JF];
+#pragma unroll
+        for (int i = 0; i < JF / 4; i++) { float4 v = __ldg(j4 + i); j[4 * i] = v.x; j[4 * i + 1] = v.y; j[4 * i + 2] = v.z; j[4 * i + 3] = v.w; }
+        products(j, acc);
+    }
+    cta_reduce_and_add(acc, key, out);
+}
+
+// B: loads only (same pattern as A), one value per thread kept alive
+__global__ void __launch_bounds__(T) kB(const int* chunk, const int* order, const float* J, double* out) {
+    const int start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
+    float sum = 0;
+    for (int t = threadIdx.x; t < count; t += T) {
+        const float4* j4 = (const float4*)(J + (size_t)order[start + t] * JF);
+#pragma unroll
+        for (int i = 0; i < JF / 4; i++) { float4 v = __ldg(j4 + i); sum += v.x + v.y + v.z + v.w; }
+    }
+    if (sum == 123.456f) out[0] = sum;
+}
+
+// D: warp-private shared tile — a warp copies 32 records with coalesced 16-byte loads (18 consecutive lanes per record),
+// each lane reads its record back with conflict-free LDS.128 (row stride 76 floats); only __syncwarp, no CTA barrier
+constexpr int ROW = 76;
+template <bool PRODUCTS>
+__global__ void __launch_bounds__(T) kD(const int* chunk, const int* order, const float* J, double* out) {
+    __shared__ __align__(16) float tile[T / 32][32 * ROW];
+    const int key = chunk[3 * blockIdx.x], start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0;
+    float* my = tile[wid];
+    __shared__ int s_r[T / 32][32];
+    for (int base = wid * 32; base < count; base += T) {
+        const int nb = min(32, count - base);
+        __syncwarp();
+        s_r[wid][lane] = lane < nb ? order[start + base + lane] : 0;
+        __syncwarp();
+#pragma unroll 6
+        for (int q = lane; q < nb * 18; q += 32) {
+            const int rec = q / 18, off = q - rec * 18;
+            const float4 v = __ldg((const float4*)(J + (size_t)s_r[wid][rec] * JF) + off);
+            *(float4*)(my + rec * ROW + 4 * off) = v;
+        }
+        __syncwarp();
+        if (lane < nb) {
+            float j[JF];
+#pragma unroll
+            for (int i = 0; i < JF / 4; i++) { float4 v = *(const float4*)(my + lane * ROW + 4 * i); j[4 * i] = v.x; j[4 * i + 1] = v.y; j[4 * i + 2] = v.z; j[4 * i + 3] = v.w; }
+            if (PRODUCTS) products(j, acc);
+            else { float s = 0; for (int i = 0; i < JF; i++) s += j[i]; acc[0] += s; }
+        }
+    }
+    if (PRODUCTS) cta_reduce_and_add(acc, key, out);
+    else if (acc[0] == 123.456f) out[0] = acc[0];
+}
+
+// E: D with the copy done by cp.async (16-byte LDGSTS straight into shared memory) and two tiles per warp, so the next
+// 32 records are in flight while the current ones are multiplied
+#include <cuda_pipeline.h>
+__global__ void __launch_bounds__(T) kE(const int* chunk, const int* order, const float* J, double* out) {
+    extern __shared__ __align__(16) float dyn[];                 // [T/32][2][32*ROW] floats + [T/32][2][32] ints
+    const int key = chunk[3 * blockIdx.x], start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float* tiles = dyn + (size_t)wid * 2 * 32 * ROW;
+    int* s_r = (int*)(dyn + (size_t)(T / 32) * 2 * 32 * ROW) + wid * 64;
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0;
+    auto issue = [&](int base, int buf) {
+        const int nb = min(32, count - base);
+        s_r[buf * 32 + lane] = lane < nb ? order[start + base + lane] : 0;
+        __syncwarp();
+        float* my = tiles + buf * 32 * ROW;
+        for (int q = lane; q < nb * 18; q += 32) {
+            const int rec = q / 18, off = q - rec * 18;
+            __pipeline_memcpy_async(my + rec * ROW + 4 * off, (const float4*)(J + (size_t)s_r[buf * 32 + rec] * JF) + off, 16);
+        }
+        __pipeline_commit();
+    };
+    int buf = 0;
+    int base = wid * 32;
+    if (base < count) issue(base, 0);
+    for (; base < count; base += T) {
+        const int next = base + T;
+        if (next < count) issue(next, buf ^ 1);
+        if (next < count) __pipeline_wait_prior(1); else __pipeline_wait_prior(0);
+        __syncwarp();
+        const int nb = min(32, count - base);
+        if (lane < nb) {
+            const float* my = tiles + buf * 32 * ROW;
+            float j[JF];
+#pragma unroll
+            for (int i = 0; i < JF / 4; i++) { float4 v = *(const float4*)(my + lane * ROW + 4 * i); j[4 * i] = v.x; j[4 * i + 1] = v.y; j[4 * i + 2] = v.z; j[4 * i + 3] = v.w; }
+            products(j, acc);
+        }
+        __syncwarp();
+        buf ^= 1;
+    }
+    cta_reduce_and_add(acc, key, out);
+}
+
+// F: persistent, warp-autonomous version of E.  The sorted gather list is padded (entries -1) so that every tile of 32
+// entries has ONE key; a warp owns a contiguous run of tiles, keeps two tiles in flight with cp.async, prefetches the
+// indices of the tile after next, and flushes its 91 sums (warp shuffles + fp64 atomics) only when the key changes.
+__global__ void __launch_bounds__(T) kF(int ntiles, int tiles_per_warp, const int* __restrict__ tile_key, const int* __restrict__ order,
+                                        const float* __restrict__ J, double* out) {
+    extern __shared__ __align__(16) float dyn[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int gw = blockIdx.x * (T / 32) + wid;
+    float* tiles = dyn + (size_t)wid * 2 * 32 * ROW;
+    int* s_r = (int*)(dyn + (size_t)(T / 32) * 2 * 32 * ROW) + wid * 64;
+    const int t0 = gw * tiles_per_warp, t1 = min(ntiles, t0 + tiles_per_warp);
+    if (t0 >= t1) return;
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0;
+    auto flush = [&](int key) {
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            float v = acc[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v != 0.f) atomicAdd(out + (size_t)key * STRIDE + i, (double)v);
+            acc[i] = 0;
+        }
+    };
+    auto issue = [&](int r, int buf) {                 // r: this lane's record of the tile (-1: padding)
+        s_r[buf * 32 + lane] = r;
+        __syncwarp();
+        float* my = tiles + buf * 32 * ROW;
+#pragma unroll 6
+        for (int q = lane; q < 32 * 18; q += 32) {
+            const int rec = q / 18, off = q - rec * 18;
+            const int rr = s_r[buf * 32 + rec];
+            if (rr >= 0) __pipeline_memcpy_async(my + rec * ROW + 4 * off, (const float4*)(J + (size_t)rr * JF) + off, 16);
+        }
+        __pipeline_commit();
+    };
+    int r_cur = order[t0 * 32 + lane];
+    int r_next = t0 + 1 < t1 ? order[(t0 + 1) * 32 + lane] : -1;
+    issue(r_cur, 0);
+    int key = tile_key[t0];
+    int buf = 0;
+    for (int t = t0; t < t1; t++) {
+        const int r_next2 = t + 2 < t1 ? order[(t + 2) * 32 + lane] : -1;     // in flight while this tile is multiplied
+        if (t + 1 < t1) { issue(r_next, buf ^ 1); __pipeline_wait_prior(1); } else __pipeline_wait_prior(0);
+        __syncwarp();
+        const int k = tile_key[t];
+        if (k != key) { flush(key); key = k; }
+        if (r_cur >= 0) {
+            const float* my = tiles + buf * 32 * ROW;
+            float j[JF];
+#pragma unroll
+            for (int i = 0; i < JF / 4; i++) { float4 v = *(const float4*)(my + lane * ROW + 4 * i); j[4 * i] = v.x; j[4 * i + 1] = v.y; j[4 * i + 2] = v.z; j[4 * i + 3] = v.w; }
+            products(j, acc);
+        }
+        __syncwarp();
+        r_cur = r_next; r_next = r_next2;
+        buf ^= 1;
+    }
+    flush(key);
+}
+
+// G: F with the tile fetched by the copy engine: each lane issues ONE cp.async.bulk of its 288-byte record into the warp's
+// stage buffer, completion on an mbarrier per (warp, stage); no address arithmetic per 16 bytes, nothing through LSU.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile("{\n.reg .pred p;\nWAIT:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE;\nbra WAIT;\nDONE:\n}" ::"r"(bar), "r"(parity) : "memory");
+}
+template <int WPC, int STAGES>
+__global__ void __launch_bounds__(32 * WPC) kG(int ntiles, int tiles_per_warp, const int* __restrict__ tile_key, const int* __restrict__ order,
+                                              const float* __restrict__ J, double* out) {
+    extern __shared__ __align__(128) float dyn[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int gw = blockIdx.x * WPC + wid;
+    float* tiles = dyn + (size_t)wid * STAGES * 32 * ROW;
+    unsigned long long* bars = (unsigned long long*)(dyn + (size_t)WPC * STAGES * 32 * ROW) + wid * STAGES;
+    const int t0 = gw * tiles_per_warp, t1 = min(ntiles, t0 + tiles_per_warp);
+    if (t0 >= t1) return;
+    if (lane == 0)
+        for (int i = 0; i < STAGES; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bars + i)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncwarp();
+    float acc[NV];
+#pragma unroll
+    for (int i = 0; i < NV; i++) acc[i] = 0;
+    auto flush = [&](int key) {
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            float v = acc[i];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v != 0.f) atomicAdd(out + (size_t)key * STRIDE + i, (double)v);
+            acc[i] = 0;
+        }
+    };
+    auto issue = [&](int r, int st) {
+        const unsigned bar = smem_u32(bars + st);
+        const unsigned m = __ballot_sync(0xffffffffu, r >= 0);
+        if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(288u * __popc(m)) : "memory");
+        __syncwarp();
+        if (r >= 0)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 288, [%2];" ::"r"(
+                             smem_u32(tiles + (st * 32 + lane) * ROW)),
+                         "l"(J + (size_t)r * JF), "r"(bar)
+                         : "memory");
+    };
+    // prologue: STAGES-1 tiles in flight
+    int rq[STAGES];                                     // indices of tiles t .. t+STAGES-1 (this lane's record)
+#pragma unroll
+    for (int i = 0; i < STAGES; i++) rq[i] = t0 + i < t1 ? order[(t0 + i) * 32 + lane] : -1;
+#pragma unroll
+    for (int i = 0; i < STAGES - 1; i++)
+        if (t0 + i < t1) issue(rq[i], i);
+    int key = tile_key[t0];
+    int st = 0;
+    unsigned phase = 0;
+    for (int t = t0; t < t1; t++) {
+        const int r_far = t + STAGES < t1 ? order[(t + STAGES) * 32 + lane] : -1;
+        int st_n = st + STAGES - 1; if (st_n >= STAGES) st_n -= STAGES;
+        if (t + STAGES - 1 < t1) issue(rq[STAGES - 1], st_n);
+        mbar_wait(smem_u32(bars + st), phase);
+        const int k = tile_key[t];
+        if (k != key) { flush(key); key = k; }
+        if (rq[0] >= 0) {
+            const float* my = tiles + (st * 32 + lane) * ROW;
+            float j[JF];
+#pragma unroll
+            for (int i = 0; i < JF / 4; i++) { float4 v = *(const float4*)(my + 4 * i); j[4 * i] = v.x; j[4 * i + 1] = v.y; j[4 * i + 2] = v.z; j[4 * i + 3] = v.w; }
+            products(j, acc);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < STAGES - 1; i++) rq[i] = rq[i + 1];
+        rq[STAGES - 1] = r_far;
+        if (++st == STAGES) { st = 0; phase ^= 1; }
+    }
+    flush(key);
+}
+
+template <int WPC, int STAGES>
+void runG(int ctas_per_sm, int ntiles, const int* dTk, const int* dPo, const float* dJ, double* dOut, void* flushbuf, size_t outn,
+          const std::vector<double>& ref, int R) {
+    const size_t smem = (size_t)WPC * STAGES * 32 * ROW * 4 + WPC * STAGES * 8;
+    CK(cudaFuncSetAttribute(kG<WPC, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kG<WPC, STAGES>, 32 * WPC, smem));
+    const int ctas = 148 * (ctas_per_sm ? ctas_per_sm : occ);
+    const int warps = ctas * WPC, tpw = (ntiles + warps - 1) / warps;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e9f;
+    for (int rep = 0; rep < 5; rep++) {
+        CK(cudaMemset(dOut, 0, outn * 8));
+        CK(cudaMemset(flushbuf, rep, 256 << 20));
+        CK(cudaDeviceSynchronize());
+        cudaEventRecord(e0);
+        kG<WPC, STAGES><<<ctas, 32 * WPC, smem>>>(ntiles, tpw, dTk, dPo, dJ, dOut);
+        cudaEventRecord(e1);
+        CK(cudaDeviceSynchronize());
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0) best = std::min(best, ms);
+    }
+    std::vector<double> o(outn);
+    CK(cudaMemcpy(o.data(), dOut, outn * 8, cudaMemcpyDeviceToHost));
+    double err = 0, nrm = 0;
+    for (size_t i = 0; i < o.size(); i++) { err += (o[i] - ref[i]) * (o[i] - ref[i]); nrm += ref[i] * ref[i]; }
+    printf("G bulk-copy warp pipeline  warps/CTA %d stages %d occ %d  tiles/warp %3d  CTAs %5d  %8.1f us  %7.1f GB/s (288 B/rec)  relerr %.2e\n", WPC,
+           STAGES, occ, tpw, ctas, best * 1e3, (double)R * 288 / (best * 1e-3) / 1e9, sqrt(err / nrm));
+}
+
+int main(int argc, char** argv) {
+    const int B = argc > 1 ? atoi(argv[1]) : 64;
+    const int n = 7, np = 2002 * B, rpp = 6, R = np * rpp;
+    std::vector<float> J((size_t)R * JF);
+    for (size_t i = 0; i < J.size(); i++) J[i] = (float)((i * 2654435761u) % 1000) * 1e-3f - 0.5f;
+    std::vector<int> key(R);
+    for (int p = 0; p < np; p++) {
+        const int h = (int)((long long)p * n / np);
+        int k = 0;
+        for (int t = 0; t < n; t++) { if (t == h) continue; key[p * rpp + k] = h + n * t + (((p * 7 + t) % 4 == 0 && t != n - 1) ? n * n : 0); k++; }
+    }
+    std::vector<int> order(R);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return key[a] < key[b]; });
+    auto chunks = [&](int clen) {
+        std::vector<int> c;
+        int s = 0;
+        while (s < R) {
+            int e = s;
+            while (e < R && key[order[e]] == key[order[s]] && e - s < clen) e++;
+            c.push_back(key[order[s]]); c.push_back(s); c.push_back(e - s);
+            s = e;
+        }
+        return c;
+    };
+    float* dJ; int *dOrder, *dChunk; double* dOut; char* flush;
+    CK(cudaMalloc(&dJ, J.size() * 4)); CK(cudaMalloc(&dOrder, R * 4)); CK(cudaMalloc(&dChunk, 3 * (R / 64 + 256) * 4));
+    CK(cudaMalloc(&dOut, 2 * n * n * STRIDE * 8)); CK(cudaMalloc(&flush, 256 << 20));
+    CK(cudaMemcpy(dJ, J.data(), J.size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dOrder, order.data(), R * 4, cudaMemcpyHostToDevice));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const size_t smemE = (size_t)(T / 32) * 2 * 32 * ROW * 4 + (T / 32) * 64 * 4;
+    CK(cudaFuncSetAttribute(kE, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemE));
+    std::vector<double> ref;
+    auto run = [&](const char* name, int clen, int which) {
+        std::vector<int> c = chunks(clen);
+        const int nc = (int)c.size() / 3;
+        CK(cudaMemcpy(dChunk, c.data(), c.size() * 4, cudaMemcpyHostToDevice));
+        float best = 1e9f;
+        for (int rep = 0; rep < 5; rep++) {
+            CK(cudaMemset(dOut, 0, 2 * n * n * STRIDE * 8));
+            CK(cudaMemset(flush, rep, 256 << 20));
+            CK(cudaDeviceSynchronize());
+            cudaEventRecord(e0);
+            switch (which) {
+                case 0: kA<<<nc, T>>>(dChunk, dOrder, dJ, dOut); break;
+                case 1: kB<<<nc, T>>>(dChunk, dOrder, dJ, dOut); break;
+                case 2: kD<true><<<nc, T>>>(dChunk, dOrder, dJ, dOut); break;
+                case 3: kD<false><<<nc, T>>>(dChunk, dOrder, dJ, dOut); break;
+                case 4: kE<<<nc, T, smemE>>>(dChunk, dOrder, dJ, dOut); break;
+            }
+            cudaEventRecord(e1);
+            CK(cudaDeviceSynchronize());
+            float ms; cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0) best = std::min(best, ms);
+        }
+        std::vector<double> o(2 * n * n * STRIDE);
+        CK(cudaMemcpy(o.data(), dOut, o.size() * 8, cudaMemcpyDeviceToHost));
+        double err = 0, nrm = 0;
+        if (which == 0 && ref.empty()) ref = o;
+        if (!ref.empty() && (which == 0 || which == 2 || which == 4))
+            for (size_t i = 0; i < o.size(); i++) { err += (o[i] - ref[i]) * (o[i] - ref[i]); nrm += ref[i] * ref[i]; }
+        printf("%-34s chunk %5d  CTAs %6d  %8.1f us  %7.1f GB/s (288 B/rec)  relerr %.2e\n", name, clen, nc, best * 1e3,
+               (double)R * 288 / (best * 1e-3) / 1e9, nrm > 0 ? sqrt(err / nrm) : 0.0);
+    };
+    printf("records %d (%d points), %.1f MB\n", R, np, (double)R * 288 / 1e6);
+    run("A thread-per-record", 128, 0);
+    run("A thread-per-record, loop", 640, 0);
+    run("B loads only (A pattern)", 128, 1);
+    run("B loads only (A pattern), loop", 640, 1);
+    run("D warp smem tile, loads only", 640, 3);
+    run("D warp smem tile", 128, 2);
+    run("D warp smem tile, loop", 640, 2);
+    run("D warp smem tile, loop", 1024, 2);
+    run("E cp.async double buffer", 640, 4);
+    run("E cp.async double buffer", 1024, 4);
+    run("E cp.async double buffer", 2048, 4);
+    {
+        std::vector<int> po, tk;
+        int s0 = 0;
+        while (s0 < R) {
+            int e = s0;
+            while (e < R && key[order[e]] == key[order[s0]]) e++;
+            for (int i = s0; i < e; i++) po.push_back(order[i]);
+            while (po.size() % 32) po.push_back(-1);
+            while (tk.size() < po.size() / 32) tk.push_back(key[order[s0]]);
+            s0 = e;
+        }
+        const int ntiles = (int)tk.size();
+        int *dPo, *dTk;
+        CK(cudaMalloc(&dPo, po.size() * 4)); CK(cudaMalloc(&dTk, tk.size() * 4));
+        CK(cudaMemcpy(dPo, po.data(), po.size() * 4, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dTk, tk.data(), tk.size() * 4, cudaMemcpyHostToDevice));
+        CK(cudaFuncSetAttribute(kF, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemE));
+        for (int ctas : {148, 296, 444, 592}) {
+            const int warps = ctas * (T / 32), tpw = (ntiles + warps - 1) / warps;
+            float best = 1e9f;
+            for (int rep = 0; rep < 5; rep++) {
+                CK(cudaMemset(dOut, 0, 2 * n * n * STRIDE * 8));
+                CK(cudaMemset(flush, rep, 256 << 20));
+                CK(cudaDeviceSynchronize());
+                cudaEventRecord(e0);
+                kF<<<ctas, T, smemE>>>(ntiles, tpw, dTk, dPo, dJ, dOut);
+                cudaEventRecord(e1);
+                CK(cudaDeviceSynchronize());
+                float ms; cudaEventElapsedTime(&ms, e0, e1);
+                if (rep > 0) best = std::min(best, ms);
+            }
+            std::vector<double> o(2 * n * n * STRIDE);
+            CK(cudaMemcpy(o.data(), dOut, o.size() * 8, cudaMemcpyDeviceToHost));
+            double err = 0, nrm = 0;
+            for (size_t i = 0; i < o.size(); i++) { err += (o[i] - ref[i]) * (o[i] - ref[i]); nrm += ref[i] * ref[i]; }
+            printf("%-34s tiles/warp %3d  CTAs %6d  %8.1f us  %7.1f GB/s (288 B/rec)  relerr %.2e\n", "F persistent warp pipeline", tpw, ctas, best * 1e3,
+                   (double)R * 288 / (best * 1e-3) / 1e9, sqrt(err / nrm));
+        }
+        const size_t outn = (size_t)2 * n * n * STRIDE;
+        runG<4, 2>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+        runG<2, 2>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+        runG<2, 3>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+        runG<1, 3>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+        runG<1, 4>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+        runG<4, 3>(0, ntiles, dTk, dPo, dJ, dOut, flush, outn, ref, R);
+    }
+    return 0;
+}
