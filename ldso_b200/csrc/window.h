@@ -39,6 +39,7 @@ struct WindowDev {
     int* order = nullptr;          // residual ids sorted by accumulator key (mode * n^2 + host + n * target)
     int* chunk = nullptr;          // [n_chunks][3] = key, start, count
     int n_chunks = 0;
+    int chunk_len = 128;           // longest chunk in the list: 128 (thread per residual) or up to 1024 (k8_top_stream_kernel)
     int* sc_blocks = nullptr;      // [n_sc_blocks][3] = host, first point, end point (K9 CTA table)
     int n_sc_blocks = 0;
     unsigned char* pmask = nullptr;   // [cap_p] point mask of marginalizePointsF

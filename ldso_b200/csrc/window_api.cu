@@ -146,7 +146,16 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     return upload(c, W.sc_blocks, blk.data(), sizeof(int) * blk.size());
 }
 
-// (re)build the K8 work list: residual ids sorted by key = mode * n^2 + host + n * target, cut into <=128 chunks
+static int sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+// (re)build the K8 work list: residual ids sorted by key = mode * n^2 + host + n * target, cut into chunks of <= 128 (one window) to <= 1024 (batched) ids
 // With `only` (a point mask) the list holds just those points' residuals, all under the mode-0 keys (addPoint<2>).
 static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
     WindowDev& W = c->win;
@@ -160,9 +169,15 @@ static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
     for (int k = 0; k < 2 * nn; k++) cnt[k + 1] += cnt[k];
     std::vector<int> order(std::max(nr, 1)), pos(cnt.begin(), cnt.end() - 1), chunk;
     for (int r = 0; r < nr; r++) if (key[r] >= 0) order[pos[key[r]]++] = r;
+    // chunk length: 128 while that already fills the machine (one window: ~100 chunks), else grown in steps of 128 so that
+    // the list stays several waves deep (batched windows; k8_top_stream_kernel pipelines tiles inside a chunk), capped at 1024
+    const int total = cnt[2 * nn];
+    int clen = 128;
+    if (total > 128 * 4 * sm_count()) clen = std::min(1024, std::max(128, total / (4 * sm_count()) / 128 * 128));
+    W.chunk_len = clen;
     for (int k = 0; k < 2 * nn; k++)
-        for (int s = cnt[k]; s < cnt[k + 1]; s += 128) {
-            chunk.push_back(k); chunk.push_back(s); chunk.push_back(std::min(128, cnt[k + 1] - s));
+        for (int s = cnt[k]; s < cnt[k + 1]; s += clen) {
+            chunk.push_back(k); chunk.push_back(s); chunk.push_back(std::min(clen, cnt[k + 1] - s));
         }
     W.n_chunks = (int)chunk.size() / 3;
     int rc = upload(c, W.order, order.data(), sizeof(int) * cnt[2 * nn]);

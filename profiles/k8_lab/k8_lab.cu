@@ -372,6 +372,22 @@ void runG(int ctas_per_sm, int ntiles, const int* dTk, const int* dPo, const flo
            STAGES, occ, tpw, ctas, best * 1e3, (double)R * 288 / (best * 1e-3) / 1e9, sqrt(err / nrm));
 }
 
+// S: plain streaming read of the record buffer (coalesced float4, 8 loads in flight per thread): what HBM gives a read-only kernel
+__global__ void __launch_bounds__(256) kS(const float4* __restrict__ J, size_t n4, float* out) {
+    float s = 0;
+    const size_t stride = (size_t)gridDim.x * 256;
+    size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 7 * stride < n4; i += 8 * stride) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = __ldg(J + i + k * stride);
+#pragma unroll
+        for (int k = 0; k < 8; k++) s += v[k].x + v[k].y + v[k].z + v[k].w;
+    }
+    for (; i < n4; i += stride) { float4 v = __ldg(J + i); s += v.x + v.y + v.z + v.w; }
+    if (s == 123.456f) out[0] = s;
+}
+
 int main(int argc, char** argv) {
     const int B = argc > 1 ? atoi(argv[1]) : 64;
     const int n = 7, np = 2002 * B, rpp = 6, R = np * rpp;
@@ -382,6 +398,10 @@ int main(int argc, char** argv) {
         const int h = (int)((long long)p * n / np);
         int k = 0;
         for (int t = 0; t < n; t++) { if (t == h) continue; key[p * rpp + k] = h + n * t + (((p * 7 + t) % 4 == 0 && t != n - 1) ? n * n : 0); k++; }
+    }
+    if (argc > 2 && argv[2][0] == 's') {                 // records already in key order: the gather becomes a stream
+        for (int r = 0; r < R; r++) key[r] = (int)((long long)r * 84 / R);
+        printf("SEQUENTIAL order\n");
     }
     std::vector<int> order(R);
     std::iota(order.begin(), order.end(), 0);
@@ -406,6 +426,20 @@ int main(int argc, char** argv) {
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     const size_t smemE = (size_t)(T / 32) * 2 * 32 * ROW * 4 + (T / 32) * 64 * 4;
     CK(cudaFuncSetAttribute(kE, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemE));
+    for (int ctas : {148 * 4, 148 * 8, 148 * 16, 148 * 32}) {
+        float best = 1e9f;
+        for (int rep = 0; rep < 5; rep++) {
+            CK(cudaMemset(flush, rep, 256 << 20));
+            CK(cudaDeviceSynchronize());
+            cudaEventRecord(e0);
+            kS<<<ctas, 256>>>((const float4*)dJ, J.size() / 4, (float*)dOut);
+            cudaEventRecord(e1);
+            CK(cudaDeviceSynchronize());
+            float ms; cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0) best = std::min(best, ms);
+        }
+        printf("S streaming read                   CTAs %6d  %8.1f us  %7.1f GB/s\n", ctas, best * 1e3, (double)J.size() * 4 / (best * 1e-3) / 1e9);
+    }
     std::vector<double> ref;
     auto run = [&](const char* name, int clen, int which) {
         std::vector<int> c = chunks(clen);

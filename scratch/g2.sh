@@ -1,0 +1,6 @@
+set -x
+timeout 600 python profiles/kernel_bench.py --json gpurun_out/kb_r1k.json > gpurun_out/kb_r1k.log 2>&1; tail -15 gpurun_out/kb_r1k.log
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches_r1k.csv python bench.py --steps 30 --warmup 30 --cpu-steps 5 > gpurun_out/ncu_launch.log 2>&1; tail -2 gpurun_out/ncu_launch.log | cut -c1-300
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k7_linearize|k8_top|k9_sc_kernel|k9_point|k10_resub" -c 5 -o gpurun_out/prof_r1k_window64 python profiles/kernel_bench.py --batches 64 --reps 1 > gpurun_out/ncu_kb.log 2>&1; tail -3 gpurun_out/ncu_kb.log
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k34_track_level|k1_pyramid|k5_trace" -s 150 -c 6 -o gpurun_out/prof_r1k_frame python bench.py --steps 6 --warmup 30 --cpu-steps 5 > gpurun_out/ncu_fr.log 2>&1; tail -3 gpurun_out/ncu_fr.log | cut -c1-300
+ls -la gpurun_out
