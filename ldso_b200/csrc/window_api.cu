@@ -4,6 +4,8 @@
 // AccumulatedSCHessian.cc:53-119) and the dense part of EnergyFunctional::solveSystemF (:310-432).
 #include "ctx.h"
 
+#include <cstdlib>
+
 #include <algorithm>
 #include <cmath>
 
@@ -174,6 +176,7 @@ static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
     const int total = cnt[2 * nn];
     int clen = 128;
     if (total > 128 * 4 * sm_count()) clen = std::min(1024, std::max(128, total / (4 * sm_count()) / 128 * 128));
+    if (const char* e = getenv("LDSO_K8_CHUNK")) clen = atoi(e);           // tuning knob of profiles/kernel_bench.py
     W.chunk_len = clen;
     for (int k = 0; k < 2 * nn; k++)
         for (int s = cnt[k]; s < cnt[k + 1]; s += clen) {
