@@ -32,7 +32,7 @@ constexpr int NV = 91;
 constexpr int K8_ROW = 84;                                              // tile row stride (floats): 72 J + 8 res_toZeroF + 4 pad, conflict-free LDS.128
 constexpr int K8_TILE_FLOATS = 32 * K8_ROW;
 static_assert(NV * (K8_THREADS + 1) <= (K8_THREADS / 32) * 2 * K8_TILE_FLOATS, "fold scratch fits in the tile buffers");
-constexpr size_t K8_STREAM_SMEM = (size_t)(K8_THREADS / 32) * 2 * K8_TILE_FLOATS * 4 + (K8_THREADS / 32) * 64 * 4;
+constexpr size_t K8_STREAM_SMEM = (size_t)(K8_THREADS / 32) * 2 * K8_TILE_FLOATS * 4;
 
 struct K8Args {
     int n, marg;
@@ -193,36 +193,38 @@ k8_top_kernel(K8Args A, const int* __restrict__ chunk, const int* __restrict__ o
 // multiplied.  No global load sits on the critical path of the multiply.
 __global__ void __launch_bounds__(K8_THREADS)
 k8_top_stream_kernel(K8Args A, const int* __restrict__ chunk, const int* __restrict__ order) {
-    extern __shared__ __align__(16) float dyn[];           // [4 warps][2][32 x K8_ROW] floats, then [4][2][32] record ids
+    extern __shared__ __align__(16) float dyn[];           // [4 warps][2][32 x K8_ROW] floats
     const int key = chunk[3 * blockIdx.x], start = chunk[3 * blockIdx.x + 1], count = chunk[3 * blockIdx.x + 2];
     const int nn = A.n * A.n;
     const int mode = A.marg ? 2 : key >= nn ? 1 : 0;
     const float* dp = A.adHTdelta + 8 * (key >= nn ? key - nn : key);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float* tiles = dyn + (size_t)wid * 2 * K8_TILE_FLOATS;
-    int* s_r = reinterpret_cast<int*>(dyn + (size_t)(K8_THREADS / 32) * 2 * K8_TILE_FLOATS) + wid * 64;
-    const int pieces = mode ? 20 : 18;                     // 16-byte pieces per record: 18 of J, 2 of res_toZeroF
     float acc[NV];
 #pragma unroll
     for (int i = 0; i < NV; i++) acc[i] = 0.f;
     int used = 0;
     auto load_id = [&](int base) -> int { return base + lane < count ? __ldg(order + start + base + lane) : -1; };
-    // start the copy of a tile whose record ids (one per lane, -1 past the end) are r
+    // start the copy of a tile whose record ids (one per lane, -1 past the end) are r.  Half a warp copies the first
+    // 256 B of a record per instruction (16 lanes x 16 B, two records per instruction), two lanes per record copy the
+    // last 32 B (and the 32 B of res_toZeroF): every address is a lane constant plus an unrolled immediate, the record
+    // id comes by shuffle — three instructions per 16-byte piece.
+    const int hi = lane >> 4, lo = lane & 15, h2 = lane >> 1, l2 = lane & 1;
     auto issue = [&](int r, int buf) {
-        s_r[buf * 32 + lane] = r;
-        __syncwarp();
+        const int rc = max(r, 0);                          // past-the-end lanes re-copy record 0 (never read)
         float* my = tiles + buf * K8_TILE_FLOATS;
-        int rec = 0, off = lane;                           // piece q = lane + 32 i of the tile: record q / pieces, piece q % pieces
-        if (off >= pieces) { off -= pieces; rec = 1; }
-        const int step = 32 - pieces;
-        for (int i = 0; i < pieces; i++) {
-            const int rr = s_r[buf * 32 + rec];
-            if (rr >= 0) {
-                const float* src = off < 18 ? A.J + (size_t)rr * LDSO_J_FLOATS + 4 * off : A.rtz + 8 * (size_t)rr + 4 * (off - 18);
-                __pipeline_memcpy_async(my + rec * K8_ROW + 4 * off, src, 16);
-            }
-            rec += 1; off += step;                         // + 32 pieces = + 1 record + (32 - pieces) pieces
-            if (off >= pieces) { off -= pieces; rec += 1; }
+        float* dst = my + hi * K8_ROW + 4 * lo;
+        const float* src = A.J + 4 * lo;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int rr = __shfl_sync(0xffffffffu, rc, 2 * i + hi);
+            __pipeline_memcpy_async(dst + 2 * i * K8_ROW, src + (size_t)rr * LDSO_J_FLOATS, 16);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            const int rr = __shfl_sync(0xffffffffu, rc, 16 * i + h2);
+            __pipeline_memcpy_async(my + (16 * i + h2) * K8_ROW + 64 + 4 * l2, A.J + (size_t)rr * LDSO_J_FLOATS + 64 + 4 * l2, 16);
+            if (mode) __pipeline_memcpy_async(my + (16 * i + h2) * K8_ROW + 72 + 4 * l2, A.rtz + 8 * (size_t)rr + 4 * l2, 16);
         }
         __pipeline_commit();
     };
