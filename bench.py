@@ -434,6 +434,7 @@ def main():
                     help="odometry: closed loop through the reference's per-frame flow (default); cadence: fixed keyframe every "
                          "6 frames on harness-built windows (heavier mapping load)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-window-roofline", action="store_true", help="skip the live 64x batched-window kernel timing (roofline_batched_window)")
     ap.add_argument("--cpu-steps", type=int, default=None, help="frames of the bounded cpu_baseline sample (default 90 / 18)")
     args = ap.parse_args()
     rank, local_rank, world = rank_info()
@@ -551,6 +552,18 @@ def main():
                 kernels=kernels,
                 host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
                 gt_error_m=gt_err, keyframes=kf_tail)
+    if args.gpus == 1 and not args.no_window_roofline:
+        # the accumulation kernels at a size where bandwidth, not launch latency, bounds them (hard part 1):
+        # the frozen configs[1] window replicated x64 (the residual population of 64 sequences, configs[4]) through
+        # K7/K8/K9/K10 as one launch each, CUDA-event timed after an L2 flush — measured live, outside the timed region
+        sys.path.insert(0, os.path.join(ROOT, "profiles"))
+        import kernel_bench
+        rows = kernel_bench.measure(gpu, [64], 3, peak)
+        line["roofline_batched_window"] = {
+            "workload": "64 x the configs[1] window (%d residuals, %d points) in one launch per kernel" % (rows[0]["residuals"], rows[0]["points"]),
+            "peak": peak, "unit": "GB/s",
+            "kernels": {r["kernel"]: {"avg_us": r["avg_us"], "bytes_per_unit": r["bytes_per_unit"], "units_per_launch": r["units_per_launch"],
+                                      "achieved": r["achieved_gbs"], "frac": r["frac"]} for r in rows}}
     if odo:
         line["trajectory"] = traj
         line["keyframes_in_timed_region"] = sum(1 for k in seq_e2e.kf_log if k["frame"] >= seq_e2e.first_step + warmup)

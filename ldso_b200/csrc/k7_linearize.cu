@@ -5,8 +5,8 @@
 //
 // Eight lanes cooperate on one residual, one per pixel of the 8-pixel pattern: each lane projects its
 // pattern pixel, fetches 4 float4 texels of the target frame's level 0 and forms its row of the
-// Jacobian.  The 2x2 inner-product blocks and the energy are summed in pattern order 0..7 by an
-// all-gather over the eight lanes, so every stored value is bit-identical to a sequential strict-IEEE
+// Jacobian.  The 2x2 inner-product blocks and the energy are summed in pattern order 0..7 (products transposed
+// through shared memory, one lane per sum), so every stored value is bit-identical to a sequential strict-IEEE
 // evaluation of the reference loop (the OUTLIER test `energy > frameEnergyTH` cannot flip on summation
 // order).  Output is one 288-byte RawResidualJacobian record per residual, written as full 32-byte sectors.
 #include "ctx.h"
@@ -28,13 +28,7 @@ struct K7Params {
     double* stats;
 };
 
-__device__ __forceinline__ float seq8(float v, int base) {
-    // sum over the 8 lanes of the group in lane order — the reference's `+=` over idx = 0..7
-    float s = 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; j++) s += __shfl_sync(0xffffffffu, v, base + j);
-    return s;
-}
+constexpr int K7_GROUP_STRIDE = 8 * 12 + 8;   // floats per residual in the transpose buffer: 4 groups of a warp land on disjoint banks
 
 __global__ void __launch_bounds__(K7_THREADS) k7_linearize_kernel(const K7Params p) {
     const int gid = blockIdx.x * K7_THREADS + threadIdx.x;
@@ -122,15 +116,38 @@ __global__ void __launch_bounds__(K7_THREADS) k7_linearize_kernel(const K7Params
     }
     const unsigned bal = __ballot_sync(0xffffffffu, lane_oob);
     if ((bal >> base) & 0xffu) oob = true;
-    // ordered sums over the pattern (all lanes take part in the shuffles)
-    const float s00 = seq8(h1 * h1, base), s11 = seq8(h2 * h2, base), s10 = seq8(h1 * h2, base);
-    const float a00 = seq8(ja0 * h1, base), a01 = seq8(ja0 * h2, base), a10 = seq8(ja1 * h1, base), a11 = seq8(ja1 * h2, base);
-    // drdA*drdA*hw*hw == ((drdA*drdA)*hw)*hw; recover drdA from ja0 only where hw != 0 — keep the exact product instead:
+    // ordered sums over the pattern: the 8 lanes of a residual hold 12 products each; they are transposed through shared
+    // memory so that lane q sums product q (lanes 0..3 also product 8 + q) over the pattern in lane order — the
+    // reference's `+=` over idx = 0..7 — and the 12 sums go back to every lane the same way.  ~40 instructions instead of
+    // the 96 shuffles + 96 adds of an all-gather per sum.
     float drdA_l = 0.f;
-    if (!oob && !lane_oob) drdA_l = p.color[8 * pt + k] - pc[26];
-    const float b00 = seq8(drdA_l * drdA_l * ja1 * ja1, base), b01 = seq8(ja0 * ja1, base), b11 = seq8(ja1 * ja1, base);
-    const float wJI2 = seq8(ja1 * ja1 * (h1 * h1 + h2 * h2), base);
-    float energyLeft = seq8(e_k, base);
+    if (!oob && !lane_oob) drdA_l = p.color[8 * pt + k] - pc[26];   // drdA*drdA*hw*hw: the exact product, not recovered from ja0
+    __shared__ __align__(16) float s_prod[K7_THREADS / 8][K7_GROUP_STRIDE];
+    __shared__ __align__(16) float s_sum[K7_THREADS / 8][12];
+    {
+        float* mine = s_prod[threadIdx.x >> 3] + 12 * k;
+        reinterpret_cast<float4*>(mine)[0] = make_float4(h1 * h1, h2 * h2, h1 * h2, ja0 * h1);
+        reinterpret_cast<float4*>(mine)[1] = make_float4(ja0 * h2, ja1 * h1, ja1 * h2, drdA_l * drdA_l * ja1 * ja1);
+        reinterpret_cast<float4*>(mine)[2] = make_float4(ja0 * ja1, ja1 * ja1, ja1 * ja1 * (h1 * h1 + h2 * h2), e_k);
+        __syncwarp();
+        const float* col = s_prod[threadIdx.x >> 3] + k;
+        float sa = 0.f, sb = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++) sa += col[12 * j];
+        if (k < 4) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) sb += col[12 * j + 8];
+        }
+        s_sum[threadIdx.x >> 3][k] = sa;
+        if (k < 4) s_sum[threadIdx.x >> 3][8 + k] = sb;
+        __syncwarp();
+    }
+    const float4 q0 = reinterpret_cast<const float4*>(s_sum[threadIdx.x >> 3])[0];
+    const float4 q1 = reinterpret_cast<const float4*>(s_sum[threadIdx.x >> 3])[1];
+    const float4 q2 = reinterpret_cast<const float4*>(s_sum[threadIdx.x >> 3])[2];
+    const float s00 = q0.x, s11 = q0.y, s10 = q0.z, a00 = q0.w, a01 = q1.x, a10 = q1.y, a11 = q1.z, b00 = q1.w;
+    const float b01 = q2.x, b11 = q2.y, wJI2 = q2.z;
+    float energyLeft = q2.w;
 
     double ret_energy = 0.0;
     int isIN = 0;

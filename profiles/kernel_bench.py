@@ -44,24 +44,13 @@ def replicate(W, B):
     return out
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--batches", default="1,8,64")
-    ap.add_argument("--reps", type=int, default=5)
-    ap.add_argument("--json", default=None)
-    args = ap.parse_args()
+def measure(gpu, batches, reps, peak):
+    """rows of {batch, kernel, avg_us, achieved_gbs, frac, ...}: CUDA-event times of K7/K8/K9/K10 on B-fold windows"""
     import torch
-    gpu = capi.load()
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = peaks.get("hbm_gbs", 6650.0)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     W0 = synth.make_window(pts_per_frame=286, **CALIB)
     rows = []
-    for B in [int(b) for b in args.batches.split(",")]:
+    for B in batches:
         W = replicate(W0, B) if B > 1 else W0
         np_, nr = len(W["u"]), len(W["target"])
         cfg = gpu.default_config(n_frame_slots=8, max_points=np_ + 64, max_residuals=nr + 64, **CALIB)
@@ -69,8 +58,7 @@ def main():
         for i, img in enumerate(W0["imgs"]):
             ctx.make_images(i, img)
         ctx.window_load(W)
-        D = 8 * W["n"] + 4
-        for rep in range(args.reps + 2):
+        for rep in range(reps + 2):
             if rep == 2:
                 ctx.sync()
                 ctx.profile_enable(True)
@@ -92,6 +80,24 @@ def main():
                              bytes_per_unit=BYTES[key], achieved_gbs=gbs, peak_gbs=peak, frac=gbs / peak,
                              points=np_, residuals=nr))
         ctx.close()
+    del flush_buf
+    return rows
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batches", default="1,8,64")
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--json", default=None)
+    args = ap.parse_args()
+    gpu = capi.load()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = peaks.get("hbm_gbs", 6650.0)
+    rows = measure(gpu, [int(b) for b in args.batches.split(",")], args.reps, peak)
     print("%5s %5s %12s %10s %12s %8s" % ("batch", "kern", "units/launch", "avg us", "GB/s (alg.)", "frac"))
     for r in rows:
         print("%5d %5s %12.0f %10.2f %12.1f %8.3f" % (r["batch"], r["kernel"], r["units_per_launch"], r["avg_us"],
