@@ -8,16 +8,17 @@
 //      dense lookup ridx[point][target] = residual id (or -1) that (b) uses.
 //  (b) k9_sc_kernel: all residuals of a point share its host frame and points are stored contiguously per host
 //      (allPoints order), so a CTA takes up to 64 points of ONE host, stages them
-//      {JpJdF per target, HdiF, bdSumF, Hcd} in shared memory and keeps its outputs in registers: a work item is
-//      one row (t1, i) x one target t2 = 8 entries of accD[h][t1][t2] (n*n*8 items), plus n*8 items for
-//      accE/accEB and 20 for accHcc/accbc.  No shared-memory atomics; one fp64 atomicAdd per output at the end.
+//      {JpJdF per target, HdiF, bdSumF, Hcd} in shared memory and keeps its outputs in registers: a thread owns a
+//      4 x 8 register tile of one accD[h][t1][t2] block (2 n^2 tiles) over one of G point groups — 3 LDS.128 + 1 LDS
+//      per 32 FMA; the first version's 1 x 8 rows were bound by their shared-memory reads — and the threads behind
+//      them one accE/accEB row or accHcc/accbc entry each.  The G groups meet in shared memory at the end; no
+//      shared-memory atomics, one fp64 atomicAdd per output per CTA.
 #include "ctx.h"
 
 namespace {
 
 constexpr int K9_THREADS = 512;
 constexpr int K9_TILE = 64;
-constexpr int K9_MAXITEMS = 3;     // n = 12: 12*12*8 + 12*8 + 20 = 1268 items <= 3 * 512
 
 __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin, const int* __restrict__ flags,
                                 const int* __restrict__ r_target, const float* __restrict__ res_pt,
@@ -66,27 +67,39 @@ __global__ void k9_point_kernel(int n, int np, const int* __restrict__ res_begin
     if (ngood == 0) max_rel_baseline[p] = 0.f;
 }
 
-__global__ void __launch_bounds__(K9_THREADS)
+// thread layout of k9_sc_kernel for a window of n frames: nD2 = 2 n^2 Schur items (one (t1, t2) pair x 4 of its 8 rows, all
+// 8 columns: 32 sums in registers), replicated over G point groups; the threads behind them own one accE/accEB row or
+// one accHcc/accbc entry each (n*8 + 20 <= 116 of them; G leaves at least 32 + ... threads, checked on the host)
+__host__ __device__ inline int k9_groups(int n) { return max(1, min(8, (K9_THREADS - 32) / (2 * n * n))); }
+
+__global__ void __launch_bounds__(K9_THREADS, 2)
 k9_sc_kernel(int n, const int* __restrict__ blocks, const int* __restrict__ ridx, const float* __restrict__ JpJdF,
              const float* __restrict__ pt_out, int cap_p, double* __restrict__ acc_sc,
              const unsigned char* __restrict__ marg) {
-    extern __shared__ float sm[];
-    float* sJ = sm;                               // [K9_TILE][n][8]
+    extern __shared__ __align__(16) float sm[];
+    float* sJ = sm;                               // [K9_TILE][n][8]   (after the last tile: the cross-group fold scratch)
     float* sHdi = sJ + K9_TILE * n * 8;           // [K9_TILE]
     float* sBd = sHdi + K9_TILE;                  // [K9_TILE]
     float* sHcd = sBd + K9_TILE;                  // [K9_TILE][4]
     const int nn = n * n;
     const int h = blocks[3 * blockIdx.x], p0 = blocks[3 * blockIdx.x + 1], p1 = blocks[3 * blockIdx.x + 2];
-    const int nD = nn * 8, nE = n * 8, nItems = nD + nE + 20;
-    float acc[K9_MAXITEMS][8];
+    const int nD2 = nn * 2, G = k9_groups(n), nE = n * 8;
+    const int tid = threadIdx.x;
+    const bool isD = tid < nD2 * G;
+    // Schur item of a D thread
+    const int item = tid % nD2, g = tid / nD2;
+    const int t2 = item % n, t1 = (item / n) >> 1, i0 = ((item / n) & 1) * 4;
+    // accE / accEB / accHcc / accbc item of an E thread (e >= nE + 20: idle)
+    const int e = tid - nD2 * G;
+    float acc[4][8];
 #pragma unroll
-    for (int q = 0; q < K9_MAXITEMS; q++)
+    for (int r = 0; r < 4; r++)
 #pragma unroll
-        for (int j = 0; j < 8; j++) acc[q][j] = 0.f;
+        for (int j = 0; j < 8; j++) acc[r][j] = 0.f;
     for (int base = p0; base < p1; base += K9_TILE) {
         const int cnt = min(K9_TILE, p1 - base);
         __syncthreads();
-        for (int i = threadIdx.x; i < K9_TILE * n * 2; i += K9_THREADS) {   // one float4 (half a JpJdF row) per thread
+        for (int i = tid; i < K9_TILE * n * 2; i += K9_THREADS) {   // one float4 (half a JpJdF row) per thread
             const int half = i & 1, t = (i >> 1) % n, q = (i >> 1) / n;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (q < cnt && (!marg || marg[base + q])) {
@@ -95,7 +108,7 @@ k9_sc_kernel(int n, const int* __restrict__ blocks, const int* __restrict__ ridx
             }
             reinterpret_cast<float4*>(sJ)[i] = v;
         }
-        for (int q = threadIdx.x; q < K9_TILE; q += K9_THREADS) {
+        for (int q = tid; q < K9_TILE; q += K9_THREADS) {
             const int p = base + q;
             const bool in = q < cnt && (!marg || marg[p]);
             sHdi[q] = in ? pt_out[PT_HDI * cap_p + p] : 0.f;
@@ -105,55 +118,73 @@ k9_sc_kernel(int n, const int* __restrict__ blocks, const int* __restrict__ ridx
                 sHcd[4 * q + k] = in ? pt_out[(PT_HCD_A + k) * cap_p + p] + pt_out[(PT_HCD_L + k) * cap_p + p] : 0.f;
         }
         __syncthreads();
+        // fp32 sums over the tile's points with fused multiply-adds (the oracle's mul/add sums differ in order anyway: 1e-4)
+        if (isD) {                                // accD[h][t1][t2] rows i0..i0+3: (HdiF * J1_i) * J2_j; 3 LDS.128 + 1 LDS per 32 FMA
+            const float* ja = sJ + t1 * 8 + i0;
+            const float* jb = sJ + t2 * 8;
+            for (int pp = g; pp < cnt; pp += G) {
+                const float hdi = sHdi[pp];
+                const float4 a4 = *reinterpret_cast<const float4*>(ja + pp * n * 8);
+                const float4 b0 = reinterpret_cast<const float4*>(jb + pp * n * 8)[0];
+                const float4 b1 = reinterpret_cast<const float4*>(jb + pp * n * 8)[1];
+                const float a[4] = {hdi * a4.x, hdi * a4.y, hdi * a4.z, hdi * a4.w};
 #pragma unroll
-        for (int q = 0; q < K9_MAXITEMS; q++) {
-            const int it = threadIdx.x + q * K9_THREADS;
-            if (it >= nItems) break;
-            if (it < nD) {                        // accD[h][t1][t2] row i: (HdiF * J1_i) * J2_j
-                const int t2 = it % n, ti = it / n, t1 = ti >> 3, i = ti & 7;
-                for (int pp = 0; pp < cnt; pp++) {
-                    const float a = sHdi[pp] * sJ[(pp * n + t1) * 8 + i];
-                    const float4 b0 = reinterpret_cast<const float4*>(sJ + (pp * n + t2) * 8)[0];
-                    const float4 b1 = reinterpret_cast<const float4*>(sJ + (pp * n + t2) * 8)[1];
-                    acc[q][0] += a * b0.x; acc[q][1] += a * b0.y; acc[q][2] += a * b0.z; acc[q][3] += a * b0.w;
-                    acc[q][4] += a * b1.x; acc[q][5] += a * b1.y; acc[q][6] += a * b1.z; acc[q][7] += a * b1.w;
+                for (int r = 0; r < 4; r++) {
+                    acc[r][0] = __fmaf_rn(a[r], b0.x, acc[r][0]); acc[r][1] = __fmaf_rn(a[r], b0.y, acc[r][1]);
+                    acc[r][2] = __fmaf_rn(a[r], b0.z, acc[r][2]); acc[r][3] = __fmaf_rn(a[r], b0.w, acc[r][3]);
+                    acc[r][4] = __fmaf_rn(a[r], b1.x, acc[r][4]); acc[r][5] = __fmaf_rn(a[r], b1.y, acc[r][5]);
+                    acc[r][6] = __fmaf_rn(a[r], b1.z, acc[r][6]); acc[r][7] = __fmaf_rn(a[r], b1.w, acc[r][7]);
                 }
-            } else if (it < nD + nE) {            // accE[h][t] row i (4 entries) and accEB[h][t][i]
-                const int e = it - nD, t = e >> 3, i = e & 7;
-                for (int pp = 0; pp < cnt; pp++) {
-                    const float a = sHdi[pp] * sJ[(pp * n + t) * 8 + i];
-                    acc[q][0] += a * sHcd[4 * pp]; acc[q][1] += a * sHcd[4 * pp + 1];
-                    acc[q][2] += a * sHcd[4 * pp + 2]; acc[q][3] += a * sHcd[4 * pp + 3];
-                    acc[q][4] += (sHdi[pp] * sBd[pp]) * sJ[(pp * n + t) * 8 + i];
-                }
-            } else {                              // accHcc[4][4], accbc[4]
-                const int e = it - nD - nE;
-                for (int pp = 0; pp < cnt; pp++) {
-                    if (e < 16) acc[q][0] += (sHdi[pp] * sHcd[4 * pp + (e >> 2)]) * sHcd[4 * pp + (e & 3)];
-                    else acc[q][0] += (sBd[pp] * sHdi[pp]) * sHcd[4 * pp + (e - 16)];
-                }
+            }
+        } else if (e < nE) {                      // accE[h][t] row i (4 entries) and accEB[h][t][i]
+            const int t = e >> 3, i = e & 7;
+            for (int pp = 0; pp < cnt; pp++) {
+                const float jv = sJ[(pp * n + t) * 8 + i];
+                const float av = sHdi[pp] * jv;
+                const float4 hc = reinterpret_cast<const float4*>(sHcd)[pp];
+                acc[0][0] = __fmaf_rn(av, hc.x, acc[0][0]); acc[0][1] = __fmaf_rn(av, hc.y, acc[0][1]);
+                acc[0][2] = __fmaf_rn(av, hc.z, acc[0][2]); acc[0][3] = __fmaf_rn(av, hc.w, acc[0][3]);
+                acc[0][4] = __fmaf_rn(sHdi[pp] * sBd[pp], jv, acc[0][4]);
+            }
+        } else if (e < nE + 20) {                 // accHcc[4][4], accbc[4]
+            const int k = e - nE;
+            for (int pp = 0; pp < cnt; pp++) {
+                if (k < 16) acc[0][0] = __fmaf_rn(sHdi[pp] * sHcd[4 * pp + (k >> 2)], sHcd[4 * pp + (k & 3)], acc[0][0]);
+                else acc[0][0] = __fmaf_rn(sBd[pp] * sHdi[pp], sHcd[4 * pp + (k - 16)], acc[0][0]);
             }
         }
     }
     // flush to the fp64 accumulators: accD[(h + n t1 + n^2 t2)][64] | accE[(h + n t)][32] | accEB[(h + n t)][8] | Hcc | bc
     const size_t offE = (size_t)nn * n * 64, offEB = offE + (size_t)nn * 32, offH = offEB + (size_t)nn * 8;
+    if (!isD) {
+        if (e < nE) {
+            const int t = e >> 3, i = e & 7;
+            double* gE = acc_sc + offE + (size_t)(h + n * t) * 32 + i * 4;
 #pragma unroll
-    for (int q = 0; q < K9_MAXITEMS; q++) {
-        const int it = threadIdx.x + q * K9_THREADS;
-        if (it >= nItems) break;
-        if (it < nD) {
-            const int t2 = it % n, ti = it / n, t1 = ti >> 3, i = ti & 7;
-            double* g = acc_sc + ((size_t)(h + n * t1 + nn * t2)) * 64 + i * 8;
+            for (int j = 0; j < 4; j++) if (acc[0][j] != 0.f) atomicAdd(gE + j, (double)acc[0][j]);
+            if (acc[0][4] != 0.f) atomicAdd(acc_sc + offEB + (size_t)(h + n * t) * 8 + i, (double)acc[0][4]);
+        } else if (e < nE + 20) {
+            if (acc[0][0] != 0.f) atomicAdd(acc_sc + offH + (e - nE), (double)acc[0][0]);
+        }
+    }
+    // the G point groups of a Schur item meet in shared memory ([group][k = row*8 + col][item]: conflict-free both ways),
+    // then every thread folds and adds a strided share of the nD2 x 32 sums: one fp64 atomic per output per CTA
+    __syncthreads();
+    float* fold = sm;
+    if (isD) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) if (acc[q][j] != 0.f) atomicAdd(g + j, (double)acc[q][j]);
-        } else if (it < nD + nE) {
-            const int e = it - nD, t = e >> 3, i = e & 7;
-            double* g = acc_sc + offE + (size_t)(h + n * t) * 32 + i * 4;
+        for (int r = 0; r < 4; r++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) if (acc[q][j] != 0.f) atomicAdd(g + j, (double)acc[q][j]);
-            if (acc[q][4] != 0.f) atomicAdd(acc_sc + offEB + (size_t)(h + n * t) * 8 + i, (double)acc[q][4]);
-        } else {
-            if (acc[q][0] != 0.f) atomicAdd(acc_sc + offH + (it - nD - nE), (double)acc[q][0]);
+            for (int j = 0; j < 8; j++) fold[((g * 32) + r * 8 + j) * nD2 + item] = acc[r][j];
+    }
+    __syncthreads();
+    for (int o = tid; o < nD2 * 32; o += K9_THREADS) {
+        const int k = o / nD2, it = o - k * nD2;
+        float v = 0.f;
+        for (int gg = 0; gg < G; gg++) v += fold[(gg * 32 + k) * nD2 + it];
+        if (v != 0.f) {
+            const int c2 = it % n, c1 = (it / n) >> 1, row = ((it / n) & 1) * 4 + (k >> 3), col = k & 7;
+            atomicAdd(acc_sc + ((size_t)(h + n * c1 + nn * c2)) * 64 + row * 8 + col, (double)v);
         }
     }
 }
@@ -198,8 +229,14 @@ int k9_accumulate_sc(ldso_gpu_ctx* c, const unsigned char* marg_mask, float prio
     const int nblk = W.n_sc_blocks;
     if (nblk > 0) {
         const int n = W.n;
-        LDSO_REQUIRE(c, n * n * 8 + n * 8 + 20 <= K9_MAXITEMS * K9_THREADS);
-        const size_t smem = sizeof(float) * (size_t)(K9_TILE * n * 8 + K9_TILE * 6);
+        const int G = k9_groups(n);
+        LDSO_REQUIRE(c, 2 * n * n * G + n * 8 + 20 <= K9_THREADS);
+        const size_t smem = sizeof(float) * std::max((size_t)(K9_TILE * n * 8 + K9_TILE * 6), (size_t)G * 32 * 2 * n * n);
+        static size_t smem_set = 0;
+        if (smem > smem_set) {
+            LDSO_CUDA_OK(c, cudaFuncSetAttribute(k9_sc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            smem_set = smem;
+        }
         prof_begin(c, c->stream);
         k9_point_kernel<<<(W.np + 127) / 128, 128, 0, c->stream>>>(n, W.np, W.res_begin, W.flags, W.r_target, W.res_pt, W.prior,
                                                                    W.idepth, W.idepth_zero, W.pt_out, W.max_rel_baseline, W.cap_p,

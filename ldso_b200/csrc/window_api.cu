@@ -11,6 +11,15 @@
 
 #define CPARS 4
 
+static int sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
 namespace {
 
 template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
@@ -135,26 +144,19 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * WIN_PT_ROWS * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.max_rel_baseline, 0, sizeof(float) * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.num_good, 0, sizeof(float) * W.cap_p, c->stream));
-    // K9 CTA table: up to 64 consecutive points of one host per CTA
+    // K9 CTA table: up to 64 consecutive points of one host per CTA (longer blocks were measured on the 64x window: no
+    // gain, the kernel is bound by its shared-memory reads, not by the fp64 atomics of the flush)
+    const int per = 64;
     std::vector<int> blk;
     int p = 0;
     while (p < np) {
         int h = host[p], e = p;
-        while (e < np && host[e] == h && e - p < 64) e++;
+        while (e < np && host[e] == h && e - p < per) e++;
         blk.push_back(h); blk.push_back(p); blk.push_back(e);
         p = e;
     }
     W.n_sc_blocks = (int)blk.size() / 3;
     return upload(c, W.sc_blocks, blk.data(), sizeof(int) * blk.size());
-}
-
-static int sm_count() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
-    }
-    return sms;
 }
 
 // (re)build the K8 work list: residual ids sorted by key = mode * n^2 + host + n * target, cut into chunks of <= 128 (one window) to <= 1024 (batched) ids
