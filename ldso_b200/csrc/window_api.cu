@@ -144,9 +144,12 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * WIN_PT_ROWS * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.max_rel_baseline, 0, sizeof(float) * W.cap_p, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(W.num_good, 0, sizeof(float) * W.cap_p, c->stream));
-    // K9 CTA table: up to 64 consecutive points of one host per CTA (longer blocks were measured on the 64x window: no
-    // gain, the kernel is bound by its shared-memory reads, not by the fp64 atomics of the flush)
-    const int per = 64;
+    // K9 CTA table: consecutive points of one host per CTA — 64 (one staging tile) for a single window, more tiles per CTA
+    // once that still leaves two CTAs per SM (batched windows): the cross-group fold and the ~3 k fp64 atomics of the
+    // flush are paid per CTA (64x window on B200: 150 us at 64 points per CTA, 95 us at 448)
+    int per = 64;
+    if (np > 64 * 2 * sm_count()) per = std::min(1024, np / (2 * sm_count()) / 64 * 64);
+    if (const char* e = getenv("LDSO_K9_BLOCK")) per = atoi(e);            // tuning knob of profiles/kernel_bench.py
     std::vector<int> blk;
     int p = 0;
     while (p < np) {
