@@ -148,7 +148,8 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     // once that still leaves two CTAs per SM (batched windows): the cross-group fold and the ~3 k fp64 atomics of the
     // flush are paid per CTA (64x window on B200: 150 us at 64 points per CTA, 95 us at 448)
     int per = 64;
-    if (np > 64 * 2 * sm_count()) per = std::min(1024, np / (2 * sm_count()) / 64 * 64);
+    const int slots = 2 * sm_count() - LDSO_MAX_WINDOW;                    // every host frame may add one short block
+    if (np > 64 * slots) per = std::min(1024, ((np + slots - 1) / slots + 63) / 64 * 64);   // one wave: no tail
     if (const char* e = getenv("LDSO_K9_BLOCK")) per = atoi(e);            // tuning knob of profiles/kernel_bench.py
     std::vector<int> blk;
     int p = 0;
