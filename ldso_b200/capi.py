@@ -85,6 +85,8 @@ class Api:
         self.fn("default_config")(C.byref(cfg))
         for k, v in kw.items():
             setattr(cfg, k, v)
+        if os.environ.get("LDSO_LM_DBG"):           # measurement only: 3 = SM clocks per LM phase on stderr (profile_get)
+            cfg.reserved[0] = int(os.environ["LDSO_LM_DBG"])
         return cfg
 
     def create(self, cfg):

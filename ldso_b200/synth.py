@@ -210,3 +210,21 @@ def make_window(seed=1001, frame_ids=(40, 46, 52, 58, 64, 70, 76), pts_per_frame
                 target=np.array(target, np.int32), state=np.array(state, np.int32), flags=np.array(flags, np.uint8),
                 res_to_zero=rng.normal(0, 2.0, (nr, 8)).astype(np.float32), HM=HM, bM=rng.normal(0, 10, D),
                 delta=rng.normal(0, 1e-3, D), w2c_gt=w2c_gt, w2c=w2c)
+
+
+def replicate_window(W, B):
+    """B copies of every point of a make_window() dict (and of its residuals), kept contiguous per host frame like the
+    reference's allPoints walk: the residual population of B sequences in one window (BASELINE configs[4])"""
+    npnt = len(W["u"])
+    order = np.argsort(np.tile(W["host"], B), kind="stable")
+    src = np.tile(np.arange(npnt), B)[order]                      # source point of every replicated point
+    cnt = np.diff(W["res_begin"])[src]
+    rb = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)
+    ridx = np.concatenate([np.arange(W["res_begin"][p], W["res_begin"][p + 1]) for p in src])
+    out = dict(W)
+    for k in ("u", "v", "idepth", "idepth_zero", "host", "color", "weights", "prior"):
+        out[k] = W[k][src]
+    for k in ("target", "state", "flags", "res_to_zero"):
+        out[k] = W[k][ridx]
+    out["res_begin"] = rb
+    return out

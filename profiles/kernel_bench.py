@@ -27,21 +27,7 @@ BYTES = {"k7": 900.0, "k8": 288.0 + 32.0, "k9": 72.0, "k10": 60.0}
 SLOTS = {"k7": (2, "residuals"), "k8": (3, "residuals"), "k9": (4, "residuals"), "k10": (8, "points")}
 
 
-def replicate(W, B):
-    """B copies of every point (and its residuals), kept contiguous per host frame like the reference's allPoints walk"""
-    npnt = len(W["u"])
-    order = np.argsort(np.tile(W["host"], B), kind="stable")
-    src = np.tile(np.arange(npnt), B)[order]                      # source point of every replicated point
-    cnt = np.diff(W["res_begin"])[src]
-    rb = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)
-    ridx = np.concatenate([np.arange(W["res_begin"][p], W["res_begin"][p + 1]) for p in src])
-    out = dict(W)
-    for k in ("u", "v", "idepth", "idepth_zero", "host", "color", "weights", "prior"):
-        out[k] = W[k][src]
-    for k in ("target", "state", "flags", "res_to_zero"):
-        out[k] = W[k][ridx]
-    out["res_begin"] = rb
-    return out
+replicate = synth.replicate_window
 
 
 def measure(gpu, batches, reps, peak):

@@ -218,3 +218,43 @@ def test_calc_energy_parity(gpu, oracle, window):
     assert abs(eg[0] - eo[0]) <= 1e-4 * abs(eo[0]) and eo[0] != 0, (eg, eo)
     assert abs(eg[1] - eo[1]) <= 1e-12 * max(abs(eo[1]), 1.0)
     g.close(); o.close()
+
+
+def test_batched_window_parity(gpu, oracle, window):
+    """10 x the window in one launch per kernel (20 k points, 120 k residuals): the work list is long enough for
+    k8_top_stream_kernel (chunks of 384+ ids, cp.async tiles) in all three modes and for several staging tiles per
+    K9 CTA.  Same checks as the single window."""
+    W = synth.replicate_window(window, 10)
+    g, o = load(gpu, W), load(oracle, W)
+    for c in (g, o):
+        c.window_linearize(True)
+    fl = o.window_residual_ints(2)
+    assert np.array_equal(g.window_residual_ints(2), fl)
+    mask = (((fl & 2) != 0) & ((fl & 1) == 0) & (np.arange(len(fl)) % 3 == 0)).astype(np.uint8)
+    g.window_fix_linearization(mask); o.window_fix_linearization(mask)
+    ag, ao = g.window_accumulate(), o.window_accumulate()                      # modes 0 and 1
+    assert np.array_equal(ag["counts"], ao["counts"]) and ao["counts"][0] > 40000 and ao["counts"][1] > 20000
+    for k in ("HA", "bA", "HL", "bL", "Hsc", "bsc"):
+        assert util.rel_err(ag[k], ao[k]) < 1e-4, (k, util.rel_err(ag[k], ao[k]))
+    n = W["n"]
+    for k in ("HA", "HL", "Hsc"):
+        for h in range(n):
+            for t in range(n):
+                bg = ag[k][4 + 8 * h:12 + 8 * h, 4 + 8 * t:12 + 8 * t]; bo = ao[k][4 + 8 * h:12 + 8 * h, 4 + 8 * t:12 + 8 * t]
+                assert np.linalg.norm(bg - bo) <= 1e-4 * np.linalg.norm(bo) + 1e-7 * np.linalg.norm(ao[k]), (k, h, t)
+    for what in range(9):                                                      # per-point sums in residual order: bit-exact
+        assert np.array_equal(bits(g.window_point_floats(what)), bits(o.window_point_floats(what))), what
+    x = o.window_solve(0, 1e-5, ao, W["HM"] * 1e4, W["bM"], W["delta"])
+    assert np.array_equal(bits(g.window_resubstitute(x, 1e-5)), bits(o.window_resubstitute(x, 1e-5)))
+    g.close(); o.close()
+    # mode 2: marginalise half of the points of a fully linearised window
+    g, o = linearised(gpu, W), linearised(oracle, W)
+    sel = np.arange(len(W["u"])) % 2 == 0
+    Hg, bg, ng = g.window_marginalize_points(sel.astype(np.uint8))
+    Ho, bo, no = o.window_marginalize_points(sel.astype(np.uint8))
+    assert ng == no and no > 5000
+    assert util.rel_err(Hg, Ho) < 1e-4 and util.rel_err(bg, bo) < 1e-4, (util.rel_err(Hg, Ho), util.rel_err(bg, bo))
+    for what in range(9):
+        a, b = g.window_point_floats(what), o.window_point_floats(what)
+        assert np.array_equal(bits(a[sel]), bits(b[sel])), what
+    g.close(); o.close()
