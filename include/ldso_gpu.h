@@ -184,6 +184,14 @@ int ldso_gpu_immature_set(ldso_gpu_ctx* ctx, int n, const int* host, const float
  * hostToFrame tables of :1171-1176.  counts_out[6]: number of points per resulting status. */
 int ldso_gpu_immature_trace(ldso_gpu_ctx* ctx, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
                             const float* aff, int counts_out[6]);
+/* the same trace without waiting for it: the kernel is queued behind the frame's other work and the call returns; the
+ * status counts are fetched later with ldso_gpu_immature_trace_counts (which waits if it has to).  Every other pool entry
+ * point completes a pending trace first, so results are the same as with ldso_gpu_immature_trace.  The reference consumes
+ * trace results only at the next keyframe (activatePointsMT, FullSystem.cc:1203-1320), so the wait leaves the frame's
+ * critical path. */
+int ldso_gpu_immature_trace_async(ldso_gpu_ctx* ctx, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
+                                  const float* aff);
+int ldso_gpu_immature_trace_counts(ldso_gpu_ctx* ctx, int counts_out[6]);
 /* any pointer may be NULL */
 int ldso_gpu_immature_get(ldso_gpu_ctx* ctx, float* idepth_min, float* idepth_max, float* quality, int* status,
                           float* last_trace_uv, float* last_trace_pixel_interval);

@@ -267,6 +267,16 @@ class Ctx:
         self._call("immature_trace", C.c_int(new_slot), C.c_int(len(Kt)), _fp(KRKi), _fp(Kt), _fp(aff), _ip(cnt))
         return cnt
 
+    def immature_trace_async(self, new_slot, KRKi, Kt, aff):
+        """the same trace queued without waiting; counts come from immature_trace_counts()"""
+        KRKi, Kt, aff = f32(KRKi), f32(Kt), f32(aff)
+        self._call("immature_trace_async", C.c_int(new_slot), C.c_int(len(Kt)), _fp(KRKi), _fp(Kt), _fp(aff))
+
+    def immature_trace_counts(self):
+        cnt = np.zeros(6, np.int32)
+        self._call("immature_trace_counts", _ip(cnt))
+        return cnt
+
     def immature_get(self, fields=None):
         """read back pool state; fields: subset of (idepth_min, idepth_max, quality, status, uv, interval), default all"""
         n = self.imm_n

@@ -210,6 +210,7 @@ void prof_drain(ldso_gpu_ctx* c) {
     c->prof_pending.clear();
 }
 extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
+    immature_trace_finalize(c);
     prof_drain(c);
     c->profile_on = on;
     if (on) for (int i = 0; i < LDSO_PROF_SLOTS; i++) { c->prof_ms[i] = 0; c->prof_launches[i] = 0; c->prof_units[i] = 0; }
@@ -217,6 +218,7 @@ extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
 }
 extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms, long long* launches, double* units) {
     LDSO_REQUIRE(c, which >= 0 && which < LDSO_PROF_SLOTS);
+    immature_trace_finalize(c);
     prof_drain(c);
     *total_ms = c->prof_ms[which]; *launches = c->prof_launches[which]; *units = c->prof_units[which];
     if (c->cfg.reserved[0] == 3 && which == LDSO_PROF_K34) {

@@ -129,6 +129,8 @@ void selector_free(ldso_gpu_ctx* c);
 void prof_begin(ldso_gpu_ctx* c, cudaStream_t s);
 int prof_end(ldso_gpu_ctx* c, cudaStream_t s, int which, double units);   // index into prof_pending or -1
 void prof_drain(ldso_gpu_ctx* c);
+int immature_trace_fence(ldso_gpu_ctx* c, int slot);   // before a frame slot is rewritten on the tracking stream
+int immature_trace_finalize(ldso_gpu_ctx* c);   // completes a trace launched without waiting (k56_immature.cu)
 void immature_free(ldso_gpu_ctx* c);
 void initializer_free(ldso_gpu_ctx* c);
 void undistort_free(ldso_gpu_ctx* c);

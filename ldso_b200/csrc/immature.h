@@ -32,6 +32,13 @@ struct ImmatureDev {
     int* src_n = nullptr;                    // device: length of the list
     int src_cap = 0, src_n_host = 0;         // host: capacity and an upper bound of the current length
     void* pinned = nullptr;
+    int* trace_cnt = nullptr;                // pinned [8]: status counts + step counts of the last trace
+    cudaEvent_t ev_ready = nullptr, ev_done = nullptr;   // tracking stream -> trace stream, trace done
+    cudaStream_t trace_stream = nullptr;     // stream of the pending trace
+    int trace_slot = -1;                     // frame slot the pending trace reads
+    bool trace_pending = false;              // a trace was launched without waiting (ldso_gpu_immature_trace_async)
+    int trace_prof_idx = -1;
+    int trace_counts[6] = {0, 0, 0, 0, 0, 0};
     size_t pinned_bytes = 0;
 };
 

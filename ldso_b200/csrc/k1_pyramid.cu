@@ -155,6 +155,7 @@ __global__ void k1_wrap_columns_kernel(float4* __restrict__ out, const float* __
 }  // namespace
 
 int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
+    if (immature_trace_fence(c, slot)) return -1;
     K1Params p;
     p.levels = c->levels;
     p.gammaWeights = c->cfg.gamma_weights_pixel_select;

@@ -539,8 +539,33 @@ __global__ void im_append_kernel(int n, int base, int host_idx, const float* __r
 // ---- host side ------------------------------------------------------------------------------------------------
 }  // namespace
 
+// a trace launched by ldso_gpu_immature_trace_async is completed (stream sync, counts, profile units) before anything
+// else touches the pool or its pinned staging buffer
+int immature_trace_finalize(ldso_gpu_ctx* c) {
+    ImmatureDev* P = (ImmatureDev*)c->immature;
+    if (!P || !P->trace_pending) return 0;
+    P->trace_pending = false;
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(P->trace_stream));
+    for (int i = 0; i < 6; i++) P->trace_counts[i] = P->trace_cnt[i];
+    // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
+    if (P->trace_prof_idx >= 0 && P->trace_prof_idx < (int)c->prof_pending.size()) c->prof_pending[P->trace_prof_idx].units = (double)P->trace_cnt[6] + 9.0 * P->trace_cnt[7];
+    P->trace_prof_idx = -1;
+    return 0;
+}
+
+// a frame slot is about to be rewritten on the tracking stream: if the pending trace (mapping stream) still reads it, the
+// tracking stream waits for it on the device
+int immature_trace_fence(ldso_gpu_ctx* c, int slot) {
+    ImmatureDev* P = (ImmatureDev*)c->immature;
+    if (P && P->trace_pending && P->trace_slot == slot && P->trace_stream != c->stream) LDSO_CUDA_OK(c, cudaStreamWaitEvent(c->stream, P->ev_done, 0));
+    return 0;
+}
+
 ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
-    if (c->immature) return (ImmatureDev*)c->immature;
+    if (c->immature) {
+        immature_trace_finalize(c);
+        return (ImmatureDev*)c->immature;
+    }
     ImmatureDev* P = new ImmatureDev();
     P->cap = c->cfg.max_immature > 16 ? c->cfg.max_immature : 16;
     const size_t N = P->cap;
@@ -563,6 +588,9 @@ ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     if (ok) cudaMemset(P->src_n, 0, 32);
     P->pinned_bytes = 4 * 32 * N + 4096;
     ok = ok && cudaMallocHost(&P->pinned, P->pinned_bytes) == cudaSuccess;
+    ok = ok && cudaMallocHost((void**)&P->trace_cnt, 32) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&P->ev_ready, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&P->ev_done, cudaEventDisableTiming) == cudaSuccess;
     c->immature = P;
     if (!ok) { c->set_error("immature pool allocation failed", __FILE__, __LINE__); return nullptr; }
     return P;
@@ -579,6 +607,9 @@ void immature_free(ldso_gpu_ctx* c) {
                     P->src_cells, P->src_n};
     for (void* p : ptrs) cudaFree(p);
     if (P->pinned) cudaFreeHost(P->pinned);
+    if (P->trace_cnt) cudaFreeHost(P->trace_cnt);
+    if (P->ev_ready) cudaEventDestroy(P->ev_ready);
+    if (P->ev_done) cudaEventDestroy(P->ev_done);
     delete P;
     c->immature = nullptr;
 }
@@ -640,22 +671,28 @@ extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, co
     return 0;
 }
 
-extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
-                                       const float* aff, int counts_out[6]) {
-    ImmatureDev* P = immature_pool(c);
+static int trace_launch(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt, const float* aff, bool async) {
+    ImmatureDev* P = immature_pool(c);          // completes a pending trace first
     if (!P) return -1;
-    LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt &&
-                        aff && counts_out);
-    for (int i = 0; i < 6; i++) counts_out[i] = 0;
+    LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt && aff);
+    for (int i = 0; i < 6; i++) P->trace_counts[i] = 0;
     if (P->n == 0) return 0;
+    // async: the trace runs on the mapping stream, behind everything queued on the tracking stream so far (the new frame's
+    // pyramid, earlier pool updates), and next to whatever the tracking stream gets afterwards (the next frame's tracker
+    // occupies 32 of the SMs)
+    cudaStream_t S = async ? c->stream_map : c->stream;
+    if (async) {
+        LDSO_CUDA_OK(c, cudaEventRecord(P->ev_ready, c->stream));
+        LDSO_CUDA_OK(c, cudaStreamWaitEvent(S, P->ev_ready, 0));
+    }
     float* st = (float*)P->pinned;
     for (int h = 0; h < n_hosts; h++) {
         float* T = st + 16 * h;
         memcpy(T, KRKi + 9 * h, 36); memcpy(T + 9, Kt + 3 * h, 12); memcpy(T + 12, aff + 2 * h, 8);
         T[14] = T[15] = 0;
     }
-    LDSO_CUDA_OK(c, ldso_copy(c, P->tables, st, 64 * (size_t)n_hosts, cudaMemcpyHostToDevice, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(P->counts, 0, 32, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, P->tables, st, 64 * (size_t)n_hosts, cudaMemcpyHostToDevice, S));
+    LDSO_CUDA_OK(c, cudaMemsetAsync(P->counts, 0, 32, S));
     K5Params p;
     p.img = c->frame[new_slot]; p.n = P->n; p.w = c->wG[0]; p.h = c->hG[0];
     p.gn_its = c->cfg.trace_gn_iterations; p.min_radius = c->cfg.min_trace_test_radius;
@@ -665,17 +702,36 @@ extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_host
     p.host = P->host; p.status = P->status; p.u = P->u; p.v = P->v; p.color = P->color; p.weights = P->weights; p.gradH = P->gradH;
     p.energyTH = P->energyTH; p.tables = P->tables; p.idmin = P->idmin; p.idmax = P->idmax; p.quality = P->quality;
     p.lastUV = P->lastUV; p.interval = P->interval; p.counts = P->counts;
-    prof_begin(c, c->stream);
-    k5_trace_kernel<<<(8 * P->n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, c->stream>>>(p);
-    const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K5, P->n);
+    prof_begin(c, S);
+    k5_trace_kernel<<<(8 * P->n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, S>>>(p);
+    P->trace_prof_idx = prof_end(c, S, LDSO_PROF_K5, P->n);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    int* cnt = (int*)(st + 16 * LDSO_MAX_WINDOW);
-    LDSO_CUDA_OK(c, ldso_copy(c, cnt, P->counts, 32, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
-    for (int i = 0; i < 6; i++) counts_out[i] = cnt[i];
-    // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
-    if (prof_idx >= 0) c->prof_pending[prof_idx].units = (double)cnt[6] + 9.0 * cnt[7];
+    LDSO_CUDA_OK(c, ldso_copy(c, P->trace_cnt, P->counts, 32, cudaMemcpyDeviceToHost, S));
+    LDSO_CUDA_OK(c, cudaEventRecord(P->ev_done, S));
+    P->trace_stream = S; P->trace_slot = new_slot;
+    P->trace_pending = true;
+    return 0;
+}
+
+extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
+                                       const float* aff, int counts_out[6]) {
+    LDSO_REQUIRE(c, counts_out);
+    if (trace_launch(c, new_slot, n_hosts, KRKi, Kt, aff, false)) return -1;
+    return ldso_gpu_immature_trace_counts(c, counts_out);
+}
+
+extern "C" int ldso_gpu_immature_trace_async(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
+                                             const float* aff) {
+    return trace_launch(c, new_slot, n_hosts, KRKi, Kt, aff, true);
+}
+
+extern "C" int ldso_gpu_immature_trace_counts(ldso_gpu_ctx* c, int counts_out[6]) {
+    LDSO_REQUIRE(c, counts_out);
+    if (immature_trace_finalize(c)) return -1;
+    ImmatureDev* P = immature_pool(c);
+    if (!P) return -1;
+    for (int i = 0; i < 6; i++) counts_out[i] = P->trace_counts[i];
     return 0;
 }
 

@@ -137,6 +137,12 @@ class Odometry:
         self.ctx.immature_append(f["slot"], len(self.frames) - 1, new["u"], new["v"], types=new["type"])
         return k
 
+    def fetch_trace_counts(self):
+        """status counts of the trace queued by the previous frame (waits only if it is still running)"""
+        if getattr(self, "_trace_log", None) is not None:
+            self._trace_log["trace"] = self.ctx.immature_trace_counts().tolist()
+            self._trace_log = None
+
     # ---- per frame (FullSystem::addActiveFrame, :78-187) ---------------------------------------------
     def tick(self, name, t0):
         t1 = time.perf_counter()
@@ -164,6 +170,7 @@ class Odometry:
             return dict(kf=True, ok=True)
         ref = self.frames[-1]
         ok, rel, aff, tr = self.track(slot)
+        self.fetch_trace_counts()
         t = self.tick("K3/K4 trackNewestCoarse", t)
         if not ok:
             self.free_slots.append(slot)
@@ -181,18 +188,20 @@ class Odometry:
             self.first_rmse = res0
         need_kf = score > 1 or 2 * self.first_rmse < res0
         # traceNewCoarse (:1157-1195)
-        counts = None
-        if self.I is not None and len(self.I["host"]):
+        # The trace is queued without waiting: nothing reads its results before the next keyframe's activation, so its
+        # status counts (log only) are fetched after the NEXT frame's tracker has returned, when the stream has drained.
+        traced = self.I is not None and len(self.I["host"]) > 0
+        if traced:
             KRKi, Kt, affs = self.host_tables(w2c, aff)
-            counts = self.ctx.immature_trace(slot, KRKi, Kt, affs)
+            self.ctx.immature_trace_async(slot, KRKi, Kt, affs)
         t = self.tick("K5 traceNewCoarse", t)
-        self.log.append(dict(frame=fid, kf=bool(need_kf), score=float(score), res=res0, iters=tr["iters"].tolist(),
-                             trace=None if counts is None else counts.tolist()))
+        self.log.append(dict(frame=fid, kf=bool(need_kf), score=float(score), res=res0, iters=tr["iters"].tolist(), trace=None))
+        self._trace_log = self.log[-1] if traced else None
         if need_kf:
             self.make_keyframe(dict(id=fid, slot=slot, w2c=w2c, aff=(float(aff[0]), float(aff[1]))))
             t = self.tick("KF makeKeyFrame total (Python orchestration included)", t)
         else:
-            self.free_slots.append(slot)
+            self.free_slots.insert(0, slot)      # oldest-first reuse: the queued trace may still be reading this slot
         return dict(kf=bool(need_kf), ok=True)
 
     def track(self, slot):

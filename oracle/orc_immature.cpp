@@ -18,6 +18,7 @@ struct Pool {
     // CoarseDistanceMap (include/frontend/CoarseTracker.h:120-160): fwdWarpedIDDistFinal and the two BFS lists
     std::vector<float> dist;
     std::vector<int> bfs1, bfs2;
+    int trace_counts[6] = {0, 0, 0, 0, 0, 0};   // last trace (orc_immature_trace_async / _counts)
 };
 Pool& pool_of(orc_ctx* c) {
     if (!c->immature) c->immature = std::make_shared<Pool>();
@@ -250,6 +251,18 @@ extern "C" int orc_immature_trace(orc_ctx* c, int new_slot, int n_hosts, const f
         int st = trace_on(c, P, k, dI, KRKi + 9 * h, Kt + 3 * h, aff + 2 * h);
         counts[st]++;
     }
+    return 0;
+}
+
+// the asynchronous pair of the product ABI: the oracle traces at once and keeps the counts
+extern "C" int orc_immature_trace_async(orc_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt, const float* aff) {
+    Pool& P = pool_of(c);
+    return orc_immature_trace(c, new_slot, n_hosts, KRKi, Kt, aff, P.trace_counts);
+}
+
+extern "C" int orc_immature_trace_counts(orc_ctx* c, int counts[6]) {
+    Pool& P = pool_of(c);
+    for (int i = 0; i < 6; i++) counts[i] = P.trace_counts[i];
     return 0;
 }
 

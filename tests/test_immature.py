@@ -107,6 +107,34 @@ def test_gpu_immature_parity(oracle, gpu, calib, kw):
     assert np.array_equal(ia, ib)
 
 
+def _run_async(api, calib="small", **kw):
+    S = util.immature_scene(calib, **kw)
+    ctx = util.make_ctx(api, calib, n_frame_slots=8)
+    return S, util.run_immature(ctx, S, async_trace=True)
+
+
+def test_oracle_async_trace_pair(oracle):
+    """immature_trace_async + immature_trace_counts give what immature_trace gives"""
+    _, a = _run(oracle)
+    _, b = _run_async(oracle)
+    for ca, cb, ta, tb in zip(a["counts"], b["counts"], a["traces"], b["traces"]):
+        assert np.array_equal(ca, cb) and ca.sum() > 0
+        for key in ("status", "idepth_min", "idepth_max", "quality", "uv", "interval"):
+            assert np.array_equal(ta[key], tb[key], equal_nan=True), key
+
+
+@pytest.mark.gpu
+def test_gpu_async_trace_matches_oracle(oracle, gpu):
+    """the trace queued without waiting (ldso_gpu_immature_trace_async): pool state and counts equal the oracle's"""
+    _, a = _run(oracle)
+    _, b = _run_async(gpu)
+    for ca, cb, ta, tb in zip(a["counts"], b["counts"], a["traces"], b["traces"]):
+        assert np.array_equal(ca, cb)
+        for key in ("status", "idepth_min", "idepth_max", "quality", "uv", "interval"):
+            assert np.array_equal(ta[key], tb[key], equal_nan=True), key
+    assert np.array_equal(a["cand"], b["cand"]) and np.array_equal(a["act"][0], b["act"][0])
+
+
 @pytest.mark.gpu
 def test_gpu_immature_edge_cases(oracle, gpu):
     """the same hand-made pool (OOB, SKIPPED, far OOB, NaN patch) through both libraries"""

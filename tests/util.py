@@ -80,7 +80,7 @@ def immature_scene(calib="small", host_ids=(40, 44), new_ids=(46, 48, 50), pts_p
                 host=np.concatenate(H), gt_idepth=np.concatenate(GT).astype(np.float32), tables=tables, w2c=w2c)
 
 
-def run_immature(ctx, S, activate=True):
+def run_immature(ctx, S, activate=True, async_trace=False):
     """Drive create -> set -> trace on every new frame -> activate through one C ABI (oracle or GPU)."""
     from ldso_b200 import window_host as wh
     nh, fr = S["n_hosts"], S["frames"]
@@ -97,8 +97,13 @@ def run_immature(ctx, S, activate=True):
                      np.full(n, 10000.0, np.float32), np.full(n, 5, np.int32))
     out = dict(color=col, weights=wgt, grad_h=gh, energy_th=eth, traces=[], counts=[])
     for ni, (KRKi, Kt, aff) in enumerate(S["tables"]):
-        out["counts"].append(ctx.immature_trace(nh + ni, KRKi, Kt, aff))
-        out["traces"].append(ctx.immature_get())
+        if async_trace:                      # queued without waiting; immature_get completes it, the counts come afterwards
+            ctx.immature_trace_async(nh + ni, KRKi, Kt, aff)
+            out["traces"].append(ctx.immature_get())
+            out["counts"].append(ctx.immature_trace_counts())
+        else:
+            out["counts"].append(ctx.immature_trace(nh + ni, KRKi, Kt, aff))
+            out["traces"].append(ctx.immature_get())
     if activate:
         c = S["calib"]
         nf = len(fr)
