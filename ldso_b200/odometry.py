@@ -211,16 +211,17 @@ class Odometry:
         T_ref = ref["w2c"]
         T_last = self.poses[ids[-1]]
         last_rel = wh.se3_mul(T_last, wh.se3_inv(T_ref))                     # lastF_2_slast
-        tries = []
-        if len(ids) >= 2:
-            motion = wh.se3_mul(T_last, wh.se3_inv(self.poses[ids[-2]]))       # sprelast -> slast, assumed to repeat
-            tries.append(wh.se3_mul(motion, last_rel))                        # constant motion
-            tries.append(wh.se3_mul(motion, wh.se3_mul(motion, last_rel)))    # double motion
-        tries.append(last_rel)                                                # zero motion
-        tries.append((np.eye(3), np.zeros(3)))                                # zero motion from the keyframe
+
+        def tries():                                                          # built on demand: the first one usually wins
+            if len(ids) >= 2:
+                motion = wh.se3_mul(T_last, wh.se3_inv(self.poses[ids[-2]]))   # sprelast -> slast, assumed to repeat
+                yield wh.se3_mul(motion, last_rel)                            # constant motion
+                yield wh.se3_mul(motion, wh.se3_mul(motion, last_rel))        # double motion
+            yield last_rel                                                    # zero motion
+            yield (np.eye(3), np.zeros(3))                                    # zero motion from the keyframe
         aff0 = self.last_aff if hasattr(self, "last_aff") else ref["aff"]
         best = None
-        for T in tries:
+        for T in tries():
             r = self.ctx.tracker_track(0, slot, rt12(T), [aff0[0], aff0[1]])
             if r["ok"] and np.isfinite(r["last_residuals"][0]):
                 if best is None or r["last_residuals"][0] < best[3]["last_residuals"][0]:

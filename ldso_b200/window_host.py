@@ -41,6 +41,19 @@ def from_to_vec_exposure(expF, expT, g2F, g2T):
     return np.float32(a), np.float32(b)
 
 
+def from_to_vec_exposure_table(exposure, g2):
+    """from_to_vec_exposure for every pair at once: a[t][h], b[t][h] (host = from, target = to), same float32 arithmetic"""
+    e = np.asarray(exposure, np.float32)
+    g = np.asarray(g2, np.float32).reshape(len(e), 2)
+    eF = np.broadcast_to(e[None, :], (len(e), len(e))).copy()
+    eT = np.broadcast_to(e[:, None], (len(e), len(e))).copy()
+    z = (eF == 0) | (eT == 0)
+    eF[z] = 1; eT[z] = 1
+    a = np.exp(g[:, None, 0] - g[None, :, 0]).astype(np.float32) * eT / eF
+    b = g[:, None, 1] - a * g[None, :, 1]
+    return a.astype(np.float32), b.astype(np.float32)
+
+
 def _pairs(w2c):
     """T_target * T_host^-1 for every pair, as stacks indexed [target][host] (float64)"""
     R = np.stack([T[0] for T in w2c]).astype(np.float64)
@@ -52,15 +65,25 @@ def _pairs(w2c):
     return Rl, tl
 
 
+_K_CACHE = {}
+
+
+def _k_matrices(fx, fy, cx, cy):
+    key = (float(fx), float(fy), float(cx), float(cy))
+    if key not in _K_CACHE:
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=np.float32)
+        _K_CACHE[key] = (K, np.linalg.inv(K.astype(np.float64)).astype(np.float32))
+    return _K_CACHE[key]
+
+
 def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
     """FrameFramePrecalc::Set for every (host, target) pair (src/internal/FrameFramePrecalc.cc:6-35).
     w2c_eval / w2c: lists of (R, t) world-to-camera at the FEJ evaluation point / current state."""
     n = len(w2c)
     fx, fy, cx, cy = [np.float32(c) for c in calib]
-    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], dtype=np.float32)
-    Ki = np.linalg.inv(K.astype(np.float64)).astype(np.float32)
-    R0, t0 = _pairs(w2c_eval)
+    K, Ki = _k_matrices(fx, fy, cx, cy)
     R, tt = _pairs(w2c)
+    R0, t0 = (R, tt) if w2c_eval is w2c else _pairs(w2c_eval)
     R0f, t0f, Rf, tf = R0.astype(np.float32), t0.astype(np.float32), R.astype(np.float32), tt.astype(np.float32)
     KRKi = (K @ Rf @ Ki).astype(np.float32)
     Kt = (K @ tf[..., None])[..., 0].astype(np.float32)
@@ -69,10 +92,9 @@ def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
     out[..., 12:21] = KRKi.reshape(n, n, 9); out[..., 21:24] = Kt
     out[..., 27:36] = Rf.reshape(n, n, 9); out[..., 36:39] = tf
     out[..., 39] = np.linalg.norm(tt, axis=-1).astype(np.float32)
-    for h in range(n):
-        for t in range(n):
-            a, b = from_to_vec_exposure(exposure[h], exposure[t], aff[h], aff[t])
-            out[t, h, 24] = a; out[t, h, 25] = b; out[t, h, 26] = np.float32(aff0[h][1])
+    a, b = from_to_vec_exposure_table(exposure, aff)
+    out[..., 24] = a; out[..., 25] = b
+    out[..., 26] = np.asarray(aff0, np.float32).reshape(n, 2)[None, :, 1]
     return out.reshape(n * n, PRECALC_STRIDE)
 
 
@@ -90,10 +112,8 @@ def adjoints(w2c_eval, aff0, exposure):
     adH[..., 6, 6] = 1; adH[..., 7, 7] = 1
     adT[..., np.arange(8), np.arange(8)] = 1
     adH[..., :6, :6] = -A.transpose(0, 1, 3, 2)
-    for h in range(n):
-        for t in range(n):
-            a, _ = from_to_vec_exposure(exposure[h], exposure[t], aff0[h], aff0[t])
-            adT[t, h, 6, 6] = -a; adH[t, h, 6, 6] = a; adT[t, h, 7, 7] = -1; adH[t, h, 7, 7] = a
+    a, _ = from_to_vec_exposure_table(exposure, aff0)
+    adT[..., 6, 6] = -a; adH[..., 6, 6] = a; adT[..., 7, 7] = -1; adH[..., 7, 7] = a
     adH *= scale[:, None]; adT *= scale[:, None]
     return adH.reshape(n * n, 8, 8), adT.reshape(n * n, 8, 8)
 
