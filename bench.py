@@ -534,8 +534,8 @@ def main():
                          "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-    # (profiles/r1k_frame_full.md: tracker 3.332864 MB + 1.024 KB, traceOn 2.419456 MB, pyramid 1.240320 MB + 0.256 KB)
-    traffic = {"k34_track_eval_kernel": 3333888.0, "k5_trace_kernel": 2419456.0, "k1_pyramid_kernel+k1_wrap_columns_kernel": 1240576.0}
+    # (profiles/r1l_frame_full.md: tracker 3.214592 MB + 0, traceOn 1.262848 MB, pyramid 1.248768 MB)
+    traffic = {"k34_track_eval_kernel": 3214592.0, "k5_trace_kernel": 1262848.0, "k1_pyramid_kernel+k1_wrap_columns_kernel": 1248768.0}
     line = dict(base, value=aggregate_fps(world, steps, t_dev), ms_per_step=1e3 * t_dev / steps,
                 e2e={"value": aggregate_fps(world, steps, t_e2e), "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
                      "d2h_bytes_per_step": d2h / steps},
@@ -548,7 +548,7 @@ def main():
                           "note": "dominant kernel by summed launch time (k34_track_level_kernel: the whole pyramid walk of one "
                                   "frame in one cooperative launch, ~38 LM evaluations); single-sequence launches are "
                                   "latency-bound (L2-resident working set), see DESIGN.md section 4; traffic from "
-                                  "profiles/r1k_frame_full.md; batched-window bandwidth figures: profiles/r1k_notes.md"},
+                                  "profiles/r1l_frame_full.md; batched-window bandwidth figures: roofline_batched_window below and profiles/r1k_notes.md"},
                 kernels=kernels,
                 host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
                 gt_error_m=gt_err, keyframes=kf_tail)
