@@ -10,6 +10,8 @@
 // The warped buffers never exist.  Algorithmic traffic: 16 B point + 4x16 B texels per point.
 #include "ctx.h"
 
+#include <cstdlib>
+
 #include <algorithm>
 #include <atomic>
 #include <cooperative_groups.h>
@@ -208,7 +210,7 @@ namespace cg = cooperative_groups;
 
 // CTAs of the cooperative launch: the grid barrier and the all-CTA fold both grow with the grid, the evaluation
 // itself is a few hundred points per CTA either way
-constexpr int LM_MAX_CTAS = 32;
+constexpr int LM_MAX_CTAS = 64;   // measured on B200 (configs[1]): 32 -> 198.5 us per frame, 48/64/96 -> 192.5 us
 constexpr int LM_THREADS = 128;   // threads per CTA of the device-resident LM kernel (the fold uses its first four warps)
 
 struct LmConst {                // the level being tracked; lives in shared memory, rewritten by thread 0 at each level start
@@ -834,7 +836,9 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
         if (!coop) { c->set_error("device lacks cooperative launch", __FILE__, __LINE__); return -1; }
         LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         LDSO_CUDA_OK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k34_track_level_kernel, LM_THREADS, 0));
-        c->trk_coop_max = std::max(1, std::min(per_sm * sms, LM_MAX_CTAS));
+        int cap = LM_MAX_CTAS;
+        if (const char* e = getenv("LDSO_LM_CTAS")) cap = atoi(e);   // tuning knob
+        c->trk_coop_max = std::max(1, std::min(per_sm * sms, cap));
     }
     int blocks = std::max(1, (nmax + LM_THREADS - 1) / LM_THREADS);   // sized for the finest level; coarser levels leave CTAs idle
     blocks = std::min(blocks, std::min(c->trk_coop_max, c->trk_max_blocks / 2));
