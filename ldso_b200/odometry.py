@@ -103,9 +103,18 @@ class Odometry:
         ids = np.array([f["id"] for f in self.frames], np.int64)
         return np.searchsorted(ids, np.asarray(host_ids, np.int64))
 
+    def _window_stacks(self):
+        """stacked R, t and affine of the window frames, rebuilt only when a frame's pose / affine object changed"""
+        Rs = [f["w2c"][0] for f in self.frames]; ts = [f["w2c"][1] for f in self.frames]; affs = [f["aff"] for f in self.frames]
+        c = getattr(self, "_stack_cache", None)
+        if (c is None or len(c[0]) != len(Rs) or any(a is not b for a, b in zip(c[0], Rs)) or any(a is not b for a, b in zip(c[1], ts))
+                or c[2] != affs):
+            c = self._stack_cache = (Rs, ts, affs, np.stack(Rs), np.stack(ts), np.array(affs, np.float32))   # holds the keyed objects alive
+        return c[3], c[4], c[5]
+
     def rel_to(self, w2c_new):
         """(R, t) of every window frame -> the frame with pose w2c_new, stacked"""
-        Rh = np.stack([f["w2c"][0] for f in self.frames]); th = np.stack([f["w2c"][1] for f in self.frames])
+        Rh, th, _ = self._window_stacks()
         R = w2c_new[0] @ Rh.transpose(0, 2, 1)
         t = w2c_new[1] - np.einsum("nij,nj->ni", R, th)
         return R, t
@@ -115,7 +124,7 @@ class Odometry:
         R, t = self.rel_to(w2c_new)
         KRKi = (self.K @ R.astype(np.float32)) @ self.Ki
         Kt = t.astype(np.float32) @ self.K.T
-        fa = np.array([f["aff"] for f in self.frames], np.float32)
+        fa = self._window_stacks()[2]
         a = np.exp(np.float32(aff_new[0]) - fa[:, 0]).astype(np.float32)          # AffLight::fromToVecExposure, exposures 1
         b = (np.float32(aff_new[1]) - a * fa[:, 1]).astype(np.float32)
         return np.ascontiguousarray(KRKi, np.float32), np.ascontiguousarray(Kt, np.float32), np.stack([a, b], 1)
