@@ -216,7 +216,8 @@ class Odometry:
     def track(self, slot):
         """FullSystem::trackNewCoarse (:218-468): motion hypotheses, first acceptable one wins"""
         ref = self.frames[-1]
-        ids = sorted(self.poses)
+        last = self.n_frames_seen - 2                                         # the two previous frames, normally consecutive ids
+        ids = [last - 1, last] if last in self.poses and last - 1 in self.poses else sorted(self.poses)
         T_ref = ref["w2c"]
         T_last = self.poses[ids[-1]]
         last_rel = wh.se3_mul(T_last, wh.se3_inv(T_ref))                     # lastF_2_slast
@@ -426,8 +427,9 @@ class Odometry:
         w2c = [f["w2c"] for f in self.frames]
         aff = [f["aff"] for f in self.frames]
         calib = (self.c["fx"], self.c["fy"], self.c["cx"], self.c["cy"])
-        precalc = wh.precalc_table(w2c, w2c, calib, aff, aff, [1.0] * n)      # evaluation point = current state (no FEJ)
-        adH, adT = wh.adjoints(w2c, aff, [1.0] * n)
+        pairs, ab = wh._pairs(w2c), wh.from_to_vec_exposure_table([1.0] * n, aff)   # shared by both tables
+        precalc = wh.precalc_table(w2c, w2c, calib, aff, aff, [1.0] * n, pairs=pairs, ab=ab)   # evaluation point = current state (no FEJ)
+        adH, adT = wh.adjoints(w2c, aff, [1.0] * n, pairs=pairs, ab=ab)
         eth = np.array([f.get("eth", 8 * 8 * 8.0) for f in self.frames], np.float32)
         return dict(n=n, precalc=precalc, frame_energy_th=eth, calib=np.array(calib, np.float32), adH=adH, adT=adT,
                     slots=np.array([f["slot"] for f in self.frames], np.int32))

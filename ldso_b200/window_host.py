@@ -76,14 +76,14 @@ def _k_matrices(fx, fy, cx, cy):
     return _K_CACHE[key]
 
 
-def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
+def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure, pairs=None, ab=None):
     """FrameFramePrecalc::Set for every (host, target) pair (src/internal/FrameFramePrecalc.cc:6-35).
     w2c_eval / w2c: lists of (R, t) world-to-camera at the FEJ evaluation point / current state."""
     n = len(w2c)
     fx, fy, cx, cy = [np.float32(c) for c in calib]
     K, Ki = _k_matrices(fx, fy, cx, cy)
-    R, tt = _pairs(w2c)
-    R0, t0 = (R, tt) if w2c_eval is w2c else _pairs(w2c_eval)
+    R, tt = pairs if pairs is not None else _pairs(w2c)                    # pairs / ab: the caller's _pairs(w2c) and
+    R0, t0 = (R, tt) if w2c_eval is w2c else _pairs(w2c_eval)                # from_to_vec_exposure_table(exposure, aff), reused
     R0f, t0f, Rf, tf = R0.astype(np.float32), t0.astype(np.float32), R.astype(np.float32), tt.astype(np.float32)
     KRKi = (K @ Rf @ Ki).astype(np.float32)
     Kt = (K @ tf[..., None])[..., 0].astype(np.float32)
@@ -92,17 +92,17 @@ def precalc_table(w2c_eval, w2c, calib, aff, aff0, exposure):
     out[..., 12:21] = KRKi.reshape(n, n, 9); out[..., 21:24] = Kt
     out[..., 27:36] = Rf.reshape(n, n, 9); out[..., 36:39] = tf
     out[..., 39] = np.linalg.norm(tt, axis=-1).astype(np.float32)
-    a, b = from_to_vec_exposure_table(exposure, aff)
+    a, b = ab if ab is not None else from_to_vec_exposure_table(exposure, aff)
     out[..., 24] = a; out[..., 25] = b
     out[..., 26] = np.asarray(aff0, np.float32).reshape(n, 2)[None, :, 1]
     return out.reshape(n * n, PRECALC_STRIDE)
 
 
-def adjoints(w2c_eval, aff0, exposure):
+def adjoints(w2c_eval, aff0, exposure, pairs=None, ab=None):
     """EnergyFunctional::setAdjointsF (src/internal/OptimizationBackend/EnergyFunctional.cc:551-609)"""
     n = len(w2c_eval)
     scale = np.array([SCALE_XI_TRANS] * 3 + [SCALE_XI_ROT] * 3 + [SCALE_A, SCALE_B])
-    Rl, tl = _pairs(w2c_eval)                                     # [t][h]
+    Rl, tl = pairs if pairs is not None else _pairs(w2c_eval)     # [t][h]
     H = np.zeros((n, n, 3, 3))
     H[..., 0, 1] = -tl[..., 2]; H[..., 0, 2] = tl[..., 1]; H[..., 1, 0] = tl[..., 2]
     H[..., 1, 2] = -tl[..., 0]; H[..., 2, 0] = -tl[..., 1]; H[..., 2, 1] = tl[..., 0]
@@ -112,7 +112,7 @@ def adjoints(w2c_eval, aff0, exposure):
     adH[..., 6, 6] = 1; adH[..., 7, 7] = 1
     adT[..., np.arange(8), np.arange(8)] = 1
     adH[..., :6, :6] = -A.transpose(0, 1, 3, 2)
-    a, _ = from_to_vec_exposure_table(exposure, aff0)
+    a, _ = ab if ab is not None else from_to_vec_exposure_table(exposure, aff0)
     adT[..., 6, 6] = -a; adH[..., 6, 6] = a; adT[..., 7, 7] = -1; adH[..., 7, 7] = a
     adH *= scale[:, None]; adT *= scale[:, None]
     return adH.reshape(n * n, 8, 8), adT.reshape(n * n, 8, 8)
