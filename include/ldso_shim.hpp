@@ -50,6 +50,8 @@ int LDSO_API(immature_set)(LDSO_SHIM_CTX*, int, const int*, const float*, const 
 int LDSO_API(immature_append)(LDSO_SHIM_CTX*, int, int, int, const float*, const float*, int*);
 int LDSO_API(immature_compact)(LDSO_SHIM_CTX*, int, int, int, const int*, int*);
 int LDSO_API(immature_trace)(LDSO_SHIM_CTX*, int, int, const float*, const float*, const float*, int*);
+int LDSO_API(immature_trace_async)(LDSO_SHIM_CTX*, int, int, const float*, const float*, const float*);
+int LDSO_API(immature_trace_counts)(LDSO_SHIM_CTX*, int*);
 int LDSO_API(immature_get)(LDSO_SHIM_CTX*, float*, float*, float*, int*, float*, float*);
 int LDSO_API(immature_activate)(LDSO_SHIM_CTX*, int, const int*, int, float*, int*, int*);
 int LDSO_API(distmap_make)(LDSO_SHIM_CTX*, int, const float*, const float*, int, const int*, const float*, const float*, const float*);
@@ -288,6 +290,12 @@ public:
                  int counts[6]) {
         c.check(LDSO_API(immature_trace)(c.h, frame.slot, nHosts, KRKi, Kt, affine, counts));
     }
+    // the same trace queued without waiting (nothing reads its results before the next keyframe's activatePointsMT; any
+    // other pool call completes it); traceCounts waits if it still runs
+    void traceOnAsync(Context& c, const FrameHessian& frame, int nHosts, const float* KRKi, const float* Kt, const float* affine) {
+        c.check(LDSO_API(immature_trace_async)(c.h, frame.slot, nHosts, KRKi, Kt, affine));
+    }
+    void traceCounts(Context& c, int counts[6]) { c.check(LDSO_API(immature_trace_counts)(c.h, counts)); }
     // deletion of OOB / activated points and of the points of a marginalised host frame
     int remove(Context& c, int dropHostIdx, bool dropOOB, const std::vector<int>& idx) {
         c.check(LDSO_API(immature_compact)(c.h, dropHostIdx, dropOOB ? 1 : 0, (int)idx.size(), idx.data(), &size));
