@@ -61,8 +61,12 @@ def rank_info():
 class ClockSampler:
     """samples nvidia-smi SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
 
-    def __init__(self, dev):
+    def __init__(self, dev, enabled=True):
+        """dev: one index or a comma-separated list (one nvidia-smi process samples them all); enabled=False: a no-op
+        sampler (under torchrun only rank 0 samples — eight ranks forking nvidia-smi ten times a second contend for the
+        driver and the host cores and slowed the very region they were watching)"""
         self.dev = dev
+        self.enabled = enabled
         self.samples = []
         self.stop = False
         self.t = threading.Thread(target=self.run, daemon=True)
@@ -73,19 +77,22 @@ class ClockSampler:
         while not self.stop:
             try:
                 o = subprocess.run(["nvidia-smi", "-i", str(self.dev), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                   capture_output=True, text=True, timeout=5).stdout.strip().split(",")
-                self.samples.append([s.strip() for s in o])
+                                   capture_output=True, text=True, timeout=5).stdout.strip().splitlines()
+                for line in o:
+                    self.samples.append([s.strip() for s in line.split(",")])
             except Exception:
                 pass
             time.sleep(0.1)
 
     def __enter__(self):
-        self.t.start()
+        if self.enabled:
+            self.t.start()
         return self
 
     def __exit__(self, *a):
         self.stop = True
-        self.t.join(timeout=6)
+        if self.enabled:
+            self.t.join(timeout=6)
 
     def summary(self):
         sm = [float(s[0]) for s in self.samples if len(s) >= 6 and s[0].replace(".", "").isdigit()]
@@ -488,7 +495,7 @@ def main():
 
     # three passes over the same sequence, one context alive at a time: device-resident input (value), host input
     # through the C ABI (e2e), and the per-kernel CUDA-event profile (roofline)
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else local_rank, enabled=(rank == 0)) as clk:
         seq = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
         seq.prime()
         barrier()
