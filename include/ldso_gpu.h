@@ -142,6 +142,24 @@ int ldso_gpu_tracker_calc_res(ldso_gpu_ctx* ctx, int tracker, int new_slot, floa
  * H (8x8 row-major) and b already divided by the padded count and scaled (SCALE_XI_TRANS etc). */
 int ldso_gpu_tracker_calc_gs(ldso_gpu_ctx* ctx, int tracker, int lvl, const double ref_to_new[12],
                              float aff_a, float aff_b, double H[64], double b[8]);
+/* ---- allocation-free variant of ldso_gpu_tracker_calc_res -------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same fused K3+K4 kernel and the same
+ * result as ldso_gpu_tracker_calc_res, but the reduction scratch (per-CTA partial sums, arrival counter, result block)
+ * is a file-scope `static __device__ __align__(256)` array of 246 KB inside the library (every GPU that loads the
+ * library holds it until the process exits) instead of the ctx's workspace, and the call allocates nothing: no
+ * cudaMalloc / cudaFree / cudaMallocHost, no allocating library routine.  Inputs are the ctx's resident tracker
+ * reference (ldso_gpu_tracker_set_ref) and frame pyramid `new_slot`, as for ldso_gpu_tracker_calc_res; the tracker's
+ * calc_gs state is NOT touched.  Limit: at most LDSO_NOALLOC_MAX_POINTS points on the level (pc_n[lvl]); more returns -2
+ * with a message in ldso_gpu_last_error.  The ctx's device must be the calling thread's current device.  All calls on a
+ * device share the one array, which keeps the previous call's contents (the call clears what must start at zero):
+ * calls that overlap on the GPU (two ctxs / two streams at once) race — serialise them.
+ * out6 as ldso_gpu_tracker_calc_res; sums52 (may be NULL): the 45 upper-triangle sums of the 9x9 system, E, flowT,
+ * flowRT, then numTermsInE, numSaturated, numTermsInWarped, flowNum. */
+#define LDSO_NOALLOC_MAX_POINTS 131072
+int ldso_gpu_tracker_calc_res_noalloc(ldso_gpu_ctx* ctx, int tracker, int new_slot, float new_exposure, int lvl,
+                                      const double ref_to_new[12], float aff_a, float aff_b, float cutoff_th,
+                                      float out6[6], double sums52[52]);
 /* ---- CoarseTracker::trackNewestCoarse (:61-310): the whole coarse-to-fine LM loop ---------------
  * pose_io / aff_io: initial guess in, result out (only written when the return value is 0).
  * Returns 0 = true, 1 = false (the reference's bool).  last_residuals[5], flow[3] as the public members

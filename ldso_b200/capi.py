@@ -213,6 +213,15 @@ class Ctx:
                    C.c_float(aff_a), C.c_float(aff_b), C.c_float(cutoff), _fp(out))
         return out
 
+    def tracker_calc_res_noalloc(self, trk, new_slot, lvl, pose12, aff_a, aff_b, cutoff, exposure=1.0):
+        """allocation-free variant (scratch in a file-scope device array of the library); returns (out6, sums52)"""
+        pose12 = np.ascontiguousarray(pose12, dtype=np.float64)
+        out = np.empty(6, dtype=np.float32)
+        sums = np.empty(52, dtype=np.float64)
+        self._call("tracker_calc_res_noalloc", C.c_int(trk), C.c_int(new_slot), C.c_float(exposure), C.c_int(lvl), _dp(pose12),
+                   C.c_float(aff_a), C.c_float(aff_b), C.c_float(cutoff), _fp(out), _dp(sums))
+        return out, sums
+
     def tracker_calc_gs(self, trk, lvl, pose12, aff_a, aff_b):
         pose12 = np.ascontiguousarray(pose12, dtype=np.float64)
         H = np.empty((8, 8), dtype=np.float64)

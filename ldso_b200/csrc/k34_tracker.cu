@@ -872,3 +872,109 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
     if (k.dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[24 + i];
     return 0;
 }
+
+// =====================================================================================================
+// Allocation-free variant of the fused K3+K4 evaluation (ldso_gpu_tracker_calc_res_noalloc, include/ldso_gpu.h).
+// No counterpart in the reference: added for callers that must not allocate
+// (CUDA-graph capture, tight serving loops).  The kernel is k34_track_eval_kernel unchanged; its reduction scratch
+// (per-CTA fp32 partials, integer partials, the arrival counter and the 64-double result block) lives in ONE file-scope
+// device array instead of the ctx's cudaMalloc'ed workspace.  Every GPU that loads the library holds the array until
+// the process exits.  All calls on a device share it: calls that overlap on the GPU race.
+#define NOALLOC_MAX_CTAS (LDSO_NOALLOC_MAX_POINTS / TRK_THREADS)
+namespace {
+constexpr size_t NA_OFF_PART = 0;                                                     // float [NOALLOC_MAX_CTAS][TRK_NRED]
+constexpr size_t NA_OFF_PART_I = NA_OFF_PART + sizeof(float) * NOALLOC_MAX_CTAS * TRK_NRED;   // int [NOALLOC_MAX_CTAS][NI]
+constexpr size_t NA_OFF_RESULT = NA_OFF_PART_I + sizeof(int) * NOALLOC_MAX_CTAS * NI;         // double [64]
+constexpr size_t NA_OFF_COUNTER = NA_OFF_RESULT + sizeof(double) * 64;                        // unsigned
+constexpr size_t NA_BYTES = ((NA_OFF_COUNTER + sizeof(unsigned) + 255) / 256) * 256;
+static_assert(NA_OFF_PART_I % 16 == 0 && NA_OFF_RESULT % 16 == 0 && NA_OFF_COUNTER % 4 == 0, "scratch carve-up alignment");
+}  // namespace
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is resolved once
+// per device, with that device current, and cached.
+static int noalloc_scratch(ldso_gpu_ctx* c, unsigned char** out) {
+    constexpr int MAXDEV = 64;
+    static std::atomic<unsigned char*> cache[MAXDEV];
+    int dev = -1;
+    LDSO_CUDA_OK(c, cudaGetDevice(&dev));
+    if (dev != c->cfg.device) { c->set_error("the ctx's device is not the calling thread's current device", __FILE__, __LINE__); return -2; }
+    if (dev < 0 || dev >= MAXDEV) { c->set_error("device ordinal out of range", __FILE__, __LINE__); return -2; }
+    unsigned char* p = cache[dev].load(std::memory_order_acquire);
+    if (!p) {
+        void* sym = nullptr;
+        LDSO_CUDA_OK(c, cudaGetSymbolAddress(&sym, g_noalloc_scratch));
+        if (!sym) { c->set_error("cudaGetSymbolAddress returned a null address", __FILE__, __LINE__); return -1; }
+        p = static_cast<unsigned char*>(sym);
+        cache[dev].store(p, std::memory_order_release);   // two racing first calls resolve the same address
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" int ldso_gpu_tracker_calc_res_noalloc(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, int lvl,
+                                                 const double ref_to_new[12], float aff_a, float aff_b, float cutoff_th,
+                                                 float out6[6], double sums52[52]) {
+    LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels);
+    LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && ref_to_new && out6);
+    const TrackerDev& T = c->trk[tracker];
+    LDSO_REQUIRE(c, T.ref_slot >= 0);
+    const int n = T.pc_n[lvl];
+    if (n > LDSO_NOALLOC_MAX_POINTS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "ldso_gpu_tracker_calc_res_noalloc: %d tracker points exceed LDSO_NOALLOC_MAX_POINTS = %d", n,
+                 LDSO_NOALLOC_MAX_POINTS);
+        c->set_error(msg, __FILE__, __LINE__);
+        return -2;
+    }
+    double res[NF + NI];
+    for (int k = 0; k < NF + NI; k++) res[k] = 0.0;
+    if (n > 0) {
+        unsigned char* base = nullptr;
+        int rc = noalloc_scratch(c, &base);
+        if (rc) return rc;
+        float* partials = reinterpret_cast<float*>(base + NA_OFF_PART);
+        int* partials_i = reinterpret_cast<int*>(base + NA_OFF_PART_I);
+        double* result = reinterpret_cast<double*>(base + NA_OFF_RESULT);
+        unsigned* counter = reinterpret_cast<unsigned*>(base + NA_OFF_COUNTER);
+        // same parameter block as k34_eval (CoarseTracker.cc:546-564, 681-685), without touching the tracker's state
+        TrkParams p;
+        double Rd[9];
+        float Rf[9];
+        ldso_sm::SE3::fromRt(ref_to_new).rotationMatrix(Rd);
+        for (int i = 0; i < 9; i++) Rf[i] = (float)Rd[i];
+        ldso_sm::mat3_mul<float>(Rf, T.Ki[lvl], p.RKi);
+        for (int i = 0; i < 3; i++) p.t[i] = (float)ref_to_new[9 + i];
+        for (int i = 0; i < 9; i++) p.Ki[i] = T.Ki[lvl][i];
+        p.fx = T.fx[lvl]; p.fy = T.fy[lvl]; p.cx = T.cx[lvl]; p.cy = T.cy[lvl];
+        p.w = T.w[lvl]; p.h = T.h[lvl]; p.n = n; p.lvl = lvl;
+        from_to_vec_exposure(T.ref_exposure, new_exposure, T.ref_aff_a, T.ref_aff_b, aff_a, aff_b, &p.aff0, &p.aff1);
+        p.aJ = p.aff0;
+        p.b0 = T.ref_aff_b;
+        p.huberTH = c->cfg.huber_th;
+        p.cutoffTH = cutoff_th;
+        p.maxEnergy = 2 * p.huberTH * cutoff_th - p.huberTH * p.huberTH;
+        const int blocks = (n + TRK_THREADS - 1) / TRK_THREADS;
+        // the array keeps the previous call's contents: the arrival counter and the result block must start at zero
+        LDSO_CUDA_OK(c, cudaMemsetAsync(result, 0, sizeof(double) * 64 + sizeof(unsigned), c->stream));
+        k34_track_eval_kernel<<<blocks, TRK_THREADS, 0, c->stream>>>(T.pc[lvl], c->frame[new_slot] + c->lvl_off[lvl], p, partials,
+                                                                     partials_i, counter, result, 1.0);
+        c->launches++;
+        LDSO_CUDA_OK(c, cudaGetLastError());
+        // read-back through the ctx's pinned 64-double block (allocated in ldso_gpu_create): no allocation here either
+        LDSO_CUDA_OK(c, ldso_copy(c, c->trk_result_pinned, result, sizeof(double) * 64, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        if (c->trk_result_pinned[63] != 1.0) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
+        for (int k = 0; k < NF + NI; k++) res[k] = c->trk_result_pinned[k];
+    }
+    // CoarseTracker.cc:664-672, as fill_vec6 in api.cu
+    const float num = (float)(int)res[NF + 3];
+    out6[0] = (float)res[45];
+    out6[1] = (float)(int)res[NF + 0];
+    out6[2] = (float)((float)res[46] / (num + 0.1));
+    out6[3] = 0;
+    out6[4] = (float)((float)res[47] / (num + 0.1));
+    out6[5] = (float)(double)((int)res[NF + 1] / (float)(int)res[NF + 0]);
+    if (sums52) for (int k = 0; k < NF + NI; k++) sums52[k] = res[k];
+    return 0;
+}
