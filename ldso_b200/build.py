@@ -39,18 +39,32 @@ def _run(cmd):
     return r.stdout + r.stderr
 
 
+def _stale(obj, deps):
+    return not os.path.exists(obj) or any(os.path.getmtime(d) > os.path.getmtime(obj) for d in deps)
+
+
 def build_gpu(force=False, verbose=False):
+    """one object per .cu (compiled in parallel, rebuilt only when the source or a header changed), then one link"""
+    from concurrent.futures import ThreadPoolExecutor
     os.makedirs(LIBDIR, exist_ok=True)
+    objdir = os.path.join(ROOT, "build", "obj")
+    os.makedirs(objdir, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
-    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
-        glob.glob(os.path.join(ROOT, "include", "*.h"))
-    if not force and _newer(GPU_LIB, deps):
-        return GPU_LIB
+    hdrs = glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
+        glob.glob(os.path.join(ROOT, "include", "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.hpp")) + [os.path.abspath(__file__)]
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", GPU_LIB] + srcs
-    out = _run(cmd)
-    if verbose:
-        print(out)
+    objs = [os.path.join(objdir, os.path.basename(s)[:-3] + ".o") for s in srcs]
+    todo = [(s, o) for s, o in zip(srcs, objs) if force or _stale(o, [s] + hdrs)]
+
+    def cc(so):
+        return _run([nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", so[1], so[0]])
+    if todo:
+        with ThreadPoolExecutor(max_workers=min(len(todo), os.cpu_count() or 4)) as ex:
+            outs = list(ex.map(cc, todo))
+        if verbose:
+            print("".join(outs))
+    if todo or not os.path.exists(GPU_LIB) or _stale(GPU_LIB, objs):
+        _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", GPU_LIB] + objs)
     return GPU_LIB
 
 
