@@ -1,12 +1,22 @@
 #!/usr/bin/env python
-"""bench.py — tracked frames/s of the LDSO hot path on B200 (BASELINE.json configs[1]) and its CPU baseline.
+"""bench.py — tracked frames/s of LDSO's per-frame pipeline on B200 and its CPU baseline.
 
-One "step" = one camera frame of the synthetic 640x480 sequence pushed through the hot path that is
-built so far (see WORKLOAD below); contract and JSON keys as in the task statement:
-  value   frames/s with the frame already resident in HBM (device pointer into K1), CUDA-event timed
-  e2e     frames/s through the host-pointer C ABI (pinned staging + H2D inside the timed region, pose read back)
-  roofline   of the dominant kernel (fused calcRes+calcGSSSE), timed live with CUDA events
-  cpu_baseline / --impl reference   the oracle restatement of the reference's CPU path on the host cores
+One "step" = FullSystem::addActiveFrame (reference src/frontend/FullSystem.cc:78-187) on the next camera frame of EVERY
+sequence of the job, through the C++ orchestrator of include/ldso_system.hpp (one C-ABI call per frame,
+ldso_gpu_system_add_active_frame; sequences of a GPU are stepped together by ldso_gpu_batch_add_active_frames):
+makeImages, trackNewCoarse with its motion hypotheses, keyframe decision, traceNewCoarse; on a keyframe
+flagFramesForMarginalization, activatePointsMT, optimize (<= 6 LM iterations of linearizeAll / accumulate / solve /
+resubstitute + the FEJ fix pass), removeOutliers, setCoarseTrackingRef, flagPointsForRemoval + marginalizePointsF (HM, bM),
+makeNewTraces, marginalizeFrame.  Workload = BASELINE.json configs[1] per sequence (640x480, 2000 desired points, 7-keyframe
+window), SEQ_PER_GPU independent sequences per GPU (configs[4]: 64 sequences over 8 GPUs), timed at steady state: window
+full, frames being marginalised.
+
+JSON keys as in the task statement:
+  value        frames/s, images already resident in HBM (device pointers), CUDA-event timed per step, max over ranks
+  e2e          frames/s through the same call with page-locked HOST images (H2D inside the timed region, poses read back)
+  single_sequence   the same two numbers for ONE sequence on the GPU (north_star's single-sequence frame rate)
+  roofline     dominant kernel, live CUDA-event duration; roofline_batched_window: K7-K10 on a 64x window
+  cpu_baseline / --impl reference   the same C++ control flow over the CPU oracle on the host cores
 """
 import argparse
 import json
@@ -21,37 +31,30 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from ldso_b200 import capi, synth  # noqa: E402
+from ldso_b200 import capi, synth, system  # noqa: E402
 
 CALIB = dict(w=640, h=480, fx=384.0, fy=384.0, cx=319.5, cy=239.5)
-N_POINTS = 2000          # setting_desiredPointDensity (preset 0)
-N_IMMATURE = 1500        # setting_desiredImmatureDensity (preset 0)
-WINDOW = 7               # setting_maxFrames (preset 0)
-KF_EVERY = 6             # a keyframe every KF_EVERY frames (the reference decides by optical flow; ~5-10 on this motion)
-BA_ITS = 6               # setting_maxOptIterations
-N_ACTIVATE = 300         # immature points activated per keyframe (~ N_POINTS / WINDOW leave with the oldest frame)
-FIRST_FRAME = 40
-PRE = (WINDOW - 1) * KF_EVERY      # frames rendered before the first stepped frame so that the window is full from the start
-IDENT = np.concatenate([np.eye(3).reshape(-1), np.zeros(3)])
-WORKLOAD = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level pyramid, %d active points, %d-keyframe window. "
-            "Per frame: makeImages (K1), trackNewestCoarse (K3/K4 LM, all levels), traceNewCoarse over the immature pool (K5). "
-            "Every %d-th frame is a keyframe: activation of %d immature points (K6), window BA = linearizeAll + %d x "
-            "(accumulate K8/K9, solve H1, resubstitute K10, linearizeAll K7) + fixLinearization pass, setCoarseTrackingRef "
-            "(K2), PixelSelector::makeMaps (A2) + ImmaturePoint construction (K6) for the new keyframe. Keyframe cadence "
-            "and the window contents (ground-truth poses/depths + noise) are fixed by the harness, not by the reference's "
-            "FullSystem heuristics" % (N_POINTS, WINDOW, KF_EVERY, N_ACTIVATE, BA_ITS))
-WORKLOAD_ODOMETRY = ("configs[1]: synthetic 640x480 sequence (seed 1001+rank), 4-level pyramid, %d desired active points, %d desired "
-                     "immature points per keyframe, %d-keyframe window, closed loop. One step = one frame through the reference's "
-                     "FullSystem::addActiveFrame flow (restated in ldso_b200/odometry.py over the C ABI): makeImages (K1), "
-                     "trackNewCoarse with motion hypotheses (K3/K4 LM), keyframe decision by optical flow, traceNewCoarse (K5); on a "
-                     "keyframe: frame selection for dropping, new residuals, activatePointsMT (K6), optimize = linearizeAll + <= %d x "
-                     "(accumulate K8/K9, solve H1, resubstitute K10, step, linearizeAll K7) + fix pass, removal of OOB/outlier points, "
-                     "setCoarseTrackingRef (K2), makeNewTraces (A2 + K6). Bootstrapped by CoarseInitializer (N1) on the first ~10 frames, "
-                     "before the timed region (the map is therefore up to scale; ATE is Sim(3)-aligned); no marginalisation prior "
-                     "(points / frames leaving the window are dropped)"
-                     % (N_POINTS, N_IMMATURE, WINDOW, BA_ITS))
-# algorithmic bytes per unit
-BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 5000.0}
+STRIDE = 3               # camera speed: every 3rd frame of the synthetic 30 Hz trajectory -> a keyframe every ~8-10 frames
+SEQ_PER_GPU = 8          # BASELINE.json configs[4]: 64 sequences / 8 GPUs
+PRIME = 90               # untimed frames per sequence before warm-up: initializer, window fills to 7, first marginalisations
+DENSITY_MODE = 1         # npoints_counter_mode (include/ldso_system.h): 1 = the window holds ~desiredPointDensity points
+WORKLOAD = ("configs[1] per sequence: synthetic 640x480 sequence (procedural box room, seed 1001+s, every %d-rd frame of the 30 Hz "
+            "trajectory), pinhole, no vignette/gamma, preset 0 / mode 1, setting_pointSelection=0, loop closing off, vision only; "
+            "4-level pyramid (setGlobalCalib's rule), desiredPointDensity 2000, desiredImmatureDensity 1500, 7-keyframe window, "
+            "<= 6 BA iterations. One step = FullSystem::addActiveFrame on the next frame of every sequence (C++ orchestrator "
+            "include/ldso_system.hpp over the C ABI): makeImages, trackNewCoarse (83 motion hypotheses), keyframe decision, "
+            "traceNewCoarse; keyframes: flagFramesForMarginalization, activatePointsMT, optimize (FEJ), removeOutliers, "
+            "setCoarseTrackingRef, flagPointsForRemoval + marginalizePointsF into HM/bM, makeNewTraces, marginalizeFrame. "
+            "Timed at steady state after %d priming frames (CoarseInitializer bootstrap, window full, frames being marginalised). "
+            "EnergyFunctional::nPoints counts the active points (npoints_counter_mode=1, upstream DSO's behaviour; the fork never "
+            "increments it). %d independent sequences per GPU stepped together (configs[4])" % (STRIDE, PRIME, SEQ_PER_GPU))
+BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 128.0, "k6": 512.0,
+                  "k10": 60.0, "k2": 8000.0, "a2": 24.0, "n2": 1.0, "n2sel": 24.0}
+PROF = [("k34_track_level_kernel", 0, "k34", "point evaluations"), ("k5_trace_kernel", 1, "k5", "search steps"),
+        ("k7_linearize_kernel", 2, "k7", "residuals"), ("k8_top_kernel", 3, "k8", "residuals"), ("k9_sc_kernel", 4, "k9", "residuals"),
+        ("k1_pyramid_kernel", 5, "k1", "frames"), ("a2_selector_kernels", 6, "a2", "pixels"), ("k6_activate_kernel", 7, "k6", "candidates"),
+        ("k10_resubstitute_kernel", 8, "k10", "points"), ("k2_coarse_depth_kernels", 9, "k2", "points"),
+        ("n2_distmap_kernels", 10, "n2", "cells"), ("n2_select_kernel", 11, "n2sel", "pool points")]
 
 
 def rank_info():
@@ -59,16 +62,11 @@ def rank_info():
 
 
 class ClockSampler:
-    """samples nvidia-smi SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+    """samples nvidia-smi SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe); one sampler
+    (rank 0) for all GPUs of the job"""
 
     def __init__(self, dev, enabled=True):
-        """dev: one index or a comma-separated list (one nvidia-smi process samples them all); enabled=False: a no-op
-        sampler (under torchrun only rank 0 samples — eight ranks forking nvidia-smi ten times a second contend for the
-        driver and the host cores and slowed the very region they were watching)"""
-        self.dev = dev
-        self.enabled = enabled
-        self.samples = []
-        self.stop = False
+        self.dev, self.enabled, self.samples, self.stop = dev, enabled, [], False
         self.t = threading.Thread(target=self.run, daemon=True)
 
     def run(self):
@@ -103,379 +101,184 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-_SEQ_CACHE = {}
+# ---- synthetic input (rendered before any CUDA context exists: the pool forks) ----------------------------------------
+def _render_chunk(args):
+    seed, lo, hi = args
+    sc = synth.Scene(seed)
+    out = []
+    for k in range(lo, hi):
+        R, t = synth.trajectory(k * STRIDE)
+        out.append((synth.render(sc, CALIB["w"], CALIB["h"], CALIB["fx"], CALIB["fy"], CALIB["cx"], CALIB["cy"], R, t)[0], t))
+    return seed, lo, out
 
 
-def rendered_sequence(seed, n_frames):
-    """the synthetic frames of a seed are rendered once per process and shared by the passes that replay them"""
-    key = seed
-    if key not in _SEQ_CACHE or len(_SEQ_CACHE[key][0]) < n_frames:
-        _SEQ_CACHE[key] = synth.make_sequence(seed, n_frames, start=FIRST_FRAME, **CALIB)
-    f, d, p = _SEQ_CACHE[key]
-    return f[:n_frames], d[:n_frames], p[:n_frames]
+def render_sequences(seeds, n_frames):
+    """{seed: (frames [n] float32 images, ground-truth camera centres [n,3])}"""
+    import multiprocessing as mp
+    chunk = 12
+    jobs = [(s, lo, min(lo + chunk, n_frames)) for s in seeds for lo in range(0, n_frames, chunk)]
+    nproc = max(1, min(len(jobs), (os.cpu_count() or 2)))
+    res = {s: [None] * n_frames for s in seeds}
+    if nproc > 1:
+        with mp.get_context("fork").Pool(nproc) as pool:
+            parts = pool.map(_render_chunk, jobs, chunksize=1)
+    else:
+        parts = [_render_chunk(j) for j in jobs]
+    for seed, lo, out in parts:
+        for i, o in enumerate(out):
+            res[seed][lo + i] = o
+    return {s: ([o[0] for o in v], np.array([o[1] for o in v])) for s, v in res.items()}
 
 
-class Sequence:
-    """Synthetic sequence + the per-frame / per-keyframe driver, written against the prefix-agnostic C ABI binding so
-    the same stepping runs the product (GPU) and, for the CPU baseline only, the oracle.  Frame f of the sequence is
-    synthetic frame FIRST_FRAME + f; frames 0..PRE are the keyframes that fill the window before stepping starts."""
+class Job:
+    """the sequences of one rank: one System each, stepped together through the library's batch runner"""
 
-    KF_SLOTS = WINDOW + 1            # ring of keyframe pyramids (window + the incoming one); 2 more slots for plain frames
+    def __init__(self, api, seeds, data, device=0, threads=None):
+        self.api, self.seeds, self.data = api, list(seeds), data
+        self.sys = [system.System(api, CALIB, gpu_kw=dict(device=device), npoints_counter_mode=DENSITY_MODE) for _ in seeds]
+        self.batch = system.Batch(self.sys, threads)
+        self.ctxs = [s.ctx() for s in self.sys]
+        self.k = 0                                   # next frame index
+        self.kf_frames = [[] for _ in seeds]
+        self.stat_log = []
 
-    def __init__(self, api, seed, n_steps, device=0):
-        from ldso_b200 import window_host as wh
-        self.api, self.wh = api, wh
-        cfg = api.default_config(device=device, affine_opt_mode_a=0.0, affine_opt_mode_b=0.0, n_frame_slots=self.KF_SLOTS + 2,
-                                 **CALIB)
-        self.ctx = api.create(cfg)
-        n_frames = PRE + 1 + n_steps
-        self.frames, self.depths, self.poses = rendered_sequence(seed, n_frames)
-        self.K = np.array([[CALIB["fx"], 0, CALIB["cx"]], [0, CALIB["fy"], CALIB["cy"]], [0, 0, 1]], dtype=np.float32)
-        self.Ki = np.linalg.inv(self.K.astype(np.float64)).astype(np.float32)
-        # everything below is prepared outside the timed region: per-keyframe window descriptions (the stand-in for the
-        # reference's host-side point/residual graph), tracking-reference point sets, per-frame host->frame tables
-        self.kfs = list(range(0, n_frames, KF_EVERY))
-        self.windows, self.ref_points = {}, {}
-        for k in self.kfs:
-            if k < PRE:
-                continue
-            ids = list(range(k - PRE, k + 1, KF_EVERY))
-            rend = [(self.frames[f], self.depths[f], self.poses[f]) for f in ids]
-            W = synth.make_window(rendered=rend, pts_per_frame=N_POINTS // WINDOW, rng_seed=5 + k, **CALIB)
-            W["HM"] = W["HM"] * 1e6; W["bM"] = W["bM"] * 0; W["delta"] = W["delta"] * 0     # frames frozen by the prior
-            W["slots"] = np.array([self.kf_slot(f) for f in ids], dtype=np.int32)
-            W["ids"] = ids
-            self.windows[k] = W
-            self.ref_points[k] = synth.pick_points(self.frames[k], self.depths[k], N_POINTS)
-        self.tables = {}
-        for f in range(PRE, n_frames):
-            k = (f - 1) // KF_EVERY * KF_EVERY if f > PRE else PRE            # newest keyframe before frame f
-            hosts = list(range(k - PRE, k + 1, KF_EVERY))
-            self.tables[f] = (hosts,) + self.host_tables(hosts, f)
-        self.ref_idx = None
-        self.phase = {}
-        self.last_rel = IDENT.copy()
-        self.results = []
-        self.kf_log = []
-        self.first_step = PRE + 1
+    def close(self):
+        self.batch.close()
+        for s in self.sys:
+            s.close()
 
-    def tick(self, name, t0):
-        """host wall-clock per phase (each phase ends with its results on the host), for the breakdown in the JSON line"""
-        t1 = time.perf_counter()
-        self.phase[name] = self.phase.get(name, 0.0) + (t1 - t0)
-        return t1
+    def step(self, ptrs, is_device, sync_after):
+        st = self.batch.step_ptrs(ptrs, is_device, sync_after)
+        for i in range(len(self.sys)):
+            if st[i, system.ST["keyframe"]]:
+                self.kf_frames[i].append(self.k)
+        self.stat_log.append(st[:, [system.ST["window"], system.ST["points"], system.ST["residuals"], system.ST["keyframe"], system.ST["lost"],
+                                    system.ST["tries"]]].copy())
+        self.k += 1
+        return st
 
-    def kf_slot(self, f):
-        return (f // KF_EVERY) % self.KF_SLOTS
+    def prime(self, ptr_of, n):
+        for _ in range(n):
+            self.step([ptr_of(i, self.k) for i in range(len(self.sys))], False, False)
+        for c in self.ctxs:
+            c.sync()
 
-    def slot(self, f):
-        return self.kf_slot(f) if f % KF_EVERY == 0 else self.KF_SLOTS + (f % 2)
-
-    def host_tables(self, hosts, f):
-        """hostToFrame KRKi / Kt / affine per host keyframe (FullSystem.cc:1171-1176), from the ground-truth poses"""
-        Rn, tn = self.poses[f]
-        KRKi, Kt, aff = [], [], []
-        for hf in hosts:
-            Rh, th = self.poses[hf]
-            R = (Rn.T @ Rh).astype(np.float32); t = (Rn.T @ (th - tn)).astype(np.float32)
-            KRKi.append((self.K @ R @ self.Ki).astype(np.float32)); Kt.append((self.K @ t).astype(np.float32)); aff.append([1.0, 0.0])
-        return np.array(KRKi, np.float32), np.array(Kt, np.float32), np.array(aff, np.float32)
-
-    # ---- immature pool (host-managed like the reference's per-frame immaturePoints lists) ----
-    def new_immature(self, f, host_idx):
-        """PixelSelector::makeMaps + ImmaturePoint constructor for keyframe f (FullSystem::makeNewTraces, :1426-1482); the new
-        points join the device-resident pool, only their pixel list visits the host"""
-        sl = self.kf_slot(f)
-        t = time.perf_counter()
-        u, v, typ, self.potential = self.ctx.select_points(sl, N_IMMATURE, potential=getattr(self, "potential", 3), border=5)
-        t = self.tick("KF A2 makeMaps -> point list", t)
-        n_pool = self.ctx.immature_append(sl, host_idx, u, v)
-        t = self.tick("KF K6 ImmaturePoint ctor + append", t)
-        return len(u), n_pool
-
-    def prime(self):
-        """untimed: pyramids of the first WINDOW keyframes, their immature points, the first tracking reference"""
-        z = np.zeros(0, np.float32)
-        self.ctx.immature_set(np.zeros(0, np.int32), z, z, np.zeros((0, 8)), np.zeros((0, 8)), np.zeros((0, 3)), z, z, z, z,
-                              np.zeros(0, np.int32))
-        for hi, f in enumerate(range(0, PRE + 1, KF_EVERY)):
-            self.ctx.make_images(self.kf_slot(f), self.frames[f])
-            self.new_immature(f, hi)
-        self.pending_remove = np.zeros(0, np.int32)
-        self.set_ref(PRE)
-
-    def set_ref(self, f):
-        u, v, idp, hdi = self.ref_points[f]
-        self.ctx.tracker_set_ref(0, self.kf_slot(f), u, v, idp, hdi)
-        self.ref_idx = f
-        self.last_rel = IDENT.copy()
-
-    # ---- per frame ----
-    def step(self, f, dev_ptr=None):
-        """frame f: makeImages, trackNewestCoarse against the current reference, traceNewCoarse; keyframe work if due"""
-        sl = self.slot(f)
-        t = time.perf_counter()
-        if dev_ptr is None:
-            self.ctx.make_images(sl, self.frames[f])
-        else:
-            self.ctx.make_images_dev(sl, dev_ptr)
-        t = self.tick("K1 makeImages", t)
-        r = self.ctx.tracker_track(0, sl, self.last_rel, [0.0, 0.0])
-        t = self.tick("K3/K4 trackNewestCoarse", t)
-        if r["ok"]:
-            self.last_rel = r["pose"]
-        self.results.append((f, self.ref_idx, r["ok"], r["pose"].copy(), r["iters"].copy()))
-        hosts, KRKi, Kt, aff = self.tables[f]
-        counts = self.ctx.immature_trace(sl, KRKi, Kt, aff)
-        t = self.tick("K5 traceNewCoarse", t)
-        if f % KF_EVERY == 0:
-            self.keyframe(f, counts)
-        return r
-
-    def keyframe(self, f, counts):
-        """FullSystem::makeKeyFrame cadence (FullSystem.cc:485-699) with harness-provided window contents"""
-        ctx, W = self.ctx, self.windows[f]
-        t = time.perf_counter()
-        # the pool stays on the device: drop the frame that leaves the window, OOB points (:1279-1284) and the points
-        # activated at the previous keyframe, then read back only what candidate selection branches on
-        ctx.immature_compact(drop_host=0, drop_oob=True, remove=self.pending_remove)
-        P = ctx.immature_get(("status", "idepth_max", "quality"))
-        t = self.tick("KF pool bookkeeping", t)
-        # activatePointsMT -> optimizeImmaturePoint (K6) on the best-traced candidates
-        ctx.window_set_frames(W, W["slots"])
-        good = np.nonzero(np.isfinite(P["idepth_max"]) & ((P["status"] == 0) | (P["status"] == 3) | (P["status"] == 4)) &
-                          (P["quality"] > 3))[0]                       # setting_minTraceQuality
-        cand = good[:N_ACTIVATE].astype(np.int32)
-        n_ok = 0
-        if len(cand):
-            idp, ok, st = ctx.immature_activate(cand, min_obs=1)
-            n_ok = int(ok.sum())
-        self.pending_remove = cand                                     # activated or dropped either way (:1301-1318)
-        t = self.tick("KF K6 activate", t)
-        # window BA: FullSystem::optimize (:844-1007)
-        ctx.window_load(W, W["slots"])
-        t = self.tick("KF window upload", t)
-        idepth = W["idepth"].copy()
-        st, _ = ctx.window_linearize(False)
-        ctx.window_apply_res()
-        t = self.tick("KF K7 linearizeAll", t)
-        e0 = st[0]
-        lam = 1e-1
-        for it in range(BA_ITS):
-            acc = ctx.window_accumulate()
-            t = self.tick("KF K8/K9 accumulate+stitch", t)
-            x = ctx.window_solve(it, lam, acc, W["HM"], W["bM"], W["delta"])
-            t = self.tick("KF H1 solve", t)
-            step = ctx.window_resubstitute(x, lam)
-            idepth = (idepth + step).astype(np.float32)
-            ctx.window_set_idepth(idepth, W["idepth_zero"])
-            ctx.window_set_frames(W, W["slots"])                        # setPrecalcValues after the step
-            t = self.tick("KF K10 resubstitute+step", t)
-            st, _ = ctx.window_linearize(False)
-            ctx.window_apply_res()
-            t = self.tick("KF K7 linearizeAll", t)
-            lam *= 0.25
-        st, eth = ctx.window_linearize(True)
-        ctx.window_apply_res()
-        hdi = ctx.window_point_floats(6)                               # HdiF, maxRelBaseline, centerProjectedTo: what
-        mrb = ctx.window_point_floats(9)                               # flagPointsForRemoval / makeCoarseDepthL0 read
-        cen = ctx.window_residual_floats(3)
-        t = self.tick("KF K7 linearizeAll", t)
-        # setCoarseTrackingRef for the next frames, then new immature points on this keyframe
-        self.set_ref(f)
-        t = self.tick("KF K2 setCoarseTrackingRef", t)
-        n_new, n_pool = self.new_immature(f, WINDOW - 1)
-        self.kf_log.append(dict(frame=f, trace_counts=counts.tolist(), activated=n_ok, candidates=int(len(cand)), e0=float(e0),
-                                e_final=float(st[0]), n_in=int(st[2]), pool=int(n_pool),
-                                residuals=int(len(W["target"])), new_immature=int(n_new)))
-
-    def gt_error(self):
-        """max translation error of the tracked relative poses vs ground truth — proves the timed work is real tracking"""
-        worst = 0.0
-        for (f, ref, ok, pose, _) in self.results:
-            gt = synth.rel_pose(self.poses[ref][0], self.poses[ref][1], self.poses[f][0], self.poses[f][1])
-            worst = max(worst, float(np.abs(pose[9:] - gt[9:]).max()))
-        return worst
+    def steady_state(self, first, last):
+        """window / point / residual statistics of the steps [first, last) and the trajectory error of every sequence"""
+        log = np.stack(self.stat_log[first:last])                          # [step][seq][6]
+        kf = log[:, :, 3] > 0
+        out = {"window_size_min": int(log[:, :, 0].min()), "window_size_max": int(log[:, :, 0].max()),
+               "points_mean": float(log[:, :, 1].mean()), "residuals_at_keyframes_mean": float(log[:, :, 2][kf].mean()) if kf.any() else 0.0,
+               "keyframes_in_timed_region": int(kf.sum()), "keyframes_per_sequence": kf.sum(0).tolist(), "lost": int(log[:, :, 4].max()),
+               "max_tries": int(log[:, :, 5].max())}
+        cnt = [s.counters() for s in self.sys]
+        out["frames_marginalised_total"] = int(sum(c["marg_frames"] for c in cnt))
+        out["points_marginalised_total"] = int(sum(c["marg_points"] for c in cnt))
+        out["residuals_linearised_total"] = int(sum(c["lin_residuals"] for c in cnt))
+        ates = []
+        for s, seed in zip(self.sys, self.seeds):
+            ids, cen, _ = s.centres()
+            gt = self.data[seed][1][ids]
+            ate, scale = system.ate_rmse(cen, gt)
+            ates.append(ate)
+        gt = self.data[self.seeds[0]][1][: self.k]
+        out["ate_rmse_m_max"] = float(max(ates))
+        out["path_m"] = float(np.linalg.norm(np.diff(gt, axis=0), axis=1).sum())
+        out["hm_norm_last_keyframe"] = float(self.sys[0].keyframe_log()["hm_norm"])
+        return out
 
 
-class ClosedLoop:
-    """The default workload: the reference's own per-frame state machine (ldso_b200/odometry.py restates the control flow of
-    FullSystem::addActiveFrame: track, trace, keyframe decision, activation, window BA, frame dropping, new tracking
-    reference, new immature points) on the synthetic sequence, bootstrapped from the ground-truth depth of frame 0.
-    Same interface as Sequence so the timing code is shared."""
-
-    PRIME = 24          # frames after the first one that are run before the warm-up steps (initialisation and the first keyframe fall here)
-
-    def __init__(self, api, seed, n_steps, device=0):
-        from ldso_b200 import odometry
-        self.odometry = odometry
-        self.frames, self.depths, self.poses = rendered_sequence(seed, 1 + self.PRIME + n_steps)
-        self.od = odometry.Odometry(api, CALIB, desired_points=N_POINTS, desired_immature=N_IMMATURE, max_frames=WINDOW,
-                                    ba_iterations=BA_ITS, device=device)
-        self.ctx = self.od.ctx
-        self.first_step = 1 + self.PRIME
-
-    @property
-    def phase(self):
-        return self.od.phase
-
-    @phase.setter
-    def phase(self, v):
-        self.od.phase = v
-
-    @property
-    def kf_log(self):
-        return [l for l in self.od.log if l.get("kf")]
-
-    def prime(self):
-        R0, t0 = self.poses[0]
-        self.od.add_frame(self.frames[0], gt_w2c=(R0.T, -R0.T @ t0))       # no depth given: CoarseInitializer (N1) bootstraps
-        for i in range(1, self.first_step):
-            self.od.add_frame(self.frames[i])
-
-    def step(self, f, dev_ptr=None):
-        return self.od.add_frame(self.frames[f], dev_ptr=dev_ptr)
-
-    def trajectory_error(self):
-        ids = sorted(self.od.poses)
-        est = np.array([-self.od.poses[i][0].T @ self.od.poses[i][1] for i in ids])
-        gt = np.array([self.poses[i][1] for i in ids])
-        ate, scale = self.odometry.ate_rmse(est, gt)
-        return dict(ate_rmse_m=ate, sim3_scale=scale, path_m=float(np.linalg.norm(np.diff(gt, axis=0), axis=1).sum()),
-                    max_abs_m=float(np.abs(est - gt).max()), frames=len(ids), lost=sum(1 for l in self.od.log if l.get("lost")))
-
-    def gt_error(self):
-        return self.trajectory_error()["ate_rmse_m"]      # the map is up to scale: only the Sim(3)-aligned error is meaningful
-
-
-def run_sequence_timed(seq, steps, warmup, use_dev, flush=None, torch=None):
-    """W untimed + K timed steps starting at frame PRE+1.  Returns (per-step seconds, launches, h2d bytes, d2h bytes)
-    of the timed region."""
-    dev_imgs = None
-    if use_dev:
-        dev_imgs = [torch.from_numpy(f).cuda() for f in seq.frames]
-        torch.cuda.synchronize()
-    i = getattr(seq, "first_step", PRE + 1)
+def timed_region(job, ptr_of, is_device, steps, warmup, flush=None):
+    """W untimed + K timed steps.  is_device: per-step CUDA-event intervals on every context's stream (covering its
+    mapping stream), the step takes the longest of them; else host wall clock around the call with every context's streams
+    drained before the clock stops.  Returns (seconds per step, launches, h2d bytes, d2h bytes, first timed step index)."""
+    n = len(job.sys)
     for _ in range(warmup):
-        seq.step(i, dev_imgs[i].data_ptr() if use_dev else None)
-        i += 1
-    seq.ctx.sync()
-    l0 = seq.ctx.launch_count()
-    io0 = seq.ctx.io_bytes()
-    seq.phase = {}
+        job.step([ptr_of(i, job.k) for i in range(n)], is_device, True)
+    first = len(job.stat_log)
+    l0 = sum(c.launch_count() for c in job.ctxs)
+    io0 = [c.io_bytes() for c in job.ctxs]
     times = []
     for _ in range(steps):
         if flush is not None:
-            flush()                      # evict L2 between timed iterations (outside the timed window)
-        if use_dev:
-            seq.ctx.timer_start()
-            seq.step(i, dev_imgs[i].data_ptr())
-            times.append(seq.ctx.timer_stop() * 1e-3)
+            flush()                                  # evict L2 between timed steps (outside the timed window)
+        ptrs = [ptr_of(i, job.k) for i in range(n)]
+        if is_device:
+            for c in job.ctxs:
+                c.timer_start()
+            job.step(ptrs, True, False)
+            times.append(max(c.timer_stop() for c in job.ctxs) * 1e-3)
         else:
             t0 = time.perf_counter()
-            seq.step(i, None)            # returns after every result of the frame has been read back to the host
+            job.step(ptrs, False, True)              # returns after every sequence's frame is done and its streams are drained
             times.append(time.perf_counter() - t0)
-        i += 1
-    io1 = seq.ctx.io_bytes()
-    return times, seq.ctx.launch_count() - l0, io1[0] - io0[0], io1[1] - io0[1]
+    io1 = [c.io_bytes() for c in job.ctxs]
+    return (times, sum(c.launch_count() for c in job.ctxs) - l0, sum(b[0] - a[0] for a, b in zip(io0, io1)),
+            sum(b[1] - a[1] for a, b in zip(io0, io1)), first)
 
 
-def rank_seed(rank):
-    """sequence s goes to GPU s mod G; one sequence per rank here"""
-    return 1001 + rank
-
-
-def max_over_ranks(vals, world, dist, torch, device):
-    """the timed region of a multi-rank run is the slowest rank's (no data-path collective: this is the only exchange)"""
-    if world <= 1:
-        return list(vals)
-    tt = torch.tensor(list(vals), dtype=torch.float64, device=device)
-    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    return tt.tolist()
-
-
-def aggregate_fps(world, steps, t_max):
-    """whole-job throughput: every rank processed `steps` frames of its own sequence in at most t_max seconds"""
-    return world * steps / t_max
-
-
-def cpu_run(WL, steps, warmup, seed, fast=True):
-    """The oracle restatement of the reference CPU path on this box's host cores (bench's cpu_baseline / reference
-    arm).  Tracking and tracing are single-threaded in the reference; linearizeAll, the Hessian accumulation and point
-    activation use its 6 worker threads (IndexThreadReduce, NUM_THREADS = 6), so both 6 and 1 oracle threads are tried
-    on a short sample and the faster setting is timed.  Returns (sequence, per-step seconds, threads, note)."""
+def cpu_arm(seeds, data, steps, warmup, threads_total):
+    """the same control flow over the CPU oracle (kind "port": the reference itself cannot be compiled here) on the host
+    cores: one worker thread per sequence, the oracle's OpenMP workers inside each (the reference's IndexThreadReduce
+    uses NUM_THREADS = 6) as far as the cores go"""
     from ldso_b200 import build
     os.environ.setdefault("OMP_WAIT_POLICY", "passive")
-    build.build_oracle()
-    api = capi.Api(build.ORACLE_FAST_LIB if fast else build.ORACLE_LIB, "orc_")
-    probe = {}
-    cand = [6, 1] if (os.cpu_count() or 1) >= 7 else [1]
-    for t in cand:
-        os.environ["ORC_THREADS"] = str(t)
-        pn = 30 if WL is ClosedLoop else KF_EVERY
-        seq = WL(api, seed, 2 * pn)
-        seq.prime()
-        probe[t] = sum(run_sequence_timed(seq, pn, pn, use_dev=False)[0]) / pn
-        seq.ctx.close()
-    best = min(probe, key=probe.get)
-    os.environ["ORC_THREADS"] = str(best)
-    seq = WL(api, seed, warmup + steps)
-    seq.prime()
-    times = run_sequence_timed(seq, steps, warmup, use_dev=False)[0]
-    note = "oracle worker threads tried on a short sample: %s" % ", ".join("%d -> %.1f ms/frame" % (t, 1e3 * v) for t, v in probe.items())
-    return seq, times, best, note
-
-
-PROF = [("k34_track_eval_kernel", 0, "k34", "points"), ("k5_trace_kernel", 1, "k5", "search steps"),
-        ("k7_linearize_kernel", 2, "k7", "residuals"), ("k8_top_kernel", 3, "k8", "residuals"),
-        ("k9_sc_kernel", 4, "k9", "residuals"), ("k1_pyramid_kernel+k1_wrap_columns_kernel", 5, "k1", "frames")]
-BYTES_PER_UNIT["k5"] = 128.0
+    lib, march = build.build_oracle_native()
+    n = len(seeds)
+    workers = max(1, min(n, threads_total))
+    inner = max(1, min(6, threads_total // workers))
+    os.environ["ORC_THREADS"] = str(inner)
+    api = capi.Api(lib, "orc_")
+    job = Job(api, seeds, data, threads=workers)
+    frames = {s: [np.ascontiguousarray(f, np.float32) for f in data[s][0]] for s in seeds}
+    ptr_of = lambda i, k: frames[seeds[i]][k].ctypes.data
+    job.prime(ptr_of, PRIME)
+    times, _, _, _, first = timed_region(job, ptr_of, False, steps, warmup)
+    st = job.steady_state(first, first + steps)
+    job.close()
+    return times, st, workers, inner, march
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=None, help="timed frames (default 120 closed loop / 42 cadence)")
-    ap.add_argument("--warmup", type=int, default=None, help="untimed frames before them (default 30 / 6)")
-    ap.add_argument("--workload", default="odometry", choices=["odometry", "cadence"],
-                    help="odometry: closed loop through the reference's per-frame flow (default); cadence: fixed keyframe every "
-                         "6 frames on harness-built windows (heavier mapping load)")
+    ap.add_argument("--steps", type=int, default=40, help="timed steps (one frame of every sequence each)")
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--sequences-per-gpu", type=int, default=SEQ_PER_GPU)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-window-roofline", action="store_true", help="skip the live 64x batched-window kernel timing (roofline_batched_window)")
-    ap.add_argument("--cpu-steps", type=int, default=None, help="frames of the bounded cpu_baseline sample (default 90 / 18)")
+    ap.add_argument("--no-window-roofline", action="store_true", help="skip the live 64x batched-window kernel timing")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-steps", type=int, default=20, help="steps of the bounded cpu_baseline sample")
     args = ap.parse_args()
     rank, local_rank, world = rank_info()
-    odo = args.workload == "odometry"
-    WL = ClosedLoop if odo else Sequence
-    steps = args.steps if args.steps is not None else (120 if odo else 42)
-    warmup = max(args.warmup if args.warmup is not None else (30 if odo else 6), 0)
-    cpu_steps = args.cpu_steps if args.cpu_steps is not None else (90 if odo else 18)
-    cpu_warm = 30 if odo else KF_EVERY
+    steps, warmup, S = args.steps, max(args.warmup, 3), args.sequences_per_gpu
+    n_frames = PRIME + warmup + steps + 1
     base = {"metric": "tracked frames/s (whole job, all sequences)", "unit": "frames/s", "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic (procedural box room, seeded, uint8-quantised)",
-            "config": {"workload": WORKLOAD_ODOMETRY if odo else WORKLOAD, "sequences": args.gpus, "parallelism": "independent sequences, no collective",
-                       "l2": "flushed with a 256 MiB write between timed steps"}}
+            "config": {"workload": WORKLOAD, "sequences": S * args.gpus, "sequences_per_gpu": S,
+                       "parallelism": "independent sequences, no collective"}}
 
     if args.impl == "reference":
+        # the reference's CPU path (oracle port) on the same config: ALL sequences of the job on this box's host cores
         if rank != 0:
             return
-        seq, times, threads, note = cpu_run(WL, steps, warmup, 1001)
-        fps = steps / sum(times)
-        line = dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps, n_gpus=args.gpus,
-                    cpu_baseline={"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
-                                  "sample": "%d frames (%d keyframes) of the same sequence, oracle restatement (-O3 "
-                                            "-march=x86-64-v3 -fopenmp); %s; host has %d cores"
-                                            % (steps, sum(1 for k in seq.kf_log if k["frame"] >= seq.first_step + warmup), note, os.cpu_count())},
-                    e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                    host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq.phase.items()},
-                    gt_error_m=seq.gt_error(), keyframes=seq.kf_log[-2:])
-        if odo:
-            line["trajectory"] = seq.trajectory_error()
-        line["config"] = dict(base["config"], l2="n/a (CPU)")
-        print(json.dumps(line))
+        seeds = [1001 + i for i in range(S * args.gpus)]
+        data = render_sequences(seeds, n_frames)
+        cores = os.cpu_count() or 1
+        times, st, workers, inner, march = cpu_arm(seeds, data, steps, warmup, cores)
+        fps = len(seeds) * steps / sum(times)
+        print(json.dumps(dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps,
+                              cpu_baseline={"value": fps, "unit": "frames/s", "cores": workers * inner, "kind": "port",
+                                            "sample": "%d steps x %d sequences after %d priming + %d warm-up frames each; oracle restatement "
+                                                      "(g++ -O3 -march=%s -fopenmp, logging compiled out), %d sequence workers x %d "
+                                                      "OpenMP threads on a %d-core host" % (steps, len(seeds), PRIME, warmup, march, workers, inner, cores)},
+                              e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                              steady_state=st)))
         return
 
+    seeds = [1001 + rank * S + i for i in range(S)]
+    data = render_sequences(seeds, n_frames)                 # before CUDA is initialised in this process
     import torch
     import torch.distributed as dist
     if world > 1:
@@ -493,35 +296,55 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # three passes over the same sequence, one context alive at a time: device-resident input (value), host input
-    # through the C ABI (e2e), and the per-kernel CUDA-event profile (roofline)
-    with ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else local_rank, enabled=(rank == 0)) as clk:
-        seq = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
-        seq.prime()
-        barrier()
-        times, launches, _, _ = run_sequence_timed(seq, steps, warmup, use_dev=True, flush=flush, torch=torch)
-        barrier()
-        gt_err, kf_tail = seq.gt_error(), seq.kf_log[-2:]
-        traj = seq.trajectory_error() if odo else None
-        seq.ctx.close()
-        seq_e2e = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
-        # e2e inputs come from page-locked host memory (the library DMAs straight out of a pinned caller buffer and
-        # stages a pageable one through its own pinned copy)
-        pinned = [torch.from_numpy(f).pin_memory() for f in seq_e2e.frames]
-        seq_e2e.frames = [t.numpy() for t in pinned]
-        seq_e2e.prime()
-        barrier()
-        times_e2e, _, h2d, d2h = run_sequence_timed(seq_e2e, steps, warmup, use_dev=False, flush=flush)
-        barrier()
-        seq_e2e.ctx.close()
-    t_dev, t_e2e = max_over_ranks([sum(times), sum(times_e2e)], world, dist, torch, "cuda")
+    pinned = {s: [torch.from_numpy(np.ascontiguousarray(f, np.float32)).pin_memory() for f in data[s][0]] for s in seeds}
+    dev = {s: [t.cuda() for t in pinned[s]] for s in seeds}
+    torch.cuda.synchronize()
+    host_ptr = lambda sd: (lambda i, k: pinned[sd[i]][k].data_ptr())
+    dev_ptr = lambda sd: (lambda i, k: dev[sd[i]][k].data_ptr())
 
-    seq_p = WL(gpu, rank_seed(rank), warmup + steps, device=local_rank)
-    seq_p.prime()
-    seq_p.ctx.sync()
-    seq_p.ctx.profile_enable(True)
-    run_sequence_timed(seq_p, steps, 0, use_dev=False, flush=flush)
-    prof = {name: seq_p.ctx.profile_get(which) + (key, unit) for (name, which, key, unit) in PROF}
+    def run_pass(sd, is_device):
+        job = Job(gpu, sd, data, device=local_rank)
+        job.prime(host_ptr(sd), PRIME)
+        barrier()
+        r = timed_region(job, dev_ptr(sd) if is_device else host_ptr(sd), is_device, steps, warmup, flush)
+        barrier()
+        st = job.steady_state(r[4], r[4] + steps)
+        phases = [s.phase_seconds() for s in job.sys]
+        job.close()
+        return r, st, phases
+
+    with ClockSampler(",".join(str(i) for i in range(world)) if world > 1 else local_rank, enabled=(rank == 0)) as clk:
+        (t_dev, launches, _, _, _), st_dev, _ = run_pass(seeds, True)
+        (t_e2e, _, h2d, d2h, _), st_e2e, _ = run_pass(seeds, False)
+    single = None
+    if args.gpus == 1:
+        (t1d, l1, _, _, _), st1, _ = run_pass(seeds[:1], True)
+        (t1e, _, h1, d1, _), _, ph1 = run_pass(seeds[:1], False)
+        single = {"value": steps / sum(t1d), "ms_per_frame": 1e3 * sum(t1d) / steps,
+                  "e2e": {"value": steps / sum(t1e), "ms_per_frame": 1e3 * sum(t1e) / steps, "h2d_bytes_per_step": h1 / steps,
+                          "d2h_bytes_per_step": d1 / steps},
+                  "gpu_launches": int(l1), "keyframes_in_timed_region": st1["keyframes_in_timed_region"],
+                  "host_phase_seconds_whole_run": ph1[0]}
+    # max over ranks of the timed region; per-rank figures travel to rank 0 for the log
+    mine = {"rank": rank, "ms_per_step": 1e3 * sum(t_dev) / steps, "ms_per_step_e2e": 1e3 * sum(t_e2e) / steps, "steady_state": st_dev}
+    if world > 1:
+        tt = torch.tensor([sum(t_dev), sum(t_e2e)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        T_dev, T_e2e = tt.tolist()
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
+    else:
+        T_dev, T_e2e, per_rank = sum(t_dev), sum(t_e2e), [mine]
+
+    # per-kernel CUDA-event profile: one sequence, steady state (separate pass, not a timed number)
+    job = Job(gpu, seeds[:1], data, device=local_rank)
+    job.prime(host_ptr(seeds[:1]), PRIME + warmup)
+    job.ctxs[0].profile_enable(True)
+    for _ in range(steps):
+        job.step([host_ptr(seeds[:1])(0, job.k)], False, True)
+    prof = {name: job.ctxs[0].profile_get(which) + (key, unit) for (name, which, key, unit) in PROF}
+    prof_kf = sum(1 for f in job.kf_frames[0] if f >= PRIME + warmup)
+    job.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -537,32 +360,25 @@ def main():
         if n == 0:
             continue
         gbs = units * BYTES_PER_UNIT[key] / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
-        kernels[name] = {"launches": int(n), "total_ms": ms, "avg_us": 1e3 * ms / n, "units_per_launch": units / n, "unit": unit,
-                         "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
+        kernels[name] = {"launches": int(n), "total_ms": ms, "ms_per_frame": ms / steps, "avg_us": 1e3 * ms / n, "units_per_launch": units / n,
+                         "unit": unit, "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-    # (profiles/r1l_frame_full.md: tracker 3.214592 MB + 0, traceOn 1.262848 MB, pyramid 1.248768 MB)
-    traffic = {"k34_track_eval_kernel": 3214592.0, "k5_trace_kernel": 1262848.0, "k1_pyramid_kernel+k1_wrap_columns_kernel": 1248768.0}
-    line = dict(base, value=aggregate_fps(world, steps, t_dev), ms_per_step=1e3 * t_dev / steps,
-                e2e={"value": aggregate_fps(world, steps, t_e2e), "unit": "frames/s", "h2d_bytes_per_step": h2d / steps,
-                     "d2h_bytes_per_step": d2h / steps},
-                gpu_launches=int(launches),
-                clocks=clk.summary(),
+    total_frames = S * world * steps
+    line = dict(base, value=total_frames / T_dev, ms_per_step=1e3 * T_dev / steps,
+                e2e={"value": total_frames / T_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps, "d2h_bytes_per_step": d2h / steps},
+                gpu_launches=int(launches), clocks=clk.summary(),
+                timing="CUDA events on every context's tracking stream (closing over its mapping stream) per step, longest context = the "
+                       "step, max over ranks; L2 flushed with a 256 MiB write between timed steps; e2e: host wall clock around the batch "
+                       "call, page-locked host images, every context's streams drained inside the window",
                 roofline={"bound": "hbm", "kernel": top, "achieved": kernels[top]["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                          "frac": kernels[top]["frac"], "traffic": traffic.get(top), "peak_source": "measured" if peaks else "fallback",
+                          "frac": kernels[top]["frac"], "traffic": None, "peak_source": "measured" if peaks else "fallback",
                           "launches": kernels[top]["launches"], "avg_us": kernels[top]["avg_us"],
                           "units_per_launch": kernels[top]["units_per_launch"],
-                          "note": "dominant kernel by summed launch time (k34_track_level_kernel: the whole pyramid walk of one "
-                                  "frame in one cooperative launch, ~38 LM evaluations); single-sequence launches are "
-                                  "latency-bound (L2-resident working set), see DESIGN.md section 4; traffic from "
-                                  "profiles/r1l_frame_full.md; batched-window bandwidth figures: roofline_batched_window below and profiles/r1k_notes.md"},
-                kernels=kernels,
-                host_phase_ms_per_step={k: 1e3 * v / steps for k, v in seq_e2e.phase.items()},
-                gt_error_m=gt_err, keyframes=kf_tail)
+                          "note": "dominant kernel by summed launch time over %d steady-state frames of one sequence (%d keyframes); "
+                                  "single-sequence launches are latency-bound (L2-resident working set, DESIGN.md section 4); "
+                                  "bandwidth-bound figures: roofline_batched_window" % (steps, prof_kf)},
+                kernels=kernels, steady_state=st_dev, steady_state_e2e=st_e2e, per_rank=per_rank, single_sequence=single)
     if args.gpus == 1 and not args.no_window_roofline:
-        # the accumulation kernels at a size where bandwidth, not launch latency, bounds them (hard part 1):
-        # the frozen configs[1] window replicated x64 (the residual population of 64 sequences, configs[4]) through
-        # K7/K8/K9/K10 as one launch each, CUDA-event timed after an L2 flush — measured live, outside the timed region
         sys.path.insert(0, os.path.join(ROOT, "profiles"))
         import kernel_bench
         rows = kernel_bench.measure(gpu, [64], 3, peak)
@@ -571,18 +387,15 @@ def main():
             "peak": peak, "unit": "GB/s",
             "kernels": {r["kernel"]: {"avg_us": r["avg_us"], "bytes_per_unit": r["bytes_per_unit"], "units_per_launch": r["units_per_launch"],
                                       "achieved": r["achieved_gbs"], "frac": r["frac"]} for r in rows}}
-    if odo:
-        line["trajectory"] = traj
-        line["keyframes_in_timed_region"] = sum(1 for k in seq_e2e.kf_log if k["frame"] >= seq_e2e.first_step + warmup)
-    if args.gpus == 1:
-        cseq, ctimes, cthreads, cnote = cpu_run(WL, min(cpu_steps, steps), cpu_warm, 1001)
-        n = len(ctimes)
-        line["cpu_baseline"] = {"value": n / sum(ctimes), "unit": "frames/s", "cores": cthreads, "kind": "port",
-                                "sample": "%d frames (%d keyframes) of the same sequence and workload through the oracle (g++ -O3 "
-                                          "-march=x86-64-v3 -fopenmp); %s; host has %d cores"
-                                          % (n, sum(1 for k in cseq.kf_log if k["frame"] >= cseq.first_step + cpu_warm), cnote, os.cpu_count())}
-        if odo:
-            line["cpu_baseline"]["trajectory"] = cseq.trajectory_error()
+    if args.gpus == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        cs = min(args.cpu_steps, steps)
+        ctimes, cst, workers, inner, march = cpu_arm(seeds, data, cs, warmup, cores)
+        line["cpu_baseline"] = {"value": S * cs / sum(ctimes), "unit": "frames/s", "cores": workers * inner, "kind": "port",
+                                "sample": "%d steps x %d sequences (the same sequences and frames) after %d priming + %d warm-up frames each "
+                                          "through the oracle (g++ -O3 -march=%s -fopenmp), %d sequence workers x %d OpenMP threads "
+                                          "on a %d-core host" % (cs, S, PRIME, warmup, march, workers, inner, cores),
+                                "steady_state": cst}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -81,6 +81,9 @@ const char* ldso_gpu_last_error(const ldso_gpu_ctx* ctx);
 int ldso_gpu_pyr_levels(const ldso_gpu_ctx* ctx);                     /* pyrLevelsUsed */
 int ldso_gpu_level_size(const ldso_gpu_ctx* ctx, int lvl, int* w, int* h); /* wG[lvl], hG[lvl] */
 int ldso_gpu_sync(ldso_gpu_ctx* ctx);                                 /* drain the ctx's streams */
+/* makes the ctx's CUDA device the calling thread's current device (cudaSetDevice(cfg.device)): call once from every host
+ * thread that is going to use the ctx (the reference's tracking and mapping threads, a batch worker) */
+int ldso_gpu_bind_thread(ldso_gpu_ctx* ctx);
 /* number of kernel launches issued through this ctx since creation (bench.py "gpu_launches") */
 long long ldso_gpu_launch_count(const ldso_gpu_ctx* ctx);
 /* bytes copied host->device / device->host by the entry points of this ctx since creation (bench.py "e2e") */

@@ -70,7 +70,8 @@ def build_gpu(force=False, verbose=False):
 
 def build_oracle(force=False):
     srcs = sorted(glob.glob(os.path.join(ORACLE_DIR, "*.cpp")))
-    deps = srcs + glob.glob(os.path.join(ORACLE_DIR, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    deps = srcs + glob.glob(os.path.join(ORACLE_DIR, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h")) + \
+        glob.glob(os.path.join(ROOT, "include", "*.hpp"))
     common = ["g++", "-std=c++17", "-O3", "-march=x86-64-v3", "-DENABLE_SSE", "-fPIC", "-shared", "-pthread",
               "-Wall", "-Wno-unused-function", "-Wno-unused-variable", "-Wno-unknown-pragmas"]
     if force or not _newer(ORACLE_LIB, deps):
@@ -78,6 +79,37 @@ def build_oracle(force=False):
     if force or not _newer(ORACLE_FAST_LIB, deps):
         _run(common + ["-fopenmp", "-o", ORACLE_FAST_LIB] + srcs)   # timing build: contraction + worker threads (ORC_THREADS)
     return ORACLE_LIB
+
+
+def build_oracle_native():
+    """the timed CPU baseline built ON the machine that runs it: -O3 -march=native -fopenmp.  The
+    library under oracle/_native/ carries a stamp of the CPU it was compiled for and is rebuilt when that differs; if the
+    compiler fails the portable x86-64-v3 build is returned."""
+    import hashlib
+    from concurrent.futures import ThreadPoolExecutor
+    build_oracle()
+    try:
+        cpu = [l for l in open("/proc/cpuinfo") if l.startswith(("model name", "flags"))][:2]
+    except OSError:
+        cpu = []
+    srcs = sorted(glob.glob(os.path.join(ORACLE_DIR, "*.cpp")))
+    deps = srcs + glob.glob(os.path.join(ORACLE_DIR, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h*"))
+    stamp = hashlib.sha1(("".join(cpu) + "".join(open(d).read() for d in deps)).encode()).hexdigest()
+    out_dir = os.path.join(ORACLE_DIR, "_native")
+    lib, stamp_file = os.path.join(out_dir, "liboracle_fast.so"), os.path.join(out_dir, "stamp")
+    if os.path.exists(lib) and os.path.exists(stamp_file) and open(stamp_file).read() == stamp:
+        return lib, "native"
+    os.makedirs(out_dir, exist_ok=True)
+    flags = ["g++", "-std=c++17", "-O3", "-march=native", "-DENABLE_SSE", "-fPIC", "-pthread", "-fopenmp", "-w"]
+    try:
+        objs = [os.path.join(out_dir, os.path.basename(s)[:-4] + ".o") for s in srcs]
+        with ThreadPoolExecutor(max_workers=len(srcs)) as ex:
+            list(ex.map(lambda so: _run(flags + ["-c", "-o", so[1], so[0]]), zip(srcs, objs)))
+        _run(["g++", "-shared", "-fopenmp", "-pthread", "-o", lib] + objs)
+        open(stamp_file, "w").write(stamp)
+        return lib, "native"
+    except Exception:
+        return ORACLE_FAST_LIB, "x86-64-v3"
 
 
 def build_all(force=False, verbose=False):

@@ -162,6 +162,10 @@ extern "C" int ldso_gpu_sync(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream_map));
     return 0;
 }
+extern "C" int ldso_gpu_bind_thread(ldso_gpu_ctx* c) {
+    LDSO_CUDA_OK(c, cudaSetDevice(c->cfg.device));
+    return 0;
+}
 extern "C" long long ldso_gpu_launch_count(const ldso_gpu_ctx* c) { return c->launches; }
 
 extern "C" int ldso_gpu_io_bytes(ldso_gpu_ctx* c, long long* h2d, long long* d2h) {
@@ -173,6 +177,10 @@ extern "C" int ldso_gpu_timer_start(ldso_gpu_ctx* c) {
     return 0;
 }
 extern "C" int ldso_gpu_timer_stop(ldso_gpu_ctx* c, float* ms) {
+    // the window closes over BOTH streams: work queued on the mapping stream (the asynchronous traceNewCoarse) is part of
+    // the frame, so the tracking stream waits for it before the stop event is recorded
+    LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream_map));
+    LDSO_CUDA_OK(c, cudaStreamWaitEvent(c->stream, c->ev_h2d, 0));
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev1, c->stream));
     LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev1));
     LDSO_CUDA_OK(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));

@@ -89,6 +89,7 @@ extern "C" int orc_level_size(const orc_ctx* c, int lvl, int* w, int* h) {
     return 0;
 }
 extern "C" int orc_sync(orc_ctx*) { return 0; }
+extern "C" int orc_bind_thread(orc_ctx*) { return 0; }   // no device on the CPU
 extern "C" long long orc_launch_count(const orc_ctx*) { return 0; }
 extern "C" int orc_set_gamma(orc_ctx* c, const float B[256]) { memcpy(c->B, B, sizeof(float) * 256); return 0; }
 

@@ -2,6 +2,7 @@
 // CPU restatement of PixelSelector (src/frontend/PixelSelector2.cc): constructor (:9-19), computeHistQuantil
 // (:28-35), makeHists (:36-109), makeMaps (:111-169), select (:171-316).
 // Decision recorded in SURVEY.md trap T3: ths / thsSmoothed are zero-filled at allocation.
+#include <mutex>
 #include "orc_common.h"
 
 #include <algorithm>
@@ -23,8 +24,13 @@ Selector& sel_of(orc_ctx* c) {
     std::shared_ptr<Selector> s = std::make_shared<Selector>();
     int w = c->wG[0], h = c->hG[0];
     s->randomPattern.resize((size_t)w * h);
-    std::srand(3141592);
-    for (int i = 0; i < w * h; i++) s->randomPattern[i] = rand() & 0xFF;
+    {   // the reference draws from the process-global libc generator (PixelSelector2.cc:11-13); contexts created from
+        // several threads must not interleave their draws
+        static std::mutex rand_mu;
+        std::lock_guard<std::mutex> lk(rand_mu);
+        std::srand(3141592);
+        for (int i = 0; i < w * h; i++) s->randomPattern[i] = rand() & 0xFF;
+    }
     s->ths.assign((size_t)(w / 32 + 1) * (h / 32 + 1) + 100, 0.f);
     s->thsSmoothed.assign((size_t)(w / 32 + 1) * (h / 32 + 1) + 100, 0.f);
     c->selector = s;

@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def declared_symbols():
-    src = open(os.path.join(ROOT, "include", "ldso_gpu.h")).read()
+    src = open(os.path.join(ROOT, "include", "ldso_gpu.h")).read() + open(os.path.join(ROOT, "include", "ldso_system.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(ldso_gpu_[a-z0-9_]+)\s*\(", src)))
 
