@@ -64,8 +64,9 @@ typedef struct ldso_gpu_config {
     float frame_energy_th_fac_median; /* 1.5 */
     float frame_energy_th_const_weight; /* 0.5 */
     int tracker_solve_mode;         /* 0 = FULL_SYM (upstream DSO), 1 = FORK_LOWER_ONLY */
-    int tracker_lm_mode;            /* 0 = LM loop of each pyramid level resident on the device (one cooperative launch per
-                                     * level), 1 = host-driven loop, one launch + read-back per evaluation */
+    int tracker_lm_mode;            /* 0 = the whole coarse-to-fine LM loop resident on the device on ONE thread-block cluster
+                                     * (DSMEM fold + cluster barrier, ordinary launch), 1 = host-driven loop, one launch +
+                                     * read-back per evaluation, 2 = device-resident on a cooperative grid (grid barrier) */
     int reserved[7];
 } ldso_gpu_config;
 

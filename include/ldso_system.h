@@ -93,8 +93,11 @@ int ldso_gpu_system_add_active_frame(ldso_gpu_system* sys, const float* image, i
                                      float exposure_time, double pose_out[12], int* status_out);
 
 /* Frame::getPose of every frame with a valid pose, in frame order: ids[n], poses[n][12] (worldToCam, keyframes carry their
- * optimised pose), is_kf[n].  Returns the number of frames written (at most max_n). */
-int ldso_gpu_system_get_trajectory(ldso_gpu_system* sys, int max_n, int* ids, double* poses, int* is_kf);
+ * optimised pose), is_kf[n].  The reference's printResult (src/frontend/FullSystem.cc:2259-2288) writes the keyframes only;
+ * a non-keyframe keeps the pose it was tracked at (relative_to_ref = 0) or, with relative_to_ref != 0, follows its
+ * tracking reference: camToTrackingRef composed with the reference keyframe's current pose (upstream DSO's
+ * FrameShell::trackingRef output).  Returns the number of frames written (at most max_n). */
+int ldso_gpu_system_get_trajectory(ldso_gpu_system* sys, int max_n, int* ids, double* poses, int* is_kf, int relative_to_ref);
 /* ids (Frame::id) of the keyframes in the window */
 int ldso_gpu_system_get_window(ldso_gpu_system* sys, int max_n, int* ids);
 

@@ -307,6 +307,8 @@ struct FrameHessian {
     SE3 Tcw;                    // Frame::getPose(): worldToCam
     AffLight shell_aff_g2l;     // Frame::aff_g2l
     bool poseValid = true;
+    FrameHessian* trackingRef = nullptr;   // the keyframe this frame was tracked against and the relative pose found then
+    SE3 camToTrackingRef;                   // (upstream DSO's FrameShell::trackingRef / camToTrackingRef)
     // ---- FrameHessian ----
     int frameID = 0, idx = 0, slot = -1;
     float ab_exposure = 0, frameEnergyTH = 8 * 8 * patternNum;
@@ -571,13 +573,18 @@ public:
         return 0;
     }
 
-    int getTrajectory(int max_n, int* ids, double* poses, int* is_kf) const {
+    // relative_to_ref = 0: Frame::getPose as the reference keeps it (a non-keyframe stays where it was tracked);
+    // 1: non-keyframes follow their tracking reference (camToTrackingRef composed with the reference's CURRENT pose, as
+    // upstream DSO's printResult does), so the whole trajectory is consistent with the bundle-adjusted keyframes
+    int getTrajectory(int max_n, int* ids, double* poses, int* is_kf, int relative_to_ref) const {
         int k = 0;
         for (const auto& f : allFrameHistory) {
             if (!f->poseValid || k >= max_n) continue;
             if (!initialized && f.get() != initializerFirstFrame) continue;
             if (ids) ids[k] = f->id;
-            if (poses) f->Tcw.toRt(poses + 12 * (size_t)k);
+            SE3 Tcw = f->Tcw;
+            if (relative_to_ref && f->kfId < 0 && f->trackingRef) Tcw = (f->trackingRef->Tcw.inverse() * f->camToTrackingRef).inverse();
+            if (poses) Tcw.toRt(poses + 12 * (size_t)k);
             if (is_kf) is_kf[k] = f->kfId >= 0 ? 1 : 0;
             k++;
         }
@@ -715,6 +722,8 @@ private:
         for (int k = 0; k < 5; k++) lastCoarseRMSE[k] = achievedRes[k];
         SE3 camToWorld = lastF->Tcw.inverse() * lastF_2_fh.inverse();
         fh->Tcw = camToWorld.inverse();
+        fh->trackingRef = lastF;
+        fh->camToTrackingRef = lastF_2_fh.inverse();
         fh->shell_aff_g2l = aff_g2l;
         if (coarseTracker->firstCoarseRMSE < 0) coarseTracker->firstCoarseRMSE = (float)achievedRes[0];
         tres[0] = achievedRes[0]; tres[1] = flowVecs[0]; tres[2] = flowVecs[1]; tres[3] = flowVecs[2];
@@ -1782,8 +1791,9 @@ private:
         if (!s || !image) return -2;                                                                                      \
         return s->impl.addActiveFrame(image, image_is_device != 0, timestamp, exposure_time, pose_out, status_out);       \
     }                                                                                                                     \
-    extern "C" int P##system_get_trajectory(P##system* s, int max_n, int* ids, double* poses, int* is_kf) {               \
-        return s->impl.getTrajectory(max_n, ids, poses, is_kf);                                                           \
+    extern "C" int P##system_get_trajectory(P##system* s, int max_n, int* ids, double* poses, int* is_kf,                 \
+                                            int relative_to_ref) {                                                        \
+        return s->impl.getTrajectory(max_n, ids, poses, is_kf, relative_to_ref);                                          \
     }                                                                                                                     \
     extern "C" int P##system_get_window(P##system* s, int max_n, int* ids) {                                              \
         int k = 0;                                                                                                        \

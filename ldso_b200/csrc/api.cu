@@ -456,9 +456,9 @@ extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot
     bool repeated = false;
     int nEval = 0, nAccept = 0, rc;
     TrackEvalOut ev;
-    const bool device_lm = c->cfg.tracker_lm_mode == 0;
+    const bool device_lm = c->cfg.tracker_lm_mode != 1;
     if (device_lm) {
-        // the level loop with its LM iterations runs inside one cooperative kernel
+        // the level loop with its LM iterations runs inside one kernel (thread-block cluster, or cooperative grid in mode 2)
         int status = 0;
         if ((rc = k34_track_all(c, tracker, coarsest_lvl, maxIterations, min_res_for_abort, cur, cur_a, cur_b, last_residuals, flow,
                                 &status, &nEval, &nAccept))) return rc;

@@ -89,7 +89,8 @@ struct ldso_gpu_ctx {
     double* trk_mailbox_dev = nullptr;      // device alias of trk_mailbox
     unsigned long long trk_seq = 0;
     double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
-    int trk_coop_max = 0;                   // co-resident CTA budget of the device-resident LM kernel
+    int trk_coop_max = 0;                   // co-resident CTA budget of the cooperative LM kernel (tracker_lm_mode = 2)
+    int trk_cluster = 0;                    // CTAs of the tracker's thread-block cluster (tracker_lm_mode = 0), chosen at first use
     WindowDev win;
     void* selector = nullptr;               // SelectorDev (a2_selector.cu), created on first use
     void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use

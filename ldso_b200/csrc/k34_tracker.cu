@@ -246,6 +246,7 @@ struct LmState {                // plain data: lives in shared memory, only thre
     int lvl, repeated, status;
     float lastRes[5], flow[3];
     double work;                // point evaluations so far (profile units)
+    double meanOld, accFlow[3]; // cluster kernel: E / n and the raw flow sums / count of the evaluation the pose stands on
 };
 
 __device__ inline ldso_sm::SE3 se3_of(const double* q, const double* t) {
@@ -737,6 +738,463 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
     if (lane == 0) *reinterpret_cast<volatile double*>(mailbox + 63) = seq;
 }
 
+
+// =====================================================================================================
+// The same pyramid walk on ONE thread-block cluster (sm_90+: distributed shared memory, hardware cluster barrier).
+// CLUSTER CTAs of CL_THREADS threads cover the level's points; per evaluation every CTA reduces its points to 52 values,
+// PUSHES them into slot [rank] of every CTA's shared-memory table (st.shared::cluster), and the cluster meets at one
+// barrier.cluster; then every CTA folds the table in fp64 in rank order (identical inputs, identical order: every CTA
+// holds the same sums, no broadcast) and runs the scalar LM transition.  Against k34_track_level_kernel this removes the
+// grid barrier and the round trip of the partials through L2, it is an ordinary (non-cooperative) launch, so the trackers
+// of several sequences run side by side on the 148 SMs, and the warp reduction is a transpose-reduce (57 shuffles per
+// warp instead of 260).  The table is double-buffered by evaluation parity: a CTA can be at most one evaluation ahead.
+constexpr int CL_THREADS = 256;
+constexpr int CL_MAX = 16;       // non-portable cluster size (needs cudaFuncAttributeNonPortableClusterSizeAllowed)
+constexpr int NV = NF + NI;      // 52
+
+// sum of acc[q] over the warp lands on lane q (q < 32) / lanes q - 32 and q - 16 (32 <= q < 48): each step halves the
+// values a lane holds and doubles the lanes summed into them
+__device__ __forceinline__ void warp_transpose_reduce48(float (&v)[NF], const int lane, float& out_lo, float& out_hi) {
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+        const bool up = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; i++) {
+            const float send = up ? v[i] : v[i + w];
+            const float keep = up ? v[i + w] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+        }
+    }
+    out_lo = v[0];
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1) {
+        const bool up = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; i++) {
+            const float send = up ? v[32 + i] : v[32 + i + w];
+            const float keep = up ? v[32 + i + w] : v[32 + i];
+            v[32 + i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+        }
+    }
+    out_hi = v[32] + __shfl_xor_sync(0xffffffffu, v[32], 16);   // lanes l and l ^ 16 both hold value 32 + (l & 15)
+}
+
+// ---- branch-free evaluation of one tracker point (same expressions as eval_point; an invalid point adds exact zeros) ----
+struct PtProj {
+    float u, v, Ku, Kv, new_idepth, refColor;
+    bool inb;
+};
+__device__ __forceinline__ PtProj cl_project(const TrkParams& p, const float4 q, const bool on) {
+    PtProj o;
+    const float x = q.x, y = q.y, id = q.z;
+    const float r0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2];
+    const float r1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5];
+    const float r2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8];
+    const float pt0 = r0 + p.t[0] * id, pt1 = r1 + p.t[1] * id, pt2 = r2 + p.t[2] * id;
+    o.u = pt0 / pt2; o.v = pt1 / pt2;
+    o.Ku = p.fx * o.u + p.cx; o.Kv = p.fy * o.v + p.cy;
+    o.new_idepth = id / pt2;
+    o.refColor = q.w;
+    o.inb = on && o.Ku > 2 && o.Kv > 2 && o.Ku < p.w - 3 && o.Kv < p.h - 3 && o.new_idepth > 0;
+    return o;
+}
+__device__ __forceinline__ void cl_accumulate(const TrkParams& p, const PtProj& o, const float4 hit, float (&acc)[NF], int& cE, int& cSat,
+                                              int& cWarp) {
+    const bool fin = o.inb && isfinite(hit.x);
+    const float residual = hit.x - (p.aff0 * o.refColor + p.aff1);
+    const float ar = fabsf(residual);
+    const float hw = ar < p.huberTH ? 1.f : p.huberTH / ar;
+    const bool sat = fin && ar > p.cutoffTH, good = fin && !sat;
+    cE += fin; cSat += sat; cWarp += good;
+    acc[45] += sat ? p.maxEnergy : (good ? hw * residual * residual * (2 - hw) : 0.f);
+    const float dx = hit.y * p.fx, dy = hit.z * p.fy;
+    float J[9];
+    J[0] = o.new_idepth * dx;
+    J[1] = o.new_idepth * dy;
+    J[2] = -(o.new_idepth * (o.u * dx + o.v * dy));
+    J[3] = -(o.u * o.v * dx + dy * (1 + o.v * o.v));
+    J[4] = o.u * o.v * dy + dx * (1 + o.u * o.u);
+    J[5] = o.u * dy - o.v * dx;
+    J[6] = p.aJ * (p.b0 - o.refColor);
+    J[7] = -1.f;
+    J[8] = residual;
+#pragma unroll
+    for (int r = 0; r < 9; r++) J[r] = good ? J[r] : 0.f;    // a dropped point may carry NaN / inf: select, do not multiply by 0
+    int kk = 0;
+#pragma unroll
+    for (int r = 0; r < 9; r++) {
+        const float Jw = J[r] * hw;
+#pragma unroll
+        for (int cidx = r; cidx < 9; cidx++) { acc[kk] = __fmaf_rn(Jw, J[cidx], acc[kk]); kk++; }   // a sum across points: fused is fine (and closer)
+    }
+}
+// the flow indicators of CoarseTracker.cc:587-617 (level 0, every 32nd point)
+__device__ __forceinline__ void cl_flow(const TrkParams& p, const float4 q, float (&acc)[NF], int& cFlow) {
+    const float x = q.x, y = q.y, id = q.z;
+    const float r0 = p.RKi[0] * x + p.RKi[1] * y + p.RKi[2];
+    const float r1 = p.RKi[3] * x + p.RKi[4] * y + p.RKi[5];
+    const float r2 = p.RKi[6] * x + p.RKi[7] * y + p.RKi[8];
+    const float pt0 = r0 + p.t[0] * id, pt1 = r1 + p.t[1] * id, pt2 = r2 + p.t[2] * id;
+    const float Ku = p.fx * (pt0 / pt2) + p.cx, Kv = p.fy * (pt1 / pt2) + p.cy;
+    const float k0 = p.Ki[0] * x + p.Ki[1] * y + p.Ki[2], k1 = p.Ki[3] * x + p.Ki[4] * y + p.Ki[5], k2 = p.Ki[6] * x + p.Ki[7] * y + p.Ki[8];
+    const float zT = k2 + p.t[2] * id, zT2 = k2 - p.t[2] * id;
+    const float KuT = p.fx * ((k0 + p.t[0] * id) / zT) + p.cx, KvT = p.fy * ((k1 + p.t[1] * id) / zT) + p.cy;
+    const float KuT2 = p.fx * ((k0 - p.t[0] * id) / zT2) + p.cx, KvT2 = p.fy * ((k1 - p.t[1] * id) / zT2) + p.cy;
+    const float z3 = r2 - p.t[2] * id;
+    const float Ku3 = p.fx * ((r0 - p.t[0] * id) / z3) + p.cx, Kv3 = p.fy * ((r1 - p.t[1] * id) / z3) + p.cy;
+    acc[46] += ((KuT - x) * (KuT - x) + (KvT - y) * (KvT - y)) + ((KuT2 - x) * (KuT2 - x) + (KvT2 - y) * (KvT2 - y));
+    acc[47] += ((Ku - x) * (Ku - x) + (Kv - y) * (Kv - y)) + ((Ku3 - x) * (Ku3 - x) + (Kv3 - y) * (Kv3 - y));
+    cFlow += 2;
+}
+
+// ---- the scalar LM transition, trimmed for latency (one thread, registers; same decisions as lm_decide / lm_candidate) ----
+// 1 / d to fp64 rounding from the hardware's 20-bit estimate and two Newton steps (the division routine costs ~3x as much
+// and sits on the dependent chain of the factorisation eight times)
+__device__ __forceinline__ double cl_rcp(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = __fma_rn(__fma_rn(-d, r, 1.0), r, r);
+    r = __fma_rn(__fma_rn(-d, r, 1.0), r, r);
+    return r;
+}
+// damped 8x8 solve, register resident, no pivoting (see lm_ldlt8_fast), reciprocals by cl_rcp
+__device__ __forceinline__ bool cl_ldlt8(const double* H, const double* bv, float lambda, int mode, double* inc) {
+    double a[8][8];
+    double dmax = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) {
+            double v = (mode == 1 && j < i) ? 0.0 : H[i * 8 + j];
+            if (i == j) { v *= (1 + lambda); dmax = fmax(dmax, fabs(v)); }
+            a[i][j] = v;
+        }
+    double y[8], inv[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) y[i] = -bv[i];
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const double d = a[k][k];
+        ok = ok && (d > 1e-12 * dmax);
+        inv[k] = cl_rcp(d);
+        double l[8];
+#pragma unroll
+        for (int i = k + 1; i < 8; i++) l[i] = a[i][k] * inv[k];
+#pragma unroll
+        for (int i = k + 1; i < 8; i++)
+#pragma unroll
+            for (int j = k + 1; j <= i; j++) a[i][j] = __fma_rn(-l[i], a[j][k], a[i][j]);
+#pragma unroll
+        for (int i = k + 1; i < 8; i++) a[i][k] = l[i];
+    }
+    if (!ok) return false;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < i; j++) y[i] = __fma_rn(-a[i][j], y[j], y[i]);
+#pragma unroll
+    for (int i = 0; i < 8; i++) y[i] *= inv[i];
+#pragma unroll
+    for (int i = 7; i >= 0; i--)
+#pragma unroll
+        for (int j = i + 1; j < 8; j++) y[i] = __fma_rn(-a[j][i], y[j], y[i]);
+#pragma unroll
+    for (int i = 0; i < 8; i++) inc[i] = y[i];
+    return true;
+}
+// SE3::exp for the small rotations of an LM increment: the four coefficient functions as even power series in theta
+// (|theta| < 0.25: the 9th term is below 1e-19), exact functions beyond
+__device__ __forceinline__ ldso_sm::SE3 cl_se3_exp(const double* a) {
+    const double* om = a + 3;
+    const double th2 = om[0] * om[0] + om[1] * om[1] + om[2] * om[2];
+    if (!(th2 < 0.0625)) return ldso_sm::SE3::exp(a);
+    // sin(th/2)/th, cos(th/2), (1 - cos th)/th^2, (th - sin th)/th^3
+    double im = 0, re = 0, A = 0, B = 0;
+    {
+        // coefficients (-1)^k / (2^(2k+1) (2k+1)!), (-1)^k / (4^k (2k)!), (-1)^k / (2k+2)!, (-1)^k / (2k+3)!
+        const double ci[9] = {0.5, -1.0 / 48, 1.0 / 3840, -1.0 / 645120, 1.0 / 185794560, -1.0 / 81749606400.0, 1.0 / 51011754393600.0,
+                              -1.0 / 42849873690624000.0, 1.0 / 46620662575398912000.0};
+        const double cr[9] = {1.0, -1.0 / 8, 1.0 / 384, -1.0 / 46080, 1.0 / 10321920, -1.0 / 3715891200.0, 1.0 / 1961990553600.0,
+                              -1.0 / 1428329123020800.0, 1.0 / 1371195958099968000.0};
+        const double cA[9] = {1.0 / 2, -1.0 / 24, 1.0 / 720, -1.0 / 40320, 1.0 / 3628800, -1.0 / 479001600, 1.0 / 87178291200.0,
+                              -1.0 / 20922789888000.0, 1.0 / 6402373705728000.0};
+        const double cB[9] = {1.0 / 6, -1.0 / 120, 1.0 / 5040, -1.0 / 362880, 1.0 / 39916800, -1.0 / 6227020800.0, 1.0 / 1307674368000.0,
+                              -1.0 / 355687428096000.0, 1.0 / 121645100408832000.0};
+#pragma unroll
+        for (int k = 8; k >= 0; k--) {
+            im = __fma_rn(im, th2, ci[k]); re = __fma_rn(re, th2, cr[k]);
+            A = __fma_rn(A, th2, cA[k]); B = __fma_rn(B, th2, cB[k]);
+        }
+    }
+    ldso_sm::SE3 r;
+    r.qw = re; r.qx = im * om[0]; r.qy = im * om[1]; r.qz = im * om[2];
+    double O[9], O2[9], V[9];
+    ldso_sm::hat(om, O);
+    ldso_sm::mat3_mul(O, O, O2);
+    for (int i = 0; i < 9; i++) V[i] = A * O[i] + B * O2[i];
+    V[0] += 1; V[4] += 1; V[8] += 1;
+    ldso_sm::mat3_vec(V, a, r.t);
+    return r;
+}
+
+// upper-triangle index t (0..44) of the 9x9 system -> (row, column)
+__constant__ unsigned char c_tri_r[45] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, 3, 3, 3, 3, 3, 3, 4, 4, 4, 4, 4, 5, 5, 5, 5, 6, 6, 6, 7, 7, 8};
+__constant__ unsigned char c_tri_c[45] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 1, 2, 3, 4, 5, 6, 7, 8, 2, 3, 4, 5, 6, 7, 8, 3, 4, 5, 6, 7, 8, 4, 5, 6, 7, 8, 5, 6, 7, 8, 6, 7, 8, 7, 8, 8};
+__device__ __forceinline__ void cl_Hb_entry(const double* r, double* H, double* b, int t) {   // lm_Hb_entry with the index table
+    const int n = ((int)r[NF + 2] + 3) & ~3;
+    const double invn = (double)(1.0f / n);
+    const int rr = c_tri_r[t], cc = c_tri_c[t];
+    auto sc = [](int i) { return i < 3 ? (double)LDSO_SCALE_XI_TRANS : i < 6 ? (double)LDSO_SCALE_XI_ROT : i == 6 ? (double)LDSO_SCALE_A : (double)LDSO_SCALE_B; };
+    const double v = r[t] * invn;
+    if (rr < 8 && cc < 8) H[rr * 8 + cc] = H[cc * 8 + rr] = v * sc(rr) * sc(cc);
+    else if (rr < 8) b[rr] = v * sc(rr);
+}
+// lm_decide with one division per evaluation: the accepted mean energy is kept, the flow indicators and the saturation
+// ratio are formed only where they are read (CoarseTracker.cc:94-99, 213-247, 664-672)
+__device__ __forceinline__ int cl_decide(const LmConst& k, LmState& s, const double* r, TrkParams& p) {
+    s.nEval++;
+    const double E = (float)r[45], nE = (int)r[NF + 0];
+    auto take = [&]() { s.meanOld = E / nE; s.accFlow[0] = r[46]; s.accFlow[1] = r[47]; s.accFlow[2] = r[NF + 3]; };
+    if (s.phase == LM_FIRST) {
+        const double satRatio = (int)r[NF + 1] / (float)(int)r[NF + 0];
+        if (satRatio > 0.6 && s.cutoffRepeat < 50) {
+            s.cutoffRepeat *= 2;
+            lm_make_params(k, s.q, s.t, s.a, s.b, k.coarseCutoff * s.cutoffRepeat, p);
+            return LM_CONT;
+        }
+        take();
+        s.hsel ^= 1;
+        s.lambda = 0.01f;
+        s.it = 0;
+        s.phase = LM_ITER;
+        return s.it >= k.maxIt ? LM_DONE : LM_SOLVE;
+    }
+    if (E / nE < s.meanOld) {
+        take();
+        s.hsel ^= 1;
+        for (int i = 0; i < 4; i++) s.q[i] = s.cq[i];
+        for (int i = 0; i < 3; i++) s.t[i] = s.ct[i];
+        s.a = s.ca; s.b = s.cb;
+        s.lambda *= 0.5;
+        s.nAccept++;
+    } else {
+        s.lambda *= 4.0;
+        if (s.lambda < 0.001f) s.lambda = 0.001f;
+    }
+    double nrm = 0;
+    for (int i = 0; i < 8; i++) nrm += s.inc[i] * s.inc[i];
+    if (!(nrm > 1e-6)) return LM_DONE;     // !(inc.norm() > 1e-3)
+    s.it++;
+    return s.it >= k.maxIt ? LM_DONE : LM_SOLVE;
+}
+__device__ __forceinline__ void cl_candidate(const LmConst& k, LmState& s, TrkParams& p) {   // lm_candidate over cl_se3_exp
+    double incS[8], inc[8];
+    const float extrapLimit = 0.001f;
+    float extrap = 1;
+    if (s.lambda < extrapLimit) extrap = sqrtf(sqrt(extrapLimit / s.lambda));
+    double sq = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        inc[i] = s.inc[i] * extrap;
+        incS[i] = inc[i] * (i < 3 ? LDSO_SCALE_XI_TRANS : i < 6 ? LDSO_SCALE_XI_ROT : i == 6 ? LDSO_SCALE_A : LDSO_SCALE_B);
+        sq += incS[i] * incS[i];
+    }
+    if (!isfinite(sq))
+        for (int i = 0; i < 8; i++) inc[i] = incS[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s.inc[i] = inc[i];
+    const ldso_sm::SE3 cand = cl_se3_exp(incS) * se3_of(s.q, s.t);
+    s.cq[0] = cand.qw; s.cq[1] = cand.qx; s.cq[2] = cand.qy; s.cq[3] = cand.qz;
+    s.ct[0] = cand.t[0]; s.ct[1] = cand.t[1]; s.ct[2] = cand.t[2];
+    s.ca = s.a; s.cb = s.b;
+    s.ca += incS[6];
+    s.cb += incS[7];
+    lm_make_params(k, s.cq, s.ct, s.ca, s.cb, k.coarseCutoff * s.cutoffRepeat, p);
+}
+
+constexpr int CL_SLOTS = 4;      // points per thread staged in shared memory per level (beyond: streamed from global memory)
+
+__global__ void __launch_bounds__(CL_THREADS)
+k34_track_cluster_kernel(const LmAll A, double* __restrict__ mailbox, double seq) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int C = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
+    __shared__ LmConst k;
+    __shared__ TrkParams sp;
+    __shared__ LmState st;
+    __shared__ double s_res[NV];
+    __shared__ float s_f[CL_THREADS / 32][NV];
+    __shared__ float s_own[NV];
+    __shared__ float s_part[2][CL_MAX][NV];      // [evaluation parity][source CTA][value]; counts travel as exact floats (< 2^24)
+    __shared__ float4 s_pc[CL_SLOTS][CL_THREADS];
+    __shared__ double s_A[64];
+    __shared__ int s_cmd;
+    __shared__ long long s_t[8];
+    long long tk = 0;
+    if (threadIdx.x < 8) s_t[threadIdx.x] = 0;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        k = A.base;
+        for (int i = 0; i < 4; i++) st.q[i] = k.q[i];
+        for (int i = 0; i < 3; i++) st.t[i] = k.t[i];
+        st.a = k.affA; st.b = k.affB;
+        st.nEval = 0; st.nAccept = 0; st.hsel = 0; st.lvl = A.coarsest; st.repeated = 0; st.status = 0; st.work = 0;
+        for (int i = 0; i < 5; i++) st.lastRes[i] = __int_as_float(0x7fc00000);
+        for (int i = 0; i < 3; i++) st.flow[i] = 1000.f;
+    }
+    cluster.sync();              // every CTA of the cluster is resident before anyone writes into a neighbour's shared memory
+    tk = clock64();
+    int gev = 0;
+    const int stride = C * CL_THREADS, first = rank * CL_THREADS + threadIdx.x;
+  while (true) {                 // one pass per pyramid level, coarsest first (CoarseTracker.cc:71)
+    if (threadIdx.x == 0) {
+        const LmLevel& L = A.lv[st.lvl];
+        for (int i = 0; i < 9; i++) k.Ki[i] = L.Ki[i];
+        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
+        k.pc = L.pc; k.img = L.img;
+        st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.lambda = 0.01f;
+        for (int i = 0; i < 8; i++) st.inc[i] = 0;
+        lm_make_params(k, st.q, st.t, st.a, st.b, k.coarseCutoff, sp);
+    }
+    __syncthreads();
+    const float4* __restrict__ pc = k.pc;
+    const float4* __restrict__ newImg = k.img;
+    const int npts = k.n, lvl0 = k.lvl == 0;
+    // this thread's points of the level stay in shared memory for all its evaluations
+#pragma unroll
+    for (int j = 0; j < CL_SLOTS; j++) {
+        const int i = first + j * stride;
+        s_pc[j][threadIdx.x] = i < npts ? __ldg(pc + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int ev = 0;; ev++, gev++) {
+        float acc[NF];
+#pragma unroll
+        for (int q = 0; q < NF; q++) acc[q] = 0.f;
+        int cnt[NI] = {0, 0, 0, 0};
+        const TrkParams P = sp;      // registers / uniform
+#pragma unroll
+        for (int j = 0; j < CL_SLOTS; j += 2) {
+            // two points in flight: projections, then eight texel loads, then the products
+            const int i0 = first + j * stride, i1 = i0 + stride;
+            const int w0 = i0 - lane;                        // first point of this warp in slot j (warps own 32 consecutive points)
+            if (w0 >= npts) break;                           // warp-uniform: this and every later slot is empty for the warp
+            const float4 q0 = s_pc[j][threadIdx.x];
+            const PtProj o0 = cl_project(P, q0, i0 < npts);
+            if (w0 + stride < npts) {                        // warp-uniform: the second slot of the pair has points too
+                const float4 q1 = s_pc[j + 1][threadIdx.x];
+                const PtProj o1 = cl_project(P, q1, i1 < npts);
+                const float4 h0 = lerp_texel(newImg, o0.inb ? o0.Ku : 3.f, o0.inb ? o0.Kv : 3.f, P.w);
+                const float4 h1 = lerp_texel(newImg, o1.inb ? o1.Ku : 3.f, o1.inb ? o1.Kv : 3.f, P.w);
+                cl_accumulate(P, o0, h0, acc, cnt[0], cnt[1], cnt[2]);
+                cl_accumulate(P, o1, h1, acc, cnt[0], cnt[1], cnt[2]);
+                if (lvl0 && (i1 & 31) == 0 && i1 < npts) cl_flow(P, q1, acc, cnt[3]);
+            } else {
+                const float4 h0 = lerp_texel(newImg, o0.inb ? o0.Ku : 3.f, o0.inb ? o0.Kv : 3.f, P.w);
+                cl_accumulate(P, o0, h0, acc, cnt[0], cnt[1], cnt[2]);
+            }
+            if (lvl0 && (i0 & 31) == 0 && i0 < npts) cl_flow(P, q0, acc, cnt[3]);
+        }
+        for (int i = first + CL_SLOTS * stride; i < npts; i += stride)    // clouds beyond CL_SLOTS points per thread
+            eval_point(P, __ldg(pc + i), i, newImg, acc, cnt[0], cnt[1], cnt[2], cnt[3]);
+        float lo, hi;
+        warp_transpose_reduce48(acc, lane, lo, hi);
+        // counts: two 16-bit fields per word (a warp sees at most 32 x points-per-thread of them)
+        unsigned c01 = (unsigned)cnt[0] | ((unsigned)cnt[1] << 16), c23 = (unsigned)cnt[2] | ((unsigned)cnt[3] << 16);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { c01 += __shfl_xor_sync(0xffffffffu, c01, o); c23 += __shfl_xor_sync(0xffffffffu, c23, o); }
+        s_f[wid][lane] = lo;
+        if (lane < 16) s_f[wid][32 + lane] = hi;
+        if (lane == 0) {
+            s_f[wid][NF + 0] = (float)(c01 & 0xffffu); s_f[wid][NF + 1] = (float)(c01 >> 16);
+            s_f[wid][NF + 2] = (float)(c23 & 0xffffu); s_f[wid][NF + 3] = (float)(c23 >> 16);
+        }
+        __syncthreads();
+        if (threadIdx.x < NV) {
+            float v = 0.f;
+#pragma unroll
+            for (int wq = 0; wq < CL_THREADS / 32; wq++) v += s_f[wq][threadIdx.x];
+            s_own[threadIdx.x] = v;
+        }
+        __syncthreads();
+        float (*tab)[NV] = s_part[gev & 1];
+        for (int idx = threadIdx.x; idx < NV * C; idx += CL_THREADS) {
+            const int dst = idx / NV, q = idx - dst * NV;
+            float* remote = cluster.map_shared_rank(&tab[rank][q], dst);
+            *remote = s_own[q];
+        }
+        if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[0] += now - tk; tk = now; }
+        cluster.sync();          // barrier.cluster arrive.release / wait.acquire: the pushed partials are visible
+        if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[1] += now - tk; tk = now; }
+        if (threadIdx.x < NV) {
+            double v = 0.0;
+            for (int r = 0; r < C; r++) v += (double)tab[r][threadIdx.x];
+            s_res[threadIdx.x] = v;
+        }
+        __syncthreads();
+        if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[2] += now - tk; tk = now; }
+        if (threadIdx.x < 45) cl_Hb_entry(s_res, st.H[st.hsel ^ 1], st.bv[st.hsel ^ 1], threadIdx.x);
+        __syncthreads();
+        const bool fixed = k.optA < 0 || k.optB < 0;
+        if (threadIdx.x == 0) {
+            st.work += npts;
+            int cmd = cl_decide(k, st, s_res, sp);
+            if (k.dbg == 3) { const long long now = clock64(); s_t[3] += now - tk; tk = now; }
+            if (cmd == LM_SOLVE && !fixed && cl_ldlt8(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, st.inc)) {
+                if (k.dbg == 3) { const long long now = clock64(); s_t[4] += now - tk; tk = now; }
+                cl_candidate(k, st, sp);
+                if (k.dbg == 3) { const long long now = clock64(); s_t[5] += now - tk; tk = now; }
+                cmd = LM_CONT;
+            }
+            s_cmd = cmd;
+        }
+        __syncthreads();
+        if (s_cmd == LM_DONE) { gev++; break; }
+        if (s_cmd == LM_SOLVE) {   // fixed affine parameters, or a pivot the fast factorisation refused
+            if (!fixed && wid == 0) lm_ldlt8_warp(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, s_A, st.inc, lane);
+            if (fixed && threadIdx.x == 0)
+                lm_solve_step_fixed(st.H[st.hsel], st.bv[st.hsel], st.lambda, k.solveMode, k.optA < 0, k.optB < 0, st.inc);
+            __syncthreads();
+            if (threadIdx.x == 0) cl_candidate(k, st, sp);
+            __syncthreads();
+        }
+    }
+    // between levels (CoarseTracker.cc:249-259), as in k34_track_level_kernel: every CTA takes the same decision
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int lvl = st.lvl;
+        st.lastRes[lvl] = sqrtf((float)st.meanOld);
+        const float num = (float)(int)st.accFlow[2];           // lm_vec6: rs[2], rs[3], rs[4]
+        st.flow[0] = (float)((float)st.accFlow[0] / (num + 0.1)); st.flow[1] = 0.f; st.flow[2] = (float)((float)st.accFlow[1] / (num + 0.1));
+        int next = lvl;
+        if ((double)st.lastRes[lvl] > 1.5 * (double)A.lv[lvl].minResForAbort) { st.status = 1; next = -1; }
+        else {
+            if (st.cutoffRepeat > 1 && !st.repeated) { next++; st.repeated = 1; }
+            next--;
+        }
+        st.lvl = next;
+    }
+    __syncthreads();
+    if (st.lvl < 0) break;
+  }
+    if (rank != 0 || wid != 0) return;
+    double v = 0.0;
+    if (lane < 4) v = st.q[lane];
+    else if (lane < 7) v = st.t[lane - 4];
+    else if (lane == 7) v = st.a;
+    else if (lane == 8) v = st.b;
+    else if (lane < 14) v = st.lastRes[lane - 9];
+    else if (lane < 17) v = st.flow[lane - 14];
+    else if (lane == 17) v = st.nEval;
+    else if (lane == 18) v = st.nAccept;
+    else if (lane == 19) v = st.status;
+    else if (lane == 20) v = st.work;
+    if (lane < 21) mailbox[lane] = v;
+    if (k.dbg == 3 && lane < 8) mailbox[24 + lane] = (double)s_t[lane];
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile double*>(mailbox + 63) = seq;
+}
+
 }  // namespace
 
 // include/AffLight.h:27-35 (float arithmetic, returned as double in the reference)
@@ -800,6 +1258,31 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     return 0;
 }
 
+// the device-resident tracker publishes one message per frame into the mapped pinned mailbox: poll it (no D2H copy, no sync)
+static int track_all_wait(ldso_gpu_ctx* c, double seq, int prof_idx, int dbg, ldso_sm::SE3& cur, float& aff_a, float& aff_b,
+                          float last_residuals[5], float flow[3], int* status, int* nEval, int* nAccept) {
+    volatile double* res = c->trk_mailbox;
+    for (unsigned spin = 1; res[63] != seq; spin++) {
+        _mm_pause();
+        if ((spin & 0xfffff) == 0) {
+            cudaError_t q = cudaStreamQuery(c->stream);
+            if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);
+            if (q == cudaSuccess && res[63] != seq) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    c->d2h_bytes += 22 * sizeof(double);
+    cur.qw = res[0]; cur.qx = res[1]; cur.qy = res[2]; cur.qz = res[3];
+    cur.t[0] = res[4]; cur.t[1] = res[5]; cur.t[2] = res[6];
+    aff_a = (float)res[7]; aff_b = (float)res[8];
+    for (int i = 0; i < 5; i++) last_residuals[i] = (float)res[9 + i];
+    for (int i = 0; i < 3; i++) flow[i] = (float)res[14 + i];
+    *nEval = (int)res[17]; *nAccept = (int)res[18]; *status = (int)res[19];
+    if (prof_idx >= 0) c->prof_pending[prof_idx].units = res[20];   // point evaluations of this launch
+    if (dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[24 + i];
+    return 0;
+}
+
 // trackNewestCoarse's level loop on the device (see k34_track_level_kernel): ONE cooperative launch walks the pyramid
 // from coarsest_lvl down, the host polls the mapped mailbox once.  In/out: pose, affine.
 int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
@@ -829,6 +1312,38 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
         L.img = c->frame[T.new_slot] + c->lvl_off[lvl];
         nmax = std::max(nmax, L.n);
     }
+    if (c->cfg.tracker_lm_mode != 2) {
+        // one thread-block cluster per tracker (ordinary launch: trackers of other sequences run beside it)
+        if (c->trk_cluster == 0) {
+            int want = CL_MAX;
+            if (const char* e = getenv("LDSO_LM_CLUSTER")) want = atoi(e);   // tuning knob: 1, 2, 4, 8 or 16 CTAs
+            LDSO_CUDA_OK(c, cudaFuncSetAttribute(k34_track_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            for (; want >= 1; want >>= 1) {
+                cudaLaunchConfig_t q = {};
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = want; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                q.gridDim = dim3(want); q.blockDim = dim3(CL_THREADS); q.attrs = at; q.numAttrs = 1;
+                int nclusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, k34_track_cluster_kernel, &q) == cudaSuccess && nclusters > 0) break;
+                cudaGetLastError();
+            }
+            if (want < 1) { c->set_error("no cluster size of the tracker kernel fits this device", __FILE__, __LINE__); return -1; }
+            c->trk_cluster = want;
+        }
+        cudaLaunchConfig_t q = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = c->trk_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        q.gridDim = dim3(c->trk_cluster); q.blockDim = dim3(CL_THREADS); q.stream = c->stream; q.attrs = at; q.numAttrs = 1;
+        double* mbx = c->trk_mailbox_dev;
+        const double sq = (double)(++c->trk_seq);
+        prof_begin(c, c->stream);
+        LDSO_CUDA_OK(c, cudaLaunchKernelEx(&q, k34_track_cluster_kernel, A, mbx, sq));
+        c->launches++;
+        const int pidx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
+        return track_all_wait(c, sq, pidx, k.dbg, cur, aff_a, aff_b, last_residuals, flow, status, nEval, nAccept);
+    }
     if (c->trk_coop_max == 0) {
         int per_sm = 0, sms = 0, dev = 0, coop = 0;
         LDSO_CUDA_OK(c, cudaGetDevice(&dev));
@@ -851,26 +1366,7 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
     LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(LM_THREADS), args, 0, c->stream));
     c->launches++;
     const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
-    volatile double* res = c->trk_mailbox;
-    for (unsigned spin = 1; res[63] != seq; spin++) {
-        _mm_pause();
-        if ((spin & 0xfffff) == 0) {
-            cudaError_t q = cudaStreamQuery(c->stream);
-            if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);
-            if (q == cudaSuccess && res[63] != seq) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
-        }
-    }
-    std::atomic_thread_fence(std::memory_order_acquire);
-    c->d2h_bytes += 22 * sizeof(double);
-    cur.qw = res[0]; cur.qx = res[1]; cur.qy = res[2]; cur.qz = res[3];
-    cur.t[0] = res[4]; cur.t[1] = res[5]; cur.t[2] = res[6];
-    aff_a = (float)res[7]; aff_b = (float)res[8];
-    for (int i = 0; i < 5; i++) last_residuals[i] = (float)res[9 + i];
-    for (int i = 0; i < 3; i++) flow[i] = (float)res[14 + i];
-    *nEval = (int)res[17]; *nAccept = (int)res[18]; *status = (int)res[19];
-    if (prof_idx >= 0) c->prof_pending[prof_idx].units = res[20];   // point evaluations of this launch
-    if (k.dbg == 3) for (int i = 0; i < 8; i++) c->lm_dbg_clocks[i] += res[24 + i];
-    return 0;
+    return track_all_wait(c, seq, prof_idx, k.dbg, cur, aff_a, aff_b, last_residuals, flow, status, nEval, nAccept);
 }
 
 // =====================================================================================================

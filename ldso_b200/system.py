@@ -111,16 +111,16 @@ class System:
         st = self.add_frame_ptr(img.ctypes.data_as(C.c_void_p), False, float(self.n_fed if timestamp is None else timestamp), exposure)
         return {k: int(st[i]) for k, i in ST.items()}, self._pose.copy()
 
-    def trajectory(self):
+    def trajectory(self, relative_to_ref=True):
         n = self.n_fed + 1
         ids = np.zeros(n, np.int32); poses = np.zeros((n, 12)); kf = np.zeros(n, np.int32)
         k = self.api.fn("system_get_trajectory")(self.h, C.c_int(n), ids.ctypes.data_as(C.c_void_p), poses.ctypes.data_as(C.c_void_p),
-                                                 kf.ctypes.data_as(C.c_void_p))
+                                                 kf.ctypes.data_as(C.c_void_p), C.c_int(1 if relative_to_ref else 0))
         return ids[:k].copy(), poses[:k].copy(), kf[:k].astype(bool)
 
-    def centres(self):
-        """camera centres (world frame) of every frame with a valid pose: ids, [n,3]"""
-        ids, poses, kf = self.trajectory()
+    def centres(self, relative_to_ref=True):
+        """camera centres (world frame) of every frame with a valid pose: ids, [n,3], is_keyframe"""
+        ids, poses, kf = self.trajectory(relative_to_ref)
         R = poses[:, :9].reshape(-1, 3, 3); t = poses[:, 9:]
         return ids, -np.einsum("nji,nj->ni", R, t), kf
 

@@ -1,7 +1,7 @@
 """GPU vs oracle through the C++ FullSystem: keyframe logs side by side, trajectory difference, timing"""
 import sys, time, numpy as np
 sys.path.insert(0, "/root/repo")
-from ldso_b200 import build, capi, system, synth, odometry
+from ldso_b200 import build, capi, system, synth
 from tests import util
 calib = sys.argv[1] if len(sys.argv) > 1 else "c1"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 150
@@ -16,7 +16,7 @@ for name, api in (("gpu", capi.load()), ("orc", capi.Api(build.ORACLE_LIB, "orc_
     dt = time.time() - t0
     ids, cen, kf = s.centres()
     gt = np.array([poses[i][1] for i in ids])
-    ate, scale = odometry.ate_rmse(cen, gt)
+    ate, scale = system.ate_rmse(cen, gt)
     res[name] = dict(sts=sts, kfs=kfs, ids=ids, cen=cen, ate=ate, scale=scale, dt=dt, cnt=s.counters(), ph=s.phase_seconds())
     print(name, "time %.2fs ATE %.3e scale %.4f" % (dt, ate, scale), s.counters())
     print(name, {k: round(v, 3) for k, v in s.phase_seconds().items()})
