@@ -36,7 +36,8 @@ from ldso_b200 import capi, synth, system  # noqa: E402
 CALIB = dict(w=640, h=480, fx=384.0, fy=384.0, cx=319.5, cy=239.5)
 STRIDE = 3               # camera speed: every 3rd frame of the synthetic 30 Hz trajectory -> a keyframe every ~8-10 frames
 SEQ_PER_GPU = 8          # BASELINE.json configs[4]: 64 sequences / 8 GPUs
-PRIME = 90               # untimed frames per sequence before warm-up: initializer, window fills to 7, first marginalisations
+PRIME = 110              # untimed frames per sequence before warm-up: initializer, window fills to 7 (frame ~62), first frames
+                         # marginalised (~70); the 20 frames after 115 hold two keyframes, the sequence's average density
 DENSITY_MODE = 1         # npoints_counter_mode (include/ldso_system.h): 1 = the window holds ~desiredPointDensity points
 WORKLOAD = ("configs[1] per sequence: synthetic 640x480 sequence (procedural box room, seed 1001+s, every %d-rd frame of the 30 Hz "
             "trajectory), pinhole, no vignette/gamma, preset 0 / mode 1, setting_pointSelection=0, loop closing off, vision only; "
@@ -157,11 +158,21 @@ class Job:
         self.k += 1
         return st
 
+    def run(self, ptr_of, n_frames, is_device, sync_after):
+        """n_frames frames of every sequence in ONE library call: no rendezvous between frames (ldso_gpu_batch_run)"""
+        n = len(self.sys)
+        st = self.batch.run_ptrs([[ptr_of(i, self.k + f) for f in range(n_frames)] for i in range(n)], is_device, sync_after)
+        for f in range(n_frames):
+            for i in range(n):
+                if st[i, f, system.ST["keyframe"]]:
+                    self.kf_frames[i].append(self.k + f)
+            self.stat_log.append(st[:, f][:, [system.ST["window"], system.ST["points"], system.ST["residuals"], system.ST["keyframe"],
+                                               system.ST["lost"], system.ST["tries"]]].copy())
+        self.k += n_frames
+        return st
+
     def prime(self, ptr_of, n):
-        for _ in range(n):
-            self.step([ptr_of(i, self.k) for i in range(len(self.sys))], False, False)
-        for c in self.ctxs:
-            c.sync()
+        self.run(ptr_of, n, False, True)
 
     def steady_state(self, first, last):
         """window / point / residual statistics of the steps [first, last) and the trajectory error of every sequence"""
@@ -189,32 +200,68 @@ class Job:
 
 
 def timed_region(job, ptr_of, is_device, steps, warmup, flush=None):
-    """W untimed + K timed steps.  is_device: per-step CUDA-event intervals on every context's stream (covering its
-    mapping stream), the step takes the longest of them; else host wall clock around the call with every context's streams
-    drained before the clock stops.  Returns (seconds per step, launches, h2d bytes, d2h bytes, first timed step index)."""
+    """W untimed + K timed steps (a step = one frame of every sequence).
+    One sequence: step by step, L2 flushed between steps; device-resident input -> CUDA events on the context's tracking stream
+    (closing over its mapping stream), host input -> wall clock around the call with the streams drained inside the window.
+    Several sequences: the K steps are ONE library call (ldso_gpu_batch_run): the sequences share nothing, so each runs its K
+    frames without waiting for the others; the region is timed as a whole (CUDA events on every context, the longest wins /
+    wall clock).  No flush there: every frame's image is new data read once, S x K x 1.2 MB of input exceeds the 126 MB L2.
+    Returns (seconds per step or [total], launches, h2d bytes, d2h bytes, first timed step index)."""
     n = len(job.sys)
-    for _ in range(warmup):
-        job.step([ptr_of(i, job.k) for i in range(n)], is_device, True)
+    if n == 1:
+        for _ in range(warmup):
+            job.step([ptr_of(0, job.k)], is_device, True)
+    else:
+        job.run(ptr_of, warmup, is_device, True)
     first = len(job.stat_log)
     l0 = sum(c.launch_count() for c in job.ctxs)
     io0 = [c.io_bytes() for c in job.ctxs]
     times = []
-    for _ in range(steps):
+    if n == 1:
+        for _ in range(steps):
+            if flush is not None:
+                flush()                                  # evict L2 between timed steps (outside the timed window)
+            if is_device:
+                job.ctxs[0].timer_start()
+                job.step([ptr_of(0, job.k)], True, False)
+                times.append(job.ctxs[0].timer_stop() * 1e-3)
+            else:
+                t0 = time.perf_counter()
+                job.step([ptr_of(0, job.k)], False, True)   # returns after the frame is done and the context's streams are drained
+                times.append(time.perf_counter() - t0)
+    else:
         if flush is not None:
-            flush()                                  # evict L2 between timed steps (outside the timed window)
-        ptrs = [ptr_of(i, job.k) for i in range(n)]
+            flush()
         if is_device:
             for c in job.ctxs:
                 c.timer_start()
-            job.step(ptrs, True, False)
+            job.run(ptr_of, steps, True, False)
             times.append(max(c.timer_stop() for c in job.ctxs) * 1e-3)
         else:
             t0 = time.perf_counter()
-            job.step(ptrs, False, True)              # returns after every sequence's frame is done and its streams are drained
+            job.run(ptr_of, steps, False, True)
             times.append(time.perf_counter() - t0)
     io1 = [c.io_bytes() for c in job.ctxs]
     return (times, sum(c.launch_count() for c in job.ctxs) - l0, sum(b[0] - a[0] for a, b in zip(io0, io1)),
             sum(b[1] - a[1] for a, b in zip(io0, io1)), first)
+
+
+def rank_seeds(rank, per_gpu):
+    """sequence s of the job goes to GPU s // per_gpu (SURVEY.md section 8e: independent sequences, no data-path exchange)"""
+    return [1001 + rank * per_gpu + i for i in range(per_gpu)]
+
+
+def reduce_over_ranks(times, mine, world, dist, torch, device):
+    """the job's timed regions are the slowest rank's (the ONLY exchange between ranks: one all_reduce(MAX) and a gather of
+    the per-rank logs, both outside the timed region).  times: list of floats; mine: this rank's log dict.
+    Returns (max over ranks of each time, [log of rank 0, log of rank 1, ...])."""
+    if world <= 1:
+        return list(times), [mine]
+    tt = torch.tensor(list(times), dtype=torch.float64, device=device)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    per_rank = [None] * world
+    dist.all_gather_object(per_rank, mine)
+    return tt.tolist(), per_rank
 
 
 def cpu_arm(seeds, data, steps, warmup, threads_total):
@@ -277,7 +324,7 @@ def main():
                               steady_state=st)))
         return
 
-    seeds = [1001 + rank * S + i for i in range(S)]
+    seeds = rank_seeds(rank, S)
     data = render_sequences(seeds, n_frames)                 # before CUDA is initialised in this process
     import torch
     import torch.distributed as dist
@@ -327,14 +374,7 @@ def main():
                   "host_phase_seconds_whole_run": ph1[0]}
     # max over ranks of the timed region; per-rank figures travel to rank 0 for the log
     mine = {"rank": rank, "ms_per_step": 1e3 * sum(t_dev) / steps, "ms_per_step_e2e": 1e3 * sum(t_e2e) / steps, "steady_state": st_dev}
-    if world > 1:
-        tt = torch.tensor([sum(t_dev), sum(t_e2e)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        T_dev, T_e2e = tt.tolist()
-        per_rank = [None] * world
-        dist.all_gather_object(per_rank, mine)
-    else:
-        T_dev, T_e2e, per_rank = sum(t_dev), sum(t_e2e), [mine]
+    (T_dev, T_e2e), per_rank = reduce_over_ranks([sum(t_dev), sum(t_e2e)], mine, world, dist, torch, "cuda")
 
     # per-kernel CUDA-event profile: one sequence, steady state (separate pass, not a timed number)
     job = Job(gpu, seeds[:1], data, device=local_rank)
@@ -367,9 +407,12 @@ def main():
     line = dict(base, value=total_frames / T_dev, ms_per_step=1e3 * T_dev / steps,
                 e2e={"value": total_frames / T_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps, "d2h_bytes_per_step": d2h / steps},
                 gpu_launches=int(launches), clocks=clk.summary(),
-                timing="CUDA events on every context's tracking stream (closing over its mapping stream) per step, longest context = the "
-                       "step, max over ranks; L2 flushed with a 256 MiB write between timed steps; e2e: host wall clock around the batch "
-                       "call, page-locked host images, every context's streams drained inside the window",
+                timing="the K steps of the S sequences of a GPU are one ldso_gpu_batch_run call (no rendezvous between frames); value: "
+                       "CUDA events on every context's tracking stream (closing over its mapping stream) around the region, longest "
+                       "context wins, max over ranks; e2e: host wall clock around the call, page-locked host images, every context's "
+                       "streams drained inside the window; L2: flushed once before the region, every frame's image is new data read "
+                       "once (S x K x 1.2 MB of input > 126 MB L2); single_sequence: step by step, L2 flushed with a 256 MiB write "
+                       "between steps",
                 roofline={"bound": "hbm", "kernel": top, "achieved": kernels[top]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                           "frac": kernels[top]["frac"], "traffic": None, "peak_source": "measured" if peaks else "fallback",
                           "launches": kernels[top]["launches"], "avg_us": kernels[top]["avg_us"],

@@ -425,6 +425,13 @@ int ldso_gpu_window_get_residual_ints(ldso_gpu_ctx* ctx, int what, int* dst);
  *       8 idepth_hessian 9 maxRelBaseline 10 numGoodResiduals (as float) 11 step */
 int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* ctx, int what, float* dst);
 
+/* everything FullSystem reads back after linearizeAll(true) in one call (one synchronisation): state_state [n_res]
+ * (-> PointHessian::lastResiduals, FullSystem.cc:1745-1751), centerProjectedTo [n_res][3] and HdiF [n_points]
+ * (-> CoarseTracker::makeCoarseDepthL0, CoarseTracker.cc:363-382), idepth_hessian, numGoodResiduals (as float) and
+ * maxRelBaseline [n_points] (-> flagPointsForRemoval, FullSystem.cc:1377-1417).  Any pointer may be NULL. */
+int ldso_gpu_window_get_keyframe_results(ldso_gpu_ctx* ctx, int* state, float* center3, float* hdi, float* idepth_hessian,
+                                         float* num_good, float* max_rel_baseline);
+
 #ifdef __cplusplus
 }
 #endif

@@ -125,8 +125,9 @@ int ldso_gpu_system_last_keyframe_log(ldso_gpu_system* sys, double out[12]);
  * (FullSystem::initializeFromInitializer draws from std::rand; sequences stepped concurrently must not share it) */
 int ldso_gpu_system_rand_sequence(unsigned seed, int n, int* out);
 /* host wall-clock seconds spent per phase since creation (0 trackNewCoarse incl. makeImages, 1 traceNewCoarse,
- * 2 activatePointsMT, 3 optimize, 4 marginalisation, 5 makeNewTraces + setCoarseTrackingRef, 6 initializer, 7 other) */
-int ldso_gpu_system_get_phase_seconds(ldso_gpu_system* sys, double out[8]);
+ * 2 activatePointsMT, 3 optimize, 4 marginalisation, 5 makeNewTraces + setCoarseTrackingRef, 6 initializer, 7 other;
+ * inside 0: 8 the makeImages call, 9 the trackNewestCoarse calls, 10 building the motion hypotheses; 11 unused) */
+int ldso_gpu_system_get_phase_seconds(ldso_gpu_system* sys, double out[12]);
 
 /* ---- several sequences per GPU (BASELINE.json configs[4]: 64 independent sequences over 1/2/4/8 GPUs) ----
  * A batch steps n systems together: worker thread t (of n_threads) owns systems t, t + n_threads, ... and feeds each its
@@ -142,6 +143,12 @@ void ldso_gpu_batch_destroy(ldso_gpu_batch* batch);
 int ldso_gpu_batch_add_active_frames(ldso_gpu_batch* batch, const float* const* images, int image_is_device,
                                      const double* timestamps, const float* exposures, int sync_after, double* poses_out,
                                      int* status_out);
+
+/* The same for n_frames frames per system in ONE call, without a rendezvous between frames: images[n][n_frames]
+ * (system-major), exposure 1, timestamps counting up; every worker feeds its systems their frames in order and a keyframe of
+ * one sequence does not hold back the others.  poses_out [n][n_frames][12], status_out [n][n_frames][LDSO_SYS_ST_N]. */
+int ldso_gpu_batch_run(ldso_gpu_batch* batch, int n_frames, const float* const* images, int image_is_device, int sync_after,
+                       double* poses_out, int* status_out);
 
 #ifdef __cplusplus
 }

@@ -53,6 +53,7 @@
         LDSO_API_FN(P, window_solve) LDSO_API_FN(P, window_resubstitute) LDSO_API_FN(P, window_marginalize_points)       \
         LDSO_API_FN(P, window_marginalize_frame) LDSO_API_FN(P, window_get_residual_floats)                              \
         LDSO_API_FN(P, window_get_residual_ints) LDSO_API_FN(P, window_get_point_floats)                                 \
+        LDSO_API_FN(P, window_get_keyframe_results)                                                                      \
     };
 // declarations of the same entry points under another prefix (test builds: the CPU oracle mirrors the ABI as orc_*)
 #define LDSO_DECLARE_API(P, CTX)                                                                                         \
@@ -104,6 +105,7 @@
     int P##window_get_residual_floats(CTX*, int, float*);                                                                \
     int P##window_get_residual_ints(CTX*, int, int*);                                                                    \
     int P##window_get_point_floats(CTX*, int, float*);                                                                   \
+    int P##window_get_keyframe_results(CTX*, int*, float*, float*, float*, float*, float*);                              \
     }
 
 namespace ldso {
@@ -459,7 +461,7 @@ public:
     std::vector<int> free_slots;
     long long counters[LDSO_SYS_CT_N] = {0};
     double kf_log[12] = {0};
-    double phase_s[8] = {0};
+    double phase_s[12] = {0};   // [0..7] see ldso_gpu_system_get_phase_seconds; [8] makeImages call, [9] trackNewestCoarse calls, [10] hypotheses
     int last_tries = 0;
     int n_pool = 0;                                               // size of the device-resident immature pool
 
@@ -507,6 +509,7 @@ public:
         // fh->makeImages(image, Hcalib) (:93)
         int rc = image_is_device ? Api::frame_make_images_dev(ctx, fh->slot, image) : Api::frame_make_images(ctx, fh->slot, image);
         if (rc < 0) return fail_api();
+        phase_s[8] += now() - t0;
         bool madeKF = false;
         if (!initialized) {
             // :95-128
@@ -641,6 +644,7 @@ private:
         return r;
     }
     int trackNewCoarse(FrameHessian* fh, double tres[4]) {
+        const double t_h0 = now();
         FrameHessian* lastF = coarseTracker->lastRef;
         AffLight aff_last_2_l(0, 0);
         std::vector<SE3> lastF_2_fh_tries;
@@ -678,6 +682,7 @@ private:
                 lastF_2_fh_tries.push_back(SE3());
             }
         }
+        phase_s[10] += now() - t_h0;
         double flowVecs[3] = {100, 100, 100};
         SE3 lastF_2_fh;
         AffLight aff_g2l(0, 0);
@@ -694,7 +699,9 @@ private:
             int iters[2];
             lastF_2_fh_this.toRt(pose);
             for (int k = 0; k < 5; k++) minRes[k] = (float)achievedRes[k];
+            const double t_t0 = now();
             int rc = Api::tracker_track(ctx, coarseTracker->dev, fh->slot, fh->ab_exposure, pose, aff, levels - 1, minRes, lastRes, flow, iters);
+            phase_s[9] += now() - t_t0;
             if (rc < 0) return fail_api();
             counters[LDSO_SYS_CT_TRACK_CALLS]++;
             const bool trackingIsGood = rc == 0;
@@ -1090,16 +1097,7 @@ private:
         std::vector<int> st(std::max(nr, 1));
         std::vector<float> cen(3 * (size_t)std::max(nr, 1)), hdi(std::max(np, 1)), idh(std::max(np, 1)), ngood(std::max(np, 1)),
             mrb(std::max(np, 1));
-        if (nr) {
-            if (Api::window_get_residual_ints(ctx, 0, st.data()) < 0) return fail_api();
-            if (Api::window_get_residual_floats(ctx, 3, cen.data()) < 0) return fail_api();
-        }
-        if (np) {
-            if (Api::window_get_point_floats(ctx, 6, hdi.data()) < 0) return fail_api();
-            if (Api::window_get_point_floats(ctx, 8, idh.data()) < 0) return fail_api();
-            if (Api::window_get_point_floats(ctx, 10, ngood.data()) < 0) return fail_api();
-            if (Api::window_get_point_floats(ctx, 9, mrb.data()) < 0) return fail_api();
-        }
+        if (Api::window_get_keyframe_results(ctx, st.data(), cen.data(), hdi.data(), idh.data(), ngood.data(), mrb.data()) < 0) return fail_api();
         for (int i = 0; i < np; i++) {
             PointHessian* p = up.pts[i];
             p->HdiF = hdi[i];
@@ -1685,12 +1683,13 @@ namespace ldso {
 template <class Sys, class Api> class BatchRunner {
 public:
     struct Job {
-        const float* image = nullptr;
+        const float* const* images = nullptr;   // n_frames image pointers of this system, fed in order
+        int n_frames = 1;
         int is_device = 0;
-        double timestamp = 0;
+        double timestamp = 0;                   // of the first frame; later frames count up by one
         float exposure = 1;
-        double* pose_out = nullptr;
-        int* status_out = nullptr;
+        double* pose_out = nullptr;             // [n_frames][12]
+        int* status_out = nullptr;              // [n_frames][LDSO_SYS_ST_N]
         int sync_after = 0;
         int rc = 0;
     };
@@ -1737,12 +1736,24 @@ private:
                 seen = generation;
                 if (quit) return;
             }
+            // frames outer, systems inner: a worker that owns several sequences advances them together; nothing waits for
+            // the other workers between frames (a keyframe of one sequence does not hold back the others)
+            int most = 0;
             for (size_t i = t; i < sys.size(); i += T) {
                 if (!bound && sys[i]->impl.ctx) Api::bind_thread(sys[i]->impl.ctx);   // the device of the ctx becomes this thread's
-                Job& j = jobs[i];
-                j.rc = sys[i]->impl.addActiveFrame(j.image, j.is_device != 0, j.timestamp, j.exposure, j.pose_out, j.status_out);
-                if (j.sync_after && j.rc >= 0 && Api::sync(sys[i]->impl.ctx) < 0) j.rc = -1;   // drains the queued trace too
+                jobs[i].rc = 0;
+                most = std::max(most, jobs[i].n_frames);
             }
+            for (int f = 0; f < most; f++)
+                for (size_t i = t; i < sys.size(); i += T) {
+                    Job& j = jobs[i];
+                    if (f >= j.n_frames || j.rc < 0) continue;
+                    j.rc = sys[i]->impl.addActiveFrame(j.images[f], j.is_device != 0, j.timestamp + f, j.exposure,
+                                                       j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
+                                                       j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
+                }
+            for (size_t i = t; i < sys.size(); i += T)
+                if (jobs[i].sync_after && jobs[i].rc >= 0 && Api::sync(sys[i]->impl.ctx) < 0) jobs[i].rc = -1;   // drains the queued trace too
             bound = true;
             {
                 std::lock_guard<std::mutex> lk(mu);
@@ -1818,8 +1829,8 @@ private:
         for (int i = 0; i < n; i++) out[i] = g.next();                                                                    \
         return 0;                                                                                                         \
     }                                                                                                                     \
-    extern "C" int P##system_get_phase_seconds(P##system* s, double out[8]) {                                             \
-        for (int i = 0; i < 8; i++) out[i] = s->impl.phase_s[i];                                                          \
+    extern "C" int P##system_get_phase_seconds(P##system* s, double out[12]) {                                            \
+        for (int i = 0; i < 12; i++) out[i] = s->impl.phase_s[i];                                                         \
         return 0;                                                                                                         \
     }                                                                                                                     \
     struct P##batch {                                                                                                     \
@@ -1839,10 +1850,28 @@ private:
         const int n = (int)b->run.sys.size();                                                                             \
         for (int i = 0; i < n; i++) {                                                                                     \
             auto& j = b->run.jobs[i];                                                                                     \
-            j.image = images[i]; j.is_device = image_is_device; j.timestamp = timestamps ? timestamps[i] : 0;             \
+            j.images = images + i; j.n_frames = 1; j.is_device = image_is_device;                                         \
+            j.timestamp = timestamps ? timestamps[i] : 0;                                                                 \
             j.exposure = exposures ? exposures[i] : 1.0f; j.sync_after = sync_after;                                      \
             j.pose_out = poses_out ? poses_out + 12 * (size_t)i : nullptr;                                                \
             j.status_out = status_out ? status_out + LDSO_SYS_ST_N * (size_t)i : nullptr;                                 \
+        }                                                                                                                 \
+        b->run.step();                                                                                                    \
+        int worst = 0;                                                                                                    \
+        for (int i = 0; i < n; i++) if (b->run.jobs[i].rc < 0) worst = b->run.jobs[i].rc;                                 \
+        return worst;                                                                                                     \
+    }                                                                                                                     \
+    extern "C" int P##batch_run(P##batch* b, int n_frames, const float* const* images, int image_is_device,              \
+                                int sync_after, double* poses_out, int* status_out) {                                     \
+        if (!b || !images || n_frames < 1) return -2;                                                                     \
+        const int n = (int)b->run.sys.size();                                                                             \
+        for (int i = 0; i < n; i++) {                                                                                     \
+            auto& j = b->run.jobs[i];                                                                                     \
+            j.images = images + (size_t)i * n_frames; j.n_frames = n_frames; j.is_device = image_is_device;               \
+            j.timestamp = (double)b->run.sys[i]->impl.allFrameHistory.size(); j.exposure = 1.0f;                          \
+            j.sync_after = sync_after;                                                                                    \
+            j.pose_out = poses_out ? poses_out + 12 * (size_t)i * n_frames : nullptr;                                     \
+            j.status_out = status_out ? status_out + LDSO_SYS_ST_N * (size_t)i * n_frames : nullptr;                      \
         }                                                                                                                 \
         b->run.step();                                                                                                    \
         int worst = 0;                                                                                                    \

@@ -473,6 +473,7 @@ static int make_maps_device(ldso_gpu_ctx* c, int slot, float density, int recurs
 
 extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor,
                                          int* potential_io, float* map_out, int* n_selected) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, map_out != nullptr);
     int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, n_selected);
     if (rc) return rc;
@@ -491,6 +492,7 @@ extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float densit
 extern "C" int ldso_gpu_select_points(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor,
                                       int* potential_io, int border, int max_points, float* u_out, float* v_out,
                                       float* type_out, int* n_points) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, u_out && v_out && type_out && n_points && border >= 0 && max_points >= 0);
     int nsel = 0;
     int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, &nsel);

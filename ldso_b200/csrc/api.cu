@@ -36,6 +36,7 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaGetDeviceCount(&ndev));
     LDSO_REQUIRE(c, cfg.device >= 0 && cfg.device < ndev);
     LDSO_CUDA_OK(c, cudaSetDevice(cfg.device));
+    LDSO_CUDA_OK(c, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cfg.device));
     // pyramid level rule of setGlobalCalib (src/internal/GlobalCalib.cc:20-28)
     int wl = cfg.w, hl = cfg.h, lv = 1;
     while (wl % 2 == 0 && hl % 2 == 0 && wl * hl > 5000 && lv < LDSO_MAX_LEVELS) { wl /= 2; hl /= 2; lv++; }
@@ -118,6 +119,8 @@ extern "C" int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out) {
 
 extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     if (!c) return;
+    int caller_dev = -1;
+    cudaGetDevice(&caller_dev);              // the caller's current device is restored below
     cudaSetDevice(c->cfg.device);
     cudaDeviceSynchronize();
     if (c->frame) {
@@ -147,7 +150,9 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     for (cudaEvent_t e : c->prof_free) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->stream_map) cudaStreamDestroy(c->stream_map);
+    const int own_dev = c->cfg.device;
     delete c;
+    if (caller_dev >= 0 && caller_dev != own_dev) cudaSetDevice(caller_dev);
 }
 
 extern "C" const char* ldso_gpu_last_error(const ldso_gpu_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
@@ -158,25 +163,30 @@ extern "C" int ldso_gpu_level_size(const ldso_gpu_ctx* c, int lvl, int* w, int* 
     return 0;
 }
 extern "C" int ldso_gpu_sync(ldso_gpu_ctx* c) {
+    LDSO_ENTER(c);
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream_map));
     return 0;
 }
 extern "C" int ldso_gpu_bind_thread(ldso_gpu_ctx* c) {
+    LDSO_ENTER(c);
     LDSO_CUDA_OK(c, cudaSetDevice(c->cfg.device));
     return 0;
 }
 extern "C" long long ldso_gpu_launch_count(const ldso_gpu_ctx* c) { return c->launches; }
 
 extern "C" int ldso_gpu_io_bytes(ldso_gpu_ctx* c, long long* h2d, long long* d2h) {
+    LDSO_ENTER(c);
     *h2d = c->h2d_bytes; *d2h = c->d2h_bytes;
     return 0;
 }
 extern "C" int ldso_gpu_timer_start(ldso_gpu_ctx* c) {
+    LDSO_ENTER(c);
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev0, c->stream));
     return 0;
 }
 extern "C" int ldso_gpu_timer_stop(ldso_gpu_ctx* c, float* ms) {
+    LDSO_ENTER(c);
     // the window closes over BOTH streams: work queued on the mapping stream (the asynchronous traceNewCoarse) is part of
     // the frame, so the tracking stream waits for it before the stop event is recorded
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream_map));
@@ -218,6 +228,7 @@ void prof_drain(ldso_gpu_ctx* c) {
     c->prof_pending.clear();
 }
 extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
+    LDSO_ENTER(c);
     immature_trace_finalize(c);
     prof_drain(c);
     c->profile_on = on;
@@ -225,6 +236,7 @@ extern "C" int ldso_gpu_profile_enable(ldso_gpu_ctx* c, int on) {
     return 0;
 }
 extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms, long long* launches, double* units) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, which >= 0 && which < LDSO_PROF_SLOTS);
     immature_trace_finalize(c);
     prof_drain(c);
@@ -238,6 +250,7 @@ extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms
 }
 
 extern "C" int ldso_gpu_set_gamma(ldso_gpu_ctx* c, const float B[256]) {
+    LDSO_ENTER(c);
     LDSO_CUDA_OK(c, ldso_copy(c, c->gammaB_dev, B, 256 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
     return 0;
@@ -245,6 +258,7 @@ extern "C" int ldso_gpu_set_gamma(ldso_gpu_ctx* c, const float B[256]) {
 
 // ---- K1 ------------------------------------------------------------------------------------------
 extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float* img) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && img);
     const size_t bytes = (size_t)c->cfg.w * c->cfg.h * sizeof(float);
     // the caller deletes its ImageAndExposure right after addActiveFrame (run_dso_tum_mono.cc:405-429):
@@ -267,11 +281,13 @@ extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float
     return k1_make_images(c, slot, c->img_dev);
 }
 extern "C" int ldso_gpu_frame_make_images_dev(ldso_gpu_ctx* c, int slot, const float* img_dev) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && img_dev);
     return k1_make_images(c, slot, img_dev);
 }
 
 extern "C" int ldso_gpu_frame_download(ldso_gpu_ctx* c, int slot, int lvl, int what, float* dst) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && lvl >= 0 && lvl < c->levels && dst);
     const size_t n = (size_t)c->wG[lvl] * c->hG[lvl];
     float4* h = (float4*)c->scratch_host;
@@ -287,6 +303,7 @@ extern "C" int ldso_gpu_frame_download(ldso_gpu_ctx* c, int slot, int lvl, int w
 
 // ---- K2 ------------------------------------------------------------------------------------------
 extern "C" int ldso_gpu_tracker_make_k(ldso_gpu_ctx* c, int tracker, float fx, float fy, float cx, float cy) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS);
     TrackerDev& T = c->trk[tracker];
     // CoarseTracker::makeK (src/frontend/CoarseTracker.cc:312-339): float state, double intermediates
@@ -313,6 +330,7 @@ extern "C" int ldso_gpu_tracker_make_k(ldso_gpu_ctx* c, int tracker, float fx, f
 extern "C" int ldso_gpu_tracker_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n_points, const float* u, const float* v,
                                         const float* idepth, const float* hdi, float ref_exposure, float ref_aff_a,
                                         float ref_aff_b) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS);
     LDSO_REQUIRE(c, ref_slot >= 0 && ref_slot < c->cfg.n_frame_slots);
     LDSO_REQUIRE(c, n_points >= 0 && (size_t)n_points * 4 <= (size_t)c->cfg.w * c->cfg.h);
@@ -324,6 +342,7 @@ extern "C" int ldso_gpu_tracker_set_ref(ldso_gpu_ctx* c, int tracker, int ref_sl
 
 extern "C" int ldso_gpu_tracker_get_pc(ldso_gpu_ctx* c, int tracker, int lvl, int* n, float* u, float* v, float* idepth,
                                        float* color) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels && n);
     TrackerDev& T = c->trk[tracker];
     int m = T.pc_n[lvl];
@@ -369,6 +388,7 @@ static void fill_Hb(const TrackEvalOut& e, double H[64], double b[8]) {
 
 extern "C" int ldso_gpu_tracker_calc_res(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, int lvl,
                                          const double ref_to_new[12], float aff_a, float aff_b, float cutoff_th, float out6[6]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels);
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && ref_to_new && out6);
     TrackerDev& T = c->trk[tracker];
@@ -388,6 +408,7 @@ extern "C" int ldso_gpu_tracker_calc_res(ldso_gpu_ctx* c, int tracker, int new_s
 
 extern "C" int ldso_gpu_tracker_calc_gs(ldso_gpu_ctx* c, int tracker, int lvl, const double ref_to_new[12], float aff_a,
                                         float aff_b, double H[64], double b[8]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && H && b);
     TrackerDev& T = c->trk[tracker];
     // the reference accumulates over the buffers left by the LAST calcRes; the fused launch already did
@@ -439,6 +460,7 @@ void solve_step(const double* H, const double* b, float lambda, int mode, float 
 extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, double pose_io[12],
                                       float aff_io[2], int coarsest_lvl, const float min_res_for_abort[5],
                                       float last_residuals[5], float flow[3], int iters_out[2]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS);
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && pose_io && aff_io && min_res_for_abort);
     LDSO_REQUIRE(c, coarsest_lvl >= 0 && coarsest_lvl < 5 && coarsest_lvl < c->levels);   // CoarseTracker.cc:65

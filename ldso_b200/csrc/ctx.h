@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -91,6 +92,11 @@ struct ldso_gpu_ctx {
     double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
     int trk_coop_max = 0;                   // co-resident CTA budget of the cooperative LM kernel (tracker_lm_mode = 2)
     int trk_cluster = 0;                    // CTAs of the tracker's thread-block cluster (tracker_lm_mode = 0), chosen at first use
+    bool k1_attr_set = false, k8_attr_set = false;   // opt-in dynamic shared memory set for this ctx's device
+    int sm_count = 148;                     // multiprocessors of the ctx's device
+    // calls on one ctx are serialised: the reference's tracking thread (trackMutex) and mapping thread (mapMutex) may both
+    // hold a pointer to it, and the two trackers, the pinned scratch and the profile lists are shared state
+    std::recursive_mutex mu;
     WindowDev win;
     void* selector = nullptr;               // SelectorDev (a2_selector.cu), created on first use
     void* immature = nullptr;               // ImmatureDev (k56_immature.cu), created on first use
@@ -117,6 +123,15 @@ struct ldso_gpu_ctx {
         err = what + buf;
     }
 };
+
+// first statement of every entry point that takes a ctx: serialise on the ctx and make its device current for the calling
+// thread (cudaSetDevice is per thread; a second host thread would otherwise run against device 0)
+#define LDSO_ENTER(ctx)                                               \
+    std::lock_guard<std::recursive_mutex> ldso_enter_guard((ctx)->mu); \
+    do {                                                              \
+        int ldso_cur_dev = -1;                                        \
+        if (cudaGetDevice(&ldso_cur_dev) != cudaSuccess || ldso_cur_dev != (ctx)->cfg.device) cudaSetDevice((ctx)->cfg.device); \
+    } while (0)
 
 // every host<->device copy of the library goes through here so that the traffic is accounted
 inline cudaError_t ldso_copy(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {

@@ -173,8 +173,10 @@ int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
     prof_begin(c, c->stream);
 #define K1_LAUNCH(LV)                                                                                                          \
     case LV: {                                                                                                                 \
-        static bool attr_set = false;                                                                                          \
-        if (!attr_set) { cudaFuncSetAttribute(k1_pyramid_kernel<LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr_set = true; } \
+        if (!c->k1_attr_set) { /* per ctx = per device: the attribute belongs to the device the ctx lives on */             \
+            LDSO_CUDA_OK(c, cudaFuncSetAttribute(k1_pyramid_kernel<LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));  \
+            c->k1_attr_set = true;                                                                                             \
+        }                                                                                                                      \
         k1_pyramid_kernel<LV><<<grid, K1_THREADS, smem, c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p);             \
     } break;
     switch (c->levels) {

@@ -47,10 +47,15 @@ __global__ void k2_dilate_kernel(float* __restrict__ idepth, float* __restrict__
     else { o0 = 1; o1 = -1; o2 = wl; o3 = -wl; }
     float sum = 0, num = 0, numn = 0;
     float b;
-    b = ws_bak[i + o0]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o0]); num = __fadd_rn(num, b); numn++; }
-    b = ws_bak[i + o1]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o1]); num = __fadd_rn(num, b); numn++; }
-    b = ws_bak[i + o2]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o2]); num = __fadd_rn(num, b); numn++; }
-    b = ws_bak[i + o3]; if (b > 0) { sum = __fadd_rn(sum, idepth[i + o3]); num = __fadd_rn(num, b); numn++; }
+    // the diagonal neighbours of the first cell of row 1 and of the last cell of row h-2 fall one element outside the
+    // plane (the reference reads past its arrays there, CoarseTracker.cc:437-466; those two cells never reach the point
+    // cloud): a neighbour outside [0, w h) counts as weight 0
+    const int n = wl * hl;
+    auto wgt = [&](int j) { return (j >= 0 && j < n) ? ws_bak[j] : 0.f; };
+    b = wgt(i + o0); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o0]); num = __fadd_rn(num, b); numn++; }
+    b = wgt(i + o1); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o1]); num = __fadd_rn(num, b); numn++; }
+    b = wgt(i + o2); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o2]); num = __fadd_rn(num, b); numn++; }
+    b = wgt(i + o3); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o3]); num = __fadd_rn(num, b); numn++; }
     if (numn > 0) {
         idepth[i] = __fdiv_rn(sum, numn);
         ws[i] = __fdiv_rn(num, numn);

@@ -1315,7 +1315,10 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
     if (c->cfg.tracker_lm_mode != 2) {
         // one thread-block cluster per tracker (ordinary launch: trackers of other sequences run beside it)
         if (c->trk_cluster == 0) {
-            int want = CL_MAX;
+            // 8 CTAs (the portable cluster size): measured on B200, one sequence tracks as fast on 8 CTAs as on 16 (the
+            // evaluation is latency-, not throughput-bound), and 8-CTA clusters of several sequences pack better into the
+            // GPCs (8 sequences: 15.2 k frames/s against 12.6 k with 16-CTA clusters)
+            int want = 8;
             if (const char* e = getenv("LDSO_LM_CLUSTER")) want = atoi(e);   // tuning knob: 1, 2, 4, 8 or 16 CTAs
             LDSO_CUDA_OK(c, cudaFuncSetAttribute(k34_track_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
             for (; want >= 1; want >>= 1) {
@@ -1411,6 +1414,7 @@ static int noalloc_scratch(ldso_gpu_ctx* c, unsigned char** out) {
 extern "C" int ldso_gpu_tracker_calc_res_noalloc(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, int lvl,
                                                  const double ref_to_new[12], float aff_a, float aff_b, float cutoff_th,
                                                  float out6[6], double sums52[52]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels);
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && ref_to_new && out6);
     const TrackerDev& T = c->trk[tracker];

@@ -592,7 +592,11 @@ ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     ok = ok && cudaEventCreateWithFlags(&P->ev_ready, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&P->ev_done, cudaEventDisableTiming) == cudaSuccess;
     c->immature = P;
-    if (!ok) { c->set_error("immature pool allocation failed", __FILE__, __LINE__); return nullptr; }
+    if (!ok) {   // free what was allocated and leave no half-built pool behind
+        immature_free(c);
+        c->set_error("immature pool allocation failed", __FILE__, __LINE__);
+        return nullptr;
+    }
     return P;
 }
 
@@ -616,6 +620,7 @@ void immature_free(ldso_gpu_ctx* c) {
 
 extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const float* u, const float* v, float* color,
                                         float* weights, float* grad_h, float* energy_th) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && n <= P->cap);
@@ -643,6 +648,7 @@ extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const 
 extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, const float* u, const float* v, const float* color,
                                      const float* weights, const float* grad_h, const float* energy_th, const float* idepth_min,
                                      const float* idepth_max, const float* quality, const int* status) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n >= 0 && n <= P->cap);
@@ -716,6 +722,7 @@ static int trace_launch(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float*
 
 extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
                                        const float* aff, int counts_out[6]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, counts_out);
     if (trace_launch(c, new_slot, n_hosts, KRKi, Kt, aff, false)) return -1;
     return ldso_gpu_immature_trace_counts(c, counts_out);
@@ -723,10 +730,12 @@ extern "C" int ldso_gpu_immature_trace(ldso_gpu_ctx* c, int new_slot, int n_host
 
 extern "C" int ldso_gpu_immature_trace_async(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float* KRKi, const float* Kt,
                                              const float* aff) {
+    LDSO_ENTER(c);
     return trace_launch(c, new_slot, n_hosts, KRKi, Kt, aff, true);
 }
 
 extern "C" int ldso_gpu_immature_trace_counts(ldso_gpu_ctx* c, int counts_out[6]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, counts_out);
     if (immature_trace_finalize(c)) return -1;
     ImmatureDev* P = immature_pool(c);
@@ -737,6 +746,7 @@ extern "C" int ldso_gpu_immature_trace_counts(ldso_gpu_ctx* c, int counts_out[6]
 
 extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* idepth_max, float* quality, int* status,
                                      float* last_trace_uv, float* last_trace_pixel_interval) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     const size_t N = P->n;
@@ -762,6 +772,7 @@ extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* 
 
 extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int* cand, int min_obs, float* idepth_out,
                                           int* ok_out, int* res_state_out) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     WindowDev& W = c->win;
@@ -803,6 +814,7 @@ static PoolPtrs pool_ptrs(ImmatureDev* P, bool alt) {
 
 extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int drop_oob, int n_remove, const int* remove_idx,
                                          int* n_out) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n_remove >= 0 && n_remove <= P->n && (n_remove == 0 || remove_idx) && n_out);
@@ -837,6 +849,7 @@ extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int dro
 
 extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx, int n, const float* u, const float* v,
                                         int* n_pool) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && P->n + n <= P->cap && n_pool);

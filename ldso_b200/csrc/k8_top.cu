@@ -332,10 +332,9 @@ int k8_accumulate_top(ldso_gpu_ctx* c, int marg) {
         A.res_pt = W.res_pt; A.acc_top = W.acc_top; A.acc_cnt = W.acc_top_cnt;
         prof_begin(c, c->stream);
         if (W.chunk_len > K8_THREADS) {
-            static bool attr_set = false;
-            if (!attr_set) {
+            if (!c->k8_attr_set) {   // per ctx = per device
                 LDSO_CUDA_OK(c, cudaFuncSetAttribute(k8_top_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K8_STREAM_SMEM));
-                attr_set = true;
+                c->k8_attr_set = true;
             }
             k8_top_stream_kernel<<<W.n_chunks, K8_THREADS, K8_STREAM_SMEM, c->stream>>>(A, W.chunk, W.order);
         } else {

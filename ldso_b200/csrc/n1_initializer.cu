@@ -675,6 +675,7 @@ void initializer_free(ldso_gpu_ctx* c) {
 
 // ---- setFirst (:656-737) --------------------------------------------------------------------------------------------
 extern "C" int ldso_gpu_init_set_first(ldso_gpu_ctx* c, int slot, int* num_points_out) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && num_points_out);
     InitDev* I = init_state(c);
     if (!I) return -1;
@@ -776,6 +777,7 @@ extern "C" int ldso_gpu_init_set_first(ldso_gpu_ctx* c, int slot, int* num_point
 extern "C" int ldso_gpu_init_track_frame(ldso_gpu_ctx* c, int slot, float exposure_first, float exposure_new, double pose_out[12],
                                          float aff_out[2], int* snapped_out, int* ready, float latest_res[3],
                                          int iters_out[LDSO_MAX_LEVELS]) {
+    LDSO_ENTER(c);
     InitDev* I = (InitDev*)c->initializer;
     LDSO_REQUIRE(c, I && I->first_slot >= 0 && slot >= 0 && slot < c->cfg.n_frame_slots && pose_out && aff_out && snapped_out && ready);
     I->new_slot = slot;
@@ -902,6 +904,7 @@ extern "C" int ldso_gpu_init_track_frame(ldso_gpu_ctx* c, int slot, float exposu
 
 extern "C" int ldso_gpu_init_get_points(ldso_gpu_ctx* c, int lvl, int* n, float* u, float* v, float* idepth, float* iR,
                                         unsigned char* is_good, float* my_type, float* last_hessian, float* energy) {
+    LDSO_ENTER(c);
     InitDev* I = (InitDev*)c->initializer;
     LDSO_REQUIRE(c, I && lvl >= 0 && lvl < I->levels && n);
     InitLevel& L = I->lv[lvl];
@@ -925,6 +928,7 @@ extern "C" int ldso_gpu_init_get_points(ldso_gpu_ctx* c, int lvl, int* n, float*
 }
 
 extern "C" int ldso_gpu_init_get_graph(ldso_gpu_ctx* c, int lvl, int* neighbours, int* parent) {
+    LDSO_ENTER(c);
     InitDev* I = (InitDev*)c->initializer;
     LDSO_REQUIRE(c, I && lvl >= 0 && lvl < I->levels && neighbours && parent);
     InitLevel& L = I->lv[lvl];
@@ -934,6 +938,7 @@ extern "C" int ldso_gpu_init_get_graph(ldso_gpu_ctx* c, int lvl, int* neighbours
 
 extern "C" int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* c, int slot, int lvl, const double ref_to_new[12], float aff_a, float aff_b,
                                              float H[64], float b[8], float Hsc[64], float bsc[8], float res[3]) {
+    LDSO_ENTER(c);
     InitDev* I = (InitDev*)c->initializer;
     LDSO_REQUIRE(c, I && I->first_slot >= 0 && lvl >= 0 && lvl < I->levels && slot >= 0 && slot < c->cfg.n_frame_slots);
     I->new_slot = slot;

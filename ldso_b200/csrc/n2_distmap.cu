@@ -190,15 +190,43 @@ __device__ __forceinline__ void stamp_source(unsigned char* D, int c0, int R, in
     }
 }
 
-__global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
+// stamp_source by the whole CTA (interior box, then the border ring where the box reaches it)
+template <int T> __device__ __forceinline__ void stamp_source_cta(unsigned char* D, int c0, int R, int w1, int h1) {
+    const int sy = c0 / w1, sx = c0 - sy * w1;
+    if (threadIdx.x == 0) D[c0] = 0;
+    if (sx == 0 || sy == 0 || sx == w1 - 1 || sy == h1 - 1 || R <= 0) return;   // uniform
+    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R), ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
+    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
+    for (int t = threadIdx.x; t < nc; t += T) {
+        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
+        const int d = ring_dist(x - sx, y - sy);
+        const int idx = x + w1 * y;
+        if (d <= R && D[idx] > d) D[idx] = (unsigned char)d;   // the source cell itself: d = 0
+    }
+    if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {   // uniform
+        __syncthreads();
+        const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
+        const int bbw = bx1 - bx0 + 1, nbc = bbw * (by1 - by0 + 1);
+        for (int t = threadIdx.x; t < nbc; t += T) {
+            const int ty = t / bbw, x = bx0 + (t - ty * bbw), y = by0 + ty;
+            if (!(x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1)) continue;
+            const int v = border_value(D, x, y, w1, h1);
+            if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
+        }
+    }
+}
+
+constexpr int N2_SEL_THREADS = 256;   // the walk meets at a CTA barrier per accepted point: a small CTA keeps that cheap
+
+__global__ void __launch_bounds__(N2_SEL_THREADS) n2_select_kernel(const N2Sel p) {
     extern __shared__ __align__(16) unsigned char D[];
-    __shared__ int s_acc, s_del;
+    __shared__ int s_acc, s_del, s_c0;
     __shared__ unsigned s_thmax;
     const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
     {
         uint4* d4 = reinterpret_cast<uint4*>(D);
         const uint4* g4 = reinterpret_cast<const uint4*>(p.dmap);
-        for (int i = threadIdx.x; i < cells16; i += N2_THREADS) d4[i] = g4[i];
+        for (int i = threadIdx.x; i < cells16; i += N2_SEL_THREADS) d4[i] = g4[i];
     }
     if (threadIdx.x == 0) { s_acc = 0; s_del = 0; s_thmax = 0u; }
     __syncthreads();
@@ -207,7 +235,7 @@ __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
     const float* flagged = skip + p.n_hosts;
     int ndel = 0;
     float thmax = 0.f;
-    for (int i = threadIdx.x; i < p.n; i += N2_THREADS) {
+    for (int i = threadIdx.x; i < p.n; i += N2_SEL_THREADS) {
         const int h = p.host[i];
         int act = 0, cell = -1;
         float fr = 0.f, th = 0.f;
@@ -243,61 +271,70 @@ __global__ void __launch_bounds__(N2_THREADS) n2_select_kernel(const N2Sel p) {
     if (ndel) atomicAdd(&s_del, ndel);
     if (thmax > 0.f) atomicMax(&s_thmax, __float_as_uint(thmax));
     __syncthreads();
-    // ---- the ordered walk, warp 0
-    if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        const float tm = __uint_as_float(s_thmax);
-        const int R = tm >= (float)N2_RMAX ? N2_RMAX : min(N2_RMAX, (int)ceilf(tm) + 1);
-        const int n0 = *p.src_n;
-        int nacc = 0;
-        // A corner cell has ONE interior neighbour, a diagonal one, which can claim it only on an odd ring.  The
-        // reference's incremental BFS therefore leaves a corner at the best value that neighbour ever offered while the
-        // walk lowered it — not a function of the final map.  Lanes 0..3 follow one corner each.
-        const int kx = (lane & 1) ? p.w1 - 1 : 0, ky = (lane & 2) ? p.h1 - 1 : 0;
-        const int qx = (lane & 1) ? p.w1 - 2 : 1, qy = (lane & 2) ? p.h1 - 2 : 1;
-        int cv = 255, qv = 255;
-        if (lane < 4) { cv = D[kx + p.w1 * ky]; qv = D[qx + p.w1 * qy]; }
-        int cell = lane < p.n ? p.cell[lane] : -1;
-        float fr = lane < p.n ? p.frac[lane] : 0.f, th = lane < p.n ? p.thr[lane] : 0.f;
-        for (int base = 0; base < p.n; base += 32) {
-            const int i = base + lane, inext = i + 32;
-            // next chunk's operands are in flight while this one is walked
-            const int cell_n = inext < p.n ? p.cell[inext] : -1;
-            const float fr_n = inext < p.n ? p.frac[inext] : 0.f, th_n = inext < p.n ? p.thr[inext] : 0.f;
-            int from = 0;
-            while (true) {
+    // ---- the ordered walk: warp 0 decides, in pool order, which candidate is accepted next; the whole CTA stamps it
+    const bool walker = threadIdx.x < 32;
+    const int lane = threadIdx.x & 31;
+    const float tm = __uint_as_float(s_thmax);
+    const int R = tm >= (float)N2_RMAX ? N2_RMAX : min(N2_RMAX, (int)ceilf(tm) + 1);
+    const int n0 = *p.src_n;
+    int nacc = 0;
+    // A corner cell has ONE interior neighbour, a diagonal one, which can claim it only on an odd ring.  The
+    // reference's incremental BFS therefore leaves a corner at the best value that neighbour ever offered while the
+    // walk lowered it — not a function of the final map.  Lanes 0..3 of the walker follow one corner each.
+    const int kx = (lane & 1) ? p.w1 - 1 : 0, ky = (lane & 2) ? p.h1 - 1 : 0;
+    const int qx = (lane & 1) ? p.w1 - 2 : 1, qy = (lane & 2) ? p.h1 - 2 : 1;
+    int cv = 255, qv = 255;
+    if (walker && lane < 4) { cv = D[kx + p.w1 * ky]; qv = D[qx + p.w1 * qy]; }
+    int cell = (walker && lane < p.n) ? p.cell[lane] : -1;
+    float fr = (walker && lane < p.n) ? p.frac[lane] : 0.f, th = (walker && lane < p.n) ? p.thr[lane] : 0.f;
+    for (int base = 0; base < p.n; base += 32) {
+        const int i = base + lane, inext = i + 32;
+        // next chunk's operands are in flight while this one is walked
+        int cell_n = -1;
+        float fr_n = 0.f, th_n = 0.f;
+        if (walker && inext < p.n) { cell_n = p.cell[inext]; fr_n = p.frac[inext]; th_n = p.thr[inext]; }
+        int from = 0;
+        while (true) {
+            if (walker) {
                 bool pass = false;
-                if (cell >= 0 && lane >= from) {
+                if (from < 32 && cell >= 0 && lane >= from) {
                     const unsigned char d = D[cell];
                     const float dist = (d == 255 ? 1000.f : (float)d) + fr;
                     pass = dist >= th;
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, pass);
-                if (!m) break;
-                const int j = __ffs(m) - 1;
-                const int c0 = __shfl_sync(0xffffffffu, cell, j);
-                if (lane == j) { p.action[i] = 2; p.src_cells[n0 + nacc] = c0; }
-                nacc++;
-                from = j + 1;
-                stamp_source(D, c0, R, p.w1, p.h1, lane);
-                if (lane < 4) {
-                    const int sy = c0 / p.w1, sx = c0 - sy * p.w1;
-                    if (sx == kx && sy == ky) cv = 0;
-                    if (sx > 0 && sy > 0 && sx < p.w1 - 1 && sy < p.h1 - 1) {
-                        qv = min(qv, ring_dist(qx - sx, qy - sy));
-                        const int cand = qv + 1;
-                        if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
-                    }
-                    if (cv < D[kx + p.w1 * ky]) D[kx + p.w1 * ky] = (unsigned char)cv;
+                int c0 = -1;
+                if (m) {
+                    const int j = __ffs(m) - 1;
+                    c0 = __shfl_sync(0xffffffffu, cell, j);
+                    if (lane == j) { p.action[i] = 2; p.src_cells[n0 + nacc] = c0; }
+                    nacc++;
+                    from = j + 1;
                 }
-                __syncwarp();
-                if (from >= 32) break;
+                if (lane == 0) s_c0 = c0;
             }
-            cell = cell_n; fr = fr_n; th = th_n;
+            __syncthreads();
+            const int c0 = s_c0;
+            if (c0 < 0) break;                       // uniform: the chunk is done
+            stamp_source_cta<N2_SEL_THREADS>(D, c0, R, p.w1, p.h1);
+            __syncthreads();
+            if (walker && lane < 4) {
+                const int sy = c0 / p.w1, sx = c0 - sy * p.w1;
+                if (sx == kx && sy == ky) cv = 0;
+                if (sx > 0 && sy > 0 && sx < p.w1 - 1 && sy < p.h1 - 1) {
+                    qv = min(qv, ring_dist(qx - sx, qy - sy));
+                    const int cand = qv + 1;
+                    if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
+                }
+                if (cv < D[kx + p.w1 * ky]) D[kx + p.w1 * ky] = (unsigned char)cv;
+            }
+            __syncthreads();                         // the corner cells are part of the map the next test reads
         }
-        if (lane == 0) { s_acc = nacc; *p.src_n = n0 + nacc; }
-        if (lane < 4) p.corner[lane] = cv;
+        __syncthreads();                             // everyone has read s_c0 before the next chunk overwrites it
+        cell = cell_n; fr = fr_n; th = th_n;
     }
+    if (threadIdx.x == 0) { s_acc = nacc; *p.src_n = n0 + nacc; }
+    if (walker && lane < 4) p.corner[lane] = cv;
     __syncthreads();
     if (threadIdx.x == 0) { p.cnt[0] = s_acc; p.cnt[1] = s_del; }
 }
@@ -342,6 +379,7 @@ int launch_map(ldso_gpu_ctx* c, ImmatureDev* P, bool after_walk) {
 }  // namespace
 
 extern "C" int ldso_gpu_immature_set_types(ldso_gpu_ctx* c, int first, int n, const float* type) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, first >= 0 && n >= 0 && first + n <= P->n && (n == 0 || type));
@@ -358,6 +396,7 @@ extern "C" int ldso_gpu_immature_set_types(ldso_gpu_ctx* c, int first, int n, co
 
 extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* KRKi, const float* Kt, int n_points,
                                      const int* host, const float* u, const float* v, const float* idepth) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt && n_points >= 0 && c->levels >= 2);
@@ -387,6 +426,7 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
 }
 
 extern "C" int ldso_gpu_distmap_get(ldso_gpu_ctx* c, float* dist) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, dist && c->levels >= 2);
@@ -403,6 +443,7 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
                                                    const unsigned char* host_skip, const unsigned char* host_flagged,
                                                    float current_min_act_dist, float min_trace_quality,
                                                    unsigned char* action_out, int counts_out[2]) {
+    LDSO_ENTER(c);
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
     LDSO_REQUIRE(c, n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt && host_skip && host_flagged && counts_out);
@@ -425,7 +466,7 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     rc = set_smem(c, (const void*)n2_select_kernel, smem);
     if (rc) return rc;
     prof_begin(c, c->stream);
-    n2_select_kernel<<<1, N2_THREADS, smem, c->stream>>>(p);
+    n2_select_kernel<<<1, N2_SEL_THREADS, smem, c->stream>>>(p);
     prof_end(c, c->stream, LDSO_PROF_N2SEL, P->n);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());

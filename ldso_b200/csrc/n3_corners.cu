@@ -156,6 +156,7 @@ void corners_free(ldso_gpu_ctx* c) {
 
 extern "C" int ldso_gpu_detect_corners(ldso_gpu_ctx* c, int slot, int nFeatures, int max_out, float* ox, float* oy, float* oscore,
                                        unsigned char* is_corner, int* n_out, int* n_corners) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && nFeatures > 0 && max_out > 0 && ox && oy && oscore && is_corner && n_out && n_corners);
     const int w = c->wG[0], h = c->hG[0];
     N3Geom G;

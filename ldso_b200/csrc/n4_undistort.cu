@@ -75,6 +75,7 @@ void undistort_free(ldso_gpu_ctx* c) {
 
 extern "C" int ldso_gpu_undistort_set(ldso_gpu_ctx* c, int w_org, int h_org, int g_depth, const float* G, const float* vignette_inv,
                                       const float* remap_x, const float* remap_y, int photometric_mode) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, w_org > 0 && h_org > 0 && (G == nullptr || g_depth == 256 || g_depth == 65536));
     LDSO_REQUIRE(c, (remap_x == nullptr) == (remap_y == nullptr));
     LDSO_REQUIRE(c, remap_x != nullptr || (w_org == c->cfg.w && h_org == c->cfg.h));
@@ -100,6 +101,7 @@ extern "C" int ldso_gpu_undistort_set(ldso_gpu_ctx* c, int w_org, int h_org, int
 
 extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
                                               float factor) {
+    LDSO_ENTER(c);
     UndistortDev* U = (UndistortDev*)c->undistort;
     LDSO_REQUIRE(c, U && U->raw && raw && slot >= 0 && slot < c->cfg.n_frame_slots && (bytes_per_pixel == 1 || bytes_per_pixel == 2));
     LDSO_REQUIRE(c, !(U->has_G && bytes_per_pixel == 2 && U->g_depth != 65536));
@@ -130,6 +132,7 @@ extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const v
 }
 
 extern "C" int ldso_gpu_undistort_get_image(ldso_gpu_ctx* c, float* image_out) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, image_out);
     const size_t bytes = sizeof(float) * (size_t)c->cfg.w * c->cfg.h;
     LDSO_CUDA_OK(c, ldso_copy(c, c->scratch_host, c->img_dev, bytes, cudaMemcpyDeviceToHost, c->stream));

@@ -11,15 +11,6 @@
 
 #define CPARS 4
 
-static int sm_count() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
-    }
-    return sms;
-}
-
 namespace {
 
 template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
@@ -111,6 +102,7 @@ void win_free(ldso_gpu_ctx* c) {
 // ---- window description --------------------------------------------------------------------------
 extern "C" int ldso_gpu_window_set_frames(ldso_gpu_ctx* c, int n, const int* slots, const float* precalc, const float* eth,
                                           const float calib[4]) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, n >= 1 && n <= LDSO_MAX_WINDOW && slots && precalc && eth && calib);
     WindowDev& W = c->win;
     for (int i = 0; i < n; i++) {
@@ -127,6 +119,7 @@ extern "C" int ldso_gpu_window_set_frames(ldso_gpu_ctx* c, int n, const int* slo
 extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* u, const float* v, const float* idepth,
                                           const float* idepth_zero, const int* host, const float* color, const float* weights,
                                           const float* prior, const int* res_begin) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, np >= 0 && np <= W.cap_p && W.n > 0);
     LDSO_REQUIRE(c, np == 0 || (u && v && idepth && idepth_zero && host && color && weights && prior && res_begin));
@@ -148,7 +141,7 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     // once that still leaves two CTAs per SM (batched windows): the cross-group fold and the ~3 k fp64 atomics of the
     // flush are paid per CTA (64x window on B200: 150 us at 64 points per CTA, 95 us at 448)
     int per = 64;
-    const int slots = 2 * sm_count() - LDSO_MAX_WINDOW;                    // every host frame may add one short block
+    const int slots = 2 * c->sm_count - LDSO_MAX_WINDOW;                    // every host frame may add one short block
     if (np > 64 * slots) per = std::min(1024, ((np + slots - 1) / slots + 63) / 64 * 64);   // one wave: no tail
     if (const char* e = getenv("LDSO_K9_BLOCK")) per = atoi(e);            // tuning knob of profiles/kernel_bench.py
     std::vector<int> blk;
@@ -182,7 +175,7 @@ static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
     // 96 k residuals 22.9 us at 128 vs 16.5 us at 384; 769 k residuals flat from 384 to 1024)
     const int total = cnt[2 * nn];
     int clen = 128;
-    if (total > 128 * 2 * sm_count()) clen = std::min(1024, std::max(384, total / (8 * sm_count()) / 128 * 128));
+    if (total > 128 * 2 * c->sm_count) clen = std::min(1024, std::max(384, total / (8 * c->sm_count) / 128 * 128));
     if (const char* e = getenv("LDSO_K8_CHUNK")) clen = atoi(e);           // tuning knob of profiles/kernel_bench.py
     W.chunk_len = clen;
     for (int k = 0; k < 2 * nn; k++)
@@ -197,6 +190,7 @@ static int build_order(ldso_gpu_ctx* c, const unsigned char* only = nullptr) {
 
 extern "C" int ldso_gpu_window_set_residuals(ldso_gpu_ctx* c, int nr, const int* target, const int* state,
                                              const unsigned char* flags, const float* res_to_zero) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, nr >= 0 && nr <= W.cap_r && (int)W.h_res_begin.size() == W.np + 1 && W.h_res_begin[W.np] == nr);
     LDSO_REQUIRE(c, nr == 0 || (target && state && flags));
@@ -234,6 +228,7 @@ extern "C" int ldso_gpu_window_set_residuals(ldso_gpu_ctx* c, int nr, const int*
 extern "C" int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* c, const double* adH, const double* adT, const float* adHTdelta,
                                             const float cDelta[4], const double cPrior[4], const double* fprior,
                                             const double* fdelta_prior) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && adH && adT && adHTdelta && cDelta && cPrior && fprior && fdelta_prior);
     const int nn = W.n * W.n;
@@ -253,6 +248,7 @@ extern "C" int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* c, const double* adH, 
 }
 
 extern "C" int ldso_gpu_window_set_idepth(ldso_gpu_ctx* c, const float* idepth, const float* idepth_zero) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, idepth && idepth_zero);
     int rc = upload(c, W.idepth, idepth, sizeof(float) * W.np);
@@ -262,6 +258,7 @@ extern "C" int ldso_gpu_window_set_idepth(ldso_gpu_ctx* c, const float* idepth, 
 
 // ---- K7 ------------------------------------------------------------------------------------------
 extern "C" int ldso_gpu_window_linearize(ldso_gpu_ctx* c, int fix, double stats[3], float* new_th) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && stats);
     int rc = k7_linearize(c, fix);
@@ -299,10 +296,13 @@ extern "C" int ldso_gpu_window_linearize(ldso_gpu_ctx* c, int fix, double stats[
     return 0;
 }
 
-extern "C" int ldso_gpu_window_apply_res(ldso_gpu_ctx* c) { return k7_apply_res(c); }
-extern "C" int ldso_gpu_window_reset_oob(ldso_gpu_ctx* c) { return k7_reset_oob(c); }
+extern "C" int ldso_gpu_window_apply_res(ldso_gpu_ctx* c) {
+    LDSO_ENTER(c); return k7_apply_res(c); }
+extern "C" int ldso_gpu_window_reset_oob(ldso_gpu_ctx* c) {
+    LDSO_ENTER(c); return k7_reset_oob(c); }
 
 extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned char* mask) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, mask || W.nr == 0);
     if (W.nr == 0) return 0;
@@ -321,6 +321,7 @@ extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned
 // ---- K8 + K9 + stitching (h1_stitch.cu) --------------------------------------------------------------
 extern "C" int ldso_gpu_window_accumulate(ldso_gpu_ctx* c, double* HA, double* bA, double* HL, double* bL, double* Hsc,
                                           double* bsc, int counts[2]) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && HA && bA && HL && bL && Hsc && bsc);
     LDSO_REQUIRE(c, (int)W.adHost.size() == 64 * W.n * W.n);
@@ -395,6 +396,7 @@ void project_out_nullspace(int D, const double* Nin, int k, double* x) {
 extern "C" int ldso_gpu_window_solve(ldso_gpu_ctx* c, int iteration, double lambda, const double* HA, const double* bA,
                                      const double* HL, const double* bL, const double* Hsc, const double* bsc, const double* HM,
                                      const double* bM, const double* delta, const double* N, int n_null, double* x_out) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && HA && bA && HL && bL && Hsc && bsc && HM && bM && delta && x_out);
     const int D = 8 * W.n + CPARS;
@@ -427,6 +429,7 @@ extern "C" int ldso_gpu_window_solve(ldso_gpu_ctx* c, int iteration, double lamb
 
 // ---- K10 -----------------------------------------------------------------------------------------
 extern "C" int ldso_gpu_window_resubstitute(ldso_gpu_ctx* c, const double* x, float lambda, float* step_out) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && x && (int)W.adHostF.size() == 64 * W.n * W.n);
     const int n = W.n;
@@ -456,6 +459,7 @@ extern "C" int ldso_gpu_window_resubstitute(ldso_gpu_ctx* c, const double* x, fl
 
 // ---- read-backs -----------------------------------------------------------------------------------
 extern "C" int ldso_gpu_window_get_residual_floats(ldso_gpu_ctx* c, int what, float* dst) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, dst && what >= 0 && what <= 6);
     const size_t nr = W.nr;
@@ -476,6 +480,7 @@ extern "C" int ldso_gpu_window_get_residual_floats(ldso_gpu_ctx* c, int what, fl
 }
 
 extern "C" int ldso_gpu_window_get_residual_ints(ldso_gpu_ctx* c, int what, int* dst) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, dst && what >= 0 && what <= 2);
     const int* src = what == 0 ? W.state : what == 1 ? W.new_state : W.flags;
@@ -483,6 +488,7 @@ extern "C" int ldso_gpu_window_get_residual_ints(ldso_gpu_ctx* c, int what, int*
 }
 
 extern "C" int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* c, int what, float* dst) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, dst && what >= 0 && what <= 11);
     const size_t np = W.np, cap = W.cap_p;
@@ -510,6 +516,40 @@ extern "C" int ldso_gpu_window_get_point_floats(ldso_gpu_ctx* c, int what, float
         case 10: return download(c, dst, W.num_good, sizeof(float) * np);
         default: return row(PT_STEP, dst);
     }
+}
+
+// what FullSystem reads after linearizeAll(true) (states -> lastResiduals, centerProjectedTo + HdiF -> makeCoarseDepthL0,
+// idepth_hessian / numGoodResiduals -> flagPointsForRemoval): ONE staged device->host copy sequence and one sync
+extern "C" int ldso_gpu_window_get_keyframe_results(ldso_gpu_ctx* c, int* state, float* center3, float* hdi, float* idepth_hessian,
+                                                    float* num_good, float* max_rel_baseline) {
+    LDSO_ENTER(c);
+    WindowDev& W = c->win;
+    const size_t nr = W.nr, np = W.np, cap = W.cap_p;
+    const size_t bytes = nr * (sizeof(int) + 4 * sizeof(float)) + 4 * np * sizeof(float) + 64;
+    char* st = (char*)staging(c, bytes);
+    LDSO_REQUIRE(c, st != nullptr);
+    int* h_state = (int*)st;
+    float* h_center = (float*)(h_state + nr);
+    float* h_pt = h_center + 4 * nr;
+    if (nr) {
+        LDSO_CUDA_OK(c, ldso_copy(c, h_state, W.state, sizeof(int) * nr, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, ldso_copy(c, h_center, W.center, sizeof(float) * 4 * nr, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (np) {
+        LDSO_CUDA_OK(c, ldso_copy(c, h_pt, W.pt_out + (size_t)PT_HDI * cap, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, ldso_copy(c, h_pt + np, W.pt_out + (size_t)PT_IDH * cap, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, ldso_copy(c, h_pt + 2 * np, W.num_good, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, ldso_copy(c, h_pt + 3 * np, W.max_rel_baseline, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
+    }
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    W.pinned_off = 0;
+    if (state) memcpy(state, h_state, sizeof(int) * nr);
+    if (center3) for (size_t r = 0; r < nr; r++) { center3[3 * r] = h_center[4 * r]; center3[3 * r + 1] = h_center[4 * r + 1]; center3[3 * r + 2] = h_center[4 * r + 2]; }
+    if (hdi) memcpy(hdi, h_pt, sizeof(float) * np);
+    if (idepth_hessian) memcpy(idepth_hessian, h_pt + np, sizeof(float) * np);
+    if (num_good) memcpy(num_good, h_pt + 2 * np, sizeof(float) * np);
+    if (max_rel_baseline) memcpy(max_rel_baseline, h_pt + 3 * np, sizeof(float) * np);
+    return 0;
 }
 
 // ---- marginalisation + energies (EnergyFunctional.cc:109-262, :473-497) -----------------------------
@@ -544,6 +584,7 @@ void invert_pos_def8(const double* M, double* res) {
 
 extern "C" int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* c, const unsigned char* marg, float fac, double* H, double* b,
                                                   int* n_res) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && H && b && (marg || W.np == 0));
     LDSO_REQUIRE(c, (int)W.adHost.size() == 64 * W.n * W.n);
@@ -584,6 +625,7 @@ extern "C" int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* c, const unsigne
 extern "C" int ldso_gpu_window_marginalize_frame(ldso_gpu_ctx* c, int n, int idx, const double* HMin, const double* bMin,
                                                  const double prior[8], const double delta_prior[8], double* HM_out,
                                                  double* bM_out) {
+    LDSO_ENTER(c);
     LDSO_REQUIRE(c, n >= 1 && n <= LDSO_MAX_WINDOW && idx >= 0 && idx < n && HMin && bMin && prior && delta_prior && HM_out && bM_out);
     const int odim = 8 * n + CPARS, ndim = odim - 8;
     // permutation that moves the frame's 8 rows/cols to the end, keeping the order of the rest (:127-146)
@@ -638,6 +680,7 @@ extern "C" int ldso_gpu_window_marginalize_frame(ldso_gpu_ctx* c, int n, int idx
 
 extern "C" int ldso_gpu_window_calc_energy(ldso_gpu_ctx* c, const double* HM, const double* bM, const double* delta,
                                            double energy[2]) {
+    LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && HM && bM && delta && energy && (int)W.fprior.size() == 8 * W.n);
     const int D = 8 * W.n + CPARS;

@@ -15,7 +15,8 @@ CT = dict(frames=0, keyframes=1, marg_frames=2, marg_points=3, lin_residuals=4, 
 KF_LOG = ("rmse", "points", "residuals", "marg_points", "dropped_points", "lin_residuals", "activated", "marg_frames",
           "min_act_dist", "frame_energy_th", "ba_iterations", "hm_norm")
 PHASES = ("trackNewCoarse+makeImages", "traceNewCoarse", "activatePointsMT", "optimize", "marginalisation",
-          "makeNewTraces+setCoarseTrackingRef", "initializer", "other")
+          "makeNewTraces+setCoarseTrackingRef", "initializer", "other", "[makeImages call]", "[trackNewestCoarse calls]",
+          "[motion hypotheses]", "[unused]")
 
 
 class SystemConfig(C.Structure):
@@ -147,7 +148,7 @@ class System:
         return dict(zip(KF_LOG, out.tolist()))
 
     def phase_seconds(self):
-        out = np.zeros(8)
+        out = np.zeros(12)
         self.api.fn("system_get_phase_seconds")(self.h, out.ctypes.data_as(C.c_void_p))
         return dict(zip(PHASES, out.tolist()))
 
@@ -213,6 +214,22 @@ class Batch:
         for s in self.systems:
             s.n_fed += 1
         return self.status
+
+    def run_ptrs(self, ptrs, is_device=False, sync_after=True):
+        """ptrs[system][frame]: raw image pointers; every system consumes its frames in order without waiting for the others
+        between frames.  Returns status [n][n_frames][16] (a fresh array)."""
+        n, nf = len(self.systems), len(ptrs[0])
+        arr = (C.c_void_p * (n * nf))(*[p for row in ptrs for p in row])
+        status = np.zeros((n, nf, 16), np.int32)
+        f = self.api.fn("batch_run")
+        f.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        rc = f(self.h, nf, arr, 1 if is_device else 0, 1 if sync_after else 0, None, status.ctypes.data_as(C.c_void_p))
+        if rc < 0:
+            msgs = [s.api.fn("system_last_error")(s.h).decode() for s in self.systems]
+            raise capi.LdsoError(f"{self.api.prefix}batch_run rc={rc}: {[m for m in msgs if m]}")
+        for s in self.systems:
+            s.n_fed += nf
+        return status
 
     def close(self):
         if self.h:

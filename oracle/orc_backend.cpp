@@ -886,6 +886,19 @@ extern "C" int orc_window_get_point_floats(orc_ctx* c, int what, float* dst) {
     return 0;
 }
 
+// everything FullSystem reads after linearizeAll(true) in one call (the GPU library answers it with one device->host copy)
+extern "C" int orc_window_get_keyframe_results(orc_ctx* c, int* state, float* center3, float* hdi, float* idepth_hessian,
+                                               float* num_good, float* max_rel_baseline) {
+    int rc = 0;
+    if (state) rc |= orc_window_get_residual_ints(c, 0, state);
+    if (center3) rc |= orc_window_get_residual_floats(c, 3, center3);
+    if (hdi) rc |= orc_window_get_point_floats(c, 6, hdi);
+    if (idepth_hessian) rc |= orc_window_get_point_floats(c, 8, idepth_hessian);
+    if (num_good) rc |= orc_window_get_point_floats(c, 10, num_good);
+    if (max_rel_baseline) rc |= orc_window_get_point_floats(c, 9, max_rel_baseline);
+    return rc;
+}
+
 // ================================================================================================
 // EnergyFunctional::marginalizePointsF (EnergyFunctional.cc:205-262), single-threaded as in the reference
 extern "C" int orc_window_marginalize_points(orc_ctx* c, const unsigned char* marg, float fac, double* H, double* b, int* n_res) {

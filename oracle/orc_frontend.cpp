@@ -301,10 +301,14 @@ extern "C" int orc_tracker_set_ref(orc_ctx* c, int tracker, int ref_slot, int n_
         for (int i = w[lvl]; i < wh; i++) {
             if (weightSumsl_bak[i] <= 0) {
                 float sum = 0, num = 0, numn = 0;
-                if (weightSumsl_bak[i + o0] > 0) { sum += idepthl[i + o0]; num += weightSumsl_bak[i + o0]; numn++; }
-                if (weightSumsl_bak[i + o1] > 0) { sum += idepthl[i + o1]; num += weightSumsl_bak[i + o1]; numn++; }
-                if (weightSumsl_bak[i + o2] > 0) { sum += idepthl[i + o2]; num += weightSumsl_bak[i + o2]; numn++; }
-                if (weightSumsl_bak[i + o3] > 0) { sum += idepthl[i + o3]; num += weightSumsl_bak[i + o3]; numn++; }
+                // the reference reads one element before / after its arrays for the first cell of row 1 and the last cell of
+                // row h-2 (:437-466; cells that never reach the point cloud): a neighbour outside the plane counts as weight 0
+                const int nAll = w[lvl] * h[lvl];
+                auto wgt = [&](int j) { return (j >= 0 && j < nAll) ? weightSumsl_bak[j] : 0.f; };
+                if (wgt(i + o0) > 0) { sum += idepthl[i + o0]; num += weightSumsl_bak[i + o0]; numn++; }
+                if (wgt(i + o1) > 0) { sum += idepthl[i + o1]; num += weightSumsl_bak[i + o1]; numn++; }
+                if (wgt(i + o2) > 0) { sum += idepthl[i + o2]; num += weightSumsl_bak[i + o2]; numn++; }
+                if (wgt(i + o3) > 0) { sum += idepthl[i + o3]; num += weightSumsl_bak[i + o3]; numn++; }
                 if (numn > 0) { idepthl[i] = sum / numn; weightSumsl[i] = num / numn; }
             }
         }

