@@ -1,0 +1,26 @@
+"""Profiling target: ONE configs[1] sequence through ldso_gpu_system_add_active_frame; the steady-state frames (after
+bench.PRIME + 5) run between cudaProfilerStart / Stop, so `ncu --profile-from-start off` sees exactly the timed workload
+of bench.py's single_sequence leg (same frames, same keyframes)."""
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from ldso_b200 import capi, system  # noqa: E402
+
+steps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+data = bench.render_sequences([1001], bench.PRIME + 5 + steps + 1)
+import torch  # noqa: E402
+gpu = capi.load()
+pin = [torch.from_numpy(f).pin_memory() for f in data[1001][0]]
+s = system.System(gpu, bench.CALIB, npoints_counter_mode=bench.DENSITY_MODE)
+ctx = s.ctx()
+for k in range(bench.PRIME + 5):
+    s.add_frame_ptr(pin[k].data_ptr())
+ctx.sync()
+torch.cuda.profiler.start()
+nkf = 0
+for k in range(bench.PRIME + 5, bench.PRIME + 5 + steps):
+    nkf += int(s.add_frame_ptr(pin[k].data_ptr())[1])
+ctx.sync()
+torch.cuda.profiler.stop()
+print("profiled frames", steps, "keyframes", nkf, "launches total", ctx.launch_count())
