@@ -403,6 +403,16 @@ int ldso_gpu_window_resubstitute(ldso_gpu_ctx* ctx, const double* x, float lambd
  * the residuals of those points are inactive afterwards. */
 int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* ctx, const unsigned char* marg, float idepth_fix_prior_marg_fac,
                                        double* H, double* b, int* n_res);
+/* The marginalisation of a keyframe in one call, on the window that is already resident (the one the last
+ * ldso_gpu_window_linearize(fix = 1) ran on; nothing is uploaded again): for the points with point_mask != 0 the inner loop of
+ * FullSystem::flagPointsForRemoval (src/frontend/FullSystem.cc:1390-1399: resetOOB, linearize, applyRes, fixLinearizationF of the
+ * active residuals) followed by EnergyFunctional::marginalizePointsF (as ldso_gpu_window_marginalize_points).  residual_dead[r]
+ * != 0: the host has dropped residual r since the upload (linearizeAll(true)'s removal list).  frame_energy_th[n]: the
+ * thresholds as they stand now (setNewFrameEnergyTH ran after the last linearisation).  n_lin: residuals whose linearisation
+ * was fixed.  Afterwards the resident window is spent: upload it again before the next optimisation. */
+int ldso_gpu_window_marginalize_subset(ldso_gpu_ctx* ctx, const unsigned char* point_mask, const unsigned char* residual_dead,
+                                       const float* frame_energy_th, float idepth_fix_prior_marg_fac, double* H, double* b,
+                                       int* n_res, int* n_lin);
 /* marginalizeFrame (:109-191), the dense part (H1, host code): moves frame idx (0-based window position, n frames) to
  * the end of HM,bM ((8n+4)^2, 8n+4), adds its prior / prior*delta_prior, takes the diagonally scaled Schur complement
  * with util::MatrixInverter::invertPosDef (src/util/MatrixInverter.cc:31-50, SVD form) of the 8x8 block and

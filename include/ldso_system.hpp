@@ -20,6 +20,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <condition_variable>
 #include <memory>
@@ -53,7 +54,7 @@
         LDSO_API_FN(P, window_solve) LDSO_API_FN(P, window_resubstitute) LDSO_API_FN(P, window_marginalize_points)       \
         LDSO_API_FN(P, window_marginalize_frame) LDSO_API_FN(P, window_get_residual_floats)                              \
         LDSO_API_FN(P, window_get_residual_ints) LDSO_API_FN(P, window_get_point_floats)                                 \
-        LDSO_API_FN(P, window_get_keyframe_results)                                                                      \
+        LDSO_API_FN(P, window_get_keyframe_results) LDSO_API_FN(P, window_marginalize_subset)                            \
     };
 // declarations of the same entry points under another prefix (test builds: the CPU oracle mirrors the ABI as orc_*)
 #define LDSO_DECLARE_API(P, CTX)                                                                                         \
@@ -106,6 +107,8 @@
     int P##window_get_residual_ints(CTX*, int, int*);                                                                    \
     int P##window_get_point_floats(CTX*, int, float*);                                                                   \
     int P##window_get_keyframe_results(CTX*, int*, float*, float*, float*, float*, float*);                              \
+    int P##window_marginalize_subset(CTX*, const unsigned char*, const unsigned char*, const float*, float, double*, double*, int*, \
+                                     int*);                                                                              \
     }
 
 namespace ldso {
@@ -246,6 +249,7 @@ struct PointFrameResidual {
 struct PointHessian {
     FrameHessian* host = nullptr;
     int feat_idx = 0;                // position among the host frame's features (Frame::features order = allPoints order)
+    int upload_idx = -1;             // row of the point in the device-resident window (set by the last upload)
     PointStatus status = PointStatus::ACTIVE;   // Point::status
     float u = 0, v = 0, my_type = 0;
     bool hasDepthPrior = false;
@@ -613,6 +617,20 @@ public:
 private:
     int wG0 = 0, hG0 = 0, levels = 0;
 
+    // optional fine-grained host timers (LDSO_SYS_PROF=1): label -> seconds, printed by the destructor
+    struct Prof {
+        std::vector<std::pair<std::string, double>> acc;
+        bool on = getenv("LDSO_SYS_PROF") != nullptr;
+        void add(const char* label, double dt) {
+            if (!on) return;
+            for (auto& a : acc) if (a.first == label) { a.second += dt; return; }
+            acc.emplace_back(label, dt);
+        }
+        ~Prof() {
+            for (auto& a : acc) fprintf(stderr, "  [sys prof] %-40s %.3f ms\n", a.first.c_str(), 1e3 * a.second);
+        }
+    } prof;
+#define LDSO_T(label, expr) do { const double _t0 = now(); expr; prof.add(label, now() - _t0); } while (0)
     static double now() {
         return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
     }
@@ -1022,7 +1040,10 @@ private:
     struct Upload {
         std::vector<PointHessian*> pts;
         std::vector<int> res_begin;
+        std::vector<FrameHessian*> res_target;   // target of every uploaded residual, in upload order
+        std::vector<unsigned char> dead;         // residuals dropped on the host since the upload
         int nr = 0;
+        bool resident = false;                   // the device window still holds exactly this upload (+ its linearisation)
     } up;
     std::vector<float> precalcBuf, ethBuf;
     std::vector<double> fpriorBuf, fdeltaPriorBuf;
@@ -1055,11 +1076,13 @@ private:
     int uploadPoints(const std::vector<PointHessian*>& pts) {
         const int np = (int)pts.size();
         up.pts = pts;
+        up.resident = false;
         up.res_begin.assign(np + 1, 0);
         std::vector<float> u(np), v(np), id(np), idz(np), col(8 * (size_t)np), wgt(8 * (size_t)np), prior(np);
         std::vector<int> host(np);
         for (int i = 0; i < np; i++) {
             const PointHessian* p = pts[i];
+            pts[i]->upload_idx = i;
             u[i] = p->u; v[i] = p->v; id[i] = p->idepth_scaled; idz[i] = p->idepth_zero_scaled; host[i] = p->host->idx; prior[i] = p->priorF;
             memcpy(&col[8 * (size_t)i], p->color, sizeof(p->color));
             memcpy(&wgt[8 * (size_t)i], p->weights, sizeof(p->weights));
@@ -1070,8 +1093,11 @@ private:
         if (np > cfg.gpu.max_points || nr > cfg.gpu.max_residuals) return fail("window exceeds max_points / max_residuals of the context");
         std::vector<int> target(nr), state(nr);
         std::vector<unsigned char> flags(nr);
+        up.res_target.resize(nr);
+        up.dead.assign(nr, 0);
         for (int i = 0, r = 0; i < np; i++)
             for (const auto& res : pts[i]->residuals) {
+                up.res_target[r] = res.target;
                 target[r] = res.target->idx;
                 state[r] = (int)res.state_state;
                 flags[r] = (unsigned char)((res.isLinearized ? LDSO_RF_LINEARIZED : 0) | (res.isActiveAndIsGoodNEW ? LDSO_RF_ACTIVE : 0) |
@@ -1116,7 +1142,10 @@ private:
             }
             // toRemove (:1749-1764): in residual order, each removal swaps the last residual in (deleteOut)
             std::vector<FrameHessian*> rm;
-            for (const auto& res : p->residuals) if (!res.isActive()) rm.push_back(res.target);
+            {
+                int rr = up.res_begin[i];
+                for (const auto& res : p->residuals) { if (!res.isActive()) { rm.push_back(res.target); up.dead[rr] = 1; } rr++; }
+            }
             for (FrameHessian* t : rm) {
                 if (p->lastResiduals_first[0] == t) p->lastResiduals_first[0] = nullptr;
                 else if (p->lastResiduals_first[1] == t) p->lastResiduals_first[1] = nullptr;
@@ -1151,11 +1180,13 @@ private:
         for (PointHessian* p : allPoints)
             for (auto& r : p->residuals) r.resetOOB();
         int rc;
-        if ((rc = uploadFrames()) < 0 || (rc = uploadPoints(allPoints)) < 0 || (rc = uploadAdjoints()) < 0) return rc;
+        LDSO_T("opt uploadFrames", rc = uploadFrames()); if (rc < 0) return rc;
+        LDSO_T("opt uploadPoints", rc = uploadPoints(allPoints)); if (rc < 0) return rc;
+        LDSO_T("opt uploadAdjoints", rc = uploadAdjoints()); if (rc < 0) return rc;
         kf_log[1] = (double)allPoints.size();
         kf_log[2] = (double)up.nr;
         double lastEnergy[3], newEnergy[3];
-        if ((rc = linearizeAll(false, lastEnergy)) < 0) return rc;
+        LDSO_T("opt linearize first", rc = linearizeAll(false, lastEnergy)); if (rc < 0) return rc;
         if (Api::window_apply_res(ctx) < 0) return fail_api();
         double lambda = 1e-1;
         std::vector<double> HA((size_t)D * D), HL((size_t)D * D), Hsc((size_t)D * D), bA(D), bL(D), bsc(D), x(D), delta(D), N;
@@ -1171,19 +1202,19 @@ private:
             // solveSystem (:1707-1714) -> EnergyFunctional::solveSystemF (EnergyFunctional.cc:280-471)
             getNullspaces(N);
             int counts[2] = {0, 0};
-            if (Api::window_accumulate(ctx, HA.data(), bA.data(), HL.data(), bL.data(), Hsc.data(), bsc.data(), counts) < 0) return fail_api();
+            LDSO_T("opt accumulate", rc = Api::window_accumulate(ctx, HA.data(), bA.data(), HL.data(), bL.data(), Hsc.data(), bsc.data(), counts)); if (rc < 0) return fail_api();
             resInA = counts[0];
             for (int i = 0; i < 4; i++) delta[i] = (double)cDeltaF[i];   // getStitchedDeltaF (EnergyFunctional.h:192-198)
             for (int h = 0; h < n; h++)
                 for (int i = 0; i < 8; i++) delta[CPARS + 8 * h + i] = frames[h]->delta[i];
-            if (Api::window_solve(ctx, iteration, lambda, HA.data(), bA.data(), HL.data(), bL.data(), Hsc.data(), bsc.data(), HM.data(),
-                                  bM.data(), delta.data(), N.data(), 7, x.data()) < 0)
-                return fail_api();
+            LDSO_T("opt solve", rc = Api::window_solve(ctx, iteration, lambda, HA.data(), bA.data(), HL.data(), bL.data(), Hsc.data(), bsc.data(), HM.data(),
+                                  bM.data(), delta.data(), N.data(), 7, x.data()));
+            if (rc < 0) return fail_api();
             lastX = x;
             counters[LDSO_SYS_CT_BA_ITERATIONS]++;
             its++;
             // resubstituteF_MT (:611-637): currentLambda is the pinned 1e-5 of SOLVER_FIX_LAMBDA
-            if (Api::window_resubstitute(ctx, x.data(), 1e-5f, pstep.data()) < 0) return fail_api();
+            LDSO_T("opt resubstitute", rc = Api::window_resubstitute(ctx, x.data(), 1e-5f, pstep.data())); if (rc < 0) return fail_api();
             for (int i = 0; i < 4; i++) Hcalib.step[i] = -x[i];
             for (FrameHessian* h : frames) {
                 for (int i = 0; i < 8; i++) h->step[i] = -x[CPARS + 8 * h->idx + i];
@@ -1193,12 +1224,13 @@ private:
             double xn = 0;
             for (int i = 0; i < D; i++) xn += x[i] * x[i];
             if (std::isnan(std::sqrt(xn))) { isLost = true; *rmse_out = 3.4e38f; return 0; }   // :907-911
-            const bool canbreak = doStepFromBackup();
+            bool canbreak = false;
+            LDSO_T("opt doStepFromBackup", canbreak = doStepFromBackup());
             // device half of setPrecalcValues + the new inverse depths
             for (size_t i = 0; i < allPoints.size(); i++) idv[i] = allPoints[i]->idepth_scaled;
-            if ((rc = uploadFrames()) < 0 || (rc = uploadAdjoints()) < 0) return rc;
-            if (!allPoints.empty() && Api::window_set_idepth(ctx, idv.data(), idv.data()) < 0) return fail_api();
-            if ((rc = linearizeAll(false, newEnergy)) < 0) return rc;
+            LDSO_T("opt it uploads", rc = uploadFrames(); if (rc >= 0) rc = uploadAdjoints(); if (rc >= 0 && !allPoints.empty() && Api::window_set_idepth(ctx, idv.data(), idv.data()) < 0) rc = fail_api());
+            if (rc < 0) return rc;
+            LDSO_T("opt it linearize", rc = linearizeAll(false, newEnergy)); if (rc < 0) return rc;
             // setting_forceAceptStep (:935): always accepted
             if (Api::window_apply_res(ctx) < 0) return fail_api();
             for (int i = 0; i < 3; i++) lastEnergy[i] = newEnergy[i];
@@ -1211,10 +1243,10 @@ private:
         FrameHessian* fh = frames.back();
         newStateZero[6] = fh->state[6]; newStateZero[7] = fh->state[7];
         fh->setEvalPT(fh->PRE_worldToCam, newStateZero);
-        setAdjointsF();
-        setPrecalcValues();
-        if ((rc = uploadFrames()) < 0 || (rc = uploadAdjoints()) < 0) return rc;
-        if ((rc = linearizeAll(true, lastEnergy)) < 0) return rc;
+        LDSO_T("opt final host tables", setAdjointsF(); setPrecalcValues());
+        LDSO_T("opt final uploads", rc = uploadFrames(); if (rc >= 0) rc = uploadAdjoints()); if (rc < 0) return rc;
+        LDSO_T("opt final linearize(true)+readback", rc = linearizeAll(true, lastEnergy)); if (rc < 0) return rc;
+        up.resident = true;
         if (!std::isfinite(lastEnergy[0]) || !std::isfinite(lastEnergy[1]) || !std::isfinite(lastEnergy[2])) isLost = true;
         for (FrameHessian* fr : frames) {   // :995-1004
             fr->Tcw = fr->PRE_camToWorld.inverse();
@@ -1308,14 +1340,15 @@ private:
             if (f == newestFr) continue;
             for (const auto& p : f->points) { ph_host.push_back(f->idx); pu.push_back(p->u); pv.push_back(p->v); pid.push_back(p->idepth_scaled); }
         }
-        if (Api::distmap_make(ctx, n, KRKi.data(), Kt.data(), (int)pu.size(), ph_host.data(), pu.data(), pv.data(), pid.data()) < 0)
-            return fail_api();
+        int rcp = 0;
+        LDSO_T("act distmap_make", rcp = Api::distmap_make(ctx, n, KRKi.data(), Kt.data(), (int)pu.size(), ph_host.data(), pu.data(), pv.data(), pid.data()));
+        if (rcp < 0) return fail_api();
         // the ordered candidate walk (:1233-1298)
         std::vector<unsigned char> action(std::max(n_pool, 1), 0);
         int cnt[2] = {0, 0};
-        if (Api::immature_select_activation(ctx, n, KRKi.data(), Kt.data(), skip.data(), flagged.data(), currentMinActDist,
-                                            cfg.min_trace_quality, action.data(), cnt) < 0)
-            return fail_api();
+        LDSO_T("act select_activation", rcp = Api::immature_select_activation(ctx, n, KRKi.data(), Kt.data(), skip.data(), flagged.data(), currentMinActDist,
+                                            cfg.min_trace_quality, action.data(), cnt));
+        if (rcp < 0) return fail_api();
         std::vector<int> cand, gone;
         for (int i = 0; i < n_pool; i++) {
             if (action[i] == 2) cand.push_back(i);
@@ -1327,7 +1360,7 @@ private:
         if (!cand.empty()) {
             int rc = uploadFrames();
             if (rc < 0) return rc;
-            if (Api::immature_activate(ctx, (int)cand.size(), cand.data(), 1, idp.data(), ok.data(), rst.data()) < 0) return fail_api();
+            LDSO_T("act immature_activate", rcp = Api::immature_activate(ctx, (int)cand.size(), cand.data(), 1, idp.data(), ok.data(), rst.data())); if (rcp < 0) return fail_api();
         }
         // walk the pool in order (frames, then features) and apply the outcome (:1313-1336)
         int pi = 0, ci = 0, n_act = 0;
@@ -1375,7 +1408,7 @@ private:
         }
         if (!gone.empty()) {
             int np2 = 0;
-            if (Api::immature_compact(ctx, -1, 0, (int)gone.size(), gone.data(), &np2) < 0) return fail_api();
+            LDSO_T("act compact", rcp = Api::immature_compact(ctx, -1, 0, (int)gone.size(), gone.data(), &np2)); if (rcp < 0) return fail_api();
             n_pool = np2;
         }
         counters[LDSO_SYS_CT_ACTIVATED] += n_act;
@@ -1453,32 +1486,43 @@ private:
         const int n = (int)frames.size(), D = CPARS + 8 * n;
         if (!toMarg.empty()) {
             int rc;
-            for (PointHessian* p : toMarg)
-                for (auto& r : p->residuals) { r.resetOOB(); r.isLinearized = false; }
-            if ((rc = uploadFrames()) < 0 || (rc = uploadPoints(toMarg)) < 0 || (rc = uploadAdjoints()) < 0) return rc;
-            double stats[3];
-            float th_keep = frames.back()->frameEnergyTH, th = 0;
-            if (Api::window_linearize(ctx, 0, stats, &th) < 0) return fail_api();   // r->linearize (:1392)
-            frames.back()->frameEnergyTH = th_keep;                                 // no setNewFrameEnergyTH on this path
-            if (Api::window_apply_res(ctx) < 0) return fail_api();                  // r->applyRes(true) (:1394)
-            std::vector<int> st(std::max(up.nr, 1));
-            if (up.nr && Api::window_get_residual_ints(ctx, 0, st.data()) < 0) return fail_api();
-            std::vector<unsigned char> mask(std::max(up.nr, 1), 0), pm(toMarg.size(), 1);
-            int nlin = 0;
-            for (size_t i = 0, r = 0; i < toMarg.size(); i++)
-                for (auto& res : toMarg[i]->residuals) {
-                    res.state_state = (ResState)st[r];
-                    res.isActiveAndIsGoodNEW = res.state_state == ResState::IN;
-                    if (res.isActive()) { mask[r] = 1; res.isLinearized = true; nlin++; }   // fixLinearizationF (:1396)
-                    r++;
-                }
-            if (up.nr && Api::window_fix_linearization(ctx, mask.data()) < 0) return fail_api();
+            std::vector<double> H((size_t)D * D), b(D);
+            int nres = 0, nlin = 0;
+            if (up.resident && !getenv("LDSO_SYS_NO_SUBSET")) {
+                // the window optimize ran on is still resident: re-judge, fix and marginalise in place (one call, no upload)
+                std::vector<unsigned char> pm(up.pts.size(), 0);
+                for (PointHessian* p : toMarg) pm[p->upload_idx] = 1;
+                std::vector<float> eth(n);
+                for (int i = 0; i < n; i++) eth[i] = frames[i]->frameEnergyTH;
+                LDSO_T("marg subset", rc = Api::window_marginalize_subset(ctx, pm.data(), up.dead.data(), eth.data(), cfg.idepth_fix_prior_marg_fac,
+                                                                          H.data(), b.data(), &nres, &nlin));
+                if (rc < 0) return fail_api();
+                up.resident = false;
+            } else {
+                // general path: a window holding just those points goes through K7 (linearize + applyRes), fixLinearizationF,
+                // addPoint<2> + the Schur accumulator
+                for (PointHessian* p : toMarg)
+                    for (auto& r : p->residuals) { r.resetOOB(); r.isLinearized = false; }
+                if ((rc = uploadFrames()) < 0 || (rc = uploadPoints(toMarg)) < 0 || (rc = uploadAdjoints()) < 0) return rc;
+                double stats[3];
+                float th_keep = frames.back()->frameEnergyTH, th = 0;
+                if (Api::window_linearize(ctx, 0, stats, &th) < 0) return fail_api();   // r->linearize (:1392)
+                frames.back()->frameEnergyTH = th_keep;                                 // no setNewFrameEnergyTH on this path
+                if (Api::window_apply_res(ctx) < 0) return fail_api();                  // r->applyRes(true) (:1394)
+                std::vector<int> st(std::max(up.nr, 1));
+                if (up.nr && Api::window_get_residual_ints(ctx, 0, st.data()) < 0) return fail_api();
+                std::vector<unsigned char> mask(std::max(up.nr, 1), 0), pm(toMarg.size(), 1);
+                for (size_t i = 0, r = 0; i < toMarg.size(); i++)
+                    for (auto& res : toMarg[i]->residuals) {
+                        if ((ResState)st[r] == ResState::IN) { mask[r] = 1; nlin++; }   // fixLinearizationF (:1396)
+                        r++;
+                    }
+                if (up.nr && Api::window_fix_linearization(ctx, mask.data()) < 0) return fail_api();
+                if (Api::window_marginalize_points(ctx, pm.data(), cfg.idepth_fix_prior_marg_fac, H.data(), b.data(), &nres) < 0) return fail_api();
+            }
             counters[LDSO_SYS_CT_LIN_RESIDUALS] += nlin;
             kf_log[5] = nlin;
             // marginalizePointsF: priorF *= setting_idepthFixPriorMargFac, addPoint<2>, SC addPoint, stitch, H = M - Msc
-            std::vector<double> H((size_t)D * D), b(D);
-            int nres = 0;
-            if (Api::window_marginalize_points(ctx, pm.data(), cfg.idepth_fix_prior_marg_fac, H.data(), b.data(), &nres) < 0) return fail_api();
             resInM += nres;
             counters[LDSO_SYS_CT_RES_IN_M] = resInM;
             for (size_t i = 0; i < (size_t)D * D; i++) HM[i] += cfg.marg_weight_fac * H[i];

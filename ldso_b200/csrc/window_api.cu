@@ -622,6 +622,124 @@ extern "C" int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* c, const unsigne
     return build_order(c);   // back to the A/L work list of the remaining residuals (inactive ones are skipped by flag)
 }
 
+// FullSystem::flagPointsForRemoval's inner loop (FullSystem.cc:1390-1399) + EnergyFunctional::marginalizePointsF (:205-262) for a
+// subset of the points of the window that is ALREADY resident (the one optimize just ran on): nothing is re-uploaded.
+// The reference re-linearises every remaining residual of such a point (resetOOB, linearize, applyRes) before it fixes the
+// linearisation.  State, tables and inverse depths have not moved since the last linearizeAll(true), so that pass reproduces the
+// Jacobians bit for bit; the one input that did change is the newest frame's energy threshold (setNewFrameEnergyTH ran after the
+// last linearisation), which can turn a residual IN -> OUTLIER.  The kernel therefore re-judges state_NewEnergyWithOutlier
+// against max(frameEnergyTH[host], frameEnergyTH[target]), applies the result (isActive) and fixes the linearisation of the
+// active ones; residuals the host has dropped since (dead != 0) stay out.
+namespace {
+__global__ void win_rejudge_fix_kernel(int nr, int n, const unsigned char* __restrict__ pmask, const unsigned char* __restrict__ dead,
+                                       const int* __restrict__ r_point, const int* __restrict__ r_target, const int* __restrict__ host,
+                                       const float* __restrict__ e_wo, const float* __restrict__ eth, int* __restrict__ state,
+                                       int* __restrict__ new_state, int* __restrict__ flags, const float* __restrict__ J,
+                                       const float* __restrict__ adHTdelta, float4 cDelta, const float* __restrict__ idepth,
+                                       const float* __restrict__ idepth_zero, float* __restrict__ rtz, int* __restrict__ n_lin) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nr) return;
+    const int pt = r_point[r];
+    if (!pmask[pt]) return;
+    int fl = flags[r] & ~LDSO_RF_LINEARIZED;
+    if (dead[r]) { flags[r] = fl & ~LDSO_RF_ACTIVE; return; }
+    const int h = host[pt], t = r_target[r];
+    const float th = fmaxf(eth[h], eth[t]);
+    const int ns = e_wo[r] > th ? LDSO_RES_OUTLIER : LDSO_RES_IN;   // every remaining residual was IN with wJI2_sum >= 2
+    new_state[r] = ns;
+    state[r] = ns;                                                  // applyRes(true) after resetOOB (state IN): state = NewState
+    if (ns != LDSO_RES_IN) { flags[r] = fl & ~LDSO_RF_ACTIVE; return; }
+    fl |= LDSO_RF_ACTIVE;
+    const float* j = J + (size_t)r * LDSO_J_FLOATS;
+    const float* dp = adHTdelta + 8 * (h + n * t);
+    const float deltaF = idepth[pt] - idepth_zero[pt];
+    float dx = 0, dy = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) { dx += j[40 + i] * dp[i]; dy += j[46 + i] * dp[i]; }
+    const float cd[4] = {cDelta.x, cDelta.y, cDelta.z, cDelta.w};
+    float cx = 0, cy = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) { cx += j[52 + i] * cd[i]; cy += j[56 + i] * cd[i]; }
+    const float Jx = dx + cx + j[60] * deltaF, Jy = dy + cy + j[61] * deltaF;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {   // fixLinearizationF (Residuals.cc:219-245), as k7_fix_lin_kernel
+        float v = j[i];
+        v = v - j[8 + i] * Jx;
+        v = v - j[16 + i] * Jy;
+        v = v - j[24 + i] * dp[6];
+        v = v - j[32 + i] * dp[7];
+        rtz[8 * (size_t)r + i] = v;
+    }
+    flags[r] = fl | LDSO_RF_LINEARIZED;
+    atomicAdd(n_lin, 1);
+}
+}  // namespace
+
+extern "C" int ldso_gpu_window_marginalize_subset(ldso_gpu_ctx* c, const unsigned char* point_mask, const unsigned char* residual_dead,
+                                                  const float* frame_energy_th, float fac, double* H, double* b, int* n_res,
+                                                  int* n_lin) {
+    LDSO_ENTER(c);
+    WindowDev& W = c->win;
+    LDSO_REQUIRE(c, W.n > 0 && H && b && frame_energy_th && (point_mask || W.np == 0) && (residual_dead || W.nr == 0));
+    LDSO_REQUIRE(c, (int)W.adHost.size() == 64 * W.n * W.n);
+    const int n = W.n, nn = n * n, D = 8 * n + CPARS;
+    for (int i = 0; i < n; i++) W.frameEnergyTH[i] = frame_energy_th[i];
+    // small uploads ride in scratch that the accumulate path rewrites anyway: thresholds + lin counter in xAd, dead mask in res_pt
+    int rc = upload(c, W.pmask, point_mask, W.np);
+    unsigned char* ddead = reinterpret_cast<unsigned char*>(W.res_pt);
+    rc |= upload(c, ddead, residual_dead, W.nr);
+    float tab[LDSO_MAX_WINDOW + 1];
+    for (int i = 0; i < n; i++) tab[i] = frame_energy_th[i];
+    tab[LDSO_MAX_WINDOW] = 0.f;
+    float* deth = W.xAd;
+    int* dlin = reinterpret_cast<int*>(W.xAd + LDSO_MAX_WINDOW);
+    rc |= upload(c, deth, tab, sizeof(tab));
+    if (rc) return -1;
+    if (W.nr > 0) {
+        float4 cd = make_float4(W.cDeltaF[0], W.cDeltaF[1], W.cDeltaF[2], W.cDeltaF[3]);
+        win_rejudge_fix_kernel<<<(W.nr + 255) / 256, 256, 0, c->stream>>>(W.nr, n, W.pmask, ddead, W.r_point, W.r_target, W.host,
+                                                                         W.new_energy_wo, deth, W.state, W.new_state, W.flags, W.J,
+                                                                         W.adHTdelta, cd, W.idepth, W.idepth_zero, W.rtz, dlin);
+        c->launches++;
+        LDSO_CUDA_OK(c, cudaGetLastError());
+    }
+    int lin_host = 0;
+    char* stl = (char*)staging(c, 64);
+    LDSO_REQUIRE(c, stl != nullptr);
+    LDSO_CUDA_OK(c, ldso_copy(c, stl, dlin, sizeof(int), cudaMemcpyDeviceToHost, c->stream));   // before K8 reuses the scratch? xAd is K10's
+    rc = build_order(c, point_mask);
+    if (rc) return rc;
+    rc = k8_accumulate_top(c, 1);
+    if (rc) return rc;
+    rc = k9_accumulate_sc(c, W.pmask, fac);
+    if (rc) return rc;
+    rc = h1_stitch(c);
+    if (rc) return rc;
+    if (W.nr > 0) {
+        win_deactivate_kernel<<<(W.nr + 255) / 256, 256, 0, c->stream>>>(W.nr, W.r_point, W.pmask, W.flags);
+        c->launches++;
+    }
+    const size_t sysz = (size_t)D * D + D;
+    const size_t bytes = sizeof(double) * 3 * sysz + sizeof(int) * nn;
+    char* st = (char*)staging(c, bytes);
+    LDSO_REQUIRE(c, st != nullptr);
+    LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * nn, cudaMemcpyDeviceToHost, c->stream));
+    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    lin_host = *(const int*)stl;
+    W.pinned_off = 0;
+    const double *M = (const double*)st, *Msc = M + 2 * sysz;
+    for (size_t i = 0; i < (size_t)D * D; i++) H[i] = M[i] - Msc[i];
+    for (int i = 0; i < D; i++) b[i] = M[(size_t)D * D + i] - Msc[(size_t)D * D + i];
+    if (n_res) {
+        const int* cnt = (const int*)(st + sizeof(double) * 3 * sysz);
+        *n_res = 0;
+        for (int k = 0; k < nn; k++) *n_res += cnt[k];
+    }
+    if (n_lin) *n_lin = lin_host;
+    return 0;   // the window is not reusable for another optimisation: the next keyframe uploads it afresh
+}
+
 extern "C" int ldso_gpu_window_marginalize_frame(ldso_gpu_ctx* c, int n, int idx, const double* HMin, const double* bMin,
                                                  const double prior[8], const double delta_prior[8], double* HM_out,
                                                  double* bM_out) {

@@ -929,6 +929,34 @@ extern "C" int orc_window_marginalize_points(orc_ctx* c, const unsigned char* ma
     return 0;
 }
 
+// FullSystem::flagPointsForRemoval's inner loop (src/frontend/FullSystem.cc:1390-1399) followed by
+// EnergyFunctional::marginalizePointsF (:205-262) for the masked points of the resident window, literally: resetOOB,
+// linearize, isLinearized = false, applyRes(true), fixLinearizationF for the active ones, then addPoint<2> + the Schur accumulator.
+// residual_dead marks the residuals FullSystem has dropped since the upload (linearizeAll(true)'s toRemove list).
+extern "C" int orc_window_marginalize_subset(orc_ctx* c, const unsigned char* point_mask, const unsigned char* residual_dead,
+                                             const float* frame_energy_th, float fac, double* H, double* b, int* n_res, int* n_lin) {
+    Window& W = c->win;
+    for (int i = 0; i < W.n; i++) W.frameEnergyTH[i] = frame_energy_th[i];
+    std::vector<unsigned char> fix(std::max(W.nr, 1), 0);
+    int nlin = 0;
+    for (int p = 0; p < W.np; p++) {
+        if (!point_mask[p]) continue;
+        for (int r = W.res_begin[p]; r < W.res_begin[p + 1]; r++) {
+            W.flags[r] &= ~LDSO_RF_LINEARIZED;
+            if (residual_dead[r]) { W.flags[r] &= ~LDSO_RF_ACTIVE; continue; }
+            W.state_NewEnergy[r] = W.state_energy[r] = 0;      // resetOOB
+            W.state_NewState[r] = LDSO_RES_OUTLIER;
+            W.state_state[r] = LDSO_RES_IN;
+            linearize_one(c, r);
+            apply_res(W, r, true);
+            if (W.flags[r] & LDSO_RF_ACTIVE) { fix[r] = 1; nlin++; }
+        }
+    }
+    orc_window_fix_linearization(c, fix.data());
+    if (n_lin) *n_lin = nlin;
+    return orc_window_marginalize_points(c, point_mask, fac, H, b, n_res);
+}
+
 // util::MatrixInverter::invertPosDef(M, fast = false) (src/util/MatrixInverter.cc:31-50)
 static void invert_pos_def(int n, const double* M, double* res) {
     std::vector<double> sv(n), Ms((size_t)n * n), U((size_t)n * n), S(n), V((size_t)n * n);
