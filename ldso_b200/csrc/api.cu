@@ -2,6 +2,9 @@
 // (frame pyramids, coarse tracker).  See include/ldso_gpu.h for the reference methods each one replaces.
 #include "ctx.h"
 
+#include <immintrin.h>
+#include <sched.h>
+
 #include <cmath>
 #include <new>
 #include <vector>
@@ -99,6 +102,15 @@ static int create_impl(ldso_gpu_ctx* c) {
     return 0;
 }
 
+bool ldso_wait_yield() {
+    static const bool y = [] { const char* e = getenv("LDSO_WAIT_YIELD"); return e && atoi(e) != 0; }();
+    return y;
+}
+void ldso_cpu_relax() {
+    if (ldso_wait_yield()) sched_yield();
+    else _mm_pause();
+}
+
 extern "C" int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out) {
     if (!cfg || !out) return -2;
     ldso_gpu_ctx* c = new (std::nothrow) ldso_gpu_ctx();
@@ -112,6 +124,7 @@ extern "C" int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out) {
         c->trk[t].row_cnt = nullptr;
         c->trk[t].pc_n_dev = nullptr;
     }
+    if (ldso_wait_yield()) { cudaSetDevice(cfg->device); cudaSetDeviceFlags(cudaDeviceScheduleYield); cudaGetLastError(); }
     int rc = create_impl(c);
     *out = c;   // returned even on failure so that the caller can read last_error, then destroy
     return rc;

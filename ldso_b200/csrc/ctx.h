@@ -133,6 +133,12 @@ struct ldso_gpu_ctx {
         if (cudaGetDevice(&ldso_cur_dev) != cudaSuccess || ldso_cur_dev != (ctx)->cfg.device) cudaSetDevice((ctx)->cfg.device); \
     } while (0)
 
+// How a host thread waits for the device.  Default: spin (lowest latency, one core per waiting thread).  With
+// LDSO_WAIT_YIELD=1 the mailbox polls call sched_yield() and the context is switched to cudaDeviceScheduleYield, so that
+// more sequence threads than cores can share a host (ldso_gpu_batch_* with many sequences per GPU).
+bool ldso_wait_yield();
+void ldso_cpu_relax();
+
 // every host<->device copy of the library goes through here so that the traffic is accounted
 inline cudaError_t ldso_copy(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
     if (kind == cudaMemcpyHostToDevice) c->h2d_bytes += (long long)bytes;

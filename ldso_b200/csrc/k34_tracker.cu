@@ -1244,7 +1244,7 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
     // poll for it instead of paying a D2H copy + stream synchronisation per LM evaluation
     const double want = (double)c->trk_seq;
     for (unsigned spin = 1; res[63] != want; spin++) {
-        _mm_pause();
+        ldso_cpu_relax();
         if ((spin & 0xfffff) == 0) {   // every ~1M polls make sure the stream is still alive
             cudaError_t q = cudaStreamQuery(c->stream);
             if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);
@@ -1263,7 +1263,7 @@ static int track_all_wait(ldso_gpu_ctx* c, double seq, int prof_idx, int dbg, ld
                           float last_residuals[5], float flow[3], int* status, int* nEval, int* nAccept) {
     volatile double* res = c->trk_mailbox;
     for (unsigned spin = 1; res[63] != seq; spin++) {
-        _mm_pause();
+        ldso_cpu_relax();
         if ((spin & 0xfffff) == 0) {
             cudaError_t q = cudaStreamQuery(c->stream);
             if (q != cudaSuccess && q != cudaErrorNotReady) LDSO_CUDA_OK(c, q);

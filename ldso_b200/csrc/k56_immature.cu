@@ -582,7 +582,8 @@ ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     da((void**)&P->interval2, 4 * N); da((void**)&P->keep, 4 * (N + 1)); da((void**)&P->pos, 4 * (N + 1));
     da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 32);
     da((void**)&P->cand, 4 * N); da((void**)&P->act_idepth, 4 * N); da((void**)&P->act_ok, 4 * N);
-    da((void**)&P->act_state, 4 * N * LDSO_MAX_WINDOW); da((void**)&P->cr, 4 * 22 * N);
+    // act_state + 4096: the activation walk's segmented candidate arrays (n2_distmap.cu)
+    da((void**)&P->act_state, 4 * (N * LDSO_MAX_WINDOW + 4096)); da((void**)&P->cr, 4 * 22 * N);
     P->src_cap = (int)(8 * N);
     da((void**)&P->src_cells, 4 * (size_t)P->src_cap); da((void**)&P->src_n, 32);   // [0] length, [1..4] corner values after a walk
     if (ok) cudaMemset(P->src_n, 0, 32);

@@ -152,93 +152,32 @@ struct N2Sel {
     const int *host, *status;
     const float *u, *v, *idmin, *idmax, *quality, *interval, *type;
     float minActDist, minQuality;
-    int* cell; float* frac; float* thr;   // scratch [n]
+    int* cell; float* frac; float* thr; int* idx; int* blk_cnt;   // candidates of classification CTA b at [256 b ...), blk_cnt[b] of them
+    int* ccell; float* cfrac; float* cthr; int* cidx;   // the same, gaps closed: the candidates in pool order
     unsigned char* action;            // [n]
-    int* cnt;                         // [2]
+    int* cnt;                         // [4]: accepted, deleted, bits of the largest candidate threshold, spare (zeroed before the launch)
     const unsigned char* dmap;
     int* src_cells; int* src_n;       // source list of the map kernels: accepted cells are appended
-    int* corner;                      // [4] values of the four corner cells after the walk (see n2_select_kernel)
+    int* corner;                      // [4] values of the four corner cells after the walk (see n2_walk_kernel)
 };
 
-// CoarseDistanceMap::addIntoDistFinal + growDistBFS(1) (CoarseTracker.cc:925-930) on the shared-memory map, by one warp,
-// out to ring R (rings beyond the largest activation threshold cannot change a decision of the walk)
-__device__ __forceinline__ void stamp_source(unsigned char* D, int c0, int R, int w1, int h1, int lane) {
-    const int sy = c0 / w1, sx = c0 - sy * w1;
-    if (lane == 0) D[c0] = 0;
-    __syncwarp();
-    if (sx == 0 || sy == 0 || sx == w1 - 1 || sy == h1 - 1 || R <= 0) return;
-    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R), ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
-    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
-    for (int t = lane; t < nc; t += 32) {
-        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
-        const int d = ring_dist(x - sx, y - sy);
-        const int idx = x + w1 * y;
-        if (d <= R && D[idx] > d) D[idx] = (unsigned char)d;
-    }
-    __syncwarp();
-    if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {
-        // the box reaches the border ring: those cells follow from their interior neighbours
-        const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
-        const int bbw = bx1 - bx0 + 1, nbc = bbw * (by1 - by0 + 1);
-        for (int t = lane; t < nbc; t += 32) {
-            const int ty = t / bbw, x = bx0 + (t - ty * bbw), y = by0 + ty;
-            if (!(x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1)) continue;
-            const int v = border_value(D, x, y, w1, h1);
-            if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
-        }
-        __syncwarp();
-    }
-}
-
-// stamp_source by the whole CTA (interior box, then the border ring where the box reaches it)
-template <int T> __device__ __forceinline__ void stamp_source_cta(unsigned char* D, int c0, int R, int w1, int h1) {
-    const int sy = c0 / w1, sx = c0 - sy * w1;
-    if (threadIdx.x == 0) D[c0] = 0;
-    if (sx == 0 || sy == 0 || sx == w1 - 1 || sy == h1 - 1 || R <= 0) return;   // uniform
-    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R), ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
-    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
-    for (int t = threadIdx.x; t < nc; t += T) {
-        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
-        const int d = ring_dist(x - sx, y - sy);
-        const int idx = x + w1 * y;
-        if (d <= R && D[idx] > d) D[idx] = (unsigned char)d;   // the source cell itself: d = 0
-    }
-    if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {   // uniform
-        __syncthreads();
-        const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
-        const int bbw = bx1 - bx0 + 1, nbc = bbw * (by1 - by0 + 1);
-        for (int t = threadIdx.x; t < nbc; t += T) {
-            const int ty = t / bbw, x = bx0 + (t - ty * bbw), y = by0 + ty;
-            if (!(x == 0 || y == 0 || x == w1 - 1 || y == h1 - 1)) continue;
-            const int v = border_value(D, x, y, w1, h1);
-            if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
-        }
-    }
-}
-
-constexpr int N2_SEL_THREADS = 256;   // the walk meets at a CTA barrier per accepted point: a small CTA keeps that cheap
-
-__global__ void __launch_bounds__(N2_SEL_THREADS) n2_select_kernel(const N2Sel p) {
-    extern __shared__ __align__(16) unsigned char D[];
-    __shared__ int s_acc, s_del, s_c0;
+// ---- the candidate walk ------------------------------------------------------------------------------------------------
+// n2_classify_kernel (grid over the pool): FullSystem.cc:1243-1296 without the ordered part — delete / keep / candidate, the
+// candidate's level-1 cell, the fraction the reference adds to the map value and its threshold; a candidate that already
+// fails against the map as it stands can never be accepted (the walk only lowers the map) and is dropped here.
+__global__ void __launch_bounds__(256) n2_classify_kernel(const N2Sel p) {
+    __shared__ int s_del, s_wc[8];
     __shared__ unsigned s_thmax;
-    const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
-    {
-        uint4* d4 = reinterpret_cast<uint4*>(D);
-        const uint4* g4 = reinterpret_cast<const uint4*>(p.dmap);
-        for (int i = threadIdx.x; i < cells16; i += N2_SEL_THREADS) d4[i] = g4[i];
-    }
-    if (threadIdx.x == 0) { s_acc = 0; s_del = 0; s_thmax = 0u; }
+    if (threadIdx.x == 0) { s_del = 0; s_thmax = 0u; }
     __syncthreads();
-    // ---- classification, all threads (FullSystem.cc:1243-1296 without the map test)
     const float* skip = p.tab + 12 * p.n_hosts;
     const float* flagged = skip + p.n_hosts;
-    int ndel = 0;
-    float thmax = 0.f;
-    for (int i = threadIdx.x; i < p.n; i += N2_SEL_THREADS) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int cell = -1;
+    float fr = 0.f, th = 0.f;
+    if (i < p.n) {
         const int h = p.host[i];
-        int act = 0, cell = -1;
-        float fr = 0.f, th = 0.f;
+        int act = 0;
         if (skip[h] == 0.f) {
             const int st = p.status[i];
             const float imax = p.idmax[i], imin = p.idmin[i];
@@ -257,7 +196,9 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_select_kernel(const N2Sel p
                         cell = x + p.w1 * y;
                         fr = p0 - floorf(p0);   // the reference takes the fraction of the homogeneous ptp[0] (FullSystem.cc:1279-1280)
                         th = p.minActDist * p.type[i];
-                        thmax = fmaxf(thmax, th);
+                        const unsigned char d = p.dmap[cell];
+                        if ((d == 255 ? 1000.f : (float)d) + fr >= th) atomicMax(&s_thmax, __float_as_uint(th));
+                        else cell = -1;
                     } else {
                         act = 1;
                     }
@@ -265,78 +206,187 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_select_kernel(const N2Sel p
             }
         }
         p.action[i] = (unsigned char)act;
-        p.cell[i] = cell; p.frac[i] = fr; p.thr[i] = th;
-        ndel += act;
+        if (act) atomicAdd(&s_del, 1);
     }
-    if (ndel) atomicAdd(&s_del, ndel);
-    if (thmax > 0.f) atomicMax(&s_thmax, __float_as_uint(thmax));
+    // the CTA's candidates, in pool order, into its segment [256 * blockIdx.x ...) of the candidate arrays
+    const unsigned m = __ballot_sync(0xffffffffu, cell >= 0);
+    if (lane == 0) s_wc[wid] = __popc(m);
     __syncthreads();
-    // ---- the ordered walk: warp 0 decides, in pool order, which candidate is accepted next; the whole CTA stamps it
-    const bool walker = threadIdx.x < 32;
-    const int lane = threadIdx.x & 31;
-    const float tm = __uint_as_float(s_thmax);
+    int rank = __popc(m & ((1u << lane) - 1)), total = 0;
+#pragma unroll
+    for (int q = 0; q < 8; q++) { if (q < wid) rank += s_wc[q]; total += s_wc[q]; }
+    if (cell >= 0) {
+        const int o = blockIdx.x * 256 + rank;
+        p.cell[o] = cell; p.frac[o] = fr; p.thr[o] = th; p.idx[o] = i;
+    }
+    if (threadIdx.x == 0) {
+        p.blk_cnt[blockIdx.x] = total;
+        if (s_del) atomicAdd(p.cnt + 1, s_del);
+        if (s_thmax) atomicMax(reinterpret_cast<unsigned*>(p.cnt + 2), s_thmax);
+    }
+}
+
+constexpr int N2_SEL_THREADS = 256;
+constexpr int N2_TPL_ROWS = 2 * N2_RMAX + 1;                       // 79
+constexpr int N2_TPL_STRIDE = ((4 + N2_TPL_ROWS + 4 + 3) / 4) * 4 + 4;   // bytes per template row: 4 of padding, the row, >= 4 of padding
+size_t tpl_bytes() { return (size_t)N2_TPL_ROWS * N2_TPL_STRIDE; }
+
+// value a border cell (not a corner) takes after a stamp
+__device__ __forceinline__ void border_fix(unsigned char* D, int x, int y, int w1, int h1) {
+    if ((x == 0 || x == w1 - 1) && (y == 0 || y == h1 - 1)) return;   // corners: followed by the walker's lanes 0..3
+    const int v = border_value(D, x, y, w1, h1);
+    if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
+}
+
+// n2_walk_kernel (one CTA; after the set-up ONE warp): the ordered walk over the surviving candidates.
+//   * the candidates are compacted in pool order (CTA-wide scan) so the warp tests 32 real candidates per step;
+//   * CoarseDistanceMap::addIntoDistFinal + growDistBFS(1) (CoarseTracker.cc:925-930) on the shared-memory map is a
+//     pointwise minimum with the ring-distance TEMPLATE of the source, out to ring R (rings beyond the largest activation
+//     threshold cannot change a decision of the walk): the template is built once per launch in shared memory and the
+//     stamp is taken four cells at a time (__vminu4 of an aligned map word and the template bytes under it, fetched from
+//     two template words by a funnel shift); border cells follow from their interior neighbours where the box reaches them;
+//   * the whole walk runs inside one warp (no CTA barrier per accepted point).
+__global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_scan[N2_SEL_THREADS / 32], s_off[N2_SEL_THREADS], s_cnt[N2_SEL_THREADS];
+    const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
+    unsigned char* D = smem;
+    unsigned char* T = smem + (size_t)cells16 * 16;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    {
+        uint4* d4 = reinterpret_cast<uint4*>(D);
+        const uint4* g4 = reinterpret_cast<const uint4*>(p.dmap);
+        for (int i = tid; i < cells16; i += N2_SEL_THREADS) d4[i] = g4[i];
+    }
+    const float tm = __uint_as_float((unsigned)p.cnt[2]);
     const int R = tm >= (float)N2_RMAX ? N2_RMAX : min(N2_RMAX, (int)ceilf(tm) + 1);
+    // template rows -R..R; byte 4 + (dx + R) of a row holds ring_dist(dx, dy) (255 beyond ring R and in the padding)
+    for (int i = tid; i < (2 * R + 1) * N2_TPL_STRIDE; i += N2_SEL_THREADS) {
+        const int row = i / N2_TPL_STRIDE, b = i - row * N2_TPL_STRIDE;
+        const int dx = b - 4 - R, dy = row - R;
+        int d = 255;
+        if (dx >= -R && dx <= R) { d = ring_dist(dx, dy); if (d > R) d = 255; }
+        T[i] = (unsigned char)d;
+    }
+    // the CTAs of the classification left their candidates in segments of 256: scan the segment lengths and close the gaps
+    const int nblk = (p.n + 255) / 256;                  // <= N2_SEL_THREADS (checked by the host)
+    const int mine = tid < nblk ? p.blk_cnt[tid] : 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) s_scan[wid] = incl;
+    __syncthreads();
+    int off = incl - mine, K = 0;
+#pragma unroll
+    for (int q = 0; q < N2_SEL_THREADS / 32; q++) { if (q < wid) off += s_scan[q]; K += s_scan[q]; }
+    s_off[tid] = off; s_cnt[tid] = mine;
+    __syncthreads();
+    for (int b = wid; b < nblk; b += N2_SEL_THREADS / 32) {
+        const int cb = s_cnt[b], ob = s_off[b];
+        for (int e = lane; e < cb; e += 32) {
+            const int src = b * 256 + e;
+            p.ccell[ob + e] = p.cell[src]; p.cfrac[ob + e] = p.frac[src]; p.cthr[ob + e] = p.thr[src]; p.cidx[ob + e] = p.idx[src];
+        }
+    }
+    __syncthreads();
+    if (wid != 0) return;
+    // ---- the walk (warp 0)
+    const int w1 = p.w1, h1 = p.h1;
+    const unsigned* T32 = reinterpret_cast<const unsigned*>(T);
+    unsigned* D32 = reinterpret_cast<unsigned*>(D);
+    const bool words = (w1 & 3) == 0;
     const int n0 = *p.src_n;
     int nacc = 0;
     // A corner cell has ONE interior neighbour, a diagonal one, which can claim it only on an odd ring.  The
     // reference's incremental BFS therefore leaves a corner at the best value that neighbour ever offered while the
-    // walk lowered it — not a function of the final map.  Lanes 0..3 of the walker follow one corner each.
-    const int kx = (lane & 1) ? p.w1 - 1 : 0, ky = (lane & 2) ? p.h1 - 1 : 0;
-    const int qx = (lane & 1) ? p.w1 - 2 : 1, qy = (lane & 2) ? p.h1 - 2 : 1;
+    // walk lowered it — not a function of the final map.  Lanes 0..3 follow one corner each.
+    const int kx = (lane & 1) ? w1 - 1 : 0, ky = (lane & 2) ? h1 - 1 : 0;
+    const int qx = (lane & 1) ? w1 - 2 : 1, qy = (lane & 2) ? h1 - 2 : 1;
     int cv = 255, qv = 255;
-    if (walker && lane < 4) { cv = D[kx + p.w1 * ky]; qv = D[qx + p.w1 * qy]; }
-    int cell = (walker && lane < p.n) ? p.cell[lane] : -1;
-    float fr = (walker && lane < p.n) ? p.frac[lane] : 0.f, th = (walker && lane < p.n) ? p.thr[lane] : 0.f;
-    for (int base = 0; base < p.n; base += 32) {
-        const int i = base + lane, inext = i + 32;
-        // next chunk's operands are in flight while this one is walked
-        int cell_n = -1;
+    if (lane < 4) { cv = D[kx + w1 * ky]; qv = D[qx + w1 * qy]; }
+    int cell = lane < K ? p.ccell[lane] : -1;
+    float fr = lane < K ? p.cfrac[lane] : 0.f, th = lane < K ? p.cthr[lane] : 0.f;
+    int idx = lane < K ? p.cidx[lane] : 0;
+    for (int base = 0; base < K; base += 32) {
+        const int inext = base + 32 + lane;
+        int cell_n = -1, idx_n = 0;
         float fr_n = 0.f, th_n = 0.f;
-        if (walker && inext < p.n) { cell_n = p.cell[inext]; fr_n = p.frac[inext]; th_n = p.thr[inext]; }
+        if (inext < K) { cell_n = p.ccell[inext]; fr_n = p.cfrac[inext]; th_n = p.cthr[inext]; idx_n = p.cidx[inext]; }
         int from = 0;
-        while (true) {
-            if (walker) {
-                bool pass = false;
-                if (from < 32 && cell >= 0 && lane >= from) {
-                    const unsigned char d = D[cell];
-                    const float dist = (d == 255 ? 1000.f : (float)d) + fr;
-                    pass = dist >= th;
-                }
-                const unsigned m = __ballot_sync(0xffffffffu, pass);
-                int c0 = -1;
-                if (m) {
-                    const int j = __ffs(m) - 1;
-                    c0 = __shfl_sync(0xffffffffu, cell, j);
-                    if (lane == j) { p.action[i] = 2; p.src_cells[n0 + nacc] = c0; }
-                    nacc++;
-                    from = j + 1;
-                }
-                if (lane == 0) s_c0 = c0;
+        while (from < 32) {
+            bool pass = false;
+            if (cell >= 0 && lane >= from) {
+                const unsigned char d = D[cell];
+                pass = (d == 255 ? 1000.f : (float)d) + fr >= th;
             }
-            __syncthreads();
-            const int c0 = s_c0;
-            if (c0 < 0) break;                       // uniform: the chunk is done
-            stamp_source_cta<N2_SEL_THREADS>(D, c0, R, p.w1, p.h1);
-            __syncthreads();
-            if (walker && lane < 4) {
-                const int sy = c0 / p.w1, sx = c0 - sy * p.w1;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (!m) break;
+            const int j = __ffs(m) - 1;
+            const int c0 = __shfl_sync(0xffffffffu, cell, j);
+            if (lane == j) { p.action[idx] = 2; p.src_cells[n0 + nacc] = c0; }
+            nacc++;
+            from = j + 1;
+            // ---- stamp c0
+            const int sy = c0 / w1, sx = c0 - sy * w1;
+            const bool interior = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1;
+            if (lane == 0) D[c0] = 0;
+            if (lane < 4) {
                 if (sx == kx && sy == ky) cv = 0;
-                if (sx > 0 && sy > 0 && sx < p.w1 - 1 && sy < p.h1 - 1) {
+                if (interior) {
                     qv = min(qv, ring_dist(qx - sx, qy - sy));
                     const int cand = qv + 1;
                     if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
                 }
-                if (cv < D[kx + p.w1 * ky]) D[kx + p.w1 * ky] = (unsigned char)cv;
+                if (cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
             }
-            __syncthreads();                         // the corner cells are part of the map the next test reads
+            if (interior && R > 0) {
+                const int ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
+                if (words) {
+                    const int x0 = sx - R;
+                    const int wlo = x0 <= 0 ? 0 : (x0 >> 2), whi = min(sx + R, w1 - 1) >> 2, wlast = (w1 >> 2) - 1;
+                    const int nw = whi - wlo + 1, slots = (yhi - ylo + 1) * nw;
+                    const float inv_nw = 1.0f / (float)nw;                  // (t + 0.5) / nw stays 0.5 / nw away from an integer: exact floor
+#pragma unroll 4
+                    for (int t = lane; t < slots; t += 32) {
+                        const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
+                        {
+                            const int y = ylo + ry, wx = wlo + wq;
+                            const int b = 4 + 4 * wx - x0;                       // template byte under the word's first cell (>= 1)
+                            const unsigned* trow = T32 + ((y - sy + R) * N2_TPL_STRIDE >> 2) + (b >> 2);
+                            unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
+                            if (wx == 0) tv |= 0xffu;                            // column 0 and column w1 - 1 are border cells
+                            if (wx == wlast) tv |= 0xff000000u;
+                            const int wi = (y * w1 >> 2) + wx;
+                            const unsigned dv = D32[wi], mv = __vminu4(dv, tv);
+                            if (mv != dv) D32[wi] = mv;
+                        }
+                    }
+                } else {
+                    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R);
+                    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
+                    for (int t = lane; t < nc; t += 32) {
+                        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
+                        const int d = ring_dist(x - sx, y - sy);
+                        const int di = x + w1 * y;
+                        if (d <= R && D[di] > d) D[di] = (unsigned char)d;
+                    }
+                }
+                if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {
+                    // the box reaches the border ring: those cells follow from their interior neighbours
+                    __syncwarp();
+                    const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
+                    if (by0 == 0) for (int x = bx0 + lane; x <= bx1; x += 32) border_fix(D, x, 0, w1, h1);
+                    if (by1 == h1 - 1) for (int x = bx0 + lane; x <= bx1; x += 32) border_fix(D, x, h1 - 1, w1, h1);
+                    if (bx0 == 0) for (int y = max(1, by0) + lane; y <= min(h1 - 2, by1); y += 32) border_fix(D, 0, y, w1, h1);
+                    if (bx1 == w1 - 1) for (int y = max(1, by0) + lane; y <= min(h1 - 2, by1); y += 32) border_fix(D, w1 - 1, y, w1, h1);
+                }
+            }
+            __syncwarp();
         }
-        __syncthreads();                             // everyone has read s_c0 before the next chunk overwrites it
-        cell = cell_n; fr = fr_n; th = th_n;
+        cell = cell_n; fr = fr_n; th = th_n; idx = idx_n;
     }
-    if (threadIdx.x == 0) { s_acc = nacc; *p.src_n = n0 + nacc; }
-    if (walker && lane < 4) p.corner[lane] = cv;
-    __syncthreads();
-    if (threadIdx.x == 0) { p.cnt[0] = s_acc; p.cnt[1] = s_del; }
+    if (lane == 0) { *p.src_n = n0 + nacc; p.cnt[0] = nacc; }
+    if (lane < 4) p.corner[lane] = cv;
 }
 
 __global__ void n2_types_kernel(int n, const float* __restrict__ src, float* __restrict__ dst) {
@@ -347,7 +397,7 @@ __global__ void n2_types_kernel(int n, const float* __restrict__ src, float* __r
 size_t map_bytes(const ldso_gpu_ctx* c) { return (((size_t)c->wG[1] * c->hG[1] + 15) / 16) * 16; }
 
 int set_smem(ldso_gpu_ctx* c, const void* fn, size_t bytes) {
-    LDSO_REQUIRE(c, bytes <= 200 * 1024);   // level-1 grids up to ~200 k cells (1232x368 -> 113 k)
+    LDSO_REQUIRE(c, bytes <= 220 * 1024);   // level-1 grids up to ~215 k cells (1232x368 -> 113 k) + the 7 KB stamp template
     LDSO_CUDA_OK(c, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     return 0;
 }
@@ -458,17 +508,26 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     p.host = P->host; p.status = P->status; p.u = P->u; p.v = P->v; p.idmin = P->idmin; p.idmax = P->idmax;
     p.quality = P->quality; p.interval = P->interval; p.type = P->type;
     p.minActDist = current_min_act_dist; p.minQuality = min_trace_quality;
-    p.cell = P->act_state; p.frac = (float*)(P->act_state + P->cap); p.thr = (float*)(P->act_state + 2 * (size_t)P->cap);
+    LDSO_REQUIRE(c, P->n <= 256 * N2_SEL_THREADS && LDSO_MAX_WINDOW >= 9);
+    {
+        int* a = P->act_state;                         // [cap][LDSO_MAX_WINDOW] ints of scratch; segments need n rounded up to 256 <= cap + 255
+        const size_t S = ((size_t)P->cap + 255) / 256 * 256;
+        LDSO_REQUIRE(c, 8 * S + 256 <= (size_t)P->cap * LDSO_MAX_WINDOW + 4096);
+        p.cell = a; p.frac = (float*)(a + S); p.thr = (float*)(a + 2 * S); p.idx = a + 3 * S;
+        p.ccell = a + 4 * S; p.cfrac = (float*)(a + 5 * S); p.cthr = (float*)(a + 6 * S); p.cidx = a + 7 * S; p.blk_cnt = a + 8 * S;
+    }
     p.action = P->action; p.cnt = P->sel_cnt; p.dmap = P->dmap; p.src_cells = P->src_cells; p.src_n = P->src_n; p.corner = P->src_n + 1;
     LDSO_REQUIRE(c, P->src_n_host + P->n <= P->src_cap);
     P->src_n_host += P->n;   // upper bound of the list length after this walk
-    const size_t smem = map_bytes(c);
-    rc = set_smem(c, (const void*)n2_select_kernel, smem);
+    const size_t smem = map_bytes(c) + tpl_bytes();
+    rc = set_smem(c, (const void*)n2_walk_kernel, smem);
     if (rc) return rc;
+    LDSO_CUDA_OK(c, cudaMemsetAsync(P->sel_cnt, 0, 16, c->stream));
     prof_begin(c, c->stream);
-    n2_select_kernel<<<1, N2_SEL_THREADS, smem, c->stream>>>(p);
+    n2_classify_kernel<<<(P->n + 255) / 256, 256, 0, c->stream>>>(p);
+    n2_walk_kernel<<<1, N2_SEL_THREADS, smem, c->stream>>>(p);
     prof_end(c, c->stream, LDSO_PROF_N2SEL, P->n);
-    c->launches++;
+    c->launches += 2;
     LDSO_CUDA_OK(c, cudaGetLastError());
     rc = launch_map(c, P, true);   // the accepted cells joined the source list: rebuild the full-radius map behind the read-back
     if (rc) return rc;

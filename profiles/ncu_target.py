@@ -19,8 +19,13 @@ for k in range(bench.PRIME + 5):
 ctx.sync()
 torch.cuda.profiler.start()
 nkf = 0
+kfl = []
 for k in range(bench.PRIME + 5, bench.PRIME + 5 + steps):
-    nkf += int(s.add_frame_ptr(pin[k].data_ptr())[1])
+    kf = int(s.add_frame_ptr(pin[k].data_ptr())[1])
+    nkf += kf
+    if kf:
+        kfl.append(s.keyframe_log())
 ctx.sync()
 torch.cuda.profiler.stop()
 print("profiled frames", steps, "keyframes", nkf, "launches total", ctx.launch_count())
+print("keyframe logs (activated, currentMinActDist, ...):", kfl)

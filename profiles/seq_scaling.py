@@ -7,20 +7,24 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from ldso_b200 import capi  # noqa: E402
 
-S_MAX = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+# usage: seq_scaling.py S_MAX            -> S = 1, 2, 4, ... S_MAX with S and S/2 worker threads
+#        seq_scaling.py S1,S2,...        -> exactly these S, one worker thread per sequence (LDSO_WAIT_YIELD=1 to oversubscribe)
+LIST = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 and "," in sys.argv[1] else None
+S_MAX = max(LIST) if LIST else (int(sys.argv[1]) if len(sys.argv) > 1 else 8)
 steps, warm = 20, 5
 seeds = [1001 + i for i in range(S_MAX)]
 data = bench.render_sequences(seeds, bench.PRIME + warm + steps + 1)
 import torch  # noqa: E402
 gpu = capi.load()
-pinned = {s: [torch.from_numpy(f).pin_memory() for f in data[s][0]] for s in seeds}
-for S in [1, 2, 4, 8, 16][: [1, 2, 4, 8, 16].index(S_MAX) + 1]:
-    for threads in sorted({S, max(1, S // 2)}, reverse=True):
+DEV = os.environ.get("SEQ_DEVICE_IMAGES", "0") != "0"      # images resident in HBM (bench.py's `value`) instead of page-locked host memory (e2e)
+pinned = {s: [torch.from_numpy(f).cuda() if DEV else torch.from_numpy(f).pin_memory() for f in data[s][0]] for s in seeds}
+for S in (LIST or [1, 2, 4, 8, 16][: [1, 2, 4, 8, 16].index(S_MAX) + 1]):
+    for threads in ([S] if LIST else sorted({S, max(1, S // 2)}, reverse=True)):
         sd = seeds[:S]
         job = bench.Job(gpu, sd, data, threads=threads)
         ptr = lambda i, k: pinned[sd[i]][k].data_ptr()
-        job.prime(ptr, bench.PRIME)
-        t, launches, h2d, d2h, first = bench.timed_region(job, ptr, False, steps, warm)
+        job.run(ptr, bench.PRIME, DEV, True)
+        t, launches, h2d, d2h, first = bench.timed_region(job, ptr, DEV, steps, warm)
         st = job.steady_state(first, first + steps)
         print("S %2d threads %2d: %.0f frames/s, %.3f ms/step, %.3f ms/frame/seq, kf %d" %
               (S, threads, S * steps / sum(t), 1e3 * sum(t) / steps, 1e3 * sum(t) / steps / S, st["keyframes_in_timed_region"]), flush=True)

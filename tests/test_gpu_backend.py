@@ -143,18 +143,37 @@ def test_gauss_newton_iterations_track_the_oracle(gpu, oracle, window):
     g.close(); o.close()
 
 
-def test_large_window_c4_shape(gpu, oracle):
-    """BASELINE config 4 shape: 752x480, 10 keyframes, 8000 points"""
-    W = synth.make_window(frame_ids=tuple(range(40, 100, 6)), pts_per_frame=800, w=752, h=480, fx=460.0, fy=460.0, cx=375.5, cy=239.5)
-    kw = dict(max_points=9000, max_residuals=80000, n_frame_slots=10)
-    g = util.make_ctx(gpu, "c4", **kw); o = util.make_ctx(oracle, "c4", **kw)
+def k7_bit_exact(g, o, W):
+    """every float of RawResidualJacobian, centerProjectedTo and the energies of the residuals linearize() touched"""
+    ns_g, ns_o = g.window_residual_ints(1), o.window_residual_ints(1)
+    assert np.array_equal(ns_g, ns_o)
+    act = ((W["flags"] & 1) == 0) & (ns_o != 1)
+    assert act.sum() > 0.3 * len(act)
+    for what in (0, 3, 4, 5):
+        a, b = g.window_residual_floats(what), o.window_residual_floats(what)
+        assert np.array_equal(bits(a[act]), bits(b[act])), what
+
+
+@pytest.mark.parametrize("calib,frame_ids,pts,kw", [
+    ("c4", tuple(range(40, 100, 6)), 800, dict(max_points=9000, max_residuals=80000, n_frame_slots=10)),   # configs[3]: 10 keyframes, 8000 points
+    ("c3", tuple(range(40, 75, 5)), 300, dict(max_points=4096, max_residuals=32768, n_frame_slots=10)),    # configs[2]: 1232x368, 7 keyframes
+])
+def test_large_window_shapes(gpu, oracle, calib, frame_ids, pts, kw):
+    """BASELINE configs[3] (752x480, 10 keyframes, 8000 points) and configs[2] (KITTI crop) windows: K7 bit-exact, states equal,
+    stitched K8 / K9 systems at 1e-4"""
+    W = synth.make_window(frame_ids=frame_ids, pts_per_frame=pts, **util.CALIB[calib])
+    g = util.make_ctx(gpu, calib, **kw); o = util.make_ctx(oracle, calib, **kw)
     for c in (g, o):
         for i, img in enumerate(W["imgs"]):
             c.make_images(i, img)
         c.window_load(W)
-        c.window_linearize(False); c.window_apply_res()
+        c.window_linearize(False)
+    k7_bit_exact(g, o, W)
+    for c in (g, o):
+        c.window_apply_res()
     assert np.array_equal(g.window_residual_ints(0), o.window_residual_ints(0))
     ag, ao = g.window_accumulate(), o.window_accumulate()
+    assert np.array_equal(ag["counts"], ao["counts"]) and ao["counts"][0] > 1000
     for k in ("HA", "bA", "HL", "bL", "Hsc", "bsc"):
         assert util.rel_err(ag[k], ao[k]) < 1e-4, (k, util.rel_err(ag[k], ao[k]))
     g.close(); o.close()
