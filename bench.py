@@ -46,12 +46,14 @@ WORKLOAD = ("configs[1] per sequence: synthetic 640x480 sequence (procedural box
             "include/ldso_system.hpp over the C ABI): makeImages, trackNewCoarse (83 motion hypotheses), keyframe decision, "
             "traceNewCoarse; keyframes: flagFramesForMarginalization, activatePointsMT, optimize (FEJ), removeOutliers, "
             "setCoarseTrackingRef, flagPointsForRemoval + marginalizePointsF into HM/bM, makeNewTraces, marginalizeFrame. "
+            "Input of a step: e2e and the CPU arm take the 8-bit sensor image (Undistort::undistort<unsigned char> in passthrough in "
+            "front of makeImages, run_dso_tum_mono.cc:405-429), value takes the float image resident in HBM. "
             "Timed at steady state after %d priming frames (CoarseInitializer bootstrap, window full, frames being marginalised). "
             "EnergyFunctional::nPoints counts the active points (npoints_counter_mode=1, upstream DSO's behaviour; the fork never "
             "increments it). %d independent sequences per GPU stepped together (configs[4])" % (STRIDE, PRIME, SEQ_PER_GPU))
 BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 128.0, "k6": 512.0,
                   "k10": 60.0, "k2": 8000.0, "a2": 24.0, "n2": 1.0, "n2sel": 24.0}
-PROF = [("k34_track_level_kernel", 0, "k34", "point evaluations"), ("k5_trace_kernel", 1, "k5", "search steps"),
+PROF = [("k34_track_cluster_kernel", 0, "k34", "point evaluations"), ("k5_trace_kernel", 1, "k5", "search steps"),
         ("k7_linearize_kernel", 2, "k7", "residuals"), ("k8_top_kernel", 3, "k8", "residuals"), ("k9_sc_kernel", 4, "k9", "residuals"),
         ("k1_pyramid_kernel", 5, "k1", "frames"), ("a2_selector_kernels", 6, "a2", "pixels"), ("k6_activate_kernel", 7, "k6", "candidates"),
         ("k10_resubstitute_kernel", 8, "k10", "points"), ("k2_coarse_depth_kernels", 9, "k2", "points"),
@@ -139,6 +141,8 @@ class Job:
         self.sys = [system.System(api, CALIB, gpu_kw=dict(device=device), npoints_counter_mode=DENSITY_MODE) for _ in seeds]
         self.batch = system.Batch(self.sys, threads)
         self.ctxs = [s.ctx() for s in self.sys]
+        for c in self.ctxs:                          # Undistort in front of makeImages: pinhole, no vignette / gamma -> passthrough
+            c.undistort_set(CALIB["w"], CALIB["h"], photometric_mode=0)
         self.k = 0                                   # next frame index
         self.kf_frames = [[] for _ in seeds]
         self.stat_log = []
@@ -171,8 +175,8 @@ class Job:
         self.k += n_frames
         return st
 
-    def prime(self, ptr_of, n):
-        self.run(ptr_of, n, False, True)
+    def prime(self, ptr_of, n, kind=0):
+        self.run(ptr_of, n, kind, True)
 
     def steady_state(self, first, last):
         """window / point / residual statistics of the steps [first, last) and the trajectory error of every sequence"""
@@ -199,8 +203,12 @@ class Job:
         return out
 
 
+RAW8 = 2    # LDSO_IMAGE_HOST_RAW8 (include/ldso_system.h): 8-bit sensor image in host memory
+
+
 def timed_region(job, ptr_of, is_device, steps, warmup, flush=None):
-    """W untimed + K timed steps (a step = one frame of every sequence).
+    """W untimed + K timed steps (a step = one frame of every sequence).  is_device: an LDSO_IMAGE_* kind (0 host float,
+    1 device float, 2 host 8-bit sensor image).
     One sequence: step by step, L2 flushed between steps; device-resident input -> CUDA events on the context's tracking stream
     (closing over its mapping stream), host input -> wall clock around the call with the streams drained inside the window.
     Several sequences: the K steps are ONE library call (ldso_gpu_batch_run): the sequences share nothing, so each runs its K
@@ -221,25 +229,25 @@ def timed_region(job, ptr_of, is_device, steps, warmup, flush=None):
         for _ in range(steps):
             if flush is not None:
                 flush()                                  # evict L2 between timed steps (outside the timed window)
-            if is_device:
+            if is_device == 1:
                 job.ctxs[0].timer_start()
                 job.step([ptr_of(0, job.k)], True, False)
                 times.append(job.ctxs[0].timer_stop() * 1e-3)
             else:
                 t0 = time.perf_counter()
-                job.step([ptr_of(0, job.k)], False, True)   # returns after the frame is done and the context's streams are drained
+                job.step([ptr_of(0, job.k)], is_device, True)   # returns after the frame is done and the context's streams are drained
                 times.append(time.perf_counter() - t0)
     else:
         if flush is not None:
             flush()
-        if is_device:
+        if is_device == 1:
             for c in job.ctxs:
                 c.timer_start()
             job.run(ptr_of, steps, True, False)
             times.append(max(c.timer_stop() for c in job.ctxs) * 1e-3)
         else:
             t0 = time.perf_counter()
-            job.run(ptr_of, steps, False, True)
+            job.run(ptr_of, steps, is_device, True)
             times.append(time.perf_counter() - t0)
     io1 = [c.io_bytes() for c in job.ctxs]
     return (times, sum(c.launch_count() for c in job.ctxs) - l0, sum(b[0] - a[0] for a, b in zip(io0, io1)),
@@ -264,6 +272,13 @@ def reduce_over_ranks(times, mine, world, dist, torch, device):
     return tt.tolist(), per_rank
 
 
+def to_raw8(f):
+    """the rendered frames are uint8-quantised floats: the 8-bit sensor image holds exactly the same values"""
+    r = np.ascontiguousarray(f, dtype=np.uint8)
+    assert np.array_equal(r.astype(np.float32), f)
+    return r
+
+
 def cpu_arm(seeds, data, steps, warmup, threads_total):
     """the same control flow over the CPU oracle (kind "port": the reference itself cannot be compiled here) on the host
     cores: one worker thread per sequence, the oracle's OpenMP workers inside each (the reference's IndexThreadReduce
@@ -277,10 +292,10 @@ def cpu_arm(seeds, data, steps, warmup, threads_total):
     os.environ["ORC_THREADS"] = str(inner)
     api = capi.Api(lib, "orc_")
     job = Job(api, seeds, data, threads=workers)
-    frames = {s: [np.ascontiguousarray(f, np.float32) for f in data[s][0]] for s in seeds}
+    frames = {s: [to_raw8(f) for f in data[s][0]] for s in seeds}          # the same 8-bit sensor images the GPU arm's e2e is fed
     ptr_of = lambda i, k: frames[seeds[i]][k].ctypes.data
-    job.prime(ptr_of, PRIME)
-    times, _, _, _, first = timed_region(job, ptr_of, False, steps, warmup)
+    job.prime(ptr_of, PRIME, RAW8)
+    times, _, _, _, first = timed_region(job, ptr_of, RAW8, steps, warmup)
     st = job.steady_state(first, first + steps)
     job.close()
     return times, st, workers, inner, march
@@ -343,17 +358,19 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    pinned = {s: [torch.from_numpy(np.ascontiguousarray(f, np.float32)).pin_memory() for f in data[s][0]] for s in seeds}
-    dev = {s: [t.cuda() for t in pinned[s]] for s in seeds}
+    # e2e input: the 8-bit sensor image in page-locked host memory (what a camera driver / image reader delivers; Undistort runs
+    # on the device in front of makeImages); value input: the float image Undistort hands over, resident in HBM
+    pinned = {s: [torch.from_numpy(to_raw8(f)).pin_memory() for f in data[s][0]] for s in seeds}
+    dev = {s: [torch.from_numpy(np.ascontiguousarray(f, np.float32)).cuda() for f in data[s][0]] for s in seeds}
     torch.cuda.synchronize()
     host_ptr = lambda sd: (lambda i, k: pinned[sd[i]][k].data_ptr())
     dev_ptr = lambda sd: (lambda i, k: dev[sd[i]][k].data_ptr())
 
     def run_pass(sd, is_device):
         job = Job(gpu, sd, data, device=local_rank)
-        job.prime(host_ptr(sd), PRIME)
+        job.prime(host_ptr(sd), PRIME, RAW8)
         barrier()
-        r = timed_region(job, dev_ptr(sd) if is_device else host_ptr(sd), is_device, steps, warmup, flush)
+        r = timed_region(job, dev_ptr(sd) if is_device else host_ptr(sd), 1 if is_device else RAW8, steps, warmup, flush)
         barrier()
         st = job.steady_state(r[4], r[4] + steps)
         phases = [s.phase_seconds() for s in job.sys]
@@ -378,10 +395,10 @@ def main():
 
     # per-kernel CUDA-event profile: one sequence, steady state (separate pass, not a timed number)
     job = Job(gpu, seeds[:1], data, device=local_rank)
-    job.prime(host_ptr(seeds[:1]), PRIME + warmup)
+    job.prime(host_ptr(seeds[:1]), PRIME + warmup, RAW8)
     job.ctxs[0].profile_enable(True)
     for _ in range(steps):
-        job.step([host_ptr(seeds[:1])(0, job.k)], False, True)
+        job.step([host_ptr(seeds[:1])(0, job.k)], RAW8, True)
     prof = {name: job.ctxs[0].profile_get(which) + (key, unit) for (name, which, key, unit) in PROF}
     prof_kf = sum(1 for f in job.kf_frames[0] if f >= PRIME + warmup)
     job.close()
@@ -409,7 +426,8 @@ def main():
                 gpu_launches=int(launches), clocks=clk.summary(),
                 timing="the K steps of the S sequences of a GPU are one ldso_gpu_batch_run call (no rendezvous between frames); value: "
                        "CUDA events on every context's tracking stream (closing over its mapping stream) around the region, longest "
-                       "context wins, max over ranks; e2e: host wall clock around the call, page-locked host images, every context's "
+                       "context wins, max over ranks; e2e: host wall clock around the call, input = the 8-bit sensor image in page-locked host "
+                       "memory (LDSO_IMAGE_HOST_RAW8: Undistort in passthrough + makeImages on the device; 0.3 MB per frame cross the bus), every context's "
                        "streams drained inside the window; L2: flushed once before the region, every frame's image is new data read "
                        "once (S x K x 1.2 MB of input > 126 MB L2); single_sequence: step by step, L2 flushed with a 256 MiB write "
                        "between steps",

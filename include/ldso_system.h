@@ -85,8 +85,17 @@ ldso_gpu_ctx* ldso_gpu_system_ctx(ldso_gpu_system* sys);
 #define LDSO_SYS_ST_FRAME_ID 9      /* Frame::id given to the frame */
 #define LDSO_SYS_ST_N 16
 
+/* what the image pointer of add_active_frame / batch_* is (the `image_is_device` argument; 0 and 1 keep their old meaning) */
+#define LDSO_IMAGE_HOST_F32 0     /* w*h floats in host memory: ImageAndExposure::image, what Undistort hands over */
+#define LDSO_IMAGE_DEVICE_F32 1   /* the same, already resident in HBM (a DEVICE pointer) */
+#define LDSO_IMAGE_HOST_RAW8 2    /* the 8-bit sensor image (w_org*h_org bytes, host): Undistort::undistort<unsigned char> */
+#define LDSO_IMAGE_HOST_RAW16 3   /* (src/frontend/Undistort.cc:366-458) runs on the device in front of makeImages; the tables
+                                     are those of ldso_gpu_undistort_set on ldso_gpu_system_ctx(sys); a quarter (half) of the bytes
+                                     of the float image cross the bus */
+
 /* FullSystem::addActiveFrame(ImageAndExposure*, imu) (src/frontend/FullSystem.cc:78-187).  image: w*h floats (irradiance
- * 0..255, what Undistort hands over); image_is_device != 0: `image` is a DEVICE pointer (inputs already resident in HBM).
+ * 0..255, what Undistort hands over); image_is_device: one of LDSO_IMAGE_* (1: `image` is a DEVICE pointer, inputs already
+ * resident in HBM; 2 / 3: `image` points to the raw 8 / 16-bit sensor image).
  * pose_out (may be NULL): worldToCam of the frame after the call (Frame::getPose), identity while initialising.
  * status_out (may be NULL): LDSO_SYS_ST_N ints.  Returns 0; 1 when the system is lost (the reference returns at once). */
 int ldso_gpu_system_add_active_frame(ldso_gpu_system* sys, const float* image, int image_is_device, double timestamp,

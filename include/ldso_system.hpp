@@ -41,7 +41,7 @@
         typedef CTX ctx_t;                                                                                              \
         LDSO_API_FN(P, default_config) LDSO_API_FN(P, create) LDSO_API_FN(P, destroy) LDSO_API_FN(P, last_error)         \
         LDSO_API_FN(P, pyr_levels) LDSO_API_FN(P, level_size) LDSO_API_FN(P, sync) LDSO_API_FN(P, bind_thread)                                    \
-        LDSO_API_FN(P, frame_make_images) LDSO_API_FN(P, frame_make_images_dev)                                          \
+        LDSO_API_FN(P, frame_make_images) LDSO_API_FN(P, frame_make_images_dev) LDSO_API_FN(P, frame_make_images_raw)    \
         LDSO_API_FN(P, tracker_make_k) LDSO_API_FN(P, tracker_set_ref) LDSO_API_FN(P, tracker_track)                     \
         LDSO_API_FN(P, select_points) LDSO_API_FN(P, detect_corners)                                                     \
         LDSO_API_FN(P, immature_create) LDSO_API_FN(P, immature_append) LDSO_API_FN(P, immature_set_types)               \
@@ -69,6 +69,7 @@
     int P##bind_thread(CTX*);                                                                                            \
     int P##frame_make_images(CTX*, int, const float*);                                                                   \
     int P##frame_make_images_dev(CTX*, int, const float*);                                                               \
+    int P##frame_make_images_raw(CTX*, int, const void*, int, float, float);                                             \
     int P##tracker_make_k(CTX*, int, float, float, float, float);                                                        \
     int P##tracker_set_ref(CTX*, int, int, int, const float*, const float*, const float*, const float*, float, float, float); \
     int P##tracker_track(CTX*, int, int, float, double*, float*, int, const float*, float*, float*, int*);               \
@@ -497,7 +498,9 @@ public:
     }
 
     // ---- FullSystem::addActiveFrame (src/frontend/FullSystem.cc:78-187) ----------------------------------------------
-    int addActiveFrame(const float* image, bool image_is_device, double timestamp, float exposure_time, double pose_out[12],
+    // image_kind: LDSO_IMAGE_HOST_F32 / _DEVICE_F32 (ImageAndExposure::image as Undistort hands it over) or LDSO_IMAGE_HOST_RAW8 /
+    // _RAW16: the sensor image, through Undistort::undistort<T> on the device in front of makeImages (run_dso_tum_mono.cc:405-429)
+    int addActiveFrame(const float* image, int image_kind, double timestamp, float exposure_time, double pose_out[12],
                        int* status_out) {
         if (isLost) { fill_status(status_out, nullptr, false); return 1; }
         const double t0 = now();
@@ -511,7 +514,12 @@ public:
         free_slots.pop_back();
         counters[LDSO_SYS_CT_FRAMES]++;
         // fh->makeImages(image, Hcalib) (:93)
-        int rc = image_is_device ? Api::frame_make_images_dev(ctx, fh->slot, image) : Api::frame_make_images(ctx, fh->slot, image);
+        int rc;
+        if (image_kind == LDSO_IMAGE_DEVICE_F32) rc = Api::frame_make_images_dev(ctx, fh->slot, image);
+        else if (image_kind == LDSO_IMAGE_HOST_F32) rc = Api::frame_make_images(ctx, fh->slot, image);
+        else if (image_kind == LDSO_IMAGE_HOST_RAW8 || image_kind == LDSO_IMAGE_HOST_RAW16)
+            rc = Api::frame_make_images_raw(ctx, fh->slot, (const void*)image, image_kind == LDSO_IMAGE_HOST_RAW8 ? 1 : 2, exposure_time, 1.0f);
+        else return fail("unknown image kind");
         if (rc < 0) return fail_api();
         phase_s[8] += now() - t0;
         bool madeKF = false;
@@ -1729,7 +1737,7 @@ public:
     struct Job {
         const float* const* images = nullptr;   // n_frames image pointers of this system, fed in order
         int n_frames = 1;
-        int is_device = 0;
+        int is_device = 0;                      // LDSO_IMAGE_* kind of the pointers
         double timestamp = 0;                   // of the first frame; later frames count up by one
         float exposure = 1;
         double* pose_out = nullptr;             // [n_frames][12]
@@ -1792,7 +1800,7 @@ private:
                 for (size_t i = t; i < sys.size(); i += T) {
                     Job& j = jobs[i];
                     if (f >= j.n_frames || j.rc < 0) continue;
-                    j.rc = sys[i]->impl.addActiveFrame(j.images[f], j.is_device != 0, j.timestamp + f, j.exposure,
+                    j.rc = sys[i]->impl.addActiveFrame(j.images[f], j.is_device, j.timestamp + f, j.exposure,
                                                        j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
                                                        j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
                 }
@@ -1844,7 +1852,7 @@ private:
     extern "C" int P##system_add_active_frame(P##system* s, const float* image, int image_is_device, double timestamp,    \
                                               float exposure_time, double pose_out[12], int* status_out) {                \
         if (!s || !image) return -2;                                                                                      \
-        return s->impl.addActiveFrame(image, image_is_device != 0, timestamp, exposure_time, pose_out, status_out);       \
+        return s->impl.addActiveFrame(image, image_is_device, timestamp, exposure_time, pose_out, status_out);            \
     }                                                                                                                     \
     extern "C" int P##system_get_trajectory(P##system* s, int max_n, int* ids, double* poses, int* is_kf,                 \
                                             int relative_to_ref) {                                                        \

@@ -941,14 +941,8 @@ __device__ __forceinline__ ldso_sm::SE3 cl_se3_exp(const double* a) {
 // upper-triangle index t (0..44) of the 9x9 system -> (row, column)
 __constant__ unsigned char c_tri_r[45] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2, 2, 3, 3, 3, 3, 3, 3, 4, 4, 4, 4, 4, 5, 5, 5, 5, 6, 6, 6, 7, 7, 8};
 __constant__ unsigned char c_tri_c[45] = {0, 1, 2, 3, 4, 5, 6, 7, 8, 1, 2, 3, 4, 5, 6, 7, 8, 2, 3, 4, 5, 6, 7, 8, 3, 4, 5, 6, 7, 8, 4, 5, 6, 7, 8, 5, 6, 7, 8, 6, 7, 8, 7, 8, 8};
-__device__ __forceinline__ void cl_Hb_entry(const double* r, double* H, double* b, int t) {   // lm_Hb_entry with the index table
-    const int n = ((int)r[NF + 2] + 3) & ~3;
-    const double invn = (double)(1.0f / n);
-    const int rr = c_tri_r[t], cc = c_tri_c[t];
-    auto sc = [](int i) { return i < 3 ? (double)LDSO_SCALE_XI_TRANS : i < 6 ? (double)LDSO_SCALE_XI_ROT : i == 6 ? (double)LDSO_SCALE_A : (double)LDSO_SCALE_B; };
-    const double v = r[t] * invn;
-    if (rr < 8 && cc < 8) H[rr * 8 + cc] = H[cc * 8 + rr] = v * sc(rr) * sc(cc);
-    else if (rr < 8) b[rr] = v * sc(rr);
+__device__ __forceinline__ double cl_scale(int i) {
+    return i < 3 ? (double)LDSO_SCALE_XI_TRANS : i < 6 ? (double)LDSO_SCALE_XI_ROT : i == 6 ? (double)LDSO_SCALE_A : (double)LDSO_SCALE_B;
 }
 // lm_decide with one division per evaluation: the accepted mean energy is kept, the flow indicators and the saturation
 // ratio are formed only where they are read (CoarseTracker.cc:94-99, 213-247, 664-672)
@@ -1030,8 +1024,10 @@ k34_track_cluster_kernel(const LmAll A, double* __restrict__ mailbox, double seq
     __shared__ double s_A[64];
     __shared__ int s_cmd;
     __shared__ long long s_t[8];
+    __shared__ unsigned char s_tri[48];          // (row << 4) | column of the 45 upper-triangle entries (lane-varying index: not constant memory)
     long long tk = 0;
     if (threadIdx.x < 8) s_t[threadIdx.x] = 0;
+    if (threadIdx.x < 45) s_tri[threadIdx.x] = (unsigned char)((c_tri_r[threadIdx.x] << 4) | c_tri_c[threadIdx.x]);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         k = A.base;
@@ -1126,14 +1122,22 @@ k34_track_cluster_kernel(const LmAll A, double* __restrict__ mailbox, double seq
         cluster.sync();          // barrier.cluster arrive.release / wait.acquire: the pushed partials are visible
         if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[1] += now - tk; tk = now; }
         if (threadIdx.x < NV) {
-            double v = 0.0;
-            for (int r = 0; r < C; r++) v += (double)tab[r][threadIdx.x];
+            // fold in rank order; the threads of the 45 H / b entries also fold the point count their entry is divided by
+            // (CoarseTracker.cc:724-726), so the scaled system is written here, without a second pass over s_res
+            double v = 0.0, cn = 0.0;
+            for (int r = 0; r < C; r++) { v += (double)tab[r][threadIdx.x]; cn += (double)tab[r][NF + 2]; }
             s_res[threadIdx.x] = v;
+            if (threadIdx.x < 45) {
+                const int n = ((int)cn + 3) & ~3;
+                const double w = v * (double)(1.0f / n);
+                const int rr = s_tri[threadIdx.x] >> 4, cc = s_tri[threadIdx.x] & 15;
+                double* H = st.H[st.hsel ^ 1];
+                if (rr < 8 && cc < 8) H[rr * 8 + cc] = H[cc * 8 + rr] = w * cl_scale(rr) * cl_scale(cc);
+                else if (rr < 8) st.bv[st.hsel ^ 1][rr] = w * cl_scale(rr);
+            }
         }
         __syncthreads();
         if (k.dbg == 3 && threadIdx.x == 0) { const long long now = clock64(); s_t[2] += now - tk; tk = now; }
-        if (threadIdx.x < 45) cl_Hb_entry(s_res, st.H[st.hsel ^ 1], st.bv[st.hsel ^ 1], threadIdx.x);
-        __syncthreads();
         const bool fixed = k.optA < 0 || k.optB < 0;
         if (threadIdx.x == 0) {
             st.work += npts;

@@ -238,17 +238,19 @@ __device__ __forceinline__ void border_fix(unsigned char* D, int x, int y, int w
     if (v < D[x + w1 * y]) D[x + w1 * y] = (unsigned char)v;
 }
 
-// n2_walk_kernel (one CTA; after the set-up ONE warp): the ordered walk over the surviving candidates.
+// n2_walk_kernel (one CTA; after the set-up four warps): the ordered walk over the surviving candidates.
 //   * the candidates are compacted in pool order (CTA-wide scan) so the warp tests 32 real candidates per step;
 //   * CoarseDistanceMap::addIntoDistFinal + growDistBFS(1) (CoarseTracker.cc:925-930) on the shared-memory map is a
 //     pointwise minimum with the ring-distance TEMPLATE of the source, out to ring R (rings beyond the largest activation
 //     threshold cannot change a decision of the walk): the template is built once per launch in shared memory and the
 //     stamp is taken four cells at a time (__vminu4 of an aligned map word and the template bytes under it, fetched from
 //     two template words by a funnel shift); border cells follow from their interior neighbours where the box reaches them;
-//   * the whole walk runs inside one warp (no CTA barrier per accepted point).
+//   * warp 0 decides which candidate is accepted next (32 candidates per test); four warps (one per scheduler: a lone warp
+//     issues one dependent instruction every ~5 cycles, and the stamp is ~300 map words) stamp it; they meet at a named
+//     barrier of 128 threads before and after each stamp.
 __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int s_scan[N2_SEL_THREADS / 32], s_off[N2_SEL_THREADS], s_cnt[N2_SEL_THREADS];
+    __shared__ int s_scan[N2_SEL_THREADS / 32], s_off[N2_SEL_THREADS], s_cnt[N2_SEL_THREADS], s_c0[2];
     const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
     unsigned char* D = smem;
     unsigned char* T = smem + (size_t)cells16 * 16;
@@ -289,8 +291,9 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) 
         }
     }
     __syncthreads();
-    if (wid != 0) return;
-    // ---- the walk (warp 0)
+    constexpr int WT = 128;                              // threads that stay for the walk: warp 0 decides, four warps stamp
+    if (tid >= WT) return;
+    // ---- the walk
     const int w1 = p.w1, h1 = p.h1;
     const unsigned* T32 = reinterpret_cast<const unsigned*>(T);
     unsigned* D32 = reinterpret_cast<unsigned*>(D);
@@ -299,94 +302,106 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) 
     int nacc = 0;
     // A corner cell has ONE interior neighbour, a diagonal one, which can claim it only on an odd ring.  The
     // reference's incremental BFS therefore leaves a corner at the best value that neighbour ever offered while the
-    // walk lowered it — not a function of the final map.  Lanes 0..3 follow one corner each.
+    // walk lowered it — not a function of the final map.  Lanes 0..3 of warp 0 follow one corner each.
     const int kx = (lane & 1) ? w1 - 1 : 0, ky = (lane & 2) ? h1 - 1 : 0;
     const int qx = (lane & 1) ? w1 - 2 : 1, qy = (lane & 2) ? h1 - 2 : 1;
     int cv = 255, qv = 255;
-    if (lane < 4) { cv = D[kx + w1 * ky]; qv = D[qx + w1 * qy]; }
-    int cell = lane < K ? p.ccell[lane] : -1;
-    float fr = lane < K ? p.cfrac[lane] : 0.f, th = lane < K ? p.cthr[lane] : 0.f;
-    int idx = lane < K ? p.cidx[lane] : 0;
-    for (int base = 0; base < K; base += 32) {
-        const int inext = base + 32 + lane;
-        int cell_n = -1, idx_n = 0;
-        float fr_n = 0.f, th_n = 0.f;
-        if (inext < K) { cell_n = p.ccell[inext]; fr_n = p.cfrac[inext]; th_n = p.cthr[inext]; idx_n = p.cidx[inext]; }
-        int from = 0;
-        while (from < 32) {
-            bool pass = false;
-            if (cell >= 0 && lane >= from) {
-                const unsigned char d = D[cell];
-                pass = (d == 255 ? 1000.f : (float)d) + fr >= th;
-            }
-            const unsigned m = __ballot_sync(0xffffffffu, pass);
-            if (!m) break;
-            const int j = __ffs(m) - 1;
-            const int c0 = __shfl_sync(0xffffffffu, cell, j);
-            if (lane == j) { p.action[idx] = 2; p.src_cells[n0 + nacc] = c0; }
-            nacc++;
-            from = j + 1;
-            // ---- stamp c0
-            const int sy = c0 / w1, sx = c0 - sy * w1;
-            const bool interior = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1;
-            if (lane == 0) D[c0] = 0;
-            if (lane < 4) {
-                if (sx == kx && sy == ky) cv = 0;
-                if (interior) {
-                    qv = min(qv, ring_dist(qx - sx, qy - sy));
-                    const int cand = qv + 1;
-                    if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
-                }
-                if (cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
-            }
-            if (interior && R > 0) {
-                const int ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
-                if (words) {
-                    const int x0 = sx - R;
-                    const int wlo = x0 <= 0 ? 0 : (x0 >> 2), whi = min(sx + R, w1 - 1) >> 2, wlast = (w1 >> 2) - 1;
-                    const int nw = whi - wlo + 1, slots = (yhi - ylo + 1) * nw;
-                    const float inv_nw = 1.0f / (float)nw;                  // (t + 0.5) / nw stays 0.5 / nw away from an integer: exact floor
-#pragma unroll 4
-                    for (int t = lane; t < slots; t += 32) {
-                        const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
-                        {
-                            const int y = ylo + ry, wx = wlo + wq;
-                            const int b = 4 + 4 * wx - x0;                       // template byte under the word's first cell (>= 1)
-                            const unsigned* trow = T32 + ((y - sy + R) * N2_TPL_STRIDE >> 2) + (b >> 2);
-                            unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
-                            if (wx == 0) tv |= 0xffu;                            // column 0 and column w1 - 1 are border cells
-                            if (wx == wlast) tv |= 0xff000000u;
-                            const int wi = (y * w1 >> 2) + wx;
-                            const unsigned dv = D32[wi], mv = __vminu4(dv, tv);
-                            if (mv != dv) D32[wi] = mv;
-                        }
-                    }
-                } else {
-                    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R);
-                    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
-                    for (int t = lane; t < nc; t += 32) {
-                        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
-                        const int d = ring_dist(x - sx, y - sy);
-                        const int di = x + w1 * y;
-                        if (d <= R && D[di] > d) D[di] = (unsigned char)d;
-                    }
-                }
-                if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {
-                    // the box reaches the border ring: those cells follow from their interior neighbours
-                    __syncwarp();
-                    const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
-                    if (by0 == 0) for (int x = bx0 + lane; x <= bx1; x += 32) border_fix(D, x, 0, w1, h1);
-                    if (by1 == h1 - 1) for (int x = bx0 + lane; x <= bx1; x += 32) border_fix(D, x, h1 - 1, w1, h1);
-                    if (bx0 == 0) for (int y = max(1, by0) + lane; y <= min(h1 - 2, by1); y += 32) border_fix(D, 0, y, w1, h1);
-                    if (bx1 == w1 - 1) for (int y = max(1, by0) + lane; y <= min(h1 - 2, by1); y += 32) border_fix(D, w1 - 1, y, w1, h1);
-                }
-            }
-            __syncwarp();
-        }
-        cell = cell_n; fr = fr_n; th = th_n; idx = idx_n;
+    if (tid < 4) { cv = D[kx + w1 * ky]; qv = D[qx + w1 * qy]; }
+    // walker state (warp 0): the chunk of 32 candidates under test, the next chunk in flight
+    int base = 0, from = 0;
+    int cell = -1, idx = 0, cell_n = -1, idx_n = 0;
+    float fr = 0.f, th = 0.f, fr_n = 0.f, th_n = 0.f;
+    if (wid == 0) {
+        if (lane < K) { cell = p.ccell[lane]; fr = p.cfrac[lane]; th = p.cthr[lane]; idx = p.cidx[lane]; }
+        if (32 + lane < K) { cell_n = p.ccell[32 + lane]; fr_n = p.cfrac[32 + lane]; th_n = p.cthr[32 + lane]; idx_n = p.cidx[32 + lane]; }
     }
-    if (lane == 0) { *p.src_n = n0 + nacc; p.cnt[0] = nacc; }
-    if (lane < 4) p.corner[lane] = cv;
+    for (int par = 0;; par ^= 1) {
+        if (wid == 0) {
+            // the next accepted candidate, in pool order (a rejected one can never pass later: the map only decreases)
+            int c0 = -1;
+            while (base < K) {
+                bool pass = false;
+                if (cell >= 0 && lane >= from) {
+                    const unsigned char d = D[cell];
+                    pass = (d == 255 ? 1000.f : (float)d) + fr >= th;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, pass);
+                if (m) {
+                    const int j = __ffs(m) - 1;
+                    c0 = __shfl_sync(0xffffffffu, cell, j);
+                    if (lane == j) { p.action[idx] = 2; p.src_cells[n0 + nacc] = c0; }
+                    nacc++;
+                    from = j + 1;
+                    break;
+                }
+                base += 32; from = 0;
+                cell = cell_n; fr = fr_n; th = th_n; idx = idx_n;
+                const int inext = base + 32 + lane;
+                cell_n = -1;
+                if (inext < K) { cell_n = p.ccell[inext]; fr_n = p.cfrac[inext]; th_n = p.cthr[inext]; idx_n = p.cidx[inext]; }
+            }
+            if (lane == 0) s_c0[par] = c0;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int c0 = s_c0[par];
+        if (c0 < 0) break;
+        // ---- stamp c0 (all four warps)
+        const int sy = c0 / w1, sx = c0 - sy * w1;
+        const bool interior = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1;
+        if (tid == 0) D[c0] = 0;
+        if (tid < 4) {
+            if (sx == kx && sy == ky) cv = 0;
+            if (interior) {
+                qv = min(qv, ring_dist(qx - sx, qy - sy));
+                const int cand = qv + 1;
+                if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
+            }
+            if (cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
+        }
+        if (interior && R > 0) {
+            const int ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
+            if (words) {
+                const int x0 = sx - R;
+                const int wlo = x0 <= 0 ? 0 : (x0 >> 2), whi = min(sx + R, w1 - 1) >> 2, wlast = (w1 >> 2) - 1;
+                const int nw = whi - wlo + 1, slots = (yhi - ylo + 1) * nw;
+                const float inv_nw = 1.0f / (float)nw;                  // (t + 0.5) / nw stays 0.5 / nw away from an integer: exact floor
+#pragma unroll 2
+                for (int t = tid; t < slots; t += WT) {
+                    const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
+                    const int y = ylo + ry, wx = wlo + wq;
+                    const int b = 4 + 4 * wx - x0;                       // template byte under the word's first cell (>= 1)
+                    const unsigned* trow = T32 + ((y - sy + R) * N2_TPL_STRIDE >> 2) + (b >> 2);
+                    unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
+                    if (wx == 0) tv |= 0xffu;                            // column 0 and column w1 - 1 are border cells
+                    if (wx == wlast) tv |= 0xff000000u;
+                    const int wi = (y * w1 >> 2) + wx;
+                    const unsigned dv = D32[wi], mv = __vminu4(dv, tv);
+                    if (mv != dv) D32[wi] = mv;
+                }
+            } else {
+                const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R);
+                const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
+                for (int t = tid; t < nc; t += WT) {
+                    const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
+                    const int d = ring_dist(x - sx, y - sy);
+                    const int di = x + w1 * y;
+                    if (d <= R && D[di] > d) D[di] = (unsigned char)d;
+                }
+            }
+            if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {   // uniform over the CTA
+                // the box reaches the border ring: those cells follow from their interior neighbours
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
+                if (by0 == 0) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, 0, w1, h1);
+                if (by1 == h1 - 1) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, h1 - 1, w1, h1);
+                if (bx0 == 0) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, 0, y, w1, h1);
+                if (bx1 == w1 - 1) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, w1 - 1, y, w1, h1);
+            }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    if (tid == 0) { *p.src_n = n0 + nacc; p.cnt[0] = nacc; }
+    if (tid < 4) p.corner[lane] = cv;
 }
 
 __global__ void n2_types_kernel(int n, const float* __restrict__ src, float* __restrict__ dst) {

@@ -99,8 +99,9 @@ class System:
         return v
 
     def add_frame_ptr(self, ptr, is_device=False, timestamp=0.0, exposure=1.0):
-        """hot loop: raw pointer in, status array (shared, overwritten by the next call) out"""
-        rc = self._add(self.h, ptr, 1 if is_device else 0, timestamp, exposure, self._pose_p, self._status_p)
+        """hot loop: raw pointer in, status array (shared, overwritten by the next call) out.  is_device: False / True, or an
+        LDSO_IMAGE_* kind (2 = host 8-bit sensor image through the device-side Undistort, see include/ldso_system.h)"""
+        rc = self._add(self.h, ptr, int(is_device), timestamp, exposure, self._pose_p, self._status_p)
         if rc < 0:
             raise capi.LdsoError(f"{self.api.prefix}system_add_active_frame rc={rc}: {self.api.fn('system_last_error')(self.h).decode()}")
         self.n_fed += 1
@@ -153,12 +154,21 @@ class System:
         return dict(zip(PHASES, out.tolist()))
 
 
-def run(api, calib, frames, **kw):
-    """feed a list of images; returns (system, per-frame status dicts, per-keyframe logs)"""
+def run(api, calib, frames, raw8=False, **kw):
+    """feed a list of images; returns (system, per-frame status dicts, per-keyframe logs).  raw8: hand the frames over as
+    8-bit sensor images (LDSO_IMAGE_HOST_RAW8: Undistort in passthrough + makeImages inside the library)"""
     s = System(api, calib, **kw)
+    if raw8:
+        s.ctx().undistort_set(calib["w"], calib["h"], photometric_mode=0)
     sts, kfs = [], []
     for img in frames:
-        st, _ = s.add_frame(img)
+        if raw8:
+            r8 = np.ascontiguousarray(img, dtype=np.uint8)
+            assert np.array_equal(r8.astype(np.float32), img)
+            st = s.add_frame_ptr(r8.ctypes.data_as(C.c_void_p), 2, float(s.n_fed))
+            st = {k: int(st[i]) for k, i in ST.items()}
+        else:
+            st, _ = s.add_frame(img)
         sts.append(st)
         if st["keyframe"]:
             kfs.append(dict(s.keyframe_log(), frame=st["frame_id"], window=s.window()))
@@ -207,7 +217,7 @@ class Batch:
         """ptrs: one raw image pointer per system; returns the shared [n,16] status array (overwritten by the next call)"""
         for i, p in enumerate(ptrs):
             self._ptrs[i] = p
-        rc = self._step(self.h, self._ptrs, 1 if is_device else 0, None, None, 1 if sync_after else 0, self._pp, self._sp)
+        rc = self._step(self.h, self._ptrs, int(is_device), None, None, 1 if sync_after else 0, self._pp, self._sp)
         if rc < 0:
             msgs = [s.api.fn("system_last_error")(s.h).decode() for s in self.systems]
             raise capi.LdsoError(f"{self.api.prefix}batch_add_active_frames rc={rc}: {[m for m in msgs if m]}")
@@ -223,7 +233,7 @@ class Batch:
         status = np.zeros((n, nf, 16), np.int32)
         f = self.api.fn("batch_run")
         f.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p, C.c_void_p]
-        rc = f(self.h, nf, arr, 1 if is_device else 0, 1 if sync_after else 0, None, status.ctypes.data_as(C.c_void_p))
+        rc = f(self.h, nf, arr, int(is_device), 1 if sync_after else 0, None, status.ctypes.data_as(C.c_void_p))
         if rc < 0:
             msgs = [s.api.fn("system_last_error")(s.h).decode() for s in self.systems]
             raise capi.LdsoError(f"{self.api.prefix}batch_run rc={rc}: {[m for m in msgs if m]}")

@@ -202,3 +202,28 @@ def test_gpu_batch_of_sequences_equals_each_alone(gpu):
         # atomics make float sums order-dependent at 1e-7: trajectories agree far below the parity tolerance
         assert np.abs(s.centres()[1] - a.centres()[1]).max() < 1e-4
     b.close()
+
+
+def _raw8_equals_float(api, exact):
+    c, frames, poses = _seq("small", 40)
+    a, sta, kfa = system.run(api, c, frames, desired_point_density=600, desired_immature_density=500)
+    b, stb, kfb = system.run(api, c, frames, raw8=True, desired_point_density=600, desired_immature_density=500)
+    assert [s["keyframe"] for s in sta] == [s["keyframe"] for s in stb] and sum(s["keyframe"] for s in sta) >= 2
+    ia, ca, _ = a.centres(); ib, cb, _ = b.centres()
+    assert np.array_equal(ia, ib)
+    if exact:   # the same float image reaches makeImages: the (deterministic) oracle repeats itself bit for bit
+        assert np.array_equal(ca, cb)
+    else:       # two GPU runs differ in the order of their atomic sums (K2 weights, fp64 accumulators): 1e-4 of the path
+        path = np.linalg.norm(np.diff(ca, axis=0), axis=1).sum()
+        assert np.abs(ca - cb).max() < 1e-4 * path, (np.abs(ca - cb).max(), path)
+    a.close(); b.close()
+
+
+def test_oracle_system_raw8_input_equals_float_input(oracle):
+    """LDSO_IMAGE_HOST_RAW8: the 8-bit sensor image through Undistort (passthrough) in front of makeImages"""
+    _raw8_equals_float(oracle, True)
+
+
+@pytest.mark.gpu
+def test_gpu_system_raw8_input_equals_float_input(gpu):
+    _raw8_equals_float(gpu, False)
