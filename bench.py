@@ -35,7 +35,9 @@ from ldso_b200 import capi, synth, system  # noqa: E402
 
 CALIB = dict(w=640, h=480, fx=384.0, fy=384.0, cx=319.5, cy=239.5)
 STRIDE = 3               # camera speed: every 3rd frame of the synthetic 30 Hz trajectory -> a keyframe every ~8-10 frames
-SEQ_PER_GPU = 8          # BASELINE.json configs[4]: 64 sequences / 8 GPUs
+SEQ_PER_GPU = 8          # BASELINE.json configs[4]: 64 sequences / 8 GPUs.  (More per GPU is faster in absolute terms — 16: 16.5 k
+                         # frames/s device-timed, 14.8 k e2e on one B200 with 16 host cores against 12.2 k at 8, profiles/r2u_bench_s16.json —
+                         # but the CPU arm gains as much from 16 single-threaded workers; --sequences-per-gpu selects it.)
 PRIME = 110              # untimed frames per sequence before warm-up: initializer, window fills to 7 (frame ~62), first frames
                          # marginalised (~70); the 20 frames after 115 hold two keyframes, the sequence's average density
 DENSITY_MODE = 1         # npoints_counter_mode (include/ldso_system.h): 1 = the window holds ~desiredPointDensity points
@@ -307,6 +309,9 @@ def main():
     ap.add_argument("--steps", type=int, default=40, help="timed steps (one frame of every sequence each)")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--sequences-per-gpu", type=int, default=SEQ_PER_GPU)
+    ap.add_argument("--threads-per-gpu", type=int, default=0,
+                    help="host worker threads per GPU (0: one per sequence as far as this rank's share of the host cores goes; a worker "
+                         "with several sequences begins all their frames before it finishes the first)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-window-roofline", action="store_true", help="skip the live 64x batched-window kernel timing")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -314,12 +319,15 @@ def main():
     args = ap.parse_args()
     rank, local_rank, world = rank_info()
     steps, warmup, S = args.steps, max(args.warmup, 3), args.sequences_per_gpu
+    host_cores = os.cpu_count() or 1
+    T = args.threads_per_gpu if args.threads_per_gpu > 0 else max(1, min(S, host_cores // max(world, 1)))
     n_frames = PRIME + warmup + steps + 1
     base = {"metric": "tracked frames/s (whole job, all sequences)", "unit": "frames/s", "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic (procedural box room, seeded, uint8-quantised)",
             "config": {"workload": WORKLOAD, "sequences": S * args.gpus, "sequences_per_gpu": S,
                        "parallelism": "independent sequences, no collective"}}
+    host = {"host_cores": host_cores, "worker_threads_per_gpu": T}
 
     if args.impl == "reference":
         # the reference's CPU path (oracle port) on the same config: ALL sequences of the job on this box's host cores
@@ -367,7 +375,7 @@ def main():
     dev_ptr = lambda sd: (lambda i, k: dev[sd[i]][k].data_ptr())
 
     def run_pass(sd, is_device):
-        job = Job(gpu, sd, data, device=local_rank)
+        job = Job(gpu, sd, data, device=local_rank, threads=min(T, len(sd)))
         job.prime(host_ptr(sd), PRIME, RAW8)
         barrier()
         r = timed_region(job, dev_ptr(sd) if is_device else host_ptr(sd), 1 if is_device else RAW8, steps, warmup, flush)
@@ -421,7 +429,7 @@ def main():
                          "unit": unit, "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
     total_frames = S * world * steps
-    line = dict(base, value=total_frames / T_dev, ms_per_step=1e3 * T_dev / steps,
+    line = dict(base, value=total_frames / T_dev, ms_per_step=1e3 * T_dev / steps, host=host,
                 e2e={"value": total_frames / T_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps, "d2h_bytes_per_step": d2h / steps},
                 gpu_launches=int(launches), clocks=clk.summary(),
                 timing="the K steps of the S sequences of a GPU are one ldso_gpu_batch_run call (no rendezvous between frames); value: "

@@ -172,6 +172,16 @@ int ldso_gpu_tracker_track(ldso_gpu_ctx* ctx, int tracker, int new_slot, float n
                            double pose_io[12], float aff_io[2], int coarsest_lvl,
                            const float min_res_for_abort[5], float last_residuals[5], float flow[3],
                            int iters_out[2]);
+/* The same call in two halves (CoarseTracker::trackNewestCoarse :61-310, no second counterpart in the reference): _begin
+ * launches the tracker kernel and returns without waiting (with tracker_lm_mode = 1, the host-driven loop, it only keeps
+ * its arguments); _end waits for the result and returns what ldso_gpu_tracker_track returns, pose / affine of the result in
+ * pose_out / aff_out (the initial guess when the return value is not 0).  One pair at a time per ctx; no other call on the ctx
+ * between the two.  A host thread that steps several sequences begins all of them before it ends the first
+ * (ldso_gpu_batch_*), so their trackers run side by side. */
+int ldso_gpu_tracker_track_begin(ldso_gpu_ctx* ctx, int tracker, int new_slot, float new_exposure, const double pose[12],
+                                 const float aff[2], int coarsest_lvl, const float min_res_for_abort[5]);
+int ldso_gpu_tracker_track_end(ldso_gpu_ctx* ctx, double pose_out[12], float aff_out[2], float last_residuals[5], float flow[3],
+                               int iters_out[2]);
 
 
 /* ---- A2: PixelSelector::makeMaps (src/frontend/PixelSelector2.cc:111-169) incl. makeHists (:36-109) and

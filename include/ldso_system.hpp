@@ -43,6 +43,7 @@
         LDSO_API_FN(P, pyr_levels) LDSO_API_FN(P, level_size) LDSO_API_FN(P, sync) LDSO_API_FN(P, bind_thread)                                    \
         LDSO_API_FN(P, frame_make_images) LDSO_API_FN(P, frame_make_images_dev) LDSO_API_FN(P, frame_make_images_raw)    \
         LDSO_API_FN(P, tracker_make_k) LDSO_API_FN(P, tracker_set_ref) LDSO_API_FN(P, tracker_track)                     \
+        LDSO_API_FN(P, tracker_track_begin) LDSO_API_FN(P, tracker_track_end)                                            \
         LDSO_API_FN(P, select_points) LDSO_API_FN(P, detect_corners)                                                     \
         LDSO_API_FN(P, immature_create) LDSO_API_FN(P, immature_append) LDSO_API_FN(P, immature_set_types)               \
         LDSO_API_FN(P, immature_compact) LDSO_API_FN(P, immature_trace_async) LDSO_API_FN(P, immature_trace_counts)      \
@@ -73,6 +74,8 @@
     int P##tracker_make_k(CTX*, int, float, float, float, float);                                                        \
     int P##tracker_set_ref(CTX*, int, int, int, const float*, const float*, const float*, const float*, float, float, float); \
     int P##tracker_track(CTX*, int, int, float, double*, float*, int, const float*, float*, float*, int*);               \
+    int P##tracker_track_begin(CTX*, int, int, float, const double*, const float*, int, const float*);                   \
+    int P##tracker_track_end(CTX*, double*, float*, float*, float*, int*);                                               \
     int P##select_points(CTX*, int, float, int, float, int*, int, int, float*, float*, float*, int*);                    \
     int P##detect_corners(CTX*, int, int, int, float*, float*, float*, unsigned char*, int*, int*);                      \
     int P##immature_create(CTX*, int, int, const float*, const float*, float*, float*, float*, float*);                  \
@@ -502,14 +505,43 @@ public:
     // _RAW16: the sensor image, through Undistort::undistort<T> on the device in front of makeImages (run_dso_tum_mono.cc:405-429)
     int addActiveFrame(const float* image, int image_kind, double timestamp, float exposure_time, double pose_out[12],
                        int* status_out) {
-        if (isLost) { fill_status(status_out, nullptr, false); return 1; }
+        const int rc = addActiveFrameBegin(image, image_kind, timestamp, exposure_time, pose_out, status_out);
+        if (rc < 0) return rc;
+        return addActiveFrameEnd();
+    }
+
+    // The same call in two halves, so that ONE host thread can keep several sequences busy (BatchRunner): Begin consumes the
+    // image (makeImages) and, once the system is initialised, builds the motion hypotheses and LAUNCHES the tracker on the
+    // first one without waiting; End waits for it and does everything else.  Between the two halves the thread is free to
+    // begin the frames of its other sequences, whose kernels then run beside this tracker.
+    struct PendingFrame {
+        bool active = false, lost = false, tracking = false, launched = false;
+        FrameHessian* fh = nullptr;
+        double t0 = 0;
+        double* pose_out = nullptr;
+        int* status_out = nullptr;
+        // trackNewCoarse between its halves
+        FrameHessian* lastF = nullptr;
+        AffLight aff_last_2_l{0, 0};
+        std::vector<SE3> tries;
+        float minRes0[5];
+    } pend;
+
+    int addActiveFrameBegin(const float* image, int image_kind, double timestamp, float exposure_time, double pose_out[12],
+                            int* status_out) {
+        if (pend.active) return fail("addActiveFrameBegin: the previous frame was not finished (addActiveFrameEnd)");
+        pend = PendingFrame();
+        pend.active = true; pend.pose_out = pose_out; pend.status_out = status_out;
+        if (isLost) { pend.lost = true; return 0; }
         const double t0 = now();
+        pend.t0 = t0;
         allFrameHistory.emplace_back(new FrameHessian());
         FrameHessian* fh = allFrameHistory.back().get();
+        pend.fh = fh;
         fh->id = (int)allFrameHistory.size() - 1;
         fh->timeStamp = timestamp;
         fh->ab_exposure = exposure_time;
-        if (free_slots.empty()) return fail("no free frame slot");
+        if (free_slots.empty()) { pend.active = false; return fail("no free frame slot"); }
         fh->slot = free_slots.back();
         free_slots.pop_back();
         counters[LDSO_SYS_CT_FRAMES]++;
@@ -519,11 +551,31 @@ public:
         else if (image_kind == LDSO_IMAGE_HOST_F32) rc = Api::frame_make_images(ctx, fh->slot, image);
         else if (image_kind == LDSO_IMAGE_HOST_RAW8 || image_kind == LDSO_IMAGE_HOST_RAW16)
             rc = Api::frame_make_images_raw(ctx, fh->slot, (const void*)image, image_kind == LDSO_IMAGE_HOST_RAW8 ? 1 : 2, exposure_time, 1.0f);
-        else return fail("unknown image kind");
-        if (rc < 0) return fail_api();
+        else { pend.active = false; return fail("unknown image kind"); }
+        if (rc < 0) { pend.active = false; return fail_api(); }
         phase_s[8] += now() - t0;
+        if (initialized) {
+            // :130-138  swap tracking reference?
+            if (coarseTracker_forNewKF->refFrameID > coarseTracker->refFrameID) std::swap(coarseTracker, coarseTracker_forNewKF);
+            pend.tracking = true;
+            rc = trackNewCoarseBegin(fh);
+            if (rc < 0) { pend.active = false; return rc; }
+        }
+        phase_s[0] += now() - t0;
+        return 0;
+    }
+
+    int addActiveFrameEnd() {
+        if (!pend.active) return fail("addActiveFrameEnd without addActiveFrameBegin");
+        pend.active = false;
+        double* pose_out = pend.pose_out;
+        int* status_out = pend.status_out;
+        if (pend.lost) { fill_status(status_out, nullptr, false); return 1; }
+        FrameHessian* fh = pend.fh;
+        const double t0 = now();
         bool madeKF = false;
-        if (!initialized) {
+        int rc;
+        if (!pend.tracking) {
             // :95-128
             int ready = 0;
             if (initializerFrameID < 0) {
@@ -553,10 +605,8 @@ public:
                 }
             }
         } else {
-            // :130-138  swap tracking reference?
-            if (coarseTracker_forNewKF->refFrameID > coarseTracker->refFrameID) std::swap(coarseTracker, coarseTracker_forNewKF);
             double tres[4];
-            rc = trackNewCoarse(fh, tres);
+            rc = trackNewCoarseEnd(fh, tres);
             if (rc < 0) return rc;
             phase_s[0] += now() - t0;
             if (!std::isfinite(tres[0]) || !std::isfinite(tres[1]) || !std::isfinite(tres[2]) || !std::isfinite(tres[3])) {
@@ -669,11 +719,13 @@ private:
         r.normalize();
         return r;
     }
-    int trackNewCoarse(FrameHessian* fh, double tres[4]) {
+    // first half: the motion hypotheses (:225-380) and the launch of trackNewestCoarse on the first one
+    int trackNewCoarseBegin(FrameHessian* fh) {
         const double t_h0 = now();
         FrameHessian* lastF = coarseTracker->lastRef;
         AffLight aff_last_2_l(0, 0);
-        std::vector<SE3> lastF_2_fh_tries;
+        std::vector<SE3>& lastF_2_fh_tries = pend.tries;
+        lastF_2_fh_tries.clear();
         if (allFrameHistory.size() == 2) {
             lastF_2_fh_tries.push_back(SE3());
         } else {
@@ -709,6 +761,25 @@ private:
             }
         }
         phase_s[10] += now() - t_h0;
+        pend.lastF = lastF;
+        pend.aff_last_2_l = aff_last_2_l;
+        {
+            double pose[12];
+            float aff[2] = {aff_last_2_l.a, aff_last_2_l.b};
+            lastF_2_fh_tries[0].toRt(pose);
+            for (int k = 0; k < 5; k++) pend.minRes0[k] = INFINITY;
+            const double t_t0 = now();
+            if (Api::tracker_track_begin(ctx, coarseTracker->dev, fh->slot, fh->ab_exposure, pose, aff, levels - 1, pend.minRes0) < 0) return fail_api();
+            phase_s[9] += now() - t_t0;
+            pend.launched = true;
+        }
+        return 0;
+    }
+    // second half: the result of the first hypothesis, further hypotheses while tracking is not good enough (:382-468)
+    int trackNewCoarseEnd(FrameHessian* fh, double tres[4]) {
+        FrameHessian* lastF = pend.lastF;
+        const AffLight aff_last_2_l = pend.aff_last_2_l;
+        const std::vector<SE3>& lastF_2_fh_tries = pend.tries;
         double flowVecs[3] = {100, 100, 100};
         SE3 lastF_2_fh;
         AffLight aff_g2l(0, 0);
@@ -726,7 +797,9 @@ private:
             lastF_2_fh_this.toRt(pose);
             for (int k = 0; k < 5; k++) minRes[k] = (float)achievedRes[k];
             const double t_t0 = now();
-            int rc = Api::tracker_track(ctx, coarseTracker->dev, fh->slot, fh->ab_exposure, pose, aff, levels - 1, minRes, lastRes, flow, iters);
+            int rc;
+            if (i == 0 && pend.launched) rc = Api::tracker_track_end(ctx, pose, aff, lastRes, flow, iters);   // launched by trackNewCoarseBegin
+            else rc = Api::tracker_track(ctx, coarseTracker->dev, fh->slot, fh->ab_exposure, pose, aff, levels - 1, minRes, lastRes, flow, iters);
             phase_s[9] += now() - t_t0;
             if (rc < 0) return fail_api();
             counters[LDSO_SYS_CT_TRACK_CALLS]++;
@@ -1796,14 +1869,22 @@ private:
                 jobs[i].rc = 0;
                 most = std::max(most, jobs[i].n_frames);
             }
-            for (int f = 0; f < most; f++)
+            for (int f = 0; f < most; f++) {
+                // begin the frame of every own sequence (makeImages + the tracker launch, nothing waits), then finish them in
+                // the same order: while one sequence's tracker runs, the thread works on the others
                 for (size_t i = t; i < sys.size(); i += T) {
                     Job& j = jobs[i];
                     if (f >= j.n_frames || j.rc < 0) continue;
-                    j.rc = sys[i]->impl.addActiveFrame(j.images[f], j.is_device, j.timestamp + f, j.exposure,
-                                                       j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
-                                                       j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
+                    j.rc = sys[i]->impl.addActiveFrameBegin(j.images[f], j.is_device, j.timestamp + f, j.exposure,
+                                                            j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
+                                                            j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
                 }
+                for (size_t i = t; i < sys.size(); i += T) {
+                    Job& j = jobs[i];
+                    if (f >= j.n_frames || j.rc < 0) continue;
+                    j.rc = sys[i]->impl.addActiveFrameEnd();
+                }
+            }
             for (size_t i = t; i < sys.size(); i += T)
                 if (jobs[i].sync_after && jobs[i].rc >= 0 && Api::sync(sys[i]->impl.ctx) < 0) jobs[i].rc = -1;   // drains the queued trace too
             bound = true;

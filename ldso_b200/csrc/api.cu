@@ -57,7 +57,8 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaStreamCreateWithFlags(&c->stream_map, cudaStreamNonBlocking));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev0));
     LDSO_CUDA_OK(c, cudaEventCreate(&c->ev1));
-    LDSO_CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_h2d, cudaEventDisableTiming));
+    LDSO_CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_h2d, cudaEventDisableTiming | (ldso_wait_block() ? cudaEventBlockingSync : 0)));
+    LDSO_CUDA_OK(c, cudaEventCreateWithFlags(&c->ev_trk, cudaEventDisableTiming | (ldso_wait_block() ? cudaEventBlockingSync : 0)));
     c->frame = new float4*[cfg.n_frame_slots]();
     for (int s = 0; s < cfg.n_frame_slots; s++) LDSO_CUDA_OK(c, cudaMalloc(&c->frame[s], off * sizeof(float4)));
     LDSO_CUDA_OK(c, cudaMalloc(&c->img_dev, npx0 * sizeof(float)));
@@ -106,6 +107,10 @@ bool ldso_wait_yield() {
     static const bool y = [] { const char* e = getenv("LDSO_WAIT_YIELD"); return e && atoi(e) != 0; }();
     return y;
 }
+bool ldso_wait_block() {
+    static const bool b = [] { const char* e = getenv("LDSO_WAIT_BLOCK"); return e && atoi(e) != 0; }();
+    return b;
+}
 void ldso_cpu_relax() {
     if (ldso_wait_yield()) sched_yield();
     else _mm_pause();
@@ -124,7 +129,8 @@ extern "C" int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out) {
         c->trk[t].row_cnt = nullptr;
         c->trk[t].pc_n_dev = nullptr;
     }
-    if (ldso_wait_yield()) { cudaSetDevice(cfg->device); cudaSetDeviceFlags(cudaDeviceScheduleYield); cudaGetLastError(); }
+    if (ldso_wait_block()) { cudaSetDevice(cfg->device); cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync); cudaGetLastError(); }
+    else if (ldso_wait_yield()) { cudaSetDevice(cfg->device); cudaSetDeviceFlags(cudaDeviceScheduleYield); cudaGetLastError(); }
     int rc = create_impl(c);
     *out = c;   // returned even on failure so that the caller can read last_error, then destroy
     return rc;
@@ -159,6 +165,7 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_h2d) cudaEventDestroy(c->ev_h2d);
+    if (c->ev_trk) cudaEventDestroy(c->ev_trk);
     prof_drain(c);
     for (cudaEvent_t e : c->prof_free) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -470,33 +477,39 @@ void solve_step(const double* H, const double* b, float lambda, int mode, float 
 
 }  // namespace
 
-extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, double pose_io[12],
-                                      float aff_io[2], int coarsest_lvl, const float min_res_for_abort[5],
-                                      float last_residuals[5], float flow[3], int iters_out[2]) {
-    LDSO_ENTER(c);
+// CoarseTracker::trackNewestCoarse in two halves (phase 1 = begin: launch without waiting, 2 = end: wait and finish,
+// 0 = both).  With the host-driven LM loop (tracker_lm_mode = 1) nothing can be launched ahead: begin only keeps its arguments.
+static int track_impl(ldso_gpu_ctx* c, int phase, int tracker, int new_slot, float new_exposure, double pose_io[12], float aff_io[2],
+                      int coarsest_lvl, const float min_res_for_abort[5], float last_residuals[5], float flow[3], int iters_out[2]) {
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS);
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && pose_io && aff_io && min_res_for_abort);
     LDSO_REQUIRE(c, coarsest_lvl >= 0 && coarsest_lvl < 5 && coarsest_lvl < c->levels);   // CoarseTracker.cc:65
     TrackerDev& T = c->trk[tracker];
     LDSO_REQUIRE(c, T.ref_slot >= 0);
-    T.new_slot = new_slot; T.new_exposure = new_exposure;
-    T.last_lvl = -1;
-    for (int i = 0; i < 5; i++) last_residuals[i] = NAN;
-    for (int i = 0; i < 3; i++) flow[i] = 1000;
     static const int maxIterations[5] = {10, 20, 50, 50, 50};
     const float extrapLimit = 0.001f;
     const float optA = c->cfg.affine_opt_mode_a, optB = c->cfg.affine_opt_mode_b;
     SE3 cur = SE3::fromRt(pose_io);
     float cur_a = aff_io[0], cur_b = aff_io[1];
+    const bool device_lm = c->cfg.tracker_lm_mode != 1;
+    if (phase != 2) {
+        T.new_slot = new_slot; T.new_exposure = new_exposure;
+        T.last_lvl = -1;
+        if (device_lm) {
+            int rc = k34_track_all_launch(c, tracker, coarsest_lvl, maxIterations, min_res_for_abort, cur, cur_a, cur_b);
+            if (rc) return rc;
+        }
+        if (phase == 1) return 0;
+    }
+    for (int i = 0; i < 5; i++) last_residuals[i] = NAN;
+    for (int i = 0; i < 3; i++) flow[i] = 1000;
     bool repeated = false;
     int nEval = 0, nAccept = 0, rc;
     TrackEvalOut ev;
-    const bool device_lm = c->cfg.tracker_lm_mode != 1;
     if (device_lm) {
         // the level loop with its LM iterations runs inside one kernel (thread-block cluster, or cooperative grid in mode 2)
         int status = 0;
-        if ((rc = k34_track_all(c, tracker, coarsest_lvl, maxIterations, min_res_for_abort, cur, cur_a, cur_b, last_residuals, flow,
-                                &status, &nEval, &nAccept))) return rc;
+        if ((rc = k34_track_all_wait(c, cur, cur_a, cur_b, last_residuals, flow, &status, &nEval, &nAccept))) return rc;
         if (status) {
             if (iters_out) { iters_out[0] = nEval; iters_out[1] = nAccept; }
             return 1;
@@ -575,4 +588,41 @@ extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot
     cur.toRt(pose_io);
     aff_io[0] = cur_a; aff_io[1] = cur_b;
     return 0;
+}
+
+extern "C" int ldso_gpu_tracker_track(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, double pose_io[12],
+                                      float aff_io[2], int coarsest_lvl, const float min_res_for_abort[5],
+                                      float last_residuals[5], float flow[3], int iters_out[2]) {
+    LDSO_ENTER(c);
+    LDSO_REQUIRE(c, last_residuals && flow);
+    LDSO_REQUIRE(c, !c->trk_pending.active);
+    return track_impl(c, 0, tracker, new_slot, new_exposure, pose_io, aff_io, coarsest_lvl, min_res_for_abort, last_residuals, flow, iters_out);
+}
+
+extern "C" int ldso_gpu_tracker_track_begin(ldso_gpu_ctx* c, int tracker, int new_slot, float new_exposure, const double pose[12],
+                                            const float aff[2], int coarsest_lvl, const float min_res_for_abort[5]) {
+    LDSO_ENTER(c);
+    LDSO_REQUIRE(c, pose && aff && min_res_for_abort);
+    LDSO_REQUIRE(c, !c->trk_pending.active);
+    auto& P = c->trk_pending;
+    P.tracker = tracker; P.new_slot = new_slot; P.new_exposure = new_exposure; P.coarsest = coarsest_lvl;
+    for (int i = 0; i < 12; i++) P.pose[i] = pose[i];
+    for (int i = 0; i < 2; i++) P.aff[i] = aff[i];
+    for (int i = 0; i < 5; i++) P.min_res[i] = min_res_for_abort[i];
+    const int rc = track_impl(c, 1, tracker, new_slot, new_exposure, P.pose, P.aff, coarsest_lvl, P.min_res, nullptr, nullptr, nullptr);
+    if (rc == 0) P.active = true;
+    return rc;
+}
+
+extern "C" int ldso_gpu_tracker_track_end(ldso_gpu_ctx* c, double pose_out[12], float aff_out[2], float last_residuals[5], float flow[3],
+                                          int iters_out[2]) {
+    LDSO_ENTER(c);
+    LDSO_REQUIRE(c, pose_out && aff_out && last_residuals && flow);
+    auto& P = c->trk_pending;
+    LDSO_REQUIRE(c, P.active);
+    P.active = false;
+    const int rc = track_impl(c, 2, P.tracker, P.new_slot, P.new_exposure, P.pose, P.aff, P.coarsest, P.min_res, last_residuals, flow, iters_out);
+    for (int i = 0; i < 12; i++) pose_out[i] = P.pose[i];
+    for (int i = 0; i < 2; i++) aff_out[i] = P.aff[i];
+    return rc;
 }

@@ -72,7 +72,7 @@ struct ldso_gpu_ctx {
     size_t lvl_off[LDSO_MAX_LEVELS + 1];   // pixel offset of each level inside a frame slot
     cudaStream_t stream = nullptr;          // tracking stream
     cudaStream_t stream_map = nullptr;      // mapping stream
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_h2d = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_h2d = nullptr, ev_trk = nullptr;
     float4** frame = nullptr;               // [n_frame_slots] device float4 pyramids {I,dx,dy,absSquaredGrad}
     float* img_dev = nullptr;               // staged input image
     float* img_pinned = nullptr;
@@ -89,6 +89,13 @@ struct ldso_gpu_ctx {
     double* trk_mailbox = nullptr;          // [64] mapped pinned: the fused tracker kernel writes its sums + a sequence number here
     double* trk_mailbox_dev = nullptr;      // device alias of trk_mailbox
     unsigned long long trk_seq = 0;
+    // ldso_gpu_tracker_track_begin .. _end: the launch in flight and the arguments of the call
+    struct TrackPending {
+        bool active = false;
+        int tracker = 0, new_slot = 0, coarsest = 0, prof_idx = -1, dbg = 0;
+        float new_exposure = 1, aff[2] = {0, 0}, min_res[5] = {0, 0, 0, 0, 0};
+        double pose[12] = {0}, seq = 0;
+    } trk_pending;
     double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
     int trk_coop_max = 0;                   // co-resident CTA budget of the cooperative LM kernel (tracker_lm_mode = 2)
     int trk_cluster = 0;                    // CTAs of the tracker's thread-block cluster (tracker_lm_mode = 0), chosen at first use
@@ -137,6 +144,7 @@ struct ldso_gpu_ctx {
 // LDSO_WAIT_YIELD=1 the mailbox polls call sched_yield() and the context is switched to cudaDeviceScheduleYield, so that
 // more sequence threads than cores can share a host (ldso_gpu_batch_* with many sequences per GPU).
 bool ldso_wait_yield();
+bool ldso_wait_block();   // LDSO_WAIT_BLOCK=1: waits sleep in the driver (cudaDeviceScheduleBlockingSync, blocking events): no core is burnt while waiting
 void ldso_cpu_relax();
 
 // every host<->device copy of the library goes through here so that the traffic is accounted
@@ -164,8 +172,9 @@ struct TrackEvalOut {
     double sums[48];   // 45 H entries (9x9 upper, row-major), E, flowT, flowRT
     int counts[4];     // numTermsInE, numSaturated, numTermsInWarped, flowNum
 };
-int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
-                  ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
-                  int* nEval, int* nAccept);
+int k34_track_all_launch(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
+                         const ldso_sm::SE3& cur, float aff_a, float aff_b);
+int k34_track_all_wait(ldso_gpu_ctx* c, ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
+                       int* nEval, int* nAccept);
 int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew, float aff_a, float aff_b, float cutoffTH,
              TrackEvalOut* out);

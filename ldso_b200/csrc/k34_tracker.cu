@@ -1266,6 +1266,7 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
 static int track_all_wait(ldso_gpu_ctx* c, double seq, int prof_idx, int dbg, ldso_sm::SE3& cur, float& aff_a, float& aff_b,
                           float last_residuals[5], float flow[3], int* status, int* nEval, int* nAccept) {
     volatile double* res = c->trk_mailbox;
+    if (ldso_wait_block()) LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_trk));   // sleep until the kernel is done instead of polling
     for (unsigned spin = 1; res[63] != seq; spin++) {
         ldso_cpu_relax();
         if ((spin & 0xfffff) == 0) {
@@ -1289,9 +1290,14 @@ static int track_all_wait(ldso_gpu_ctx* c, double seq, int prof_idx, int dbg, ld
 
 // trackNewestCoarse's level loop on the device (see k34_track_level_kernel): ONE cooperative launch walks the pyramid
 // from coarsest_lvl down, the host polls the mapped mailbox once.  In/out: pose, affine.
-int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
-                  ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
-                  int* nEval, int* nAccept) {
+int k34_track_all_wait(ldso_gpu_ctx* c, ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,
+                       int* nEval, int* nAccept) {
+    const auto& P = c->trk_pending;
+    return track_all_wait(c, P.seq, P.prof_idx, P.dbg, cur, aff_a, aff_b, last_residuals, flow, status, nEval, nAccept);
+}
+
+int k34_track_all_launch(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
+                         const ldso_sm::SE3& cur, float aff_a, float aff_b) {
     TrackerDev& T = c->trk[tracker];
     LmAll A;
     memset(&A, 0, sizeof(A));
@@ -1348,8 +1354,9 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
         prof_begin(c, c->stream);
         LDSO_CUDA_OK(c, cudaLaunchKernelEx(&q, k34_track_cluster_kernel, A, mbx, sq));
         c->launches++;
-        const int pidx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
-        return track_all_wait(c, sq, pidx, k.dbg, cur, aff_a, aff_b, last_residuals, flow, status, nEval, nAccept);
+        c->trk_pending.seq = sq; c->trk_pending.prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0); c->trk_pending.dbg = k.dbg;
+        if (ldso_wait_block()) LDSO_CUDA_OK(c, cudaEventRecord(c->ev_trk, c->stream));
+        return 0;
     }
     if (c->trk_coop_max == 0) {
         int per_sm = 0, sms = 0, dev = 0, coop = 0;
@@ -1372,8 +1379,9 @@ int k34_track_all(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* max
     prof_begin(c, c->stream);
     LDSO_CUDA_OK(c, cudaLaunchCooperativeKernel((void*)k34_track_level_kernel, dim3(blocks), dim3(LM_THREADS), args, 0, c->stream));
     c->launches++;
-    const int prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0);
-    return track_all_wait(c, seq, prof_idx, k.dbg, cur, aff_a, aff_b, last_residuals, flow, status, nEval, nAccept);
+    c->trk_pending.seq = seq; c->trk_pending.prof_idx = prof_end(c, c->stream, LDSO_PROF_K34, 0); c->trk_pending.dbg = k.dbg;
+    if (ldso_wait_block()) LDSO_CUDA_OK(c, cudaEventRecord(c->ev_trk, c->stream));
+    return 0;
 }
 
 // =====================================================================================================

