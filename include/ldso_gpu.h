@@ -74,8 +74,12 @@ typedef struct ldso_gpu_config {
 void ldso_gpu_default_config(ldso_gpu_config* cfg);
 
 /* Context life cycle.  create() derives the pyramid level count with the rule of setGlobalCalib
- * (src/internal/GlobalCalib.cc:20-28), allocates every device buffer once (no allocation on the
- * per-frame path), and creates the ctx's streams. */
+ * (src/internal/GlobalCalib.cc:20-28), allocates the frame pyramids, the two trackers, the window (points, residuals,
+ * accumulators) and the tracker's reduction workspace, and creates the ctx's streams.  The other subsystems allocate their
+ * buffers once, at their first use: selector, immature pool, corner detector (first keyframe), undistorter
+ * (ldso_gpu_undistort_set), initializer (ldso_gpu_init_set_first: its per-level point arrays are sized by the first
+ * frame's point count, so each set_first allocates them anew).  A tracked frame (makeImages, trackNewestCoarse,
+ * traceNewCoarse) and a keyframe of an initialised sequence allocate nothing. */
 int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out);
 void ldso_gpu_destroy(ldso_gpu_ctx* ctx);
 const char* ldso_gpu_last_error(const ldso_gpu_ctx* ctx);

@@ -306,7 +306,7 @@ extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, mask || W.nr == 0);
     if (W.nr == 0) return 0;
-    // the mask rides in the (currently unused) res_pt scratch rows? no: keep it simple, stage it in `order`'s tail
+    // the mask is staged in res_pt (scratch at this point)
     unsigned char* dmask = reinterpret_cast<unsigned char*>(W.res_pt);   // res_pt is rewritten by the next K8 launch
     int rc = upload(c, dmask, mask, W.nr);
     if (rc) return rc;
