@@ -331,6 +331,13 @@ int ldso_gpu_undistort_set(ldso_gpu_ctx* ctx, int w_org, int h_org, int g_depth,
  * benchmark_varBlurNoise) are not part of this path. */
 int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* ctx, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
                                    float factor);
+/* FrameHessian::makeImages (FrameHessian.cc:59-128; with kind 2 / 3 behind Undistort::undistort<T>, as
+ * ldso_gpu_frame_make_images_raw with factor 1) QUEUED without waiting: for a caller that was handed its frames up front
+ * (ldso_gpu_batch_run prepares the next frame of a sequence while the current one is being tracked).  kind: 0 host float
+ * image, 1 device float image, 2 / 3 host 8 / 16-bit sensor image (the LDSO_IMAGE_* values of include/ldso_system.h).  A
+ * page-locked `image` must stay valid until the ctx's tracking stream has been waited for (ldso_gpu_sync, or the end of a
+ * tracker call on that slot); a pageable one is consumed before the call returns. */
+int ldso_gpu_frame_make_images_async(ldso_gpu_ctx* ctx, int slot, const void* image, int kind, float exposure_time);
 /* ImageAndExposure::image of the last ldso_gpu_frame_make_images_raw: w*h floats */
 int ldso_gpu_undistort_get_image(ldso_gpu_ctx* ctx, float* image_out);
 

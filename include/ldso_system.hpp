@@ -42,6 +42,7 @@
         LDSO_API_FN(P, default_config) LDSO_API_FN(P, create) LDSO_API_FN(P, destroy) LDSO_API_FN(P, last_error)         \
         LDSO_API_FN(P, pyr_levels) LDSO_API_FN(P, level_size) LDSO_API_FN(P, sync) LDSO_API_FN(P, bind_thread)                                    \
         LDSO_API_FN(P, frame_make_images) LDSO_API_FN(P, frame_make_images_dev) LDSO_API_FN(P, frame_make_images_raw)    \
+        LDSO_API_FN(P, frame_make_images_async)                                                                         \
         LDSO_API_FN(P, tracker_make_k) LDSO_API_FN(P, tracker_set_ref) LDSO_API_FN(P, tracker_track)                     \
         LDSO_API_FN(P, tracker_track_begin) LDSO_API_FN(P, tracker_track_end)                                            \
         LDSO_API_FN(P, select_points) LDSO_API_FN(P, detect_corners)                                                     \
@@ -71,6 +72,7 @@
     int P##frame_make_images(CTX*, int, const float*);                                                                   \
     int P##frame_make_images_dev(CTX*, int, const float*);                                                               \
     int P##frame_make_images_raw(CTX*, int, const void*, int, float, float);                                             \
+    int P##frame_make_images_async(CTX*, int, const void*, int, float);                                                  \
     int P##tracker_make_k(CTX*, int, float, float, float, float);                                                        \
     int P##tracker_set_ref(CTX*, int, int, int, const float*, const float*, const float*, const float*, float, float, float); \
     int P##tracker_track(CTX*, int, int, float, double*, float*, int, const float*, float*, float*, int*);               \
@@ -527,6 +529,19 @@ public:
         float minRes0[5];
     } pend;
 
+    // The NEXT frame's pyramid, built one frame ahead (BatchRunner, which holds all the frames of a call): queued behind the
+    // current frame's tracker on the tracking stream, it runs while the host finishes the current frame, and the next
+    // addActiveFrameBegin finds its image already consumed.  The image must stay valid until that frame has been tracked.
+    struct Prefetched { bool valid = false; const float* image = nullptr; int slot = -1; } pre;
+    int prefetchImage(const float* image, int image_kind, float exposure_time) {
+        if (pre.valid || isLost || !initialized || free_slots.size() < 3) return 0;
+        const int slot = free_slots.back();
+        if (Api::frame_make_images_async(ctx, slot, (const void*)image, image_kind, exposure_time) < 0) return fail_api();
+        free_slots.pop_back();
+        pre.valid = true; pre.image = image; pre.slot = slot;
+        return 0;
+    }
+
     int addActiveFrameBegin(const float* image, int image_kind, double timestamp, float exposure_time, double pose_out[12],
                             int* status_out) {
         if (pend.active) return fail("addActiveFrameBegin: the previous frame was not finished (addActiveFrameEnd)");
@@ -541,13 +556,25 @@ public:
         fh->id = (int)allFrameHistory.size() - 1;
         fh->timeStamp = timestamp;
         fh->ab_exposure = exposure_time;
-        if (free_slots.empty()) { pend.active = false; return fail("no free frame slot"); }
-        fh->slot = free_slots.back();
-        free_slots.pop_back();
+        if (pre.valid && pre.image != image) {   // a frame was prepared that is not the one that came: give its slot back
+            free_slots.push_back(pre.slot);
+            pre.valid = false;
+        }
+        if (!pre.valid && free_slots.empty()) { pend.active = false; return fail("no free frame slot"); }
         counters[LDSO_SYS_CT_FRAMES]++;
         // fh->makeImages(image, Hcalib) (:93)
         int rc;
-        if (image_kind == LDSO_IMAGE_DEVICE_F32) rc = Api::frame_make_images_dev(ctx, fh->slot, image);
+        if (pre.valid) {
+            fh->slot = pre.slot;
+            pre.valid = false;
+            rc = 0;
+        } else {
+            fh->slot = free_slots.back();
+            free_slots.pop_back();
+            rc = 1;
+        }
+        if (rc == 0) {}
+        else if (image_kind == LDSO_IMAGE_DEVICE_F32) rc = Api::frame_make_images_dev(ctx, fh->slot, image);
         else if (image_kind == LDSO_IMAGE_HOST_F32) rc = Api::frame_make_images(ctx, fh->slot, image);
         else if (image_kind == LDSO_IMAGE_HOST_RAW8 || image_kind == LDSO_IMAGE_HOST_RAW16)
             rc = Api::frame_make_images_raw(ctx, fh->slot, (const void*)image, image_kind == LDSO_IMAGE_HOST_RAW8 ? 1 : 2, exposure_time, 1.0f);
@@ -1820,6 +1847,7 @@ public:
     };
     std::vector<Sys*> sys;
     std::vector<Job> jobs;
+    bool prefetch = getenv("LDSO_NO_PREFETCH") == nullptr;   // measurement knob: LDSO_NO_PREFETCH=1 prepares no frame ahead
     BatchRunner(int n, Sys** systems, int n_threads) : sys(systems, systems + n), jobs(n) {
         const int T = std::max(1, std::min(n_threads, n));
         for (int t = 0; t < T; t++) workers.emplace_back([this, t, T] { loop(t, T); });
@@ -1878,6 +1906,9 @@ private:
                     j.rc = sys[i]->impl.addActiveFrameBegin(j.images[f], j.is_device, j.timestamp + f, j.exposure,
                                                             j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
                                                             j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
+                    // the next frame of this call is at hand: its copy and pyramid queue up behind the tracker just launched
+                    if (j.rc >= 0 && prefetch && f + 1 < j.n_frames && sys[i]->impl.prefetchImage(j.images[f + 1], j.is_device, j.exposure) < 0)
+                        j.rc = -1;
                 }
                 for (size_t i = t; i < sys.size(); i += T) {
                     Job& j = jobs[i];
@@ -1908,7 +1939,7 @@ private:
         P##default_config(&c->gpu);                                                                                       \
         /* mode=1 of examples/run_dso_tum_mono.cc:283-288: no photometric calibration, a and b free without prior */      \
         c->gpu.affine_opt_mode_a = 0; c->gpu.affine_opt_mode_b = 0;                                                       \
-        c->gpu.max_points = 12288; c->gpu.max_residuals = 98304; c->gpu.max_immature = 16384; c->gpu.n_frame_slots = 11;  \
+        c->gpu.max_points = 12288; c->gpu.max_residuals = 98304; c->gpu.max_immature = 16384; c->gpu.n_frame_slots = 12;  \
         c->desired_immature_density = 1500; c->desired_point_density = 2000; c->min_points_remaining = 0.05f;             \
         c->max_log_aff_fac_in_window = 0.7f; c->min_frames = 5; c->max_frames = 7; c->min_frame_age = 1;                  \
         c->max_opt_iterations = 6; c->min_opt_iterations = 1; c->th_opt_iterations = 1.2f;                                \

@@ -300,6 +300,31 @@ extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float
     LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, c->img_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
     return k1_make_images(c, slot, c->img_dev);
 }
+// makeImages of a frame whose image stays valid until the ctx's tracking stream has been waited for (a batch that was handed
+// all its frames up front, ldso_gpu_batch_run): the copy and the pyramid are queued and the call returns at once.  kind: an
+// LDSO_IMAGE_* value (include/ldso_system.h).  A pageable host pointer cannot be copied asynchronously: it takes the waiting path.
+extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
+                                              float factor);
+int n4_make_images_raw_async(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time, float factor);
+extern "C" int ldso_gpu_frame_make_images_async(ldso_gpu_ctx* c, int slot, const void* image, int kind, float exposure_time) {
+    LDSO_ENTER(c);
+    LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && image && kind >= 0 && kind <= 3);
+    if (kind == 1) return k1_make_images(c, slot, (const float*)image);
+    cudaPointerAttributes attr;
+    const bool pinned = cudaPointerGetAttributes(&attr, image) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    if (!pinned) {
+        (void)cudaGetLastError();
+        if (kind == 0) return ldso_gpu_frame_make_images(c, slot, (const float*)image);
+        return ldso_gpu_frame_make_images_raw(c, slot, image, kind == 2 ? 1 : 2, exposure_time, 1.0f);
+    }
+    if (kind == 0) {
+        const size_t bytes = (size_t)c->cfg.w * c->cfg.h * sizeof(float);
+        LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, image, bytes, cudaMemcpyHostToDevice, c->stream));
+        return k1_make_images(c, slot, c->img_dev);
+    }
+    return n4_make_images_raw_async(c, slot, image, kind == 2 ? 1 : 2, exposure_time, 1.0f);
+}
+
 extern "C" int ldso_gpu_frame_make_images_dev(ldso_gpu_ctx* c, int slot, const float* img_dev) {
     LDSO_ENTER(c);
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && img_dev);

@@ -99,9 +99,8 @@ extern "C" int ldso_gpu_undistort_set(ldso_gpu_ctx* c, int w_org, int h_org, int
     return 0;
 }
 
-extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
-                                              float factor) {
-    LDSO_ENTER(c);
+// wait = false: the (page-locked) raw image stays valid until the tracking stream has been waited for; nothing waits here
+static int make_images_raw_impl(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time, float factor, bool wait) {
     UndistortDev* U = (UndistortDev*)c->undistort;
     LDSO_REQUIRE(c, U && U->raw && raw && slot >= 0 && slot < c->cfg.n_frame_slots && (bytes_per_pixel == 1 || bytes_per_pixel == 2));
     LDSO_REQUIRE(c, !(U->has_G && bytes_per_pixel == 2 && U->g_depth != 65536));
@@ -114,7 +113,7 @@ extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const v
         memcpy(U->raw_pinned, raw, bytes);
     }
     LDSO_CUDA_OK(c, ldso_copy(c, U->raw, pinned ? raw : (const void*)U->raw_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
-    if (pinned) LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream));
+    if (pinned && wait) LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream));
     N4Params p;
     p.w = c->cfg.w; p.h = c->cfg.h; p.w_org = U->w_org; p.h_org = U->h_org; p.bpp = bytes_per_pixel; p.factor = factor;
     // PhotometricUndistorter::processFrame (:197-199): no calibration, no exposure or calibration switched off -> factor * raw
@@ -127,8 +126,17 @@ extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const v
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
     const int rc = k1_make_images(c, slot, c->img_dev);
-    if (pinned) LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_h2d));
+    if (pinned && wait) LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_h2d));
     return rc;
+}
+
+extern "C" int ldso_gpu_frame_make_images_raw(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time,
+                                              float factor) {
+    LDSO_ENTER(c);
+    return make_images_raw_impl(c, slot, raw, bytes_per_pixel, exposure_time, factor, true);
+}
+int n4_make_images_raw_async(ldso_gpu_ctx* c, int slot, const void* raw, int bytes_per_pixel, float exposure_time, float factor) {
+    return make_images_raw_impl(c, slot, raw, bytes_per_pixel, exposure_time, factor, false);
 }
 
 extern "C" int ldso_gpu_undistort_get_image(ldso_gpu_ctx* c, float* image_out) {

@@ -750,3 +750,10 @@ extern "C" int orc_undistort_get_image(orc_ctx* c, float* image_out) {
     memcpy(image_out, U->image.data(), sizeof(float) * U->image.size());
     return 0;
 }
+
+// ldso_gpu_frame_make_images_async: on the CPU nothing is queued, the image is consumed at once
+extern "C" int orc_frame_make_images(orc_ctx* c, int slot, const float* img);
+extern "C" int orc_frame_make_images_async(orc_ctx* c, int slot, const void* image, int kind, float exposure_time) {
+    if (kind == 0 || kind == 1) return orc_frame_make_images(c, slot, (const float*)image);
+    return orc_frame_make_images_raw(c, slot, image, kind == 2 ? 1 : 2, exposure_time, 1.0f);
+}
