@@ -36,9 +36,25 @@ __global__ void k2_pool_kernel(const float* __restrict__ id_lm, const float* __r
     ws_l[i] = __fadd_rn(__fadd_rn(__fadd_rn(ws_lm[bidx], ws_lm[bidx + 1]), ws_lm[bidx + wlm1]), ws_lm[bidx + wlm1 + 1]);
 }
 
+// all levels in one launch (blockIdx.y = level): the planes of different levels do not depend on each other here
+struct K2Planes {
+    int levels;
+    int w[LDSO_MAX_LEVELS], h[LDSO_MAX_LEVELS];
+    float* idepth[LDSO_MAX_LEVELS];
+    float* ws[LDSO_MAX_LEVELS];
+    float* ws_bak[LDSO_MAX_LEVELS];
+};
+__global__ void k2_backup_all_kernel(const K2Planes p) {
+    const int l = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.w[l] * p.h[l]) p.ws_bak[l][i] = p.ws[l][i];
+}
 // reads ws_bak (pre-dilation copy), writes idepth/ws only where ws_bak<=0, reads idepth only where ws_bak>0
-__global__ void k2_dilate_kernel(float* __restrict__ idepth, float* __restrict__ ws, const float* __restrict__ ws_bak, int wl,
-                                 int hl, int diagonal) {
+__global__ void k2_dilate_all_kernel(const K2Planes p) {
+    const int l = blockIdx.y;
+    float* __restrict__ idepth = p.idepth[l];
+    float* __restrict__ ws = p.ws[l];
+    const float* __restrict__ ws_bak = p.ws_bak[l];
+    const int wl = p.w[l], hl = p.h[l], diagonal = l < 2 ? 1 : 0;
     int i = blockIdx.x * blockDim.x + threadIdx.x + wl;
     if (i >= wl * hl - wl) return;
     if (ws_bak[i] > 0) return;
@@ -47,10 +63,10 @@ __global__ void k2_dilate_kernel(float* __restrict__ idepth, float* __restrict__
     else { o0 = 1; o1 = -1; o2 = wl; o3 = -wl; }
     float sum = 0, num = 0, numn = 0;
     float b;
+    const int n = wl * hl;
     // the diagonal neighbours of the first cell of row 1 and of the last cell of row h-2 fall one element outside the
     // plane (the reference reads past its arrays there, CoarseTracker.cc:437-466; those two cells never reach the point
     // cloud): a neighbour outside [0, w h) counts as weight 0
-    const int n = wl * hl;
     auto wgt = [&](int j) { return (j >= 0 && j < n) ? ws_bak[j] : 0.f; };
     b = wgt(i + o0); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o0]); num = __fadd_rn(num, b); numn++; }
     b = wgt(i + o1); if (b > 0) { sum = __fadd_rn(sum, idepth[i + o1]); num = __fadd_rn(num, b); numn++; }
@@ -194,11 +210,15 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
                                                         T.w[l - 1]);
         c->launches++;
     }
-    for (int l = 0; l < L; l++) {
-        int nl = T.w[l] * T.h[l];
-        LDSO_CUDA_OK(c, ldso_copy(c, T.wsum_bak[l], T.wsum[l], nl * sizeof(float), cudaMemcpyDeviceToDevice, s));
-        k2_dilate_kernel<<<(nl + 255) / 256, 256, 0, s>>>(T.idepth[l], T.wsum[l], T.wsum_bak[l], T.w[l], T.h[l], l < 2 ? 1 : 0);
-        c->launches++;
+    {
+        // weightSums_bak = weightSums, then the dilation (CoarseTracker.cc:425-470): two launches over all levels
+        K2Planes q;
+        q.levels = L;
+        for (int l = 0; l < L; l++) { q.w[l] = T.w[l]; q.h[l] = T.h[l]; q.idepth[l] = T.idepth[l]; q.ws[l] = T.wsum[l]; q.ws_bak[l] = T.wsum_bak[l]; }
+        const dim3 grid((unsigned)((n0 + 255) / 256), (unsigned)L);
+        k2_backup_all_kernel<<<grid, 256, 0, s>>>(q);
+        k2_dilate_all_kernel<<<grid, 256, 0, s>>>(q);
+        c->launches += 2;
     }
     K2Levels p;
     p.levels = L;

@@ -250,7 +250,9 @@ __device__ __forceinline__ void border_fix(unsigned char* D, int x, int y, int w
 //     barrier of 128 threads before and after each stamp.
 __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int s_scan[N2_SEL_THREADS / 32], s_off[N2_SEL_THREADS], s_cnt[N2_SEL_THREADS], s_c0[2];
+    __shared__ int s_scan[N2_SEL_THREADS / 32], s_off[N2_SEL_THREADS], s_cnt[N2_SEL_THREADS], s_c0[2], s_list[2][32];
+    __shared__ float s_inv[32];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = 1.0f / (float)max((int)threadIdx.x, 1);
     const int cells = p.w1 * p.h1, cells16 = (cells + 15) / 16;
     unsigned char* D = smem;
     unsigned char* T = smem + (size_t)cells16 * 16;
@@ -291,8 +293,7 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) 
         }
     }
     __syncthreads();
-    constexpr int WT = 128;                              // threads that stay for the walk: warp 0 decides, four warps stamp
-    if (tid >= WT) return;
+    constexpr int WT = N2_SEL_THREADS;                   // warp 0 decides, the whole CTA stamps
     // ---- the walk
     const int w1 = p.w1, h1 = p.h1;
     const unsigned* T32 = reinterpret_cast<const unsigned*>(T);
@@ -317,88 +318,175 @@ __global__ void __launch_bounds__(N2_SEL_THREADS) n2_walk_kernel(const N2Sel p) 
     }
     for (int par = 0;; par ^= 1) {
         if (wid == 0) {
-            // the next accepted candidate, in pool order (a rejected one can never pass later: the map only decreases)
-            int c0 = -1;
+            // The candidates accepted next, in pool order (a rejected one can never pass later: the map only decreases).
+            // All lanes that pass against the map as it stands are resolved at once, in registers: lane j is accepted unless
+            // an earlier lane accepted in this round would have stamped its cell below its threshold — the very test the
+            // reference makes after each addIntoDistFinal, with the closed-form ring distance between two interior cells.
+            // A passing candidate on a border cell takes its value from its neighbours instead: then only the first
+            // passing lane is accepted and the rest of the chunk is tested again after the stamp.
+            int count = -1;
             while (base < K) {
                 bool pass = false;
+                int cx_ = 0, cy_ = 0;
                 if (cell >= 0 && lane >= from) {
                     const unsigned char d = D[cell];
                     pass = (d == 255 ? 1000.f : (float)d) + fr >= th;
+                    cy_ = cell / w1; cx_ = cell - cy_ * w1;
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, pass);
                 if (m) {
-                    const int j = __ffs(m) - 1;
-                    c0 = __shfl_sync(0xffffffffu, cell, j);
-                    if (lane == j) { p.action[idx] = 2; p.src_cells[n0 + nacc] = c0; }
-                    nacc++;
-                    from = j + 1;
+                    const bool onborder = pass && (cx_ == 0 || cy_ == 0 || cx_ == w1 - 1 || cy_ == h1 - 1);
+                    unsigned acc = 0;
+                    if (__ballot_sync(0xffffffffu, onborder)) {
+                        acc = 1u << (__ffs(m) - 1);
+                        from = __ffs(m);
+                    } else {
+                        bool blocked = false;
+                        for (unsigned rem = m; rem; rem &= rem - 1) {
+                            const int j = __ffs(rem) - 1;
+                            if (__shfl_sync(0xffffffffu, (int)blocked, j)) continue;
+                            acc |= 1u << j;
+                            const int sjx = __shfl_sync(0xffffffffu, cx_, j), sjy = __shfl_sync(0xffffffffu, cy_, j);
+                            if (pass && lane > j) {
+                                const int d = ring_dist(cx_ - sjx, cy_ - sjy);
+                                if (d <= R && !((float)d + fr >= th)) blocked = true;
+                            }
+                        }
+                        from = 32;                      // every lane of the chunk is decided
+                    }
+                    count = __popc(acc);
+                    const bool mine = (acc >> lane) & 1u;
+                    if (mine) {
+                        const int r = __popc(acc & ((1u << lane) - 1));
+                        p.action[idx] = 2; p.src_cells[n0 + nacc + r] = cell;
+                        s_list[par][r] = cx_ | (cy_ << 16);
+                    }
+                    // a source whose box reaches the border ring changes border cells, whose values depend on the order of the
+                    // stamps (a diagonal neighbour counts on odd rings only): such a round is stamped one source at a time
+                    const bool edge = mine && (cx_ - R <= 1 || cy_ - R <= 1 || cx_ + R >= w1 - 2 || cy_ + R >= h1 - 2);
+                    if (__ballot_sync(0xffffffffu, edge)) count |= 0x100;
+                    nacc += count & 0xff;
                     break;
                 }
+                from = 32;
+                if (from >= 32) {
+                    base += 32; from = 0;
+                    cell = cell_n; fr = fr_n; th = th_n; idx = idx_n;
+                    const int inext = base + 32 + lane;
+                    cell_n = -1;
+                    if (inext < K) { cell_n = p.ccell[inext]; fr_n = p.cfrac[inext]; th_n = p.cthr[inext]; idx_n = p.cidx[inext]; }
+                }
+            }
+            if (count > 0 && from >= 32) {              // the chunk is finished: the next one is tested after the stamps
                 base += 32; from = 0;
                 cell = cell_n; fr = fr_n; th = th_n; idx = idx_n;
                 const int inext = base + 32 + lane;
                 cell_n = -1;
                 if (inext < K) { cell_n = p.ccell[inext]; fr_n = p.cfrac[inext]; th_n = p.cthr[inext]; idx_n = p.cidx[inext]; }
             }
-            if (lane == 0) s_c0[par] = c0;
+            if (lane == 0) s_c0[par] = count;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int c0 = s_c0[par];
-        if (c0 < 0) break;
-        // ---- stamp c0 (all four warps)
-        const int sy = c0 / w1, sx = c0 - sy * w1;
-        const bool interior = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1;
-        if (tid == 0) D[c0] = 0;
-        if (tid < 4) {
-            if (sx == kx && sy == ky) cv = 0;
-            if (interior) {
-                qv = min(qv, ring_dist(qx - sx, qy - sy));
-                const int cand = qv + 1;
-                if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
-            }
-            if (cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
-        }
-        if (interior && R > 0) {
-            const int ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
-            if (words) {
-                const int x0 = sx - R;
-                const int wlo = x0 <= 0 ? 0 : (x0 >> 2), whi = min(sx + R, w1 - 1) >> 2, wlast = (w1 >> 2) - 1;
-                const int nw = whi - wlo + 1, slots = (yhi - ylo + 1) * nw;
-                const float inv_nw = 1.0f / (float)nw;                  // (t + 0.5) / nw stays 0.5 / nw away from an integer: exact floor
-#pragma unroll 2
-                for (int t = tid; t < slots; t += WT) {
-                    const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
-                    const int y = ylo + ry, wx = wlo + wq;
-                    const int b = 4 + 4 * wx - x0;                       // template byte under the word's first cell (>= 1)
-                    const unsigned* trow = T32 + ((y - sy + R) * N2_TPL_STRIDE >> 2) + (b >> 2);
-                    unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
-                    if (wx == 0) tv |= 0xffu;                            // column 0 and column w1 - 1 are border cells
-                    if (wx == wlast) tv |= 0xff000000u;
-                    const int wi = (y * w1 >> 2) + wx;
-                    const unsigned dv = D32[wi], mv = __vminu4(dv, tv);
-                    if (mv != dv) D32[wi] = mv;
-                }
+        __syncthreads();
+        const int round = s_c0[par];
+        if (round < 0) break;
+        const int count = round & 0xff;
+        if (!(round & 0x100) && words) {
+            // ---- no source of the round reaches the border ring: the sources are stamped side by side, one warp each (warp 0
+            // follows the corners); where two boxes overlap the word-wise minimum is taken with a compare-and-swap
+            if (wid == 0) {
+                if (lane < 4)
+                    for (int k = 0; k < count; k++) {
+                        const int c = s_list[par][k], sx = c & 0xffff, sy = c >> 16;
+                        qv = min(qv, ring_dist(qx - sx, qy - sy));
+                        const int cand = qv + 1;
+                        if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
+                    }
+                if (lane < 4 && cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
             } else {
-                const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R);
-                const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
-                for (int t = tid; t < nc; t += WT) {
-                    const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
-                    const int d = ring_dist(x - sx, y - sy);
-                    const int di = x + w1 * y;
-                    if (d <= R && D[di] > d) D[di] = (unsigned char)d;
+                for (int k = wid - 1; k < count; k += N2_SEL_THREADS / 32 - 1) {
+                    const int c = s_list[par][k], sx = c & 0xffff, sy = c >> 16;
+                    const int x0 = sx - R, ylo = sy - R;                    // the box is interior: no clamping
+                    const int wlo = x0 >> 2, nw = ((sx + R) >> 2) - wlo + 1, slots = (2 * R + 1) * nw;
+                    const float inv_nw = s_inv[nw];
+#pragma unroll 2
+                    for (int t = lane; t < slots; t += 32) {
+                        const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
+                        const int y = ylo + ry, wx = wlo + wq;
+                        const int b = 4 + 4 * wx - x0;
+                        const unsigned* trow = T32 + (ry * N2_TPL_STRIDE >> 2) + (b >> 2);
+                        const unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
+                        unsigned* dw = D32 + (y * w1 >> 2) + wx;
+                        unsigned dv = *dw;
+                        for (;;) {
+                            const unsigned mv = __vminu4(dv, tv);
+                            if (mv == dv) break;
+                            const unsigned seen = atomicCAS(dw, dv, mv);
+                            if (seen == dv) break;
+                            dv = seen;
+                        }
+                    }
                 }
             }
-            if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {   // uniform over the CTA
-                // the box reaches the border ring: those cells follow from their interior neighbours
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
-                if (by0 == 0) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, 0, w1, h1);
-                if (by1 == h1 - 1) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, h1 - 1, w1, h1);
-                if (bx0 == 0) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, 0, y, w1, h1);
-                if (bx1 == w1 - 1) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, w1 - 1, y, w1, h1);
-            }
+            __syncthreads();
+            continue;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        for (int k = 0; k < count; k++) {
+            // ---- stamp source k of the round (all warps), one source at a time
+            const int cpk = s_list[par][k];
+            const int sx = cpk & 0xffff, sy = cpk >> 16, c0 = sx + w1 * sy;
+            const bool interior = sx > 0 && sy > 0 && sx < w1 - 1 && sy < h1 - 1;
+            if (tid == 0) D[c0] = 0;
+            if (tid < 4) {
+                if (sx == kx && sy == ky) cv = 0;
+                if (interior) {
+                    qv = min(qv, ring_dist(qx - sx, qy - sy));
+                    const int cand = qv + 1;
+                    if ((cand & 1) && cand <= N2_RMAX) cv = min(cv, cand);
+                }
+                if (cv < D[kx + w1 * ky]) D[kx + w1 * ky] = (unsigned char)cv;
+            }
+            if (interior && R > 0) {
+                const int ylo = max(1, sy - R), yhi = min(h1 - 2, sy + R);
+                if (words) {
+                    const int x0 = sx - R;
+                    const int wlo = x0 <= 0 ? 0 : (x0 >> 2), whi = min(sx + R, w1 - 1) >> 2, wlast = (w1 >> 2) - 1;
+                    const int nw = whi - wlo + 1, slots = (yhi - ylo + 1) * nw;
+                    const float inv_nw = 1.0f / (float)nw;                  // (t + 0.5) / nw stays 0.5 / nw away from an integer: exact floor
+#pragma unroll 2
+                    for (int t = tid; t < slots; t += WT) {
+                        const int ry = (int)(((float)t + 0.5f) * inv_nw), wq = t - ry * nw;
+                        const int y = ylo + ry, wx = wlo + wq;
+                        const int b = 4 + 4 * wx - x0;                       // template byte under the word's first cell (>= 1)
+                        const unsigned* trow = T32 + ((y - sy + R) * N2_TPL_STRIDE >> 2) + (b >> 2);
+                        unsigned tv = __funnelshift_r(trow[0], trow[1], 8 * (b & 3));
+                        if (wx == 0) tv |= 0xffu;                            // column 0 and column w1 - 1 are border cells
+                        if (wx == wlast) tv |= 0xff000000u;
+                        const int wi = (y * w1 >> 2) + wx;
+                        const unsigned dv = D32[wi], mv = __vminu4(dv, tv);
+                        if (mv != dv) D32[wi] = mv;
+                    }
+                } else {
+                    const int xlo = max(1, sx - R), xhi = min(w1 - 2, sx + R);
+                    const int bw = xhi - xlo + 1, nc = bw * (yhi - ylo + 1);
+                    for (int t = tid; t < nc; t += WT) {
+                        const int ty = t / bw, x = xlo + (t - ty * bw), y = ylo + ty;
+                        const int d = ring_dist(x - sx, y - sy);
+                        const int di = x + w1 * y;
+                        if (d <= R && D[di] > d) D[di] = (unsigned char)d;
+                    }
+                }
+                if (sx - R <= 1 || sy - R <= 1 || sx + R >= w1 - 2 || sy + R >= h1 - 2) {   // uniform over the CTA
+                    // the box reaches the border ring: those cells follow from their interior neighbours
+                    __syncthreads();
+                    const int bx0 = max(0, sx - R - 1), bx1 = min(w1 - 1, sx + R + 1), by0 = max(0, sy - R - 1), by1 = min(h1 - 1, sy + R + 1);
+                    if (by0 == 0) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, 0, w1, h1);
+                    if (by1 == h1 - 1) for (int x = bx0 + tid; x <= bx1; x += WT) border_fix(D, x, h1 - 1, w1, h1);
+                    if (bx0 == 0) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, 0, y, w1, h1);
+                    if (bx1 == w1 - 1) for (int y = max(1, by0) + tid; y <= min(h1 - 2, by1); y += WT) border_fix(D, w1 - 1, y, w1, h1);
+                }
+            }
+            __syncthreads();
+        }
     }
     if (tid == 0) { *p.src_n = n0 + nacc; p.cnt[0] = nacc; }
     if (tid < 4) p.corner[lane] = cv;
