@@ -505,15 +505,16 @@ extern "C" int ldso_gpu_select_points(ldso_gpu_ctx* c, int slot, float density, 
     a2_list_emit_kernel<<<(h + 7) / 8, 256, 0, s>>>(S->map, w, h, border, S->row_cnt, S->list, S->max_list);
     c->launches += 3;
     LDSO_CUDA_OK(c, cudaGetLastError());
+    // the list holds at most the nsel selected pixels: its length and that many entries come back in ONE round trip
     int* total = (int*)S->counts_pinned;
+    const int bound = std::min(std::min(nsel, max_points), S->max_list);
+    float* hl = (float*)c->scratch_host;
     LDSO_CUDA_OK(c, ldso_copy(c, total, S->row_cnt + h, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (bound > 0) LDSO_CUDA_OK(c, ldso_copy(c, hl, S->list, sizeof(float) * 3 * (size_t)bound, cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
-    int n = std::min(std::min(*total, max_points), S->max_list);
+    int n = std::min(*total, bound);
     *n_points = n;
     if (n == 0) return 0;
-    float* hl = (float*)c->scratch_host;
-    LDSO_CUDA_OK(c, ldso_copy(c, hl, S->list, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
     for (int i = 0; i < n; i++) { u_out[i] = hl[3 * i]; v_out[i] = hl[3 * i + 1]; type_out[i] = hl[3 * i + 2]; }
     return 0;
 }
