@@ -73,6 +73,12 @@ typedef struct ldso_gpu_config {
 /* Fill cfg with src/Setting.cc defaults + preset=0 (examples/run_dso_tum_mono.cc:65-83). */
 void ldso_gpu_default_config(ldso_gpu_config* cfg);
 
+/* Cooperative waiting (no counterpart in the reference; used by ldso_gpu_batch_*).  While a hook is installed for the CALLING
+ * THREAD, every wait inside the library (stream / event synchronisation, the tracker's mailbox poll) polls and calls
+ * hook(arg) between polls instead of spinning, so a scheduler can run another sequence on the same thread until the device
+ * has caught up.  hook = NULL restores the plain blocking waits.  Thread-local: it affects calls made from this thread only. */
+int ldso_gpu_set_wait_hook(void (*hook)(void*), void* arg);
+
 /* Context life cycle.  create() derives the pyramid level count with the rule of setGlobalCalib
  * (src/internal/GlobalCalib.cc:20-28), allocates the frame pyramids, the two trackers, the window (points, residuals,
  * accumulators) and the tracker's reduction workspace, and creates the ctx's streams.  The other subsystems allocate their

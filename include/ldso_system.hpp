@@ -29,6 +29,8 @@
 #include <thread>
 #include <vector>
 
+#include <ucontext.h>
+
 #include "ldso_gpu.h"
 #include "ldso_smallmat.h"
 #include "ldso_system.h"
@@ -40,7 +42,7 @@
     struct NAME {                                                                                                       \
         typedef CTX ctx_t;                                                                                              \
         LDSO_API_FN(P, default_config) LDSO_API_FN(P, create) LDSO_API_FN(P, destroy) LDSO_API_FN(P, last_error)         \
-        LDSO_API_FN(P, pyr_levels) LDSO_API_FN(P, level_size) LDSO_API_FN(P, sync) LDSO_API_FN(P, bind_thread)                                    \
+        LDSO_API_FN(P, pyr_levels) LDSO_API_FN(P, level_size) LDSO_API_FN(P, sync) LDSO_API_FN(P, bind_thread) LDSO_API_FN(P, set_wait_hook)                                    \
         LDSO_API_FN(P, frame_make_images) LDSO_API_FN(P, frame_make_images_dev) LDSO_API_FN(P, frame_make_images_raw)    \
         LDSO_API_FN(P, frame_make_images_async)                                                                         \
         LDSO_API_FN(P, tracker_make_k) LDSO_API_FN(P, tracker_set_ref) LDSO_API_FN(P, tracker_track)                     \
@@ -69,6 +71,7 @@
     int P##level_size(const CTX*, int, int*, int*);                                                                      \
     int P##sync(CTX*);                                                                                                   \
     int P##bind_thread(CTX*);                                                                                            \
+    int P##set_wait_hook(void (*)(void*), void*);                                                                        \
     int P##frame_make_images(CTX*, int, const float*);                                                                   \
     int P##frame_make_images_dev(CTX*, int, const float*);                                                               \
     int P##frame_make_images_raw(CTX*, int, const void*, int, float, float);                                             \
@@ -1848,6 +1851,7 @@ public:
     std::vector<Sys*> sys;
     std::vector<Job> jobs;
     bool prefetch = getenv("LDSO_NO_PREFETCH") == nullptr;   // measurement knob: LDSO_NO_PREFETCH=1 prepares no frame ahead
+    bool fibers = getenv("LDSO_NO_FIBERS") == nullptr;       // measurement knob: LDSO_NO_FIBERS=1 runs a worker's sequences one after the other
     BatchRunner(int n, Sys** systems, int n_threads) : sys(systems, systems + n), jobs(n) {
         const int T = std::max(1, std::min(n_threads, n));
         for (int t = 0; t < T; t++) workers.emplace_back([this, t, T] { loop(t, T); });
@@ -1879,6 +1883,44 @@ private:
     long long generation = 0;
     int pending = 0;
     bool quit = false;
+    // ---- fibers: one per sequence of a worker -------------------------------------------------------------------------
+    static constexpr size_t kFiberStack = 1 << 20;
+    struct Fiber {
+        ucontext_t uc;
+        std::vector<char> stack;
+        BatchRunner* runner = nullptr;
+        size_t job = 0;
+        bool done = false;
+    };
+    struct Worker {
+        ucontext_t sched;
+        std::vector<Fiber> fib;
+        Fiber* cur = nullptr;
+    };
+    static Fiber*& current_fiber() { static thread_local Fiber* f = nullptr; return f; }
+    static void fiber_entry() {
+        Fiber* f = current_fiber();
+        f->runner->run_job(f->job);
+        f->done = true;                                    // returning resumes uc_link = the scheduler
+    }
+    static void fiber_yield(void* arg) {                   // the library's wait hook
+        Worker* w = (Worker*)arg;
+        if (w->cur) swapcontext(&w->cur->uc, &w->sched);
+    }
+    // all frames of one sequence: begin (makeImages + the tracker launch, nothing waits), prepare the next frame behind it, end
+    void run_job(size_t i) {
+        Job& j = jobs[i];
+        for (int f = 0; f < j.n_frames && j.rc >= 0; f++) {
+            j.rc = sys[i]->impl.addActiveFrameBegin(j.images[f], j.is_device, j.timestamp + f, j.exposure,
+                                                    j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
+                                                    j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
+            // the next frame of this call is at hand: its copy and pyramid queue up behind the tracker just launched
+            if (j.rc >= 0 && prefetch && f + 1 < j.n_frames && sys[i]->impl.prefetchImage(j.images[f + 1], j.is_device, j.exposure) < 0)
+                j.rc = -1;
+            if (j.rc >= 0) j.rc = sys[i]->impl.addActiveFrameEnd();
+        }
+        if (j.sync_after && j.rc >= 0 && Api::sync(sys[i]->impl.ctx) < 0) j.rc = -1;   // drains the queued trace too
+    }
     void loop(int t, int T) {
         long long seen = 0;
         bool bound = false;
@@ -1889,35 +1931,46 @@ private:
                 seen = generation;
                 if (quit) return;
             }
-            // frames outer, systems inner: a worker that owns several sequences advances them together; nothing waits for
-            // the other workers between frames (a keyframe of one sequence does not hold back the others)
-            int most = 0;
+            // Every own sequence runs its frames on a FIBER of this thread (its own stack, ucontext): wherever the library
+            // would wait for the device (tracker mailbox, stream / event synchronisation: ~30 round trips per keyframe) the
+            // wait hook switches to the scheduler below, which resumes the next sequence.  The thread therefore never spins
+            // while one of its sequences has host work to do, a keyframe of one sequence holds back neither the other
+            // workers nor the worker's other sequences, and the kernels of all of them overlap on the GPU.
+            std::vector<size_t> own;
             for (size_t i = t; i < sys.size(); i += T) {
                 if (!bound && sys[i]->impl.ctx) Api::bind_thread(sys[i]->impl.ctx);   // the device of the ctx becomes this thread's
                 jobs[i].rc = 0;
-                most = std::max(most, jobs[i].n_frames);
+                own.push_back(i);
             }
-            for (int f = 0; f < most; f++) {
-                // begin the frame of every own sequence (makeImages + the tracker launch, nothing waits), then finish them in
-                // the same order: while one sequence's tracker runs, the thread works on the others
-                for (size_t i = t; i < sys.size(); i += T) {
-                    Job& j = jobs[i];
-                    if (f >= j.n_frames || j.rc < 0) continue;
-                    j.rc = sys[i]->impl.addActiveFrameBegin(j.images[f], j.is_device, j.timestamp + f, j.exposure,
-                                                            j.pose_out ? j.pose_out + 12 * (size_t)f : nullptr,
-                                                            j.status_out ? j.status_out + LDSO_SYS_ST_N * (size_t)f : nullptr);
-                    // the next frame of this call is at hand: its copy and pyramid queue up behind the tracker just launched
-                    if (j.rc >= 0 && prefetch && f + 1 < j.n_frames && sys[i]->impl.prefetchImage(j.images[f + 1], j.is_device, j.exposure) < 0)
-                        j.rc = -1;
+            if (own.size() <= 1 || !fibers) {
+                for (size_t i : own) run_job(i);
+            } else {
+                Worker w;
+                w.fib.resize(own.size());
+                for (size_t k = 0; k < own.size(); k++) {
+                    Fiber& f = w.fib[k];
+                    f.runner = this; f.job = own[k]; f.done = false;
+                    f.stack.resize(kFiberStack);
+                    getcontext(&f.uc);
+                    f.uc.uc_stack.ss_sp = f.stack.data();
+                    f.uc.uc_stack.ss_size = f.stack.size();
+                    f.uc.uc_link = &w.sched;
+                    makecontext(&f.uc, (void (*)())&BatchRunner::fiber_entry, 0);
                 }
-                for (size_t i = t; i < sys.size(); i += T) {
-                    Job& j = jobs[i];
-                    if (f >= j.n_frames || j.rc < 0) continue;
-                    j.rc = sys[i]->impl.addActiveFrameEnd();
+                Api::set_wait_hook(&BatchRunner::fiber_yield, &w);
+                for (size_t left = own.size(); left > 0;) {
+                    for (size_t k = 0; k < own.size(); k++) {
+                        Fiber& f = w.fib[k];
+                        if (f.done) continue;
+                        w.cur = &f;
+                        current_fiber() = &f;
+                        swapcontext(&w.sched, &f.uc);      // runs the sequence until its next wait (or its end: uc_link)
+                        w.cur = nullptr;
+                        if (f.done) left--;
+                    }
                 }
+                Api::set_wait_hook(nullptr, nullptr);
             }
-            for (size_t i = t; i < sys.size(); i += T)
-                if (jobs[i].sync_after && jobs[i].rc >= 0 && Api::sync(sys[i]->impl.ctx) < 0) jobs[i].rc = -1;   // drains the queued trace too
             bound = true;
             {
                 std::lock_guard<std::mutex> lk(mu);

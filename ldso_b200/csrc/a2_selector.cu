@@ -394,7 +394,7 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     a2_cand0_kernel<<<(int)(((size_t)nslots * lpb + 127) / 128), 128, 0, s>>>(g, l0, S->thsS, S->mask, S->cand, nslots, lpb);
     prof_end(c, s, LDSO_PROF_A2, (double)g.w * g.h);
     LDSO_CUDA_OK(c, ldso_copy(c, S->mask_pinned, S->mask, (size_t)nslots * sizeof(unsigned short), cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     // the ordered scan: which direction each pot-block sees, and the running level-0 count
     int n2 = 0;
     const unsigned char* rp = S->rp_host.data();
@@ -410,7 +410,7 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
     prof_end(c, s, LDSO_PROF_A2, 0);
     c->launches += 2;
     LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     n[0] = n2; n[1] = S->counts_pinned[1]; n[2] = S->counts_pinned[2];
     return 0;
 }
@@ -462,7 +462,7 @@ static int make_maps_device(ldso_gpu_ctx* c, int slot, float density, int recurs
         a2_thin_apply_kernel<<<(h + 7) / 8, 256, 0, s>>>(S->map, w, h, S->row_cnt, S->rp, charTH, S->counts + 4);
         c->launches += 3;
         LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+        LDSO_CUDA_OK(c, ldso_stream_sync(s));
         numHaveSub -= S->counts_pinned[4];
     }
     *potential_io = ideal;
@@ -481,7 +481,7 @@ extern "C" int ldso_gpu_select_make_maps(ldso_gpu_ctx* c, int slot, float densit
     const int w = c->wG[0], h = c->hG[0];
     float* hmap = (float*)c->scratch_host;
     LDSO_CUDA_OK(c, ldso_copy(c, hmap, S->map, sizeof(float) * (size_t)w * h, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(map_out, hmap, sizeof(float) * (size_t)w * h);
     return 0;
 }
@@ -511,7 +511,7 @@ extern "C" int ldso_gpu_select_points(ldso_gpu_ctx* c, int slot, float density, 
     float* hl = (float*)c->scratch_host;
     LDSO_CUDA_OK(c, ldso_copy(c, total, S->row_cnt + h, sizeof(int), cudaMemcpyDeviceToHost, s));
     if (bound > 0) LDSO_CUDA_OK(c, ldso_copy(c, hl, S->list, sizeof(float) * 3 * (size_t)bound, cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     int n = std::min(*total, bound);
     *n_points = n;
     if (n == 0) return 0;

@@ -111,9 +111,38 @@ bool ldso_wait_block() {
     static const bool b = [] { const char* e = getenv("LDSO_WAIT_BLOCK"); return e && atoi(e) != 0; }();
     return b;
 }
+namespace {
+thread_local void (*t_wait_hook)(void*) = nullptr;
+thread_local void* t_wait_arg = nullptr;
+// cudaErrorNotReady from a query is not a failure: make sure it does not linger as the thread's "last error"
+inline void forget_not_ready() {
+    if (cudaPeekAtLastError() == cudaErrorNotReady) (void)cudaGetLastError();
+}
+}  // namespace
+extern "C" int ldso_gpu_set_wait_hook(void (*hook)(void*), void* arg) {
+    t_wait_hook = hook; t_wait_arg = arg;
+    return 0;
+}
 void ldso_cpu_relax() {
-    if (ldso_wait_yield()) sched_yield();
+    if (t_wait_hook) t_wait_hook(t_wait_arg);
+    else if (ldso_wait_yield()) sched_yield();
     else _mm_pause();
+}
+cudaError_t ldso_stream_sync(cudaStream_t s) {
+    if (!t_wait_hook) return cudaStreamSynchronize(s);
+    for (bool waited = false;; waited = true) {
+        const cudaError_t e = cudaStreamQuery(s);
+        if (e != cudaErrorNotReady) { if (waited) forget_not_ready(); return e; }
+        t_wait_hook(t_wait_arg);
+    }
+}
+cudaError_t ldso_event_sync(cudaEvent_t ev) {
+    if (!t_wait_hook) return cudaEventSynchronize(ev);
+    for (bool waited = false;; waited = true) {
+        const cudaError_t e = cudaEventQuery(ev);
+        if (e != cudaErrorNotReady) { if (waited) forget_not_ready(); return e; }
+        t_wait_hook(t_wait_arg);
+    }
 }
 
 extern "C" int ldso_gpu_create(const ldso_gpu_config* cfg, ldso_gpu_ctx** out) {
@@ -184,8 +213,8 @@ extern "C" int ldso_gpu_level_size(const ldso_gpu_ctx* c, int lvl, int* w, int* 
 }
 extern "C" int ldso_gpu_sync(ldso_gpu_ctx* c) {
     LDSO_ENTER(c);
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream_map));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream_map));
     return 0;
 }
 extern "C" int ldso_gpu_bind_thread(ldso_gpu_ctx* c) {
@@ -212,7 +241,7 @@ extern "C" int ldso_gpu_timer_stop(ldso_gpu_ctx* c, float* ms) {
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream_map));
     LDSO_CUDA_OK(c, cudaStreamWaitEvent(c->stream, c->ev_h2d, 0));
     LDSO_CUDA_OK(c, cudaEventRecord(c->ev1, c->stream));
-    LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev1));
+    LDSO_CUDA_OK(c, ldso_event_sync(c->ev1));
     LDSO_CUDA_OK(c, cudaEventElapsedTime(ms, c->ev0, c->ev1));
     return 0;
 }
@@ -239,7 +268,7 @@ int prof_end(ldso_gpu_ctx* c, cudaStream_t s, int which, double units) {
 void prof_drain(ldso_gpu_ctx* c) {
     for (auto& r : c->prof_pending) {
         float ms = 0;
-        cudaEventSynchronize(r.e1);
+        ldso_event_sync(r.e1);
         if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
             c->prof_ms[r.which] += ms; c->prof_launches[r.which]++; c->prof_units[r.which] += r.units;
         }
@@ -272,7 +301,7 @@ extern "C" int ldso_gpu_profile_get(ldso_gpu_ctx* c, int which, double* total_ms
 extern "C" int ldso_gpu_set_gamma(ldso_gpu_ctx* c, const float B[256]) {
     LDSO_ENTER(c);
     LDSO_CUDA_OK(c, ldso_copy(c, c->gammaB_dev, B, 256 * sizeof(float), cudaMemcpyHostToDevice, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     return 0;
 }
 
@@ -291,11 +320,11 @@ extern "C" int ldso_gpu_frame_make_images(ldso_gpu_ctx* c, int slot, const float
         LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, img, bytes, cudaMemcpyHostToDevice, c->stream));
         LDSO_CUDA_OK(c, cudaEventRecord(c->ev_h2d, c->stream));
         int rc = k1_make_images(c, slot, c->img_dev);
-        LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_h2d));
+        LDSO_CUDA_OK(c, ldso_event_sync(c->ev_h2d));
         return rc;
     }
     (void)cudaGetLastError();                            // an unregistered pointer is reported as an error on some drivers
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // previous H2D out of img_pinned has drained
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // previous H2D out of img_pinned has drained
     memcpy(c->img_pinned, img, bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, c->img_dev, c->img_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
     return k1_make_images(c, slot, c->img_dev);
@@ -337,7 +366,7 @@ extern "C" int ldso_gpu_frame_download(ldso_gpu_ctx* c, int slot, int lvl, int w
     const size_t n = (size_t)c->wG[lvl] * c->hG[lvl];
     float4* h = (float4*)c->scratch_host;
     LDSO_CUDA_OK(c, ldso_copy(c, h, c->frame[slot] + c->lvl_off[lvl], n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     if (what == 0) {
         for (size_t i = 0; i < n; i++) { dst[3 * i] = h[i].x; dst[3 * i + 1] = h[i].y; dst[3 * i + 2] = h[i].z; }
     } else {
@@ -395,7 +424,7 @@ extern "C" int ldso_gpu_tracker_get_pc(ldso_gpu_ctx* c, int tracker, int lvl, in
     if (m == 0 || !(u || v || idepth || color)) return 0;
     float4* h = (float4*)c->scratch_host;
     LDSO_CUDA_OK(c, ldso_copy(c, h, T.pc[lvl], (size_t)m * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     for (int i = 0; i < m; i++) {
         if (u) u[i] = h[i].x;
         if (v) v[i] = h[i].y;

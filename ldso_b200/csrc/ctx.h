@@ -144,6 +144,12 @@ struct ldso_gpu_ctx {
 // LDSO_WAIT_YIELD=1 the mailbox polls call sched_yield() and the context is switched to cudaDeviceScheduleYield, so that
 // more sequence threads than cores can share a host (ldso_gpu_batch_* with many sequences per GPU).
 bool ldso_wait_yield();
+// Every wait of the library goes through these two (and ldso_cpu_relax for the mailbox polls).  Without a hook they are
+// cudaStreamSynchronize / cudaEventSynchronize.  With a hook installed for the calling thread (ldso_gpu_set_wait_hook: the
+// batch runner's cooperative scheduler) they poll and call the hook between polls, so the thread runs another sequence
+// instead of spinning.
+cudaError_t ldso_stream_sync(cudaStream_t s);
+cudaError_t ldso_event_sync(cudaEvent_t e);
 bool ldso_wait_block();   // LDSO_WAIT_BLOCK=1: waits sleep in the driver (cudaDeviceScheduleBlockingSync, blocking events): no core is burnt while waiting
 void ldso_cpu_relax();
 

@@ -238,7 +238,7 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
     LDSO_CUDA_OK(c, cudaGetLastError());
     int* hn = (int*)c->trk_result_pinned;
     LDSO_CUDA_OK(c, ldso_copy(c, hn, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     for (int l = 0; l < L; l++) T.pc_n[l] = hn[l];
     T.ref_slot = ref_slot;
     T.last_lvl = -1;

@@ -1266,7 +1266,7 @@ int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew
 static int track_all_wait(ldso_gpu_ctx* c, double seq, int prof_idx, int dbg, ldso_sm::SE3& cur, float& aff_a, float& aff_b,
                           float last_residuals[5], float flow[3], int* status, int* nEval, int* nAccept) {
     volatile double* res = c->trk_mailbox;
-    if (ldso_wait_block()) LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_trk));   // sleep until the kernel is done instead of polling
+    if (ldso_wait_block()) LDSO_CUDA_OK(c, ldso_event_sync(c->ev_trk));   // sleep until the kernel is done instead of polling
     for (unsigned spin = 1; res[63] != seq; spin++) {
         ldso_cpu_relax();
         if ((spin & 0xfffff) == 0) {
@@ -1475,7 +1475,7 @@ extern "C" int ldso_gpu_tracker_calc_res_noalloc(ldso_gpu_ctx* c, int tracker, i
         LDSO_CUDA_OK(c, cudaGetLastError());
         // read-back through the ctx's pinned 64-double block (allocated in ldso_gpu_create): no allocation here either
         LDSO_CUDA_OK(c, ldso_copy(c, c->trk_result_pinned, result, sizeof(double) * 64, cudaMemcpyDeviceToHost, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         if (c->trk_result_pinned[63] != 1.0) { c->set_error("tracker kernel finished without publishing", __FILE__, __LINE__); return -1; }
         for (int k = 0; k < NF + NI; k++) res[k] = c->trk_result_pinned[k];
     }

@@ -545,7 +545,7 @@ int immature_trace_finalize(ldso_gpu_ctx* c) {
     ImmatureDev* P = (ImmatureDev*)c->immature;
     if (!P || !P->trace_pending) return 0;
     P->trace_pending = false;
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(P->trace_stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(P->trace_stream));
     for (int i = 0; i < 6; i++) P->trace_counts[i] = P->trace_cnt[i];
     // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
     if (P->trace_prof_idx >= 0 && P->trace_prof_idx < (int)c->prof_pending.size()) c->prof_pending[P->trace_prof_idx].units = (double)P->trace_cnt[6] + 9.0 * P->trace_cnt[7];
@@ -637,7 +637,7 @@ extern "C" int ldso_gpu_immature_create(ldso_gpu_ctx* c, int slot, int n, const 
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
     LDSO_CUDA_OK(c, ldso_copy(c, st, P->cr + 2 * (size_t)n, 80 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     for (int i = 0; i < n; i++) {
         const float* r = st + 20 * (size_t)i;
         memcpy(color + 8 * i, r, 32); memcpy(weights + 8 * i, r + 8, 32); memcpy(grad_h + 3 * i, r + 16, 12);
@@ -674,7 +674,7 @@ extern "C" int ldso_gpu_immature_set(ldso_gpu_ctx* c, int n, const int* host, co
     LDSO_CUDA_OK(c, cudaMemsetAsync(P->lastUV, 0, 8 * N, c->stream));
     LDSO_CUDA_OK(c, cudaMemsetAsync(P->interval, 0, 4 * N, c->stream));
     im_fill_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, 1.f, P->type);   // my_type: see ldso_gpu_immature_set_types
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     return 0;
 }
 
@@ -766,7 +766,7 @@ extern "C" int ldso_gpu_immature_get(ldso_gpu_ctx* c, float* idepth_min, float* 
     LDSO_CUDA_OK(c, get(idepth_min, P->idmin, 4 * N)); LDSO_CUDA_OK(c, get(idepth_max, P->idmax, 4 * N));
     LDSO_CUDA_OK(c, get(quality, P->quality, 4 * N)); LDSO_CUDA_OK(c, get(status, P->status, 4 * N));
     LDSO_CUDA_OK(c, get(last_trace_uv, P->lastUV, 8 * N)); LDSO_CUDA_OK(c, get(last_trace_pixel_interval, P->interval, 4 * N));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     for (int i = 0; i < nj; i++) memcpy(jobs[i].dst, st + jobs[i].off, jobs[i].bytes);
     return 0;
 }
@@ -801,7 +801,7 @@ extern "C" int ldso_gpu_immature_activate(ldso_gpu_ctx* c, int n_cand, const int
     LDSO_CUDA_OK(c, ldso_copy(c, st, P->act_idepth, 4 * N, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st + N, P->act_ok, 4 * N, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st + 2 * N, P->act_state, 4 * N * W.n, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(idepth_out, st, 4 * N); memcpy(ok_out, st + N, 4 * N); memcpy(res_state_out, st + 2 * N, 4 * N * W.n);
     return 0;
 }
@@ -838,7 +838,7 @@ extern "C" int ldso_gpu_immature_compact(ldso_gpu_ctx* c, int drop_host, int dro
     LDSO_CUDA_OK(c, cudaGetLastError());
     int* total = (int*)P->pinned + P->cap;
     LDSO_CUDA_OK(c, ldso_copy(c, total, P->pos + n, 4, cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     std::swap(P->host, P->host2); std::swap(P->status, P->status2); std::swap(P->u, P->u2); std::swap(P->v, P->v2);
     std::swap(P->color, P->color2); std::swap(P->weights, P->weights2); std::swap(P->gradH, P->gradH2);
     std::swap(P->energyTH, P->energyTH2); std::swap(P->idmin, P->idmin2); std::swap(P->idmax, P->idmax2);
@@ -867,7 +867,7 @@ extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx,
         c->launches += 2;
         LDSO_CUDA_OK(c, cudaGetLastError());
         P->n += n;
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the pinned staging is reused by the next entry point
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
     }
     *n_pool = P->n;
     return 0;

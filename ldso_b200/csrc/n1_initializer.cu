@@ -488,7 +488,7 @@ int make_pixel_status(ldso_gpu_ctx* c, InitDev* I, int slot, int lvl, float desi
     }
     int* cnt = (int*)I->pinned;
     LDSO_CUDA_OK(c, ldso_copy(c, cnt, I->count_dev, 4, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     numGoodPoints = *cnt;
     const float quotia = numGoodPoints / (float)(desiredDensity);
     int newSparsity = (I->sparsityFactor * sqrtf(quotia)) + 0.7f;
@@ -499,7 +499,7 @@ int make_pixel_status(ldso_gpu_ctx* c, InitDev* I, int slot, int lvl, float desi
         I->sparsityFactor = newSparsity;
         unsigned char* st = (unsigned char*)I->pinned + 64;
         LDSO_CUDA_OK(c, ldso_copy(c, st, I->map_dev, (size_t)w * h, cudaMemcpyDeviceToHost, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         memcpy(map_host, st, (size_t)w * h);
         return 0;
     }
@@ -523,7 +523,7 @@ int pull(ldso_gpu_ctx* c, InitDev* I, InitLevel& L, std::initializer_list<int> f
         LDSO_CUDA_OK(c, ldso_copy(c, g, L.good, L.n, cudaMemcpyDeviceToHost, c->stream));
         *good_out = g;
     }
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     return 0;
 }
 
@@ -557,7 +557,7 @@ int opt_reg(ldso_gpu_ctx* c, InitDev* I, int lvl) {
         }
     }
     LDSO_CUDA_OK(c, ldso_copy(c, L.F(F_IR), iR, sizeof(float) * L.n, cudaMemcpyHostToDevice, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the staging is reused
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the staging is reused
     return 0;
 }
 
@@ -603,7 +603,7 @@ int reset_points(ldso_gpu_ctx* c, InitDev* I, int lvl) {
         LDSO_CUDA_OK(c, ldso_copy(c, L.F(F_IDN), a3[1], sizeof(float) * L.n, cudaMemcpyHostToDevice, c->stream));
         LDSO_CUDA_OK(c, ldso_copy(c, L.F(F_IR), st + 2 * (size_t)L.n, sizeof(float) * L.n, cudaMemcpyHostToDevice, c->stream));
         LDSO_CUDA_OK(c, ldso_copy(c, L.good, gs, L.n, cudaMemcpyHostToDevice, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     }
     return 0;
 }
@@ -638,7 +638,7 @@ int calc_res_and_gs(ldso_gpu_ctx* c, InitDev* I, int lvl, const SE3& refToNew, d
                                                         I->result, result_host_dev);
     c->launches += 2;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     c->d2h_bytes += 128 * sizeof(double);
     const double* r0 = I->result_pinned;
     const double* r1 = I->result_pinned + 64;
@@ -748,7 +748,7 @@ extern "C" int ldso_gpu_init_set_first(ldso_gpu_ctx* c, int slot, int* num_point
         LDSO_CUDA_OK(c, cudaMemsetAsync(L.Jb_new, 0, sizeof(float) * 10 * cap, c->stream));
         LDSO_CUDA_OK(c, cudaMemcpyAsync(L.nb, nbT.data(), sizeof(int) * 10 * cap, cudaMemcpyHostToDevice, c->stream));
         if (n) LDSO_CUDA_OK(c, cudaMemcpyAsync(L.parent, L.parent_host.data(), sizeof(int) * n, cudaMemcpyHostToDevice, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         c->h2d_bytes += (long long)(sizeof(float) * F_NUM * cap + cap + sizeof(int) * 11 * cap);
     }
     // children lists for propagateUp: level l + 1 gets the CSR of level l's parent links (children in index order)
@@ -890,7 +890,7 @@ extern "C" int ldso_gpu_init_track_frame(ldso_gpu_ctx* c, int slot, float exposu
         if ((rc = opt_reg(c, I, i + 1))) return rc;
     }
     LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     I->frameID++;
     if (!I->snapped) I->snappedAt = 0;
     if (I->snapped && I->snappedAt == 0) I->snappedAt = I->frameID;
@@ -916,12 +916,12 @@ extern "C" int ldso_gpu_init_get_points(ldso_gpu_ctx* c, int lvl, int* n, float*
     for (int k = 0; k < 7; k++) {
         if (!outs[k]) continue;
         LDSO_CUDA_OK(c, ldso_copy(c, st, L.F(fields[k]), sizeof(float) * L.n, cudaMemcpyDeviceToHost, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         memcpy(outs[k], st, sizeof(float) * L.n);
     }
     if (is_good) {
         LDSO_CUDA_OK(c, ldso_copy(c, st, L.good, L.n, cudaMemcpyDeviceToHost, c->stream));
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         memcpy(is_good, st, L.n);
     }
     return 0;

@@ -543,7 +543,7 @@ extern "C" int ldso_gpu_immature_set_types(ldso_gpu_ctx* c, int first, int n, co
     n2_types_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, P->cr, P->type + first);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the pinned staging is reused by the next entry point
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
     return 0;
 }
 
@@ -574,7 +574,7 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
     prof_end(c, c->stream, LDSO_PROF_N2, c->wG[1] * c->hG[1]);
     c->launches++;
     if (rc) return rc;
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));   // the pinned staging is reused by the next entry point
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
     return 0;
 }
 
@@ -587,7 +587,7 @@ extern "C" int ldso_gpu_distmap_get(ldso_gpu_ctx* c, float* dist) {
     LDSO_REQUIRE(c, cells <= P->pinned_bytes);
     unsigned char* st = (unsigned char*)P->pinned;
     LDSO_CUDA_OK(c, ldso_copy(c, st, P->dmap, cells, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     for (size_t i = 0; i < cells; i++) dist[i] = st[i] == 255 ? 1000.f : (float)st[i];
     return 0;
 }
@@ -638,7 +638,7 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     LDSO_REQUIRE(c, (size_t)P->n + 4096 <= P->pinned_bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, sa, P->action, P->n, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st, P->sel_cnt, 8, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(action_out, sa, P->n);
     counts_out[0] = ((int*)st)[0]; counts_out[1] = ((int*)st)[1];
     return 0;

@@ -196,7 +196,7 @@ extern "C" int ldso_gpu_detect_corners(ldso_gpu_ctx* c, int slot, int nFeatures,
     LDSO_CUDA_OK(c, ldso_copy(c, st, D->misc, 16, cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, ldso_copy(c, st + 16, D->out, sizeof(float) * 3 * need, cudaMemcpyDeviceToHost, s));
     LDSO_CUDA_OK(c, ldso_copy(c, st + 16 + sizeof(float) * 3 * need, D->flag, need, cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(s));
+    LDSO_CUDA_OK(c, ldso_stream_sync(s));
     const int n = ((int*)st)[1];
     const float* xys = (const float*)(st + 16);
     const unsigned char* fl = (const unsigned char*)(st + 16 + sizeof(float) * 3 * need);

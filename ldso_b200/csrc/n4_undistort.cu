@@ -109,7 +109,7 @@ static int make_images_raw_impl(ldso_gpu_ctx* c, int slot, const void* raw, int 
     const bool pinned = cudaPointerGetAttributes(&attr, raw) == cudaSuccess && attr.type == cudaMemoryTypeHost;
     if (!pinned) {
         (void)cudaGetLastError();
-        LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
         memcpy(U->raw_pinned, raw, bytes);
     }
     LDSO_CUDA_OK(c, ldso_copy(c, U->raw, pinned ? raw : (const void*)U->raw_pinned, bytes, cudaMemcpyHostToDevice, c->stream));
@@ -126,7 +126,7 @@ static int make_images_raw_impl(ldso_gpu_ctx* c, int slot, const void* raw, int 
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
     const int rc = k1_make_images(c, slot, c->img_dev);
-    if (pinned && wait) LDSO_CUDA_OK(c, cudaEventSynchronize(c->ev_h2d));
+    if (pinned && wait) LDSO_CUDA_OK(c, ldso_event_sync(c->ev_h2d));
     return rc;
 }
 
@@ -144,7 +144,7 @@ extern "C" int ldso_gpu_undistort_get_image(ldso_gpu_ctx* c, float* image_out) {
     LDSO_REQUIRE(c, image_out);
     const size_t bytes = sizeof(float) * (size_t)c->cfg.w * c->cfg.h;
     LDSO_CUDA_OK(c, ldso_copy(c, c->scratch_host, c->img_dev, bytes, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(image_out, c->scratch_host, bytes);
     return 0;
 }

@@ -25,7 +25,7 @@ void* staging(ldso_gpu_ctx* c, size_t bytes) {
     WindowDev& W = c->win;
     const size_t need = (bytes + 255) & ~(size_t)255;
     if (W.pinned_off + need > W.pinned_bytes) {
-        if (W.pinned_off > 0) { cudaStreamSynchronize(c->stream); W.pinned_off = 0; }
+        if (W.pinned_off > 0) { ldso_stream_sync(c->stream); W.pinned_off = 0; }
         if (need > W.pinned_bytes) {
             if (W.pinned) cudaFreeHost(W.pinned);
             W.pinned = nullptr;
@@ -53,7 +53,7 @@ int download(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
     void* st = staging(c, bytes);
     if (!st) { c->set_error("pinned staging allocation failed", __FILE__, __LINE__); return -1; }
     LDSO_CUDA_OK(c, ldso_copy(c, st, src, bytes, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(dst, st, bytes);
     c->win.pinned_off = 0;   // everything queued before has completed
     return 0;
@@ -269,7 +269,7 @@ extern "C" int ldso_gpu_window_linearize(ldso_gpu_ctx* c, int fix, double stats[
     LDSO_REQUIRE(c, st != nullptr);
     LDSO_CUDA_OK(c, ldso_copy(c, st, W.stats, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     if (W.nr) LDSO_CUDA_OK(c, ldso_copy(c, st + 4 * sizeof(double), W.new_energy_wo, sizeof(float) * W.nr, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     W.pinned_off = 0;
     const double* ds = (const double*)st;
     stats[0] = ds[0]; stats[1] = 0; stats[2] = ds[1];
@@ -314,7 +314,7 @@ extern "C" int ldso_gpu_window_fix_linearization(ldso_gpu_ctx* c, const unsigned
     if (rc) return rc;
     for (int r = 0; r < W.nr; r++)
         if (mask[r]) W.h_lin[r] = 1;
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     return build_order(c);
 }
 
@@ -338,7 +338,7 @@ extern "C" int ldso_gpu_window_accumulate(ldso_gpu_ctx* c, double* HA, double* b
     LDSO_REQUIRE(c, st != nullptr);
     LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * 2 * nn, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     W.pinned_off = 0;
     const double* sys = (const double*)st;
     double* Hs[3] = {HA, HL, Hsc};
@@ -541,7 +541,7 @@ extern "C" int ldso_gpu_window_get_keyframe_results(ldso_gpu_ctx* c, int* state,
         LDSO_CUDA_OK(c, ldso_copy(c, h_pt + 2 * np, W.num_good, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
         LDSO_CUDA_OK(c, ldso_copy(c, h_pt + 3 * np, W.max_rel_baseline, sizeof(float) * np, cudaMemcpyDeviceToHost, c->stream));
     }
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     W.pinned_off = 0;
     if (state) memcpy(state, h_state, sizeof(int) * nr);
     if (center3) for (size_t r = 0; r < nr; r++) { center3[3 * r] = h_center[4 * r]; center3[3 * r + 1] = h_center[4 * r + 1]; center3[3 * r + 2] = h_center[4 * r + 2]; }
@@ -609,7 +609,7 @@ extern "C" int ldso_gpu_window_marginalize_points(ldso_gpu_ctx* c, const unsigne
     LDSO_REQUIRE(c, st != nullptr);
     LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * nn, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     W.pinned_off = 0;
     const double *M = (const double*)st, *Msc = M + 2 * sysz;
     for (size_t i = 0; i < (size_t)D * D; i++) H[i] = M[i] - Msc[i];
@@ -725,7 +725,7 @@ extern "C" int ldso_gpu_window_marginalize_subset(ldso_gpu_ctx* c, const unsigne
     LDSO_REQUIRE(c, st != nullptr);
     LDSO_CUDA_OK(c, ldso_copy(c, st, W.stitched, sizeof(double) * 3 * sysz, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_copy(c, st + sizeof(double) * 3 * sysz, W.acc_top_cnt, sizeof(int) * nn, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, cudaStreamSynchronize(c->stream));
+    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     lin_host = *(const int*)stl;
     W.pinned_off = 0;
     const double *M = (const double*)st, *Msc = M + 2 * sysz;

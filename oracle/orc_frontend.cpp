@@ -757,3 +757,6 @@ extern "C" int orc_frame_make_images_async(orc_ctx* c, int slot, const void* ima
     if (kind == 0 || kind == 1) return orc_frame_make_images(c, slot, (const float*)image);
     return orc_frame_make_images_raw(c, slot, image, kind == 2 ? 1 : 2, exposure_time, 1.0f);
 }
+
+// ldso_gpu_set_wait_hook: the CPU path never waits for a device
+extern "C" int orc_set_wait_hook(void (*)(void*), void*) { return 0; }

@@ -204,6 +204,25 @@ def test_gpu_batch_of_sequences_equals_each_alone(gpu):
     b.close()
 
 
+@pytest.mark.gpu
+def test_gpu_batch_on_one_worker_thread_interleaves_sequences(gpu):
+    """three sequences on ONE worker thread (ldso_gpu_batch_run): each runs on a fiber, every wait for the device switches to
+    the next sequence (ldso_gpu_set_wait_hook), frames are prepared one ahead; the results are those of each sequence alone"""
+    c = util.CALIB["c1"]
+    seqs = [synth.make_sequence(1001 + i, 40, start=0, stride=3, **c)[0] for i in range(3)]
+    alone = [system.run(gpu, c, fr, npoints_counter_mode=1)[0] for fr in seqs]
+    ss = [system.System(gpu, c, npoints_counter_mode=1) for _ in seqs]
+    b = system.Batch(ss, 1)
+    imgs = [[np.ascontiguousarray(f, np.float32) for f in fr] for fr in seqs]
+    st = b.run_ptrs([[im.ctypes.data for im in row] for row in imgs], sync_after=True)
+    assert st.shape[:2] == (3, 40) and st[:, -1, system.ST["initialized"]].all() and not st[:, :, system.ST["lost"]].any()
+    for s, a in zip(ss, alone):
+        ca, cb = a.counters(), s.counters()
+        assert ca["keyframes"] == cb["keyframes"] >= 3
+        assert np.abs(s.centres()[1] - a.centres()[1]).max() < 1e-4
+    b.close()
+
+
 def _raw8_equals_float(api, exact):
     c, frames, poses = _seq("small", 40)
     a, sta, kfa = system.run(api, c, frames, desired_point_density=600, desired_immature_density=500)
