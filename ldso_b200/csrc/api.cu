@@ -2,6 +2,9 @@
 // (frame pyramids, coarse tracker).  See include/ldso_gpu.h for the reference methods each one replaces.
 #include "ctx.h"
 
+#include <cuda.h>
+#include <atomic>
+
 #include <immintrin.h>
 #include <sched.h>
 
@@ -128,8 +131,71 @@ void ldso_cpu_relax() {
     else if (ldso_wait_yield()) sched_yield();
     else _mm_pause();
 }
+namespace {
+// Hooked stream wait without driver calls in the poll loop: a stream memory operation (cuStreamWriteValue32, obtained through
+// the runtime so that the library does not link against libcuda) writes a sequence number into mapped pinned memory behind
+// the work queued so far, and the host polls that word.  One 4 KB pinned block per waiting thread, one word per stream.
+typedef CUresult (*StreamWrite32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+StreamWrite32Fn stream_write32() {
+    static const StreamWrite32Fn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (getenv("LDSO_WAIT_QUERY")) return (StreamWrite32Fn) nullptr;     // measurement knob: poll with cudaStreamQuery instead
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            return (StreamWrite32Fn) nullptr;
+        }
+        return (StreamWrite32Fn)p;
+    }();
+    return fn;
+}
+struct WaitSlots {
+    volatile unsigned* host = nullptr;
+    unsigned* dev = nullptr;
+    int n = 0;
+    cudaStream_t stream[1024];
+    unsigned seq[1024];
+    bool failed = false;
+};
+thread_local WaitSlots t_slots;
+int wait_slot(cudaStream_t s) {
+    WaitSlots& W = t_slots;
+    for (int i = 0; i < W.n; i++) if (W.stream[i] == s) return i;
+    if (W.failed || W.n >= 1024) return -1;
+    if (!W.host) {
+        void* h = nullptr; void* d = nullptr;
+        if (cudaHostAlloc(&h, 4096, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess || cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+            (void)cudaGetLastError();
+            W.failed = true;
+            return -1;
+        }
+        memset(h, 0, 4096);
+        W.host = (volatile unsigned*)h; W.dev = (unsigned*)d;
+    }
+    W.stream[W.n] = s; W.seq[W.n] = 0;
+    return W.n++;
+}
+}  // namespace
 cudaError_t ldso_stream_sync(cudaStream_t s) {
     if (!t_wait_hook) return cudaStreamSynchronize(s);
+    const StreamWrite32Fn wr = stream_write32();
+    const int slot = wr ? wait_slot(s) : -1;
+    if (slot >= 0) {
+        WaitSlots& W = t_slots;
+        const unsigned want = ++W.seq[slot];
+        if (wr((CUstream)s, (CUdeviceptr)(W.dev + slot), want, 0) == CUDA_SUCCESS) {
+            for (unsigned spin = 1; W.host[slot] != want; spin++) {
+                t_wait_hook(t_wait_arg);
+                if ((spin & 0xfff) == 0) {                 // now and then make sure the stream is still alive
+                    const cudaError_t e = cudaStreamQuery(s);
+                    if (e != cudaErrorNotReady && e != cudaSuccess) return e;
+                    if (e == cudaErrorNotReady) forget_not_ready();
+                }
+            }
+            std::atomic_thread_fence(std::memory_order_acquire);
+            return cudaSuccess;
+        }
+    }
     for (bool waited = false;; waited = true) {
         const cudaError_t e = cudaStreamQuery(s);
         if (e != cudaErrorNotReady) { if (waited) forget_not_ready(); return e; }

@@ -37,6 +37,8 @@ struct ImmatureDev {
     cudaStream_t trace_stream = nullptr;     // stream of the pending trace
     int trace_slot = -1;                     // frame slot the pending trace reads
     bool trace_pending = false;              // a trace was launched without waiting (ldso_gpu_immature_trace_async)
+    int trace_parity = 0;                    // which of the two device count blocks the last trace wrote
+    bool trace_cnt_valid = false, trace_counts_fresh = false, trace_launched = false;
     int trace_prof_idx = -1;
     int trace_counts[6] = {0, 0, 0, 0, 0, 0};
     size_t pinned_bytes = 0;

@@ -97,9 +97,11 @@ struct K5Params {
     float max_pix_search, slack_interval, stepsize, min_improvement, huberTH, gn_threshold, extra_slack;
     const int* host;
     int* status;
-    const float *u, *v, *color, *weights, *gradH, *energyTH, *tables;
+    const float *u, *v, *color, *weights, *gradH, *energyTH;
     float *idmin, *idmax, *quality, *lastUV, *interval;
-    int* counts;
+    int* counts;         // [8] of this launch (zero on entry)
+    int* counts_next;    // [8] of the next launch: zeroed here (the launches are ordered on one stream or by events)
+    float tab[16 * LDSO_MAX_WINDOW];   // per host: KRKi[9] Kt[3] aff[2] pad[2] — rides in the kernel parameters, no copy
 };
 
 __global__ void __launch_bounds__(IM_THREADS) k5_trace_kernel(const K5Params p) {
@@ -107,6 +109,7 @@ __global__ void __launch_bounds__(IM_THREADS) k5_trace_kernel(const K5Params p) 
     __shared__ float errors[IM_PTS][100];
     __shared__ int cnt[8];   // [0..5] status histogram, [6] search steps, [7] points that reached the search
     if (threadIdx.x < 8) cnt[threadIdx.x] = 0;
+    if (blockIdx.x == 0 && threadIdx.x < 8) p.counts_next[threadIdx.x] = 0;
     __syncthreads();
     const int gid = blockIdx.x * IM_THREADS + threadIdx.x;
     const int pt = gid >> 3, k = gid & 7;
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(IM_THREADS) k5_trace_kernel(const K5Params p) 
     }
     if (result == -1) {
         write_trace = true;
-        const float* T = p.tables + 16 * p.host[pt];
+        const float* T = p.tab + 16 * p.host[pt];
         Kt0 = T[9]; Kt1 = T[10]; Kt2 = T[11]; aff0 = T[12]; aff1 = T[13];
         R00 = T[0]; R01 = T[1]; R10 = T[3]; R11 = T[4];
         idepth_min = p.idmin[pt]; idepth_max = p.idmax[pt]; quality = p.quality[pt];
@@ -546,9 +549,13 @@ int immature_trace_finalize(ldso_gpu_ctx* c) {
     if (!P || !P->trace_pending) return 0;
     P->trace_pending = false;
     LDSO_CUDA_OK(c, ldso_stream_sync(P->trace_stream));
-    for (int i = 0; i < 6; i++) P->trace_counts[i] = P->trace_cnt[i];
-    // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
-    if (P->trace_prof_idx >= 0 && P->trace_prof_idx < (int)c->prof_pending.size()) c->prof_pending[P->trace_prof_idx].units = (double)P->trace_cnt[6] + 9.0 * P->trace_cnt[7];
+    P->trace_counts_fresh = false;
+    if (P->trace_cnt_valid) {
+        for (int i = 0; i < 6; i++) P->trace_counts[i] = P->trace_cnt[i];
+        P->trace_counts_fresh = true;
+        // profile unit of K5 = one epipolar search step (8 bilinear samples); the fixed per-point part counts as 9 steps
+        if (P->trace_prof_idx >= 0 && P->trace_prof_idx < (int)c->prof_pending.size()) c->prof_pending[P->trace_prof_idx].units = (double)P->trace_cnt[6] + 9.0 * P->trace_cnt[7];
+    }
     P->trace_prof_idx = -1;
     return 0;
 }
@@ -580,13 +587,13 @@ ImmatureDev* immature_pool(ldso_gpu_ctx* c) {
     da((void**)&P->color2, 32 * N); da((void**)&P->weights2, 32 * N); da((void**)&P->gradH2, 12 * N); da((void**)&P->energyTH2, 4 * N);
     da((void**)&P->idmin2, 4 * N); da((void**)&P->idmax2, 4 * N); da((void**)&P->quality2, 4 * N); da((void**)&P->lastUV2, 8 * N);
     da((void**)&P->interval2, 4 * N); da((void**)&P->keep, 4 * (N + 1)); da((void**)&P->pos, 4 * (N + 1));
-    da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 32);
+    da((void**)&P->tables, 4 * 16 * LDSO_MAX_WINDOW); da((void**)&P->counts, 64);
     da((void**)&P->cand, 4 * N); da((void**)&P->act_idepth, 4 * N); da((void**)&P->act_ok, 4 * N);
     // act_state + 4096: the activation walk's segmented candidate arrays (n2_distmap.cu)
     da((void**)&P->act_state, 4 * (N * LDSO_MAX_WINDOW + 4096)); da((void**)&P->cr, 4 * 22 * N);
     P->src_cap = (int)(8 * N);
     da((void**)&P->src_cells, 4 * (size_t)P->src_cap); da((void**)&P->src_n, 32);   // [0] length, [1..4] corner values after a walk
-    if (ok) cudaMemset(P->src_n, 0, 32);
+    if (ok) { cudaMemset(P->src_n, 0, 32); cudaMemset(P->counts, 0, 64); }
     P->pinned_bytes = 4 * 32 * N + 4096;
     ok = ok && cudaMallocHost(&P->pinned, P->pinned_bytes) == cudaSuccess;
     ok = ok && cudaMallocHost((void**)&P->trace_cnt, 32) == cudaSuccess;
@@ -683,7 +690,7 @@ static int trace_launch(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float*
     if (!P) return -1;
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && n_hosts >= 1 && n_hosts <= LDSO_MAX_WINDOW && KRKi && Kt && aff);
     for (int i = 0; i < 6; i++) P->trace_counts[i] = 0;
-    if (P->n == 0) return 0;
+    if (P->n == 0) { P->trace_counts_fresh = true; return 0; }
     // async: the trace runs on the mapping stream, behind everything queued on the tracking stream so far (the new frame's
     // pyramid, earlier pool updates), and next to whatever the tracking stream gets afterwards (the next frame's tracker
     // occupies 32 of the SMs)
@@ -692,32 +699,39 @@ static int trace_launch(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float*
         LDSO_CUDA_OK(c, cudaEventRecord(P->ev_ready, c->stream));
         LDSO_CUDA_OK(c, cudaStreamWaitEvent(S, P->ev_ready, 0));
     }
-    float* st = (float*)P->pinned;
+    K5Params p;
     for (int h = 0; h < n_hosts; h++) {
-        float* T = st + 16 * h;
+        float* T = p.tab + 16 * h;
         memcpy(T, KRKi + 9 * h, 36); memcpy(T + 9, Kt + 3 * h, 12); memcpy(T + 12, aff + 2 * h, 8);
         T[14] = T[15] = 0;
     }
-    LDSO_CUDA_OK(c, ldso_copy(c, P->tables, st, 64 * (size_t)n_hosts, cudaMemcpyHostToDevice, S));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(P->counts, 0, 32, S));
-    K5Params p;
+    for (int i = 16 * n_hosts; i < 16 * LDSO_MAX_WINDOW; i++) p.tab[i] = 0;
+    c->h2d_bytes += 64 * (long long)n_hosts;
     p.img = c->frame[new_slot]; p.n = P->n; p.w = c->wG[0]; p.h = c->hG[0];
     p.gn_its = c->cfg.trace_gn_iterations; p.min_radius = c->cfg.min_trace_test_radius;
     p.max_pix_search = c->cfg.max_pix_search; p.slack_interval = c->cfg.trace_slack_interval; p.stepsize = c->cfg.trace_stepsize;
     p.min_improvement = c->cfg.trace_min_improvement; p.huberTH = c->cfg.huber_th; p.gn_threshold = c->cfg.trace_gn_threshold;
     p.extra_slack = c->cfg.trace_extra_slack_on_th;
     p.host = P->host; p.status = P->status; p.u = P->u; p.v = P->v; p.color = P->color; p.weights = P->weights; p.gradH = P->gradH;
-    p.energyTH = P->energyTH; p.tables = P->tables; p.idmin = P->idmin; p.idmax = P->idmax; p.quality = P->quality;
-    p.lastUV = P->lastUV; p.interval = P->interval; p.counts = P->counts;
+    p.energyTH = P->energyTH; p.idmin = P->idmin; p.idmax = P->idmax; p.quality = P->quality;
+    p.lastUV = P->lastUV; p.interval = P->interval;
+    P->trace_parity ^= 1;                      // two count blocks: each launch zeroes the one of the next launch
+    p.counts = P->counts + 8 * P->trace_parity; p.counts_next = P->counts + 8 * (P->trace_parity ^ 1);
     prof_begin(c, S);
     k5_trace_kernel<<<(8 * P->n + IM_THREADS - 1) / IM_THREADS, IM_THREADS, 0, S>>>(p);
     P->trace_prof_idx = prof_end(c, S, LDSO_PROF_K5, P->n);
     c->launches++;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, ldso_copy(c, P->trace_cnt, P->counts, 32, cudaMemcpyDeviceToHost, S));
+    // the status counts come back only when somebody asks (ldso_gpu_immature_trace_counts) or the profile needs its units
+    P->trace_cnt_valid = false;
+    if (c->profile_on) {
+        LDSO_CUDA_OK(c, ldso_copy(c, P->trace_cnt, p.counts, 32, cudaMemcpyDeviceToHost, S));
+        P->trace_cnt_valid = true;
+    }
     LDSO_CUDA_OK(c, cudaEventRecord(P->ev_done, S));
     P->trace_stream = S; P->trace_slot = new_slot;
     P->trace_pending = true;
+    P->trace_launched = true;
     return 0;
 }
 
@@ -741,6 +755,12 @@ extern "C" int ldso_gpu_immature_trace_counts(ldso_gpu_ctx* c, int counts_out[6]
     if (immature_trace_finalize(c)) return -1;
     ImmatureDev* P = immature_pool(c);
     if (!P) return -1;
+    if (!P->trace_counts_fresh && P->trace_launched) {   // the counts of the last trace are still on the device
+        LDSO_CUDA_OK(c, ldso_copy(c, P->trace_cnt, P->counts + 8 * P->trace_parity, 32, cudaMemcpyDeviceToHost, c->stream));
+        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
+        for (int i = 0; i < 6; i++) P->trace_counts[i] = P->trace_cnt[i];
+        P->trace_counts_fresh = true;
+    }
     for (int i = 0; i < 6; i++) counts_out[i] = P->trace_counts[i];
     return 0;
 }

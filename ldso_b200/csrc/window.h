@@ -21,6 +21,10 @@ struct WindowDev {
     float fxl = 0, fyl = 0, cxl = 0, cyl = 0, fxli = 0, fyli = 0;
     // device: frames
     float* precalc = nullptr;      // [n*n][32]
+    // pools the per-upload arrays below are carved from (one H2D copy / one memset per upload): see carve_points / carve_residuals
+    float* pool_p = nullptr;       // points: u v idepth idepth_zero prior host res_begin color[8] weights[8], stride q = np rounded up
+    int* pool_ri = nullptr;        // residual ints: r_target r_point state flags new_state, stride r = nr rounded up
+    float* pool_rz = nullptr;      // residual floats that start at zero: energy new_energy new_energy_wo rtz[8] JpJdF[8] center[4] res_pt[8] J[72]
     // device: points (SoA)
     float *u = nullptr, *v = nullptr, *idepth = nullptr, *idepth_zero = nullptr, *prior = nullptr;
     float *color = nullptr, *weights = nullptr;   // [cap_p][8]
@@ -61,6 +65,7 @@ struct WindowDev {
     std::vector<unsigned char> h_lin;
     std::vector<double> adHost, adTarget, fprior, fdelta_prior;
     std::vector<float> adHostF, adTargetF;
+    bool ad_dev_valid = false;     // adH_dev / adT_dev hold adHost / adTarget
     float cDeltaF[4] = {0, 0, 0, 0};
     double cPrior[4] = {0, 0, 0, 0};
     // pinned staging

@@ -68,15 +68,11 @@ int win_alloc(ldso_gpu_ctx* c) {
     const size_t P = W.cap_p, R = W.cap_r, M = LDSO_MAX_WINDOW;
     int rc = 0;
     rc |= dalloc(c, &W.precalc, M * M * LDSO_PRECALC_STRIDE);
-    rc |= dalloc(c, &W.u, P); rc |= dalloc(c, &W.v, P); rc |= dalloc(c, &W.idepth, P); rc |= dalloc(c, &W.idepth_zero, P);
-    rc |= dalloc(c, &W.prior, P); rc |= dalloc(c, &W.color, 8 * P); rc |= dalloc(c, &W.weights, 8 * P);
-    rc |= dalloc(c, &W.host, P); rc |= dalloc(c, &W.res_begin, P + 1);
-    rc |= dalloc(c, &W.pt_out, WIN_PT_ROWS * P); rc |= dalloc(c, &W.max_rel_baseline, P); rc |= dalloc(c, &W.num_good, P);
-    rc |= dalloc(c, &W.r_point, R); rc |= dalloc(c, &W.r_target, R); rc |= dalloc(c, &W.state, R); rc |= dalloc(c, &W.new_state, R);
-    rc |= dalloc(c, &W.flags, R); rc |= dalloc(c, &W.energy, R); rc |= dalloc(c, &W.new_energy, R);
-    rc |= dalloc(c, &W.new_energy_wo, R);
-    rc |= dalloc(c, &W.J, R * LDSO_J_FLOATS); rc |= dalloc(c, &W.rtz, R * 8); rc |= dalloc(c, &W.JpJdF, R * 8);
-    rc |= dalloc(c, &W.center, R * 4); rc |= dalloc(c, &W.res_pt, R * 8);
+    rc |= dalloc(c, &W.pool_p, (P + 8) * 24);
+    rc |= dalloc(c, &W.pt_out, (WIN_PT_ROWS + 2) * P);          // + max_rel_baseline, num_good: one memset per upload
+    W.max_rel_baseline = W.pt_out + (size_t)WIN_PT_ROWS * P; W.num_good = W.max_rel_baseline + P;
+    rc |= dalloc(c, &W.pool_ri, (R + 8) * 5);
+    rc |= dalloc(c, &W.pool_rz, (R + 8) * 103);
     rc |= dalloc(c, &W.order, R); rc |= dalloc(c, &W.chunk, 3 * (R / 1 + 2 * M * M + 8));
     rc |= dalloc(c, &W.sc_blocks, 3 * (P + M + 8));
     rc |= dalloc(c, &W.ridx, P * M); rc |= dalloc(c, &W.pmask, P);
@@ -91,12 +87,29 @@ int win_alloc(ldso_gpu_ctx* c) {
 
 void win_free(ldso_gpu_ctx* c) {
     WindowDev& W = c->win;
-    void* ptrs[] = {W.precalc, W.u, W.v, W.idepth, W.idepth_zero, W.prior, W.color, W.weights, W.host, W.res_begin, W.pt_out,
-                    W.max_rel_baseline, W.num_good, W.r_point, W.r_target, W.state, W.new_state, W.flags, W.energy, W.new_energy,
-                    W.new_energy_wo, W.J, W.rtz, W.JpJdF, W.center, W.res_pt, W.order, W.chunk, W.sc_blocks, W.ridx, W.pmask, W.adHTdelta, W.xAd,
+    void* ptrs[] = {W.precalc, W.pool_p, W.pt_out, W.pool_ri, W.pool_rz, W.order, W.chunk, W.sc_blocks, W.ridx, W.pmask, W.adHTdelta, W.xAd,
                     W.stats, W.acc_top, W.acc_top_cnt, W.acc_sc, W.adH_dev, W.adT_dev, W.prior_dev, W.stitched};
     for (void* p : ptrs) cudaFree(p);
     if (W.pinned) cudaFreeHost(W.pinned);
+}
+
+// The per-upload arrays are carved from their pools with strides rounded to the upload's size, in the order the host stages
+// them, so that a window upload is ONE host-to-device copy (+ one memset) per group instead of one per array.
+static size_t carve_points(WindowDev& W, int np) {
+    const size_t q = ((size_t)np + 4) & ~(size_t)3;             // >= np + 1 (res_begin), multiple of 4 floats (16 B)
+    float* b = W.pool_p;
+    W.u = b; W.v = b + q; W.idepth = b + 2 * q; W.idepth_zero = b + 3 * q; W.prior = b + 4 * q;
+    W.host = (int*)(b + 5 * q); W.res_begin = (int*)(b + 6 * q); W.color = b + 7 * q; W.weights = b + 15 * q;
+    return q;
+}
+static size_t carve_residuals(WindowDev& W, int nr) {
+    const size_t r = ((size_t)nr + 7) & ~(size_t)7;             // multiple of 8: the 288-byte J records stay 32-byte aligned
+    int* bi = W.pool_ri;
+    W.r_target = bi; W.r_point = bi + r; W.state = bi + 2 * r; W.flags = bi + 3 * r; W.new_state = bi + 4 * r;
+    float* z = W.pool_rz;
+    W.energy = z; W.new_energy = z + r; W.new_energy_wo = z + 2 * r; W.rtz = z + 3 * r; W.JpJdF = z + 11 * r; W.center = z + 19 * r;
+    W.res_pt = z + 23 * r; W.J = z + 31 * r;
+    return r;
 }
 
 // ---- window description --------------------------------------------------------------------------
@@ -127,16 +140,18 @@ extern "C" int ldso_gpu_window_set_points(ldso_gpu_ctx* c, int np, const float* 
     W.np = np;
     W.h_host.assign(host, host + np);
     W.h_res_begin.assign(res_begin, res_begin + np + 1);
-    int rc = 0;
-    rc |= upload(c, W.u, u, sizeof(float) * np); rc |= upload(c, W.v, v, sizeof(float) * np);
-    rc |= upload(c, W.idepth, idepth, sizeof(float) * np); rc |= upload(c, W.idepth_zero, idepth_zero, sizeof(float) * np);
-    rc |= upload(c, W.host, host, sizeof(int) * np); rc |= upload(c, W.color, color, sizeof(float) * 8 * np);
-    rc |= upload(c, W.weights, weights, sizeof(float) * 8 * np); rc |= upload(c, W.prior, prior, sizeof(float) * np);
-    rc |= upload(c, W.res_begin, res_begin, sizeof(int) * (np + 1));
-    if (rc) return -1;
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * WIN_PT_ROWS * W.cap_p, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.max_rel_baseline, 0, sizeof(float) * W.cap_p, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.num_good, 0, sizeof(float) * W.cap_p, c->stream));
+    {
+        const size_t q = carve_points(W, np);
+        const size_t bytes = sizeof(float) * 23 * q;
+        float* st = (float*)staging(c, bytes);
+        LDSO_REQUIRE(c, st != nullptr);
+        memcpy(st, u, sizeof(float) * np); memcpy(st + q, v, sizeof(float) * np); memcpy(st + 2 * q, idepth, sizeof(float) * np);
+        memcpy(st + 3 * q, idepth_zero, sizeof(float) * np); memcpy(st + 4 * q, prior, sizeof(float) * np);
+        memcpy(st + 5 * q, host, sizeof(int) * np); memcpy(st + 6 * q, res_begin, sizeof(int) * (np + 1));
+        memcpy(st + 7 * q, color, sizeof(float) * 8 * np); memcpy(st + 15 * q, weights, sizeof(float) * 8 * np);
+        LDSO_CUDA_OK(c, ldso_copy(c, W.pool_p, st, bytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    LDSO_CUDA_OK(c, cudaMemsetAsync(W.pt_out, 0, sizeof(float) * (WIN_PT_ROWS + 2) * W.cap_p, c->stream));
     // K9 CTA table: consecutive points of one host per CTA — 64 (one staging tile) for a single window, more tiles per CTA
     // once that still leaves two CTAs per SM (batched windows): the cross-group fold and the ~3 k fp64 atomics of the
     // flush are paid per CTA (64x window on B200: 150 us at 64 points per CTA, 95 us at 448)
@@ -207,20 +222,20 @@ extern "C" int ldso_gpu_window_set_residuals(ldso_gpu_ctx* c, int nr, const int*
         W.h_lin[r] = (flags[r] & LDSO_RF_LINEARIZED) ? 1 : 0;
     }
     int rc = 0;
-    rc |= upload(c, W.r_target, target, sizeof(int) * nr); rc |= upload(c, W.r_point, W.h_point.data(), sizeof(int) * nr);
-    rc |= upload(c, W.state, state, sizeof(int) * nr); rc |= upload(c, W.flags, fl.data(), sizeof(int) * nr);
-    if (rc) return -1;
-    std::vector<int> ns(nr, LDSO_RES_OUTLIER);
-    rc |= upload(c, W.new_state, ns.data(), sizeof(int) * nr);
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.energy, 0, sizeof(float) * nr, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.new_energy, 0, sizeof(float) * nr, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.new_energy_wo, 0, sizeof(float) * nr, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.J, 0, sizeof(float) * (size_t)nr * LDSO_J_FLOATS, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.JpJdF, 0, sizeof(float) * (size_t)nr * 8, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.center, 0, sizeof(float) * (size_t)nr * 4, c->stream));
-    LDSO_CUDA_OK(c, cudaMemsetAsync(W.res_pt, 0, sizeof(float) * (size_t)nr * 8, c->stream));
+    {
+        const size_t r = carve_residuals(W, nr);
+        const size_t bytes = sizeof(int) * 5 * r;
+        int* st = (int*)staging(c, std::max<size_t>(bytes, 16));
+        LDSO_REQUIRE(c, st != nullptr);
+        if (nr) {
+            memcpy(st, target, sizeof(int) * nr); memcpy(st + r, W.h_point.data(), sizeof(int) * nr); memcpy(st + 2 * r, state, sizeof(int) * nr);
+            memcpy(st + 3 * r, fl.data(), sizeof(int) * nr);
+            for (int i = 0; i < nr; i++) st[4 * r + i] = LDSO_RES_OUTLIER;
+            LDSO_CUDA_OK(c, ldso_copy(c, W.pool_ri, st, bytes, cudaMemcpyHostToDevice, c->stream));
+            LDSO_CUDA_OK(c, cudaMemsetAsync(W.pool_rz, 0, sizeof(float) * 103 * r, c->stream));
+        }
+    }
     if (res_to_zero) rc |= upload(c, W.rtz, res_to_zero, sizeof(float) * 8 * (size_t)nr);
-    else LDSO_CUDA_OK(c, cudaMemsetAsync(W.rtz, 0, sizeof(float) * (size_t)nr * 8, c->stream));
     if (rc) return -1;
     return build_order(c);
 }
@@ -232,16 +247,26 @@ extern "C" int ldso_gpu_window_set_adjoints(ldso_gpu_ctx* c, const double* adH, 
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, W.n > 0 && adH && adT && adHTdelta && cDelta && cPrior && fprior && fdelta_prior);
     const int nn = W.n * W.n;
-    W.adHost.assign(adH, adH + 64 * nn); W.adTarget.assign(adT, adT + 64 * nn);
-    W.adHostF.resize(64 * nn); W.adTargetF.resize(64 * nn);
-    for (int i = 0; i < 64 * nn; i++) { W.adHostF[i] = (float)adH[i]; W.adTargetF[i] = (float)adT[i]; }
+    // the adjoints change only with the linearisation point (setAdjointsF): inside optimize's iterations the same matrices come
+    // again with new deltas, and their 2 x 25 KB are not sent a second time
+    const bool same_ad = (int)W.adHost.size() == 64 * nn && (int)W.adTarget.size() == 64 * nn && W.ad_dev_valid &&
+                         memcmp(W.adHost.data(), adH, sizeof(double) * 64 * nn) == 0 && memcmp(W.adTarget.data(), adT, sizeof(double) * 64 * nn) == 0;
+    if (!same_ad) {
+        W.adHost.assign(adH, adH + 64 * nn); W.adTarget.assign(adT, adT + 64 * nn);
+        W.adHostF.resize(64 * nn); W.adTargetF.resize(64 * nn);
+        for (int i = 0; i < 64 * nn; i++) { W.adHostF[i] = (float)adH[i]; W.adTargetF[i] = (float)adT[i]; }
+    }
     for (int i = 0; i < 4; i++) { W.cDeltaF[i] = cDelta[i]; W.cPrior[i] = cPrior[i]; }
     W.fprior.assign(fprior, fprior + 8 * W.n); W.fdelta_prior.assign(fdelta_prior, fdelta_prior + 8 * W.n);
     std::vector<double> pr(8 + 16 * (size_t)W.n);
     for (int i = 0; i < 4; i++) { pr[i] = cPrior[i]; pr[4 + i] = (double)cDelta[i]; }
     for (int i = 0; i < 8 * W.n; i++) { pr[8 + i] = fprior[i]; pr[8 + 8 * W.n + i] = fdelta_prior[i]; }
-    int rc = upload(c, W.adH_dev, adH, sizeof(double) * 64 * nn);
-    rc |= upload(c, W.adT_dev, adT, sizeof(double) * 64 * nn);
+    int rc = 0;
+    if (!same_ad) {
+        rc |= upload(c, W.adH_dev, adH, sizeof(double) * 64 * nn);
+        rc |= upload(c, W.adT_dev, adT, sizeof(double) * 64 * nn);
+        W.ad_dev_valid = rc == 0;
+    }
     rc |= upload(c, W.prior_dev, pr.data(), sizeof(double) * pr.size());
     rc |= upload(c, W.adHTdelta, adHTdelta, sizeof(float) * 8 * nn);
     return rc ? -1 : 0;
@@ -251,9 +276,13 @@ extern "C" int ldso_gpu_window_set_idepth(ldso_gpu_ctx* c, const float* idepth, 
     LDSO_ENTER(c);
     WindowDev& W = c->win;
     LDSO_REQUIRE(c, idepth && idepth_zero);
-    int rc = upload(c, W.idepth, idepth, sizeof(float) * W.np);
-    rc |= upload(c, W.idepth_zero, idepth_zero, sizeof(float) * W.np);
-    return rc ? -1 : 0;
+    if (W.np == 0) return 0;
+    const size_t q = (size_t)(W.idepth_zero - W.idepth);        // the two arrays are neighbours in the point pool (carve_points)
+    float* st = (float*)staging(c, sizeof(float) * 2 * q);
+    LDSO_REQUIRE(c, st != nullptr);
+    memcpy(st, idepth, sizeof(float) * W.np); memcpy(st + q, idepth_zero, sizeof(float) * W.np);
+    LDSO_CUDA_OK(c, ldso_copy(c, W.idepth, st, sizeof(float) * (q + W.np), cudaMemcpyHostToDevice, c->stream));
+    return 0;
 }
 
 // ---- K7 ------------------------------------------------------------------------------------------
