@@ -18,6 +18,13 @@ JSON keys as in the task statement:
   roofline     dominant kernel, live CUDA-event duration; roofline_batched_window: K7-K10 on a 64x window
   cpu_baseline / --impl reference   the same C++ control flow over the CPU oracle on the host cores
 """
+import os as _os
+
+# Every sequence owns two CUDA streams; with the default 8 hardware work queues the streams of different sequences share queues
+# and a small kernel of one sequence waits behind the tracker of another (16 sequences: 15.5 k -> 19.9 k frames/s with 32,
+# profiles/r2z_seq_conn32.log).  Must be in the environment before the CUDA context exists.
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 import argparse
 import json
 import os

@@ -694,6 +694,8 @@ static int trace_launch(ldso_gpu_ctx* c, int new_slot, int n_hosts, const float*
     // async: the trace runs on the mapping stream, behind everything queued on the tracking stream so far (the new frame's
     // pyramid, earlier pool updates), and next to whatever the tracking stream gets afterwards (the next frame's tracker
     // occupies 32 of the SMs)
+    static const bool one_stream = getenv("LDSO_TRACE_ON_TRACKING_STREAM") != nullptr;   // measurement knob: no second stream per sequence
+    if (one_stream) async = false;
     cudaStream_t S = async ? c->stream_map : c->stream;
     if (async) {
         LDSO_CUDA_OK(c, cudaEventRecord(P->ev_ready, c->stream));
