@@ -60,6 +60,9 @@ WORKLOAD = ("configs[1] per sequence: synthetic 640x480 sequence (procedural box
             "Timed at steady state after %d priming frames (CoarseInitializer bootstrap, window full, frames being marginalised). "
             "EnergyFunctional::nPoints counts the active points (npoints_counter_mode=1, upstream DSO's behaviour; the fork never "
             "increments it). %d independent sequences per GPU stepped together (configs[4])" % (STRIDE, PRIME, SEQ_PER_GPU))
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/r2w_k34_full.md:
+# 3.05 MB read, 0 written by one tracker launch, against 12.8 MB algorithmic: the level's points and texels stay in L2 / shared memory)
+NCU_TRAFFIC = {"k34_track_cluster_kernel": 3052288}
 BYTES_PER_UNIT = {"k34": 80.0, "k7": 900.0, "k8": 288.0, "k9": 72.0, "k1": 4 * 640 * 480 + 16 * 408000.0, "k5": 128.0, "k6": 512.0,
                   "k10": 60.0, "k2": 8000.0, "a2": 24.0, "n2": 1.0, "n2sel": 24.0}
 PROF = [("k34_track_cluster_kernel", 0, "k34", "point evaluations"), ("k5_trace_kernel", 1, "k5", "search steps"),
@@ -447,7 +450,7 @@ def main():
                        "once (S x K x 1.2 MB of input > 126 MB L2); single_sequence: step by step, L2 flushed with a 256 MiB write "
                        "between steps",
                 roofline={"bound": "hbm", "kernel": top, "achieved": kernels[top]["achieved_gbs"], "peak": peak, "unit": "GB/s",
-                          "frac": kernels[top]["frac"], "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                          "frac": kernels[top]["frac"], "traffic": NCU_TRAFFIC.get(top), "peak_source": "measured" if peaks else "fallback",
                           "launches": kernels[top]["launches"], "avg_us": kernels[top]["avg_us"],
                           "units_per_launch": kernels[top]["units_per_launch"],
                           "note": "dominant kernel by summed launch time over %d steady-state frames of one sequence (%d keyframes); "
