@@ -30,6 +30,7 @@ struct ImmatureDev {
     int* sel_cnt = nullptr;                  // [4] candidates, deleted
     int* src_cells = nullptr;                // [src_cap] level-1 cell of every source of the map (active points, then accepted ones), -1 = none
     int* src_n = nullptr;                    // device: length of the list
+    bool map_stale = false;                  // accepted cells were appended to src_cells after dmap was built
     int src_cap = 0, src_n_host = 0;         // host: capacity and an upper bound of the current length
     void* pinned = nullptr;
     int* trace_cnt = nullptr;                // pinned [8]: status counts + step counts of the last trace

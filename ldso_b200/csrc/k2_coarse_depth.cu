@@ -88,14 +88,11 @@ struct K2Levels {
     const float4* ref[LDSO_MAX_LEVELS];
 };
 
-__device__ __forceinline__ bool k2_valid(const K2Levels& p, int l, int i, float& nid, float& color) {
-    float wsum = p.ws[l][i];
+__device__ __forceinline__ bool k2_valid_values(float wsum, float idepth, float color, float& nid) {
     if (!(wsum > 0)) return false;
-    nid = __fdiv_rn(p.idepth[l][i], wsum);
-    color = p.ref[l][i].x;
+    nid = __fdiv_rn(idepth, wsum);
     return isfinite(color) && (nid > 0);
 }
-
 // one warp per interior row (y in [2,h-2)) of every level: count
 __global__ void k2_count_rows_kernel(const K2Levels p, int* __restrict__ row_cnt) {
     int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -106,9 +103,22 @@ __global__ void k2_count_rows_kernel(const K2Levels p, int* __restrict__ row_cnt
     int y = row - p.row_base[l] + 2;
     int wl = p.w[l];
     int cnt = 0;
-    for (int x = 2 + lane; x < wl - 2; x += 32) {
-        float nid, col;
-        cnt += k2_valid(p, l, x + y * wl, nid, col) ? 1 : 0;
+    const float* __restrict__ ws = p.ws[l];
+    const float* __restrict__ idp = p.idepth[l];
+    const float4* __restrict__ ref = p.ref[l];
+    for (int x0 = 2; x0 < wl - 2; x0 += 128) {          // four loads of every plane in flight per lane
+        float w4[4], d4[4], c4[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = x0 + 32 * k + lane;
+            w4[k] = 0.f; d4[k] = 0.f; c4[k] = 0.f;
+            if (x < wl - 2) { const int i = x + y * wl; w4[k] = ws[i]; d4[k] = idp[i]; c4[k] = ref[i].x; }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            float nid;
+            cnt += k2_valid_values(w4[k], d4[k], c4[k], nid) ? 1 : 0;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     if (lane == 0) row_cnt[row] = cnt;
@@ -163,18 +173,30 @@ __global__ void k2_emit_rows_kernel(const K2Levels p, const int* __restrict__ ro
     int wl = p.w[l];
     int off = row_off[row];
     float4* pc = p.pc[l];
-    for (int x0 = 2; x0 < wl - 2; x0 += 32) {
-        int x = x0 + lane;
-        bool ok = false;
-        float nid = 0, col = 0;
-        if (x < wl - 2) {
-            int i = x + y * wl;
-            ok = k2_valid(p, l, i, nid, col);
-            p.idepth[l][i] = ok ? nid : -1.f;
+    const float* __restrict__ ws = p.ws[l];
+    float* idp = p.idepth[l];
+    const float4* __restrict__ ref = p.ref[l];
+    for (int x0 = 2; x0 < wl - 2; x0 += 128) {          // four loads of every plane in flight per lane; a cell is read before it is rewritten
+        float w4[4], d4[4], c4[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = x0 + 32 * k + lane;
+            w4[k] = 0.f; d4[k] = 0.f; c4[k] = 0.f;
+            if (x < wl - 2) { const int i = x + y * wl; w4[k] = ws[i]; d4[k] = idp[i]; c4[k] = ref[i].x; }
         }
-        unsigned m = __ballot_sync(0xffffffffu, ok);
-        if (ok) pc[off + __popc(m & ((1u << lane) - 1u))] = make_float4((float)x, (float)y, nid, col);
-        off += __popc(m);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = x0 + 32 * k + lane;
+            bool ok = false;
+            float nid = 0;
+            if (x < wl - 2) {
+                ok = k2_valid_values(w4[k], d4[k], c4[k], nid);
+                idp[x + y * wl] = ok ? nid : -1.f;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            if (ok) pc[off + __popc(m & ((1u << lane) - 1u))] = make_float4((float)x, (float)y, nid, c4[k]);
+            off += __popc(m);
+        }
     }
 }
 

@@ -569,6 +569,7 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
     }
     LDSO_REQUIRE(c, n_points <= P->src_cap);
     P->src_n_host = n_points;
+    P->map_stale = false;
     prof_begin(c, c->stream);
     n2_project_kernel<<<(n_points + 255) / 256 + 1, 256, 0, c->stream>>>(c->wG[1], c->hG[1], n_points, P->tables, (const int*)P->cr,
                                                                         P->cr + N, P->cr + 2 * N, P->cr + 3 * N, P->src_cells, P->src_n);
@@ -587,6 +588,11 @@ extern "C" int ldso_gpu_distmap_get(ldso_gpu_ctx* c, float* dist) {
     LDSO_REQUIRE(c, dist && c->levels >= 2);
     const size_t cells = (size_t)c->wG[1] * c->hG[1];
     LDSO_REQUIRE(c, cells <= P->pinned_bytes);
+    if (P->map_stale) {    // fwdWarpedIDDistFinal after the walk of activatePointsMT: nothing on the path reads it, only debug code
+        const int rc = launch_map(c, P, true);
+        if (rc) return rc;
+        P->map_stale = false;
+    }
     unsigned char* st = (unsigned char*)P->pinned;
     LDSO_CUDA_OK(c, ldso_copy(c, st, P->dmap, cells, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
@@ -606,6 +612,11 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     counts_out[0] = counts_out[1] = 0;
     if (P->n == 0) return 0;
     float* st = (float*)P->pinned;
+    if (P->map_stale) {    // a second walk on the same map: it starts from the map the first walk left
+        const int rcm = launch_map(c, P, true);
+        if (rcm) return rcm;
+        P->map_stale = false;
+    }
     int rc = put_tables(c, P, n_hosts, KRKi, Kt, host_skip, host_flagged, st);
     if (rc) return rc;
     N2Sel p;
@@ -634,8 +645,7 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     prof_end(c, c->stream, LDSO_PROF_N2SEL, P->n);
     c->launches += 2;
     LDSO_CUDA_OK(c, cudaGetLastError());
-    rc = launch_map(c, P, true);   // the accepted cells joined the source list: rebuild the full-radius map behind the read-back
-    if (rc) return rc;
+    P->map_stale = true;   // the accepted cells joined the source list: the full-radius map is rebuilt when somebody reads it (ldso_gpu_distmap_get)
     unsigned char* sa = (unsigned char*)P->pinned + 4096;
     LDSO_REQUIRE(c, (size_t)P->n + 4096 <= P->pinned_bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, sa, P->action, P->n, cudaMemcpyDeviceToHost, c->stream));
