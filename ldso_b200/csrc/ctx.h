@@ -99,6 +99,7 @@ struct ldso_gpu_ctx {
     double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
     int trk_coop_max = 0;                   // co-resident CTA budget of the cooperative LM kernel (tracker_lm_mode = 2)
     int trk_cluster = 0;                    // CTAs of the tracker's thread-block cluster (tracker_lm_mode = 0), chosen at first use
+    size_t k9_smem_set = 0;                 // dynamic shared memory opted in for k9_sc_kernel on this ctx's device
     size_t n2_smem_set = 0;                 // dynamic shared memory opted in for the activation walk on this ctx's device
     bool k1_attr_set = false, k8_attr_set = false;   // opt-in dynamic shared memory set for this ctx's device
     int sm_count = 148;                     // multiprocessors of the ctx's device
