@@ -36,8 +36,17 @@
 #include "ldso_system.h"
 
 // ---- binding of the C ABI by symbol prefix ---------------------------------------------------------------------------
+#ifdef LDSO_API_TIMING   // measurement build: seconds spent inside the C ABI, so that (wall - this) is the orchestrator's own host work
+#include <chrono>
+namespace ldso { inline double& api_seconds() { static thread_local double s = 0; return s; }
+struct ApiTimer { std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+                  ~ApiTimer() { api_seconds() += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); } }; }
+#define LDSO_API_FN(P, name) \
+    template <class... A> static inline auto name(A... a) -> decltype(P##name(a...)) { ldso::ApiTimer ldso_api_timer; return P##name(a...); }
+#else
 #define LDSO_API_FN(P, name) \
     template <class... A> static inline auto name(A... a) -> decltype(P##name(a...)) { return P##name(a...); }
+#endif
 #define LDSO_DEFINE_API(NAME, P, CTX)                                                                                   \
     struct NAME {                                                                                                       \
         typedef CTX ctx_t;                                                                                              \
@@ -60,6 +69,12 @@
         LDSO_API_FN(P, window_get_residual_ints) LDSO_API_FN(P, window_get_point_floats)                                 \
         LDSO_API_FN(P, window_get_keyframe_results) LDSO_API_FN(P, window_marginalize_subset)                            \
     };
+// optional fine-grained host timers of the orchestrator (LDSO_SYS_PROF=1, FullSystemT::prof): label -> seconds
+#ifdef LDSO_API_TIMING
+#define LDSO_T(label, expr) do { const double _t0 = now(), _a0 = ldso::api_seconds(); expr; prof.add(label, now() - _t0, ldso::api_seconds() - _a0); } while (0)
+#else
+#define LDSO_T(label, expr) do { const double _t0 = now(); expr; prof.add(label, now() - _t0); } while (0)
+#endif
 // declarations of the same entry points under another prefix (test builds: the CPU oracle mirrors the ABI as orc_*)
 #define LDSO_DECLARE_API(P, CTX)                                                                                         \
     extern "C" {                                                                                                        \
@@ -588,7 +603,7 @@ public:
             // :130-138  swap tracking reference?
             if (coarseTracker_forNewKF->refFrameID > coarseTracker->refFrameID) std::swap(coarseTracker, coarseTracker_forNewKF);
             pend.tracking = true;
-            rc = trackNewCoarseBegin(fh);
+            LDSO_T("frame trackNewCoarseBegin", rc = trackNewCoarseBegin(fh));
             if (rc < 0) { pend.active = false; return rc; }
         }
         phase_s[0] += now() - t0;
@@ -636,7 +651,7 @@ public:
             }
         } else {
             double tres[4];
-            rc = trackNewCoarseEnd(fh, tres);
+            LDSO_T("frame trackNewCoarseEnd", rc = trackNewCoarseEnd(fh, tres));
             if (rc < 0) return rc;
             phase_s[0] += now() - t0;
             if (!std::isfinite(tres[0]) || !std::isfinite(tres[1]) || !std::isfinite(tres[2]) || !std::isfinite(tres[3])) {
@@ -659,7 +674,7 @@ public:
                 bool b2 = 2 * coarseTracker->firstCoarseRMSE < tres[0];
                 needToMakeKF = allFrameHistory.size() == 1 || b1 || b2;
             }
-            rc = deliverTrackedFrame(fh, needToMakeKF);
+            LDSO_T("frame deliverTrackedFrame (KF or trace)", rc = deliverTrackedFrame(fh, needToMakeKF));
             if (rc < 0) return rc;
             madeKF = needToMakeKF;
         }
@@ -707,18 +722,20 @@ private:
 
     // optional fine-grained host timers (LDSO_SYS_PROF=1): label -> seconds, printed by the destructor
     struct Prof {
-        std::vector<std::pair<std::string, double>> acc;
+        std::vector<std::pair<std::string, std::pair<double, double>>> acc;   // label -> (wall seconds, seconds inside the C ABI)
         bool on = getenv("LDSO_SYS_PROF") != nullptr;
-        void add(const char* label, double dt) {
+        void add(const char* label, double dt, double api = 0) {
             if (!on) return;
-            for (auto& a : acc) if (a.first == label) { a.second += dt; return; }
-            acc.emplace_back(label, dt);
+            for (auto& a : acc) if (a.first == label) { a.second.first += dt; a.second.second += api; return; }
+            acc.emplace_back(label, std::make_pair(dt, api));
         }
         ~Prof() {
-            for (auto& a : acc) fprintf(stderr, "  [sys prof] %-40s %.3f ms\n", a.first.c_str(), 1e3 * a.second);
+            for (auto& a : acc)
+                fprintf(stderr, "  [sys prof] %-40s %.3f ms (host outside the C ABI %.3f ms)\n", a.first.c_str(), 1e3 * a.second.first,
+                        1e3 * (a.second.first - a.second.second));
         }
     } prof;
-#define LDSO_T(label, expr) do { const double _t0 = now(); expr; prof.add(label, now() - _t0); } while (0)
+
     static double now() {
         return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
     }
@@ -1784,12 +1801,12 @@ private:
             }
         }
         phase_s[7] += now() - t0;
-        if ((rc = activatePointsMT()) < 0) return rc;
+        LDSO_T("KF activatePointsMT", rc = activatePointsMT()); if (rc < 0) return rc;
         makeIDX();
         t0 = now();
         fh->frameEnergyTH = frames.back()->frameEnergyTH;
         float rmse = 0;
-        if ((rc = optimize(cfg.max_opt_iterations, &rmse)) < 0) return rc;
+        LDSO_T("KF optimize", rc = optimize(cfg.max_opt_iterations, &rmse)); if (rc < 0) return rc;
         kf_log[0] = rmse;
         kf_log[9] = fh->frameEnergyTH;
         phase_s[3] += now() - t0;
@@ -1801,21 +1818,21 @@ private:
         }
         if (isLost) return 0;
         t0 = now();
-        removeOutliers();
+        LDSO_T("KF removeOutliers", removeOutliers());
         phase_s[4] += now() - t0;
         t0 = now();
-        if ((rc = setCoarseTrackingRef(coarseTracker_forNewKF)) < 0) return rc;
+        LDSO_T("KF setCoarseTrackingRef", rc = setCoarseTrackingRef(coarseTracker_forNewKF)); if (rc < 0) return rc;
         phase_s[5] += now() - t0;
         t0 = now();
-        if ((rc = flagAndMarginalizePoints()) < 0) return rc;
+        LDSO_T("KF flagAndMarginalizePoints", rc = flagAndMarginalizePoints()); if (rc < 0) return rc;
         phase_s[4] += now() - t0;
         t0 = now();
-        if ((rc = makeNewTraces(fh)) < 0) return rc;
+        LDSO_T("KF makeNewTraces", rc = makeNewTraces(fh)); if (rc < 0) return rc;
         phase_s[5] += now() - t0;
         t0 = now();
         for (size_t i = 0; i < frames.size(); i++)
             if (frames[i]->flaggedForMarginalization) {
-                if ((rc = marginalizeFrame(frames[i])) < 0) return rc;
+                LDSO_T("KF marginalizeFrame", rc = marginalizeFrame(frames[i])); if (rc < 0) return rc;
                 i = 0;   // as the reference: restart the scan (after its i++)
             }
         double hn = 0;
@@ -1981,6 +1998,11 @@ private:
 };
 }  // namespace ldso
 
+#ifdef LDSO_API_TIMING
+#define LDSO_API_TIMING_EXPORT out[11] = ldso::api_seconds();
+#else
+#define LDSO_API_TIMING_EXPORT
+#endif
 // ---- the extern "C" face (include/ldso_system.h) for a symbol prefix ----------------------------------------------------
 #define LDSO_DEFINE_SYSTEM_EXPORTS(P, API)                                                                                 \
     struct P##system {                                                                                                    \
@@ -2048,6 +2070,7 @@ private:
     }                                                                                                                     \
     extern "C" int P##system_get_phase_seconds(P##system* s, double out[12]) {                                            \
         for (int i = 0; i < 12; i++) out[i] = s->impl.phase_s[i];                                                         \
+        LDSO_API_TIMING_EXPORT                                                                                            \
         return 0;                                                                                                         \
     }                                                                                                                     \
     struct P##batch {                                                                                                     \

@@ -106,6 +106,19 @@ static int create_impl(ldso_gpu_ctx* c) {
     return 0;
 }
 
+int ldso_raise_smem(ldso_gpu_ctx* c, const void* fn, size_t bytes, int slot) {
+    constexpr int MAXDEV = 64, NSLOT = 4;
+    static size_t have[MAXDEV][NSLOT] = {};
+    static std::mutex mu;
+    const int dev = c->cfg.device;
+    LDSO_REQUIRE(c, dev >= 0 && dev < MAXDEV && slot >= 0 && slot < NSLOT);
+    std::lock_guard<std::mutex> lk(mu);
+    if (bytes <= have[dev][slot]) return 0;
+    LDSO_CUDA_OK(c, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    have[dev][slot] = bytes;
+    return 0;
+}
+
 bool ldso_wait_yield() {
     static const bool y = [] { const char* e = getenv("LDSO_WAIT_YIELD"); return e && atoi(e) != 0; }();
     return y;

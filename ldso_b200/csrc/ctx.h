@@ -99,8 +99,6 @@ struct ldso_gpu_ctx {
     double lm_dbg_clocks[8] = {0};          // cfg.reserved[0] == 3: SM clocks per LM phase (measurement only)
     int trk_coop_max = 0;                   // co-resident CTA budget of the cooperative LM kernel (tracker_lm_mode = 2)
     int trk_cluster = 0;                    // CTAs of the tracker's thread-block cluster (tracker_lm_mode = 0), chosen at first use
-    size_t k9_smem_set = 0;                 // dynamic shared memory opted in for k9_sc_kernel on this ctx's device
-    size_t n2_smem_set = 0;                 // dynamic shared memory opted in for the activation walk on this ctx's device
     bool k1_attr_set = false, k8_attr_set = false;   // opt-in dynamic shared memory set for this ctx's device
     int sm_count = 148;                     // multiprocessors of the ctx's device
     // calls on one ctx are serialised: the reference's tracking thread (trackMutex) and mapping thread (mapMutex) may both
@@ -154,6 +152,10 @@ cudaError_t ldso_stream_sync(cudaStream_t s);
 cudaError_t ldso_event_sync(cudaEvent_t e);
 bool ldso_wait_block();   // LDSO_WAIT_BLOCK=1: waits sleep in the driver (cudaDeviceScheduleBlockingSync, blocking events): no core is burnt while waiting
 void ldso_cpu_relax();
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize of `fn` on the ctx's device is raised to at least `bytes` (never lowered: other
+// contexts of the process launch the same kernel with their own sizes).  slot: one per kernel, see api.cu
+int ldso_raise_smem(ldso_gpu_ctx* c, const void* fn, size_t bytes, int slot);
 
 // every host<->device copy of the library goes through here so that the traffic is accounted
 inline cudaError_t ldso_copy(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {

@@ -281,9 +281,9 @@ int k9_accumulate_sc(ldso_gpu_ctx* c, const unsigned char* marg_mask, float prio
         const int G = k9_groups(n);
         LDSO_REQUIRE(c, 2 * n * n * G + n * 8 + 20 <= K9_THREADS);
         const size_t smem = sizeof(float) * std::max((size_t)2 * (K9_TILE * n * 8 + K9_TILE * 6), (size_t)G * 32 * 2 * n * n);
-        if (smem > c->k9_smem_set) {   // per ctx = per device
-            LDSO_CUDA_OK(c, cudaFuncSetAttribute(k9_sc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            c->k9_smem_set = smem;
+        {
+            const int rc = ldso_raise_smem(c, (const void*)k9_sc_kernel, smem, 0);
+            if (rc) return rc;
         }
         prof_begin(c, c->stream);
         k9_point_kernel<<<(W.np + 127) / 128, 128, 0, c->stream>>>(n, W.np, W.res_begin, W.flags, W.r_target, W.res_pt, W.prior,

@@ -501,10 +501,7 @@ size_t map_bytes(const ldso_gpu_ctx* c) { return (((size_t)c->wG[1] * c->hG[1] +
 
 int set_smem(ldso_gpu_ctx* c, const void* fn, size_t bytes) {
     LDSO_REQUIRE(c, bytes <= 220 * 1024);   // level-1 grids up to ~215 k cells (1232x368 -> 113 k) + the 7 KB stamp template
-    if (c->n2_smem_set == bytes) return 0;
-    LDSO_CUDA_OK(c, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    c->n2_smem_set = bytes;
-    return 0;
+    return ldso_raise_smem(c, fn, bytes, 1);
 }
 
 // per-host tables -> device (P->tables is sized for K5's 16 floats per host: 12 + skip + flag fit)

@@ -277,3 +277,19 @@ def test_batched_window_parity(gpu, oracle, window):
         a, b = g.window_point_floats(what), o.window_point_floats(what)
         assert np.array_equal(bits(a[sel]), bits(b[sel])), what
     g.close(); o.close()
+
+
+def test_contexts_with_different_window_sizes_share_the_kernels(gpu, window):
+    """several sequences live in one process (configs[4]) and their windows have different sizes at the same time: a context with
+    a small window must not lower the dynamic shared-memory opt-in another context's K9 launch needs (regression: the batch
+    failed with 'invalid argument' while the windows of its sequences were still growing)"""
+    small = synth.make_window(frame_ids=(40, 46, 52), pts_per_frame=200)
+    a = load(gpu, window)
+    a.window_linearize(False); a.window_apply_res()
+    ref = a.window_accumulate()
+    b = load(gpu, small)                     # created after a: its first K9 launch asks for less shared memory
+    b.window_linearize(False); b.window_apply_res()
+    accb = b.window_accumulate()
+    again = a.window_accumulate()            # the 7-frame window again
+    assert util.rel_err(again["Hsc"], ref["Hsc"]) < 1e-6 and np.abs(accb["Hsc"]).max() > 0
+    a.close(); b.close()
