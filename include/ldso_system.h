@@ -154,8 +154,11 @@ int ldso_gpu_batch_add_active_frames(ldso_gpu_batch* batch, const float* const* 
                                      int* status_out);
 
 /* The same for n_frames frames per system in ONE call, without a rendezvous between frames: images[n][n_frames]
- * (system-major), exposure 1, timestamps counting up; every worker feeds its systems their frames in order and a keyframe of
- * one sequence does not hold back the others.  poses_out [n][n_frames][12], status_out [n][n_frames][LDSO_SYS_ST_N]. */
+ * (system-major; they must stay valid until the call returns), exposure 1, timestamps counting up.  Every worker runs its
+ * systems as fibers: where the library would wait for the device it switches to the worker's next system
+ * (ldso_gpu_set_wait_hook), and frame k+1 of a system is prepared (copy, Undistort, pyramid) behind the tracker launch of its
+ * frame k; a keyframe of one sequence holds back neither the other workers nor the worker's other sequences.
+ * poses_out [n][n_frames][12], status_out [n][n_frames][LDSO_SYS_ST_N]. */
 int ldso_gpu_batch_run(ldso_gpu_batch* batch, int n_frames, const float* const* images, int image_is_device, int sync_after,
                        double* poses_out, int* status_out);
 
