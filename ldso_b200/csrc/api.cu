@@ -88,6 +88,9 @@ static int create_impl(ldso_gpu_ctx* c) {
         LDSO_CUDA_OK(c, cudaMalloc(&T.row_cnt, (T.row_base[lv] + 1) * sizeof(int)));
         LDSO_CUDA_OK(c, cudaMalloc(&T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int)));
         LDSO_CUDA_OK(c, cudaMemset(T.pc_n_dev, 0, LDSO_MAX_LEVELS * sizeof(int)));
+        LDSO_CUDA_OK(c, cudaMallocHost((void**)&T.pc_n_pinned, LDSO_MAX_LEVELS * sizeof(int)));
+        memset(T.pc_n_pinned, 0, LDSO_MAX_LEVELS * sizeof(int));
+        LDSO_CUDA_OK(c, cudaEventCreateWithFlags(&T.ev_pc_n, cudaEventDisableTiming));
         int rc = ldso_gpu_tracker_make_k(c, t, cfg.fx, cfg.fy, cfg.cx, cfg.cy);
         if (rc) return rc;
     }
@@ -259,6 +262,8 @@ extern "C" void ldso_gpu_destroy(ldso_gpu_ctx* c) {
             cudaFree(c->trk[t].idepth[l]); cudaFree(c->trk[t].wsum[l]); cudaFree(c->trk[t].wsum_bak[l]); cudaFree(c->trk[t].pc[l]);
         }
         cudaFree(c->trk[t].row_cnt); cudaFree(c->trk[t].pc_n_dev);
+        if (c->trk[t].pc_n_pinned) cudaFreeHost(c->trk[t].pc_n_pinned);
+        if (c->trk[t].ev_pc_n) cudaEventDestroy(c->trk[t].ev_pc_n);
     }
     win_free(c);
     selector_free(c);
@@ -498,6 +503,7 @@ extern "C" int ldso_gpu_tracker_get_pc(ldso_gpu_ctx* c, int tracker, int lvl, in
     LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels && n);
     TrackerDev& T = c->trk[tracker];
+    if (trk_pc_n_sync(c, T)) return -1;
     int m = T.pc_n[lvl];
     *n = m;
     if (m == 0 || !(u || v || idepth || color)) return 0;

@@ -53,7 +53,10 @@ struct TrackerDev {
     float4* pc[LDSO_MAX_LEVELS];   // {u, v, idepth, color}  (pc_u, pc_v, pc_idepth, pc_color)
     int* row_cnt;                  // per-row valid counts / offsets for the ordered compaction (all levels)
     int* pc_n_dev;                 // [LDSO_MAX_LEVELS]
-    int pc_n[LDSO_MAX_LEVELS];     // host mirror
+    int pc_n[LDSO_MAX_LEVELS];     // host mirror (valid after trk_pc_n_sync)
+    int* pc_n_pinned = nullptr;    // [LDSO_MAX_LEVELS] pinned: setCoarseTrackingRef's counts arrive here without a wait
+    cudaEvent_t ev_pc_n = nullptr; // recorded behind that copy
+    bool pc_n_valid = true;
     int row_base[LDSO_MAX_LEVELS + 1];
     int ref_slot = -1;
     float ref_exposure = 1, ref_aff_a = 0, ref_aff_b = 0;
@@ -157,6 +160,10 @@ void ldso_cpu_relax();
 // contexts of the process launch the same kernel with their own sizes).  slot: one per kernel, see api.cu
 int ldso_raise_smem(ldso_gpu_ctx* c, const void* fn, size_t bytes, int slot);
 
+// Pinned staging ring of the ctx (window_api.cu): a block for a queued host-to-device copy on the TRACKING stream; the caller may
+// return without waiting (the ring is rewound only after a synchronisation of that stream)
+void* ldso_staging(ldso_gpu_ctx* c, size_t bytes);
+
 // every host<->device copy of the library goes through here so that the traffic is accounted
 inline cudaError_t ldso_copy(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
     if (kind == cudaMemcpyHostToDevice) c->h2d_bytes += (long long)bytes;
@@ -182,6 +189,8 @@ struct TrackEvalOut {
     double sums[48];   // 45 H entries (9x9 upper, row-major), E, flowT, flowRT
     int counts[4];     // numTermsInE, numSaturated, numTermsInWarped, flowNum
 };
+// the host mirror of the tracker's point counts: waits for the copy queued by k2_set_ref if it has not been read yet
+int trk_pc_n_sync(ldso_gpu_ctx* c, TrackerDev& T);
 int k34_track_all_launch(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const int* maxIt, const float* min_res_for_abort,
                          const ldso_sm::SE3& cur, float aff_a, float aff_b);
 int k34_track_all_wait(ldso_gpu_ctx* c, ldso_sm::SE3& cur, float& aff_a, float& aff_b, float last_residuals[5], float flow[3], int* status,

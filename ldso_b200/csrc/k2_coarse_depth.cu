@@ -207,10 +207,11 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
     TrackerDev& T = c->trk[tracker];
     cudaStream_t s = c->stream;
     const int L = c->levels;
-    // upload the point list through the pinned scratch buffer (4 arrays)
-    float* hp = c->scratch_host;
+    // upload the point list (4 arrays) through the ctx's staging ring: queued, nothing waits
     float* dp = (float*)c->img_dev;   // reuse of the staged-image buffer: n <= w*h/4 guaranteed by max_points check
     if (n > 0) {
+        float* hp = (float*)ldso_staging(c, 4 * (size_t)n * sizeof(float));
+        LDSO_REQUIRE(c, hp != nullptr);
         memcpy(hp, u, n * sizeof(float));
         memcpy(hp + n, v, n * sizeof(float));
         memcpy(hp + 2 * n, id, n * sizeof(float));
@@ -258,11 +259,20 @@ int k2_set_ref(ldso_gpu_ctx* c, int tracker, int ref_slot, int n, const float* u
     c->launches += 3;
     prof_end(c, s, LDSO_PROF_K2, n);
     LDSO_CUDA_OK(c, cudaGetLastError());
-    int* hn = (int*)c->trk_result_pinned;
-    LDSO_CUDA_OK(c, ldso_copy(c, hn, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
-    LDSO_CUDA_OK(c, ldso_stream_sync(s));
-    for (int l = 0; l < L; l++) T.pc_n[l] = hn[l];
+    // the point counts come back without a wait: the cluster tracker reads them on the device (LmLevel::n_dev), a host reader
+    // (calc_res, get_pc, the other LM modes) waits for the event first (trk_pc_n_sync)
+    LDSO_CUDA_OK(c, ldso_copy(c, T.pc_n_pinned, T.pc_n_dev, LDSO_MAX_LEVELS * sizeof(int), cudaMemcpyDeviceToHost, s));
+    LDSO_CUDA_OK(c, cudaEventRecord(T.ev_pc_n, s));
+    T.pc_n_valid = false;
     T.ref_slot = ref_slot;
     T.last_lvl = -1;
+    return 0;
+}
+
+int trk_pc_n_sync(ldso_gpu_ctx* c, TrackerDev& T) {
+    if (T.pc_n_valid) return 0;
+    LDSO_CUDA_OK(c, ldso_event_sync(T.ev_pc_n));
+    for (int l = 0; l < LDSO_MAX_LEVELS; l++) T.pc_n[l] = T.pc_n_pinned[l];
+    T.pc_n_valid = true;
     return 0;
 }

@@ -226,6 +226,7 @@ struct LmConst {                // the level being tracked; lives in shared memo
 struct LmLevel {
     float Ki[9], fx, fy, cx, cy;
     int w, h, n, maxIt;
+    const int* n_dev;           // if set: the level's point count is read on the device (the host has not waited for it)
     float minResForAbort;
     const float4 *pc, *img;
 };
@@ -590,7 +591,7 @@ k34_track_level_kernel(const LmAll A, float* __restrict__ partials, int* __restr
     if (threadIdx.x == 0) {
         const LmLevel& L = A.lv[st.lvl];
         for (int i = 0; i < 9; i++) k.Ki[i] = L.Ki[i];
-        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
+        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n_dev ? *L.n_dev : L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
         k.pc = L.pc; k.img = L.img;
         st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.lambda = 0.01f;
         for (int i = 0; i < 8; i++) st.inc[i] = 0;
@@ -1046,7 +1047,7 @@ k34_track_cluster_kernel(const LmAll A, double* __restrict__ mailbox, double seq
     if (threadIdx.x == 0) {
         const LmLevel& L = A.lv[st.lvl];
         for (int i = 0; i < 9; i++) k.Ki[i] = L.Ki[i];
-        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
+        k.fx = L.fx; k.fy = L.fy; k.cx = L.cx; k.cy = L.cy; k.w = L.w; k.h = L.h; k.n = L.n_dev ? *L.n_dev : L.n; k.lvl = st.lvl; k.maxIt = L.maxIt;
         k.pc = L.pc; k.img = L.img;
         st.cutoffRepeat = 1; st.phase = LM_FIRST; st.it = 0; st.lambda = 0.01f;
         for (int i = 0; i < 8; i++) st.inc[i] = 0;
@@ -1214,6 +1215,7 @@ static inline void from_to_vec_exposure(float exposureF, float exposureT, float 
 int k34_eval(ldso_gpu_ctx* c, int tracker, int lvl, const ldso_sm::SE3& refToNew, float aff_a, float aff_b, float cutoffTH,
              TrackEvalOut* out) {
     TrackerDev& T = c->trk[tracker];
+    if (trk_pc_n_sync(c, T)) return -1;
     TrkParams p;
     double Rd[9];
     refToNew.rotationMatrix(Rd);
@@ -1312,11 +1314,14 @@ int k34_track_all_launch(ldso_gpu_ctx* c, int tracker, int coarsest_lvl, const i
     k.dbg = c->cfg.reserved[0];
     A.coarsest = coarsest_lvl;
     int nmax = 1;
+    const bool n_on_device = c->cfg.tracker_lm_mode != 2;   // the cluster kernel's grid does not depend on the point counts
+    if (!n_on_device && trk_pc_n_sync(c, T)) return -1;
     for (int lvl = 0; lvl <= coarsest_lvl; lvl++) {
         LmLevel& L = A.lv[lvl];
         for (int i = 0; i < 9; i++) L.Ki[i] = T.Ki[lvl][i];
         L.fx = T.fx[lvl]; L.fy = T.fy[lvl]; L.cx = T.cx[lvl]; L.cy = T.cy[lvl];
-        L.w = T.w[lvl]; L.h = T.h[lvl]; L.n = T.pc_n[lvl]; L.maxIt = maxIt[lvl];
+        L.w = T.w[lvl]; L.h = T.h[lvl]; L.maxIt = maxIt[lvl];
+        L.n = n_on_device ? 0 : T.pc_n[lvl]; L.n_dev = n_on_device ? T.pc_n_dev + lvl : nullptr;
         L.minResForAbort = min_res_for_abort[lvl];
         L.pc = T.pc[lvl];
         L.img = c->frame[T.new_slot] + c->lvl_off[lvl];
@@ -1429,6 +1434,7 @@ extern "C" int ldso_gpu_tracker_calc_res_noalloc(ldso_gpu_ctx* c, int tracker, i
     LDSO_ENTER(c);
     LDSO_REQUIRE(c, tracker >= 0 && tracker < LDSO_NUM_TRACKERS && lvl >= 0 && lvl < c->levels);
     LDSO_REQUIRE(c, new_slot >= 0 && new_slot < c->cfg.n_frame_slots && ref_to_new && out6);
+    if (trk_pc_n_sync(c, c->trk[tracker])) return -1;   // (a wait, not an allocation)
     const TrackerDev& T = c->trk[tracker];
     LDSO_REQUIRE(c, T.ref_slot >= 0);
     const int n = T.pc_n[lvl];

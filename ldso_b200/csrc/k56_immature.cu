@@ -878,7 +878,8 @@ extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx,
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && n >= 0 && P->n + n <= P->cap && n_pool);
     LDSO_REQUIRE(c, host_idx >= 0 && host_idx < LDSO_MAX_WINDOW && (n == 0 || (u && v)));
     if (n > 0) {
-        float* st = (float*)P->pinned;
+        float* st = (float*)ldso_staging(c, 8 * (size_t)n);   // queued: nothing waits here
+        LDSO_REQUIRE(c, st != nullptr);
         memcpy(st, u, 4 * (size_t)n); memcpy(st + n, v, 4 * (size_t)n);
         LDSO_CUDA_OK(c, ldso_copy(c, P->cr, st, 8 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
         float eth = 8 * c->cfg.outlier_th;
@@ -889,7 +890,6 @@ extern "C" int ldso_gpu_immature_append(ldso_gpu_ctx* c, int slot, int host_idx,
         c->launches += 2;
         LDSO_CUDA_OK(c, cudaGetLastError());
         P->n += n;
-        LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
     }
     *n_pool = P->n;
     return 0;

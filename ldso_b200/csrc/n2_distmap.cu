@@ -536,13 +536,10 @@ extern "C" int ldso_gpu_immature_set_types(ldso_gpu_ctx* c, int first, int n, co
     if (!P) return -1;
     LDSO_REQUIRE(c, first >= 0 && n >= 0 && first + n <= P->n && (n == 0 || type));
     if (n == 0) return 0;
-    float* st = (float*)P->pinned;
+    float* st = (float*)ldso_staging(c, sizeof(float) * n);   // queued: nothing waits here; the copy goes straight into place
+    LDSO_REQUIRE(c, st != nullptr);
     memcpy(st, type, sizeof(float) * n);
-    LDSO_CUDA_OK(c, ldso_copy(c, P->cr, st, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
-    n2_types_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(n, P->cr, P->type + first);
-    c->launches++;
-    LDSO_CUDA_OK(c, cudaGetLastError());
-    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
+    LDSO_CUDA_OK(c, ldso_copy(c, P->type + first, st, sizeof(float) * n, cudaMemcpyHostToDevice, c->stream));
     return 0;
 }
 
@@ -555,7 +552,8 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
     LDSO_REQUIRE(c, n_points == 0 || (host && u && v && idepth));
     LDSO_REQUIRE(c, (size_t)n_points * 4 <= (size_t)22 * P->cap && sizeof(float) * (4 * (size_t)n_points + 16 * LDSO_MAX_WINDOW) <= P->pinned_bytes);
     for (int i = 0; i < n_points; i++) LDSO_REQUIRE(c, host[i] < n_hosts);
-    float* st = (float*)P->pinned;
+    float* st = (float*)ldso_staging(c, sizeof(float) * (4 * (size_t)n_points + 16 * LDSO_MAX_WINDOW));   // queued: nothing waits here
+    LDSO_REQUIRE(c, st != nullptr);
     int rc = put_tables(c, P, n_hosts, KRKi, Kt, nullptr, nullptr, st);
     if (rc) return rc;
     float* sp = st + 16 * LDSO_MAX_WINDOW;
@@ -573,9 +571,7 @@ extern "C" int ldso_gpu_distmap_make(ldso_gpu_ctx* c, int n_hosts, const float* 
     rc = launch_map(c, P, false);
     prof_end(c, c->stream, LDSO_PROF_N2, c->wG[1] * c->hG[1]);
     c->launches++;
-    if (rc) return rc;
-    LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));   // the pinned staging is reused by the next entry point
-    return 0;
+    return rc;
 }
 
 extern "C" int ldso_gpu_distmap_get(ldso_gpu_ctx* c, float* dist) {
@@ -608,7 +604,8 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     LDSO_REQUIRE(c, (action_out || P->n == 0) && c->levels >= 2);
     counts_out[0] = counts_out[1] = 0;
     if (P->n == 0) return 0;
-    float* st = (float*)P->pinned;
+    float* st = (float*)ldso_staging(c, sizeof(float) * 16 * LDSO_MAX_WINDOW);
+    LDSO_REQUIRE(c, st != nullptr);
     if (P->map_stale) {    // a second walk on the same map: it starts from the map the first walk left
         const int rcm = launch_map(c, P, true);
         if (rcm) return rcm;
@@ -646,9 +643,10 @@ extern "C" int ldso_gpu_immature_select_activation(ldso_gpu_ctx* c, int n_hosts,
     unsigned char* sa = (unsigned char*)P->pinned + 4096;
     LDSO_REQUIRE(c, (size_t)P->n + 4096 <= P->pinned_bytes);
     LDSO_CUDA_OK(c, ldso_copy(c, sa, P->action, P->n, cudaMemcpyDeviceToHost, c->stream));
-    LDSO_CUDA_OK(c, ldso_copy(c, st, P->sel_cnt, 8, cudaMemcpyDeviceToHost, c->stream));
+    int* cnt_h = (int*)P->pinned;
+    LDSO_CUDA_OK(c, ldso_copy(c, cnt_h, P->sel_cnt, 8, cudaMemcpyDeviceToHost, c->stream));
     LDSO_CUDA_OK(c, ldso_stream_sync(c->stream));
     memcpy(action_out, sa, P->n);
-    counts_out[0] = ((int*)st)[0]; counts_out[1] = ((int*)st)[1];
+    counts_out[0] = cnt_h[0]; counts_out[1] = cnt_h[1];
     return 0;
 }

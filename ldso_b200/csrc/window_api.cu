@@ -11,17 +11,7 @@
 
 #define CPARS 4
 
-namespace {
-
-template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
-    LDSO_CUDA_OK(c, cudaMalloc((void**)p, n * sizeof(T)));
-    return 0;
-}
-
-// Pinned staging ring.  Uploads are queued: the host buffer is copied into the ring at the cursor and the H2D copy
-// is issued without waiting (the caller may reuse its buffer at once; kernels on the same stream are ordered behind
-// the copy).  The ring is only rewound after a stream synchronisation, so a window upload costs one sync at most.
-void* staging(ldso_gpu_ctx* c, size_t bytes) {
+void* ldso_staging(ldso_gpu_ctx* c, size_t bytes) {
     WindowDev& W = c->win;
     const size_t need = (bytes + 255) & ~(size_t)255;
     if (W.pinned_off + need > W.pinned_bytes) {
@@ -38,6 +28,19 @@ void* staging(ldso_gpu_ctx* c, size_t bytes) {
     W.pinned_off += need;
     return p;
 }
+
+
+namespace {
+
+template <class T> int dalloc(ldso_gpu_ctx* c, T** p, size_t n) {
+    LDSO_CUDA_OK(c, cudaMalloc((void**)p, n * sizeof(T)));
+    return 0;
+}
+
+// Pinned staging ring.  Uploads are queued: the host buffer is copied into the ring at the cursor and the H2D copy
+// is issued without waiting (the caller may reuse its buffer at once; kernels on the same stream are ordered behind
+// the copy).  The ring is only rewound after a stream synchronisation, so a window upload costs one sync at most.
+inline void* staging(ldso_gpu_ctx* c, size_t bytes) { return ldso_staging(c, bytes); }
 
 int upload(ldso_gpu_ctx* c, void* dst, const void* src, size_t bytes) {
     if (bytes == 0) return 0;
