@@ -416,8 +416,9 @@ static int select_pass(ldso_gpu_ctx* c, SelectorDev* S, int slot, int pot, float
 }
 
 // makeMaps with the map left on the device (S->map)
+// exact_count = false: *n_selected is an upper bound (the pixels the random thinning removes are not counted: no read-back)
 static int make_maps_device(ldso_gpu_ctx* c, int slot, float density, int recursions_left, float th_factor, int* potential_io,
-                            int* n_selected) {
+                            int* n_selected, bool exact_count = true) {
     LDSO_REQUIRE(c, slot >= 0 && slot < c->cfg.n_frame_slots && potential_io && n_selected);
     LDSO_REQUIRE(c, c->levels >= 3 && *potential_io >= 1);
     int rc = selector_init(c);
@@ -461,9 +462,11 @@ static int make_maps_device(ldso_gpu_ctx* c, int slot, float density, int recurs
         a2_thin_scan_kernel<<<1, 1024, 0, s>>>(S->row_cnt, h);
         a2_thin_apply_kernel<<<(h + 7) / 8, 256, 0, s>>>(S->map, w, h, S->row_cnt, S->rp, charTH, S->counts + 4);
         c->launches += 3;
-        LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
-        LDSO_CUDA_OK(c, ldso_stream_sync(s));
-        numHaveSub -= S->counts_pinned[4];
+        if (exact_count) {
+            LDSO_CUDA_OK(c, ldso_copy(c, S->counts_pinned, S->counts, 8 * sizeof(int), cudaMemcpyDeviceToHost, s));
+            LDSO_CUDA_OK(c, ldso_stream_sync(s));
+            numHaveSub -= S->counts_pinned[4];
+        }
     }
     *potential_io = ideal;
     *n_selected = numHaveSub;
@@ -495,7 +498,7 @@ extern "C" int ldso_gpu_select_points(ldso_gpu_ctx* c, int slot, float density, 
     LDSO_ENTER(c);
     LDSO_REQUIRE(c, u_out && v_out && type_out && n_points && border >= 0 && max_points >= 0);
     int nsel = 0;
-    int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, &nsel);
+    int rc = make_maps_device(c, slot, density, recursions_left, th_factor, potential_io, &nsel, false);   // the list below carries its own length
     if (rc) return rc;
     SelectorDev* S = (SelectorDev*)c->selector;
     cudaStream_t s = c->stream;
