@@ -213,3 +213,131 @@ def test_oracle_constructor_and_trace_match_the_numpy_witness(oracle):
             pts[i].update(status=int(t["status"][i]), idepth_min=t["idepth_min"][i], idepth_max=t["idepth_max"][i], quality=t["quality"][i])
     assert GOOD in seen and len(seen) >= 3      # several exits of traceOn were exercised (OOB / OUTLIER / SKIPPED / BADCONDITION)
     ctx.close()
+
+
+# ---- K6, second half: FullSystem::optimizeImmaturePoint (src/frontend/FullSystem.cc:1035-1155) over
+# ImmaturePoint::linearizeResidual (src/internal/ImmaturePoint.cc:319-389), projectPoint / derive_idepth
+# (include/internal/ResidualProjections.h:12-92), scalar float32 -------------------------------------------------------------
+IN, ST_OOB, ST_OUTLIER = 0, 1, 2                      # ResState (include/internal/Residuals.h)
+MIN_IDEPTH_H_ACT, GN_ITS_ACT = F(100), 3              # src/Setting.cc:25, :47
+
+
+def linearize_residual(P, T, slack, tmp, Hdd, bd, idepth):
+    """-> (energy, Hdd, bd); tmp = [state, energy, new_state, new_energy] of this target, updated in place"""
+    if tmp[0] == ST_OOB:
+        tmp[2] = ST_OOB
+        return tmp[1], Hdd, bd
+    R, t, aff, dI, fx, fy, cx, cy, fxi, fyi, w, h = T
+    energy = F(0)
+    for idx in range(8):
+        dx, dy = int(PATTERN[idx][0]), int(PATTERN[idx][1])
+        k0, k1 = F(F(P["u"] + dx - cx) * fxi), F(F(P["v"] + dy - cy) * fyi)
+        ptp = [F(F(F(R[r, 0] * k0) + F(R[r, 1] * k1)) + F(R[r, 2] * F(1))) + F(t[r] * idepth) for r in range(3)]
+        ptp = [F(x) for x in ptp]
+        drescale = F(F(1) / ptp[2])
+        if not (drescale > 0):
+            tmp[2] = ST_OOB
+            return tmp[1], Hdd, bd
+        u, v = F(ptp[0] * drescale), F(ptp[1] * drescale)
+        Ku, Kv = F(F(u * fx) + cx), F(F(v * fy) + cy)
+        if not (Ku > F(1.1) and Kv > F(1.1) and Ku < w - 3 and Kv < h - 3):
+            tmp[2] = ST_OOB
+            return tmp[1], Hdd, bd
+        hit = lerp3(dI, w, np.array([Ku], F), np.array([Kv], F))[0]
+        if not np.isfinite(hit[0]):
+            tmp[2] = ST_OOB
+            return tmp[1], Hdd, bd
+        residual = F(hit[0] - F(F(aff[0] * P["color"][idx]) + aff[1]))
+        hw = F(1) if abs(residual) < HUBER_TH else F(HUBER_TH / abs(residual))
+        wgt = P["weights"][idx]
+        energy = F(energy + F(F(F(F(F(wgt * wgt) * hw) * residual) * residual) * F(F(2) - hw)))
+        dxi, dyi = F(hit[1] * fx), F(hit[2] * fy)
+        d_idepth = F(F(F(dxi * drescale) * F(t[0] - F(t[2] * u))) + F(F(dyi * drescale) * F(t[1] - F(t[2] * v))))   # * SCALE_IDEPTH = 1
+        hw = F(hw * F(wgt * wgt))
+        Hdd = F(Hdd + F(F(hw * d_idepth) * d_idepth))
+        bd = F(bd + F(F(hw * residual) * d_idepth))
+    lim = F(P["energyTH"] * F(slack))
+    if energy > lim:
+        energy = lim
+        tmp[2] = ST_OUTLIER
+    else:
+        tmp[2] = IN
+    tmp[3] = energy
+    return energy, Hdd, bd
+
+
+def optimize_immature_point(P, host, targets, min_obs):
+    """-> (idepth or None, final residual states per frame (-1 for the host))"""
+    n = len(targets)
+    tmp = {f: [IN, F(0), ST_OUTLIER, F(0)] for f in range(n) if f != host}
+    lastE = lastH = lastb = F(0)
+    cur = F(F(P["idepth_max"] + P["idepth_min"]) * F(0.5))
+    for f in tmp:
+        e, lastH, lastb = linearize_residual(P, targets[f], 1000, tmp[f], lastH, lastb, cur)
+        lastE = F(lastE + e)
+        tmp[f][0], tmp[f][1] = tmp[f][2], tmp[f][3]
+    if not np.isfinite(lastE) or lastH < MIN_IDEPTH_H_ACT:
+        return None, None
+    lam = F(0.1)
+    for it in range(GN_ITS_ACT):
+        H = F(lastH * F(F(1) + lam))
+        step = F(np.float64(1.0) / np.float64(H) * np.float64(lastb))
+        new_id = F(cur - step)
+        newH = newb = newE = F(0)
+        for f in tmp:
+            e, newH, newb = linearize_residual(P, targets[f], 1, tmp[f], newH, newb, new_id)
+            newE = F(newE + e)
+        if not np.isfinite(lastE) or newH < MIN_IDEPTH_H_ACT:
+            return None, None
+        if newE < lastE:
+            cur, lastH, lastb, lastE = new_id, newH, newb, newE
+            for f in tmp:
+                tmp[f][0], tmp[f][1] = tmp[f][2], tmp[f][3]
+            lam = F(lam * F(0.5))
+        else:
+            lam = F(lam * F(5))
+        if abs(step) < np.float64(0.0001) * np.float64(cur):
+            break
+    if not np.isfinite(cur):
+        return None, None
+    states = [-1 if f == host else tmp[f][0] for f in range(n)]
+    if sum(1 for s in states if s == IN) < min_obs:
+        return None, states
+    return cur, states
+
+
+def test_oracle_activation_matches_the_numpy_witness(oracle):
+    from ldso_b200 import window_host as wh
+    S = util.immature_scene("small", pts_per_host=90)
+    c = S["calib"]
+    w, h = c["w"], c["h"]
+    ctx = util.make_ctx(oracle, "small", n_frame_slots=8)
+    res = util.run_immature(ctx, S, activate=True)
+    nf = len(S["frames"])
+    dIs = [ctx.download(i, 0, 0).reshape(-1, 3).astype(F) for i in range(nf)]
+    pc = wh.precalc_table(S["w2c"], S["w2c"], (c["fx"], c["fy"], c["cx"], c["cy"]), [(0.0, 0.0)] * nf, [(0.0, 0.0)] * nf, [1.0] * nf)
+    fx, fy, cx, cy = F(c["fx"]), F(c["fy"]), F(c["cx"]), F(c["cy"])
+    fxi, fyi = F(F(1) / fx), F(F(1) / fy)
+    last = res["traces"][-1]
+    idepth_o, ok_o, st_o = res["act"]
+    cand = res["cand"]
+    assert len(cand) > 60
+    n_ok = n_equal = 0
+    for q, pt in enumerate(cand):
+        host = int(S["host"][pt])
+        P = dict(u=F(S["u"][pt]), v=F(S["v"][pt]), color=res["color"][pt], weights=res["weights"][pt], energyTH=res["energy_th"][pt],
+                 idepth_min=last["idepth_min"][pt], idepth_max=last["idepth_max"][pt])
+        targets = []
+        for f in range(nf):
+            e = pc[host + nf * f]
+            targets.append((e[27:36].reshape(3, 3), e[36:39], e[24:26], dIs[f], fx, fy, cx, cy, fxi, fyi, w, h))
+        idp, states = optimize_immature_point(P, host, targets, 1)
+        if ok_o[q]:
+            n_ok += 1
+            assert idp is not None and states == st_o[q].tolist(), (q, states, st_o[q])
+            assert idp == idepth_o[q] or abs(idp - idepth_o[q]) <= 2e-6 * abs(idepth_o[q]), (q, idp, idepth_o[q])
+            n_equal += idp == idepth_o[q]
+        else:
+            assert idp is None, (q, idp)
+    assert n_ok > 40 and n_equal > 0.95 * n_ok, (n_ok, n_equal)
+    ctx.close()
