@@ -305,7 +305,8 @@ int ldso_gpu_init_get_points(ldso_gpu_ctx* ctx, int lvl, int* n, float* u, float
                              unsigned char* is_good, float* my_type, float* last_hessian, float* energy);
 /* neighbours [n][10] and parent [n] of level lvl (makeNN) */
 int ldso_gpu_init_get_graph(ldso_gpu_ctx* ctx, int lvl, int* neighbours, int* parent);
-/* one calcResAndGS (:186-342) at level lvl for the given refToNew / affine, on the current point state: H, Hsc 8x8 and
+/* resetPoints(lvl) (:739-761) + one calcResAndGS (:186-342) at level lvl for the given refToNew / affine, on the current point
+ * state (as trackFrame starts a level, :84-85): H, Hsc 8x8 and
  * b, bsc as floats, res[3] = {energy, alphaEnergy, num}.  For parity tests of the per-point kernels. */
 int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* ctx, int slot, int lvl, const double ref_to_new[12], float aff_a, float aff_b,
                                   float H[64], float b[8], float Hsc[64], float bsc[8], float res[3]);

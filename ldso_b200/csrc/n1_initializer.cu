@@ -944,7 +944,9 @@ extern "C" int ldso_gpu_init_calc_res_and_gs(ldso_gpu_ctx* c, int slot, int lvl,
     I->new_slot = slot;
     I->alphaK = 2.5f * 2.5f; I->alphaW = 150 * 150; I->regWeight = 0.8f; I->couplingWeight = 1;
     GS g;
-    int rc = calc_res_and_gs(c, I, lvl, SE3::fromRt(ref_to_new), aff_a, aff_b, &g);
+    int rc = reset_points(c, I, lvl);        // trackFrame's resetPoints(lvl) (:84): idepth_new = idepth (setFirst leaves it unset)
+    if (rc) return rc;
+    rc = calc_res_and_gs(c, I, lvl, SE3::fromRt(ref_to_new), aff_a, aff_b, &g);
     if (rc) return rc;
     memcpy(H, g.H, sizeof(g.H)); memcpy(b, g.b, sizeof(g.b)); memcpy(Hsc, g.Hsc, sizeof(g.Hsc)); memcpy(bsc, g.bsc, sizeof(g.bsc));
     memcpy(res, g.res, sizeof(g.res));

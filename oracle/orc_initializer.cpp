@@ -681,6 +681,7 @@ extern "C" int orc_init_calc_res_and_gs(orc_ctx* c, int slot, int lvl, const dou
     if (I->first_slot < 0 || lvl < 0 || lvl >= I->levels) return -2;
     I->new_slot = slot;
     I->alphaK = 2.5f * 2.5f; I->alphaW = 150 * 150; I->regWeight = 0.8f; I->couplingWeight = 1;
+    resetPoints(I, lvl);                     // trackFrame's resetPoints(lvl) (:84): idepth_new = idepth (setFirst leaves it unset)
     calcResAndGS(c, I, lvl, H, b, Hsc, bsc, SE3::fromRt(ref_to_new), aff_a, aff_b, res);
     return 0;
 }

@@ -117,6 +117,7 @@ def test_gpu_calc_res_and_gs_matches_oracle(gpu, oracle, calib):
         for x, y in zip(a[:4], b[:4]):
             assert util.rel_err(x, y) < 1e-4
         assert np.allclose(a[4], b[4], rtol=1e-4)
+        assert b[4][0] > 0 and np.abs(b[2]).max() > 0      # points took part: a photometric energy and a Schur complement exist
     g.close(); o.close()
 
 
