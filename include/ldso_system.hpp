@@ -1913,6 +1913,8 @@ private:
         ucontext_t sched;
         std::vector<Fiber> fib;
         Fiber* cur = nullptr;
+        unsigned long long resumed_at = 0;      // time-stamp counter when the current fiber was resumed
+        int idle_polls = 0;                     // consecutive resumes that only polled (no host work between resume and yield)
     };
     static Fiber*& current_fiber() { static thread_local Fiber* f = nullptr; return f; }
     static void fiber_entry() {
@@ -1922,7 +1924,11 @@ private:
     }
     static void fiber_yield(void* arg) {                   // the library's wait hook
         Worker* w = (Worker*)arg;
-        if (w->cur) swapcontext(&w->cur->uc, &w->sched);
+        if (!w->cur) return;
+        // a fiber that yields again within ~1 us of being resumed has only looked at its flag
+        if (__builtin_ia32_rdtsc() - w->resumed_at < 3000) w->idle_polls++;
+        else w->idle_polls = 0;
+        swapcontext(&w->cur->uc, &w->sched);
     }
     // all frames of one sequence: begin (makeImages + the tracker launch, nothing waits), prepare the next frame behind it, end
     void run_job(size_t i) {
@@ -1981,9 +1987,16 @@ private:
                         if (f.done) continue;
                         w.cur = &f;
                         current_fiber() = &f;
+                        w.resumed_at = __builtin_ia32_rdtsc();
                         swapcontext(&w.sched, &f.uc);      // runs the sequence until its next wait (or its end: uc_link)
                         w.cur = nullptr;
-                        if (f.done) left--;
+                        if (f.done) { left--; w.idle_polls = 0; }
+                        // every live sequence of this worker is waiting for the device: ease off for ~1 us instead of hammering the
+                        // flags (the core's other hardware thread and the memory system belong to workers that have work)
+                        if (w.idle_polls >= (int)left && left > 0) {
+                            for (int i = 0; i < 32; i++) __builtin_ia32_pause();
+                            w.idle_polls = 0;
+                        }
                     }
                 }
                 Api::set_wait_hook(nullptr, nullptr);
