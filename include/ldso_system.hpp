@@ -1947,6 +1947,7 @@ private:
     void loop(int t, int T) {
         long long seen = 0;
         bool bound = false;
+        Worker w;                                   // the fibers' stacks live as long as the worker: allocated once
         for (;;) {
             {
                 std::unique_lock<std::mutex> lk(mu);
@@ -1968,12 +1969,12 @@ private:
             if (own.size() <= 1 || !fibers) {
                 for (size_t i : own) run_job(i);
             } else {
-                Worker w;
-                w.fib.resize(own.size());
+                if (w.fib.size() != own.size()) w.fib = std::vector<Fiber>(own.size());   // (a worker's share never changes)
+                w.idle_polls = 0;
                 for (size_t k = 0; k < own.size(); k++) {
                     Fiber& f = w.fib[k];
                     f.runner = this; f.job = own[k]; f.done = false;
-                    f.stack.resize(kFiberStack);
+                    if (f.stack.size() != kFiberStack) f.stack.resize(kFiberStack);
                     getcontext(&f.uc);
                     f.uc.uc_stack.ss_sp = f.stack.data();
                     f.uc.uc_stack.ss_size = f.stack.size();
