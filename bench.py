@@ -438,6 +438,15 @@ def main():
         kernels[name] = {"launches": int(n), "total_ms": ms, "ms_per_frame": ms / steps, "avg_us": 1e3 * ms / n, "units_per_launch": units / n,
                          "unit": unit, "bytes_per_unit": BYTES_PER_UNIT[key], "achieved_gbs": gbs, "frac": gbs / peak}
     top = max(kernels, key=lambda k: kernels[k]["total_ms"])
+    # evaluations per second of kernel time, tracker and window BA apart (one sequence)
+    evals = {}
+    trk, k7, k8 = (kernels.get(k) for k in ("k34_track_cluster_kernel", "k7_linearize_kernel", "k8_top_kernel"))
+    if trk and trk["total_ms"] > 0:
+        evals["tracker_point_evals_per_s"] = trk["units_per_launch"] * trk["launches"] / (trk["total_ms"] * 1e-3)
+    if k7 and k8 and k7["total_ms"] > 0:
+        # a BA evaluation = one residual through K7 + its K8 contribution: K7's residuals over K7's time plus K8's time per residual
+        per_res = k7["total_ms"] / (k7["units_per_launch"] * k7["launches"]) + k8["total_ms"] / (k8["units_per_launch"] * k8["launches"])
+        evals["ba_residual_evals_per_s"] = 1e3 / per_res
     total_frames = S * world * steps
     line = dict(base, value=total_frames / T_dev, ms_per_step=1e3 * T_dev / steps, host=host,
                 e2e={"value": total_frames / T_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d / steps, "d2h_bytes_per_step": d2h / steps},
@@ -456,7 +465,7 @@ def main():
                           "note": "dominant kernel by summed launch time over %d steady-state frames of one sequence (%d keyframes); "
                                   "single-sequence launches are latency-bound (L2-resident working set, DESIGN.md section 4); "
                                   "bandwidth-bound figures: roofline_batched_window" % (steps, prof_kf)},
-                kernels=kernels, steady_state=st_dev, steady_state_e2e=st_e2e, per_rank=per_rank, single_sequence=single)
+                kernels=kernels, evals_per_s=evals, steady_state=st_dev, steady_state_e2e=st_e2e, per_rank=per_rank, single_sequence=single)
     if args.gpus == 1 and not args.no_window_roofline:
         sys.path.insert(0, os.path.join(ROOT, "profiles"))
         import kernel_bench

@@ -248,3 +248,54 @@ def test_oracle_system_raw8_input_equals_float_input(oracle):
 @pytest.mark.gpu
 def test_gpu_system_raw8_input_equals_float_input(gpu):
     _raw8_equals_float(gpu, False)
+
+
+def _lost_run(api, black=True):
+    """40 frames of the small sequence, then frames without any structure: no motion hypothesis tracks, the achieved residual
+    stays NaN and FullSystem::addActiveFrame sets isLost (FullSystem.cc:144-150); every later frame returns at once (:86)"""
+    c, frames, poses = _seq("small", 40)
+    s = system.System(api, c, desired_point_density=600, desired_immature_density=500)
+    sts = [s.add_frame(f)[0] for f in frames]
+    assert sts[-1]["initialized"] and not sts[-1]["lost"]
+    n_before = (len(s.trajectory()[0]), s.window())
+    flat = np.zeros_like(frames[0]) if black else np.full_like(frames[0], 255.0)
+    after = []
+    for k in range(3):
+        after.append(s.add_frame(flat if k < 2 else frames[-1])[0])      # even a good frame does not bring a lost system back
+    return s, sts, after, n_before
+
+
+def test_oracle_system_goes_lost_on_a_structureless_frame_and_stays_lost(oracle):
+    for black in (True, False):
+        s, sts, after, n_before = _lost_run(oracle, black)
+        assert [a["lost"] for a in after] == [1, 1, 1]
+        assert not any(a["keyframe"] for a in after)
+        # the frame that lost the system is in the history (it was tracked, :142), the later ones never enter (:86-87)
+        assert len(s.trajectory()[0]) == n_before[0] + 1
+        assert s.window() == n_before[1]                     # no keyframe was made of it: the window is what it was
+        s.close()
+
+
+@pytest.mark.gpu
+def test_gpu_system_goes_lost_like_the_oracle(gpu, oracle):
+    sg, stg, ag, ng = _lost_run(gpu)
+    so, sto, ao, no = _lost_run(oracle)
+    assert [a["lost"] for a in ag] == [a["lost"] for a in ao] == [1, 1, 1]
+    assert ng == no and len(sg.trajectory()[0]) == len(so.trajectory()[0]) == no[0] + 1
+    assert sg.window() == so.window() == no[1]
+
+
+def test_oracle_system_flags_a_failed_initialisation(oracle):
+    """makeKeyFrame's tests on the RMSE of keyframes 2, 3 and 4 (FullSystem.cc:584-601: > 20 / 13 / 9 times
+    benchmark_initializerSlackFactor): with the slack turned down every window fails them, with the default none does;
+    the caller resets on initFailed (examples/run_dso_tum_mono.cc), the system itself carries on"""
+    c, frames, poses = _seq("small", 45)
+    s, sts, kfs = system.run(oracle, c, frames, desired_point_density=600, desired_immature_density=500, initializer_slack_factor=1e-3)
+    kf_frames = [k["frame"] for k in kfs]
+    assert len(kf_frames) >= 2
+    flagged = [st["frame_id"] for st in sts if st["init_failed"]]
+    assert flagged and flagged[0] == kf_frames[1]                    # the first keyframe after the initializer's is keyframe 2
+    assert all(st["init_failed"] for st in sts if st["frame_id"] >= kf_frames[1]) and not sts[-1]["lost"]
+    s2, sts2, kfs2 = system.run(oracle, c, frames, desired_point_density=600, desired_immature_density=500)
+    assert not any(st["init_failed"] for st in sts2)
+    assert [k["frame"] for k in kfs2] == kf_frames                   # the flag changes nothing else
