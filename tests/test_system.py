@@ -299,3 +299,36 @@ def test_oracle_system_flags_a_failed_initialisation(oracle):
     s2, sts2, kfs2 = system.run(oracle, c, frames, desired_point_density=600, desired_immature_density=500)
     assert not any(st["init_failed"] for st in sts2)
     assert [k["frame"] for k in kfs2] == kf_frames                   # the flag changes nothing else
+
+
+def _dimmed(frames, depth, start=20, rate=0.1):
+    """the same sequence through an auto-exposure that is not reported (exposure_time stays 1): after the bootstrap the image is
+    dimmed by up to `depth`, so the affine brightness pair (a, b) of the tracker and of the window has to absorb it"""
+    gain = [1.0 - (depth * abs(np.sin(rate * (k - start))) if k > start else 0.0) for k in range(len(frames))]
+    return [np.floor(f * g).astype(np.float32) for f, g in zip(frames, gain)]
+
+
+def test_oracle_system_follows_a_brightness_change_with_its_affine_parameters(oracle):
+    c, frames, poses = _seq("small", 60)
+    kw = dict(desired_point_density=600, desired_immature_density=500)
+    for depth in (0.25, 0.4):
+        s, sts, kfs = system.run(oracle, c, _dimmed(frames, depth), **kw)
+        assert not sts[-1]["lost"]
+        ate, scale, path, ids, _ = _ate(s, poses)
+        assert ate < 0.01 * path, (depth, ate, path)     # as good as on the constant-brightness sequence (0.5 % of the path)
+        s.close()
+
+
+@pytest.mark.gpu
+def test_gpu_system_follows_a_brightness_change_like_the_oracle(gpu, oracle):
+    c, frames, poses = _seq("small", 60)
+    kw = dict(desired_point_density=600, desired_immature_density=500)
+    fr = _dimmed(frames, 0.4)
+    sg, stg, kg = system.run(gpu, c, fr, **kw)
+    so, sto, ko = system.run(oracle, c, fr, **kw)
+    assert not stg[-1]["lost"] and not sto[-1]["lost"]
+    ag, _, path, ids_g, cen_g = _ate(sg, poses)
+    ao, _, _, ids_o, cen_o = _ate(so, poses)
+    assert np.array_equal(ids_g, ids_o)
+    assert ag < 0.01 * path and ao < 0.01 * path and abs(ag - ao) < 0.005 * path, (ag, ao, path)
+    assert kg[0]["frame"] == ko[0]["frame"]              # later keyframes sit on the brightness term's threshold: not compared
