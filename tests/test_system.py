@@ -332,3 +332,39 @@ def test_gpu_system_follows_a_brightness_change_like_the_oracle(gpu, oracle):
     assert np.array_equal(ids_g, ids_o)
     assert ag < 0.01 * path and ao < 0.01 * path and abs(ag - ao) < 0.005 * path, (ag, ao, path)
     assert kg[0]["frame"] == ko[0]["frame"]              # later keyframes sit on the brightness term's threshold: not compared
+
+
+def _exposure_run(api, c, frames, reported):
+    s = system.System(api, c, desired_point_density=600, desired_immature_density=500)
+    kfs, st = [], None
+    for k, f in enumerate(frames):
+        g = 1 - 0.3 * abs(np.sin(0.15 * k))              # the shutter closes by up to 30 %, from the first frame on
+        st, _ = s.add_frame(np.floor(f * g).astype(np.float32), exposure=g if reported else 1.0)
+        if st["keyframe"]:
+            kfs.append(k)
+    return s, st, kfs
+
+
+def test_oracle_system_uses_the_reported_exposure_time(oracle):
+    """ImageAndExposure::exposure_time -> fh->ab_exposure -> AffLight::fromToVecExposure everywhere (tracker, precalc, adjoints,
+    initializer): with the exposure reported the changing brightness costs nothing, bootstrap included; unreported, the
+    bootstrap's own brightness estimate is dropped by the fork (initializeFromInitializer ignores thisToNext_aff) and the first
+    window never recovers"""
+    c, frames, poses = _seq("small", 60)
+    s, st, kfs = _exposure_run(oracle, c, frames, True)
+    ate, _, path, _, _ = _ate(s, poses)
+    assert not st["lost"] and ate < 0.01 * path and len(kfs) <= 6, (ate, path, kfs)
+    s2, st2, kfs2 = _exposure_run(oracle, c, frames, False)
+    ate2, _, path2, _, _ = _ate(s2, poses)
+    assert st2["lost"] or ate2 > 5 * ate or len(kfs2) > 3 * len(kfs)
+
+
+@pytest.mark.gpu
+def test_gpu_system_uses_the_reported_exposure_time(gpu, oracle):
+    c, frames, poses = _seq("small", 60)
+    sg, stg, kg = _exposure_run(gpu, c, frames, True)
+    so, sto, ko = _exposure_run(oracle, c, frames, True)
+    ag, _, path, ids_g, _ = _ate(sg, poses)
+    ao, _, _, ids_o, _ = _ate(so, poses)
+    assert not stg["lost"] and np.array_equal(ids_g, ids_o) and kg[0] == ko[0]
+    assert ag < 0.01 * path and abs(ag - ao) < 0.005 * path, (ag, ao, path)
