@@ -368,3 +368,24 @@ def test_gpu_system_uses_the_reported_exposure_time(gpu, oracle):
     ao, _, _, ids_o, _ = _ate(so, poses)
     assert not stg["lost"] and np.array_equal(ids_g, ids_o) and kg[0] == ko[0]
     assert ag < 0.01 * path and abs(ag - ao) < 0.005 * path, (ag, ao, path)
+
+
+def test_oracle_batch_run_in_two_calls_reuses_its_workers(oracle):
+    """ldso_gpu_batch_run: all frames of a call handed over together (a worker prepares frame k+1 behind frame k and runs its
+    sequences on fibers whose stacks it keeps from call to call); two calls of 18 frames equal 36 single frames, on one worker
+    thread as on two"""
+    c = util.CALIB["small"]
+    kw = dict(desired_point_density=600, desired_immature_density=500)
+    seqs = [synth.make_sequence(1001 + i, 36, start=0, **c)[0] for i in range(3)]
+    alone = [system.run(oracle, c, fr, **kw)[0].centres()[1] for fr in seqs]
+    imgs = [[np.ascontiguousarray(f, np.float32) for f in fr] for fr in seqs]
+    for threads in (1, 2):
+        ss = [system.System(oracle, c, **kw) for _ in seqs]
+        b = system.Batch(ss, threads)
+        for lo in (0, 18):
+            st = b.run_ptrs([[im.ctypes.data for im in row[lo:lo + 18]] for row in imgs], sync_after=True)
+            assert st.shape[:2] == (3, 18) and not st[:, :, system.ST["lost"]].any()
+        assert st[:, -1, system.ST["initialized"]].all()
+        for i, s in enumerate(ss):
+            assert np.array_equal(s.centres()[1], alone[i])
+        b.close()
