@@ -67,9 +67,7 @@ static int create_impl(ldso_gpu_ctx* c) {
     LDSO_CUDA_OK(c, cudaMalloc(&c->img_dev, npx0 * sizeof(float)));
     LDSO_CUDA_OK(c, cudaMallocHost(&c->img_pinned, npx0 * sizeof(float)));
     LDSO_CUDA_OK(c, cudaMallocHost(&c->scratch_host, npx0 * sizeof(float4)));
-    // B[256] followed by one ticket word per frame slot (k1_pyramid.cu: the CTA that finishes last patches the wrap columns)
-    LDSO_CUDA_OK(c, cudaMalloc(&c->gammaB_dev, 256 * sizeof(float) + cfg.n_frame_slots * sizeof(unsigned int)));
-    LDSO_CUDA_OK(c, cudaMemset(c->gammaB_dev + 256, 0, cfg.n_frame_slots * sizeof(unsigned int)));
+    LDSO_CUDA_OK(c, cudaMalloc(&c->gammaB_dev, 256 * sizeof(float)));
     float B[256];
     for (int i = 0; i < 256; i++) B[i] = (float)i;
     LDSO_CUDA_OK(c, cudaMemcpy(c->gammaB_dev, B, sizeof(B), cudaMemcpyHostToDevice));

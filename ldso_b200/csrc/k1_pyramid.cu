@@ -9,10 +9,8 @@
 // hit L2), output is written once: 4 + 16*sum_l(w_l h_l)/(w h) ~ 25.3 B per level-0 pixel.
 //
 // The reference's gradient loop runs over the flat index range [w, w(h-1)) (FrameHessian.cc:95), so
-// column 0 reads the previous row's last pixel and column w-1 the next row's first one.  Those pixels
-// belong to other tiles, so the two columns are patched at the end of the SAME launch by the CTA that
-// finishes last (a ticket per frame slot, taken behind a __threadfence): it reads the I channel the
-// other CTAs wrote through L2 and rewrites dx and absSquaredGrad of the 2(h_l - 2) border pixels per level.
+// column 0 reads the previous row's last pixel and column w-1 the next row's first one.  Those two
+// columns are patched by k1_wrap_columns_kernel, which reads the I channel written by the tile pass.
 #include "ctx.h"
 
 namespace {
@@ -47,11 +45,9 @@ __device__ __forceinline__ float abs_sq_grad(float I, float dx, float dy, const 
 // L = number of pyramid levels, a template parameter so that the shared-memory tile geometry is a compile-time constant:
 // the fill / box / store loops unroll completely and all global loads of a thread are in flight at once
 template <int L>
-__global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __restrict__ img, float4* out,
-                                                                 const float* __restrict__ B, const K1Params p,
-                                                                 unsigned int* ticket) {
+__global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __restrict__ img, float4* __restrict__ out,
+                                                                 const float* __restrict__ B, const K1Params p) {
     extern __shared__ float sm[];
-    __shared__ bool s_last;
     const int tid = threadIdx.x;
     const int X0 = blockIdx.x * K1_TW, Y0 = blockIdx.y * K1_TH;
     int soff[LDSO_MAX_LEVELS], sw[LDSO_MAX_LEVELS], sh[LDSO_MAX_LEVELS];
@@ -131,34 +127,29 @@ __global__ void __launch_bounds__(K1_THREADS) k1_pyramid_kernel(const float* __r
             o[(size_t)gy * wl + gx] = make_float4(I, dx, dy, ag);
         }
     }
-    // columns 0 and w-1 of rows 1..h-2: neighbours wrap to the adjacent row (flat-index loop of the reference).  The last CTA
-    // of the grid patches them: every CTA publishes its texels (fence), then takes a ticket.
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const unsigned int total = gridDim.x * gridDim.y;
-        s_last = atomicAdd(ticket, 1u) == total - 1;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-#pragma unroll
-    for (int l = 0; l < L; l++) {
-        const int wl = p.w[l], rows = p.h[l] - 2;
-        float4* o = out + p.off[l];
-        for (int i = tid; i < 2 * rows; i += K1_THREADS) {
-            const int y = 1 + (i >> 1);
-            const int x = (i & 1) ? wl - 1 : 0;
-            const size_t idx = (size_t)y * wl + x;
-            float4 t = __ldcg(o + idx);                      // L2: these texels were written by other CTAs of this launch
-            const float left = __ldcg(&o[idx - 1].x), right = __ldcg(&o[idx + 1].x);
-            const float dx = clamp_grad(__fmul_rn(0.5f, __fsub_rn(right, left)));
+}
+
+// columns 0 and w-1 of rows 1..h-2: neighbours wrap to the adjacent row (flat-index loop of the reference)
+__global__ void k1_wrap_columns_kernel(float4* __restrict__ out, const float* __restrict__ B, const K1Params p) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int l = 0; l < p.levels; l++) {
+        int rows = p.h[l] - 2;
+        if (i < 2 * rows) {
+            int y = 1 + (i >> 1);
+            int wl = p.w[l];
+            int x = (i & 1) ? wl - 1 : 0;
+            float4* o = out + p.off[l];
+            size_t idx = (size_t)y * wl + x;
+            float4 t = o[idx];
+            float left = o[idx - 1].x, right = o[idx + 1].x;
+            float dx = clamp_grad(__fmul_rn(0.5f, __fsub_rn(right, left)));
             t.y = dx;
             t.w = abs_sq_grad(t.x, dx, t.z, B, p.gammaWeights);
-            o[idx] = t;                                      // .x is rewritten with the value it has: a neighbour's read of it is unaffected
+            o[idx] = t;
+            return;
         }
+        i -= 2 * rows;
     }
-    if (tid == 0) *ticket = 0;                               // ready for the next launch on this slot (stream order)
 }
 
 }  // namespace
@@ -168,17 +159,17 @@ int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
     K1Params p;
     p.levels = c->levels;
     p.gammaWeights = c->cfg.gamma_weights_pixel_select;
-    int smem_floats = 0;
+    int smem_floats = 0, border = 0;
     for (int l = 0; l < c->levels; l++) {
         p.w[l] = c->wG[l];
         p.h[l] = c->hG[l];
         p.off[l] = (unsigned int)c->lvl_off[l];
         int hl = 1 << (c->levels - 1 - l);
         smem_floats += ((K1_TW >> l) + 2 * hl) * ((K1_TH >> l) + 2 * hl);
+        border += 2 * (c->hG[l] - 2);
     }
     dim3 grid((c->wG[0] + K1_TW - 1) / K1_TW, (c->hG[0] + K1_TH - 1) / K1_TH);
     const size_t smem = smem_floats * sizeof(float);
-    unsigned int* ticket = reinterpret_cast<unsigned int*>(c->gammaB_dev + 256) + slot;   // one per frame slot, zero between launches
     prof_begin(c, c->stream);
 #define K1_LAUNCH(LV)                                                                                                          \
     case LV: {                                                                                                                 \
@@ -186,15 +177,16 @@ int k1_make_images(ldso_gpu_ctx* c, int slot, const float* img_dev) {
             LDSO_CUDA_OK(c, cudaFuncSetAttribute(k1_pyramid_kernel<LV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));  \
             c->k1_attr_set = true;                                                                                             \
         }                                                                                                                      \
-        k1_pyramid_kernel<LV><<<grid, K1_THREADS, smem, c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p, ticket);     \
+        k1_pyramid_kernel<LV><<<grid, K1_THREADS, smem, c->stream>>>(img_dev, c->frame[slot], c->gammaB_dev, p);             \
     } break;
     switch (c->levels) {
         K1_LAUNCH(1) K1_LAUNCH(2) K1_LAUNCH(3) K1_LAUNCH(4) K1_LAUNCH(5) K1_LAUNCH(6)
         default: LDSO_REQUIRE(c, c->levels >= 1 && c->levels <= 6);
     }
 #undef K1_LAUNCH
+    k1_wrap_columns_kernel<<<(border + 127) / 128, 128, 0, c->stream>>>(c->frame[slot], c->gammaB_dev, p);
     prof_end(c, c->stream, LDSO_PROF_K1, 1);
-    c->launches += 1;
+    c->launches += 2;
     LDSO_CUDA_OK(c, cudaGetLastError());
     return 0;
 }
