@@ -90,12 +90,40 @@ def backend(api):
     return out
 
 
+def closed_loop(api):
+    """FullSystem::addActiveFrame over 60 frames of the 'small' sequence through the C++ orchestrator (include/ldso_system.hpp):
+    bootstrap, keyframes, activation, window optimisation.  Deterministic on the CPU oracle only (the GPU's atomic sums move
+    the last bits), so this part pins the oracle + orchestrator pair and is not in PARTS"""
+    from ldso_b200 import system
+    c = util.CALIB["small"]
+    frames, depths, poses = synth.make_sequence(1001, 60, start=0, stride=1, **c)
+    s, sts, kfs = system.run(api, c, frames, desired_point_density=600, desired_immature_density=500)
+    ids, tr, kf = s.trajectory()
+    out = dict(ids=ids.astype(np.int32), poses=tr, is_kf=kf.astype(np.uint8),
+               kf_frames=np.array([k["frame"] for k in kfs], np.int32),
+               kf_points=np.array([k["points"] for k in kfs], np.int32),
+               kf_residuals=np.array([k["residuals"] for k in kfs], np.int32),
+               kf_activated=np.array([k["activated"] for k in kfs], np.int32),
+               kf_rmse=np.array([k["rmse"] for k in kfs], np.float64),
+               window=np.array(s.window(), np.int32), cpu=np.array(cpu_model()))
+    s.close()
+    return out
+
+
+def cpu_model():
+    try:
+        return [l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name")][0]
+    except (OSError, IndexError):
+        return "unknown"
+
+
 PARTS = dict(frontend=frontend, selector=selector, immature=immature, backend=backend)
+CPU_PARTS = dict(closed_loop=closed_loop)
 
 if __name__ == "__main__":
     build.build_oracle()
     api = capi.Api(build.ORACLE_LIB, "orc_")
-    for name, fn in PARTS.items():
+    for name, fn in list(PARTS.items()) + list(CPU_PARTS.items()):
         d = fn(api)
         np.savez_compressed(os.path.join(OUT, name + ".npz"), **d)
         print(name, sum(v.nbytes for v in d.values()) // 1024, "KiB raw")

@@ -50,3 +50,16 @@ def test_oracle_reproduces_golden(oracle, part):
 @pytest.mark.parametrize("part", list(mg.PARTS))
 def test_gpu_reproduces_golden(gpu, part):
     check(mg.PARTS[part](gpu), np.load(os.path.join(HERE, part + ".npz")), exact_floats=True)
+
+
+def test_oracle_closed_loop_reproduces_golden(oracle):
+    """the orchestrator over the oracle on 60 frames: same keyframes, same counts, same trajectory as the committed run"""
+    gold = np.load(os.path.join(HERE, "closed_loop.npz"))
+    if str(gold["cpu"]) != mg.cpu_model():
+        # 60 frames of feedback: a last-bit difference of libm's CPU-specific variants can move a keyframe decision
+        pytest.skip("fixture generated on another CPU model (%s)" % gold["cpu"])
+    got = mg.closed_loop(oracle)
+    for k in ("ids", "is_kf", "kf_frames", "kf_points", "kf_residuals", "kf_activated", "window"):
+        assert np.array_equal(got[k], gold[k]), k
+    assert np.abs(got["poses"] - gold["poses"]).max() < 1e-9
+    assert np.abs(got["kf_rmse"] / gold["kf_rmse"] - 1).max() < 1e-6
