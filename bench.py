@@ -313,6 +313,14 @@ def cpu_arm(seeds, data, steps, warmup, threads_total):
     return times, st, workers, inner, march
 
 
+def cpu_single_sequence(seed, data, steps, warmup, cores):
+    """ONE sequence through the oracle with the reference's thread count (IndexThreadReduce: NUM_THREADS = 6 workers,
+    include/Settings.h:11): the CPU side of north_star's single-sequence frame rate"""
+    times, _, workers, inner, march = cpu_arm([seed], data, steps, warmup, min(cores, 6))
+    return {"value": steps / sum(times), "unit": "frames/s", "cores": workers * inner,
+            "sample": "%d steps of sequence %d after %d priming + %d warm-up frames, %d OpenMP threads" % (steps, seed, PRIME, warmup, inner)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -348,7 +356,8 @@ def main():
         cores = os.cpu_count() or 1
         times, st, workers, inner, march = cpu_arm(seeds, data, steps, warmup, cores)
         fps = len(seeds) * steps / sum(times)
-        print(json.dumps(dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps,
+        single = cpu_single_sequence(seeds[0], data, steps, warmup, cores)
+        print(json.dumps(dict(base, impl="reference", value=fps, ms_per_step=1e3 * sum(times) / steps, single_sequence=single,
                               cpu_baseline={"value": fps, "unit": "frames/s", "cores": workers * inner, "kind": "port",
                                             "sample": "%d steps x %d sequences after %d priming + %d warm-up frames each; oracle restatement "
                                                       "(g++ -O3 -march=%s -fopenmp, logging compiled out), %d sequence workers x %d "
@@ -483,7 +492,8 @@ def main():
                                 "sample": "%d steps x %d sequences (the same sequences and frames) after %d priming + %d warm-up frames each "
                                           "through the oracle (g++ -O3 -march=%s -fopenmp), %d sequence workers x %d OpenMP threads "
                                           "on a %d-core host" % (cs, S, PRIME, warmup, march, workers, inner, cores),
-                                "steady_state": cst}
+                                "steady_state": cst,
+                                "single_sequence": cpu_single_sequence(seeds[0], data, cs, warmup, cores)}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
